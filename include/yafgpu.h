@@ -1,0 +1,417 @@
+/* yafgpu.h — C ABI of the B200-native path-tracing hot path for libYafaRay.
+ *
+ * This is the drop-in boundary.  Everything a
+ * reference-side adaptor needs in order to replace the CPU hot path
+ *
+ *   Scene::update() accelerator build      /root/reference/src/common/scene.cc:788-831
+ *   SurfaceIntegrator::render()            /root/reference/include/integrator/integrator.h:73-85
+ *     = TiledIntegrator::render/renderPass /root/reference/src/integrator/integrator_tiled.cc:116-345
+ *   ImageFilm::addSample accumulation      /root/reference/src/common/imagefilm.cc:925-1015
+ *
+ * is exported here as plain C: POD structs, pointers and sizes only; no C++
+ * types, no exceptions, no torch types.  The caller keeps ownership of every
+ * pointer it passes in; the library copies what it needs before returning.
+ * Every function returns 0 on success and a non-zero yafgpu_status otherwise;
+ * yafgpu_last_error() gives the message.  There is NO CPU fallback: if no
+ * CUDA device is usable, yafgpu_create() fails.
+ *
+ * Descriptors are PARAMETER-level for cameras, lights, materials, film and
+ * integrator: the fields are the values the reference's factories read from
+ * their ParamMap (after defaults), cited per struct.  Derived constants (camera
+ * axes, light areas, CDFs, filter tables) are computed inside the library the
+ * way the reference constructors compute them.  Geometry is flattened: triangles
+ * in the reference's GLOBAL TRIANGLE ORDER (scene.cc:807-817: ascending object
+ * id, each mesh in addTriangle order), which is also the id space of every hit
+ * record this API returns.
+ */
+#ifndef YAFGPU_H
+#define YAFGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YAFGPU_ABI_VERSION 1
+
+typedef struct yafgpu_ctx yafgpu_ctx;
+
+typedef enum yafgpu_status
+{
+	YAFGPU_OK = 0,
+	YAFGPU_ERR_INVALID = 1,     /* bad argument / malformed descriptor */
+	YAFGPU_ERR_UNSUPPORTED = 2, /* feature of the reference not implemented on the device (refused, never approximated) */
+	YAFGPU_ERR_CUDA = 3,        /* CUDA runtime error */
+	YAFGPU_ERR_STATE = 4,       /* call order violated (e.g. render before upload) */
+	YAFGPU_ERR_NOMEM = 5
+} yafgpu_status;
+
+/* ---- geometry -------------------------------------------------------------------------- */
+
+/* Material::Visibility, /root/reference/include/material/material.h (NormalVisible, VisibleNoShadows,
+ * InvisibleShadowsOnly, Invisible) */
+enum { YAFGPU_VIS_NORMAL = 0, YAFGPU_VIS_NO_SHADOWS = 1, YAFGPU_VIS_SHADOW_ONLY = 2, YAFGPU_VIS_INVISIBLE = 3 };
+
+/* Flattened triangle soup.  Mirrors what TriangleObject holds per mesh
+ * (/root/reference/include/object_geom/object_geom_mesh.h:84-144), concatenated over meshes:
+ *   points   : vertex positions (3 floats each); when a mesh has orco the reference stores
+ *              position and orco interleaved (getVertex(pa+1) is the orco, triangle.cc:47-49) and so does this array
+ *   normals  : vertex normals after smoothing (3 floats each)
+ *   uv       : uv_values_ (2 floats each)
+ * Per triangle (n_tris entries, global order):
+ *   tri_vidx : 3 indices into points (pa_, pb_, pc_, already offset to the global array)
+ *   tri_nidx : 3 indices into normals, -1 = use geometric normal (na_, nb_, nc_; triangle.cc:38-40); may be NULL
+ *   tri_uvidx: 3 indices into uv, may be NULL (no mesh has uv)
+ *   tri_mat  : material index into yafgpu_scene_desc.materials
+ *   tri_obj  : index into objects
+ */
+typedef struct yafgpu_object
+{
+	int32_t has_orco;      /* TriangleObject::has_orco_ */
+	int32_t has_uv;        /* TriangleObject::has_uv_ (tri_uvidx valid for its triangles) */
+	int32_t smooth;        /* is_smooth_ || normals_exported_ (triangle.cc:36) */
+	int32_t light;         /* index of the light this object is tagged with (ObjectGeometric::setLight), -1 = none */
+	int32_t first_tri;     /* first global triangle id */
+	int32_t n_tris;
+	int32_t obj_id;        /* reference ObjId_t, informational */
+	int32_t pass_index;    /* obj_pass_index, informational */
+} yafgpu_object;
+
+typedef struct yafgpu_geometry
+{
+	const float *points;      size_t n_points;
+	const float *normals;     size_t n_normals;
+	const float *uv;          size_t n_uv;
+	const int32_t *tri_vidx;
+	const int32_t *tri_nidx;
+	const int32_t *tri_uvidx;
+	const int32_t *tri_mat;
+	const int32_t *tri_obj;
+	size_t n_tris;
+	const yafgpu_object *objects; size_t n_objects;
+} yafgpu_geometry;
+
+/* ---- materials ------------------------------------------------------------------------- */
+
+typedef enum yafgpu_material_type
+{
+	YAFGPU_MAT_SHINYDIFFUSE = 0,  /* "shinydiffusemat"  material_shiny_diffuse.cc:599-688 */
+	YAFGPU_MAT_GLOSSY = 1,        /* "glossy"           material_glossy.cc:407-480 */
+	YAFGPU_MAT_COATED_GLOSSY = 2, /* "coated_glossy"    material_coated_glossy.cc:465-545 */
+	YAFGPU_MAT_GLASS = 3,         /* "glass"            material_glass.cc:311-379 */
+	YAFGPU_MAT_ROUGH_GLASS = 4,   /* "rough_glass"      material_rough_glass.cc:322-401 */
+	YAFGPU_MAT_BLEND = 5,         /* "blend_mat"        material_blend.cc:464-518 */
+	YAFGPU_MAT_MIRROR = 6,        /* "mirror"           material_glass.cc (MirrorMaterial) */
+	YAFGPU_MAT_NULL = 7,          /* "null"             material_glass.cc (NullMaterial) */
+	YAFGPU_MAT_LIGHT = 8          /* "light_mat"        material_simple.cc:38-73 */
+} yafgpu_material_type;
+
+typedef struct yafgpu_mat_shinydiffuse
+{
+	float color[3];          /* "color" */
+	float mirror_color[3];   /* "mirror_color" */
+	float diffuse_reflect;   /* "diffuse_reflect" */
+	float specular_reflect;  /* "specular_reflect" (mirror strength) */
+	float transparency;      /* "transparency" */
+	float translucency;      /* "translucency" */
+	float emit;              /* "emit" */
+	float ior;               /* "IOR" (used only with fresnel_effect) */
+	int32_t fresnel_effect;  /* "fresnel_effect" */
+	float transmit_filter;   /* "transmit_filter" */
+	int32_t oren_nayar;      /* "diffuse_brdf" == "oren_nayar" */
+	float sigma;             /* "sigma" */
+} yafgpu_mat_shinydiffuse;
+
+typedef struct yafgpu_mat_glossy /* also the base of coated_glossy */
+{
+	float color[3];          /* "color" (glossy colour) */
+	float diffuse_color[3];  /* "diffuse_color" */
+	float mirror_color[3];   /* coated only: "mirror_color" */
+	float diffuse_reflect;   /* "diffuse_reflect" */
+	float glossy_reflect;    /* "glossy_reflect" */
+	float specular_reflect;  /* coated only: "specular_reflect" */
+	float exponent;          /* "exponent" */
+	float exp_u, exp_v;      /* "exp_u", "exp_v" */
+	float ior;               /* coated only: "IOR" */
+	int32_t as_diffuse;      /* "as_diffuse" */
+	int32_t anisotropic;     /* "anisotropic" */
+	int32_t oren_nayar;      /* "diffuse_brdf" == "Oren-Nayar" */
+	float sigma;             /* "sigma" */
+} yafgpu_mat_glossy;
+
+typedef struct yafgpu_mat_glass /* glass and rough_glass */
+{
+	float ior;               /* "IOR" */
+	float filter_color[3];   /* "filter_color" */
+	float transmit_filter;   /* "transmit_filter" */
+	float mirror_color[3];   /* "mirror_color" */
+	float dispersion_power;  /* "dispersion_power" */
+	int32_t fake_shadows;    /* "fake_shadows" */
+	float alpha;             /* rough_glass only: "alpha" */
+	int32_t has_absorption;  /* "absorption" given and < 1 in some channel */
+	float absorption[3];     /* "absorption" */
+	float absorption_dist;   /* "absorption_dist" */
+} yafgpu_mat_glass;
+
+typedef struct yafgpu_mat_blend
+{
+	int32_t material1;       /* index of "material1" */
+	int32_t material2;       /* index of "material2" */
+	float blend_value;       /* "blend_value" */
+} yafgpu_mat_blend;
+
+typedef struct yafgpu_mat_simple /* mirror: color*reflect; light_mat: color*power, double_sided */
+{
+	float color[3];
+	float strength;          /* mirror "reflect" / light_mat "power" */
+	int32_t double_sided;
+} yafgpu_mat_simple;
+
+typedef struct yafgpu_material
+{
+	int32_t type;                 /* yafgpu_material_type */
+	int32_t visibility;           /* "visibility" */
+	int32_t receive_shadows;      /* "receive_shadows" */
+	int32_t flat_material;        /* "flat_material" (shinydiffuse) */
+	int32_t additional_depth;     /* "additionaldepth" */
+	float transparent_bias_factor;            /* "transparentbias_factor" */
+	int32_t transparent_bias_multiply_raydepth; /* "transparentbias_multiply_raydepth" */
+	float sampling_factor;        /* "samplingfactor" */
+	int32_t mat_pass_index;       /* "mat_pass_index" */
+	int32_t reserved[3];
+	union
+	{
+		yafgpu_mat_shinydiffuse shinydiffuse;
+		yafgpu_mat_glossy glossy;
+		yafgpu_mat_glass glass;
+		yafgpu_mat_blend blend;
+		yafgpu_mat_simple simple;
+		float pad_[32];
+	} u;
+} yafgpu_material;
+
+/* ---- lights ---------------------------------------------------------------------------- */
+
+typedef enum yafgpu_light_type
+{
+	YAFGPU_LIGHT_POINT = 0,      /* "pointlight"  light_point.cc:101-133 */
+	YAFGPU_LIGHT_SUN = 1,        /* "sunlight"    light_sun.cc:95-125 */
+	YAFGPU_LIGHT_AREA = 2,       /* "arealight"   light_area.cc:174-213 */
+	YAFGPU_LIGHT_MESH = 3,       /* "meshlight"   light_meshlight.cc:228-263 */
+	YAFGPU_LIGHT_BACKGROUND = 4  /* "bglight"     light_background.cc:251-283 (created by a background with ibl=true) */
+} yafgpu_light_type;
+
+typedef struct yafgpu_light
+{
+	int32_t type;            /* yafgpu_light_type */
+	int32_t light_enabled;   /* "light_enabled" */
+	int32_t cast_shadows;    /* "cast_shadows" */
+	int32_t photon_only;     /* "photon_only" (such lights never illuminate; light_area.cc:69) */
+	int32_t samples;         /* "samples" (sun/area/mesh/bg) */
+	int32_t object;          /* area/mesh: index into yafgpu_geometry.objects of the "object" param, -1 = none */
+	int32_t double_sided;    /* mesh: "double_sided" */
+	int32_t abs_intersect;   /* bg: "abs_intersect" */
+	float color[3];          /* "color" */
+	float power;             /* "power" */
+	float from[3];           /* point: "from"; sun: "direction"; area: "corner" */
+	float point1[3];         /* area: "point1" */
+	float point2[3];         /* area: "point2" */
+	float angle;             /* sun: "angle" (degrees) */
+	float clamp_intersect;   /* bg: ibl_clamp_sampling */
+	int32_t shoot_caustic;   /* "with_caustic" (bg light: gates caustic-path background hits) */
+	int32_t shoot_diffuse;   /* "with_diffuse" */
+	int32_t reserved[2];
+} yafgpu_light;
+
+/* ---- camera ---------------------------------------------------------------------------- */
+
+typedef enum yafgpu_camera_type { YAFGPU_CAM_PERSPECTIVE = 0 } yafgpu_camera_type;
+enum { YAFGPU_BK_DISK1 = 0, YAFGPU_BK_DISK2 = 1, YAFGPU_BK_TRI = 3, YAFGPU_BK_SQR = 4, YAFGPU_BK_PENTA = 5, YAFGPU_BK_HEXA = 6, YAFGPU_BK_RING = 7 };
+enum { YAFGPU_BB_NONE = 0, YAFGPU_BB_CENTER = 1, YAFGPU_BB_EDGE = 2 };
+
+/* "perspective": camera_perspective.cc:206-252 and Camera::Camera camera.cc:46-66 */
+typedef struct yafgpu_camera
+{
+	int32_t type;
+	int32_t resx, resy;      /* "resx", "resy" */
+	float from[3], to[3], up[3];
+	float focal;             /* "focal" */
+	float aperture;          /* "aperture" */
+	float dof_distance;      /* "dof_distance" */
+	float aspect_ratio;      /* "aspect_ratio" */
+	float near_clip;         /* "nearClip" */
+	float far_clip;          /* "farClip" */
+	int32_t bokeh_type;      /* "bokeh_type" */
+	int32_t bokeh_bias;      /* "bokeh_bias" */
+	float bokeh_rotation;    /* "bokeh_rotation" */
+} yafgpu_camera;
+
+/* ---- background ------------------------------------------------------------------------ */
+
+typedef enum yafgpu_background_type
+{
+	YAFGPU_BG_NONE = 0,
+	YAFGPU_BG_CONSTANT = 1,   /* "constant"    background_constant.cc:52-86 */
+	YAFGPU_BG_TEXTURE = 2     /* "textureback" background_texture.cc:90-165 (image given as decoded linear float RGB) */
+} yafgpu_background_type;
+
+typedef struct yafgpu_background
+{
+	int32_t type;
+	float color[3];          /* constant: "color" (before *power) */
+	float power;             /* "power" */
+	int32_t ibl;             /* "ibl": a yafgpu_light of type BACKGROUND must then be present in lights[] */
+	int32_t with_caustic;    /* "with_caustic" -> Background::shootsCaustic() */
+	int32_t mapping_angular; /* texture: "mapping" == probe/angular */
+	float rotation;          /* texture: "rotation" (degrees) */
+	/* texture: pixels as ImageHandler::getPixel returns them, row-major, y down, RGB float32 */
+	const float *tex_rgb; int32_t tex_w, tex_h;
+	int32_t tex_interp;      /* 0 = none, 1 = bilinear (texture "interpolate") */
+} yafgpu_background;
+
+/* ---- film, AA and integrator settings -------------------------------------------------- */
+
+enum { YAFGPU_FILTER_BOX = 0, YAFGPU_FILTER_MITCHELL = 1, YAFGPU_FILTER_GAUSS = 2, YAFGPU_FILTER_LANCZOS = 3 };
+
+/* RenderEnvironment::createImageFilm environment.cc:456-584 and setupScene :679-813 */
+typedef struct yafgpu_film_desc
+{
+	int32_t width, height;   /* "width", "height" */
+	int32_t xstart, ystart;  /* "xstart", "ystart" */
+	float aa_pixelwidth;     /* "AA_pixelwidth" */
+	int32_t filter_type;     /* "filter_type" */
+	int32_t tile_size;       /* "tile_size" (multi-GPU interleave unit) */
+	int32_t premult;         /* "premult" */
+	float aa_clamp_samples;  /* "AA_clamp_samples" */
+	float aa_clamp_indirect; /* "AA_clamp_indirect" */
+	int32_t aa_passes;       /* "AA_passes": only whether >1 matters to the sampler (integrator_tiled.cc:394) */
+	float aa_light_sample_multiplier;    /* current value of TiledIntegrator::aa_light_sample_multiplier_ */
+	float aa_indirect_sample_multiplier; /* current value of aa_indirect_sample_multiplier_ */
+	uint32_t base_sampling_offset;       /* ImageFilm::getBaseSamplingOffset() (imagefilm.h:127) */
+} yafgpu_film_desc;
+
+typedef enum yafgpu_integrator_type
+{
+	YAFGPU_INT_DIRECTLIGHT = 0, /* "directlighting" integrator_direct_light.cc:196-250 */
+	YAFGPU_INT_PATHTRACING = 1  /* "pathtracing"    integrator_path_tracer.cc:349-423 */
+} yafgpu_integrator_type;
+
+typedef struct yafgpu_integrator_desc
+{
+	int32_t type;
+	int32_t raydepth;        /* "raydepth" */
+	int32_t transp_shad;     /* "transpShad" */
+	int32_t shadow_depth;    /* "shadowDepth" */
+	int32_t path_samples;    /* "path_samples" */
+	int32_t bounces;         /* "bounces" */
+	int32_t rr_min_bounces;  /* "russian_roulette_min_bounces" */
+	int32_t no_recursive;    /* "no_recursive" */
+	int32_t trace_caustics;  /* caustic_type in {path, both} (integrator_path_tracer.cc:87); photon maps are refused */
+	int32_t bg_transp;       /* "bg_transp" */
+	int32_t bg_transp_refract; /* "bg_transp_refract" */
+	int32_t do_ao;           /* "do_AO" */
+	int32_t ao_samples;      /* "AO_samples" */
+	float ao_distance;       /* "AO_distance" */
+	float ao_color[3];       /* "AO_color" */
+	/* Scene::shadow_bias_, ray_min_dist_ and their auto flags (scene.h:230-234, scene.cc:823-824) */
+	float shadow_bias; int32_t shadow_bias_auto;
+	float ray_min_dist; int32_t ray_min_dist_auto;
+} yafgpu_integrator_desc;
+
+typedef struct yafgpu_scene_desc
+{
+	uint32_t abi_version;    /* YAFGPU_ABI_VERSION */
+	yafgpu_geometry geometry;
+	const yafgpu_material *materials; size_t n_materials;
+	const yafgpu_light *lights;       size_t n_lights;   /* in Scene::lights_ order */
+	yafgpu_camera camera;
+	yafgpu_background background;
+	yafgpu_film_desc film;
+	yafgpu_integrator_desc integrator;
+} yafgpu_scene_desc;
+
+/* ---- rays and hits (parity probe + traversal microbench) -------------------------------- */
+
+typedef struct yafgpu_ray { float from[3]; float tmin; float dir[3]; float tmax; } yafgpu_ray; /* tmax < 0 = infinite (scene.cc:900) */
+typedef struct yafgpu_hit { float t, u, v; int32_t tri; } yafgpu_hit;                          /* tri = global triangle id, -1 = miss; u,v = Möller–Trumbore b_1,b_2 */
+
+enum { YAFGPU_TRACE_CLOSEST = 0,      /* Scene::intersect          scene.cc:896-927 */
+       YAFGPU_TRACE_SHADOW = 1,       /* Scene::isShadowed opaque  scene.cc:962-995  (hit.tri = -1 unshadowed, else the blocker found; t = 1) */
+       YAFGPU_TRACE_SHADOW_TRANSP = 2 /* Scene::isShadowed transp. scene.cc:997-1035 (u,v,t reused: filt r,g,b in t,u,v) */ };
+
+/* ---- render pass ----------------------------------------------------------------------- */
+
+/* One call of TiledIntegrator::renderPass (integrator_tiled.cc:261-307) for this context's share of the image. */
+typedef struct yafgpu_pass_desc
+{
+	int32_t n_samples;       /* samples per pixel in this pass */
+	int32_t offset;          /* pass_offs: sampling offset incl. base offset (integrator_tiled.cc:263,335) */
+	int32_t adaptive;        /* 1: only pixels flagged in resample_mask are sampled (imagefilm.cc:917-920) */
+	int32_t aa_pass_number;
+	const uint8_t *resample_mask; /* adaptive only: width*height bytes (host), non-zero = sample this pixel */
+	/* sub-range of the pass's samples to render now: sample indices [sample_begin, sample_end); both 0 = all.
+	 * Lets a caller split one pass into bounded steps without changing any sample's random numbers. */
+	int32_t sample_begin, sample_end;
+	/* image partition for multi-GPU: this context renders tiles t with (t % part_count) == part_index, tiles being the
+	 * tile_size x tile_size raster grid of ImageSplitter (imagesplitter.cc:37-50).  part_count <= 1 = whole image. */
+	int32_t part_index, part_count;
+} yafgpu_pass_desc;
+
+typedef struct yafgpu_stats
+{
+	uint64_t rays_camera, rays_extension, rays_shadow, rays_shadow_transp, rays_light_probe;
+	uint64_t camera_samples;
+	uint64_t kernel_launches;
+	uint64_t bvh_nodes, bvh_bytes, tri_bytes;
+	uint64_t nodes_visited, tris_tested;   /* filled only when the context was created with YAFGPU_FLAG_COUNT_TRAVERSAL */
+	double ms_build, ms_trace, ms_shade, ms_film, ms_total; /* CUDA-event times accumulated since the last reset */
+	uint64_t waves, wave_retries;
+} yafgpu_stats;
+
+enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2 };
+
+/* ---- entry points ---------------------------------------------------------------------- */
+
+/* Create a context on CUDA device `device`.  Fails (no fallback) when the device is not usable. */
+int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags);
+void yafgpu_destroy(yafgpu_ctx *ctx);
+const char *yafgpu_last_error(const yafgpu_ctx *ctx); /* ctx may be NULL: error of the last failed yafgpu_create */
+int yafgpu_abi_version(void);
+
+/* Replaces the geometry branch of Scene::update() (scene.cc:788-831): copies the scene to HBM, builds the BVH
+ * (instead of `new TriKdTree`, kdtree_triangle.cc:76-157), initialises lights (Light::init) and the film (ImageFilm::init). */
+int yafgpu_upload_scene(yafgpu_ctx *ctx, const yafgpu_scene_desc *desc);
+/* Scene::getSceneBound() (scene.cc): 6 floats min xyz, max xyz */
+int yafgpu_scene_bound(yafgpu_ctx *ctx, float *bound6);
+
+/* Scene::intersect / Scene::isShadowed on a batch of host rays (H2D, trace, D2H).  shadow_depth = max_depth of scene.cc:997. */
+int yafgpu_trace(yafgpu_ctx *ctx, const yafgpu_ray *rays, size_t n, yafgpu_hit *hits, int mode, int shadow_depth);
+/* Same with device pointers (no copies): for microbenchmarks that keep rays resident in HBM. */
+int yafgpu_trace_device(yafgpu_ctx *ctx, const void *d_rays, size_t n, void *d_hits, int mode, int shadow_depth);
+
+/* ImageFilm::init (imagefilm.cc:219-268): zero the film accumulators. */
+int yafgpu_film_clear(yafgpu_ctx *ctx);
+/* TiledIntegrator::renderPass: trace + shade + ImageFilm::addSample for the pass; asynchronous on the context's stream. */
+int yafgpu_render_pass(yafgpu_ctx *ctx, const yafgpu_pass_desc *pass);
+/* Wait for all queued work; returns the first asynchronous error. */
+int yafgpu_sync(yafgpu_ctx *ctx);
+/* Film accumulators, width*height*5 floats: Pixel{Rgba col_; float weight_} (util_image_buffers.h:36-47) row-major. */
+int yafgpu_read_film(yafgpu_ctx *ctx, float *rgbaw);
+/* Device address of the same accumulator array (for NCCL reduction by the caller) and its float count. */
+int yafgpu_film_device_ptr(yafgpu_ctx *ctx, void **d_ptr, size_t *n_floats);
+/* Replace the accumulators (after a cross-GPU reduction, or to resume from a loaded film: imagefilm.cc:1506-1535). */
+int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
+/* Update per-pass AA multipliers between passes (integrator_tiled.cc:216-218). */
+int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
+
+int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
+int yafgpu_reset_stats(yafgpu_ctx *ctx);
+/* Raw CUDA stream handle of the context (cudaStream_t), so callers can time with events on the launching stream. */
+void *yafgpu_stream(yafgpu_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YAFGPU_H */

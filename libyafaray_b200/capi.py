@@ -1,0 +1,182 @@
+"""ctypes binding of the C ABI declared in include/yafgpu.h (libyafgpu.so).
+
+This is plumbing only: every struct below mirrors the header field for field.  The library is loaded eagerly and the
+import FAILS LOUDLY when the CUDA extension has not been built — there is no CPU fallback and no eager/PyTorch path.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libyafgpu.so")
+
+ABI_VERSION = 1
+
+# enums (include/yafgpu.h)
+OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE, ERR_NOMEM = range(6)
+VIS_NORMAL, VIS_NO_SHADOWS, VIS_SHADOW_ONLY, VIS_INVISIBLE = range(4)
+(MAT_SHINYDIFFUSE, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_ROUGH_GLASS, MAT_BLEND, MAT_MIRROR, MAT_NULL,
+ MAT_LIGHT) = range(9)
+LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND = range(5)
+CAM_PERSPECTIVE = 0
+BK = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}
+BB = {"uniform": 0, "center": 1, "edge": 2}
+BG_NONE, BG_CONSTANT, BG_TEXTURE = range(3)
+FILTERS = {"box": 0, "mitchell": 1, "gauss": 2, "lanczos": 3}
+INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
+TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
+FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES = 1, 2
+
+f32, i32, u32, u64 = C.c_float, C.c_int32, C.c_uint32, C.c_uint64
+F3 = f32 * 3
+pf, pi = C.POINTER(f32), C.POINTER(i32)
+
+
+class Object(C.Structure):
+    _fields_ = [("has_orco", i32), ("has_uv", i32), ("smooth", i32), ("light", i32), ("first_tri", i32),
+                ("n_tris", i32), ("obj_id", i32), ("pass_index", i32)]
+
+
+class Geometry(C.Structure):
+    _fields_ = [("points", pf), ("n_points", C.c_size_t), ("normals", pf), ("n_normals", C.c_size_t),
+                ("uv", pf), ("n_uv", C.c_size_t), ("tri_vidx", pi), ("tri_nidx", pi), ("tri_uvidx", pi),
+                ("tri_mat", pi), ("tri_obj", pi), ("n_tris", C.c_size_t),
+                ("objects", C.POINTER(Object)), ("n_objects", C.c_size_t)]
+
+
+class MatShinyDiffuse(C.Structure):
+    _fields_ = [("color", F3), ("mirror_color", F3), ("diffuse_reflect", f32), ("specular_reflect", f32),
+                ("transparency", f32), ("translucency", f32), ("emit", f32), ("ior", f32), ("fresnel_effect", i32),
+                ("transmit_filter", f32), ("oren_nayar", i32), ("sigma", f32)]
+
+
+class MatGlossy(C.Structure):
+    _fields_ = [("color", F3), ("diffuse_color", F3), ("mirror_color", F3), ("diffuse_reflect", f32),
+                ("glossy_reflect", f32), ("specular_reflect", f32), ("exponent", f32), ("exp_u", f32), ("exp_v", f32),
+                ("ior", f32), ("as_diffuse", i32), ("anisotropic", i32), ("oren_nayar", i32), ("sigma", f32)]
+
+
+class MatGlass(C.Structure):
+    _fields_ = [("ior", f32), ("filter_color", F3), ("transmit_filter", f32), ("mirror_color", F3),
+                ("dispersion_power", f32), ("fake_shadows", i32), ("alpha", f32), ("has_absorption", i32),
+                ("absorption", F3), ("absorption_dist", f32)]
+
+
+class MatBlend(C.Structure):
+    _fields_ = [("material1", i32), ("material2", i32), ("blend_value", f32)]
+
+
+class MatSimple(C.Structure):
+    _fields_ = [("color", F3), ("strength", f32), ("double_sided", i32)]
+
+
+class MatUnion(C.Union):
+    _fields_ = [("shinydiffuse", MatShinyDiffuse), ("glossy", MatGlossy), ("glass", MatGlass), ("blend", MatBlend),
+                ("simple", MatSimple), ("pad_", f32 * 32)]
+
+
+class Material(C.Structure):
+    _fields_ = [("type", i32), ("visibility", i32), ("receive_shadows", i32), ("flat_material", i32),
+                ("additional_depth", i32), ("transparent_bias_factor", f32),
+                ("transparent_bias_multiply_raydepth", i32), ("sampling_factor", f32), ("mat_pass_index", i32),
+                ("reserved", i32 * 3), ("u", MatUnion)]
+
+
+class Light(C.Structure):
+    _fields_ = [("type", i32), ("light_enabled", i32), ("cast_shadows", i32), ("photon_only", i32), ("samples", i32),
+                ("object", i32), ("double_sided", i32), ("abs_intersect", i32), ("color", F3), ("power", f32),
+                ("from_", F3), ("point1", F3), ("point2", F3), ("angle", f32), ("clamp_intersect", f32),
+                ("shoot_caustic", i32), ("shoot_diffuse", i32), ("reserved", i32 * 2)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("type", i32), ("resx", i32), ("resy", i32), ("from_", F3), ("to", F3), ("up", F3), ("focal", f32),
+                ("aperture", f32), ("dof_distance", f32), ("aspect_ratio", f32), ("near_clip", f32), ("far_clip", f32),
+                ("bokeh_type", i32), ("bokeh_bias", i32), ("bokeh_rotation", f32)]
+
+
+class Background(C.Structure):
+    _fields_ = [("type", i32), ("color", F3), ("power", f32), ("ibl", i32), ("with_caustic", i32),
+                ("mapping_angular", i32), ("rotation", f32), ("tex_rgb", pf), ("tex_w", i32), ("tex_h", i32),
+                ("tex_interp", i32)]
+
+
+class FilmDesc(C.Structure):
+    _fields_ = [("width", i32), ("height", i32), ("xstart", i32), ("ystart", i32), ("aa_pixelwidth", f32),
+                ("filter_type", i32), ("tile_size", i32), ("premult", i32), ("aa_clamp_samples", f32),
+                ("aa_clamp_indirect", f32), ("aa_passes", i32), ("aa_light_sample_multiplier", f32),
+                ("aa_indirect_sample_multiplier", f32), ("base_sampling_offset", u32)]
+
+
+class IntegratorDesc(C.Structure):
+    _fields_ = [("type", i32), ("raydepth", i32), ("transp_shad", i32), ("shadow_depth", i32), ("path_samples", i32),
+                ("bounces", i32), ("rr_min_bounces", i32), ("no_recursive", i32), ("trace_caustics", i32),
+                ("bg_transp", i32), ("bg_transp_refract", i32), ("do_ao", i32), ("ao_samples", i32),
+                ("ao_distance", f32), ("ao_color", F3), ("shadow_bias", f32), ("shadow_bias_auto", i32),
+                ("ray_min_dist", f32), ("ray_min_dist_auto", i32)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("abi_version", u32), ("geometry", Geometry), ("materials", C.POINTER(Material)),
+                ("n_materials", C.c_size_t), ("lights", C.POINTER(Light)), ("n_lights", C.c_size_t),
+                ("camera", Camera), ("background", Background), ("film", FilmDesc), ("integrator", IntegratorDesc)]
+
+
+class PassDesc(C.Structure):
+    _fields_ = [("n_samples", i32), ("offset", i32), ("adaptive", i32), ("aa_pass_number", i32),
+                ("resample_mask", C.POINTER(C.c_uint8)), ("sample_begin", i32), ("sample_end", i32),
+                ("part_index", i32), ("part_count", i32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("rays_camera", u64), ("rays_extension", u64), ("rays_shadow", u64), ("rays_shadow_transp", u64),
+                ("rays_light_probe", u64), ("camera_samples", u64), ("kernel_launches", u64), ("bvh_nodes", u64),
+                ("bvh_bytes", u64), ("tri_bytes", u64), ("nodes_visited", u64), ("tris_tested", u64),
+                ("ms_build", C.c_double), ("ms_trace", C.c_double), ("ms_shade", C.c_double), ("ms_film", C.c_double),
+                ("ms_total", C.c_double), ("waves", u64), ("wave_retries", u64)]
+
+
+# every entry point include/yafgpu.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "yafgpu_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_uint]),
+    "yafgpu_destroy": (None, [C.c_void_p]),
+    "yafgpu_last_error": (C.c_char_p, [C.c_void_p]),
+    "yafgpu_abi_version": (C.c_int, []),
+    "yafgpu_upload_scene": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc)]),
+    "yafgpu_scene_bound": (C.c_int, [C.c_void_p, pf]),
+    "yafgpu_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
+    "yafgpu_trace_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
+    "yafgpu_film_clear": (C.c_int, [C.c_void_p]),
+    "yafgpu_render_pass": (C.c_int, [C.c_void_p, C.POINTER(PassDesc)]),
+    "yafgpu_sync": (C.c_int, [C.c_void_p]),
+    "yafgpu_read_film": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "yafgpu_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "yafgpu_write_film": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "yafgpu_set_aa_multipliers": (C.c_int, [C.c_void_p, f32, f32]),
+    "yafgpu_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "yafgpu_reset_stats": (C.c_int, [C.c_void_p]),
+    "yafgpu_stream": (C.c_void_p, [C.c_void_p]),
+}
+
+
+class YafGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("yafgpu error %d: %s" % (code, msg))
+        self.code = code
+
+
+def load():
+    """dlopen libyafgpu.so and bind every declared symbol; raises when the extension is missing (no fallback)."""
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libyafgpu.so is not built (%s): run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                          "there is no CPU fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError when a declared symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if lib.yafgpu_abi_version() != ABI_VERSION:
+        raise ImportError("libyafgpu.so ABI version mismatch")
+    return lib
+
+
+lib = load()

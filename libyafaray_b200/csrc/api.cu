@@ -1,0 +1,430 @@
+// C ABI of include/yafgpu.h: context life cycle, scene upload (Scene::update() geometry branch, scene.cc:788-831),
+// batch tracing (Scene::intersect / isShadowed probes) and film access.  The integrator lives in integrator.cu.
+#include "context.h"
+#include "host_prep.h"
+#include "bvh_build.h"
+#include "traverse.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <new>
+
+static std::string g_create_err;
+
+namespace yg {
+
+int setErr(yafgpu_ctx *ctx, int code, const std::string &msg)
+{
+	if(ctx) ctx->err = msg; else g_create_err = msg;
+	return code;
+}
+int cudaErr(yafgpu_ctx *ctx, cudaError_t e, const char *what)
+{
+	return setErr(ctx, YAFGPU_ERR_CUDA, std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what);
+}
+
+template<class T> static cudaError_t upload(T *&dst, const T *src, size_t n, cudaStream_t s)
+{
+	dst = nullptr;
+	cudaError_t e = cudaMalloc(&dst, sizeof(T) * (n ? n : 1));
+	if(e != cudaSuccess) return e;
+	if(n) e = cudaMemcpyAsync(dst, src, sizeof(T) * n, cudaMemcpyHostToDevice, s);
+	return e;
+}
+
+static void freeScene(yafgpu_ctx *c)
+{
+	cudaFree(c->d_points); cudaFree(c->d_normals); cudaFree(c->d_uv); cudaFree(c->d_tri_ng); cudaFree(c->d_tri_vidx);
+	cudaFree(c->d_tri_mat); cudaFree(c->d_mat_triflags); cudaFree(c->d_tris); cudaFree(c->d_objects); cudaFree(c->d_mats);
+	cudaFree(c->d_lights); cudaFree(c->d_light_tables); cudaFree(c->d_bg_tex); cudaFree(c->d_nodes); cudaFree(c->d_acc_tris);
+	cudaFree(c->film.pix);
+	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
+	c->d_tris = nullptr; c->d_objects = nullptr; c->d_mats = nullptr; c->d_lights = nullptr; c->d_light_tables = nullptr; c->d_bg_tex = nullptr;
+	c->d_nodes = nullptr; c->d_acc_tris = nullptr; c->film.pix = nullptr;
+	c->uploaded = false;
+}
+
+// builds TriShade records (global triangle order) from the flat index arrays
+__global__ void k_tri_shade(int n, const int *__restrict__ vidx, const int *__restrict__ nidx, const int *__restrict__ uvidx,
+                            const int *__restrict__ mat, const int *__restrict__ obj, const float *__restrict__ ng, TriShade *__restrict__ out)
+{
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n) return;
+	TriShade t;
+	for(int k = 0; k < 3; ++k)
+	{
+		t.v[k] = vidx[3 * i + k];
+		t.n[k] = nidx ? nidx[3 * i + k] : -1;
+		t.uv[k] = uvidx ? uvidx[3 * i + k] : -1;
+		t.ng[k] = ng[3 * i + k];
+	}
+	t.mat = mat[i]; t.obj = obj[i];
+	out[i] = t;
+}
+
+// ---- batch trace kernels (parity probe + microbench) -----------------------------------------------------------------
+template<bool COUNT>
+__global__ void __launch_bounds__(128) k_trace_batch(Accel acc, const yafgpu_ray *__restrict__ rays, size_t n, yafgpu_hit *__restrict__ hits,
+                                                        int mode, unsigned long long *__restrict__ counters)
+{
+	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	for(size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+	{
+		const float4 a = __ldg((const float4 *)rays + 2 * i), b = __ldg((const float4 *)rays + 2 * i + 1);
+		RayD r; r.o = mk(a.x, a.y, a.z); r.tmin = a.w; r.d = mk(b.x, b.y, b.z); r.tmax = b.w;
+		float4 out;
+		if(mode == YAFGPU_TRACE_CLOSEST)
+		{
+			HitD h = traceClosest<COUNT>(acc, r, &tc);
+			out = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+		}
+		else
+		{
+			// Scene::isShadowed scene.cc:962-970: shift the origin, shorten the segment
+			V3 o = r.o + r.d * r.tmin;
+			float dist = (r.tmax < 0.f) ? __int_as_float(0x7f800000) : r.tmax - 2 * r.tmin;
+			int blocker = traceShadow<COUNT>(acc, o, r.d, dist, &tc);
+			out = make_float4(blocker >= 0 ? 1.f : 0.f, 0.f, 0.f, __int_as_float(blocker));
+		}
+		((float4 *)hits)[i] = out;
+	}
+	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+}
+
+} // namespace yg
+
+using namespace yg;
+
+extern "C" {
+
+int yafgpu_abi_version(void) { return YAFGPU_ABI_VERSION; }
+
+const char *yafgpu_last_error(const yafgpu_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags)
+{
+	if(!out) return setErr(nullptr, YAFGPU_ERR_INVALID, "yafgpu_create: out is NULL");
+	*out = nullptr;
+	int n_dev = 0;
+	cudaError_t e = cudaGetDeviceCount(&n_dev);
+	if(e != cudaSuccess || n_dev == 0)
+		return setErr(nullptr, YAFGPU_ERR_CUDA, std::string("yafgpu_create: no usable CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback");
+	if(device < 0 || device >= n_dev) return setErr(nullptr, YAFGPU_ERR_INVALID, "yafgpu_create: device index out of range");
+	if((e = cudaSetDevice(device)) != cudaSuccess) return cudaErr(nullptr, e, "cudaSetDevice");
+	yafgpu_ctx *c = new(std::nothrow) yafgpu_ctx();
+	if(!c) return setErr(nullptr, YAFGPU_ERR_NOMEM, "out of host memory");
+	c->device = device; c->flags = flags;
+	memset(&c->scene, 0, sizeof(c->scene)); memset(&c->film, 0, sizeof(c->film)); memset(&c->stats, 0, sizeof(c->stats));
+	if((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { delete c; return cudaErr(nullptr, e, "cudaStreamCreate"); }
+	cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
+	FaureTables *ft = new FaureTables();
+	yg_build_faure_tables(*ft);
+	e = cudaMalloc(&c->d_faure, sizeof(FaureTables));
+	if(e == cudaSuccess) e = cudaMemcpy(c->d_faure, ft, sizeof(FaureTables), cudaMemcpyHostToDevice);
+	delete ft;
+	if(e == cudaSuccess) e = cudaMalloc(&c->d_counters, sizeof(unsigned long long) * CNT_N);
+	if(e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * CNT_N);
+	if(e != cudaSuccess) { yafgpu_destroy(c); return cudaErr(nullptr, e, "context allocation"); }
+	*out = c;
+	return YAFGPU_OK;
+}
+
+void yafgpu_destroy(yafgpu_ctx *c)
+{
+	if(!c) return;
+	cudaSetDevice(c->device);
+	if(c->stream) cudaStreamSynchronize(c->stream);
+	freeScene(c);
+	freeWavefront(c);
+	cudaFree(c->d_faure); cudaFree(c->d_counters);
+	if(c->ev0) cudaEventDestroy(c->ev0);
+	if(c->ev1) cudaEventDestroy(c->ev1);
+	if(c->stream) cudaStreamDestroy(c->stream);
+	delete c;
+}
+
+void *yafgpu_stream(yafgpu_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
+{
+	if(!c || !desc) return setErr(c, YAFGPU_ERR_INVALID, "yafgpu_upload_scene: NULL argument");
+	if(desc->abi_version != YAFGPU_ABI_VERSION) return setErr(c, YAFGPU_ERR_INVALID, "yafgpu_upload_scene: ABI version mismatch");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	freeScene(c);
+	const yafgpu_geometry &g = desc->geometry;
+	if(g.n_tris > 0 && (!g.points || !g.tri_vidx || !g.tri_mat || !g.tri_obj || !g.objects))
+		return setErr(c, YAFGPU_ERR_INVALID, "geometry arrays missing");
+	if(g.n_tris > (size_t)(1u << 28)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "more than 2^28 triangles");
+	// validate indices on the host (cheap, and a bad index would otherwise be an illegal address on the device)
+	for(size_t i = 0; i < g.n_tris; ++i)
+	{
+		for(int k = 0; k < 3; ++k)
+		{
+			const int v = g.tri_vidx[3 * i + k];
+			if(v < 0 || (size_t)v >= g.n_points) return setErr(c, YAFGPU_ERR_INVALID, "tri_vidx out of range");
+			if(g.tri_nidx) { const int q = g.tri_nidx[3 * i + k]; if(q >= (int)g.n_normals) return setErr(c, YAFGPU_ERR_INVALID, "tri_nidx out of range"); }
+			if(g.tri_uvidx) { const int q = g.tri_uvidx[3 * i + k]; if(q >= (int)g.n_uv) return setErr(c, YAFGPU_ERR_INVALID, "tri_uvidx out of range"); }
+		}
+		if(g.tri_mat[i] < 0 || (size_t)g.tri_mat[i] >= desc->n_materials) return setErr(c, YAFGPU_ERR_INVALID, "tri_mat out of range");
+		if(g.tri_obj[i] < 0 || (size_t)g.tri_obj[i] >= g.n_objects) return setErr(c, YAFGPU_ERR_INVALID, "tri_obj out of range");
+	}
+
+	// materials / lights / camera / film: reference constructors restated on the host (host_prep.h)
+	c->h_mats.assign(desc->n_materials, MatDev());
+	std::vector<unsigned> triflags(desc->n_materials ? desc->n_materials : 1, 0u);
+	for(size_t i = 0; i < desc->n_materials; ++i)
+	{
+		std::string err;
+		if(!prepMaterial(desc->materials[i], c->h_mats[i], err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
+	}
+	for(size_t i = 0; i < desc->n_materials; ++i)
+	{
+		MatDev &m = c->h_mats[i];
+		if(m.type == YAFGPU_MAT_BLEND && (m.mat1 < 0 || m.mat2 < 0 || (size_t)m.mat1 >= desc->n_materials || (size_t)m.mat2 >= desc->n_materials))
+			return setErr(c, YAFGPU_ERR_INVALID, "blend material child index out of range");
+		triflags[i] = triFlagsOf(m);
+	}
+	c->h_lights.assign(desc->n_lights, LightDev());
+	for(size_t i = 0; i < desc->n_lights; ++i)
+	{
+		std::string err;
+		if(!prepLight(desc->lights[i], c->h_lights[i], err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "light " + std::to_string(i) + ": " + err);
+		if(c->h_lights[i].object >= (int)g.n_objects) return setErr(c, YAFGPU_ERR_INVALID, "light object index out of range");
+	}
+	SceneDev &s = c->scene;
+	memset(&s, 0, sizeof(s));
+	{
+		std::string err;
+		if(!prepCamera(desc->camera, s.cam, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, err);
+	}
+	const yafgpu_integrator_desc &in = desc->integrator;
+	if(in.type != YAFGPU_INT_DIRECTLIGHT && in.type != YAFGPU_INT_PATHTRACING) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "integrator type");
+	if(in.bg_transp || in.bg_transp_refract) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bg_transp / bg_transp_refract (alpha output) not implemented on the device");
+	if(in.do_ao) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "do_AO not implemented on the device");
+	if(in.raydepth + 1 + in.bounces + 8 > YG_MAX_ITERS) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "raydepth + bounces too large for the wavefront schedule");
+	s.integ.type = in.type; s.integ.r_depth = in.raydepth; s.integ.tr_shad = in.transp_shad; s.integ.s_depth = in.shadow_depth;
+	s.integ.n_paths = in.path_samples; s.integ.max_bounces = in.bounces; s.integ.rr_min_bounces = in.rr_min_bounces;
+	s.integ.no_recursive = in.no_recursive; s.integ.trace_caustics = in.trace_caustics;
+	s.integ.shadow_bias = in.shadow_bias; s.integ.shadow_bias_auto = in.shadow_bias_auto;
+	s.integ.ray_min_dist = in.ray_min_dist; s.integ.ray_min_dist_auto = in.ray_min_dist_auto;
+	s.integ.aa_light_sample_multiplier = desc->film.aa_light_sample_multiplier;
+	s.integ.aa_indirect_sample_multiplier = desc->film.aa_indirect_sample_multiplier;
+	s.integ.aa_clamp_indirect = desc->film.aa_clamp_indirect;
+	// Scene::update scene.cc:823-824
+	if(in.shadow_bias_auto) s.integ.shadow_bias = (float)0.0005;
+	if(in.ray_min_dist_auto) s.integ.ray_min_dist = (float)0.00005;
+
+	const yafgpu_background &bg = desc->background;
+	s.bg.type = bg.type;
+	if(bg.type == YAFGPU_BG_CONSTANT) for(int k = 0; k < 3; ++k) s.bg.color[k] = bg.color[k] * bg.power; // background_constant.cc:86
+	else if(bg.type != YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "background type not implemented on the device yet");
+	s.bg.has_ibl = bg.ibl; s.bg.shoots_caustic = bg.with_caustic;
+	if(bg.ibl) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "background IBL light not implemented on the device yet");
+
+	// tag objects with their light (AreaLight::init light_area.cc:55-63): the LAST light naming the object wins, as setLight overwrites
+	std::vector<ObjDev> objs(g.n_objects ? g.n_objects : 1);
+	for(size_t i = 0; i < g.n_objects; ++i) { objs[i].has_orco = g.objects[i].has_orco; objs[i].has_uv = g.objects[i].has_uv; objs[i].smooth = g.objects[i].smooth; objs[i].light = g.objects[i].light; }
+	for(size_t i = 0; i < desc->n_lights; ++i)
+		if((desc->lights[i].type == YAFGPU_LIGHT_AREA || desc->lights[i].type == YAFGPU_LIGHT_MESH) && desc->lights[i].object >= 0) objs[desc->lights[i].object].light = (int)i;
+
+	cudaStream_t st = c->stream;
+	c->n_tris = g.n_tris; c->n_points = g.n_points; c->n_normals = g.n_normals; c->n_uv = g.n_uv; c->n_objects = g.n_objects;
+	c->n_mats = desc->n_materials; c->n_lights = desc->n_lights;
+	int *d_nidx = nullptr, *d_uvidx = nullptr, *d_obj = nullptr;
+	YG_CUDA(c, upload(c->d_points, g.points, g.n_points * 3, st));
+	YG_CUDA(c, upload(c->d_normals, g.normals, g.n_normals * 3, st));
+	YG_CUDA(c, upload(c->d_uv, g.uv, g.n_uv * 2, st));
+	YG_CUDA(c, upload(c->d_tri_vidx, g.tri_vidx, g.n_tris * 3, st));
+	YG_CUDA(c, upload(c->d_tri_mat, g.tri_mat, g.n_tris, st));
+	YG_CUDA(c, upload(c->d_mat_triflags, triflags.data(), triflags.size(), st));
+	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
+	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
+	YG_CUDA(c, upload(c->d_lights, c->h_lights.data(), c->h_lights.size(), st));
+	YG_CUDA(c, cudaMalloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1)));
+	YG_CUDA(c, cudaMalloc(&c->d_tris, sizeof(TriShade) * (g.n_tris ? g.n_tris : 1)));
+	if(g.tri_nidx) YG_CUDA(c, upload(d_nidx, g.tri_nidx, g.n_tris * 3, st));
+	if(g.tri_uvidx) YG_CUDA(c, upload(d_uvidx, g.tri_uvidx, g.n_tris * 3, st));
+	YG_CUDA(c, upload(d_obj, g.tri_obj, g.n_tris, st));
+
+	// K1: accelerator
+	cudaEventRecord(c->ev0, st);
+	Accel &a = s.accel;
+	a.n_tris = (int)g.n_tris;
+	if(g.n_tris > 0)
+	{
+		BvhBuildInput bi; bi.n_tris = (int)g.n_tris; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx; bi.tri_mat = c->d_tri_mat;
+		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng;
+		BvhBuildOutput bo;
+		cudaError_t e = buildBvh(bi, bo, st);
+		if(e != cudaSuccess) { cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj); return cudaErr(c, e, "buildBvh"); }
+		c->d_nodes = bo.nodes; c->d_acc_tris = bo.tris;
+		a.nodes = bo.nodes; a.tris = bo.tris; a.n_nodes = bo.n_nodes; a.root = bo.root;
+		memcpy(c->scene_bound, bo.bound, sizeof(bo.bound));
+		// tree bound grown by 0.1 % per axis (kdtree_triangle.cc:112-116; double arithmetic on float members)
+		for(int k = 0; k < 3; ++k)
+		{
+			double foo = (double)(bo.bound[3 + k] - bo.bound[k]) * 0.001;
+			a.bmin[k] = (float)((double)bo.bound[k] - foo); a.bmax[k] = (float)((double)bo.bound[3 + k] + foo);
+			c->scene_bound[k] = a.bmin[k]; c->scene_bound[3 + k] = a.bmax[k]; // Scene::scene_bound_ = tree_->getBound() scene.cc:820
+		}
+		k_tri_shade<<<(unsigned)((g.n_tris + 255) / 256), 256, 0, st>>>((int)g.n_tris, c->d_tri_vidx, d_nidx, d_uvidx, c->d_tri_mat, d_obj, c->d_tri_ng, c->d_tris);
+	}
+	cudaEventRecord(c->ev1, st);
+	cudaError_t e = cudaStreamSynchronize(st);
+	cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj);
+	if(e != cudaSuccess) return cudaErr(c, e, "scene upload");
+	float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->stats.ms_build += ms;
+	c->stats.bvh_nodes = a.n_nodes; c->stats.bvh_bytes = (uint64_t)a.n_nodes * sizeof(BvhNode); c->stats.tri_bytes = (uint64_t)g.n_tris * sizeof(TriAccel);
+
+	s.points = c->d_points; s.normals = c->d_normals; s.uv = c->d_uv; s.tris = c->d_tris; s.objects = c->d_objects;
+	s.materials = c->d_mats; s.lights = c->d_lights; s.n_lights = (int)desc->n_lights; s.light_tables = c->d_light_tables; s.faure = c->d_faure;
+
+	// film (ImageFilm ctor + init)
+	prepFilm(desc->film, c->film);
+	c->tile_size = desc->film.tile_size > 0 ? desc->film.tile_size : 32;
+	if(desc->film.width <= 0 || desc->film.height <= 0 || desc->film.width > 65535 || desc->film.height > 65535) return setErr(c, YAFGPU_ERR_INVALID, "film size");
+	if(desc->film.premult) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "premult film not implemented on the device");
+	YG_CUDA(c, cudaMalloc(&c->film.pix, sizeof(float) * 5 * (size_t)c->film.w * c->film.h));
+	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
+	YG_CUDA(c, cudaStreamSynchronize(st));
+	c->uploaded = true;
+	return YAFGPU_OK;
+}
+
+int yafgpu_scene_bound(yafgpu_ctx *c, float *b)
+{
+	if(!c || !b) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	memcpy(b, c->scene_bound, sizeof(float) * 6);
+	return YAFGPU_OK;
+}
+
+int yafgpu_trace_device(yafgpu_ctx *c, const void *d_rays, size_t n, void *d_hits, int mode, int shadow_depth)
+{
+	if(!c) return YAFGPU_ERR_INVALID;
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	if(mode == YAFGPU_TRACE_SHADOW_TRANSP) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "transparent-shadow batch trace is only reachable through the integrator");
+	(void)shadow_depth;
+	if(n == 0) return YAFGPU_OK;
+	YG_CUDA(c, cudaSetDevice(c->device));
+	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	size_t want = (n + 127) / 128;
+	unsigned grid = (unsigned)(want < (size_t)sms * 16 ? want : (size_t)sms * 16);
+	if(c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL)
+		k_trace_batch<true><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_counters);
+	else
+		k_trace_batch<false><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_counters);
+	YG_CUDA(c, cudaGetLastError());
+	c->stats.kernel_launches++;
+	if(mode == YAFGPU_TRACE_CLOSEST) c->stats.rays_extension += n; else c->stats.rays_shadow += n;
+	return YAFGPU_OK;
+}
+
+int yafgpu_trace(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_hit *hits, int mode, int shadow_depth)
+{
+	if(!c || (n && (!rays || !hits))) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	if(n == 0) return YAFGPU_OK;
+	YG_CUDA(c, cudaSetDevice(c->device));
+	void *d_r = nullptr, *d_h = nullptr;
+	YG_CUDA(c, cudaMalloc(&d_r, n * sizeof(yafgpu_ray)));
+	cudaError_t e = cudaMalloc(&d_h, n * sizeof(yafgpu_hit));
+	if(e != cudaSuccess) { cudaFree(d_r); return cudaErr(c, e, "cudaMalloc hits"); }
+	e = cudaMemcpyAsync(d_r, rays, n * sizeof(yafgpu_ray), cudaMemcpyHostToDevice, c->stream);
+	int rc = (e == cudaSuccess) ? yafgpu_trace_device(c, d_r, n, d_h, mode, shadow_depth) : cudaErr(c, e, "H2D rays");
+	if(rc == YAFGPU_OK)
+	{
+		e = cudaMemcpyAsync(hits, d_h, n * sizeof(yafgpu_hit), cudaMemcpyDeviceToHost, c->stream);
+		if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+		if(e != cudaSuccess) rc = cudaErr(c, e, "D2H hits");
+	}
+	cudaFree(d_r); cudaFree(d_h);
+	return rc;
+}
+
+int yafgpu_film_clear(yafgpu_ctx *c)
+{
+	if(!c || !c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, c->stream));
+	return YAFGPU_OK;
+}
+
+int yafgpu_render_pass(yafgpu_ctx *c, const yafgpu_pass_desc *pass)
+{
+	if(!c || !pass) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	return renderPass(c, pass);
+}
+
+int yafgpu_sync(yafgpu_ctx *c)
+{
+	if(!c) return YAFGPU_ERR_INVALID;
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	return YAFGPU_OK;
+}
+
+int yafgpu_read_film(yafgpu_ctx *c, float *out)
+{
+	if(!c || !out) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaMemcpyAsync(out, c->film.pix, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, cudaMemcpyDeviceToHost, c->stream));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	return YAFGPU_OK;
+}
+
+int yafgpu_write_film(yafgpu_ctx *c, const float *in)
+{
+	if(!c || !in) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaMemcpyAsync(c->film.pix, in, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, cudaMemcpyHostToDevice, c->stream));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	return YAFGPU_OK;
+}
+
+int yafgpu_film_device_ptr(yafgpu_ctx *c, void **p, size_t *n)
+{
+	if(!c || !p || !n) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	*p = c->film.pix; *n = (size_t)5 * c->film.w * c->film.h;
+	return YAFGPU_OK;
+}
+
+int yafgpu_set_aa_multipliers(yafgpu_ctx *c, float light_mult, float indirect_mult)
+{
+	if(!c || !c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	c->scene.integ.aa_light_sample_multiplier = light_mult; c->scene.integ.aa_indirect_sample_multiplier = indirect_mult;
+	return YAFGPU_OK;
+}
+
+int yafgpu_get_stats(yafgpu_ctx *c, yafgpu_stats *out)
+{
+	if(!c || !out) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	unsigned long long h[CNT_N];
+	YG_CUDA(c, cudaMemcpy(h, c->d_counters, sizeof(h), cudaMemcpyDeviceToHost));
+	*out = c->stats;
+	out->rays_camera += h[CNT_RAYS_CAMERA]; out->rays_extension += h[CNT_RAYS_EXTENSION]; out->rays_shadow += h[CNT_RAYS_SHADOW];
+	out->rays_shadow_transp += h[CNT_RAYS_SHADOW_TRANSP]; out->rays_light_probe += h[CNT_RAYS_LIGHT_PROBE];
+	out->camera_samples += h[CNT_CAMERA_SAMPLES]; out->nodes_visited = h[CNT_NODES]; out->tris_tested = h[CNT_TRIS];
+	return YAFGPU_OK;
+}
+
+int yafgpu_reset_stats(yafgpu_ctx *c)
+{
+	if(!c) return YAFGPU_ERR_INVALID;
+	YG_CUDA(c, cudaSetDevice(c->device));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	uint64_t nodes = c->stats.bvh_nodes, nb = c->stats.bvh_bytes, tb = c->stats.tri_bytes; double mb = c->stats.ms_build;
+	memset(&c->stats, 0, sizeof(c->stats));
+	c->stats.bvh_nodes = nodes; c->stats.bvh_bytes = nb; c->stats.tri_bytes = tb; c->stats.ms_build = mb;
+	YG_CUDA(c, cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * CNT_N));
+	return YAFGPU_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,55 @@
+// yafgpu context: owns all device memory of one GPU (internal header, not part of the C ABI).
+#pragma once
+#include "../../include/yafgpu.h"
+#include "scene_dev.cuh"
+#include "wavefront.h"
+#include <string>
+#include <vector>
+
+struct yafgpu_ctx
+{
+	int device = 0;
+	unsigned flags = 0;
+	cudaStream_t stream = nullptr;
+	std::string err;
+	bool uploaded = false;
+
+	// scene arrays (device)
+	float *d_points = nullptr, *d_normals = nullptr, *d_uv = nullptr, *d_tri_ng = nullptr;
+	int *d_tri_vidx = nullptr, *d_tri_mat = nullptr;
+	unsigned *d_mat_triflags = nullptr;
+	yg::TriShade *d_tris = nullptr;
+	yg::ObjDev *d_objects = nullptr;
+	yg::MatDev *d_mats = nullptr;
+	yg::LightDev *d_lights = nullptr;
+	float *d_light_tables = nullptr;
+	float *d_bg_tex = nullptr;
+	yg::FaureTables *d_faure = nullptr;
+	yg::BvhNode *d_nodes = nullptr;
+	yg::TriAccel *d_acc_tris = nullptr;
+	size_t n_tris = 0, n_points = 0, n_normals = 0, n_uv = 0, n_objects = 0, n_mats = 0, n_lights = 0;
+
+	yg::SceneDev scene;   // by-value kernel argument
+	yg::FilmDev film;     // by-value kernel argument
+	float scene_bound[6] = {0, 0, 0, 0, 0, 0};
+	std::vector<yg::MatDev> h_mats;
+	std::vector<yg::LightDev> h_lights;
+	int tile_size = 32;
+
+	// wavefront state
+	yg::Wavefront wf;
+
+	// stats
+	yafgpu_stats stats;
+	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+namespace yg {
+int setErr(yafgpu_ctx *ctx, int code, const std::string &msg);
+int cudaErr(yafgpu_ctx *ctx, cudaError_t e, const char *what);
+int renderPass(yafgpu_ctx *ctx, const yafgpu_pass_desc *pass); // integrator.cu
+void freeWavefront(yafgpu_ctx *ctx);
+}
+
+#define YG_CUDA(ctx, call) do { cudaError_t e__ = (call); if(e__ != cudaSuccess) return yg::cudaErr(ctx, e__, #call); } while(0)

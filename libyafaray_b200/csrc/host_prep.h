@@ -1,0 +1,270 @@
+// Host-side restatement of the reference CONSTRUCTORS: turns the parameter-level descriptors of include/yafgpu.h into
+// the device records of scene_dev.cuh, computing derived constants the way the reference does (file:line per function).
+// Compiled with -ffp-contract=off; uses the same YG_HD math as the kernels.
+#pragma once
+#include "../../include/yafgpu.h"
+#include "scene_dev.cuh"
+#include <string>
+#include <vector>
+#include <cstring>
+
+namespace yg {
+
+enum : unsigned
+{
+	BsdfNone = 0x0000, BsdfSpecular = 0x0001, BsdfGlossy = 0x0002, BsdfDiffuse = 0x0004, BsdfDispersive = 0x0008,
+	BsdfReflect = 0x0010, BsdfTransmit = 0x0020, BsdfFilter = 0x0040, BsdfEmit = 0x0080, BsdfVolumetric = 0x0100,
+	BsdfAllSpecular = BsdfSpecular | BsdfReflect | BsdfTransmit,
+	BsdfAllGlossy = BsdfGlossy | BsdfReflect | BsdfTransmit,
+	BsdfAll = BsdfSpecular | BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit | BsdfFilter
+}; // material.h:50-66
+
+inline void cp3(float *d, const float *s) { d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; }
+inline void st3(float *d, V3 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; }
+inline V3 ld3(const float *s) { return mk(s[0], s[1], s[2]); }
+
+// ShinyDiffuseMaterial ctor + factory + config(): material_shiny_diffuse.cc:26-92,599-700
+inline bool prepShinyDiffuse(const yafgpu_material &m, MatDev &d, std::string &err)
+{
+	const yafgpu_mat_shinydiffuse &p = m.u.shinydiffuse;
+	cp3(d.diffuse_col, p.color); cp3(d.mirror_col, p.mirror_color);
+	d.mirror_strength = p.specular_reflect; d.transparency_strength = p.transparency; d.translucency_strength = p.translucency;
+	d.diffuse_strength = p.diffuse_reflect; d.transmit_filter_strength = p.transmit_filter;
+	for(int k = 0; k < 3; ++k) d.emit_col[k] = p.emit * p.color[k];
+	d.emit_strength = p.emit;
+	d.bsdf_flags = BsdfNone;
+	if(p.emit > 0.f) d.bsdf_flags |= BsdfEmit;
+	d.ior = 1.f; d.ior_squared = 1.f; d.has_fresnel = 0;
+	if(p.fresnel_effect) { d.ior = p.ior; d.ior_squared = p.ior * p.ior; d.has_fresnel = 1; }
+	d.use_oren_nayar = 0;
+	if(p.oren_nayar)
+	{	// initOrenNayar :198-204 (double)
+		double s2 = (double)p.sigma * (double)p.sigma;
+		d.oren_a = (float)(1.0 - 0.5 * (s2 / (s2 + 0.33)));
+		d.oren_b = (float)(0.45 * s2 / (s2 + 0.09));
+		d.use_oren_nayar = 1;
+	}
+	// config() :46-92 without shader nodes
+	d.n_bsdf = 0; d.is_mirror = d.is_transparent = d.is_translucent = d.is_diffuse = 0;
+	float acc = 1.f;
+	if(d.mirror_strength > 0.00001f)
+	{
+		d.is_mirror = 1;
+		if(!d.has_fresnel) acc = 1.f - d.mirror_strength;
+		d.bsdf_flags |= BsdfSpecular | BsdfReflect;
+		d.c_flags[d.n_bsdf] = BsdfSpecular | BsdfReflect; d.c_index[d.n_bsdf] = 0; ++d.n_bsdf;
+	}
+	if(d.transparency_strength * acc > 0.00001f)
+	{
+		d.is_transparent = 1;
+		acc *= 1.f - d.transparency_strength;
+		d.bsdf_flags |= BsdfTransmit | BsdfFilter;
+		d.c_flags[d.n_bsdf] = BsdfTransmit | BsdfFilter; d.c_index[d.n_bsdf] = 1; ++d.n_bsdf;
+	}
+	if(d.translucency_strength * acc > 0.00001f)
+	{
+		d.is_translucent = 1;
+		acc *= 1.f - d.transparency_strength; // sic: the reference multiplies by (1 - transparency) here as well (:78)
+		d.bsdf_flags |= BsdfDiffuse | BsdfTransmit;
+		d.c_flags[d.n_bsdf] = BsdfDiffuse | BsdfTransmit; d.c_index[d.n_bsdf] = 2; ++d.n_bsdf;
+	}
+	if(d.diffuse_strength * acc > 0.00001f)
+	{
+		d.is_diffuse = 1;
+		d.bsdf_flags |= BsdfDiffuse | BsdfReflect;
+		d.c_flags[d.n_bsdf] = BsdfDiffuse | BsdfReflect; d.c_index[d.n_bsdf] = 3; ++d.n_bsdf;
+	}
+	(void)err;
+	return true;
+}
+
+// GlassMaterial ctor + factory: material_glass.cc:32-49,311-379
+inline bool prepGlass(const yafgpu_material &m, MatDev &d, std::string &err)
+{
+	const yafgpu_mat_glass &p = m.u.glass;
+	d.ior = p.ior;
+	// filt * filt_col + Rgb(1.f - filt): filt is a double in the factory; Rgb ops are float (double -> float at the call)
+	const float filt = p.transmit_filter;
+	for(int k = 0; k < 3; ++k) d.filter_col[k] = filt * p.filter_color[k] + (1.f - filt);
+	cp3(d.spec_refl_col, p.mirror_color);
+	d.fake_shadow = p.fake_shadows ? 1 : 0;
+	d.bsdf_flags = BsdfAllSpecular;
+	if(d.fake_shadow) d.bsdf_flags |= BsdfFilter;
+	d.tm_flags = d.fake_shadow ? (BsdfFilter | BsdfTransmit) : (BsdfSpecular | BsdfTransmit);
+	d.disperse = 0;
+	if(p.dispersion_power > 0.f) { err = "glass: dispersion_power > 0 (spectral dispersion) is not implemented on the device"; return false; }
+	d.absorb = 0;
+	if(p.has_absorption) { err = "glass: Beer absorption volume handler is not implemented on the device"; return false; }
+	return true;
+}
+
+inline unsigned triFlagsOf(const MatDev &d)
+{
+	unsigned f = 0;
+	if(d.visibility == YAFGPU_VIS_NORMAL || d.visibility == YAFGPU_VIS_NO_SHADOWS) f |= TRI_VIS_CAMERA;
+	if(d.visibility == YAFGPU_VIS_NORMAL || d.visibility == YAFGPU_VIS_SHADOW_ONLY) f |= TRI_VIS_SHADOW;
+	bool transp = false;
+	if(d.type == YAFGPU_MAT_SHINYDIFFUSE) transp = d.is_transparent;          // material_shiny_diffuse.h:53
+	if(d.type == YAFGPU_MAT_GLASS || d.type == YAFGPU_MAT_ROUGH_GLASS) transp = d.fake_shadow; // material_glass.h:40
+	if(transp) f |= TRI_TRANSPARENT;
+	return f;
+}
+
+inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
+{
+	memset(&d, 0, sizeof(d));
+	d.type = m.type; d.visibility = m.visibility; d.receive_shadows = m.receive_shadows; d.flat = m.flat_material;
+	d.additional_depth = m.additional_depth; d.transp_bias_factor = m.transparent_bias_factor;
+	d.transp_bias_mult = m.transparent_bias_multiply_raydepth; d.sampling_factor = m.sampling_factor;
+	switch(m.type)
+	{
+		case YAFGPU_MAT_SHINYDIFFUSE: return prepShinyDiffuse(m, d, err);
+		case YAFGPU_MAT_GLASS: return prepGlass(m, d, err);
+		case YAFGPU_MAT_LIGHT: // LightMaterial material_simple.cc:38-41,63-73
+			for(int k = 0; k < 3; ++k) d.simple_col[k] = m.u.simple.color[k] * m.u.simple.strength;
+			d.double_sided = m.u.simple.double_sided; d.bsdf_flags = BsdfEmit;
+			return true;
+		case YAFGPU_MAT_NULL: d.bsdf_flags = BsdfNone; return true;
+		default:
+			err = "material type " + std::to_string(m.type) + " is not implemented on the device yet";
+			return false;
+	}
+}
+
+// Light constructors
+inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
+{
+	memset(&d, 0, sizeof(d));
+	d.type = l.type; d.enabled = l.light_enabled; d.cast_shadows = l.cast_shadows; d.photon_only = l.photon_only;
+	d.samples = l.samples; d.object = l.object; d.double_sided = l.double_sided; d.abs_intersect = l.abs_intersect;
+	d.clamp_intersect = l.clamp_intersect; d.shoot_caustic = l.shoot_caustic;
+	switch(l.type)
+	{
+		case YAFGPU_LIGHT_POINT: // PointLight::PointLight light_point.cc:29-36
+			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+			cp3(d.pos, l.from);
+			return true;
+		case YAFGPU_LIGHT_AREA: // AreaLight::AreaLight light_area.cc:34-53; factory passes (p1 - corner), (p2 - corner) :200
+		{
+			V3 c = ld3(l.from), v1 = ld3(l.point1) - c, v2 = ld3(l.point2) - c;
+			V3 fn = cross(v2, v1);
+			// color_ = col * inte * M_PI : Rgb*float, then Rgb * (float)M_PI (Rgb::operator*(float))
+			for(int k = 0; k < 3; ++k) d.color[k] = (l.color[k] * l.power) * (float)YG_M_PI;
+			d.area = normLen(fn);
+			d.inv_area = (float)(1.0 / (double)d.area);
+			V3 nrm = -fn;
+			V3 du = normalize(v1);
+			V3 dv = cross(nrm, du);
+			st3(d.pos, c); st3(d.to_x, v1); st3(d.to_y, v2); st3(d.fnormal, fn); st3(d.normal, nrm);
+			st3(d.du, du); st3(d.dv, dv);
+			st3(d.c2, c + v1); st3(d.c3, c + (v1 + v2)); st3(d.c4, c + v2);
+			return true;
+		}
+		case YAFGPU_LIGHT_SUN: // SunLight::SunLight light_sun.cc:28-42
+		{
+			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+			V3 dir = ld3(l.from);
+			V3 ndir = normalize(dir);
+			V3 du, dv;
+			createCs(dir, du, dv); // sic: the un-normalised parameter
+			float angle = l.angle;
+			if(angle > 80.f) angle = 80.f;
+			d.cos_angle = fCos((float)((double)angle * 0.01745329251994329576922));
+			d.invpdf = (float)(YG_M_2PI * (double)(1.f - d.cos_angle));
+			d.pdf = (float)(1.0 / (double)d.invpdf);
+			for(int k = 0; k < 3; ++k) d.col_pdf[k] = d.color[k] * d.pdf;
+			st3(d.pos, ndir); st3(d.du, du); st3(d.dv, dv);
+			return true;
+		}
+		default:
+			err = "light type " + std::to_string(l.type) + " is not implemented on the device yet";
+			return false;
+	}
+}
+
+// Camera::Camera camera.cc:46-66 + PerspectiveCamera ctor/setAxis camera_perspective.cc:29-82
+inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
+{
+	memset(&d, 0, sizeof(d));
+	if(c.type != YAFGPU_CAM_PERSPECTIVE) { err = "camera type not implemented on the device"; return false; }
+	d.resx = c.resx; d.resy = c.resy;
+	const V3 pos = ld3(c.from), look = ld3(c.to), up = ld3(c.up);
+	const float aspect_ratio = c.aspect_ratio * (float)c.resy / (float)c.resx;
+	V3 cam_y = up - pos, cam_z = look - pos;
+	V3 cam_x = cross(cam_z, cam_y);
+	cam_y = cross(cam_z, cam_x);
+	cam_x = normalize(cam_x); cam_y = normalize(cam_y); cam_z = normalize(cam_z);
+	st3(d.near_n, cam_z);
+	st3(d.near_p, pos + cam_z * c.near_clip);
+	st3(d.far_p, pos + cam_z * c.far_clip);
+	d.aperture = c.aperture; d.dof_distance = c.dof_distance;
+	st3(d.dof_rt, c.aperture * cam_x); st3(d.dof_up, c.aperture * cam_y);
+	V3 vright = cam_x;
+	V3 vup = aspect_ratio * cam_y;
+	// vto = (camZ * focal) - 0.5 * (vup + vright): 0.5 is double -> operator*(float, Vec3) narrows it to float first
+	V3 vto = (cam_z * c.focal) - 0.5f * (vup + vright);
+	vup = vup / (float)c.resy;
+	vright = vright / (float)c.resx;
+	st3(d.pos, pos); st3(d.vright, vright); st3(d.vup, vup); st3(d.vto, vto);
+	d.bokeh_type = c.bokeh_type; d.bokeh_bias = c.bokeh_bias; d.n_ls = 0;
+	int ns = c.bokeh_type;
+	if(ns >= 3 && ns <= 6)
+	{
+		float w = (float)((double)c.bokeh_rotation * 0.01745329251994329576922), wi = (float)(YG_M_2PI / (double)(float)ns);
+		ns = (ns + 2) * 2;
+		d.n_ls = ns;
+		for(int i = 0; i < ns; i += 2) { d.ls[i] = fCos(w); d.ls[i + 1] = fSin(w); w += wi; }
+	}
+	return true;
+}
+
+// filter kernels imagefilm.cc:60-122
+inline float filtBox(float, float) { return 1.f; }
+inline float filtMitchell(float dx, float dy)
+{
+	float x = 2.f * fSqrt(dx * dx + dy * dy);
+	if(x >= 2.f) return 0.f;
+	if(x >= 1.f) return (float)(x * (x * (x * -0.38888889f + 2.0f) - 3.33333333f) + 1.77777778f);
+	return (float)(x * x * (1.16666666f * x - 2.0f) + 0.88888889f);
+}
+inline float filtGauss(float dx, float dy)
+{
+	float r2 = dx * dx + dy * dy;
+	// std::max(0.f, float(fExp__(-6 * r_2) - GAUSS_EXP)): GAUSS_EXP 0.00247875 is a double literal
+	return fmaxf(0.f, (float)((double)fExp(-6 * r2) - 0.00247875));
+}
+inline float filtLanczos2(float dx, float dy)
+{
+	float x = fSqrt(dx * dx + dy * dy);
+	if(x == 0.f) return 1.f;
+	if(-2 < x && x < 2)
+	{
+		float a = (float)(YG_M_PI * (double)x);
+		float b = (float)(1.57079632679489661923 * (double)x);
+		return (fSin(a) * fSin(b)) / (a * b);
+	}
+	return 0.f;
+}
+
+// ImageFilm::ImageFilm imagefilm.cc:124-187
+inline void prepFilm(const yafgpu_film_desc &f, FilmDev &d)
+{
+	d.w = f.width; d.h = f.height; d.cx0 = f.xstart; d.cy0 = f.ystart; d.cx1 = f.xstart + f.width; d.cy1 = f.ystart + f.height;
+	d.filterw = (float)((double)f.aa_pixelwidth * 0.5);
+	float (*fn)(float, float) = filtBox;
+	switch(f.filter_type)
+	{
+		case YAFGPU_FILTER_MITCHELL: fn = filtMitchell; d.filterw *= 2.6f; break;
+		case YAFGPU_FILTER_LANCZOS: fn = filtLanczos2; break;
+		case YAFGPU_FILTER_GAUSS: fn = filtGauss; d.filterw *= 2.f; break;
+		default: fn = filtBox;
+	}
+	d.filterw = fminf(fmaxf(0.501f, d.filterw), 0.5f * 8);
+	const float scale = 1.f / 16.f;
+	for(int y = 0; y < 16; ++y) for(int x = 0; x < 16; ++x) d.table[y * 16 + x] = fn((x + .5f) * scale, (y + .5f) * scale);
+	d.table_scale = (float)(0.9999 * 16 / (double)d.filterw);
+	d.clamp_samples = f.aa_clamp_samples; d.premult = f.premult; d.aa_passes = f.aa_passes;
+	d.base_sampling_offset = f.base_sampling_offset;
+}
+
+} // namespace yg

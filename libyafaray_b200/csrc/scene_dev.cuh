@@ -1,0 +1,145 @@
+// HBM layout of the flattened scene.  Plain-old-data views handed to every kernel by value.
+#pragma once
+#include "dev_math.cuh"
+#include "dev_qmc.cuh"
+
+namespace yg {
+
+// ---- accelerator ---------------------------------------------------------------------------------------------------
+// Triangle record used by traversal: 48 B, three float4, stored in BVH (Morton) order.
+//   v0e  = (a.x, a.y, a.z, eps)           a = vertex pa_, eps = intersection_bias_factor_ (triangle.h:197-207)
+//   e1i  = (edge_1.xyz, bits of global triangle id)
+//   e2f  = (edge_2.xyz, bits of flags)    flags: TRI_VIS_CAMERA | TRI_VIS_SHADOW | TRI_TRANSPARENT
+// Full float32 precision is mandatory: Möller–Trumbore must reproduce Triangle::intersect (triangle.h:223-259) exactly.
+struct TriAccel { float4 v0e, e1i, e2f; };
+enum { TRI_VIS_CAMERA = 1,  // visibility in {Normal, VisibleNoShadows}      kdtree_triangle.cc:786
+       TRI_VIS_SHADOW = 2,  // visibility in {Normal, InvisibleShadowsOnly}  kdtree_triangle.cc:938
+       TRI_TRANSPARENT = 4  // Material::isTransparent()                     kdtree_triangle.cc:1106
+};
+
+// BVH2 node, 64 B = one 4 x float4 burst (two 32 B sectors):
+//   n0 = (c0.min.x, c0.min.y, c0.min.z, c0.max.x)
+//   n1 = (c0.max.y, c0.max.z, c1.min.x, c1.min.y)
+//   n2 = (c1.min.z, c1.max.x, c1.max.y, c1.max.z)
+//   n3 = (bits child0, bits child1, unused, unused)
+// child >= 0: internal node index; child < 0: leaf, ~child = (first << 3) | (count - 1) into the TriAccel array.
+struct BvhNode { float4 n0, n1, n2, n3; };
+
+struct Accel
+{
+	const BvhNode *nodes;
+	const TriAccel *tris;
+	int n_nodes, n_tris;
+	int root;          // encoded like a child (a 1-triangle scene has a leaf root)
+	float bmin[3], bmax[3]; // tree bound grown by 0.1 % as TriKdTree does (kdtree_triangle.cc:112-116)
+};
+
+// ---- shading data (global triangle order) ---------------------------------------------------------------------------
+struct TriShade
+{
+	int v[3];     // indices into points
+	int n[3];     // indices into normals or -1
+	int uv[3];    // indices into uv or -1
+	int mat;      // material index
+	int obj;      // object index
+	float ng[3];  // geometric normal, Triangle::recNormal (triangle.h:274-281)
+};
+
+struct ObjDev { int has_orco, has_uv, smooth, light; };
+
+// Material record after the reference constructors' preprocessing (one per yafgpu_material).
+struct MatDev
+{
+	int type, visibility, receive_shadows, flat;
+	int additional_depth, transp_bias_mult;
+	float transp_bias_factor, sampling_factor;
+	unsigned bsdf_flags;   // Material::bsdf_flags_
+	// shinydiffuse (material_shiny_diffuse.cc:25-92,599-688)
+	float diffuse_col[3], mirror_col[3], emit_col[3];
+	float diffuse_strength, mirror_strength, transparency_strength, translucency_strength, emit_strength;
+	float transmit_filter_strength;
+	float ior, ior_squared;
+	int has_fresnel, is_mirror, is_transparent, is_translucent, is_diffuse;
+	int n_bsdf; unsigned c_flags[4]; int c_index[4];
+	int use_oren_nayar; float oren_a, oren_b;
+	// glass / rough glass (material_glass.cc:32-49, material_rough_glass.cc)
+	float filter_col[3], spec_refl_col[3];
+	unsigned tm_flags; int fake_shadow, disperse; float cauchy_a, cauchy_b; float alpha_rough;
+	int absorb; float beer_sigma_a[3];
+	// glossy / coated glossy
+	float gloss_col[3], diff_col[3], gl_mirror_col[3];
+	float gl_diffuse, gl_glossy, gl_exponent, exp_u, exp_v, gl_mirror_strength;
+	int as_diffuse, anisotropic, with_diffuse, gl_oren_nayar; float gl_oren_a, gl_oren_b;
+	// blend
+	int mat1, mat2; float blend_val;
+	// simple (light_mat / mirror)
+	float simple_col[3]; int double_sided;
+};
+
+// Light record after constructor preprocessing.
+struct LightDev
+{
+	int type, enabled, cast_shadows, photon_only, samples, object, double_sided, abs_intersect;
+	float color[3];     // post-constructor colour (e.g. area: col*power*pi)
+	float pos[3];       // point position / sun direction / area corner
+	float to_x[3], to_y[3], fnormal[3], normal[3]; // area
+	float c2[3], c3[3], c4[3];                     // area corners
+	float area, inv_area;
+	// sun (light_sun.cc:29-55)
+	float du[3], dv[3]; float cos_angle, pdf, invpdf; float col_pdf[3];
+	// mesh / background: offsets into LightTables
+	int cdf_offset, cdf_count; float cdf_integral;
+	int tri_first, tri_count;
+	float clamp_intersect; int shoot_caustic;
+};
+
+struct CameraDev
+{
+	float pos[3], vright[3], vup[3], vto[3], dof_rt[3], dof_up[3];
+	float near_n[3], near_p[3], far_p[3];
+	float aperture, dof_distance;
+	int resx, resy, bokeh_type, bokeh_bias, n_ls;
+	float ls[20];
+};
+
+struct BackgroundDev
+{
+	int type; float color[3]; // constant: col*power
+	int has_ibl, shoots_caustic;
+	int mapping_angular; float rotation, power; const float *tex; int tex_w, tex_h, tex_interp;
+};
+
+struct IntegratorDev
+{
+	int type, r_depth, tr_shad, s_depth, n_paths, max_bounces, rr_min_bounces, no_recursive, trace_caustics;
+	int transp_bg, transp_refr_bg, do_ao, ao_samples; float ao_dist, ao_col[3];
+	float shadow_bias; int shadow_bias_auto; float ray_min_dist; int ray_min_dist_auto;
+	float aa_light_sample_multiplier, aa_indirect_sample_multiplier, aa_clamp_indirect;
+};
+
+struct FilmDev
+{
+	float *pix;         // w*h*5: r,g,b,a,weight
+	int w, h, cx0, cy0, cx1, cy1;
+	float filterw, table_scale, clamp_samples;
+	int premult, aa_passes;
+	unsigned base_sampling_offset;
+	float table[256];   // 16x16 filter table, imagefilm.cc:167-174
+};
+
+struct SceneDev
+{
+	Accel accel;
+	const float *points, *normals, *uv;
+	const TriShade *tris;
+	const ObjDev *objects;
+	const MatDev *materials;
+	const LightDev *lights; int n_lights;
+	const float *light_tables;
+	const FaureTables *faure;
+	CameraDev cam;
+	BackgroundDev bg;
+	IntegratorDev integ;
+};
+
+} // namespace yg

@@ -1,0 +1,162 @@
+// K3/K4 device traversal: closest hit and any hit over the BVH2 of scene_dev.cuh.
+//
+// Semantics follow the reference, not a generic ray tracer:
+//   closest : Scene::intersect -> TriKdTree::intersect (/root/reference/src/common/scene.cc:896-927, kdtree_triangle.cc:684-837)
+//             accept t_hit < z && t_hit >= ray.tmin && visibility in {Normal, VisibleNoShadows}; z starts at dist.
+//   shadow  : Scene::isShadowed -> TriKdTree::intersectS (scene.cc:962-995, kdtree_triangle.cc:840-977)
+//             caller has already moved the origin by dir*tmin and set dist = tmax - 2*tmin; accept t_hit < dist && t_hit >= 0
+//             && visibility in {Normal, InvisibleShadowsOnly}.
+//   triangle: Triangle::intersect (/root/reference/include/common/triangle.h:223-259), float32 Möller–Trumbore on the cached
+//             a, edge_1, edge_2, eps, same operation order, no FMA contraction (-fmad=false).
+// Equal-t candidates: the kd-tree keeps the first one it visits (strict <); a BVH visits in another order, so the tie is
+// broken deterministically towards the LOWER global triangle id (documented tie rule).
+#pragma once
+#include "scene_dev.cuh"
+
+namespace yg {
+
+struct RayD { V3 o; float tmin; V3 d; float tmax; };
+struct HitD { float t, u, v; int tri; };
+
+#define YG_STACK 96
+
+// Möller–Trumbore exactly as triangle.h:223-259. Returns true and t,u,v when the reference would return true.
+YG_D bool triIntersect(const float4 v0e, const float4 e1i, const float4 e2f, const V3 o, const V3 d, float &t, float &u, float &v)
+{
+	const V3 e1 = mk(e1i.x, e1i.y, e1i.z), e2 = mk(e2f.x, e2f.y, e2f.z);
+	const V3 pvec = cross(d, e2);
+	const float det = dot(e1, pvec);
+	const float eps = v0e.w;
+	if(det > -eps && det < eps) return false;
+	const float inv_det = 1.f / det;
+	const V3 tvec = mk(o.x - v0e.x, o.y - v0e.y, o.z - v0e.z);
+	u = dot(tvec, pvec) * inv_det;
+	if(u < 0.f || u > 1.f) return false;
+	const V3 qvec = cross(tvec, e1);
+	v = dot(d, qvec) * inv_det;
+	if((v < 0.f) || ((u + v) > 1.f)) return false;
+	t = dot(e2, qvec) * inv_det;
+	if(t < eps) return false;
+	return true;
+}
+
+// slab test of one child box against [tlo, thi]; conservative (NaN-safe min/max, far side widened by 2 ulp-ish)
+YG_D bool slab(float bx0, float by0, float bz0, float bx1, float by1, float bz1, const V3 o, const V3 id, float tlo, float thi, float &tnear)
+{
+	float t0 = (bx0 - o.x) * id.x, t1 = (bx1 - o.x) * id.x;
+	float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
+	t0 = (by0 - o.y) * id.y; t1 = (by1 - o.y) * id.y;
+	tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
+	t0 = (bz0 - o.z) * id.z; t1 = (bz1 - o.z) * id.z;
+	tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
+	tf *= 1.0000004f;
+	tnear = tn;
+	return tn <= tf && tf >= tlo && tn <= thi;
+}
+
+struct TravCounters { unsigned long long nodes, tris; };
+
+// Closest hit. `dist` = ray.tmax < 0 ? inf : ray.tmax (scene.cc:900-901).
+template<bool COUNT>
+YG_D HitD traceClosest(const Accel &acc, const RayD &r, TravCounters *cnt)
+{
+	HitD h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.tri = -1;
+	float z = (r.tmax < 0.f) ? __int_as_float(0x7f800000) : r.tmax;
+	const V3 id = mk(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
+	const float tlo = r.tmin * 0.99f;
+	int stack[YG_STACK];
+	int sp = 0;
+	int cur = acc.root;
+	if(acc.n_tris == 0) return h;
+	for(;;)
+	{
+		if(cur >= 0)
+		{
+			const BvhNode *nd = acc.nodes + cur;
+			const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
+			if(COUNT) cnt->nodes++;
+			float ta, tb;
+			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, r.o, id, tlo, z, ta);
+			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, r.o, id, tlo, z, tb);
+			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+			if(ha && hb)
+			{
+				const bool a_first = ta <= tb;
+				cur = a_first ? ca : cb;
+				if(sp < YG_STACK) stack[sp++] = a_first ? cb : ca;
+				continue;
+			}
+			if(ha) { cur = ca; continue; }
+			if(hb) { cur = cb; continue; }
+		}
+		else
+		{
+			const int code = ~cur;
+			const int first = code >> 3, count = (code & 7) + 1;
+			for(int k = 0; k < count; ++k)
+			{
+				const TriAccel *tp = acc.tris + first + k;
+				const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
+				if(COUNT) cnt->tris++;
+				float t, u, v;
+				if(!triIntersect(v0e, e1i, e2f, r.o, r.d, t, u, v)) continue;
+				if(!(__float_as_int(e2f.w) & TRI_VIS_CAMERA)) continue;
+				const int id_ = __float_as_int(e1i.w);
+				if(t >= r.tmin && (t < z || (t == z && h.tri >= 0 && id_ < h.tri)))
+				{
+					z = t; h.t = t; h.u = u; h.v = v; h.tri = id_;
+				}
+			}
+		}
+		if(sp == 0) break;
+		cur = stack[--sp];
+	}
+	return h;
+}
+
+// Any hit for opaque shadows. The caller passes the ALREADY SHIFTED origin and dist (scene.cc:965-970).
+// Returns the global id of a blocker (any), or -1.
+template<bool COUNT>
+YG_D int traceShadow(const Accel &acc, const V3 o, const V3 d, float dist, TravCounters *cnt)
+{
+	if(acc.n_tris == 0) return -1;
+	const V3 id = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+	int stack[YG_STACK];
+	int sp = 0;
+	int cur = acc.root;
+	for(;;)
+	{
+		if(cur >= 0)
+		{
+			const BvhNode *nd = acc.nodes + cur;
+			const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
+			if(COUNT) cnt->nodes++;
+			float ta, tb;
+			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, 0.f, dist, ta);
+			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, 0.f, dist, tb);
+			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+			if(ha && hb) { cur = ca; if(sp < YG_STACK) stack[sp++] = cb; continue; }
+			if(ha) { cur = ca; continue; }
+			if(hb) { cur = cb; continue; }
+		}
+		else
+		{
+			const int code = ~cur;
+			const int first = code >> 3, count = (code & 7) + 1;
+			for(int k = 0; k < count; ++k)
+			{
+				const TriAccel *tp = acc.tris + first + k;
+				const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
+				if(COUNT) cnt->tris++;
+				float t, u, v;
+				if(!triIntersect(v0e, e1i, e2f, o, d, t, u, v)) continue;
+				if(t < dist && t >= 0.f && (__float_as_int(e2f.w) & TRI_VIS_SHADOW)) return __float_as_int(e1i.w);
+			}
+		}
+		if(sp == 0) break;
+		cur = stack[--sp];
+	}
+	return -1;
+}
+
+} // namespace yg

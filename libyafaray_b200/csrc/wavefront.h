@@ -1,0 +1,73 @@
+// Wavefront state of the integrator: SoA task queues in HBM.
+//
+// A "task" is one ray that must be traced to its closest hit and then shaded.  Two kinds exist, mirroring the two places
+// where the reference calls Scene::intersect on the hot path:
+//   TASK_INTEGRATE : one call of PathIntegrator/DirectLightIntegrator::integrate() (integrator_path_tracer.cc:112-347):
+//                    camera rays and the rays spawned by recursiveRaytrace (integrator_montecarlo.cc:782-1028)
+//   TASK_PATH      : one vertex of the path loop of PathIntegrator::integrate (integrator_path_tracer.cc:185-295)
+// Every task carries the RGB factor its result is multiplied with before it is added to the camera sample it belongs to
+// (`slot`), which turns the reference's recursion tree into a flat work list.  Shadow rays are a third, lighter record:
+// the contribution is computed first and added to the sample only if the any-hit trace finds the segment unoccluded.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace yg {
+
+enum { TASK_INTEGRATE = 0, TASK_PATH = 1 };
+
+// packed task state (uint32), see packState()/fields below
+//  bit 0      kind
+//  bits 1-5   raylevel (0..31)
+//  bits 6-11  depth of the path vertex (0..63)
+//  bits 12-19 ray_division (1..255)
+//  bit 20     chromatic
+//  bit 21     include_lights
+//  bit 22     caustic
+//  bits 23-27 additional_depth (0..31)
+struct TaskQueue
+{
+	float4 *ray_o;   // from.xyz, tmin
+	float4 *ray_d;   // dir.xyz, tmax (<0 = infinite)
+	float4 *hit;     // t, u, v, bits(tri)     written by k_trace
+	float4 *wgt;     // weight rgb, wavelength
+	uint4 *st;       // slot, offs (path) , packed, ray_offset
+	float2 *dc;      // dc_1, dc_2
+};
+
+struct ShadowQueue
+{
+	float4 *ray_o;   // from.xyz (NOT yet shifted), tmin
+	float4 *ray_d;   // dir.xyz, tmax
+	float4 *contrib; // rgb contribution if unoccluded, bits(slot)
+};
+
+enum { CNT_RAYS_CAMERA = 0, CNT_RAYS_EXTENSION, CNT_RAYS_SHADOW, CNT_RAYS_SHADOW_TRANSP, CNT_RAYS_LIGHT_PROBE,
+       CNT_CAMERA_SAMPLES, CNT_NODES, CNT_TRIS, CNT_N };
+
+#define YG_MAX_ITERS 96
+
+struct WaveCtl // lives in device memory, zeroed at wave start
+{
+	int n_tasks[YG_MAX_ITERS + 2];   // number of tasks queued for iteration i
+	int n_shadow[YG_MAX_ITERS + 2];  // number of shadow rays queued by iteration i
+	int overflow;                     // a queue ran out of capacity: the wave is discarded and retried smaller
+	int pad;
+};
+
+struct Wavefront
+{
+	TaskQueue q[2];
+	ShadowQueue sq;
+	float4 *acc = nullptr;        // per camera sample: rgb sum, alpha
+	uint32_t *pixels = nullptr;   // pass pixel list: x | y << 16
+	size_t pixels_cap = 0;
+	WaveCtl *ctl = nullptr;
+	WaveCtl *h_ctl = nullptr;     // pinned mirror
+	int wave_cap = 0;             // camera samples per wave
+	int task_cap = 0;             // tasks per queue
+	int shadow_cap = 0;           // shadow rays per iteration
+	bool allocated = false;
+};
+
+} // namespace yg

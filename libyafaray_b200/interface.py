@@ -1,0 +1,516 @@
+"""Host-side mirror of the reference's scene-building API.
+
+`Interface` follows `yafaray4::Interface` (/root/reference/include/interface/interface.h:48-139,
+/root/reference/src/interface/interface.cc:121-457): the same imperative calls (startScene, startTriMesh, addVertex,
+addTriangle, paramsSet*, create{Material,Light,Camera,Background,Integrator}, render) with the same argument meaning,
+and the same parameter keys and in-code defaults the reference's factories use (cited per factory below).
+
+It produces two things from one description:
+  * `to_xml(path)`   — the reference's XML scene format (as parsed by /root/reference/src/common/import_xml.cc), so the
+                       oracle renders exactly the same scene through the unchanged XML loader;
+  * `scene_desc()`   — the flattened POD descriptor of include/yafgpu.h, handed to the CUDA library through the C ABI.
+This module never computes a pixel: all rendering happens in libyafgpu.so.
+"""
+import ctypes as C
+import numpy as np
+
+from . import capi
+
+
+class _Mesh:
+    def __init__(self, oid, has_orco, has_uv, typ, pass_index):
+        self.id, self.has_orco, self.has_uv, self.type, self.pass_index = oid, has_orco, has_uv, typ, pass_index
+        self.points, self.normals, self.uvs = [], [], []   # points: interleaved with orco when has_orco
+        self.faces, self.face_uv, self.face_mat = [], [], []
+        self.np_points = self.np_faces = self.np_normals = None  # bulk path
+        self.np_mat = None
+        self.smooth_angle = None
+        self.normals_exported = False
+
+    def n_tris(self):
+        return len(self.np_faces) if self.np_faces is not None else len(self.faces)
+
+
+class Interface:
+    """Python mirror of yafaray4::Interface (see module docstring)."""
+
+    def __init__(self):
+        self.params, self.eparams, self._cparams = {}, [], None
+        self._cparams = self.params
+        self.materials, self.lights, self.cameras, self.backgrounds, self.integrators, self.textures = {}, {}, {}, {}, {}, {}
+        self.meshes = {}
+        self._cur = None
+        self._next_free_id = 2 ** 31 - 1  # scene.cc:42 state_.next_free_id_ = INT_MAX, counting down
+        self.render_params = None
+        self.scene_type = 0
+
+    # ---- ParamMap building (interface.cc:239-321) -----------------------------------------------------------------
+    def paramsSetPoint(self, name, x, y, z): self._cparams[name] = ("point", (float(x), float(y), float(z)))
+    def paramsSetString(self, name, s): self._cparams[name] = ("string", str(s))
+    def paramsSetBool(self, name, b): self._cparams[name] = ("bool", bool(b))
+    def paramsSetInt(self, name, i): self._cparams[name] = ("int", int(i))
+    def paramsSetFloat(self, name, f): self._cparams[name] = ("float", float(f))
+    def paramsSetColor(self, name, r, g, b, a=1.0): self._cparams[name] = ("color", (float(r), float(g), float(b), float(a)))
+
+    def paramsClearAll(self):
+        self.params, self.eparams = {}, []
+        self._cparams = self.params
+
+    def paramsStartList(self):
+        self.eparams.append({})
+        self._cparams = self.eparams[-1]
+
+    def paramsPushList(self):
+        self.eparams.append({})
+        self._cparams = self.eparams[-1]
+
+    def paramsEndList(self): self._cparams = self.params
+
+    # ---- scene (interface.cc:121-237) -----------------------------------------------------------------------------
+    def startScene(self, type=0):
+        self.scene_type = type
+        return True
+
+    def startGeometry(self): return True
+    def endGeometry(self): return True
+
+    def getNextFreeId(self):
+        i = self._next_free_id
+        self._next_free_id -= 1
+        return i
+
+    def startTriMesh(self, id, vertices, triangles, has_orco, has_uv=False, type=0, obj_pass_index=0):
+        if id in self.meshes:
+            return False
+        self._cur = _Mesh(id, bool(has_orco), bool(has_uv), type, obj_pass_index)
+        self.meshes[id] = self._cur
+        return True
+
+    def endTriMesh(self):
+        self._cur = None
+        return True
+
+    def addVertex(self, x, y, z, ox=None, oy=None, oz=None):
+        m = self._cur
+        m.points.append((x, y, z))
+        if m.has_orco:
+            m.points.append((ox, oy, oz))
+            return (len(m.points) - 1) // 2
+        return len(m.points) - 1
+
+    def addNormal(self, nx, ny, nz):
+        # Scene::addNormal: attaches to the last vertex, marks normals_exported_ (scene.cc:236-262)
+        m = self._cur
+        m.normals.append((nx, ny, nz))
+        m.normals_exported = True
+
+    def addUv(self, u, v):
+        self._cur.uvs.append((u, v))
+        return len(self._cur.uvs) - 1
+
+    def addTriangle(self, a, b, c, *rest):
+        m = self._cur
+        if len(rest) == 1:
+            mat = rest[0]
+            uv = None
+        else:
+            uv, mat = tuple(rest[:3]), rest[3]
+        m.faces.append((a, b, c))
+        m.face_uv.append(uv)
+        m.face_mat.append(mat)
+        return True
+
+    def addTriMeshArrays(self, id, points, faces, mat, normals=None, obj_pass_index=0):
+        """Bulk equivalent of startTriMesh/addVertex*/addTriangle*/endTriMesh for large procedural meshes
+        (points float32 [nv,3], faces int32 [nt,3], one material name or an int32 [nt] array of indices into
+        `mat` when `mat` is a list of names)."""
+        m = _Mesh(id, False, False, 0, obj_pass_index)
+        m.np_points = np.ascontiguousarray(points, dtype=np.float32)
+        m.np_faces = np.ascontiguousarray(faces, dtype=np.int32)
+        m.np_normals = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32)
+        m.normals_exported = normals is not None
+        m.np_mat = mat
+        self.meshes[id] = m
+        return True
+
+    def smoothMesh(self, id, angle):
+        raise NotImplementedError("smoothMesh: pass explicit vertex normals (addNormal); the reference-side adaptor "
+                                  "exports the normals Scene::smoothMesh produced (scene.cc:420-539)")
+
+    # ---- factories (interface.cc:323-372): store the ParamMap under the name ---------------------------------------
+    def _take(self):
+        p, e = dict(self.params), [dict(x) for x in self.eparams]
+        return p, e
+
+    def createMaterial(self, name):
+        self.materials[name] = self._take()
+        return name
+
+    def createLight(self, name):
+        self.lights[name] = self._take()[0]
+        return name
+
+    def createCamera(self, name):
+        self.cameras[name] = self._take()[0]
+        return name
+
+    def createBackground(self, name):
+        self.backgrounds[name] = self._take()[0]
+        return name
+
+    def createIntegrator(self, name):
+        self.integrators[name] = self._take()[0]
+        return name
+
+    def setRenderParams(self):
+        """What Interface::render does with the current ParamMap (interface.cc:395-404): they become the <render> block."""
+        self.render_params = dict(self.params)
+
+    def render(self, output=None):
+        from .render import render_scene
+        self.setRenderParams()
+        return render_scene(self, output)
+
+    # ---- XML export (format parsed by /root/reference/src/common/import_xml.cc:227-776) ---------------------------
+    @staticmethod
+    def _xml_param(name, tv, indent="\t"):
+        t, v = tv
+        if t == "point": return '%s<%s x="%r" y="%r" z="%r"/>\n' % (indent, name, v[0], v[1], v[2])
+        if t == "color": return '%s<%s r="%r" g="%r" b="%r" a="%r"/>\n' % (indent, name, v[0], v[1], v[2], v[3])
+        if t == "string": return '%s<%s sval="%s"/>\n' % (indent, name, v)
+        if t == "bool": return '%s<%s bval="%s"/>\n' % (indent, name, "true" if v else "false")
+        if t == "int": return '%s<%s ival="%d"/>\n' % (indent, name, v)
+        if t == "float": return '%s<%s fval="%r"/>\n' % (indent, name, v)
+        raise ValueError(t)
+
+    def to_xml(self, path):
+        if self.render_params is None:
+            self.setRenderParams()
+        w = []
+        w.append('<?xml version="1.0"?>\n<scene type="%s">\n\n' % ("triangle" if self.scene_type == 0 else "universal"))
+        for name, (p, e) in self.materials.items():
+            w.append('<material name="%s">\n' % name)
+            for k, tv in p.items(): w.append(self._xml_param(k, tv))
+            for le in e:
+                w.append("\t<list_element>\n")
+                for k, tv in le.items(): w.append(self._xml_param(k, tv, "\t\t"))
+                w.append("\t</list_element>\n")
+            w.append("</material>\n\n")
+        for tag, table in (("light", self.lights), ("camera", self.cameras), ("background", self.backgrounds),
+                           ("integrator", self.integrators)):
+            for name, p in table.items():
+                w.append('<%s name="%s">\n' % (tag, name))
+                for k, tv in p.items(): w.append(self._xml_param(k, tv))
+                w.append("</%s>\n\n" % tag)
+        for oid in sorted(self.meshes):
+            m = self.meshes[oid]
+            if m.np_faces is not None:
+                raise NotImplementedError("bulk meshes are not exported to XML (use startTriMesh/addVertex for oracle scenes)")
+            nv = len(m.points) // 2 if m.has_orco else len(m.points)
+            w.append('<mesh id="%d" vertices="%d" faces="%d" has_orco="%s" has_uv="%s" type="%d" obj_pass_index="%d">\n'
+                     % (oid, nv, len(m.faces), "true" if m.has_orco else "false", "true" if m.has_uv else "false", m.type, m.pass_index))
+            for i in range(nv):
+                if m.has_orco:
+                    p, o = m.points[2 * i], m.points[2 * i + 1]
+                    w.append('\t<p x="%r" y="%r" z="%r" ox="%r" oy="%r" oz="%r"/>\n' % (p[0], p[1], p[2], o[0], o[1], o[2]))
+                else:
+                    p = m.points[i]
+                    w.append('\t<p x="%r" y="%r" z="%r"/>\n' % (p[0], p[1], p[2]))
+                if m.normals_exported:
+                    n = m.normals[i]
+                    w.append('\t<n x="%r" y="%r" z="%r"/>\n' % (n[0], n[1], n[2]))
+            for u, v in m.uvs:
+                w.append('\t<uv u="%r" v="%r"/>\n' % (u, v))
+            cur = None
+            for f, uv, mat in zip(m.faces, m.face_uv, m.face_mat):
+                if mat != cur:
+                    w.append('\t<set_material sval="%s"/>\n' % mat)
+                    cur = mat
+                if uv is None: w.append('\t<f a="%d" b="%d" c="%d"/>\n' % f)
+                else: w.append('\t<f a="%d" b="%d" c="%d" uv_a="%d" uv_b="%d" uv_c="%d"/>\n' % (f + uv))
+            w.append("</mesh>\n\n")
+        w.append("<render>\n")
+        for k, tv in self.render_params.items(): w.append(self._xml_param(k, tv))
+        w.append("</render>\n</scene>\n")
+        with open(path, "w") as fh:
+            fh.write("".join(w))
+        return path
+
+    # ---- flattening to the C ABI descriptor ----------------------------------------------------------------------
+    @staticmethod
+    def _g(p, key, default):
+        """ParamMap::getParam semantics: missing key keeps the in-code default (include/common/param.h:91-106)."""
+        if key not in p:
+            return default
+        return p[key][1]
+
+    def _material_record(self, name, index_of):
+        p, _e = self.materials[name]
+        g = self._g
+        t = g(p, "type", "")
+        m = capi.Material()
+        vis = {"normal": capi.VIS_NORMAL, "no_shadows": capi.VIS_NO_SHADOWS, "shadow_only": capi.VIS_SHADOW_ONLY,
+               "invisible": capi.VIS_INVISIBLE}.get(g(p, "visibility", "normal"), capi.VIS_NORMAL)
+        m.visibility = vis
+        m.receive_shadows = int(g(p, "receive_shadows", True))
+        m.flat_material = int(g(p, "flat_material", False))
+        m.additional_depth = int(g(p, "additionaldepth", 0))
+        m.transparent_bias_factor = g(p, "transparentbias_factor", 0.0)
+        m.transparent_bias_multiply_raydepth = int(g(p, "transparentbias_multiply_raydepth", False))
+        m.sampling_factor = g(p, "samplingfactor", 1.0)
+        m.mat_pass_index = int(g(p, "mat_pass_index", 0))
+        for k in p:
+            if k.endswith("_shader"):
+                raise NotImplementedError("material '%s': shader nodes (%s) are not implemented on the device" % (name, k))
+        col = lambda key, d: capi.F3(*[np.float32(x) for x in g(p, key, d)[:3]])
+        if t == "shinydiffusemat":  # material_shiny_diffuse.cc:599-688
+            m.type = capi.MAT_SHINYDIFFUSE
+            s = m.u.shinydiffuse
+            s.color, s.mirror_color = col("color", (1, 1, 1, 1)), col("mirror_color", (1, 1, 1, 1))
+            s.diffuse_reflect, s.specular_reflect = g(p, "diffuse_reflect", 1.0), g(p, "specular_reflect", 0.0)
+            s.transparency, s.translucency, s.emit = g(p, "transparency", 0.0), g(p, "translucency", 0.0), g(p, "emit", 0.0)
+            s.ior, s.fresnel_effect = g(p, "IOR", 1.33), int(g(p, "fresnel_effect", False))
+            s.transmit_filter = g(p, "transmit_filter", 1.0)
+            s.oren_nayar = int(g(p, "diffuse_brdf", "") == "oren_nayar")
+            s.sigma = g(p, "sigma", 0.1)
+        elif t in ("glass", "rough_glass"):  # material_glass.cc:311-379, material_rough_glass.cc:322-401
+            m.type = capi.MAT_GLASS if t == "glass" else capi.MAT_ROUGH_GLASS
+            s = m.u.glass
+            s.ior = g(p, "IOR", 1.4)
+            s.filter_color, s.mirror_color = col("filter_color", (1, 1, 1, 1)), col("mirror_color", (1, 1, 1, 1))
+            s.transmit_filter, s.dispersion_power = g(p, "transmit_filter", 0.0), g(p, "dispersion_power", 0.0)
+            s.fake_shadows = int(g(p, "fake_shadows", False))
+            s.alpha = g(p, "alpha", 0.5)
+            ab = g(p, "absorption", (1, 1, 1, 1))
+            s.has_absorption = int("absorption" in p and min(ab[:3]) < 1.0)
+            s.absorption = capi.F3(*[np.float32(x) for x in ab[:3]])
+            s.absorption_dist = g(p, "absorption_dist", 1.0)
+        elif t in ("glossy", "coated_glossy"):  # material_glossy.cc:407-480, material_coated_glossy.cc:465-545
+            m.type = capi.MAT_GLOSSY if t == "glossy" else capi.MAT_COATED_GLOSSY
+            s = m.u.glossy
+            s.color, s.diffuse_color = col("color", (1, 1, 1, 1)), col("diffuse_color", (1, 1, 1, 1))
+            s.mirror_color = col("mirror_color", (1, 1, 1, 1))
+            s.diffuse_reflect, s.glossy_reflect = g(p, "diffuse_reflect", 0.0), g(p, "glossy_reflect", 1.0 if t == "glossy" else 0.0)
+            s.specular_reflect = g(p, "specular_reflect", 0.0)
+            s.exponent, s.exp_u, s.exp_v = g(p, "exponent", 50.0), g(p, "exp_u", 50.0), g(p, "exp_v", 50.0)
+            s.ior = g(p, "IOR", 1.4)
+            s.as_diffuse, s.anisotropic = int(g(p, "as_diffuse", False)), int(g(p, "anisotropic", False))
+            s.oren_nayar = int(g(p, "diffuse_brdf", "") == "Oren-Nayar")
+            s.sigma = g(p, "sigma", 0.1)
+        elif t == "blend_mat":  # material_blend.cc:464-518
+            m.type = capi.MAT_BLEND
+            m.u.blend.material1 = index_of(g(p, "material1", ""))
+            m.u.blend.material2 = index_of(g(p, "material2", ""))
+            m.u.blend.blend_value = g(p, "blend_value", 0.5)
+        elif t == "light_mat":  # material_simple.cc:63-73
+            m.type = capi.MAT_LIGHT
+            m.u.simple.color = col("color", (1, 1, 1, 1))
+            m.u.simple.strength = g(p, "power", 1.0)
+            m.u.simple.double_sided = int(g(p, "double_sided", False))
+        elif t == "null":
+            m.type = capi.MAT_NULL
+        else:
+            raise NotImplementedError("material type '%s'" % t)
+        return m
+
+    def _light_record(self, p, obj_index_of_id):
+        g = self._g
+        t = g(p, "type", "")
+        l = capi.Light()
+        l.light_enabled, l.cast_shadows = int(g(p, "light_enabled", True)), int(g(p, "cast_shadows", True))
+        l.photon_only = int(g(p, "photon_only", False))
+        l.shoot_caustic, l.shoot_diffuse = int(g(p, "with_caustic", True)), int(g(p, "with_diffuse", True))
+        l.color = capi.F3(*[np.float32(x) for x in g(p, "color", (1, 1, 1, 1))[:3]])
+        l.power = g(p, "power", 1.0)
+        l.samples = int(g(p, "samples", 4))
+        l.object = -1
+        pt = lambda key, d: capi.F3(*[np.float32(x) for x in g(p, key, d)])
+        if t == "pointlight":  # light_point.cc:101-133
+            l.type, l.from_ = capi.LIGHT_POINT, pt("from", (0, 0, 0))
+        elif t == "sunlight":  # light_sun.cc:95-125
+            l.type, l.from_, l.angle = capi.LIGHT_SUN, pt("direction", (0, 0, 1)), g(p, "angle", 0.27)
+        elif t == "arealight":  # light_area.cc:174-213
+            l.type = capi.LIGHT_AREA
+            l.from_, l.point1, l.point2 = pt("corner", (0, 0, 0)), pt("point1", (0, 0, 0)), pt("point2", (0, 0, 0))
+            l.object = obj_index_of_id(int(g(p, "object", 0)))
+        elif t == "meshlight":  # light_meshlight.cc:228-263
+            l.type = capi.LIGHT_MESH
+            l.object = obj_index_of_id(int(g(p, "object", 0)))
+            l.double_sided = int(g(p, "double_sided", False))
+        else:
+            raise NotImplementedError("light type '%s'" % t)
+        return l
+
+    def scene_desc(self):
+        """Flatten to capi.SceneDesc.  Returns (desc, keepalive) — keepalive owns the numpy/ctypes buffers."""
+        if self.render_params is None:
+            self.setRenderParams()
+        g, rp = self._g, self.render_params
+        keep = []
+        mat_names = list(self.materials.keys())
+        mat_index = {n: i for i, n in enumerate(mat_names)}
+
+        def index_of(n):
+            if n not in mat_index:
+                raise KeyError("unknown material '%s'" % n)
+            return mat_index[n]
+        mats = (capi.Material * max(1, len(mat_names)))()
+        for i, n in enumerate(mat_names):
+            mats[i] = self._material_record(n, index_of)
+
+        # geometry in the reference's global triangle order: ascending object id (scene.cc:796-817)
+        pts, nrm, uvs, vidx, nidx, uvidx, tmat, tobj, objs = [], [], [], [], [], [], [], [], []
+        p_off = n_off = uv_off = t_off = 0
+        any_n = any_uv = False
+        obj_index = {}
+        for oid in sorted(self.meshes):
+            m = self.meshes[oid]
+            if (m.type & 0xFF) != 0:
+                raise NotImplementedError("only TRIM meshes (type 0) are supported")
+            if m.type & 0x0100 or m.type & 0x0200:  # INVISIBLEM / BASEMESH are skipped by Scene::update (scene.cc:799-800)
+                continue
+            o = capi.Object()
+            o.has_orco, o.has_uv, o.smooth, o.light = int(m.has_orco), int(m.has_uv), int(m.normals_exported), -1
+            o.first_tri, o.obj_id, o.pass_index = t_off, oid & 0x7fffffff, m.pass_index
+            obj_index[oid] = len(objs)
+            if m.np_faces is not None:
+                P, F = m.np_points, m.np_faces
+                nt = len(F)
+                pts.append(P)
+                vidx.append(F + p_off)
+                if m.np_normals is not None:
+                    nrm.append(m.np_normals); nidx.append(F + n_off); n_off += len(m.np_normals); any_n = True
+                else:
+                    nidx.append(np.full((nt, 3), -1, np.int32))
+                uvidx.append(np.full((nt, 3), -1, np.int32))
+                if isinstance(m.np_mat, str):
+                    tmat.append(np.full(nt, index_of(m.np_mat), np.int32))
+                else:
+                    names, per_tri = m.np_mat
+                    lut = np.array([index_of(n) for n in names], np.int32)
+                    tmat.append(lut[np.asarray(per_tri)])
+                p_off += len(P)
+            else:
+                P = np.array(m.points, np.float32).reshape(-1, 3)
+                F = np.array(m.faces, np.int32).reshape(-1, 3)
+                nt = len(F)
+                stride = 2 if m.has_orco else 1  # Scene::addTriangle doubles the indices with orco (scene.cc:615)
+                pts.append(P)
+                vidx.append(F * stride + p_off)
+                if m.normals_exported:
+                    # normals_ is resized to points_.size() and indexed by vertex id (scene.cc:594-604,619-633)
+                    N = np.zeros((len(P), 3), np.float32)
+                    nn = np.array(m.normals, np.float32).reshape(-1, 3)
+                    N[:len(nn)] = nn
+                    nrm.append(N); nidx.append(F + n_off); n_off += len(N); any_n = True
+                else:
+                    nidx.append(np.full((nt, 3), -1, np.int32))
+                if m.has_uv:
+                    UV = np.array(m.uvs, np.float32).reshape(-1, 2)
+                    uvs.append(UV)
+                    uvidx.append(np.array([u for u in m.face_uv], np.int32).reshape(-1, 3) + uv_off)
+                    uv_off += len(UV); any_uv = True
+                else:
+                    uvidx.append(np.full((nt, 3), -1, np.int32))
+                tmat.append(np.array([index_of(n) for n in m.face_mat], np.int32))
+                p_off += len(P)
+            tobj.append(np.full(nt, len(objs), np.int32))
+            o.n_tris = nt
+            t_off += nt
+            objs.append(o)
+
+        def cat(lst, shape, dt):
+            a = np.concatenate(lst).astype(dt, copy=False) if lst else np.zeros(shape, dt)
+            a = np.ascontiguousarray(a)
+            keep.append(a)
+            return a
+        A_pts, A_nrm, A_uv = cat(pts, (0, 3), np.float32), cat(nrm, (0, 3), np.float32), cat(uvs, (0, 2), np.float32)
+        A_v, A_n, A_u = cat(vidx, (0, 3), np.int32), cat(nidx, (0, 3), np.int32), cat(uvidx, (0, 3), np.int32)
+        A_m, A_o = cat(tmat, (0,), np.int32), cat(tobj, (0,), np.int32)
+        objarr = (capi.Object * max(1, len(objs)))(*objs)
+        pfl = lambda a: a.ctypes.data_as(capi.pf)
+        pin = lambda a: a.ctypes.data_as(capi.pi)
+        d = capi.SceneDesc()
+        d.abi_version = capi.ABI_VERSION
+        ge = d.geometry
+        ge.points, ge.n_points = pfl(A_pts), len(A_pts)
+        ge.normals, ge.n_normals = pfl(A_nrm), len(A_nrm)
+        ge.uv, ge.n_uv = pfl(A_uv), len(A_uv)
+        ge.tri_vidx, ge.tri_mat, ge.tri_obj, ge.n_tris = pin(A_v), pin(A_m), pin(A_o), len(A_m)
+        ge.tri_nidx = pin(A_n) if any_n else None
+        ge.tri_uvidx = pin(A_u) if any_uv else None
+        ge.objects, ge.n_objects = objarr, len(objs)
+        d.materials, d.n_materials = mats, len(mat_names)
+
+        def obj_index_of_id(oid):
+            return obj_index.get(oid, -1) if oid else -1
+        lts = [self._light_record(p, obj_index_of_id) for p in self.lights.values()]
+        larr = (capi.Light * max(1, len(lts)))(*lts)
+        d.lights, d.n_lights = larr, len(lts)
+        keep += [mats, objarr, larr]
+
+        # camera "perspective" (camera_perspective.cc:206-252)
+        cp = self.cameras[g(rp, "camera_name", next(iter(self.cameras)))]
+        if g(cp, "type", "") != "perspective":
+            raise NotImplementedError("camera type '%s'" % g(cp, "type", ""))
+        c = d.camera
+        c.type, c.resx, c.resy = capi.CAM_PERSPECTIVE, int(g(cp, "resx", 320)), int(g(cp, "resy", 200))
+        c.from_ = capi.F3(*[np.float32(x) for x in g(cp, "from", (0, 1, 0))])
+        c.to = capi.F3(*[np.float32(x) for x in g(cp, "to", (0, 0, 0))])
+        c.up = capi.F3(*[np.float32(x) for x in g(cp, "up", (0, 1, 1))])
+        c.focal, c.aperture, c.dof_distance = g(cp, "focal", 1.0), g(cp, "aperture", 0.0), g(cp, "dof_distance", 0.0)
+        c.aspect_ratio, c.near_clip, c.far_clip = g(cp, "aspect_ratio", 1.0), g(cp, "nearClip", 0.0), g(cp, "farClip", -1.0)
+        c.bokeh_type, c.bokeh_bias = capi.BK.get(g(cp, "bokeh_type", "disk1"), 0), capi.BB.get(g(cp, "bokeh_bias", "uniform"), 0)
+        c.bokeh_rotation = g(cp, "bokeh_rotation", 0.0)
+
+        # background (background_constant.cc:52-86)
+        b = d.background
+        b.type = capi.BG_NONE
+        bname = g(rp, "background_name", None)
+        if bname is not None and bname in self.backgrounds:
+            bp = self.backgrounds[bname]
+            if g(bp, "type", "") != "constant":
+                raise NotImplementedError("background type '%s'" % g(bp, "type", ""))
+            b.type = capi.BG_CONSTANT
+            b.color = capi.F3(*[np.float32(x) for x in g(bp, "color", (0, 0, 0, 1))[:3]])
+            b.power, b.ibl, b.with_caustic = g(bp, "power", 1.0), int(g(bp, "ibl", False)), int(g(bp, "with_caustic", True))
+
+        # film + AA (environment.cc:456-584, 679-813)
+        f = d.film
+        f.width, f.height = int(g(rp, "width", 320)), int(g(rp, "height", 240))
+        f.xstart, f.ystart = int(g(rp, "xstart", 0)), int(g(rp, "ystart", 0))
+        f.aa_pixelwidth = g(rp, "AA_pixelwidth", 1.5)
+        f.filter_type = capi.FILTERS.get(g(rp, "filter_type", "box"), 0)
+        f.tile_size, f.premult = int(g(rp, "tile_size", 32)), int(g(rp, "premult", False))
+        f.aa_clamp_samples, f.aa_clamp_indirect = g(rp, "AA_clamp_samples", 0.0), g(rp, "AA_clamp_indirect", 0.0)
+        f.aa_passes = int(g(rp, "AA_passes", 1))
+        f.aa_light_sample_multiplier = f.aa_indirect_sample_multiplier = 1.0
+        f.base_sampling_offset = int(g(rp, "adv_base_sampling_offset", 0)) + int(g(rp, "adv_computer_node", 0)) * 100000
+
+        # integrator (integrator_path_tracer.cc:349-423, integrator_direct_light.cc:196-250)
+        ip = self.integrators[g(rp, "integrator_name", next(iter(self.integrators)))]
+        it = d.integrator
+        tname = g(ip, "type", "")
+        if tname == "pathtracing":
+            it.type = capi.INT_PATHTRACING
+            it.raydepth, it.shadow_depth = int(g(ip, "raydepth", 5)), int(g(ip, "shadowDepth", 5))
+            it.path_samples, it.bounces = int(g(ip, "path_samples", 32)), int(g(ip, "bounces", 3))
+            it.rr_min_bounces, it.no_recursive = int(g(ip, "russian_roulette_min_bounces", 0)), int(g(ip, "no_recursive", False))
+            cm = g(ip, "caustic_type", "path")
+            if cm in ("photon", "both"):
+                raise NotImplementedError("caustic photon maps are out of scope (SURVEY.md §8f #4)")
+            it.trace_caustics = int(cm != "none")  # ctor default caustic_type_ = Path (integrator_path_tracer.cc:35)
+        elif tname == "directlighting":
+            it.type = capi.INT_DIRECTLIGHT
+            it.raydepth, it.shadow_depth = int(g(ip, "raydepth", 5)), int(g(ip, "shadowDepth", 5))
+            if g(ip, "caustics", False):
+                raise NotImplementedError("caustic photon maps are out of scope (SURVEY.md §8f #4)")
+        else:
+            raise NotImplementedError("integrator type '%s'" % tname)
+        it.transp_shad = int(g(ip, "transpShad", False))
+        it.bg_transp, it.bg_transp_refract = int(g(ip, "bg_transp", False)), int(g(ip, "bg_transp_refract", False))
+        it.do_ao, it.ao_samples, it.ao_distance = int(g(ip, "do_AO", False)), int(g(ip, "AO_samples", 32)), g(ip, "AO_distance", 1.0)
+        it.ao_color = capi.F3(*[np.float32(x) for x in g(ip, "AO_color", (1, 1, 1, 1))[:3]])
+        it.shadow_bias_auto, it.shadow_bias = int(g(rp, "adv_auto_shadow_bias_enabled", True)), g(rp, "adv_shadow_bias_value", 0.0005)
+        it.ray_min_dist_auto, it.ray_min_dist = int(g(rp, "adv_auto_min_raydist_enabled", True)), g(rp, "adv_min_raydist_value", 0.00005)
+        return d, keep

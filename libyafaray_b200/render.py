@@ -1,0 +1,160 @@
+"""Host mirror of the reference's render control for the hot path.
+
+`Context` wraps one yafgpu context (one GPU).  `render_scene` follows TiledIntegrator::render
+(/root/reference/src/integrator/integrator_tiled.cc:116-259): pass 0 with AA_minsamples, then AA_passes-1 passes of
+ceil(AA_inc_samples * multiplier) samples with growing sampling offsets.  Adaptive resampling (ImageFilm::nextPass
+flagging) is evaluated on the host film between passes when AA_threshold > 0.
+"""
+import ctypes as C
+import math
+import struct
+
+import numpy as np
+
+from . import capi
+
+
+def _check(ctx, rc):
+    if rc != capi.OK:
+        msg = capi.lib.yafgpu_last_error(ctx)
+        raise capi.YafGpuError(rc, msg.decode() if msg else "?")
+
+
+class Context:
+    """One GPU context of libyafgpu.so (include/yafgpu.h)."""
+
+    def __init__(self, device=0, flags=0):
+        h = C.c_void_p()
+        rc = capi.lib.yafgpu_create(C.byref(h), device, flags)
+        if rc != capi.OK:
+            msg = capi.lib.yafgpu_last_error(None)
+            raise capi.YafGpuError(rc, msg.decode() if msg else "?")
+        self.h = h
+        self.width = self.height = 0
+        self._keep = None
+
+    def close(self):
+        if self.h:
+            capi.lib.yafgpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, desc, keep=None):
+        self._keep = keep
+        _check(self.h, capi.lib.yafgpu_upload_scene(self.h, C.byref(desc)))
+        self.width, self.height = desc.film.width, desc.film.height
+
+    def scene_bound(self):
+        b = (capi.f32 * 6)()
+        _check(self.h, capi.lib.yafgpu_scene_bound(self.h, b))
+        return np.array(b[:], np.float32)
+
+    def trace(self, rays, mode=capi.TRACE_CLOSEST, shadow_depth=2):
+        """rays: float32 [n,8] (from xyz, tmin, dir xyz, tmax). Returns structured hits (t,u,v,tri)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.zeros(len(rays), dtype=[("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("tri", "<i4")])
+        _check(self.h, capi.lib.yafgpu_trace(self.h, rays.ctypes.data, len(rays), hits.ctypes.data, mode, shadow_depth))
+        return hits
+
+    def trace_device(self, d_rays_ptr, n, d_hits_ptr, mode=capi.TRACE_CLOSEST, shadow_depth=2):
+        _check(self.h, capi.lib.yafgpu_trace_device(self.h, d_rays_ptr, n, d_hits_ptr, mode, shadow_depth))
+
+    def film_clear(self):
+        _check(self.h, capi.lib.yafgpu_film_clear(self.h))
+
+    def render_pass(self, n_samples, offset=0, adaptive=False, aa_pass_number=0, mask=None, sample_begin=0, sample_end=0,
+                    part_index=0, part_count=1):
+        p = capi.PassDesc()
+        p.n_samples, p.offset, p.adaptive, p.aa_pass_number = n_samples, offset, int(adaptive), aa_pass_number
+        p.sample_begin, p.sample_end, p.part_index, p.part_count = sample_begin, sample_end, part_index, part_count
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, np.uint8)
+            p.resample_mask = mask.ctypes.data_as(C.POINTER(C.c_uint8))
+        _check(self.h, capi.lib.yafgpu_render_pass(self.h, C.byref(p)))
+
+    def sync(self):
+        _check(self.h, capi.lib.yafgpu_sync(self.h))
+
+    def read_film(self):
+        out = np.empty((self.height, self.width, 5), np.float32)
+        _check(self.h, capi.lib.yafgpu_read_film(self.h, out.ctypes.data))
+        return out
+
+    def write_film(self, film):
+        film = np.ascontiguousarray(film, np.float32)
+        _check(self.h, capi.lib.yafgpu_write_film(self.h, film.ctypes.data))
+
+    def film_device_ptr(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        _check(self.h, capi.lib.yafgpu_film_device_ptr(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def set_aa_multipliers(self, light, indirect):
+        _check(self.h, capi.lib.yafgpu_set_aa_multipliers(self.h, light, indirect))
+
+    def stats(self):
+        s = capi.Stats()
+        _check(self.h, capi.lib.yafgpu_get_stats(self.h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in capi.Stats._fields_}
+
+    def reset_stats(self):
+        _check(self.h, capi.lib.yafgpu_reset_stats(self.h))
+
+    def stream(self):
+        return capi.lib.yafgpu_stream(self.h)
+
+
+def film_to_image(film):
+    """Pixel::normalized (util_image_buffers.h:39-43): col / weight when weight != 0."""
+    w = film[..., 4:5]
+    return np.where(w != 0, film[..., :4] / np.where(w != 0, w, 1), 0).astype(np.float32)
+
+
+def load_film(path):
+    """Read the raw film dump written by oracle/ref_driver/yaf_ref.cc (`YGF1`, w, h, w*h*5 float32)."""
+    with open(path, "rb") as fh:
+        if fh.read(4) != b"YGF1":
+            raise ValueError("not a YGF1 film")
+        w, h = struct.unpack("<ii", fh.read(8))
+        return np.frombuffer(fh.read(), np.float32).reshape(h, w, 5).copy()
+
+
+def render_scene(iface, output=None, device=0, ctx=None):
+    """TiledIntegrator::render pass schedule (integrator_tiled.cc:116-259) driving the GPU passes. Returns the film."""
+    g, rp = iface._g, iface.render_params
+    desc, keep = iface.scene_desc()
+    own = ctx is None
+    if own:
+        ctx = Context(device)
+    ctx.upload(desc, keep)
+    aa_passes, aa_samples = int(g(rp, "AA_passes", 1)), int(g(rp, "AA_minsamples", 1))
+    aa_inc = int(g(rp, "AA_inc_samples", aa_samples))
+    smf = np.float32(g(rp, "AA_sample_multiplier_factor", 1.0))
+    lmf = np.float32(g(rp, "AA_light_sample_multiplier_factor", 1.0))
+    imf = np.float32(g(rp, "AA_indirect_sample_multiplier_factor", 1.0))
+    threshold = g(rp, "AA_threshold", 0.05)
+    base = desc.film.base_sampling_offset
+    ctx.film_clear()
+    ctx.render_pass(aa_samples, 0 + base, False, 0)
+    acum = aa_samples
+    sm, lm, im = np.float32(1), np.float32(1), np.float32(1)
+    for i in range(1, aa_passes):
+        sm, lm, im = np.float32(sm * smf), np.float32(lm * lmf), np.float32(im * imf)
+        ctx.set_aa_multipliers(float(lm), float(im))
+        n = int(math.ceil(np.float32(aa_inc) * sm))
+        if threshold > 0:
+            raise NotImplementedError("adaptive AA (AA_threshold > 0 with AA_passes > 1): set AA_threshold 0")
+        ctx.render_pass(n, acum + base, True, i)  # threshold 0: doMoreSamples() is true for every pixel (imagefilm.cc:917-920)
+        acum += n
+    ctx.sync()
+    film = ctx.read_film()
+    if output is not None:
+        output(film)
+    if own:
+        ctx.close()
+    return film

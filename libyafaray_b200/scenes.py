@@ -1,0 +1,192 @@
+"""Synthetic workloads of BASELINE.json's configs, built through the Interface mirror so that the SAME description
+goes to the CUDA path (scene_desc) and, as XML, to the reference (oracle).  Shapes follow SURVEY.md §8(d).
+"""
+import numpy as np
+
+from .interface import Interface
+
+
+def _quad(y, a, b, c, d, mat):
+    """two triangles a-b-c, a-c-d"""
+    ia, ib, ic, id_ = [y.addVertex(*p) for p in (a, b, c, d)]
+    y.addTriangle(ia, ib, ic, mat)
+    y.addTriangle(ia, ic, id_, mat)
+
+
+def _box(y, lo, hi, mat, rot_deg=0.0):
+    """axis-aligned box rotated about its vertical axis; outward-facing triangles (12)"""
+    cx, cy = 0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1])
+    cs, sn = np.cos(np.radians(rot_deg)), np.sin(np.radians(rot_deg))
+
+    def P(x, yy, z):
+        dx, dy = x - cx, yy - cy
+        return (float(cx + cs * dx - sn * dy), float(cy + sn * dx + cs * dy), float(z))
+    v = [P(lo[0], lo[1], lo[2]), P(hi[0], lo[1], lo[2]), P(hi[0], hi[1], lo[2]), P(lo[0], hi[1], lo[2]),
+         P(lo[0], lo[1], hi[2]), P(hi[0], lo[1], hi[2]), P(hi[0], hi[1], hi[2]), P(lo[0], hi[1], hi[2])]
+    idx = [y.addVertex(*p) for p in v]
+    faces = [(0, 2, 1), (0, 3, 2), (4, 5, 6), (4, 6, 7), (0, 1, 5), (0, 5, 4), (1, 2, 6), (1, 6, 5), (2, 3, 7), (2, 7, 6),
+             (3, 0, 4), (3, 4, 7)]
+    for a, b, c in faces:
+        y.addTriangle(idx[a], idx[b], idx[c], mat)
+
+
+def _shiny(y, name, col, **kw):
+    y.paramsClearAll()
+    y.paramsSetString("type", "shinydiffusemat")
+    y.paramsSetColor("color", *col)
+    for k, v in kw.items():
+        if isinstance(v, bool): y.paramsSetBool(k, v)
+        elif isinstance(v, int): y.paramsSetInt(k, v)
+        elif isinstance(v, float): y.paramsSetFloat(k, v)
+        elif isinstance(v, str): y.paramsSetString(k, v)
+        else: y.paramsSetColor(k, *v)
+    return y.createMaterial(name)
+
+
+def render_block(y, width, height, spp, integrator="pt", camera="cam", background="bg", aa_passes=1, filter_type="box",
+                 pixelwidth=1.5, threads=1, inc_samples=None, **extra):
+    y.paramsClearAll()
+    y.paramsSetString("camera_name", camera)
+    y.paramsSetString("integrator_name", integrator)
+    y.paramsSetString("volintegrator_name", "volintegr")
+    if background:
+        y.paramsSetString("background_name", background)
+    y.paramsSetInt("width", width); y.paramsSetInt("height", height)
+    y.paramsSetInt("AA_passes", aa_passes); y.paramsSetInt("AA_minsamples", spp)
+    y.paramsSetInt("AA_inc_samples", inc_samples if inc_samples is not None else spp)
+    y.paramsSetFloat("AA_threshold", 0.0)
+    y.paramsSetFloat("AA_pixelwidth", pixelwidth)
+    y.paramsSetString("filter_type", filter_type)
+    y.paramsSetString("color_space", "LinearRGB")
+    y.paramsSetString("tiles_order", "linear")
+    y.paramsSetInt("tile_size", 32)
+    y.paramsSetInt("threads", threads)
+    for k, v in extra.items():
+        if isinstance(v, bool): y.paramsSetBool(k, v)
+        elif isinstance(v, int): y.paramsSetInt(k, v)
+        elif isinstance(v, float): y.paramsSetFloat(k, v)
+        else: y.paramsSetString(k, v)
+    y.setRenderParams()
+
+
+def _vol_none(y):
+    y.paramsClearAll()
+    y.paramsSetString("type", "none")
+    y.createIntegrator("volintegr")
+
+
+def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2,
+                light_samples=4, integrator="pathtracing", glass=True, light_power=30.0, filter_type="box",
+                aa_passes=1, extra_point_light=False, transp_shad=False, no_recursive=False, **render_extra):
+    """BASELINE config 2: Cornell box, PathIntegrator, area light, ShinyDiffuse + Glass (36 triangles)."""
+    y = Interface()
+    y.startScene(0)
+    white = _shiny(y, "white", (0.75, 0.75, 0.75))
+    red = _shiny(y, "red", (0.63, 0.065, 0.05))
+    green = _shiny(y, "green", (0.14, 0.45, 0.09))
+    y.paramsClearAll()
+    if glass:
+        y.paramsSetString("type", "glass"); y.paramsSetFloat("IOR", 1.5)
+        y.paramsSetColor("filter_color", 1.0, 1.0, 1.0); y.paramsSetColor("mirror_color", 1.0, 1.0, 1.0)
+        gl = y.createMaterial("glassmat")
+    else:
+        gl = _shiny(y, "glassmat", (0.3, 0.3, 0.7))
+    y.paramsClearAll()
+    y.paramsSetString("type", "light_mat"); y.paramsSetColor("color", 1.0, 1.0, 1.0); y.paramsSetFloat("power", light_power)
+    lm = y.createMaterial("lightmat")
+
+    y.startGeometry()
+    y.startTriMesh(1, 20, 10, False, False, 0)
+    _quad(y, (-1, -1, 0), (1, -1, 0), (1, 1, 0), (-1, 1, 0), white)       # floor (normal +z)
+    _quad(y, (-1, -1, 2), (-1, 1, 2), (1, 1, 2), (1, -1, 2), white)       # ceiling (normal -z)
+    _quad(y, (-1, 1, 0), (1, 1, 0), (1, 1, 2), (-1, 1, 2), white)         # back wall
+    _quad(y, (-1, -1, 0), (-1, 1, 0), (-1, 1, 2), (-1, -1, 2), red)       # left wall
+    _quad(y, (1, -1, 0), (1, -1, 2), (1, 1, 2), (1, 1, 0), green)         # right wall
+    y.endTriMesh()
+    y.startTriMesh(2, 8, 12, False, False, 0)
+    _box(y, (-0.65, 0.05, 0.0), (-0.05, 0.65, 1.2), white, rot_deg=18.0)   # tall diffuse box
+    y.endTriMesh()
+    y.startTriMesh(3, 8, 12, False, False, 0)
+    _box(y, (0.1, -0.55, 0.0), (0.7, 0.05, 0.6), gl, rot_deg=-17.0)        # short glass box
+    y.endTriMesh()
+    y.startTriMesh(20, 4, 2, False, False, 0)
+    z = 1.98
+    _quad(y, (-0.15, -0.15, z), (-0.15, 0.15, z), (0.15, 0.15, z), (0.15, -0.15, z), lm)  # emitter quad, normal -z
+    y.endTriMesh()
+    y.endGeometry()
+
+    y.paramsClearAll()
+    y.paramsSetString("type", "arealight")
+    y.paramsSetPoint("corner", -0.15, -0.15, z)
+    y.paramsSetPoint("point1", -0.15, 0.15, z)
+    y.paramsSetPoint("point2", 0.15, -0.15, z)
+    y.paramsSetColor("color", 1.0, 1.0, 1.0); y.paramsSetFloat("power", light_power)
+    y.paramsSetInt("samples", light_samples); y.paramsSetInt("object", 20)
+    y.createLight("ceiling")
+    if extra_point_light:
+        y.paramsClearAll()
+        y.paramsSetString("type", "pointlight"); y.paramsSetPoint("from", 0.5, -0.6, 1.5)
+        y.paramsSetColor("color", 1.0, 0.9, 0.8); y.paramsSetFloat("power", 1.5)
+        y.createLight("fill")
+
+    y.paramsClearAll()
+    y.paramsSetString("type", "perspective")
+    y.paramsSetPoint("from", 0.0, -3.9, 1.0); y.paramsSetPoint("to", 0.0, 0.0, 1.0); y.paramsSetPoint("up", 0.0, -3.9, 2.0)
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.1)
+    y.createCamera("cam")
+
+    y.paramsClearAll()
+    y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.02, 0.02, 0.03); y.paramsSetFloat("power", 1.0)
+    y.createBackground("bg")
+
+    y.paramsClearAll()
+    y.paramsSetString("type", integrator)
+    y.paramsSetInt("raydepth", raydepth); y.paramsSetInt("shadowDepth", 4); y.paramsSetBool("transpShad", transp_shad)
+    if integrator == "pathtracing":
+        y.paramsSetInt("path_samples", path_samples); y.paramsSetInt("bounces", bounces)
+        y.paramsSetInt("russian_roulette_min_bounces", rr_min_bounces); y.paramsSetBool("no_recursive", no_recursive)
+    y.createIntegrator("pt")
+    _vol_none(y)
+    render_block(y, width, height, spp, filter_type=filter_type, aa_passes=aa_passes, **render_extra)
+    return y
+
+
+def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting", filter_type="gauss"):
+    """Small DirectLight + point-light scene in the spirit of BASELINE config 1 (tests/test01 geometry is 6 cubes on
+    a ground quad lit by one point light; its textures are 'next' scope, so flat colours are used)."""
+    y = Interface()
+    y.startScene(0)
+    ground = _shiny(y, "ground", (0.8, 0.8, 0.8))
+    cols = [(0.9, 0.2, 0.2), (0.2, 0.9, 0.2), (0.2, 0.2, 0.9), (0.9, 0.9, 0.2), (0.9, 0.2, 0.9), (0.2, 0.9, 0.9)]
+    mats = [_shiny(y, "cube%d" % i, c, diffuse_reflect=0.5 + 0.1 * (i % 3)) for i, c in enumerate(cols)]
+    y.startGeometry()
+    for i in range(6):
+        y.startTriMesh(1 + i, 8, 12, False, False, 0)
+        x0, y0 = -4.4 + 2.6 * (i % 3), 1.4 - 3.4 * (i // 3)
+        _box(y, (x0, y0, 1e-5), (x0 + 2.0, y0 + 2.0, 2.0), mats[i], rot_deg=7.0 * i)
+        y.endTriMesh()
+    y.startTriMesh(7, 4, 2, False, False, 0)
+    _quad(y, (-10, -10, 0), (10, -10, 0), (10, 10, 0), (-10, 10, 0), ground)
+    y.endTriMesh()
+    y.endGeometry()
+    y.paramsClearAll()
+    y.paramsSetString("type", "pointlight"); y.paramsSetPoint("from", 5.27648, -4.88993, 8.89514)
+    y.paramsSetColor("color", 1.0, 1.0, 1.0); y.paramsSetFloat("power", 72.0)
+    y.createLight("Point")
+    y.paramsClearAll()
+    y.paramsSetString("type", "perspective")
+    y.paramsSetPoint("from", 8.64791, -7.22615, 8.1295); y.paramsSetPoint("to", 8.03447, -6.65603, 7.58301)
+    y.paramsSetPoint("up", 8.25644, -6.8447, 8.9669)
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.09375)
+    y.createCamera("cam")
+    y.paramsClearAll()
+    y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.854296, 0.854296, 0.854296); y.paramsSetFloat("power", 0.5)
+    y.createBackground("bg")
+    y.paramsClearAll()
+    y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", 8); y.paramsSetInt("shadowDepth", 2)
+    if integrator == "pathtracing":
+        y.paramsSetInt("path_samples", 2); y.paramsSetInt("bounces", 3); y.paramsSetInt("russian_roulette_min_bounces", 8)
+    y.createIntegrator("pt")
+    _vol_none(y)
+    render_block(y, width, height, spp, filter_type=filter_type)
+    return y
