@@ -393,7 +393,8 @@ int yafgpu_trace_device(yafgpu_ctx *ctx, const void *d_rays, size_t n, void *d_h
 
 /* ImageFilm::init (imagefilm.cc:219-268): zero the film accumulators. */
 int yafgpu_film_clear(yafgpu_ctx *ctx);
-/* TiledIntegrator::renderPass: trace + shade + ImageFilm::addSample for the pass; asynchronous on the context's stream. */
+/* TiledIntegrator::renderPass: trace + shade + ImageFilm::addSample for the pass (or the sample sub-range given).
+ * Returns when the pass is in the film accumulators (the wave scheduler reads queue counters back after every wave). */
 int yafgpu_render_pass(yafgpu_ctx *ctx, const yafgpu_pass_desc *pass);
 /* Wait for all queued work; returns the first asynchronous error. */
 int yafgpu_sync(yafgpu_ctx *ctx);
@@ -406,6 +407,9 @@ int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
 /* Update per-pass AA multipliers between passes (integrator_tiled.cc:216-218). */
 int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
 
+/* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave, default 2^20),
+ * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8). */
+int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);
 int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
 int yafgpu_reset_stats(yafgpu_ctx *ctx);
 /* Raw CUDA stream handle of the context (cudaStream_t), so callers can time with events on the launching stream. */

@@ -152,6 +152,7 @@ SYMBOLS = {
     "yafgpu_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "yafgpu_write_film": (C.c_int, [C.c_void_p, C.c_void_p]),
     "yafgpu_set_aa_multipliers": (C.c_int, [C.c_void_p, f32, f32]),
+    "yafgpu_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),
     "yafgpu_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "yafgpu_reset_stats": (C.c_int, [C.c_void_p]),
     "yafgpu_stream": (C.c_void_p, [C.c_void_p]),

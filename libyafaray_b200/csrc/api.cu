@@ -36,7 +36,9 @@ static void freeScene(yafgpu_ctx *c)
 	cudaFree(c->d_points); cudaFree(c->d_normals); cudaFree(c->d_uv); cudaFree(c->d_tri_ng); cudaFree(c->d_tri_vidx);
 	cudaFree(c->d_tri_mat); cudaFree(c->d_mat_triflags); cudaFree(c->d_tris); cudaFree(c->d_objects); cudaFree(c->d_mats);
 	cudaFree(c->d_lights); cudaFree(c->d_light_tables); cudaFree(c->d_bg_tex); cudaFree(c->d_nodes); cudaFree(c->d_acc_tris);
-	cudaFree(c->film.pix);
+	cudaFree(c->film.pix); cudaFree(c->d_light_accels); c->d_light_accels = nullptr;
+	for(void *q : c->light_bvh_ptrs) cudaFree(q);
+	c->light_bvh_ptrs.clear();
 	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
 	c->d_tris = nullptr; c->d_objects = nullptr; c->d_mats = nullptr; c->d_lights = nullptr; c->d_light_tables = nullptr; c->d_bg_tex = nullptr;
 	c->d_nodes = nullptr; c->d_acc_tris = nullptr; c->film.pix = nullptr;
@@ -179,17 +181,21 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	for(size_t i = 0; i < desc->n_materials; ++i)
 	{
-		MatDev &m = c->h_mats[i];
-		if(m.type == YAFGPU_MAT_BLEND && (m.mat1 < 0 || m.mat2 < 0 || (size_t)m.mat1 >= desc->n_materials || (size_t)m.mat2 >= desc->n_materials))
-			return setErr(c, YAFGPU_ERR_INVALID, "blend material child index out of range");
-		triflags[i] = triFlagsOf(m);
+		std::string err;
+		if(c->h_mats[i].type == YAFGPU_MAT_BLEND && !finishBlend(c->h_mats, i, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
 	}
-	c->h_lights.assign(desc->n_lights, LightDev());
+	for(size_t i = 0; i < desc->n_materials; ++i) triflags[i] = triFlagsOf(c->h_mats[i]);
+	c->h_lights.clear();
+	std::vector<size_t> light_src; // descriptor index of every kept light; disabled lights are never added (Scene::addLight scene.cc:688-698)
 	for(size_t i = 0; i < desc->n_lights; ++i)
 	{
+		if(!desc->lights[i].light_enabled) continue;
 		std::string err;
-		if(!prepLight(desc->lights[i], c->h_lights[i], err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "light " + std::to_string(i) + ": " + err);
-		if(c->h_lights[i].object >= (int)g.n_objects) return setErr(c, YAFGPU_ERR_INVALID, "light object index out of range");
+		LightDev ld;
+		if(!prepLight(desc->lights[i], ld, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "light " + std::to_string(i) + ": " + err);
+		if(ld.object >= (int)g.n_objects) return setErr(c, YAFGPU_ERR_INVALID, "light object index out of range");
+		if(ld.type == YAFGPU_LIGHT_MESH && ld.object < 0) return setErr(c, YAFGPU_ERR_INVALID, "meshlight without a valid object");
+		c->h_lights.push_back(ld); light_src.push_back(i);
 	}
 	SceneDev &s = c->scene;
 	memset(&s, 0, sizeof(s));
@@ -219,17 +225,28 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	if(bg.type == YAFGPU_BG_CONSTANT) for(int k = 0; k < 3; ++k) s.bg.color[k] = bg.color[k] * bg.power; // background_constant.cc:86
 	else if(bg.type != YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "background type not implemented on the device yet");
 	s.bg.has_ibl = bg.ibl; s.bg.shoots_caustic = bg.with_caustic;
-	if(bg.ibl) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "background IBL light not implemented on the device yet");
+	// light tables: MeshLight::initIs area CDFs, BackgroundLight::init row/column CDFs
+	std::vector<float> light_tab;
+	for(size_t i = 0; i < c->h_lights.size(); ++i)
+	{
+		LightDev &ld = c->h_lights[i];
+		if(ld.type == YAFGPU_LIGHT_MESH) buildMeshLightTables(g, g.objects[ld.object], ld, light_tab);
+		else if(ld.type == YAFGPU_LIGHT_BACKGROUND)
+		{
+			if(bg.type == YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_INVALID, "bglight without a background");
+			buildBgLightTables(s.bg, ld, light_tab);
+		}
+	}
 
 	// tag objects with their light (AreaLight::init light_area.cc:55-63): the LAST light naming the object wins, as setLight overwrites
 	std::vector<ObjDev> objs(g.n_objects ? g.n_objects : 1);
 	for(size_t i = 0; i < g.n_objects; ++i) { objs[i].has_orco = g.objects[i].has_orco; objs[i].has_uv = g.objects[i].has_uv; objs[i].smooth = g.objects[i].smooth; objs[i].light = g.objects[i].light; }
-	for(size_t i = 0; i < desc->n_lights; ++i)
-		if((desc->lights[i].type == YAFGPU_LIGHT_AREA || desc->lights[i].type == YAFGPU_LIGHT_MESH) && desc->lights[i].object >= 0) objs[desc->lights[i].object].light = (int)i;
+	for(size_t i = 0; i < c->h_lights.size(); ++i)
+		if((c->h_lights[i].type == YAFGPU_LIGHT_AREA || c->h_lights[i].type == YAFGPU_LIGHT_MESH) && c->h_lights[i].object >= 0) objs[c->h_lights[i].object].light = (int)i;
 
 	cudaStream_t st = c->stream;
 	c->n_tris = g.n_tris; c->n_points = g.n_points; c->n_normals = g.n_normals; c->n_uv = g.n_uv; c->n_objects = g.n_objects;
-	c->n_mats = desc->n_materials; c->n_lights = desc->n_lights;
+	c->n_mats = desc->n_materials; c->n_lights = c->h_lights.size();
 	int *d_nidx = nullptr, *d_uvidx = nullptr, *d_obj = nullptr;
 	YG_CUDA(c, upload(c->d_points, g.points, g.n_points * 3, st));
 	YG_CUDA(c, upload(c->d_normals, g.normals, g.n_normals * 3, st));
@@ -239,7 +256,6 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, upload(c->d_mat_triflags, triflags.data(), triflags.size(), st));
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
 	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
-	YG_CUDA(c, upload(c->d_lights, c->h_lights.data(), c->h_lights.size(), st));
 	YG_CUDA(c, cudaMalloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1)));
 	YG_CUDA(c, cudaMalloc(&c->d_tris, sizeof(TriShade) * (g.n_tris ? g.n_tris : 1)));
 	if(g.tri_nidx) YG_CUDA(c, upload(d_nidx, g.tri_nidx, g.n_tris * 3, st));
@@ -269,6 +285,26 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		}
 		k_tri_shade<<<(unsigned)((g.n_tris + 255) / 256), 256, 0, st>>>((int)g.n_tris, c->d_tri_vidx, d_nidx, d_uvidx, c->d_tri_mat, d_obj, c->d_tri_ng, c->d_tris);
 	}
+	// mesh lights intersect their own accelerator (MeshLight::initIs builds a private TriKdTree, light_meshlight.cc:72)
+	std::vector<Accel> laccels;
+	for(size_t i = 0; i < c->h_lights.size(); ++i)
+	{
+		LightDev &ld = c->h_lights[i];
+		if(ld.type != YAFGPU_LIGHT_MESH || ld.tri_count <= 0) continue;
+		BvhBuildInput bi; bi.n_tris = ld.tri_count; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx + 3 * (size_t)ld.tri_first;
+		bi.tri_mat = c->d_tri_mat + ld.tri_first; bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng + 3 * (size_t)ld.tri_first;
+		BvhBuildOutput bo;
+		cudaError_t e2 = buildBvh(bi, bo, st);
+		if(e2 != cudaSuccess) { cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj); return cudaErr(c, e2, "buildBvh (mesh light)"); }
+		Accel la; memset(&la, 0, sizeof(la));
+		la.nodes = bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root;
+		c->light_bvh_ptrs.push_back(bo.nodes); c->light_bvh_ptrs.push_back(bo.tris);
+		ld.accel = (int)laccels.size();
+		laccels.push_back(la);
+	}
+	YG_CUDA(c, upload(c->d_light_accels, laccels.data(), laccels.size(), st));
+	YG_CUDA(c, upload(c->d_lights, c->h_lights.data(), c->h_lights.size(), st));
+	YG_CUDA(c, upload(c->d_light_tables, light_tab.data(), light_tab.size(), st));
 	cudaEventRecord(c->ev1, st);
 	cudaError_t e = cudaStreamSynchronize(st);
 	cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj);
@@ -277,7 +313,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	c->stats.bvh_nodes = a.n_nodes; c->stats.bvh_bytes = (uint64_t)a.n_nodes * sizeof(BvhNode); c->stats.tri_bytes = (uint64_t)g.n_tris * sizeof(TriAccel);
 
 	s.points = c->d_points; s.normals = c->d_normals; s.uv = c->d_uv; s.tris = c->d_tris; s.objects = c->d_objects;
-	s.materials = c->d_mats; s.lights = c->d_lights; s.n_lights = (int)desc->n_lights; s.light_tables = c->d_light_tables; s.faure = c->d_faure;
+	s.materials = c->d_mats; s.lights = c->d_lights; s.n_lights = (int)c->h_lights.size(); s.light_tables = c->d_light_tables; s.light_accels = c->d_light_accels; s.faure = c->d_faure;
 
 	// film (ImageFilm ctor + init)
 	prepFilm(desc->film, c->film);
@@ -399,6 +435,15 @@ int yafgpu_set_aa_multipliers(yafgpu_ctx *c, float light_mult, float indirect_mu
 	if(!c || !c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
 	c->scene.integ.aa_light_sample_multiplier = light_mult; c->scene.integ.aa_indirect_sample_multiplier = indirect_mult;
 	return YAFGPU_OK;
+}
+
+int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
+{
+	if(!c || !name) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	const std::string n(name);
+	if(n == "wave_size") { if(value < 1024 || value > (1 << 24)) return setErr(c, YAFGPU_ERR_INVALID, "wave_size out of range"); c->wave_cap_override = (int)value; return YAFGPU_OK; }
+	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
+	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);
 }
 
 int yafgpu_get_stats(yafgpu_ctx *c, yafgpu_stats *out)

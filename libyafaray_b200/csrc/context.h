@@ -23,6 +23,8 @@ struct yafgpu_ctx
 	yg::MatDev *d_mats = nullptr;
 	yg::LightDev *d_lights = nullptr;
 	float *d_light_tables = nullptr;
+	yg::Accel *d_light_accels = nullptr;
+	std::vector<void *> light_bvh_ptrs; // node/triangle arrays of the mesh-light accelerators
 	float *d_bg_tex = nullptr;
 	yg::FaureTables *d_faure = nullptr;
 	yg::BvhNode *d_nodes = nullptr;
@@ -35,6 +37,7 @@ struct yafgpu_ctx
 	std::vector<yg::MatDev> h_mats;
 	std::vector<yg::LightDev> h_lights;
 	int tile_size = 32;
+	int wave_cap_override = 0, task_fan_override = 0; // yafgpu_set_option
 
 	// wavefront state
 	yg::Wavefront wf;

@@ -94,6 +94,23 @@ YG_HD Col operator+(Col a, Col b) { return mkc(a.r + b.r, a.g + b.g, a.b + b.b);
 YG_HD Col operator*(Col a, Col b) { return mkc(a.r * b.r, a.g * b.g, a.b * b.b); }
 YG_HD Col operator*(Col a, float f) { return mkc(a.r * f, a.g * f, a.b * f); }
 YG_HD Col operator*(float f, Col a) { return mkc(a.r * f, a.g * f, a.b * f); }
+YG_HD Col operator/(Col a, float f) { return mkc(a.r / f, a.g / f, a.b / f); }
+// Rgb::clampProportionalRgb color.h:412-447
+YG_HD Col clampProportional(Col c, float max_value)
+{
+	if(max_value > 0.f)
+	{
+		const float max_rgb = fmaxf(c.r, fmaxf(c.g, c.b));
+		const float k = max_value / max_rgb;
+		if(max_rgb > max_value)
+		{
+			if(c.r >= max_rgb) { c.r = max_value; c.g *= k; c.b *= k; }
+			else if(c.g >= max_rgb) { c.g = max_value; c.r *= k; c.b *= k; }
+			else { c.b = max_value; c.r *= k; c.g *= k; }
+		}
+	}
+	return c;
+}
 YG_HD bool isBlack(Col c) { return c.r == 0 && c.g == 0 && c.b == 0; }
 YG_HD float maxc(Col c) { return fmaxf(c.r, fmaxf(c.g, c.b)); }
 

@@ -3,21 +3,14 @@
 // Compiled with -ffp-contract=off; uses the same YG_HD math as the kernels.
 #pragma once
 #include "../../include/yafgpu.h"
-#include "scene_dev.cuh"
+#include "lights.cuh"
 #include <string>
 #include <vector>
 #include <cstring>
 
 namespace yg {
 
-enum : unsigned
-{
-	BsdfNone = 0x0000, BsdfSpecular = 0x0001, BsdfGlossy = 0x0002, BsdfDiffuse = 0x0004, BsdfDispersive = 0x0008,
-	BsdfReflect = 0x0010, BsdfTransmit = 0x0020, BsdfFilter = 0x0040, BsdfEmit = 0x0080, BsdfVolumetric = 0x0100,
-	BsdfAllSpecular = BsdfSpecular | BsdfReflect | BsdfTransmit,
-	BsdfAllGlossy = BsdfGlossy | BsdfReflect | BsdfTransmit,
-	BsdfAll = BsdfSpecular | BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit | BsdfFilter
-}; // material.h:50-66
+
 
 inline void cp3(float *d, const float *s) { d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; }
 inline void st3(float *d, V3 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; }
@@ -98,6 +91,65 @@ inline bool prepGlass(const yafgpu_material &m, MatDev &d, std::string &err)
 	return true;
 }
 
+
+inline void orenInit(double sigma, float &a, float &b)
+{	// initOrenNayar (material_glossy.cc:66-72, material_coated_glossy.cc:84-90): doubles narrowed into float members
+	double s2 = sigma * sigma;
+	a = (float)(1.0 - 0.5 * (s2 / (s2 + 0.33)));
+	b = (float)(0.45 * s2 / (s2 + 0.09));
+}
+
+// GlossyMaterial ctor + factory material_glossy.cc:32-49,407-480; CoatedGlossyMaterial material_coated_glossy.cc:41-65,465-545
+inline bool prepGlossy(const yafgpu_material &m, MatDev &d, std::string &err, bool coated)
+{
+	const yafgpu_mat_glossy &p = m.u.glossy;
+	cp3(d.gloss_col, p.color); cp3(d.diff_col, p.diffuse_color); cp3(d.gl_mirror_col, p.mirror_color);
+	d.gl_exponent = p.exponent; d.gl_glossy = p.glossy_reflect; d.gl_diffuse = p.diffuse_reflect; d.as_diffuse = p.as_diffuse ? 1 : 0;
+	d.gl_mirror_strength = p.specular_reflect;
+	d.anisotropic = p.anisotropic ? 1 : 0; d.exp_u = p.exp_u; d.exp_v = p.exp_v;
+	d.with_diffuse = p.diffuse_reflect > 0 ? 1 : 0;
+	d.gl_oren_nayar = 0;
+	if(p.oren_nayar) { orenInit((double)p.sigma, d.gl_oren_a, d.gl_oren_b); d.gl_oren_nayar = 1; }
+	// initBsdf: p_diffuse = min(0.6, 1 - glossy / (glossy + (1 - glossy) * diffuse))
+	d.p_diffuse = fminf(0.6f, 1.f - (d.gl_glossy / (d.gl_glossy + (1.f - d.gl_glossy) * d.gl_diffuse)));
+	if(!coated)
+	{
+		d.bsdf_flags = BsdfNone;
+		if(d.with_diffuse) d.bsdf_flags = BsdfDiffuse | BsdfReflect;
+		d.bsdf_flags |= d.as_diffuse ? (BsdfDiffuse | BsdfReflect) : (BsdfGlossy | BsdfReflect);
+	}
+	else
+	{
+		double ior = (double)p.ior;
+		if(ior == 1.0) ior = (double)1.0000001f;
+		d.ior = (float)ior;
+		d.c_flags[0] = BsdfSpecular | BsdfReflect;
+		d.c_flags[1] = d.as_diffuse ? (BsdfDiffuse | BsdfReflect) : (BsdfGlossy | BsdfReflect);
+		if(d.with_diffuse) { d.c_flags[2] = BsdfDiffuse | BsdfReflect; d.n_bsdf = 3; }
+		else { d.c_flags[2] = BsdfNone; d.n_bsdf = 2; }
+		d.bsdf_flags = d.c_flags[0] | d.c_flags[1] | d.c_flags[2];
+	}
+	(void)err;
+	return true;
+}
+
+// RoughGlassMaterial ctor + factory material_rough_glass.cc:33-48,322-401
+inline bool prepRoughGlass(const yafgpu_material &m, MatDev &d, std::string &err)
+{
+	const yafgpu_mat_glass &p = m.u.glass;
+	d.ior = p.ior;
+	const float filt = p.transmit_filter;
+	for(int k = 0; k < 3; ++k) d.filter_col[k] = filt * p.filter_color[k] + (1.f - filt);
+	cp3(d.spec_refl_col, p.mirror_color);
+	d.alpha_rough = fmaxf(1e-4f, fminf(p.alpha * 0.5f, 1.f));
+	d.fake_shadow = p.fake_shadows ? 1 : 0;
+	d.bsdf_flags = BsdfAllGlossy;
+	if(d.fake_shadow) d.bsdf_flags |= BsdfFilter;
+	if(p.dispersion_power > 0.f) { err = "rough_glass: dispersion_power > 0 (spectral dispersion) is not implemented on the device"; return false; }
+	if(p.has_absorption) { err = "rough_glass: Beer absorption volume handler is not implemented on the device"; return false; }
+	return true;
+}
+
 inline unsigned triFlagsOf(const MatDev &d)
 {
 	unsigned f = 0;
@@ -106,6 +158,7 @@ inline unsigned triFlagsOf(const MatDev &d)
 	bool transp = false;
 	if(d.type == YAFGPU_MAT_SHINYDIFFUSE) transp = d.is_transparent;          // material_shiny_diffuse.h:53
 	if(d.type == YAFGPU_MAT_GLASS || d.type == YAFGPU_MAT_ROUGH_GLASS) transp = d.fake_shadow; // material_glass.h:40
+	if(d.type == YAFGPU_MAT_BLEND) transp = d.is_transparent; // set by finishBlend (material_blend.cc:332-335)
 	if(transp) f |= TRI_TRANSPARENT;
 	return f;
 }
@@ -125,10 +178,39 @@ inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
 			d.double_sided = m.u.simple.double_sided; d.bsdf_flags = BsdfEmit;
 			return true;
 		case YAFGPU_MAT_NULL: d.bsdf_flags = BsdfNone; return true;
+		case YAFGPU_MAT_GLOSSY: return prepGlossy(m, d, err, false);
+		case YAFGPU_MAT_COATED_GLOSSY: return prepGlossy(m, d, err, true);
+		case YAFGPU_MAT_ROUGH_GLASS: return prepRoughGlass(m, d, err);
+		case YAFGPU_MAT_MIRROR: // MirrorMaterial material_glass.h:79-84
+			for(int k = 0; k < 3; ++k) d.simple_col[k] = m.u.simple.color[k] * m.u.simple.strength;
+			d.bsdf_flags = BsdfSpecular;
+			return true;
+		case YAFGPU_MAT_BLEND: // BlendMaterial ctor material_blend.cc:37-49; flags/additional depth resolved by finishBlend() once all materials exist
+			d.mat1 = m.u.blend.material1; d.mat2 = m.u.blend.material2; d.blend_val = m.u.blend.blend_value;
+			return true;
 		default:
 			err = "material type " + std::to_string(m.type) + " is not implemented on the device yet";
 			return false;
 	}
+}
+
+inline bool matIsTransparent(const MatDev &d)
+{
+	if(d.type == YAFGPU_MAT_SHINYDIFFUSE) return d.is_transparent;
+	if(d.type == YAFGPU_MAT_GLASS || d.type == YAFGPU_MAT_ROUGH_GLASS) return d.fake_shadow;
+	return false;
+}
+// second pass over blend materials (children must be leaf materials)
+inline bool finishBlend(std::vector<MatDev> &mats, size_t i, std::string &err)
+{
+	MatDev &d = mats[i];
+	if(d.mat1 < 0 || d.mat2 < 0 || (size_t)d.mat1 >= mats.size() || (size_t)d.mat2 >= mats.size()) { err = "blend_mat: child index out of range"; return false; }
+	const MatDev &a = mats[d.mat1], &b = mats[d.mat2];
+	if(a.type == YAFGPU_MAT_BLEND || b.type == YAFGPU_MAT_BLEND) { err = "blend_mat of blend_mat is not implemented on the device"; return false; }
+	d.bsdf_flags = a.bsdf_flags | b.bsdf_flags;
+	d.additional_depth = a.additional_depth > b.additional_depth ? a.additional_depth : b.additional_depth;
+	d.is_transparent = (matIsTransparent(a) || matIsTransparent(b)) ? 1 : 0;
+	return true;
 }
 
 // Light constructors
@@ -176,9 +258,91 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 			st3(d.pos, ndir); st3(d.du, du); st3(d.dv, dv);
 			return true;
 		}
+		case YAFGPU_LIGHT_MESH: // MeshLight::MeshLight light_meshlight.cc:32-43: color_ = col * inte; tables/BVH built by the caller (initIs)
+			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+			d.accel = -1;
+			return true;
+		case YAFGPU_LIGHT_BACKGROUND: // BackgroundLight ctor light_background.cc:56-65; tables built by buildBgLightTables (init)
+			return true;
 		default:
-			err = "light type " + std::to_string(l.type) + " is not implemented on the device yet";
+			err = "light type " + std::to_string(l.type) + " is not supported";
 			return false;
+	}
+}
+
+
+// MeshLight::initIs light_meshlight.cc:55-73 + Pdf1D/cumulateStep1DDf__ util_sample.h:89-124: appends cdf[count+1] to `tab`
+inline void buildMeshLightTables(const yafgpu_geometry &g, const yafgpu_object &o, LightDev &d, std::vector<float> &tab)
+{
+	const int n = o.n_tris;
+	std::vector<float> areas(n);
+	double total_area = 0.0;
+	for(int i = 0; i < n; ++i)
+	{
+		const int *vi = g.tri_vidx + 3 * (size_t)(o.first_tri + i);
+		const V3 a = ld3(g.points + 3 * (size_t)vi[0]), b = ld3(g.points + 3 * (size_t)vi[1]), c = ld3(g.points + 3 * (size_t)vi[2]);
+		areas[i] = (float)(0.5 * (double)length(cross(b - a, c - a))); // Triangle::surfaceArea triangle.cc:169-179
+		total_area += (double)areas[i];
+	}
+	d.area = (float)total_area; d.inv_area = (float)(1.0 / total_area);
+	d.tri_first = o.first_tri; d.tri_count = n;
+	d.cdf_offset = (int)tab.size(); d.cdf_count = n;
+	std::vector<float> cdf(n + 1);
+	double c = 0.0, delta = 1.0 / (double)n;
+	cdf[0] = 0.f;
+	for(int i = 1; i < n + 1; ++i) { c += (double)areas[i - 1] * delta; cdf[i] = (float)c; }
+	const float integral = (float)c;
+	for(int i = 1; i < n + 1; ++i) cdf[i] /= integral;
+	d.cdf_integral = integral;
+	tab.insert(tab.end(), cdf.begin(), cdf.end());
+}
+
+// BackgroundLight::init light_background.cc:78-120 (layout read by lights.cuh bgRow/bgCalcFrom*)
+inline void buildBgLightTables(const BackgroundDev &bg, LightDev &d, std::vector<float> &tab)
+{
+	const int nv = 360, max_u = 720, min_s = 16;
+	std::vector<float> fu(max_u), fv(nv);
+	struct Row { std::vector<float> func, cdf; float integral; };
+	std::vector<Row> rows(nv);
+	auto cumulate = [](const std::vector<float> &f, int n, std::vector<float> &cdf, float &integral)
+	{
+		cdf.assign(n + 1, 0.f);
+		double c = 0.0, delta = 1.0 / (double)n;
+		for(int i = 1; i < n + 1; ++i) { c += (double)f[i - 1] * delta; cdf[i] = (float)c; }
+		integral = (float)c;
+		for(int i = 1; i < n + 1; ++i) cdf[i] /= integral;
+	};
+	const float inv = 1.f / (float)nv;
+	for(int y = 0; y < nv; ++y)
+	{
+		const float fy = ((float)y + 0.5f) * inv;
+		const float sintheta = bgSinSample(fy);
+		const int nu = min_s + (int)(sintheta * (float)(max_u - min_s));
+		const float inu = 1.f / (float)nu;
+		rows[y].func.resize(nu);
+		for(int x = 0; x < nu; ++x)
+		{
+			const float fx = ((float)x + 0.5f) * inu;
+			const Col e = bgEval(bg, invSpheremap(fx, fy));
+			rows[y].func[x] = ((e.r + e.g + e.b) * 0.333333f) * sintheta; // Rgb::energy color.h:58
+		}
+		cumulate(rows[y].func, nu, rows[y].cdf, rows[y].integral);
+		fv[y] = rows[y].integral;
+	}
+	std::vector<float> vcdf; float vint;
+	cumulate(fv, nv, vcdf, vint);
+	d.cdf_offset = (int)tab.size(); d.cdf_count = nv; d.cdf_integral = vint;
+	tab.insert(tab.end(), fv.begin(), fv.end());
+	tab.insert(tab.end(), vcdf.begin(), vcdf.end());
+	const size_t rowinfo = tab.size();
+	tab.resize(rowinfo + 4 * (size_t)nv);
+	for(int y = 0; y < nv; ++y)
+	{
+		const int off = (int)tab.size(), cnt = (int)rows[y].func.size();
+		tab[rowinfo + 4 * y + 0] = i2f(off); tab[rowinfo + 4 * y + 1] = i2f(cnt);
+		tab[rowinfo + 4 * y + 2] = rows[y].integral; tab[rowinfo + 4 * y + 3] = 1.f / rows[y].integral;
+		tab.insert(tab.end(), rows[y].func.begin(), rows[y].func.end());
+		tab.insert(tab.end(), rows[y].cdf.begin(), rows[y].cdf.end());
 	}
 }
 
@@ -206,6 +370,7 @@ inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
 	vup = vup / (float)c.resy;
 	vright = vright / (float)c.resx;
 	st3(d.pos, pos); st3(d.vright, vright); st3(d.vup, vup); st3(d.vto, vto);
+	if(c.aperture != 0.f && (c.bokeh_type != YAFGPU_BK_DISK1)) { err = "camera: only bokeh_type disk1 is implemented on the device"; return false; }
 	d.bokeh_type = c.bokeh_type; d.bokeh_bias = c.bokeh_bias; d.n_ls = 0;
 	int ns = c.bokeh_type;
 	if(ns >= 3 && ns <= 6)

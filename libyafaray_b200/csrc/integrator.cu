@@ -1,6 +1,811 @@
-// placeholder, replaced by the wavefront integrator
+// Wavefront integrator: K2 raygen, K3 closest-hit trace, K5-K8 shading (surface setup, light sampling, BSDFs, path logic),
+// K4 shadow trace and K9 film accumulation.  Replaces, for one render pass,
+//   TiledIntegrator::renderPass/renderTile      /root/reference/src/integrator/integrator_tiled.cc:261-521
+//   PathIntegrator::integrate                   /root/reference/src/integrator/integrator_path_tracer.cc:112-347
+//   DirectLightIntegrator::integrate            /root/reference/src/integrator/integrator_direct_light.cc:97-194
+//   MonteCarloIntegrator::estimate*DirectLight,
+//     doLightEstimation, recursiveRaytrace      /root/reference/src/integrator/integrator_montecarlo.cc:47-345,782-1028
+//   Scene::isShadowed (opaque / transparent)    /root/reference/src/common/scene.cc:962-1035
+//   ImageFilm::addSample                        /root/reference/src/common/imagefilm.cc:925-1015
+//
+// The reference evaluates one camera sample at a time as a recursion TREE (integrate -> recursiveRaytrace -> integrate ...,
+// plus n_paths independent paths per integrate call).  Here the tree is flattened into a work list: every node is a task
+// carrying the RGB factor its result is multiplied with on the way up to the camera sample (`slot`), so siblings and
+// children can be shaded in any order and in parallel; results are summed into acc[slot] with float atomics and each
+// camera sample is splatted into the film once, at the end of its wave.
+//
+// Deliberate deviations from the reference — all concern state that is schedule dependent on the CPU:
+//   * Russian roulette draws come from a hash of (camera sample, path, depth) instead of the per-tile rand()-seeded MWC;
+//   * estimateOneDirectLight picks its light from a hash instead of the per-thread Halton counter;
+//   * RenderState::include_lights_ is "true" for every integrate() task (the reference leaves it at whatever the last
+//     path of a sibling subtree wrote, integrator_path_tracer.cc:212,253).
 #include "context.h"
+#include "lights.cuh"
+#include <algorithm>
+#include <cstdio>
+
 namespace yg {
-int renderPass(yafgpu_ctx *ctx, const yafgpu_pass_desc *) { return setErr(ctx, YAFGPU_ERR_UNSUPPORTED, "integrator not built yet"); }
-void freeWavefront(yafgpu_ctx *) {}
+
+#define YG_DN __device__ __noinline__
+
+struct WaveParams
+{
+	int n_slots;        // camera samples in this wave = n_pix * n_smp
+	int pix_base, n_pix; // pixel-list range of the wave
+	int sample_base;    // first sample index of the wave inside the pass
+	int n_samples_pass; // samples per pixel of the whole pass (integrator_tiled.cc:385,400)
+	int pass_offs;      // sampling offset of the pass (integrator_tiled.cc:335)
+	int aa_passes;
+	int task_cap, shadow_cap;
+	unsigned seed;
+};
+
+// ---- packed task state (wavefront.h) ---------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned packState(int kind, int raylevel, int depth, int ray_division, int caustic, int add_depth)
+{
+	return (unsigned)kind | ((unsigned)raylevel << 1) | ((unsigned)depth << 6) | ((unsigned)min(ray_division, 255) << 12) | ((unsigned)caustic << 22) |
+	       ((unsigned)min(add_depth, 31) << 23);
 }
+__device__ __forceinline__ int stKind(unsigned p) { return p & 1; }
+__device__ __forceinline__ int stRaylevel(unsigned p) { return (p >> 1) & 31; }
+__device__ __forceinline__ int stDepth(unsigned p) { return (p >> 6) & 63; }
+__device__ __forceinline__ int stDivision(unsigned p) { return (p >> 12) & 255; }
+__device__ __forceinline__ int stCaustic(unsigned p) { return (p >> 22) & 1; }
+__device__ __forceinline__ int stAddDepth(unsigned p) { return (p >> 23) & 31; }
+
+// warp-aggregated queue slot allocation
+__device__ __forceinline__ int allocSlot(int *counter)
+{
+	const unsigned m = __activemask();
+	const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+	int base = 0;
+	if(lane == leader) base = atomicAdd(counter, __popc(m));
+	base = __shfl_sync(m, base, leader);
+	return base + __popc(m & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ unsigned hash3(unsigned a, unsigned b, unsigned c)
+{
+	unsigned h = a * 0x9E3779B1u;
+	h ^= b + 0x7F4A7C15u + (h << 6) + (h >> 2);
+	h *= 0x85EBCA6Bu; h ^= h >> 13;
+	h ^= c + 0x165667B1u + (h << 6) + (h >> 2);
+	h *= 0xC2B2AE35u; h ^= h >> 16;
+	h *= 0x27D4EB2Fu; h ^= h >> 15;
+	return h;
+}
+__device__ __forceinline__ float hashRand(unsigned a, unsigned b, unsigned c) { return (float)((double)hash3(a, b, c) * YG_MULT_RATIO); } // Random::operator() is x * 2^-32
+
+__device__ __forceinline__ void accAdd(float4 *acc, int slot, Col c)
+{
+	float *p = (float *)(acc + slot);
+	if(c.r != 0.f) atomicAdd(p, c.r);
+	if(c.g != 0.f) atomicAdd(p + 1, c.g);
+	if(c.b != 0.f) atomicAdd(p + 2, c.b);
+}
+
+struct SlotInfo { int x, y, sample; unsigned sampling_offs; int pixel_sample; };
+__device__ __forceinline__ SlotInfo slotInfo(const WaveParams &wp, const uint32_t *__restrict__ pixels, int slot)
+{
+	SlotInfo s;
+	const int pi = slot % wp.n_pix, si = slot / wp.n_pix;
+	const uint32_t pxy = __ldg(pixels + wp.pix_base + pi);
+	s.x = (int)(pxy & 0xffffu); s.y = (int)(pxy >> 16);
+	s.sample = wp.sample_base + si;
+	s.sampling_offs = fnv32a((uint32_t)s.y * fnv32a((uint32_t)s.x)); // fnv32ABuf__(i * fnv32ABuf__(j)) integrator_tiled.cc:379
+	s.pixel_sample = wp.pass_offs + s.sample;                          // :389
+	return s;
+}
+// pixel-sample position integrator_tiled.cc:392-403
+__device__ __forceinline__ void samplePos(const WaveParams &wp, const SlotInfo &si, float &dx, float &dy)
+{
+	dx = 0.5f; dy = 0.5f;
+	if(wp.aa_passes > 1)
+	{
+		dx = riVdC((uint32_t)si.pixel_sample, si.sampling_offs);
+		dy = riS((uint32_t)si.pixel_sample, si.sampling_offs);
+	}
+	else if(wp.n_samples_pass > 1)
+	{
+		const float d_1 = (float)(1.0 / (double)(float)wp.n_samples_pass);
+		dx = (float)((0.5 + (double)(float)si.sample) * (double)d_1);
+		dy = riLp((uint32_t)si.sample + si.sampling_offs);
+	}
+}
+
+// ---- K2: camera rays ---------------------------------------------------------------------------------------------------
+// shirleyDisk__ util_sample.h (concentric map) used by the default bokeh
+__device__ void shirleyDisk(float r_1, float r_2, float &u, float &v)
+{
+	float phi = 0.f, r = 0.f;
+	const float a = 2.f * r_1 - 1.f, b = 2.f * r_2 - 1.f;
+	if(a > -b)
+	{
+		if(a > b) { r = a; phi = (float)(0.78539816339744830962 * (double)(b / a)); }
+		else { r = b; phi = (float)(0.78539816339744830962 * (double)(2.f - a / b)); }
+	}
+	else
+	{
+		if(a < b) { r = -a; phi = (float)(0.78539816339744830962 * (double)(4.f + b / a)); }
+		else { r = -b; if(b != 0) phi = (float)(0.78539816339744830962 * (double)(6.f - a / b)); else phi = 0.f; }
+	}
+	u = r * fCos(phi); v = r * fSin(phi);
+}
+
+__global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue q)
+{
+	for(int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < wp.n_slots; slot += gridDim.x * blockDim.x)
+	{
+		const SlotInfo si = slotInfo(wp, pixels, slot);
+		float dx, dy;
+		samplePos(wp, si, dx, dy);
+		// PerspectiveCamera::shootRay camera_perspective.cc:133-155
+		const CameraDev &c = sc.cam;
+		const float px = (float)si.x + dx, py = (float)si.y + dy;
+		V3 from = ldv(c.pos);
+		V3 dir = normalize((ldv(c.vright) * px + ldv(c.vup) * py) + ldv(c.vto));
+		const V3 nn = ldv(c.near_n);
+		// rayPlaneIntersection__ util_geometry.h:34-37 (near and far plane share the normal)
+		const float tmin = dot(nn, ldv(c.near_p) - from) / dot(dir, nn);
+		const float tmax = dot(nn, ldv(c.far_p) - from) / dot(dir, nn);
+		if(c.aperture != 0)
+		{
+			Halton hu, hv; hu.setBase(3); hv.setBase(5);
+			hu.setStart((uint32_t)wp.pass_offs + si.sampling_offs + (uint32_t)si.sample);
+			hv.setStart((uint32_t)wp.pass_offs + si.sampling_offs + (uint32_t)si.sample);
+			const float lu = hu.getNext(), lv = hv.getNext();
+			float u, v;
+			shirleyDisk(lu, lv, u, v); // bokeh disk1 (other bokeh types are refused at upload)
+			const V3 li = ldv(c.dof_rt) * u + ldv(c.dof_up) * v;
+			from = from + li;
+			dir = normalize((dir * c.dof_distance) - li);
+		}
+		q.ray_o[slot] = make_float4(from.x, from.y, from.z, tmin);
+		q.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, tmax);
+		q.wgt[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+		q.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+		q.st[slot] = make_uint4((unsigned)slot, 0u, packState(TASK_INTEGRATE, 0, 0, 1, 0, 0), 0u);
+		q.dc[slot] = make_float2(0.f, 0.f);
+	}
+}
+
+// ---- K3: closest hit for every queued task -----------------------------------------------------------------------------
+template<bool COUNT>
+__global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int *__restrict__ n_tasks, int task_cap, unsigned long long *__restrict__ counters)
+{
+	const int n = min(*n_tasks, task_cap);
+	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	{
+		const float4 a = q.ray_o[i], b = q.ray_d[i];
+		RayD r; r.o = mk(a.x, a.y, a.z); r.tmin = a.w; r.d = mk(b.x, b.y, b.z); r.tmax = b.w;
+		const HitD h = traceClosest<COUNT>(acc, r, &tc);
+		q.hit[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+	}
+	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+}
+
+// ---- shading helpers ---------------------------------------------------------------------------------------------------
+struct ShadeCtx
+{
+	const SceneDev *sc;
+	WaveParams wp;
+	TaskQueue out;
+	ShadowQueue sq;
+	float4 *acc;
+	WaveCtl *ctl;
+	int iter;
+};
+
+__device__ __forceinline__ void pushShadow(const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, float tmax, Col contrib)
+{
+	if(isBlack(contrib)) return;
+	const int k = allocSlot(&cx.ctl->n_shadow[cx.iter]);
+	if(k >= cx.wp.shadow_cap) { cx.ctl->overflow = 1; return; }
+	cx.sq.ray_o[k] = make_float4(from.x, from.y, from.z, tmin);
+	cx.sq.ray_d[k] = make_float4(dir.x, dir.y, dir.z, tmax);
+	cx.sq.contrib[k] = make_float4(contrib.r, contrib.g, contrib.b, __int_as_float(slot));
+}
+
+__device__ __forceinline__ void pushTask(const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2)
+{
+	const int k = allocSlot(&cx.ctl->n_tasks[cx.iter + 1]);
+	if(k >= cx.wp.task_cap) { cx.ctl->overflow = 1; return; }
+	cx.out.ray_o[k] = make_float4(from.x, from.y, from.z, tmin);
+	cx.out.ray_d[k] = make_float4(dir.x, dir.y, dir.z, -1.f);
+	cx.out.wgt[k] = make_float4(wgt.r, wgt.g, wgt.b, 0.f);
+	cx.out.thr[k] = make_float4(thr.r, thr.g, thr.b, 0.f);
+	cx.out.st[k] = make_uint4((unsigned)slot, offs, packed, ray_offset);
+	cx.out.dc[k] = make_float2(dc1, dc2);
+}
+
+// MonteCarloIntegrator::doLightEstimation integrator_montecarlo.cc:78-345 (Combined pass only).
+// `W` is the factor the returned colour would be multiplied with before reaching the camera sample; every term is queued
+// as a shadow ray carrying its finished contribution (or added at once when the light/material pair casts no shadow).
+YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, int li, const SurfPt &sp, V3 wo, unsigned loffs, int ray_division, Col W)
+{
+	const SceneDev &sc = *cx.sc;
+	const LightDev &L = sc.lights[li];
+	const MatDev &m = sc.materials[sp.mat];
+	const bool cast_shadows = L.cast_shadows && m.receive_shadows;
+	const unsigned l_offs = loffs * 4567u;
+	const float plen = length(sp.p);
+	const float sh_tmin = sc.integ.shadow_bias_auto ? sc.integ.shadow_bias * fmaxf(1.f, plen) : sc.integ.shadow_bias;
+	if(lightIsDirac(L.type))
+	{
+		Col lcol; V3 ldir; float tmax;
+		if(lightIlluminate(L, sp, lcol, ldir, tmax))
+		{
+			const float angle = m.flat ? 1.f : fabsf(dot(sp.n, ldir));
+			const Col surf_col = matEval(sc, m, sp, wo, ldir, BsdfAll);
+			const Col c = W * ((surf_col * lcol) * angle);
+			if(cast_shadows) pushShadow(cx, slot, sp.p, sh_tmin, ldir, tmax, c);
+			else accAdd(cx.acc, slot, c);
+		}
+		return;
+	}
+	int n = (int)ceilf((float)L.samples * sc.integ.aa_light_sample_multiplier);
+	if(ray_division > 1) n = max(1, n / ray_division);
+	const float inv_ns = 1.f / (float)n;
+	const unsigned offs = (unsigned)n * (unsigned)si.pixel_sample + si.sampling_offs + l_offs;
+	const bool can_intersect = lightCanIntersect(L.type) && !(L.type == YAFGPU_LIGHT_MESH && L.accel < 0);
+	Halton hal_2, hal_3; hal_2.setBase(2); hal_3.setBase(3);
+	hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
+	for(int i = 0; i < n; ++i)
+	{
+		const float s1 = hal_2.getNext(), s2 = hal_3.getNext();
+		Col lscol; float lpdf, tmax; V3 ldir;
+		if(!lightIllumSample(sc, L, sp, s1, s2, lscol, lpdf, ldir, tmax)) continue;
+		if(!(lpdf > 1e-6f)) continue;
+		const Col surf_col = matEval(sc, m, sp, wo, ldir, BsdfAll);
+		const float angle = m.flat ? 1.f : fabsf(dot(sp.n, ldir));
+		Col c;
+		if(can_intersect)
+		{
+			const float m_pdf = matPdf(sc, m, sp, wo, ldir, BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit);
+			if(m_pdf > 1e-6f)
+			{
+				const float l_2 = lpdf * lpdf, m_2 = m_pdf * m_pdf;
+				const float w = l_2 / (l_2 + m_2);
+				c = (((surf_col * lscol) * angle) * w) / lpdf;
+			}
+			else c = ((surf_col * lscol) * angle) / lpdf;
+		}
+		else c = ((surf_col * lscol) * angle) / lpdf;
+		c = W * (c * inv_ns);
+		if(cast_shadows) pushShadow(cx, slot, sp.p, sh_tmin, ldir, tmax, c);
+		else accAdd(cx.acc, slot, c);
+	}
+	if(can_intersect)
+	{
+		hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
+		const float b_tmin = sc.integ.ray_min_dist_auto ? sc.integ.ray_min_dist * fmaxf(1.f, plen) : sc.integ.ray_min_dist;
+		for(int i = 0; i < n; ++i)
+		{
+			BSample s; s.s1 = hal_2.getNext(); s.s2 = hal_3.getNext(); s.pdf = 0.f; s.sampled = BsdfNone;
+			s.flags = BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit;
+			float Wm = 0.f; V3 bdir = mk(0.f);
+			const Col surf_col = matSample(sc, m, sp, wo, bdir, s, Wm);
+			Col lcol; float light_pdf, t;
+			if(s.pdf > 1e-6f && lightIntersect(sc, L, sp.p, bdir, b_tmin, t, lcol, light_pdf))
+			{
+				if(!(light_pdf > 1e-6f)) continue;
+				const float l_pdf = 1.f / light_pdf;
+				const float l_2 = l_pdf * l_pdf, m_2 = s.pdf * s.pdf;
+				const float w = m_2 / (l_2 + m_2);
+				const Col c = W * ((((surf_col * lcol) * w) * Wm) * inv_ns);
+				if(cast_shadows) pushShadow(cx, slot, sp.p, b_tmin, bdir, t, c);
+				else accAdd(cx.acc, slot, c);
+			}
+		}
+	}
+}
+
+// ---- K5-K8: one thread per task ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
+                                               float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter)
+{
+	const int n = min(ctl->n_tasks[iter], wp.task_cap);
+	ShadeCtx cx; cx.sc = &sc; cx.wp = wp; cx.out = out; cx.sq = sq; cx.acc = acc; cx.ctl = ctl; cx.iter = iter;
+	const IntegratorDev &ig = sc.integ;
+	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	{
+		const float4 ro = in.ray_o[i], rd = in.ray_d[i], hh = in.hit[i], wg = in.wgt[i];
+		const uint4 st = in.st[i];
+		const int slot = (int)st.x;
+		const unsigned packed = st.z;
+		const V3 from = mk(ro.x, ro.y, ro.z), dir = mk(rd.x, rd.y, rd.z);
+		const Col W = mkc(wg.x, wg.y, wg.z);
+		const int tri = __float_as_int(hh.w);
+		const SlotInfo si = slotInfo(wp, pixels, slot);
+		const int ray_division = stDivision(packed);
+
+		if(stKind(packed) == TASK_INTEGRATE)
+		{
+			// ---- PathIntegrator::integrate / DirectLightIntegrator::integrate ----
+			if(tri < 0)
+			{
+				if(sc.bg.type != YAFGPU_BG_NONE) accAdd(acc, slot, W * bgEval(sc.bg, dir));
+				continue;
+			}
+			SurfPt sp;
+			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp); // Point3 h = ray.from_ + z * ray.dir_ (scene.cc:908)
+			const MatDev &m = sc.materials[sp.mat];
+			const unsigned bsdfs = m.bsdf_flags;
+			const V3 wo = -dir;
+			const int raylevel = stRaylevel(packed);
+			const int additional_depth = max(stAddDepth(packed), m.additional_depth);
+			const float2 dcv = in.dc[i];
+			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit(sc, m, sp, wo, true));
+			if(bsdfs & BsdfDiffuse)
+			{	// estimateAllDirectLight integrator_montecarlo.cc:47-60
+				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation(cx, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
+			}
+			if(ig.type == YAFGPU_INT_PATHTRACING)
+			{	// integrator_path_tracer.cc:174-298: first path segment, sampled here; the rest of each path is a TASK_PATH chain
+				unsigned path_flags = ig.no_recursive ? BsdfAll : BsdfDiffuse;
+				if(bsdfs & path_flags)
+				{
+					path_flags |= (BsdfDiffuse | BsdfReflect | BsdfTransmit);
+					const int n_samples = max(1, ig.n_paths / ray_division);
+					const float inv_n = 1.f / (float)n_samples;
+					for(int k = 0; k < n_samples; ++k)
+					{
+						const unsigned offs = (unsigned)ig.n_paths * (unsigned)si.pixel_sample + si.sampling_offs + (unsigned)k;
+						float s_1 = riVdC(offs);
+						float s_2 = (float)scrHaltonT(*sc.faure, 2, offs);
+						if(ray_division > 1) { s_1 = addMod1(s_1, dcv.x); s_2 = addMod1(s_2, dcv.y); }
+						BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = path_flags; s.pdf = 0.f; s.sampled = BsdfNone;
+						float w = 0.f; V3 wi = mk(0.f);
+						Col scol = matSample(sc, m, sp, wo, wi, s, w);
+						scol = scol * w;
+						if(isBlack(scol) || s.sampled == BsdfNone) continue; // contributes exactly zero in the reference as well
+						pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, (W * scol) * inv_n, scol, offs,
+						         packState(TASK_PATH, raylevel, 0, ray_division, 0, 0), 0u, 0.f, 0.f);
+					}
+				}
+			}
+			// ---- recursiveRaytrace integrator_montecarlo.cc:782-1028 ----
+			const int rl = raylevel + 1;
+			if(rl <= ig.r_depth + additional_depth)
+			{
+				if((bsdfs & BsdfGlossy) && rl < 20)
+				{
+					int gsam = 8;
+					const int old_division = ray_division, old_offset = (int)st.w;
+					if(old_division > 1) gsam = max(1, gsam / old_division);
+					const int new_division = old_division * gsam;
+					int branch = new_division * old_offset;
+					const unsigned offs = (unsigned)gsam * (unsigned)si.pixel_sample + si.sampling_offs;
+					const float d_1 = 1.f / (float)gsam;
+					Halton hal_2, hal_3; hal_2.setBase(2); hal_3.setBase(3);
+					hal_2.setStart(offs); hal_3.setStart(offs);
+					for(int ns = 0; ns < gsam; ++ns)
+					{
+						const float dc1 = (float)scrHaltonT(*sc.faure, 2 * rl + 1, (unsigned)branch + si.sampling_offs);
+						const float dc2 = (float)scrHaltonT(*sc.faure, 2 * rl + 2, (unsigned)branch + si.sampling_offs);
+						const unsigned ray_offset = (unsigned)branch;
+						++branch;
+						const float s_1 = hal_2.getNext(), s_2 = hal_3.getNext();
+						const unsigned child = packState(TASK_INTEGRATE, rl, 0, new_division, 0, additional_depth);
+						if(m.bsdf_flags & BsdfGlossy)
+						{
+							if((m.bsdf_flags & BsdfReflect) && !(m.bsdf_flags & BsdfTransmit))
+							{
+								BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfReflect; s.pdf = 0.f; s.sampled = BsdfNone;
+								float w = 0.f; V3 wi = mk(0.f);
+								const Col mcol = matSample(sc, m, sp, wo, wi, s, w);
+								const Col f = (mcol * w) * d_1;
+								if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2);
+							}
+							else if((m.bsdf_flags & BsdfReflect) && (m.bsdf_flags & BsdfTransmit))
+							{
+								BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfAllGlossy; s.pdf = 0.f; s.sampled = BsdfNone;
+								Col mcol[2] = {mkc(0.f), mkc(0.f)}; float w[2] = {0.f, 0.f}; V3 d2[2] = {mk(0.f), mk(0.f)};
+								mcol[0] = matSample2(sc, m, sp, wo, d2, mcol[1], s, w);
+								if((s.sampled & BsdfReflect) && !(s.sampled & BsdfDispersive))
+								{
+									const Col f = (mcol[0] * w[0]) * d_1;
+									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2);
+								}
+								if(s.sampled & BsdfTransmit)
+								{
+									const Col f = (mcol[1] * w[1]) * d_1;
+									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[1], W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2);
+								}
+							}
+						}
+					}
+				}
+				if((bsdfs & (BsdfSpecular | BsdfFilter)) && rl < 20)
+				{
+					bool refl = false, refr = false;
+					V3 d2[2]; Col rcol[2];
+					matSpecular(sc, m, sp, wo, rl, refl, refr, d2, rcol);
+					const unsigned child = packState(TASK_INTEGRATE, rl, 0, ray_division, 0, additional_depth);
+					if(refl && !isBlack(rcol[0])) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * rcol[0], mkc(1.f), 0u, child, st.w, dcv.x, dcv.y);
+					if(refr && !isBlack(rcol[1]))
+					{
+						V3 o = sp.p;
+						float tb = m.transp_bias_factor;
+						if(tb > 0.f)
+						{
+							if(m.transp_bias_mult) tb *= (float)rl;
+							o = sp.p + d2[1] * tb;
+						}
+						pushTask(cx, slot, o, ig.ray_min_dist, d2[1], W * rcol[1], mkc(1.f), 0u, child, st.w, dcv.x, dcv.y);
+					}
+				}
+			}
+		}
+		else
+		{
+			// ---- one vertex of the path loop, integrator_path_tracer.cc:214-294 ----
+			const int depth = stDepth(packed);
+			const bool caustic = stCaustic(packed);
+			if(tri < 0)
+			{
+				if(depth >= 1 && caustic && sc.bg.type != YAFGPU_BG_NONE && sc.bg.has_ibl && sc.bg.shoots_caustic) accAdd(acc, slot, W * bgEval(sc.bg, dir));
+				continue;
+			}
+			SurfPt sp;
+			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp);
+			const MatDev &m = sc.materials[sp.mat];
+			const unsigned bsdfs = m.bsdf_flags;
+			const V3 pwo = -dir;
+			const float4 th = in.thr[i];
+			Col thr = mkc(th.x, th.y, th.z);
+			Col Wp = W;
+			const unsigned offs = st.y;
+			bool direct = (depth == 0) || (bsdfs & BsdfDiffuse);
+			if(depth >= 1 && depth > ig.rr_min_bounces)
+			{	// Russian roulette :282-288
+				const float random_value = hashRand(wp.seed ^ (unsigned)(wp.pix_base + slot), offs, (unsigned)depth);
+				const float probability = maxc(thr);
+				if(probability <= 0.f || probability < random_value) continue;
+				const float ip = 1.f / probability;
+				thr = thr * ip; Wp = Wp * ip;
+			}
+			if(direct && sc.n_lights > 0 && (bsdfs & (BsdfDiffuse | BsdfGlossy)))
+			{	// estimateOneDirectLight integrator_montecarlo.cc:62-76 (a material without diffuse/glossy lobes evaluates to black)
+				const float u = hashRand(wp.seed + 0x51ED270Bu + (unsigned)(wp.pix_base + slot), offs, (unsigned)depth);
+				const int lnum = min((int)(u * (float)sc.n_lights), sc.n_lights - 1);
+				doLightEstimation(cx, slot, si, lnum, sp, pwo, (unsigned)lnum, ray_division, Wp * (float)sc.n_lights);
+			}
+			if(bsdfs & BsdfEmit)
+			{
+				if(depth == 0) accAdd(acc, slot, Wp * matEmit(sc, m, sp, pwo, false));  // include_lights_ = false (:212)
+				else if(caustic) accAdd(acc, slot, Wp * matEmit(sc, m, sp, pwo, true)); // include_lights_ = caustic (:253,290)
+			}
+			const int nd = depth + 1;
+			if(nd < ig.max_bounces)
+			{
+				BSample s; s.flags = BsdfAll; s.pdf = 0.f; s.sampled = BsdfNone;
+				s.s1 = (float)scrHaltonT(*sc.faure, 4 * nd + 3, offs);
+				s.s2 = (float)scrHaltonT(*sc.faure, 4 * nd + 4, offs);
+				float w = 0.f; V3 wi = mk(0.f);
+				Col scol = matSample(sc, m, sp, pwo, wi, s, w);
+				scol = scol * w;
+				if(isBlack(scol)) continue;
+				const bool ncaustic = ig.trace_caustics && (s.sampled & (BsdfSpecular | BsdfGlossy | BsdfFilter));
+				pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, Wp * scol, thr * scol, offs,
+				         packState(TASK_PATH, stRaylevel(packed), nd, ray_division, ncaustic ? 1 : 0, 0), 0u, 0.f, 0.f);
+			}
+		}
+	}
+}
+
+// ---- K4: shadow rays ---------------------------------------------------------------------------------------------------
+// TriKdTree::intersectTs kdtree_triangle.cc:983-1162: every shadow-visible triangle in (tmin, dist); opaque -> blocked;
+// transparent -> filt *= getTransparency, at most max_depth of them (a BVH holds each triangle once, so the reference's
+// std::set of already-filtered triangles is implicit).
+__device__ bool traceShadowTransp(const SceneDev &sc, V3 o, V3 d, float tmin, float dist, int max_depth, Col &filt)
+{
+	const Accel &acc = sc.accel;
+	filt = mkc(1.f);
+	if(acc.n_tris == 0) return false;
+	const V3 id = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+	int stack[YG_STACK];
+	int sp_ = 0, cur = acc.root, depth = 0;
+	for(;;)
+	{
+		if(cur >= 0)
+		{
+			const BvhNode *nd = acc.nodes + cur;
+			const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
+			float ta, tb;
+			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, 0.f, dist, ta);
+			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, 0.f, dist, tb);
+			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+			if(ha && hb) { cur = ca; if(sp_ < YG_STACK) stack[sp_++] = cb; continue; }
+			if(ha) { cur = ca; continue; }
+			if(hb) { cur = cb; continue; }
+		}
+		else
+		{
+			const int code = ~cur;
+			const int first = code >> 3, count = (code & 7) + 1;
+			for(int k = 0; k < count; ++k)
+			{
+				const TriAccel *tp = acc.tris + first + k;
+				const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
+				float t, u, v;
+				if(!triIntersect(v0e, e1i, e2f, o, d, t, u, v)) continue;
+				const int fl = __float_as_int(e2f.w);
+				if(!(t < dist && t >= tmin && (fl & TRI_VIS_SHADOW))) continue;
+				if(!(fl & TRI_TRANSPARENT)) return true;
+				if(depth >= max_depth) return true;
+				SurfPt sp;
+				getSurface(sc, __float_as_int(e1i.w), u, v, o + t * d, sp);
+				filt = filt * matTransparency(sc, sc.materials[sp.mat], sp, d);
+				++depth;
+			}
+		}
+		if(sp_ == 0) break;
+		cur = stack[--sp_];
+	}
+	return false;
+}
+
+template<bool COUNT>
+__global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ SceneDev sc, ShadowQueue sq, const int *__restrict__ n_shadow, int shadow_cap, float4 *__restrict__ acc,
+                                                unsigned long long *__restrict__ counters)
+{
+	const int n = min(*n_shadow, shadow_cap);
+	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	{
+		const float4 a = sq.ray_o[i], b = sq.ray_d[i], c = sq.contrib[i];
+		const V3 dir = mk(b.x, b.y, b.z);
+		// Scene::isShadowed scene.cc:965-970: shift the origin by tmin, shorten the segment by 2 tmin
+		const V3 o = mk(a.x, a.y, a.z) + dir * a.w;
+		const float dist = (b.w < 0.f) ? __int_as_float(0x7f800000) : b.w - 2 * a.w;
+		Col contrib = mkc(c.x, c.y, c.z);
+		if(sc.integ.tr_shad)
+		{
+			Col filt;
+			if(traceShadowTransp(sc, o, dir, a.w, dist, sc.integ.s_depth, filt)) continue;
+			contrib = contrib * filt;
+		}
+		else if(traceShadow<COUNT>(sc.accel, o, dir, dist, &tc) >= 0) continue;
+		accAdd(acc, __float_as_int(c.w), contrib);
+	}
+	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+}
+
+// ---- K9: ImageFilm::addSample imagefilm.cc:925-1015 (Combined pass) --------------------------------------------------------
+__device__ __forceinline__ int round2Int(double v) { return (int)(v + (.5 - 1.4e-11)); } // util_math.h:34-43 (FAST_INT off)
+
+__global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, const uint32_t *__restrict__ pixels, const float4 *__restrict__ acc, const WaveCtl *__restrict__ ctl)
+{
+	if(ctl->overflow) return; // the wave is discarded and re-rendered in smaller pieces
+	for(int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < wp.n_slots; slot += gridDim.x * blockDim.x)
+	{
+		const SlotInfo si = slotInfo(wp, pixels, slot);
+		float dx, dy;
+		samplePos(wp, si, dx, dy);
+		const float4 a = acc[slot];
+		Col col = clampProportional(mkc(a.x, a.y, a.z), film.clamp_samples);
+		const float alpha = 1.f;
+		const int x = si.x, y = si.y;
+		const double fw = (double)film.filterw;
+		const int dx_0 = max(film.cx0 - x, round2Int((double)dx - fw));
+		const int dx_1 = min(film.cx1 - x - 1, round2Int((double)dx + fw - 1.0));
+		const int dy_0 = max(film.cy0 - y, round2Int((double)dy - fw));
+		const int dy_1 = min(film.cy1 - y - 1, round2Int((double)dy + fw - 1.0));
+		const double x_offs = (double)dx - 0.5, y_offs = (double)dy - 0.5;
+		int x_index[9], y_index[9];
+		for(int i = dx_0, n = 0; i <= dx_1 && n < 9; ++i, ++n) x_index[n] = (int)floor(fabs(((double)i - x_offs) * (double)film.table_scale));
+		for(int i = dy_0, n = 0; i <= dy_1 && n < 9; ++i, ++n) y_index[n] = (int)floor(fabs(((double)i - y_offs) * (double)film.table_scale));
+		const int x_0 = x + dx_0, x_1 = x + dx_1, y_0 = y + dy_0, y_1 = y + dy_1;
+		for(int j = y_0; j <= y_1; ++j)
+			for(int i = x_0; i <= x_1; ++i)
+			{
+				const float filter_wt = film.table[y_index[j - y_0] * 16 + x_index[i - x_0]];
+				float *p = film.pix + 5 * ((size_t)(j - film.cy0) * film.w + (i - film.cx0));
+				atomicAdd(p + 0, col.r * filter_wt);
+				atomicAdd(p + 1, col.g * filter_wt);
+				atomicAdd(p + 2, col.b * filter_wt);
+				atomicAdd(p + 3, alpha * filter_wt);
+				atomicAdd(p + 4, filter_wt);
+			}
+	}
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------------------
+static unsigned hashSeed(unsigned a, unsigned b, unsigned c)
+{
+	unsigned h = a * 0x9E3779B1u + 0x7F4A7C15u;
+	h ^= b + (h << 6) + (h >> 2); h *= 0x85EBCA6Bu; h ^= h >> 13;
+	h ^= c + (h << 6) + (h >> 2); h *= 0xC2B2AE35u; h ^= h >> 16;
+	return h;
+}
+void freeWavefront(yafgpu_ctx *c)
+{
+	Wavefront &w = c->wf;
+	for(int k = 0; k < 2; ++k)
+	{
+		cudaFree(w.q[k].ray_o); cudaFree(w.q[k].ray_d); cudaFree(w.q[k].hit); cudaFree(w.q[k].wgt); cudaFree(w.q[k].thr); cudaFree(w.q[k].st); cudaFree(w.q[k].dc);
+		w.q[k] = TaskQueue();
+	}
+	cudaFree(w.sq.ray_o); cudaFree(w.sq.ray_d); cudaFree(w.sq.contrib); w.sq = ShadowQueue();
+	cudaFree(w.acc); cudaFree(w.pixels); cudaFree(w.ctl);
+	if(w.h_ctl) cudaFreeHost(w.h_ctl);
+	w.acc = nullptr; w.pixels = nullptr; w.ctl = nullptr; w.h_ctl = nullptr; w.pixels_cap = 0;
+	w.allocated = false; w.pixels_key.clear();
+}
+
+static cudaError_t allocWavefront(yafgpu_ctx *c, int wave_cap, int task_cap, int shadow_cap)
+{
+	Wavefront &w = c->wf;
+	if(w.allocated && w.wave_cap == wave_cap && w.task_cap == task_cap && w.shadow_cap == shadow_cap) return cudaSuccess;
+	uint32_t *pix = w.pixels; size_t pcap = w.pixels_cap; std::vector<int> key = w.pixels_key; // keep the pixel list
+	w.pixels = nullptr;
+	freeWavefront(c);
+	w.pixels = pix; w.pixels_cap = pcap; w.pixels_key = key;
+	cudaError_t e = cudaSuccess;
+#define A(p, T, n) if(e == cudaSuccess) e = cudaMalloc(&(p), sizeof(T) * (size_t)(n))
+	for(int k = 0; k < 2; ++k)
+	{
+		A(w.q[k].ray_o, float4, task_cap); A(w.q[k].ray_d, float4, task_cap); A(w.q[k].hit, float4, task_cap); A(w.q[k].wgt, float4, task_cap);
+		A(w.q[k].thr, float4, task_cap); A(w.q[k].st, uint4, task_cap); A(w.q[k].dc, float2, task_cap);
+	}
+	A(w.sq.ray_o, float4, shadow_cap); A(w.sq.ray_d, float4, shadow_cap); A(w.sq.contrib, float4, shadow_cap);
+	A(w.acc, float4, wave_cap); A(w.ctl, WaveCtl, 1);
+#undef A
+	if(e == cudaSuccess) e = cudaMallocHost(&w.h_ctl, sizeof(WaveCtl));
+	if(e != cudaSuccess) { uint32_t *p2 = w.pixels; w.pixels = nullptr; freeWavefront(c); w.pixels = p2; return e; }
+	w.wave_cap = wave_cap; w.task_cap = task_cap; w.shadow_cap = shadow_cap; w.allocated = true;
+	return cudaSuccess;
+}
+
+// pixel list of a pass in tile order: ImageSplitter raster tiles (imagesplitter.cc:37-50), rows inside a tile
+static int buildPixelList(yafgpu_ctx *c, const yafgpu_pass_desc *p, size_t &n_out)
+{
+	Wavefront &w = c->wf;
+	const FilmDev &f = c->film;
+	const int ts = c->tile_size;
+	const int part_count = p->part_count > 1 ? p->part_count : 1, part_index = p->part_count > 1 ? p->part_index : 0;
+	const bool masked = p->adaptive && p->resample_mask;
+	std::vector<int> key = {f.w, f.h, f.cx0, f.cy0, ts, part_index, part_count};
+	if(!masked && w.pixels && w.pixels_key == key) { n_out = w.pixels_n; return YAFGPU_OK; }
+	std::vector<uint32_t> px;
+	px.reserve((size_t)f.w * f.h / part_count + 1024);
+	const int ntx = (f.w + ts - 1) / ts, nty = (f.h + ts - 1) / ts;
+	for(int ty = 0; ty < nty; ++ty) for(int tx = 0; tx < ntx; ++tx)
+	{
+		const int t = ty * ntx + tx;
+		if(t % part_count != part_index) continue;
+		const int x0 = tx * ts, y0 = ty * ts, x1 = std::min(x0 + ts, f.w), y1 = std::min(y0 + ts, f.h);
+		for(int y = y0; y < y1; ++y) for(int x = x0; x < x1; ++x)
+		{
+			if(masked && !p->resample_mask[(size_t)y * f.w + x]) continue;
+			px.push_back((uint32_t)(x + f.cx0) | ((uint32_t)(y + f.cy0) << 16));
+		}
+	}
+	if(px.size() > w.pixels_cap)
+	{
+		cudaFree(w.pixels); w.pixels = nullptr; w.pixels_cap = 0;
+		YG_CUDA(c, cudaMalloc(&w.pixels, sizeof(uint32_t) * (px.size() + 1)));
+		w.pixels_cap = px.size() + 1;
+	}
+	if(!px.empty()) YG_CUDA(c, cudaMemcpyAsync(w.pixels, px.data(), sizeof(uint32_t) * px.size(), cudaMemcpyHostToDevice, c->stream));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream)); // px goes out of scope
+	w.pixels_n = px.size(); n_out = px.size();
+	if(masked) w.pixels_key.clear(); else w.pixels_key = key;
+	return YAFGPU_OK;
+}
+
+static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &overflow)
+{
+	Wavefront &w = c->wf;
+	cudaStream_t st = c->stream;
+	const bool count = (c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL) != 0;
+	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	YG_CUDA(c, cudaMemsetAsync(w.ctl, 0, sizeof(WaveCtl), st));
+	YG_CUDA(c, cudaMemsetAsync(w.acc, 0, sizeof(float4) * (size_t)wp.n_slots, st));
+	YG_CUDA(c, cudaMemcpyAsync(&w.ctl->n_tasks[0], &wp.n_slots, sizeof(int), cudaMemcpyHostToDevice, st));
+	const int g256 = std::min((wp.n_slots + 255) / 256, sms * 8);
+	k_raygen<<<g256, 256, 0, st>>>(c->scene, wp, w.pixels, w.q[0]);
+	const int gt = sms * 16, gs = sms * 8;
+	for(int it = 0; it < max_iters; ++it)
+	{
+		TaskQueue &in = w.q[it & 1], &out = w.q[(it + 1) & 1];
+		if(count) k_trace<true><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, c->d_counters);
+		else k_trace<false><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, c->d_counters);
+		k_shade<<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it);
+		if(count) k_shadow<true><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
+		else k_shadow<false><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
+		c->stats.kernel_launches += 3;
+	}
+	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl);
+	c->stats.kernel_launches += 2;
+	YG_CUDA(c, cudaGetLastError());
+	YG_CUDA(c, cudaMemcpyAsync(w.h_ctl, w.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
+	YG_CUDA(c, cudaStreamSynchronize(st));
+	overflow = w.h_ctl->overflow != 0;
+	c->stats.waves++;
+	if(overflow) { c->stats.wave_retries++; return YAFGPU_OK; }
+	c->stats.rays_camera += (uint64_t)wp.n_slots;
+	c->stats.camera_samples += (uint64_t)wp.n_slots;
+	for(int it = 1; it <= max_iters; ++it) c->stats.rays_extension += (uint64_t)w.h_ctl->n_tasks[it];
+	uint64_t sh = 0;
+	for(int it = 0; it < max_iters; ++it) sh += (uint64_t)w.h_ctl->n_shadow[it];
+	if(c->scene.integ.tr_shad) c->stats.rays_shadow_transp += sh; else c->stats.rays_shadow += sh;
+	return YAFGPU_OK;
+}
+
+int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
+{
+	if(p->n_samples <= 0) return setErr(c, YAFGPU_ERR_INVALID, "n_samples must be positive");
+	if(p->adaptive && p->resample_mask == nullptr && false) return setErr(c, YAFGPU_ERR_INVALID, "adaptive pass without mask");
+	int s_begin = p->sample_begin, s_end = p->sample_end;
+	if(s_begin == 0 && s_end == 0) s_end = p->n_samples;
+	if(s_begin < 0 || s_end > p->n_samples || s_begin >= s_end) return setErr(c, YAFGPU_ERR_INVALID, "sample range");
+	size_t n_pix = 0;
+	int rc = buildPixelList(c, p, n_pix);
+	if(rc != YAFGPU_OK) return rc;
+	if(n_pix == 0) return YAFGPU_OK;
+
+	const IntegratorDev &ig = c->scene.integ;
+	int max_add = 0;
+	for(const MatDev &m : c->h_mats) max_add = std::max(max_add, m.additional_depth);
+	const int rdepth = std::min(ig.r_depth + max_add, 19);
+	const int max_iters = std::min(YG_MAX_ITERS, rdepth + 1 + (ig.type == YAFGPU_INT_PATHTRACING ? ig.max_bounces + 1 : 0));
+
+	// wave sizing: a wave covers `n_pix_w` pixels x `n_smp_w` samples
+	const int wave_cap = c->wave_cap_override > 0 ? c->wave_cap_override : (1 << 20);
+	const int fan = c->task_fan_override > 0 ? c->task_fan_override : 8;
+	cudaError_t e = allocWavefront(c, wave_cap, wave_cap * fan, wave_cap * fan);
+	if(e != cudaSuccess) return cudaErr(c, e, "wavefront allocation");
+	Wavefront &w = c->wf;
+
+	cudaEventRecord(c->ev0, c->stream);
+	const int n_smp = s_end - s_begin;
+	size_t pix0 = 0;
+	int smp0 = 0;
+	int cur_cap = wave_cap;
+	while(smp0 < n_smp)
+	{
+		WaveParams wp;
+		// fill a wave: whole-pixel-list x several samples when the list is small, else a slice of the list for one sample
+		if((size_t)cur_cap >= n_pix && pix0 == 0)
+		{
+			wp.n_pix = (int)n_pix; wp.pix_base = 0;
+			const int ns = std::max(1, std::min(n_smp - smp0, (int)((size_t)cur_cap / n_pix)));
+			wp.n_slots = wp.n_pix * ns;
+		}
+		else
+		{
+			wp.pix_base = (int)pix0; wp.n_pix = (int)std::min((size_t)cur_cap, n_pix - pix0);
+			wp.n_slots = wp.n_pix;
+		}
+		wp.sample_base = s_begin + smp0;
+		wp.n_samples_pass = p->n_samples; wp.pass_offs = p->offset; wp.aa_passes = c->film.aa_passes;
+		wp.task_cap = w.task_cap; wp.shadow_cap = w.shadow_cap;
+		wp.seed = hashSeed((unsigned)p->offset, (unsigned)wp.sample_base, (unsigned)p->aa_pass_number);
+		bool overflow = false;
+		rc = runWave(c, wp, max_iters, overflow);
+		if(rc != YAFGPU_OK) return rc;
+		if(overflow)
+		{
+			if(cur_cap <= 1024) return setErr(c, YAFGPU_ERR_NOMEM, "wavefront queues overflow even at the smallest wave size");
+			cur_cap /= 2;
+			continue; // retry the same range with a smaller wave
+		}
+		const int ns_done = wp.n_slots / wp.n_pix;
+		if(wp.pix_base == 0 && (size_t)wp.n_pix == n_pix) smp0 += ns_done;
+		else
+		{
+			pix0 += (size_t)wp.n_pix;
+			if(pix0 >= n_pix) { pix0 = 0; smp0 += 1; }
+		}
+	}
+	cudaEventRecord(c->ev1, c->stream);
+	cudaStreamSynchronize(c->stream);
+	float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+	c->stats.ms_total += ms;
+	return YAFGPU_OK;
+}
+
+} // namespace yg

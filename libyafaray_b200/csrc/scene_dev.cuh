@@ -35,7 +35,7 @@ struct Accel
 };
 
 // ---- shading data (global triangle order) ---------------------------------------------------------------------------
-struct TriShade
+struct __align__(16) TriShade // 64 B = four 16 B loads
 {
 	int v[3];     // indices into points
 	int n[3];     // indices into normals or -1
@@ -43,6 +43,7 @@ struct TriShade
 	int mat;      // material index
 	int obj;      // object index
 	float ng[3];  // geometric normal, Triangle::recNormal (triangle.h:274-281)
+	int pad[2];
 };
 
 struct ObjDev { int has_orco, has_uv, smooth, light; };
@@ -68,7 +69,7 @@ struct MatDev
 	int absorb; float beer_sigma_a[3];
 	// glossy / coated glossy
 	float gloss_col[3], diff_col[3], gl_mirror_col[3];
-	float gl_diffuse, gl_glossy, gl_exponent, exp_u, exp_v, gl_mirror_strength;
+	float gl_diffuse, gl_glossy, gl_exponent, exp_u, exp_v, gl_mirror_strength, p_diffuse;
 	int as_diffuse, anisotropic, with_diffuse, gl_oren_nayar; float gl_oren_a, gl_oren_b;
 	// blend
 	int mat1, mat2; float blend_val;
@@ -90,6 +91,7 @@ struct LightDev
 	// mesh / background: offsets into LightTables
 	int cdf_offset, cdf_count; float cdf_integral;
 	int tri_first, tri_count;
+	int accel;          // mesh light: index into SceneDev::light_accels (its own BVH, as MeshLight builds its own kd-tree), -1 = none
 	float clamp_intersect; int shoot_caustic;
 };
 
@@ -136,6 +138,7 @@ struct SceneDev
 	const MatDev *materials;
 	const LightDev *lights; int n_lights;
 	const float *light_tables;
+	const Accel *light_accels;
 	const FaureTables *faure;
 	CameraDev cam;
 	BackgroundDev bg;

@@ -11,6 +11,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <vector>
 
 namespace yg {
 
@@ -21,8 +22,6 @@ enum { TASK_INTEGRATE = 0, TASK_PATH = 1 };
 //  bits 1-5   raylevel (0..31)
 //  bits 6-11  depth of the path vertex (0..63)
 //  bits 12-19 ray_division (1..255)
-//  bit 20     chromatic
-//  bit 21     include_lights
 //  bit 22     caustic
 //  bits 23-27 additional_depth (0..31)
 struct TaskQueue
@@ -30,7 +29,8 @@ struct TaskQueue
 	float4 *ray_o;   // from.xyz, tmin
 	float4 *ray_d;   // dir.xyz, tmax (<0 = infinite)
 	float4 *hit;     // t, u, v, bits(tri)     written by k_trace
-	float4 *wgt;     // weight rgb, wavelength
+	float4 *wgt;     // rgb factor from this task's result up to the camera sample
+	float4 *thr;     // TASK_PATH: throughput of the path alone (Russian roulette uses it, integrator_path_tracer.cc:285)
 	uint4 *st;       // slot, offs (path) , packed, ray_offset
 	float2 *dc;      // dc_1, dc_2
 };
@@ -61,7 +61,8 @@ struct Wavefront
 	ShadowQueue sq;
 	float4 *acc = nullptr;        // per camera sample: rgb sum, alpha
 	uint32_t *pixels = nullptr;   // pass pixel list: x | y << 16
-	size_t pixels_cap = 0;
+	size_t pixels_cap = 0, pixels_n = 0;
+	std::vector<int> pixels_key; // parameters the cached pixel list was built for
 	WaveCtl *ctl = nullptr;
 	WaveCtl *h_ctl = nullptr;     // pinned mirror
 	int wave_cap = 0;             // camera samples per wave

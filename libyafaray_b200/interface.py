@@ -290,11 +290,11 @@ class Interface:
             s = m.u.glossy
             s.color, s.diffuse_color = col("color", (1, 1, 1, 1)), col("diffuse_color", (1, 1, 1, 1))
             s.mirror_color = col("mirror_color", (1, 1, 1, 1))
-            s.diffuse_reflect, s.glossy_reflect = g(p, "diffuse_reflect", 0.0), g(p, "glossy_reflect", 1.0 if t == "glossy" else 0.0)
-            s.specular_reflect = g(p, "specular_reflect", 0.0)
+            s.diffuse_reflect, s.glossy_reflect = g(p, "diffuse_reflect", 0.0), g(p, "glossy_reflect", 1.0)
+            s.specular_reflect = g(p, "specular_reflect", 1.0)
             s.exponent, s.exp_u, s.exp_v = g(p, "exponent", 50.0), g(p, "exp_u", 50.0), g(p, "exp_v", 50.0)
             s.ior = g(p, "IOR", 1.4)
-            s.as_diffuse, s.anisotropic = int(g(p, "as_diffuse", False)), int(g(p, "anisotropic", False))
+            s.as_diffuse, s.anisotropic = int(g(p, "as_diffuse", True)), int(g(p, "anisotropic", False))
             s.oren_nayar = int(g(p, "diffuse_brdf", "") == "Oren-Nayar")
             s.sigma = g(p, "sigma", 0.1)
         elif t == "blend_mat":  # material_blend.cc:464-518
