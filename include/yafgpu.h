@@ -368,6 +368,11 @@ typedef struct yafgpu_stats
 	uint64_t nodes_visited, tris_tested;   /* filled only when the context was created with YAFGPU_FLAG_COUNT_TRAVERSAL */
 	double ms_build, ms_trace, ms_shade, ms_film, ms_total; /* CUDA-event times accumulated since the last reset */
 	uint64_t waves, wave_retries;
+	/* filled only with YAFGPU_FLAG_TIME_STAGES: per-kernel-class CUDA-event time and NON-EMPTY launch counts
+	 * (ms_trace = closest-hit kernel, ms_shadow = any-hit kernel, ms_shade = shading kernel, ms_film = raygen + film splat) */
+	double ms_shadow;
+	uint64_t launches_trace, launches_shadow, launches_shade;
+	uint64_t rays_in_timed_trace, rays_in_timed_shadow;
 } yafgpu_stats;
 
 enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2 };

@@ -132,7 +132,9 @@ class Stats(C.Structure):
                 ("rays_light_probe", u64), ("camera_samples", u64), ("kernel_launches", u64), ("bvh_nodes", u64),
                 ("bvh_bytes", u64), ("tri_bytes", u64), ("nodes_visited", u64), ("tris_tested", u64),
                 ("ms_build", C.c_double), ("ms_trace", C.c_double), ("ms_shade", C.c_double), ("ms_film", C.c_double),
-                ("ms_total", C.c_double), ("waves", u64), ("wave_retries", u64)]
+                ("ms_total", C.c_double), ("waves", u64), ("wave_retries", u64), ("ms_shadow", C.c_double),
+                ("launches_trace", u64), ("launches_shadow", u64), ("launches_shade", u64), ("rays_in_timed_trace", u64),
+                ("rays_in_timed_shadow", u64)]
 
 
 # every entry point include/yafgpu.h declares: name -> (restype, argtypes)

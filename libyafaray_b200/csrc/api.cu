@@ -138,6 +138,7 @@ void yafgpu_destroy(yafgpu_ctx *c)
 	freeScene(c);
 	freeWavefront(c);
 	cudaFree(c->d_faure); cudaFree(c->d_counters);
+	for(cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
 	if(c->ev0) cudaEventDestroy(c->ev0);
 	if(c->ev1) cudaEventDestroy(c->ev1);
 	if(c->stream) cudaStreamDestroy(c->stream);

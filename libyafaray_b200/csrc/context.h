@@ -46,6 +46,7 @@ struct yafgpu_ctx
 	yafgpu_stats stats;
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	std::vector<cudaEvent_t> stage_events; // YAFGPU_FLAG_TIME_STAGES
 };
 
 namespace yg {

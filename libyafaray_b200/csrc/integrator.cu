@@ -708,14 +708,22 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	const int g256 = std::min((wp.n_slots + 255) / 256, sms * 8);
 	k_raygen<<<g256, 256, 0, st>>>(c->scene, wp, w.pixels, w.q[0]);
 	const int gt = sms * 16, gs = sms * 8;
+	const bool timed = (c->flags & YAFGPU_FLAG_TIME_STAGES) != 0;
+	std::vector<cudaEvent_t> &ev = c->stage_events;
+	size_t ne = 0;
+	auto mark = [&]() { if(!timed) return; if(ne >= ev.size()) { cudaEvent_t e; cudaEventCreate(&e); ev.push_back(e); } cudaEventRecord(ev[ne++], st); };
+	mark();
 	for(int it = 0; it < max_iters; ++it)
 	{
 		TaskQueue &in = w.q[it & 1], &out = w.q[(it + 1) & 1];
 		if(count) k_trace<true><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, c->d_counters);
 		else k_trace<false><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, c->d_counters);
+		mark();
 		k_shade<<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it);
+		mark();
 		if(count) k_shadow<true><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
 		else k_shadow<false><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
+		mark();
 		c->stats.kernel_launches += 3;
 	}
 	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl);
@@ -725,6 +733,16 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	YG_CUDA(c, cudaStreamSynchronize(st));
 	overflow = w.h_ctl->overflow != 0;
 	c->stats.waves++;
+	if(timed && !overflow)
+	{
+		for(int it = 0; it < max_iters; ++it)
+		{
+			float a = 0.f, b = 0.f, d = 0.f;
+			cudaEventElapsedTime(&a, ev[3 * it], ev[3 * it + 1]); cudaEventElapsedTime(&b, ev[3 * it + 1], ev[3 * it + 2]); cudaEventElapsedTime(&d, ev[3 * it + 2], ev[3 * it + 3]);
+			if(w.h_ctl->n_tasks[it] > 0) { c->stats.ms_trace += a; c->stats.ms_shade += b; c->stats.launches_trace++; c->stats.launches_shade++; c->stats.rays_in_timed_trace += (uint64_t)w.h_ctl->n_tasks[it]; }
+			if(w.h_ctl->n_shadow[it] > 0) { c->stats.ms_shadow += d; c->stats.launches_shadow++; c->stats.rays_in_timed_shadow += (uint64_t)w.h_ctl->n_shadow[it]; }
+		}
+	}
 	if(overflow) { c->stats.wave_retries++; return YAFGPU_OK; }
 	c->stats.rays_camera += (uint64_t)wp.n_slots;
 	c->stats.camera_samples += (uint64_t)wp.n_slots;

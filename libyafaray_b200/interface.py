@@ -474,6 +474,17 @@ class Interface:
             b.type = capi.BG_CONSTANT
             b.color = capi.F3(*[np.float32(x) for x in g(bp, "color", (0, 0, 0, 1))[:3]])
             b.power, b.ibl, b.with_caustic = g(bp, "power", 1.0), int(g(bp, "ibl", False)), int(g(bp, "with_caustic", True))
+            if b.ibl:
+                # ConstantBackground::factory creates and adds a "bglight" AFTER all parsed lights (background_constant.cc:69-83)
+                bl = capi.Light()
+                bl.type, bl.light_enabled, bl.cast_shadows = capi.LIGHT_BACKGROUND, 1, int(g(bp, "cast_shadows", True))
+                bl.samples, bl.object = int(g(bp, "ibl_samples", 16)), -1
+                bl.shoot_caustic, bl.shoot_diffuse = int(g(bp, "with_caustic", True)), int(g(bp, "with_diffuse", True))
+                bl.abs_intersect, bl.clamp_intersect = 0, 0.0
+                lts.append(bl)
+                larr = (capi.Light * len(lts))(*lts)
+                d.lights, d.n_lights = larr, len(lts)
+                keep.append(larr)
 
         # film + AA (environment.cc:456-584, 679-813)
         f = d.film

@@ -104,10 +104,10 @@ def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, ray
     _quad(y, (1, -1, 0), (1, -1, 2), (1, 1, 2), (1, 1, 0), green)         # right wall
     y.endTriMesh()
     y.startTriMesh(2, 8, 12, False, False, 0)
-    _box(y, (-0.65, 0.05, 0.0), (-0.05, 0.65, 1.2), white, rot_deg=18.0)   # tall diffuse box
+    _box(y, (-0.65, 0.05, 0.002), (-0.05, 0.65, 1.2), white, rot_deg=18.0)   # tall diffuse box
     y.endTriMesh()
     y.startTriMesh(3, 8, 12, False, False, 0)
-    _box(y, (0.1, -0.55, 0.0), (0.7, 0.05, 0.6), gl, rot_deg=-17.0)        # short glass box
+    _box(y, (0.1, -0.55, 0.002), (0.7, 0.05, 0.6), gl, rot_deg=-17.0)   # lifted off the floor: coplanar faces are epsilon ties        # short glass box
     y.endTriMesh()
     y.startTriMesh(20, 4, 2, False, False, 0)
     z = 1.98

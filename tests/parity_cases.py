@@ -1,0 +1,156 @@
+"""Parity cases shared by tests/ and tools/make_golden.py: name -> (scene builder, kind).
+
+kind "exact"     : deterministic in the reference (no Russian roulette draw, one light): compared per pixel at 1e-5.
+kind "converged" : Monte-Carlo; the golden file holds a high-spp reference render (tools/make_golden.py) and the test
+                   compares a high-spp GPU render with it (north_star: per-pixel RMSE <= 1e-3 relative to the converged image).
+"""
+from libyafaray_b200 import scenes
+
+W, H = 64, 36
+
+
+def _cornell(**kw):
+    return lambda spp: scenes.cornell_box(W, H, spp, **kw)
+
+
+EXACT = {
+    "simple_dl_gauss": lambda: scenes.simple_point_scene(160, 90, 1),
+    "simple_dl_box4": lambda: scenes.simple_point_scene(160, 90, 4, filter_type="box"),
+    "simple_pt_box8": lambda: scenes.simple_point_scene(160, 90, 8, integrator="pathtracing", filter_type="box"),
+    "cornell_dl_noglass": lambda: scenes.cornell_box(160, 90, 4, integrator="directlighting", glass=False),
+    "cornell_dl_glass": lambda: scenes.cornell_box(160, 90, 4, integrator="directlighting"),
+    "cornell_dl_mitchell": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", filter_type="mitchell", aa_passes=2),
+}
+
+# name -> (builder(spp), converged spp of the golden reference)
+CONVERGED = {
+    "cornell_pt": (_cornell(path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2), 65536),
+    "cornell_pt_noglass": (_cornell(glass=False, path_samples=1, bounces=4, raydepth=4, rr_min_bounces=1), 32768),
+}
+
+
+def trace_rays(n, lo, hi, seed=1, tmin=5e-5):
+    """Fixed ray set: origins uniform in the (enlarged) scene bound, isotropic directions, seeded."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    o = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    r = np.zeros((n, 8), np.float32)
+    r[:, 0:3], r[:, 3], r[:, 4:7], r[:, 7] = o, tmin, d, -1.0
+    return r
+
+
+def grid_mesh_scene(n_side=64, seed=3, width=64, height=36):
+    """Procedural displaced grid (2*n_side^2 triangles) in the spirit of config 3, small enough for the oracle."""
+    import numpy as np
+    from libyafaray_b200.interface import Interface
+    rng = np.random.default_rng(seed)
+    y = Interface()
+    y.startScene(0)
+    for k, col in enumerate([(0.8, 0.3, 0.3), (0.3, 0.8, 0.3), (0.3, 0.3, 0.8)]):
+        y.paramsClearAll(); y.paramsSetString("type", "shinydiffusemat"); y.paramsSetColor("color", *col)
+        y.createMaterial("m%d" % k)
+    xs = np.linspace(-4, 4, n_side + 1, dtype=np.float32)
+    zz = (rng.random((n_side + 1, n_side + 1)) * 0.6).astype(np.float32)
+    y.startGeometry()
+    y.startTriMesh(1, (n_side + 1) ** 2, 2 * n_side * n_side, False, False, 0)
+    for j in range(n_side + 1):
+        for i in range(n_side + 1):
+            y.addVertex(float(xs[i]), float(xs[j]), float(zz[j, i]))
+    for j in range(n_side):
+        for i in range(n_side):
+            a = j * (n_side + 1) + i
+            m = "m%d" % ((i + j) % 3)
+            y.addTriangle(a, a + 1, a + n_side + 2, m)
+            y.addTriangle(a, a + n_side + 2, a + n_side + 1, m)
+    y.endTriMesh()
+    y.endGeometry()
+    y.paramsClearAll(); y.paramsSetString("type", "pointlight"); y.paramsSetPoint("from", 0.5, -1.0, 6.0)
+    y.paramsSetColor("color", 1, 1, 1); y.paramsSetFloat("power", 40.0); y.createLight("L")
+    y.paramsClearAll(); y.paramsSetString("type", "perspective")
+    y.paramsSetPoint("from", 0, -9, 5); y.paramsSetPoint("to", 0, 0, 0); y.paramsSetPoint("up", 0, -9, 6)
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.2); y.createCamera("cam")
+    y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.1, 0.1, 0.2); y.createBackground("bg")
+    y.paramsClearAll(); y.paramsSetString("type", "directlighting"); y.paramsSetInt("raydepth", 2); y.createIntegrator("pt")
+    scenes._vol_none(y)
+    scenes.render_block(y, width, height, 1)
+    return y
+
+
+TRACE = {
+    "simple": lambda: scenes.simple_point_scene(),
+    "cornell": lambda: scenes.cornell_box(64, 36, 1),
+    "grid64": lambda: grid_mesh_scene(64),
+}
+TRACE_BOUNDS = {"simple": ((-14, -14, -4), (14, 14, 6)), "cornell": ((-1.4, -1.4, -0.4), (1.4, 1.4, 2.4)), "grid64": ((-5, -5, -1), (5, 5, 2))}
+
+
+def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, **integ):
+    """Every material and light type of the hot path in one small scene (configs 3/4 in miniature): glossy, coated_glossy,
+    rough_glass, blend_mat, mirror, glass and shinydiffuse boxes on a ground quad; sun + mesh light + constant-background IBL."""
+    from libyafaray_b200.interface import Interface
+    y = Interface(); y.startScene(0)
+
+    def mat(name, typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ)
+        for k, v in kw.items():
+            if isinstance(v, bool): y.paramsSetBool(k, v)
+            elif isinstance(v, int): y.paramsSetInt(k, v)
+            elif isinstance(v, float): y.paramsSetFloat(k, v)
+            elif isinstance(v, str): y.paramsSetString(k, v)
+            else: y.paramsSetColor(k, *v)
+        return y.createMaterial(name)
+    ground = mat("ground", "shinydiffusemat", color=(0.7, 0.7, 0.65))
+    mats = [
+        mat("gloss", "glossy", color=(0.9, 0.6, 0.2), diffuse_color=(0.5, 0.3, 0.1), diffuse_reflect=0.4, glossy_reflect=0.8, exponent=200.0, as_diffuse=False),
+        mat("coated", "coated_glossy", color=(0.2, 0.5, 0.9), diffuse_color=(0.1, 0.2, 0.5), diffuse_reflect=0.5, glossy_reflect=0.7, exponent=80.0, IOR=1.8, as_diffuse=False),
+        mat("rough", "rough_glass", IOR=1.5, alpha=0.3, filter_color=(0.9, 1.0, 0.9), transmit_filter=1.0),
+        mat("aniso", "glossy", color=(0.8, 0.8, 0.8), diffuse_color=(0.3, 0.3, 0.3), diffuse_reflect=0.3, anisotropic=True, exp_u=20.0, exp_v=800.0, as_diffuse=True),
+        mat("mirr", "shinydiffusemat", color=(0.6, 0.2, 0.2), specular_reflect=0.5, mirror_color=(1.0, 1.0, 1.0), fresnel_effect=True, IOR=1.6, diffuse_reflect=0.9),
+        mat("glas", "glass", IOR=1.45, filter_color=(1.0, 0.9, 0.9), transmit_filter=0.8, fake_shadows=transp_shad),
+        mat("sd_on", "shinydiffusemat", color=(0.3, 0.7, 0.3), diffuse_brdf="oren_nayar", sigma=0.4, transparency=0.3, translucency=0.2),
+    ]
+    y.paramsClearAll(); y.paramsSetString("type", "blend_mat"); y.paramsSetString("material1", "gloss"); y.paramsSetString("material2", "mirr")
+    y.paramsSetFloat("blend_value", 0.35)
+    mats.append(y.createMaterial("blend"))
+    lm = mat("lightmat", "light_mat", color=(1.0, 0.95, 0.8), power=6.0)
+    y.startGeometry()
+    y.startTriMesh(1, 4, 2, False, False, 0)
+    scenes._quad(y, (-8, -8, 0), (8, -8, 0), (8, 8, 0), (-8, 8, 0), ground)
+    y.endTriMesh()
+    for i, m in enumerate(mats):
+        y.startTriMesh(2 + i, 8, 12, False, False, 0)
+        x0, y0 = -3.6 + 1.9 * (i % 4), -0.4 + 2.2 * (i // 4)
+        scenes._box(y, (x0, y0, 0.003), (x0 + 1.2, y0 + 1.2, 1.0 + 0.15 * i), m, rot_deg=11.0 * i)
+        y.endTriMesh()
+    if meshlight:
+        y.startTriMesh(30, 4, 2, False, False, 0)
+        scenes._quad(y, (-1.0, 0.5, 3.5), (-1.0, 1.5, 3.5), (1.0, 1.5, 3.5), (1.0, 0.5, 3.5), lm)   # normal -z
+        y.endTriMesh()
+    y.endGeometry()
+    if meshlight:
+        y.paramsClearAll(); y.paramsSetString("type", "meshlight"); y.paramsSetInt("object", 30); y.paramsSetColor("color", 1.0, 0.95, 0.8)
+        y.paramsSetFloat("power", 6.0); y.paramsSetInt("samples", 2); y.createLight("ml")
+    if sun:
+        y.paramsClearAll(); y.paramsSetString("type", "sunlight"); y.paramsSetPoint("direction", 0.4, -0.5, 0.8); y.paramsSetFloat("angle", 2.0)
+        y.paramsSetColor("color", 1.0, 0.9, 0.8); y.paramsSetFloat("power", 1.2); y.paramsSetInt("samples", 2); y.createLight("sun")
+    y.paramsClearAll(); y.paramsSetString("type", "perspective")
+    y.paramsSetPoint("from", 0.5, -7.5, 4.0); y.paramsSetPoint("to", 0.0, 0.8, 0.6); y.paramsSetPoint("up", 0.5, -7.5, 5.0)
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3); y.createCamera("cam")
+    y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.35, 0.45, 0.7); y.paramsSetFloat("power", 0.8)
+    y.paramsSetBool("ibl", ibl); y.paramsSetInt("ibl_samples", 3); y.createBackground("bg")
+    y.paramsClearAll(); y.paramsSetString("type", integrator)
+    y.paramsSetInt("raydepth", integ.get("raydepth", 4)); y.paramsSetInt("shadowDepth", 3); y.paramsSetBool("transpShad", transp_shad)
+    if integrator == "pathtracing":
+        y.paramsSetInt("path_samples", integ.get("path_samples", 2)); y.paramsSetInt("bounces", integ.get("bounces", 4))
+        y.paramsSetInt("russian_roulette_min_bounces", integ.get("rr_min_bounces", 1))
+    y.createIntegrator("pt")
+    scenes._vol_none(y)
+    scenes.render_block(y, width, height, spp)
+    return y
+
+
+EXACT["zoo_dl_point_free"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3)
+EXACT["zoo_dl_transpshad"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, transp_shad=True)
+CONVERGED["zoo_pt"] = (lambda spp: material_zoo_scene(W, H, spp), 8192)

@@ -1,0 +1,138 @@
+"""CPU-side tests (`-m "not gpu"`): the C ABI library loads and exports every declared symbol, the host mirror of the
+reference interface, the oracle and its golden fixtures, and the world_size-2 film reduction (gloo)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tests import oracle_util as ou, parity_cases as pc, qmc_ref  # noqa: E402
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "yafgpu.h")).read()
+    names = set(re.findall(r"^(?:int|void|const char \*|void \*)\s*\*?(yafgpu_\w+)\(", hdr, re.M))
+    assert len(names) >= 18
+    lib = ctypes.CDLL(os.path.join(ROOT, "libyafaray_b200", "libyafgpu.so"))
+    for n in names:
+        assert hasattr(lib, n), n
+    from libyafaray_b200 import capi
+    assert set(capi.SYMBOLS) == names
+    assert lib.yafgpu_abi_version() == capi.ABI_VERSION
+
+
+def test_struct_sizes_match_header():
+    """ctypes mirrors vs the C compiler's view of include/yafgpu.h."""
+    from libyafaray_b200 import capi
+    src = '#include "yafgpu.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(yafgpu_material), sizeof(yafgpu_light), sizeof(yafgpu_scene_desc), sizeof(yafgpu_pass_desc), sizeof(yafgpu_stats), sizeof(yafgpu_camera), sizeof(yafgpu_object));return 0;}\n'
+    with tempfile.TemporaryDirectory() as td:
+        open(os.path.join(td, "a.c"), "w").write(src)
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), os.path.join(td, "a.c"), "-o", os.path.join(td, "a")])
+        out = subprocess.check_output([os.path.join(td, "a")]).decode().split()
+    want = [ctypes.sizeof(t) for t in (capi.Material, capi.Light, capi.SceneDesc, capi.PassDesc, capi.Stats, capi.Camera, capi.Object)]
+    assert [int(x) for x in out] == want
+
+
+def test_no_gpu_fails_loudly():
+    """Without a CUDA device the product must refuse, not fall back."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from libyafaray_b200 import Context, capi
+    with pytest.raises(capi.YafGpuError):
+        Context(0)
+
+
+def test_interface_xml_and_descriptor():
+    from libyafaray_b200 import scenes
+    y = scenes.cornell_box(64, 36, 2)
+    d, keep = y.scene_desc()
+    assert d.geometry.n_tris == 36 and d.n_lights == 1 and d.n_materials == 5
+    objs = [d.geometry.objects[i] for i in range(d.geometry.n_objects)]
+    assert [o.first_tri for o in objs] == [0, 10, 22, 34]           # ascending object id = global triangle order
+    assert d.lights[0].object == 3                                   # arealight tagged to mesh id 20
+    with tempfile.TemporaryDirectory() as td:
+        xml = y.to_xml(os.path.join(td, "s.xml"))
+        txt = open(xml).read()
+    assert txt.count("<f ") == 36 and 'sval="pathtracing"' in txt
+
+
+def test_golden_fixtures_present_and_sane():
+    for name in pc.EXACT:
+        f = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
+        assert f.ndim == 3 and f.shape[2] == 5 and np.isfinite(f).all() and f[..., 4].min() > 0
+
+
+@pytest.mark.skipif(ou.ref_bin("ieee") is None, reason="oracle/_ref not built")
+def test_oracle_reproduces_golden_film():
+    """The committed fixture is what the reference CPU code renders (single thread, bit-reproducible)."""
+    name = "simple_dl_gauss"
+    film, _ = ou.run_reference_render(pc.EXACT[name]())
+    gold = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
+    assert np.array_equal(film, gold)
+
+
+@pytest.mark.skipif(ou.ref_bin("ieee") is None, reason="oracle/_ref not built")
+def test_oracle_kat_matches_independent_restatement():
+    with tempfile.TemporaryDirectory() as td:
+        p = os.path.join(td, "kat.bin")
+        subprocess.check_call([ou.ref_bin("ieee"), "kat", p], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        kat = ou.read_kat(p)
+    for i in range(0, 4096, 37):
+        x = (i * 2654435761 + i) & 0xFFFFFFFF
+        h = qmc_ref.fnv32a(x)
+        assert kat["fnv32"][i] == h
+        assert kat["riVdC"][i] == qmc_ref.ri_vdc(x, h)
+        assert kat["riS"][i] == qmc_ref.ri_s(x, h)
+        assert kat["riLp"][i] == qmc_ref.ri_lp((x + h) & 0xFFFFFFFF)
+        assert kat["riVdC0"][i] == qmc_ref.ri_vdc(i)
+    # filter tables: box is all ones; gauss decreases from the centre
+    ft = kat["filter_tables"].reshape(4, 16, 16)
+    assert (ft[0] == 1).all() and ft[2][0, 0] > ft[2][8, 8] >= 0
+
+
+def test_tile_owner_map_partitions_image():
+    from libyafaray_b200 import parallel
+    om = parallel.owner_map(100, 70, 32, 3)
+    assert om.shape == (70, 100) and set(np.unique(om)) == {0, 1, 2}
+    assert om[0, 0] == 0 and om[0, 32] == 1 and om[0, 64] == 2 and om[0, 96] == 0 and om[32, 0] == 1  # 4 tiles per row
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    from libyafaray_b200 import parallel
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    w, h, ts = 96, 64, 32
+    rng = np.random.default_rng(7)
+    full = rng.random((h, w, 5)).astype(np.float32)
+    own = parallel.owner_map(w, h, ts, world) == rank
+    mine = full * own[..., None]
+    # filter spill: every rank also deposits a little into its neighbours' pixels
+    spill = np.roll(mine, 1, axis=1) * 0.25
+    film = torch.from_numpy(mine + spill)
+    parallel.reduce_film(film, 0)
+    if rank == 0:
+        want = full + np.roll(full, 1, axis=1) * 0.25
+        q.put(float(np.abs(film.numpy() - want).max()))
+    dist.destroy_process_group()
+
+
+def test_film_reduce_world2_gloo():
+    import torch.multiprocessing as mp
+    ctxm = mp.get_context("spawn")
+    q = ctxm.Queue()
+    port = 29500 + (os.getpid() % 400)
+    ps = [ctxm.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    for p in ps:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) < 1e-6
