@@ -6,6 +6,7 @@
 #include "traverse.cuh"
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <new>
 
 static std::string g_create_err;
@@ -36,7 +37,7 @@ static void freeScene(yafgpu_ctx *c)
 	cudaFree(c->d_points); cudaFree(c->d_normals); cudaFree(c->d_uv); cudaFree(c->d_tri_ng); cudaFree(c->d_tri_vidx);
 	cudaFree(c->d_tri_mat); cudaFree(c->d_mat_triflags); cudaFree(c->d_tris); cudaFree(c->d_objects); cudaFree(c->d_mats);
 	cudaFree(c->d_lights); cudaFree(c->d_light_tables); cudaFree(c->d_bg_tex); cudaFree(c->d_nodes); cudaFree(c->d_acc_tris);
-	cudaFree(c->film.pix); cudaFree(c->d_light_accels); c->d_light_accels = nullptr;
+	cudaFree(c->film.pix); cudaFree(c->d_mat_bucket); c->d_mat_bucket = nullptr; cudaFree(c->d_light_accels); c->d_light_accels = nullptr;
 	for(void *q : c->light_bvh_ptrs) cudaFree(q);
 	c->light_bvh_ptrs.clear();
 	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
@@ -255,6 +256,14 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, upload(c->d_tri_vidx, g.tri_vidx, g.n_tris * 3, st));
 	YG_CUDA(c, upload(c->d_tri_mat, g.tri_mat, g.n_tris, st));
 	YG_CUDA(c, upload(c->d_mat_triflags, triflags.data(), triflags.size(), st));
+	{	// sort buckets of the shading kernel: materials ranked by (type, index) so that equal code paths are adjacent
+		std::vector<int> order(c->h_mats.size()), bucket(c->h_mats.size() ? c->h_mats.size() : 1, 0);
+		for(size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+		std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return c->h_mats[a].type < c->h_mats[b].type; });
+		c->n_mat_buckets = (int)std::min<size_t>(std::max<size_t>(order.size(), 1), 4096);
+		for(size_t r = 0; r < order.size(); ++r) bucket[order[r]] = (int)(r * (size_t)c->n_mat_buckets / std::max<size_t>(order.size(), 1));
+		YG_CUDA(c, upload(c->d_mat_bucket, bucket.data(), bucket.size(), st));
+	}
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
 	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
 	YG_CUDA(c, cudaMalloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1)));

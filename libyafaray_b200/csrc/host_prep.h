@@ -258,8 +258,8 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 			st3(d.pos, ndir); st3(d.du, du); st3(d.dv, dv);
 			return true;
 		}
-		case YAFGPU_LIGHT_MESH: // MeshLight::MeshLight light_meshlight.cc:32-43: color_ = col * inte; tables/BVH built by the caller (initIs)
-			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+		case YAFGPU_LIGHT_MESH: // MeshLight::factory light_meshlight.cc:251: color * (float)power * M_PI; tables/BVH built by the caller (initIs)
+			for(int k = 0; k < 3; ++k) d.color[k] = (l.color[k] * l.power) * (float)YG_M_PI;
 			d.accel = -1;
 			return true;
 		case YAFGPU_LIGHT_BACKGROUND: // BackgroundLight ctor light_background.cc:56-65; tables built by buildBgLightTables (init)

@@ -170,19 +170,87 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, cons
 }
 
 // ---- K3: closest hit for every queued task -----------------------------------------------------------------------------
+// Besides the hit record the kernel bins every task by (task kind, material) — the key of the counting sort that makes
+// warps of the shading kernel run ONE material's code (the reference dispatches per hit through a virtual call; here
+// divergence inside a warp is the cost that matters, ncu: 2.6 active threads per instruction without the sort).
+struct SortBins
+{
+	const int *tri_mat;     // per global triangle: material index
+	const int *mat_bucket;  // per material: rank in (type, id) order
+	int n_mat;              // buckets: kind * n_mat + mat_bucket, last bucket (2 * n_mat) = miss
+	int *key;               // per task: bucket
+	int *hist;              // per bucket: count (zeroed before the launch)
+};
+
+// warp-aggregated atomicAdd(&counter[key], 1) for the lanes named in `valid`; returns this lane's slot
+__device__ __forceinline__ int binAdd(int *counter, int key, unsigned valid)
+{
+	const unsigned m = __match_any_sync(valid, key);
+	const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+	int base = 0;
+	if(lane == leader) base = atomicAdd(counter + key, __popc(m));
+	base = __shfl_sync(m, base, leader);
+	return base + __popc(m & ((1u << lane) - 1u));
+}
+
 template<bool COUNT>
-__global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int *__restrict__ n_tasks, int task_cap, unsigned long long *__restrict__ counters)
+__global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int *__restrict__ n_tasks, int task_cap, SortBins bins, unsigned long long *__restrict__ counters)
 {
 	const int n = min(*n_tasks, task_cap);
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
-	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	const int stride = gridDim.x * blockDim.x;
+	for(int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride)
 	{
+		const int i = base + (threadIdx.x & 31);
+		const bool valid = i < n;
+		const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+		if(!valid) continue;
 		const float4 a = q.ray_o[i], b = q.ray_d[i];
 		RayD r; r.o = mk(a.x, a.y, a.z); r.tmin = a.w; r.d = mk(b.x, b.y, b.z); r.tmax = b.w;
 		const HitD h = traceClosest<COUNT>(acc, r, &tc);
 		q.hit[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+		const int kind = (int)(q.st[i].z & 1u);
+		const int key = h.tri < 0 ? 2 * bins.n_mat : kind * bins.n_mat + __ldg(bins.mat_bucket + __ldg(bins.tri_mat + h.tri));
+		bins.key[i] = key;
+		binAdd(bins.hist, key, vmask);
 	}
 	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+}
+
+// exclusive scan of the bucket counts (one block; at most a few thousand buckets)
+__global__ void __launch_bounds__(1024) k_bin_scan(const int *__restrict__ hist, int *__restrict__ offs, int nb)
+{
+	__shared__ int part[1024];
+	const int per = (nb + 1023) / 1024;
+	const int b0 = threadIdx.x * per;
+	int sum = 0;
+	for(int k = 0; k < per; ++k) if(b0 + k < nb) sum += hist[b0 + k];
+	part[threadIdx.x] = sum;
+	__syncthreads();
+	for(int d = 1; d < 1024; d <<= 1)
+	{
+		const int v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+		__syncthreads();
+		part[threadIdx.x] += v;
+		__syncthreads();
+	}
+	int run = part[threadIdx.x] - sum;
+	for(int k = 0; k < per; ++k) if(b0 + k < nb) { offs[b0 + k] = run; run += hist[b0 + k]; }
+}
+
+// scatter: perm[slot in bucket order] = task index
+__global__ void __launch_bounds__(256) k_bin_scatter(const int *__restrict__ n_tasks, int task_cap, const int *__restrict__ key, int *__restrict__ offs, int *__restrict__ perm)
+{
+	const int n = min(*n_tasks, task_cap);
+	const int stride = gridDim.x * blockDim.x;
+	for(int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride)
+	{
+		const int i = base + (threadIdx.x & 31);
+		const bool valid = i < n;
+		const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+		if(!valid) continue;
+		perm[binAdd(offs, key[i], vmask)] = i;
+	}
 }
 
 // ---- shading helpers ---------------------------------------------------------------------------------------------------
@@ -303,13 +371,14 @@ YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, i
 
 // ---- K5-K8: one thread per task ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
-                                               float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter)
+                                               float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter, const int *__restrict__ perm)
 {
 	const int n = min(ctl->n_tasks[iter], wp.task_cap);
 	ShadeCtx cx; cx.sc = &sc; cx.wp = wp; cx.out = out; cx.sq = sq; cx.acc = acc; cx.ctl = ctl; cx.iter = iter;
 	const IntegratorDev &ig = sc.integ;
-	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	for(int ii = blockIdx.x * blockDim.x + threadIdx.x; ii < n; ii += gridDim.x * blockDim.x)
 	{
+		const int i = perm[ii]; // tasks in (kind, material) order: a warp shades one material
 		const float4 ro = in.ray_o[i], rd = in.ray_d[i], hh = in.hit[i], wg = in.wgt[i];
 		const uint4 st = in.st[i];
 		const int slot = (int)st.x;
@@ -331,6 +400,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp); // Point3 h = ray.from_ + z * ray.dir_ (scene.cc:908)
 			const MatDev &m = sc.materials[sp.mat];
+			matInitBsdf(m, sp);
 			const unsigned bsdfs = m.bsdf_flags;
 			const V3 wo = -dir;
 			const int raylevel = stRaylevel(packed);
@@ -451,6 +521,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp);
 			const MatDev &m = sc.materials[sp.mat];
+			matInitBsdf(m, sp);
 			const unsigned bsdfs = m.bsdf_flags;
 			const V3 pwo = -dir;
 			const float4 th = in.thr[i];
@@ -629,7 +700,8 @@ void freeWavefront(yafgpu_ctx *c)
 		w.q[k] = TaskQueue();
 	}
 	cudaFree(w.sq.ray_o); cudaFree(w.sq.ray_d); cudaFree(w.sq.contrib); w.sq = ShadowQueue();
-	cudaFree(w.acc); cudaFree(w.pixels); cudaFree(w.ctl);
+	cudaFree(w.acc); cudaFree(w.pixels); cudaFree(w.ctl); cudaFree(w.key); cudaFree(w.perm); cudaFree(w.hist);
+	w.key = w.perm = w.hist = nullptr;
 	if(w.h_ctl) cudaFreeHost(w.h_ctl);
 	w.acc = nullptr; w.pixels = nullptr; w.ctl = nullptr; w.h_ctl = nullptr; w.pixels_cap = 0;
 	w.allocated = false; w.pixels_key.clear();
@@ -652,6 +724,7 @@ static cudaError_t allocWavefront(yafgpu_ctx *c, int wave_cap, int task_cap, int
 	}
 	A(w.sq.ray_o, float4, shadow_cap); A(w.sq.ray_d, float4, shadow_cap); A(w.sq.contrib, float4, shadow_cap);
 	A(w.acc, float4, wave_cap); A(w.ctl, WaveCtl, 1);
+	A(w.key, int, task_cap); A(w.perm, int, task_cap); A(w.hist, int, 2 * YG_MAX_BUCKETS);
 #undef A
 	if(e == cudaSuccess) e = cudaMallocHost(&w.h_ctl, sizeof(WaveCtl));
 	if(e != cudaSuccess) { uint32_t *p2 = w.pixels; w.pixels = nullptr; freeWavefront(c); w.pixels = p2; return e; }
@@ -716,15 +789,20 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	for(int it = 0; it < max_iters; ++it)
 	{
 		TaskQueue &in = w.q[it & 1], &out = w.q[(it + 1) & 1];
-		if(count) k_trace<true><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, c->d_counters);
-		else k_trace<false><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, c->d_counters);
+		SortBins bins; bins.tri_mat = c->d_tri_mat; bins.mat_bucket = c->d_mat_bucket; bins.n_mat = c->n_mat_buckets; bins.key = w.key; bins.hist = w.hist;
+		const int nb = 2 * c->n_mat_buckets + 1;
+		cudaMemsetAsync(w.hist, 0, sizeof(int) * nb, st);
+		if(count) k_trace<true><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, c->d_counters);
+		else k_trace<false><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, c->d_counters);
 		mark();
-		k_shade<<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it);
+		k_bin_scan<<<1, 1024, 0, st>>>(w.hist, w.hist + YG_MAX_BUCKETS, nb);
+		k_bin_scatter<<<sms * 4, 256, 0, st>>>(&w.ctl->n_tasks[it], wp.task_cap, w.key, w.hist + YG_MAX_BUCKETS, w.perm);
+		k_shade<<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm);
 		mark();
 		if(count) k_shadow<true><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
 		else k_shadow<false><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
 		mark();
-		c->stats.kernel_launches += 3;
+		c->stats.kernel_launches += 5;
 	}
 	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl);
 	c->stats.kernel_launches += 2;

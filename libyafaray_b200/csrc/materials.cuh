@@ -984,6 +984,17 @@ YG_D Col leafTransparency(const MatDev &m, const SurfPt &sp, V3 wo)
 	return mkc(0.f);
 }
 
+// BlendMaterial::initBsdf replaces the surface point by blendSurfacePoints__(sp, sp, ival) (material_blend.cc:77-104,
+// surface.cc:137-151): lerp__(a, a, alpha) = a * alpha + a * (1 - alpha) in float, which is not exactly `a`.
+YG_D V3 blendLerp(V3 a, float al, float ial) { return a * al + a * ial; }
+YG_D void matInitBsdf(const MatDev &m, SurfPt &sp)
+{
+	if(m.type != YAFGPU_MAT_BLEND) return;
+	const float ival = fminf(1.f, fmaxf(0.f, 1.f - m.blend_val));
+	const float al = ival, ial = (float)(1.0 - (double)ival);
+	sp.n = blendLerp(sp.n, al, ial); sp.nu = blendLerp(sp.nu, al, ial); sp.nv = blendLerp(sp.nv, al, ial);
+}
+
 // ---- top level: BlendMaterial dispatch (children are leaf materials; nesting is refused at upload) ----------------------
 
 YG_D Col matEval(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdfs)

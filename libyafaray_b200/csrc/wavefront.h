@@ -46,6 +46,7 @@ enum { CNT_RAYS_CAMERA = 0, CNT_RAYS_EXTENSION, CNT_RAYS_SHADOW, CNT_RAYS_SHADOW
        CNT_CAMERA_SAMPLES, CNT_NODES, CNT_TRIS, CNT_N };
 
 #define YG_MAX_ITERS 96
+#define YG_MAX_BUCKETS 8200 /* 2 task kinds x up to 4096 material buckets + miss */
 
 struct WaveCtl // lives in device memory, zeroed at wave start
 {
@@ -64,6 +65,8 @@ struct Wavefront
 	size_t pixels_cap = 0, pixels_n = 0;
 	std::vector<int> pixels_key; // parameters the cached pixel list was built for
 	WaveCtl *ctl = nullptr;
+	int *key = nullptr, *perm = nullptr; // per task: sort bucket, and the bucket-ordered permutation read by the shading kernel
+	int *hist = nullptr;                 // [2][YG_MAX_BUCKETS]: bucket counts, bucket offsets
 	WaveCtl *h_ctl = nullptr;     // pinned mirror
 	int wave_cap = 0;             // camera samples per wave
 	int task_cap = 0;             // tasks per queue

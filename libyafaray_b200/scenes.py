@@ -190,3 +190,84 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
     _vol_none(y)
     render_block(y, width, height, spp, filter_type=filter_type)
     return y
+
+
+def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=12345, bounces=8, raydepth=8, path_samples=1,
+                    rr_min_bounces=2, integrator="pathtracing", smooth=True):
+    """BASELINE config 3: procedural displaced-grid terrain of ~n_tris triangles (2*n^2) with materials cycling over
+    glossy / coated_glossy / rough_glass / shinydiffuse in 16x16-quad patches, a sun and an area light, path depth 8.
+    Built through the bulk mesh call (numpy arrays); value-noise displacement from a seeded generator."""
+    n = max(2, int(round((n_tris / 2) ** 0.5)))
+    rng = np.random.default_rng(seed)
+    y = Interface()
+    y.startScene(0)
+
+    def mat(name, typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ)
+        for k, v in kw.items():
+            if isinstance(v, bool): y.paramsSetBool(k, v)
+            elif isinstance(v, int): y.paramsSetInt(k, v)
+            elif isinstance(v, float): y.paramsSetFloat(k, v)
+            elif isinstance(v, str): y.paramsSetString(k, v)
+            else: y.paramsSetColor(k, *v)
+        return y.createMaterial(name)
+    names = [
+        mat("gloss_a", "glossy", color=(0.9, 0.7, 0.3), diffuse_color=(0.6, 0.4, 0.2), diffuse_reflect=0.5, glossy_reflect=0.7, exponent=500.0, as_diffuse=False),
+        mat("coat_a", "coated_glossy", color=(0.3, 0.5, 0.9), diffuse_color=(0.2, 0.3, 0.6), diffuse_reflect=0.6, glossy_reflect=0.6, exponent=100.0, IOR=1.8, as_diffuse=False),
+        mat("rough_a", "rough_glass", IOR=1.5, alpha=0.2, filter_color=(0.9, 1.0, 0.95), transmit_filter=1.0),
+        mat("diff_a", "shinydiffusemat", color=(0.7, 0.7, 0.7)),
+        mat("gloss_b", "glossy", color=(0.8, 0.8, 0.8), diffuse_color=(0.4, 0.5, 0.3), diffuse_reflect=0.7, glossy_reflect=0.4, exponent=50.0, as_diffuse=True),
+        mat("coat_b", "coated_glossy", color=(0.9, 0.3, 0.3), diffuse_color=(0.6, 0.2, 0.2), diffuse_reflect=0.7, glossy_reflect=0.5, exponent=2000.0, IOR=1.8, as_diffuse=False),
+    ]
+    # value noise: three octaves of bilinearly interpolated random lattices
+    xs = np.linspace(0.0, 1.0, n + 1, dtype=np.float32)
+    h = np.zeros((n + 1, n + 1), np.float32)
+    for cells, amp in ((8, 1.6), (64, 0.35), (512, 0.06)):
+        lat = rng.random((cells + 2, cells + 2)).astype(np.float32)
+        f = xs * cells
+        i0 = np.minimum(f.astype(np.int32), cells); t = (f - i0).astype(np.float32)
+        t = t * t * (3 - 2 * t)
+        a = lat[i0][:, i0]; b = lat[i0][:, i0 + 1]; c = lat[i0 + 1][:, i0]; d = lat[i0 + 1][:, i0 + 1]
+        tx, ty = t[None, :], t[:, None]
+        h += amp * ((a * (1 - tx) + b * tx) * (1 - ty) + (c * (1 - tx) + d * tx) * ty)
+    X, Y = np.meshgrid(xs * 20 - 10, xs * 20 - 10)
+    P = np.stack([X, Y, h], axis=-1).reshape(-1, 3).astype(np.float32)
+    j, i = np.meshgrid(np.arange(n, dtype=np.int32), np.arange(n, dtype=np.int32), indexing="ij")
+    a = (j * (n + 1) + i).reshape(-1)
+    F = np.empty((2 * n * n, 3), np.int32)
+    F[0::2] = np.stack([a, a + 1, a + n + 2], axis=1)
+    F[1::2] = np.stack([a, a + n + 2, a + n + 1], axis=1)
+    patch = ((j // 16) * 7 + (i // 16) * 3).reshape(-1) % len(names)
+    per_tri = np.repeat(patch, 2).astype(np.int32)
+    normals = None
+    if smooth:
+        gy, gx = np.gradient(h, 20.0 / n)
+        N = np.stack([-gx, -gy, np.ones_like(h)], axis=-1)
+        N /= np.linalg.norm(N, axis=-1, keepdims=True)
+        normals = N.reshape(-1, 3).astype(np.float32)
+    y.startGeometry()
+    y.addTriMeshArrays(1, P, F, (names, per_tri), normals=normals)
+    lm = mat("lightmat", "light_mat", color=(1.0, 1.0, 1.0), power=40.0)
+    y.startTriMesh(2, 4, 2, False, False, 0)
+    z = 6.0
+    _quad(y, (-2, -2, z), (-2, 2, z), (2, 2, z), (2, -2, z), lm)
+    y.endTriMesh()
+    y.endGeometry()
+    y.paramsClearAll(); y.paramsSetString("type", "arealight"); y.paramsSetPoint("corner", -2, -2, z); y.paramsSetPoint("point1", -2, 2, z)
+    y.paramsSetPoint("point2", 2, -2, z); y.paramsSetColor("color", 1.0, 1.0, 1.0); y.paramsSetFloat("power", 40.0)
+    y.paramsSetInt("samples", 1); y.paramsSetInt("object", 2); y.createLight("area")
+    y.paramsClearAll(); y.paramsSetString("type", "sunlight"); y.paramsSetPoint("direction", 0.5, -0.4, 0.75); y.paramsSetFloat("angle", 1.0)
+    y.paramsSetColor("color", 1.0, 0.95, 0.85); y.paramsSetFloat("power", 1.5); y.paramsSetInt("samples", 1); y.createLight("sun")
+    y.paramsClearAll(); y.paramsSetString("type", "perspective")
+    y.paramsSetPoint("from", 0.0, -13.0, 7.0); y.paramsSetPoint("to", 0.0, 0.0, 0.8); y.paramsSetPoint("up", 0.0, -13.0, 8.0)
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.4); y.createCamera("cam")
+    y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.4, 0.5, 0.7); y.paramsSetFloat("power", 1.0)
+    y.createBackground("bg")
+    y.paramsClearAll(); y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", raydepth); y.paramsSetInt("shadowDepth", 2)
+    if integrator == "pathtracing":
+        y.paramsSetInt("path_samples", path_samples); y.paramsSetInt("bounces", bounces)
+        y.paramsSetInt("russian_roulette_min_bounces", rr_min_bounces)
+    y.createIntegrator("pt")
+    _vol_none(y)
+    render_block(y, width, height, spp)
+    return y

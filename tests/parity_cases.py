@@ -86,7 +86,7 @@ TRACE = {
 TRACE_BOUNDS = {"simple": ((-14, -14, -4), (14, 14, 6)), "cornell": ((-1.4, -1.4, -0.4), (1.4, 1.4, 2.4)), "grid64": ((-5, -5, -1), (5, 5, 2))}
 
 
-def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, **integ):
+def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, only_mat=None, **integ):
     """Every material and light type of the hot path in one small scene (configs 3/4 in miniature): glossy, coated_glossy,
     rough_glass, blend_mat, mirror, glass and shinydiffuse boxes on a ground quad; sun + mesh light + constant-background IBL."""
     from libyafaray_b200.interface import Interface
@@ -120,6 +120,8 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
     scenes._quad(y, (-8, -8, 0), (8, -8, 0), (8, 8, 0), (-8, 8, 0), ground)
     y.endTriMesh()
     for i, m in enumerate(mats):
+        if only_mat is not None:
+            m = mats[only_mat]
         y.startTriMesh(2 + i, 8, 12, False, False, 0)
         x0, y0 = -3.6 + 1.9 * (i % 4), -0.4 + 2.2 * (i // 4)
         scenes._box(y, (x0, y0, 0.003), (x0 + 1.2, y0 + 1.2, 1.0 + 0.15 * i), m, rot_deg=11.0 * i)
@@ -151,6 +153,9 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
     return y
 
 
+# path tracing without Russian roulette and with ONE light is deterministic in the reference as well
+EXACT["cornell_pt_norr"] = lambda: scenes.cornell_box(160, 90, 16, path_samples=2, bounces=6, raydepth=6, rr_min_bounces=99)
+EXACT["zoo_pt_mesh_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, rr_min_bounces=99)
 EXACT["zoo_dl_point_free"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3)
 EXACT["zoo_dl_transpshad"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, transp_shad=True)
 CONVERGED["zoo_pt"] = (lambda spp: material_zoo_scene(W, H, spp), 8192)
