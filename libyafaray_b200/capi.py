@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libyafgpu.so")
+LIB_PATH = os.environ.get("YAFGPU_LIB") or os.path.join(_HERE, "libyafgpu.so")  # YAFGPU_LIB: kernel-variant experiments (tools/)
 
 ABI_VERSION = 1
 

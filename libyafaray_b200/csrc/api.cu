@@ -260,8 +260,17 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		std::vector<int> order(c->h_mats.size()), bucket(c->h_mats.size() ? c->h_mats.size() : 1, 0);
 		for(size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
 		std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return c->h_mats[a].type < c->h_mats[b].type; });
-		c->n_mat_buckets = (int)std::min<size_t>(std::max<size_t>(order.size(), 1), 4096);
-		for(size_t r = 0; r < order.size(); ++r) bucket[order[r]] = (int)(r * (size_t)c->n_mat_buckets / std::max<size_t>(order.size(), 1));
+		// one bucket per material while they fit, else one per type: a bucket never mixes types (per-type shading kernels)
+		const bool per_mat = order.size() <= 4096;
+		c->n_mat_buckets = per_mat ? (int)std::max<size_t>(order.size(), 1) : YG_N_MAT_TYPES;
+		for(int t = 0; t < YG_N_MAT_TYPES; ++t) { c->type_b0[t] = 0; c->type_b1[t] = -1; }
+		for(size_t r = 0; r < order.size(); ++r)
+		{
+			const int t = c->h_mats[order[r]].type, b = per_mat ? (int)r : t;
+			bucket[order[r]] = b;
+			if(c->type_b1[t] < 0) c->type_b0[t] = b;
+			c->type_b1[t] = b;
+		}
 		YG_CUDA(c, upload(c->d_mat_bucket, bucket.data(), bucket.size(), st));
 	}
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));

@@ -18,7 +18,8 @@ struct yafgpu_ctx
 	float *d_points = nullptr, *d_normals = nullptr, *d_uv = nullptr, *d_tri_ng = nullptr;
 	int *d_tri_vidx = nullptr, *d_tri_mat = nullptr;
 	unsigned *d_mat_triflags = nullptr;
-	int *d_mat_bucket = nullptr; int n_mat_buckets = 1; // material -> sort bucket (rank in (type, id) order, folded to <= 4096)
+	int type_b0[16] = {0}, type_b1[16] = {-1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1}; // per material type: bucket range, b1 < b0 = type absent
+	int *d_mat_bucket = nullptr; int n_mat_buckets = 1; // material -> sort bucket (rank in (type, id) order; one bucket per type above 4096 materials)
 	yg::TriShade *d_tris = nullptr;
 	yg::ObjDev *d_objects = nullptr;
 	yg::MatDev *d_mats = nullptr;

@@ -13,6 +13,7 @@
 
 #define YG_HD __host__ __device__ __forceinline__
 #define YG_D __device__ __forceinline__
+#define YG_DN static __device__ __noinline__
 
 namespace yg {
 

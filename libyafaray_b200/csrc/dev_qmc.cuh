@@ -48,25 +48,28 @@ YG_HD uint32_t fnv32a(uint32_t value)
 	return hash;
 }
 
-// Halton util_mcqmc.h:28-85 — incremental generator, double precision
-struct Halton
+// Halton util_mcqmc.h:28-85 — incremental generator, double precision.  BASE is a compile-time constant so that `% BASE`
+// and `/ BASE` become multiply-shift sequences; the arithmetic (order of the double additions and multiplications, the
+// 0.9999999999 guard) is the reference's.
+template<uint32_t BASE>
+struct HaltonB
 {
-	uint32_t base;
-	double inv_base, value;
-	YG_HD void setBase(int b) { base = (uint32_t)b; inv_base = 1.0 / (double)b; value = 0; }
+	double value;
 	YG_HD void setStart(uint32_t i)
 	{
+		const double inv_base = 1.0 / (double)BASE;
 		double factor = inv_base;
 		value = 0.0;
 		while(i > 0)
 		{
-			value += (double)(i % base) * factor;
-			i /= base;
+			value += (double)(i % BASE) * factor;
+			i /= BASE;
 			factor *= inv_base;
 		}
 	}
 	YG_HD float getNext()
 	{
+		const double inv_base = 1.0 / (double)BASE;
 		double r = 0.9999999999 - value;
 		if(inv_base < r) value += inv_base;
 		else
@@ -75,6 +78,23 @@ struct Halton
 			while(h >= r) { hh = h; h *= inv_base; }
 			value += hh + h - 1.0;
 		}
+		return fmaxf(0.f, fminf(1.f, (float)value));
+	}
+};
+
+// Base 2.  Every intermediate of the reference's loops is exact in double here: the digits are bits, `factor` is a power of
+// two, and a partial sum has at most 33 significant bits (32-bit start index plus the increments of one light/BSDF loop).
+// The 1e-10 guard of getNext cannot change a branch either, because 1 - value and the candidate power of two differ by a
+// multiple of 2^-33 = 1.16e-10.  Element i of the sequence is therefore exactly bitreverse64(i) * 2^-64, which is what this
+// computes — same bits as the incremental generator (the exact-render tests pin it), without the loops.
+struct Halton2
+{
+	unsigned long long idx;
+	YG_HD void setStart(uint32_t i) { idx = i; }
+	__device__ __forceinline__ float getNext()
+	{
+		++idx;
+		const double value = (double)__brevll(idx) * 5.42101086242752217e-20; // 2^-64
 		return fmaxf(0.f, fminf(1.f, (float)value));
 	}
 };
@@ -113,11 +133,15 @@ YG_HD double scrHaltonT(const FaureTables &tab, int dim, uint32_t n)
 	double value = 0.0;
 	const short *sigma = tab.sigma + tab.offset[dim];
 	const uint32_t base = (uint32_t)tab.base[dim];
+	// n % base without an integer division: floor(n / base) = (uint)(n * (1/base) + 2^-10) is exact for n < 2^32, base <= 227
+	// (the product is off by < 2^-20, the fractional part of n / base is a multiple of 1/base <= 1 - 1/227)
+	const double true_inv = 1.0 / (double)base;
 	double f, factor, dn = (double)n;
 	f = factor = tab.inv_base[dim];
 	while(n > 0)
 	{
-		value += (double)sigma[n % base] * factor;
+		const uint32_t q = (uint32_t)((double)n * true_inv + 0.0009765625);
+		value += (double)sigma[n - q * base] * factor;
 		dn *= f;
 		n = (uint32_t)dn;
 		factor *= f;

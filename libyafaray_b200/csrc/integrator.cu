@@ -26,7 +26,6 @@
 
 namespace yg {
 
-#define YG_DN __device__ __noinline__
 
 struct WaveParams
 {
@@ -150,7 +149,7 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, cons
 		const float tmax = dot(nn, ldv(c.far_p) - from) / dot(dir, nn);
 		if(c.aperture != 0)
 		{
-			Halton hu, hv; hu.setBase(3); hv.setBase(5);
+			HaltonB<3> hu; HaltonB<5> hv;
 			hu.setStart((uint32_t)wp.pass_offs + si.sampling_offs + (uint32_t)si.sample);
 			hv.setStart((uint32_t)wp.pass_offs + si.sampling_offs + (uint32_t)si.sample);
 			const float lu = hu.getNext(), lv = hv.getNext();
@@ -290,7 +289,19 @@ __device__ __forceinline__ void pushTask(const ShadeCtx &cx, int slot, V3 from, 
 // MonteCarloIntegrator::doLightEstimation integrator_montecarlo.cc:78-345 (Combined pass only).
 // `W` is the factor the returned colour would be multiplied with before reaching the camera sample; every term is queued
 // as a shadow ray carrying its finished contribution (or added at once when the light/material pair casts no shadow).
-YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, int li, const SurfPt &sp, V3 wo, unsigned loffs, int ray_division, Col W)
+#ifndef YG_DLE_INLINE
+#define YG_DLE_INLINE 1
+#endif
+#ifndef YG_SHADE_MINB
+#define YG_SHADE_MINB 4
+#endif
+#if YG_DLE_INLINE
+#define YG_DLE YG_D
+#else
+#define YG_DLE YG_DN
+#endif
+template<int MT>
+YG_DLE void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, int li, const SurfPt &sp, V3 wo, unsigned loffs, int ray_division, Col W)
 {
 	const SceneDev &sc = *cx.sc;
 	const LightDev &L = sc.lights[li];
@@ -305,7 +316,7 @@ YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, i
 		if(lightIlluminate(L, sp, lcol, ldir, tmax))
 		{
 			const float angle = m.flat ? 1.f : fabsf(dot(sp.n, ldir));
-			const Col surf_col = matEval(sc, m, sp, wo, ldir, BsdfAll);
+			const Col surf_col = matEval<MT>(sc, m, sp, wo, ldir, BsdfAll);
 			const Col c = W * ((surf_col * lcol) * angle);
 			if(cast_shadows) pushShadow(cx, slot, sp.p, sh_tmin, ldir, tmax, c);
 			else accAdd(cx.acc, slot, c);
@@ -317,20 +328,21 @@ YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, i
 	const float inv_ns = 1.f / (float)n;
 	const unsigned offs = (unsigned)n * (unsigned)si.pixel_sample + si.sampling_offs + l_offs;
 	const bool can_intersect = lightCanIntersect(L.type) && !(L.type == YAFGPU_LIGHT_MESH && L.accel < 0);
-	Halton hal_2, hal_3; hal_2.setBase(2); hal_3.setBase(3);
+	Halton2 hal_2; HaltonB<3> hal_3;
 	hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
+	const double hal_3_start = hal_3.value; // the BSDF loop below restarts both sequences at the same element
 	for(int i = 0; i < n; ++i)
 	{
 		const float s1 = hal_2.getNext(), s2 = hal_3.getNext();
 		Col lscol; float lpdf, tmax; V3 ldir;
 		if(!lightIllumSample(sc, L, sp, s1, s2, lscol, lpdf, ldir, tmax)) continue;
 		if(!(lpdf > 1e-6f)) continue;
-		const Col surf_col = matEval(sc, m, sp, wo, ldir, BsdfAll);
+		const Col surf_col = matEval<MT>(sc, m, sp, wo, ldir, BsdfAll);
 		const float angle = m.flat ? 1.f : fabsf(dot(sp.n, ldir));
 		Col c;
 		if(can_intersect)
 		{
-			const float m_pdf = matPdf(sc, m, sp, wo, ldir, BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit);
+			const float m_pdf = matPdf<MT>(sc, m, sp, wo, ldir, BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit);
 			if(m_pdf > 1e-6f)
 			{
 				const float l_2 = lpdf * lpdf, m_2 = m_pdf * m_pdf;
@@ -346,14 +358,14 @@ YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, i
 	}
 	if(can_intersect)
 	{
-		hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
+		hal_2.setStart(offs - 1u); hal_3.value = hal_3_start;
 		const float b_tmin = sc.integ.ray_min_dist_auto ? sc.integ.ray_min_dist * fmaxf(1.f, plen) : sc.integ.ray_min_dist;
 		for(int i = 0; i < n; ++i)
 		{
 			BSample s; s.s1 = hal_2.getNext(); s.s2 = hal_3.getNext(); s.pdf = 0.f; s.sampled = BsdfNone;
 			s.flags = BsdfGlossy | BsdfDiffuse | BsdfDispersive | BsdfReflect | BsdfTransmit;
 			float Wm = 0.f; V3 bdir = mk(0.f);
-			const Col surf_col = matSample(sc, m, sp, wo, bdir, s, Wm);
+			const Col surf_col = matSample<MT>(sc, m, sp, wo, bdir, s, Wm);
 			Col lcol; float light_pdf, t;
 			if(s.pdf > 1e-6f && lightIntersect(sc, L, sp.p, bdir, b_tmin, t, lcol, light_pdf))
 			{
@@ -369,16 +381,33 @@ YG_DN void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, i
 	}
 }
 
-// ---- K5-K8: one thread per task ----------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
-                                               float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter, const int *__restrict__ perm)
+// ---- K5-K8: one thread per task, one kernel per material type -----------------------------------------------------------
+// k_shade<MT> shades the tasks whose hit material is of type MT (MT_MISS: the rays that left the scene).  The counting sort
+// leaves the tasks of one type in two contiguous runs of `perm` (one per task kind); `ends` holds the bucket end offsets the
+// scatter kernel leaves behind, [b0, b1] is the bucket range of the type inside one kind (host-known), so a launch needs no
+// host-side knowledge of the counts.  Compiling the material code in per type keeps each kernel's instruction footprint
+// (and register allocation) to what that BSDF needs: the single generic kernel was 278 k SASS instructions.
+enum { MT_MISS = 100 };
+
+template<int MT>
+__global__ void __launch_bounds__(128, YG_SHADE_MINB) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
+                                               float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter, const int *__restrict__ perm,
+                                               const int *__restrict__ ends, int n_mat, int b0, int b1)
 {
-	const int n = min(ctl->n_tasks[iter], wp.task_cap);
 	ShadeCtx cx; cx.sc = &sc; cx.wp = wp; cx.out = out; cx.sq = sq; cx.acc = acc; cx.ctl = ctl; cx.iter = iter;
 	const IntegratorDev &ig = sc.integ;
+	// runs of this type: kind 0 buckets [b0, b1], kind 1 buckets [n_mat + b0, n_mat + b1]; the miss bucket is 2 * n_mat
+	int start_a, len_a, start_b, len_b;
+	if(MT == MT_MISS) { start_a = ends[2 * n_mat - 1]; len_a = ends[2 * n_mat] - start_a; start_b = 0; len_b = 0; }
+	else
+	{
+		start_a = b0 > 0 ? ends[b0 - 1] : 0; len_a = ends[b1] - start_a;
+		start_b = ends[n_mat + b0 - 1]; len_b = ends[n_mat + b1] - start_b;
+	}
+	const int n = len_a + len_b;
 	for(int ii = blockIdx.x * blockDim.x + threadIdx.x; ii < n; ii += gridDim.x * blockDim.x)
 	{
-		const int i = perm[ii]; // tasks in (kind, material) order: a warp shades one material
+		const int i = perm[ii < len_a ? start_a + ii : start_b + (ii - len_a)];
 		const float4 ro = in.ray_o[i], rd = in.ray_d[i], hh = in.hit[i], wg = in.wgt[i];
 		const uint4 st = in.st[i];
 		const int slot = (int)st.x;
@@ -392,7 +421,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 		if(stKind(packed) == TASK_INTEGRATE)
 		{
 			// ---- PathIntegrator::integrate / DirectLightIntegrator::integrate ----
-			if(tri < 0)
+			if(MT == MT_MISS || tri < 0)
 			{
 				if(sc.bg.type != YAFGPU_BG_NONE) accAdd(acc, slot, W * bgEval(sc.bg, dir));
 				continue;
@@ -400,16 +429,16 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp); // Point3 h = ray.from_ + z * ray.dir_ (scene.cc:908)
 			const MatDev &m = sc.materials[sp.mat];
-			matInitBsdf(m, sp);
+			matInitBsdf<MT>(m, sp);
 			const unsigned bsdfs = m.bsdf_flags;
 			const V3 wo = -dir;
 			const int raylevel = stRaylevel(packed);
 			const int additional_depth = max(stAddDepth(packed), m.additional_depth);
 			const float2 dcv = in.dc[i];
-			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit(sc, m, sp, wo, true));
+			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit<MT>(sc, m, sp, wo, true));
 			if(bsdfs & BsdfDiffuse)
 			{	// estimateAllDirectLight integrator_montecarlo.cc:47-60
-				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation(cx, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
+				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation<MT>(cx, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
 			}
 			if(ig.type == YAFGPU_INT_PATHTRACING)
 			{	// integrator_path_tracer.cc:174-298: first path segment, sampled here; the rest of each path is a TASK_PATH chain
@@ -427,7 +456,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 						if(ray_division > 1) { s_1 = addMod1(s_1, dcv.x); s_2 = addMod1(s_2, dcv.y); }
 						BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = path_flags; s.pdf = 0.f; s.sampled = BsdfNone;
 						float w = 0.f; V3 wi = mk(0.f);
-						Col scol = matSample(sc, m, sp, wo, wi, s, w);
+						Col scol = matSample<MT>(sc, m, sp, wo, wi, s, w);
 						scol = scol * w;
 						if(isBlack(scol) || s.sampled == BsdfNone) continue; // contributes exactly zero in the reference as well
 						pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, (W * scol) * inv_n, scol, offs,
@@ -448,7 +477,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 					int branch = new_division * old_offset;
 					const unsigned offs = (unsigned)gsam * (unsigned)si.pixel_sample + si.sampling_offs;
 					const float d_1 = 1.f / (float)gsam;
-					Halton hal_2, hal_3; hal_2.setBase(2); hal_3.setBase(3);
+					Halton2 hal_2; HaltonB<3> hal_3;
 					hal_2.setStart(offs); hal_3.setStart(offs);
 					for(int ns = 0; ns < gsam; ++ns)
 					{
@@ -464,7 +493,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 							{
 								BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfReflect; s.pdf = 0.f; s.sampled = BsdfNone;
 								float w = 0.f; V3 wi = mk(0.f);
-								const Col mcol = matSample(sc, m, sp, wo, wi, s, w);
+								const Col mcol = matSample<MT>(sc, m, sp, wo, wi, s, w);
 								const Col f = (mcol * w) * d_1;
 								if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2);
 							}
@@ -472,7 +501,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 							{
 								BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfAllGlossy; s.pdf = 0.f; s.sampled = BsdfNone;
 								Col mcol[2] = {mkc(0.f), mkc(0.f)}; float w[2] = {0.f, 0.f}; V3 d2[2] = {mk(0.f), mk(0.f)};
-								mcol[0] = matSample2(sc, m, sp, wo, d2, mcol[1], s, w);
+								mcol[0] = matSample2<MT>(sc, m, sp, wo, d2, mcol[1], s, w);
 								if((s.sampled & BsdfReflect) && !(s.sampled & BsdfDispersive))
 								{
 									const Col f = (mcol[0] * w[0]) * d_1;
@@ -491,7 +520,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 				{
 					bool refl = false, refr = false;
 					V3 d2[2]; Col rcol[2];
-					matSpecular(sc, m, sp, wo, rl, refl, refr, d2, rcol);
+					matSpecular<MT>(sc, m, sp, wo, rl, refl, refr, d2, rcol);
 					const unsigned child = packState(TASK_INTEGRATE, rl, 0, ray_division, 0, additional_depth);
 					if(refl && !isBlack(rcol[0])) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * rcol[0], mkc(1.f), 0u, child, st.w, dcv.x, dcv.y);
 					if(refr && !isBlack(rcol[1]))
@@ -513,7 +542,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 			// ---- one vertex of the path loop, integrator_path_tracer.cc:214-294 ----
 			const int depth = stDepth(packed);
 			const bool caustic = stCaustic(packed);
-			if(tri < 0)
+			if(MT == MT_MISS || tri < 0)
 			{
 				if(depth >= 1 && caustic && sc.bg.type != YAFGPU_BG_NONE && sc.bg.has_ibl && sc.bg.shoots_caustic) accAdd(acc, slot, W * bgEval(sc.bg, dir));
 				continue;
@@ -521,7 +550,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp);
 			const MatDev &m = sc.materials[sp.mat];
-			matInitBsdf(m, sp);
+			matInitBsdf<MT>(m, sp);
 			const unsigned bsdfs = m.bsdf_flags;
 			const V3 pwo = -dir;
 			const float4 th = in.thr[i];
@@ -541,12 +570,12 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 			{	// estimateOneDirectLight integrator_montecarlo.cc:62-76 (a material without diffuse/glossy lobes evaluates to black)
 				const float u = hashRand(wp.seed + 0x51ED270Bu + (unsigned)(wp.pix_base + slot), offs, (unsigned)depth);
 				const int lnum = min((int)(u * (float)sc.n_lights), sc.n_lights - 1);
-				doLightEstimation(cx, slot, si, lnum, sp, pwo, (unsigned)lnum, ray_division, Wp * (float)sc.n_lights);
+				doLightEstimation<MT>(cx, slot, si, lnum, sp, pwo, (unsigned)lnum, ray_division, Wp * (float)sc.n_lights);
 			}
 			if(bsdfs & BsdfEmit)
 			{
-				if(depth == 0) accAdd(acc, slot, Wp * matEmit(sc, m, sp, pwo, false));  // include_lights_ = false (:212)
-				else if(caustic) accAdd(acc, slot, Wp * matEmit(sc, m, sp, pwo, true)); // include_lights_ = caustic (:253,290)
+				if(depth == 0) accAdd(acc, slot, Wp * matEmit<MT>(sc, m, sp, pwo, false));  // include_lights_ = false (:212)
+				else if(caustic) accAdd(acc, slot, Wp * matEmit<MT>(sc, m, sp, pwo, true)); // include_lights_ = caustic (:253,290)
 			}
 			const int nd = depth + 1;
 			if(nd < ig.max_bounces)
@@ -555,7 +584,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ SceneDev 
 				s.s1 = (float)scrHaltonT(*sc.faure, 4 * nd + 3, offs);
 				s.s2 = (float)scrHaltonT(*sc.faure, 4 * nd + 4, offs);
 				float w = 0.f; V3 wi = mk(0.f);
-				Col scol = matSample(sc, m, sp, pwo, wi, s, w);
+				Col scol = matSample<MT>(sc, m, sp, pwo, wi, s, w);
 				scol = scol * w;
 				if(isBlack(scol)) continue;
 				const bool ncaustic = ig.trace_caustics && (s.sampled & (BsdfSpecular | BsdfGlossy | BsdfFilter));
@@ -788,6 +817,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	mark();
 	for(int it = 0; it < max_iters; ++it)
 	{
+		int n_launch = 0;
 		TaskQueue &in = w.q[it & 1], &out = w.q[(it + 1) & 1];
 		SortBins bins; bins.tri_mat = c->d_tri_mat; bins.mat_bucket = c->d_mat_bucket; bins.n_mat = c->n_mat_buckets; bins.key = w.key; bins.hist = w.hist;
 		const int nb = 2 * c->n_mat_buckets + 1;
@@ -797,12 +827,17 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		mark();
 		k_bin_scan<<<1, 1024, 0, st>>>(w.hist, w.hist + YG_MAX_BUCKETS, nb);
 		k_bin_scatter<<<sms * 4, 256, 0, st>>>(&w.ctl->n_tasks[it], wp.task_cap, w.key, w.hist + YG_MAX_BUCKETS, w.perm);
-		k_shade<<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm);
+		const int *ends = w.hist + YG_MAX_BUCKETS; // the scatter kernel advanced every bucket's offset to its end
+#define YG_SHADE(T) if(c->type_b1[T] >= c->type_b0[T]) { k_shade<T><<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, c->type_b0[T], c->type_b1[T]); ++n_launch; }
+		YG_SHADE(YAFGPU_MAT_SHINYDIFFUSE) YG_SHADE(YAFGPU_MAT_GLOSSY) YG_SHADE(YAFGPU_MAT_COATED_GLOSSY) YG_SHADE(YAFGPU_MAT_GLASS) YG_SHADE(YAFGPU_MAT_ROUGH_GLASS)
+		YG_SHADE(YAFGPU_MAT_BLEND) YG_SHADE(YAFGPU_MAT_MIRROR) YG_SHADE(YAFGPU_MAT_NULL) YG_SHADE(YAFGPU_MAT_LIGHT)
+#undef YG_SHADE
+		k_shade<MT_MISS><<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
 		mark();
 		if(count) k_shadow<true><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
 		else k_shadow<false><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, c->d_counters);
 		mark();
-		c->stats.kernel_launches += 5;
+		c->stats.kernel_launches += 4 + n_launch;
 	}
 	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl);
 	c->stats.kernel_launches += 2;

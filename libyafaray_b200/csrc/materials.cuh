@@ -246,9 +246,13 @@ YG_D V3 glassNormal(const SurfPt &sp, V3 wo, bool outside)
 	return (cos_wo_n <= 0) ? sp.n : normalize(sp.n - k * wo);
 }
 
+// MT >= 0: the material type is a compile-time constant (per-material shading kernels, integrator.cu); MT < 0: read it from the record
+template<int MT> YG_D int mtypeOf(const MatDev &m) { return MT >= 0 ? MT : m.type; }
+
+template<int MT>
 YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdfs)
 {
-	switch(m.type)
+	switch(mtypeOf<MT>(m))
 	{
 		case YAFGPU_MAT_SHINYDIFFUSE:
 		{	// material_shiny_diffuse.cc:244-293
@@ -327,9 +331,10 @@ YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdf
 	}
 }
 
+template<int MT>
 YG_D float leafPdf(const MatDev &m, const SurfPt &sp, V3 wo, V3 wi, unsigned bsdfs)
 {
-	switch(m.type)
+	switch(mtypeOf<MT>(m))
 	{
 		case YAFGPU_MAT_SHINYDIFFUSE:
 		{	// material_shiny_diffuse.cc:410-460
@@ -419,9 +424,10 @@ YG_D float leafPdf(const MatDev &m, const SurfPt &sp, V3 wo, V3 wi, unsigned bsd
 }
 
 // Material::sample. Returns the colour; wi, s.pdf, s.sampled and w as the reference leaves them.
+template<int MT>
 YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s, float &w)
 {
-	switch(m.type)
+	switch(mtypeOf<MT>(m))
 	{
 		case YAFGPU_MAT_SHINYDIFFUSE:
 		{	// material_shiny_diffuse.cc:308-408
@@ -791,9 +797,10 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 }
 
 // two-direction sample (only RoughGlass implements it; the base class returns black and touches nothing, material.h:131)
+template<int MT>
 YG_D Col leafSample2(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tcol, BSample &s, float *w)
 {
-	if(m.type != YAFGPU_MAT_ROUGH_GLASS) return mkc(0.f);
+	if(mtypeOf<MT>(m) != YAFGPU_MAT_ROUGH_GLASS) return mkc(0.f);
 	// material_rough_glass.cc:174-291
 	const V3 n = faceForward(sp.ng, sp.n, wo);
 	const bool outside = dot(sp.ng, wo) > 0.f;
@@ -853,9 +860,10 @@ YG_D Col leafSample2(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tco
 	return ret;
 }
 
+template<int MT>
 YG_D void leafSpecular(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, bool &refl, bool &refr, V3 *dir, Col *col)
 {
-	switch(m.type)
+	switch(mtypeOf<MT>(m))
 	{
 		case YAFGPU_MAT_SHINYDIFFUSE:
 		{	// material_shiny_diffuse.cc:474-528
@@ -948,10 +956,11 @@ YG_D void leafSpecular(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, b
 	}
 }
 
+template<int MT>
 YG_D Col leafEmit(const MatDev &m, const SurfPt &sp, V3 wo, bool include_lights)
 {
-	if(m.type == YAFGPU_MAT_SHINYDIFFUSE) return ldc(m.emit_col); // :295-306
-	if(m.type == YAFGPU_MAT_LIGHT)
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_SHINYDIFFUSE) return ldc(m.emit_col); // :295-306
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_LIGHT)
 	{	// material_simple.cc:50-58
 		if(!include_lights) return mkc(0.f);
 		if(m.double_sided) return ldc(m.simple_col);
@@ -961,9 +970,10 @@ YG_D Col leafEmit(const MatDev &m, const SurfPt &sp, V3 wo, bool include_lights)
 }
 
 // Material::getTransparency (only called when isTransparent())
+template<int MT>
 YG_D Col leafTransparency(const MatDev &m, const SurfPt &sp, V3 wo)
 {
-	if(m.type == YAFGPU_MAT_SHINYDIFFUSE)
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_SHINYDIFFUSE)
 	{	// :530-567
 		if(!m.is_transparent) return mkc(0.f);
 		float accum = 1.f;
@@ -974,7 +984,7 @@ YG_D Col leafTransparency(const MatDev &m, const SurfPt &sp, V3 wo)
 		const float tf = m.transmit_filter_strength;
 		return accum * (tf * ldc(m.diffuse_col) + mkc(1.f - tf));
 	}
-	if(m.type == YAFGPU_MAT_GLASS || m.type == YAFGPU_MAT_ROUGH_GLASS)
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_GLASS || mtypeOf<MT>(m) == YAFGPU_MAT_ROUGH_GLASS)
 	{	// material_glass.cc:218-229, material_rough_glass.cc:293-303
 		const V3 n = faceForward(sp.ng, sp.n, wo);
 		float kr, kt;
@@ -987,32 +997,47 @@ YG_D Col leafTransparency(const MatDev &m, const SurfPt &sp, V3 wo)
 // BlendMaterial::initBsdf replaces the surface point by blendSurfacePoints__(sp, sp, ival) (material_blend.cc:77-104,
 // surface.cc:137-151): lerp__(a, a, alpha) = a * alpha + a * (1 - alpha) in float, which is not exactly `a`.
 YG_D V3 blendLerp(V3 a, float al, float ial) { return a * al + a * ial; }
+template<int MT>
 YG_D void matInitBsdf(const MatDev &m, SurfPt &sp)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return;
+	if(mtypeOf<MT>(m) != YAFGPU_MAT_BLEND) return;
 	const float ival = fminf(1.f, fmaxf(0.f, 1.f - m.blend_val));
 	const float al = ival, ial = (float)(1.0 - (double)ival);
 	sp.n = blendLerp(sp.n, al, ial); sp.nu = blendLerp(sp.nu, al, ial); sp.nv = blendLerp(sp.nv, al, ial);
 }
 
 // ---- top level: BlendMaterial dispatch (children are leaf materials; nesting is refused at upload) ----------------------
+// The children of a blend are reached through ONE out-of-line copy of each generic leaf function (type read from the record),
+// so the blend kernel's code stays small; every other kernel inlines exactly its own material's code.
+YG_DN Col leafEvalG(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdfs) { return leafEval<-1>(m, sp, wo, wl, bsdfs); }
+YG_DN float leafPdfG(const MatDev &m, const SurfPt &sp, V3 wo, V3 wi, unsigned bsdfs) { return leafPdf<-1>(m, sp, wo, wi, bsdfs); }
+YG_DN Col leafSampleG(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s, float &w) { return leafSample<-1>(m, sp, wo, wi, s, w); }
+YG_DN Col leafSample2G(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tcol, BSample &s, float *w) { return leafSample2<-1>(m, sp, wo, dir, tcol, s, w); }
+YG_DN void leafSpecularG(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, bool &refl, bool &refr, V3 *dir, Col *col) { leafSpecular<-1>(m, sp, wo, raylevel, refl, refr, dir, col); }
+YG_DN Col leafEmitG(const MatDev &m, const SurfPt &sp, V3 wo, bool include_lights) { return leafEmit<-1>(m, sp, wo, include_lights); }
+YG_DN Col leafTransparencyG(const MatDev &m, const SurfPt &sp, V3 wo) { return leafTransparency<-1>(m, sp, wo); }
 
+#define YG_NOT_BLEND(MT, m) ((MT) >= 0 ? (MT) != YAFGPU_MAT_BLEND : (m).type != YAFGPU_MAT_BLEND)
+
+template<int MT>
 YG_D Col matEval(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdfs)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return leafEval(m, sp, wo, wl, bsdfs);
+	if(YG_NOT_BLEND(MT, m)) return leafEval<MT>(m, sp, wo, wl, bsdfs);
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
-	const Col c1 = leafEval(sc.materials[m.mat1], sp, wo, wl, bsdfs), c2 = leafEval(sc.materials[m.mat2], sp, wo, wl, bsdfs);
+	const Col c1 = leafEvalG(sc.materials[m.mat1], sp, wo, wl, bsdfs), c2 = leafEvalG(sc.materials[m.mat2], sp, wo, wl, bsdfs);
 	return c1 * ival + c2 * val;
 }
+template<int MT>
 YG_D float matPdf(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, V3 wi, unsigned bsdfs)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return leafPdf(m, sp, wo, wi, bsdfs);
+	if(YG_NOT_BLEND(MT, m)) return leafPdf<MT>(m, sp, wo, wi, bsdfs);
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
-	return leafPdf(sc.materials[m.mat1], sp, wo, wi, bsdfs) * ival + leafPdf(sc.materials[m.mat2], sp, wo, wi, bsdfs) * val;
+	return leafPdfG(sc.materials[m.mat1], sp, wo, wi, bsdfs) * ival + leafPdfG(sc.materials[m.mat2], sp, wo, wi, bsdfs) * val;
 }
+template<int MT>
 YG_D Col matSample(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s, float &w)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return leafSample(m, sp, wo, wi, s, w);
+	if(YG_NOT_BLEND(MT, m)) return leafSample<MT>(m, sp, wo, wi, s, w);
 	// material_blend.cc:131-214
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
 	const MatDev &m1 = sc.materials[m.mat1], &m2 = sc.materials[m.mat2];
@@ -1022,8 +1047,8 @@ YG_D Col matSample(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo,
 	V3 wi_1 = mk(0.f), wi_2 = mk(0.f);
 	float w_1 = 0.f, w_2 = 0.f;
 	s2.pdf = s1.pdf = s.pdf = 0.f;
-	if(s.flags & m1.bsdf_flags) { col1 = leafSample(m1, sp, wo, wi_1, s1, w_1); s1d = true; }
-	if(s.flags & m2.bsdf_flags) { col2 = leafSample(m2, sp, wo, wi_2, s2, w_2); s2d = true; }
+	if(s.flags & m1.bsdf_flags) { col1 = leafSampleG(m1, sp, wo, wi_1, s1, w_1); s1d = true; }
+	if(s.flags & m2.bsdf_flags) { col2 = leafSampleG(m2, sp, wo, wi_2, s2, w_2); s2d = true; }
 	if(s1d && s2d)
 	{
 		wi = normalize(wi_2 + wi_1);
@@ -1036,28 +1061,30 @@ YG_D Col matSample(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo,
 	else if(s2d) { wi = wi_2; s.pdf = s2.pdf; s.sampled = s2.sampled; col1 = col2; w = w_2; }
 	return col1;
 }
+template<int MT>
 YG_D Col matSample2(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tcol, BSample &s, float *w)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return leafSample2(m, sp, wo, dir, tcol, s, w);
+	if(YG_NOT_BLEND(MT, m)) return leafSample2<MT>(m, sp, wo, dir, tcol, s, w);
 	// material_blend.cc:216-237
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
-	if(val <= 0.f) return leafSample2(sc.materials[m.mat1], sp, wo, dir, tcol, s, w);
-	if(val >= 1.f) return leafSample2(sc.materials[m.mat2], sp, wo, dir, tcol, s, w);
-	const Col a = leafSample2(sc.materials[m.mat1], sp, wo, dir, tcol, s, w);
-	const Col b = leafSample2(sc.materials[m.mat2], sp, wo, dir, tcol, s, w);
+	if(val <= 0.f) return leafSample2G(sc.materials[m.mat1], sp, wo, dir, tcol, s, w);
+	if(val >= 1.f) return leafSample2G(sc.materials[m.mat2], sp, wo, dir, tcol, s, w);
+	const Col a = leafSample2G(sc.materials[m.mat1], sp, wo, dir, tcol, s, w);
+	const Col b = leafSample2G(sc.materials[m.mat2], sp, wo, dir, tcol, s, w);
 	return a * ival + b * val;
 }
+template<int MT>
 YG_D void matSpecular(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, bool &refl, bool &refr, V3 *dir, Col *col)
 {
-	if(m.type != YAFGPU_MAT_BLEND) { leafSpecular(m, sp, wo, raylevel, refl, refr, dir, col); return; }
+	if(YG_NOT_BLEND(MT, m)) { leafSpecular<MT>(m, sp, wo, raylevel, refl, refr, dir, col); return; }
 	// material_blend.cc:259-325
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
 	refl = false; refr = false;
 	bool r1 = false, t1 = false;
 	V3 d1[2] = {mk(0.f), mk(0.f)};
 	Col c1[2] = {mkc(0.f), mkc(0.f)};
-	leafSpecular(sc.materials[m.mat1], sp, wo, raylevel, r1, t1, d1, c1);
-	leafSpecular(sc.materials[m.mat2], sp, wo, raylevel, refl, refr, dir, col);
+	leafSpecularG(sc.materials[m.mat1], sp, wo, raylevel, r1, t1, d1, c1);
+	leafSpecularG(sc.materials[m.mat2], sp, wo, raylevel, refl, refr, dir, col);
 	if(refl && r1) { col[0] = c1[0] * ival + col[0] * val; dir[0] = normalize(dir[0] + d1[0]); }
 	else if(r1) { col[0] = c1[0] * ival; dir[0] = d1[0]; }
 	else col[0] = col[0] * val;
@@ -1067,17 +1094,19 @@ YG_D void matSpecular(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 
 	refr = refr || t1;
 	refl = refl || r1;
 }
+template<int MT>
 YG_D Col matEmit(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, bool include_lights)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return leafEmit(m, sp, wo, include_lights);
+	if(YG_NOT_BLEND(MT, m)) return leafEmit<MT>(m, sp, wo, include_lights);
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
-	return leafEmit(sc.materials[m.mat1], sp, wo, include_lights) * ival + leafEmit(sc.materials[m.mat2], sp, wo, include_lights) * val;
+	return leafEmitG(sc.materials[m.mat1], sp, wo, include_lights) * ival + leafEmitG(sc.materials[m.mat2], sp, wo, include_lights) * val;
 }
+// used by the shadow kernel on whatever transparent material the segment crosses: generic
 YG_D Col matTransparency(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo)
 {
-	if(m.type != YAFGPU_MAT_BLEND) return leafTransparency(m, sp, wo);
+	if(m.type != YAFGPU_MAT_BLEND) return leafTransparency<-1>(m, sp, wo);
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
-	return leafTransparency(sc.materials[m.mat1], sp, wo) * ival + leafTransparency(sc.materials[m.mat2], sp, wo) * val;
+	return leafTransparencyG(sc.materials[m.mat1], sp, wo) * ival + leafTransparencyG(sc.materials[m.mat2], sp, wo) * val;
 }
 
 } // namespace yg

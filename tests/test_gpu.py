@@ -98,8 +98,12 @@ def test_render_matches_reference_film(ctx, name):
     d = np.abs(gi[..., :3] - ri[..., :3]).max(axis=2)
     # a decision that sits within an ulp of its threshold (component pick, total reflection, geometric side test) may fall
     # the other way on either side: such isolated pixels are tolerated, everything else must agree to float rounding
-    assert (d > tol).mean() <= 2e-3, (int((d > tol).sum()), float(d.max()))
-    assert ou.rel_rmse(gi, ri) <= 1e-3
+    flip = d > tol
+    assert flip.mean() <= 2e-3, (int(flip.sum()), float(d.max()))
+    keep = ~flip
+    assert ou.rel_rmse(gi[keep][None], ri[keep][None]) <= 1e-5
+    # whole image, flipped pixels included: one flipped sample of a 4-spp fixture moves its pixel by up to 25 %
+    assert ou.rel_rmse(gi, ri) <= (1e-3 if not flip.any() else 5e-3)
     assert np.abs(gi[..., 3] - ri[..., 3]).max() <= 1e-5
 
 
