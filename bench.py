@@ -261,21 +261,48 @@ def gpu_arm(args, rank, world, local_rank):
         s2 = side_run(capi.FLAG_TIME_STAGES)        # kernel durations (CUDA events around every launch, no counting code)
         s3 = side_run(capi.FLAG_COUNT_TRAVERSAL)    # nodes visited / triangles tested on the same steps
         s2["nodes_visited"], s2["tris_tested"] = s3["nodes_visited"], s3["tris_tested"]
+        line["wave0_tasks"], line["wave0_shadow"] = s2["last_wave_tasks"], s2["last_wave_shadow"]
         peak, how = hbm_peak()
         n_trace, n_shadow = s2["rays_in_timed_trace"], s2["rays_in_timed_shadow"]
+        ms_tr, ms_sh, ms_shd = s2["ms_trace"], s2["ms_shadow"], s2["ms_shade"]
+        # Algorithmic bytes.  Traversal: 48 B ray+hit, 64 B per node visited, 48 B per triangle
+        # tested (counters cover closest-hit AND shadow rays).  Shading: per task 108 B queue record in (ray_o, ray_d, hit, wgt,
+        # thr|dc, st, perm), 104 B per task spawned, 48 B per shadow ray queued, 136 B of triangle/vertex/normal data per hit
+        # when the scene does not fit the caches (36 triangles do: counted 0 here).
         node_b, tri_b = 64, 48
-        # traversal counters cover closest-hit AND shadow rays; split by ray count for the per-kernel figure
-        alg_total = 48.0 * (n_trace + n_shadow) + node_b * s2["nodes_visited"] + tri_b * s2["tris_tested"]
-        ms_tr, ms_sh = s2["ms_trace"], s2["ms_shadow"]
-        ach = alg_total / ((ms_tr + ms_sh) / 1e3) / 1e9 if ms_tr + ms_sh > 0 else 0.0
-        line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                            "peak_source": how, "kernel": "k_trace + k_shadow (BVH traversal)",
-                            "algorithmic_bytes_per_ray": alg_total / max(1, n_trace + n_shadow),
+        alg_trav = 48.0 * (n_trace + n_shadow) + node_b * s2["nodes_visited"] + tri_b * s2["tris_tested"]
+        spawned = max(0, n_trace - s2["camera_samples"])
+        geom_b = 136.0 if desc.geometry.n_tris > 100000 else 0.0
+        alg_shade = (108.0 + geom_b) * n_trace + 104.0 * spawned + 48.0 * n_shadow
+        kern = {
+            "k_shade": {"ms": ms_shd, "launches": s2["launches_shade"], "alg_bytes": alg_shade, "units": n_trace, "unit": "task"},
+            "k_trace+k_shadow": {"ms": ms_tr + ms_sh, "launches": s2["launches_trace"] + s2["launches_shadow"], "alg_bytes": alg_trav,
+                                 "units": n_trace + n_shadow, "unit": "ray"},
+        }
+        dom = max(kern, key=lambda k: kern[k]["ms"])
+        for k, v in kern.items():
+            v["achieved_gbs"] = v["alg_bytes"] / (v["ms"] / 1e3) / 1e9 if v["ms"] > 0 else 0.0
+            v["frac"] = v["achieved_gbs"] / peak
+            v["avg_launch_ms"] = v["ms"] / max(1, v["launches"])
+            v["alg_bytes_per_unit"] = v["alg_bytes"] / max(1, v["units"])
+            v["share_of_step"] = v["ms"] / max(1e-9, s2["ms_total"])
+        traffic = None
+        try:   # dram bytes per unit of the dominant kernel from the committed ncu --set full capture (profiles/)
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as fh:
+                t = json.load(fh).get(dom)
+            if t:
+                traffic = t["dram_bytes_per_unit"] * kern[dom]["units"] / max(1, kern[dom]["launches"])
+        except Exception:
+            pass
+        d = kern[dom]
+        line["roofline"] = {"bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": d["frac"], "traffic": traffic,
+                            "peak_source": how, "kernel": dom, "algorithmic_bytes_per_launch": d["alg_bytes"] / max(1, d["launches"]),
+                            "avg_launch_ms": d["avg_launch_ms"], "kernels": kern,
                             "nodes_per_ray": s2["nodes_visited"] / max(1, n_trace + n_shadow), "tris_per_ray": s2["tris_tested"] / max(1, n_trace + n_shadow),
-                            "avg_launch_ms": {"k_trace": ms_tr / max(1, s2["launches_trace"]), "k_shadow": ms_sh / max(1, s2["launches_shadow"]),
-                                              "k_shade": s2["ms_shade"] / max(1, s2["launches_shade"])},
-                            "stage_ms": {"trace": ms_tr, "shadow": ms_sh, "shade": s2["ms_shade"], "total": s2["ms_total"]},
-                            "note": "durations from a TIME_STAGES context, node/triangle counts from a COUNT_TRAVERSAL context, both on the same steps; the 36-triangle Cornell scene lives in L1/L2, so HBM traffic is queue traffic"}
+                            "stage_ms": {"trace": ms_tr, "shadow": ms_sh, "shade": ms_shd, "total": s2["ms_total"]},
+                            "note": "durations: CUDA events around every launch in a TIME_STAGES context on the context's own stream; node/triangle "
+                                    "counts: a COUNT_TRAVERSAL context on the same steps; k_shade = the per-material shading kernels of one iteration "
+                                    "(incl. the 2 sort kernels); Cornell's 36 triangles live in L1, so its traversal figure is cache bandwidth, not HBM"}
         # ---- CPU baseline (bounded sample) ----
         if not args.no_cpu:
             cores = os.cpu_count() or 1

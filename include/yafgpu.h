@@ -373,6 +373,8 @@ typedef struct yafgpu_stats
 	double ms_shadow;
 	uint64_t launches_trace, launches_shadow, launches_shade;
 	uint64_t rays_in_timed_trace, rays_in_timed_shadow;
+	/* queue lengths of the most recent wave, per wavefront iteration (first 16): tasks traced+shaded, shadow rays traced */
+	uint32_t last_wave_tasks[16], last_wave_shadow[16];
 } yafgpu_stats;
 
 enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2 };

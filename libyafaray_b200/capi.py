@@ -134,7 +134,7 @@ class Stats(C.Structure):
                 ("ms_build", C.c_double), ("ms_trace", C.c_double), ("ms_shade", C.c_double), ("ms_film", C.c_double),
                 ("ms_total", C.c_double), ("waves", u64), ("wave_retries", u64), ("ms_shadow", C.c_double),
                 ("launches_trace", u64), ("launches_shadow", u64), ("launches_shade", u64), ("rays_in_timed_trace", u64),
-                ("rays_in_timed_shadow", u64)]
+                ("rays_in_timed_shadow", u64), ("last_wave_tasks", C.c_uint32 * 16), ("last_wave_shadow", C.c_uint32 * 16)]
 
 
 # every entry point include/yafgpu.h declares: name -> (restype, argtypes)

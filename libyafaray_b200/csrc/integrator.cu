@@ -857,6 +857,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		}
 	}
 	if(overflow) { c->stats.wave_retries++; return YAFGPU_OK; }
+	for(int it = 0; it < 16; ++it) { c->stats.last_wave_tasks[it] = (uint32_t)w.h_ctl->n_tasks[it]; c->stats.last_wave_shadow[it] = (uint32_t)w.h_ctl->n_shadow[it]; }
 	c->stats.rays_camera += (uint64_t)wp.n_slots;
 	c->stats.camera_samples += (uint64_t)wp.n_slots;
 	for(int it = 1; it <= max_iters; ++it) c->stats.rays_extension += (uint64_t)w.h_ctl->n_tasks[it];

@@ -100,7 +100,7 @@ class Context:
     def stats(self):
         s = capi.Stats()
         _check(self.h, capi.lib.yafgpu_get_stats(self.h, C.byref(s)))
-        return {k: getattr(s, k) for k, _ in capi.Stats._fields_}
+        return {k: (list(getattr(s, k)) if hasattr(getattr(s, k), "__len__") else getattr(s, k)) for k, _ in capi.Stats._fields_}
 
     def reset_stats(self):
         _check(self.h, capi.lib.yafgpu_reset_stats(self.h))
