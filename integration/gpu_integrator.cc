@@ -1,0 +1,600 @@
+// GpuIntegrator — the reference-side adaptor of the yafgpu C ABI (include/yafgpu.h).
+//
+// This translation unit is compiled AGAINST THE REFERENCE'S HEADERS and linked into a libYafaRay front end in place of
+// nothing: no reference source file is edited.  It plugs the GPU path in behind the reference's own integrator surface
+//
+//     class SurfaceIntegrator : Integrator        include/integrator/integrator.h:48-85
+//         virtual bool preprocess();               called by Scene::update()            src/common/scene.cc:886
+//         virtual bool render(int, ImageFilm *);   called by Scene::render()            src/common/scene.cc:1060
+//         virtual void cleanup();                                                        src/common/scene.cc:1062
+//
+// so that scenes keep arriving through the unchanged XML loader / Interface API, and the reference keeps doing everything
+// outside the hot path (parsing, smoothing, film flush, colour space, image output).
+//
+// Substitution happens at link time with GNU ld's --wrap (flags in oracle/Makefile, explained in INTEGRATION.md):
+//   RenderEnvironment::create{Material,Light,Camera,Background,Integrator}, setupScene        src/common/environment.cc
+// are wrapped to (a) keep a copy of the ParamMap each object was created from — the reference's factories consume the
+// parameters and keep only constructor results — and (b) hand back a GpuIntegrator for `type` "pathtracing" and
+// "directlighting" (what Integrator::factory would dispatch, src/integrator/integrator.cc:35-56).  A maintainer with
+// commit access would instead add the two type strings to that factory and keep the ParamMaps in the environment tables.
+//
+// YAFGPU_DISABLE=1 in the environment leaves the reference's CPU integrators in place.  There is no CPU fallback: when the
+// GPU path is selected and anything fails (no device, unsupported feature), preprocess()/render() log Y_ERROR and return false.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iomanip>
+#include <iostream>
+#include <limits>
+#include <list>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <set>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+
+// read-only access to state the reference keeps private (mesh arrays, film buffers, environment tables); layouts unchanged
+#define private public
+#define protected public
+#include "yafaray_config.h"
+#include "common/environment.h"
+#include "common/scene.h"
+#include "common/imagefilm.h"
+#include "common/param.h"
+#include "common/session.h"
+#include "common/logging.h"
+#include "common/timer.h"
+#include "common/triangle.h"
+#include "common/monitor.h"
+#include "object_geom/object_geom_mesh.h"
+#include "material/material.h"
+#include "light/light.h"
+#include "camera/camera.h"
+#include "background/background.h"
+#include "integrator/integrator.h"
+#undef private
+#undef protected
+
+#include "yafgpu.h"
+
+BEGIN_YAFARAY
+
+namespace {
+
+// ---- what the wrapped factories remember ----------------------------------------------------------------------------
+struct Recorded
+{
+	std::map<const void *, ParamMap> params;     // object -> the ParamMap it was created from
+	std::map<const void *, std::string> names;
+	std::vector<const Material *> materials;     // creation order = material index on the device
+	ParamMap film;                               // the <render> block as setupScene saw it
+	ParamMap integrator;
+	std::string background_name;
+};
+Recorded &rec() { static Recorded r; return r; }
+
+template <class T> T par(const ParamMap &p, const char *key, T def) { p.getParam(key, def); return def; }
+void par3(const ParamMap &p, const char *key, float *out, float d0, float d1, float d2)
+{
+	Point3 v(d0, d1, d2);
+	p.getParam(key, v);
+	out[0] = v.x_; out[1] = v.y_; out[2] = v.z_;
+}
+void parCol(const ParamMap &p, const char *key, float *out, float d)
+{
+	Rgb c(d);
+	p.getParam(key, c);
+	out[0] = c.r_; out[1] = c.g_; out[2] = c.b_;
+}
+bool hasShaderNodes(const ParamMap &p)
+{
+	for(auto it = p.begin(); it != p.end(); ++it)
+	{
+		const std::string &k = it->first;
+		if(k.size() > 7 && k.compare(k.size() - 7, 7, "_shader") == 0) return true;
+	}
+	return false;
+}
+
+// ---- ParamMap -> C ABI records (same keys and in-code defaults as the reference factories) ------------------------------
+bool materialRecord(const Material *m, yafgpu_material &out, std::string &err)
+{
+	memset(&out, 0, sizeof(out));
+	auto it = rec().params.find(m);
+	if(it == rec().params.end()) { err = "material was not created through RenderEnvironment::createMaterial"; return false; }
+	const ParamMap &p = it->second;
+	const std::string name = rec().names[m];
+	if(hasShaderNodes(p)) { err = "material '" + name + "': shader nodes are not implemented on the device"; return false; }
+	const std::string type = par<std::string>(p, "type", "");
+	const std::string vis = par<std::string>(p, "visibility", "normal");     // material factories: e.g. material_shiny_diffuse.cc:626-649
+	out.visibility = vis == "no_shadows" ? YAFGPU_VIS_NO_SHADOWS : vis == "shadow_only" ? YAFGPU_VIS_SHADOW_ONLY : vis == "invisible" ? YAFGPU_VIS_INVISIBLE : YAFGPU_VIS_NORMAL;
+	out.receive_shadows = par<bool>(p, "receive_shadows", true);
+	out.flat_material = par<bool>(p, "flat_material", false);
+	out.additional_depth = par<int>(p, "additionaldepth", 0);
+	out.transparent_bias_factor = par<float>(p, "transparentbias_factor", 0.f);
+	out.transparent_bias_multiply_raydepth = par<bool>(p, "transparentbias_multiply_raydepth", false);
+	out.sampling_factor = par<float>(p, "samplingfactor", 1.f);
+	out.mat_pass_index = par<int>(p, "mat_pass_index", 0);
+	auto indexOf = [&](const std::string &child) -> int
+	{
+		for(size_t i = 0; i < rec().materials.size(); ++i) if(rec().names[rec().materials[i]] == child) return (int)i;
+		return -1;
+	};
+	if(type == "shinydiffusemat")
+	{	// material_shiny_diffuse.cc:599-688
+		out.type = YAFGPU_MAT_SHINYDIFFUSE;
+		yafgpu_mat_shinydiffuse &s = out.u.shinydiffuse;
+		parCol(p, "color", s.color, 1.f); parCol(p, "mirror_color", s.mirror_color, 1.f);
+		s.diffuse_reflect = par<float>(p, "diffuse_reflect", 1.f); s.specular_reflect = par<float>(p, "specular_reflect", 0.f);
+		s.transparency = par<float>(p, "transparency", 0.f); s.translucency = par<float>(p, "translucency", 0.f);
+		s.emit = par<float>(p, "emit", 0.f); s.ior = par<float>(p, "IOR", 1.33f);
+		s.fresnel_effect = par<bool>(p, "fresnel_effect", false); s.transmit_filter = par<float>(p, "transmit_filter", 1.f);
+		s.oren_nayar = par<std::string>(p, "diffuse_brdf", "") == "oren_nayar"; s.sigma = par<float>(p, "sigma", 0.1f);
+	}
+	else if(type == "glass" || type == "rough_glass")
+	{	// material_glass.cc:311-379, material_rough_glass.cc:322-401
+		out.type = type == "glass" ? YAFGPU_MAT_GLASS : YAFGPU_MAT_ROUGH_GLASS;
+		yafgpu_mat_glass &s = out.u.glass;
+		s.ior = par<float>(p, "IOR", 1.4f);
+		parCol(p, "filter_color", s.filter_color, 1.f); parCol(p, "mirror_color", s.mirror_color, 1.f);
+		s.transmit_filter = par<float>(p, "transmit_filter", 0.f); s.dispersion_power = par<float>(p, "dispersion_power", 0.f);
+		s.fake_shadows = par<bool>(p, "fake_shadows", false); s.alpha = par<float>(p, "alpha", 0.5f);
+		Rgb absorb(1.f);
+		const bool has = p.getParam("absorption", absorb);
+		s.has_absorption = has && (absorb.r_ < 1.f || absorb.g_ < 1.f || absorb.b_ < 1.f);
+		s.absorption[0] = absorb.r_; s.absorption[1] = absorb.g_; s.absorption[2] = absorb.b_;
+		s.absorption_dist = par<float>(p, "absorption_dist", 1.f);
+	}
+	else if(type == "glossy" || type == "coated_glossy")
+	{	// material_glossy.cc:407-480, material_coated_glossy.cc:465-545
+		out.type = type == "glossy" ? YAFGPU_MAT_GLOSSY : YAFGPU_MAT_COATED_GLOSSY;
+		yafgpu_mat_glossy &s = out.u.glossy;
+		parCol(p, "color", s.color, 1.f); parCol(p, "diffuse_color", s.diffuse_color, 1.f); parCol(p, "mirror_color", s.mirror_color, 1.f);
+		s.diffuse_reflect = par<float>(p, "diffuse_reflect", 0.f); s.glossy_reflect = par<float>(p, "glossy_reflect", 1.f);
+		s.specular_reflect = par<float>(p, "specular_reflect", 1.f);
+		s.exponent = par<float>(p, "exponent", 50.f); s.exp_u = par<float>(p, "exp_u", 50.f); s.exp_v = par<float>(p, "exp_v", 50.f);
+		s.ior = par<float>(p, "IOR", 1.4f);
+		s.as_diffuse = par<bool>(p, "as_diffuse", true); s.anisotropic = par<bool>(p, "anisotropic", false);
+		s.oren_nayar = par<std::string>(p, "diffuse_brdf", "") == "Oren-Nayar"; s.sigma = par<float>(p, "sigma", 0.1f);
+	}
+	else if(type == "blend_mat")
+	{	// material_blend.cc:464-518
+		out.type = YAFGPU_MAT_BLEND;
+		out.u.blend.material1 = indexOf(par<std::string>(p, "material1", ""));
+		out.u.blend.material2 = indexOf(par<std::string>(p, "material2", ""));
+		out.u.blend.blend_value = par<float>(p, "blend_value", 0.5f);
+	}
+	else if(type == "light_mat")
+	{	// material_simple.cc:63-73
+		out.type = YAFGPU_MAT_LIGHT;
+		parCol(p, "color", out.u.simple.color, 1.f);
+		out.u.simple.strength = par<float>(p, "power", 1.f);
+		out.u.simple.double_sided = par<bool>(p, "double_sided", false);
+	}
+	else if(type == "null") out.type = YAFGPU_MAT_NULL;
+	else { err = "material '" + name + "': type '" + type + "' is not implemented on the device"; return false; }
+	return true;
+}
+
+bool lightRecord(const Light *l, const std::map<int, int> &obj_index_of_id, yafgpu_light &out, std::string &err)
+{
+	memset(&out, 0, sizeof(out));
+	auto it = rec().params.find(l);
+	if(it == rec().params.end()) { err = "light was not created through RenderEnvironment::createLight"; return false; }
+	const ParamMap &p = it->second;
+	const std::string type = par<std::string>(p, "type", "");
+	out.light_enabled = par<bool>(p, "light_enabled", true); out.cast_shadows = par<bool>(p, "cast_shadows", true);
+	out.photon_only = par<bool>(p, "photon_only", false);
+	out.shoot_caustic = par<bool>(p, "with_caustic", true); out.shoot_diffuse = par<bool>(p, "with_diffuse", true);
+	parCol(p, "color", out.color, 1.f);
+	out.power = par<float>(p, "power", 1.f);
+	out.samples = par<int>(p, "samples", 4);
+	out.object = -1;
+	auto objectOf = [&]() -> int
+	{
+		const int id = par<int>(p, "object", 0);
+		auto f = obj_index_of_id.find(id);
+		return (id != 0 && f != obj_index_of_id.end()) ? f->second : -1;
+	};
+	if(type == "pointlight") { out.type = YAFGPU_LIGHT_POINT; par3(p, "from", out.from, 0.f, 0.f, 0.f); }               // light_point.cc:101-133
+	else if(type == "sunlight") { out.type = YAFGPU_LIGHT_SUN; par3(p, "direction", out.from, 0.f, 0.f, 1.f); out.angle = par<float>(p, "angle", 0.27f); } // light_sun.cc:95-125
+	else if(type == "arealight")
+	{	// light_area.cc:174-213
+		out.type = YAFGPU_LIGHT_AREA;
+		par3(p, "corner", out.from, 0.f, 0.f, 0.f); par3(p, "point1", out.point1, 0.f, 0.f, 0.f); par3(p, "point2", out.point2, 0.f, 0.f, 0.f);
+		out.object = objectOf();
+	}
+	else if(type == "meshlight")
+	{	// light_meshlight.cc:228-263
+		out.type = YAFGPU_LIGHT_MESH;
+		out.object = objectOf();
+		out.double_sided = par<bool>(p, "double_sided", false);
+	}
+	else if(type == "bglight")
+	{	// light_background.cc:251-283 (created by a background with ibl=true, background_constant.cc:69-83)
+		out.type = YAFGPU_LIGHT_BACKGROUND;
+		out.samples = par<int>(p, "samples", 16);
+		out.abs_intersect = par<bool>(p, "abs_intersect", false);
+		out.clamp_intersect = 0.f;
+	}
+	else { err = "light type '" + type + "' is not implemented on the device"; return false; }
+	return true;
+}
+
+} // namespace
+
+// ---- the integrator ---------------------------------------------------------------------------------------------------
+class GpuIntegrator final : public SurfaceIntegrator
+{
+	public:
+		explicit GpuIntegrator(const ParamMap &params) : params_(params)
+		{
+			type_ = Surface;
+			integrator_name_ = "GPU " + par<std::string>(params, "type", "");
+			integrator_short_name_ = "GPU";
+		}
+		~GpuIntegrator() override { if(ctx_) yafgpu_destroy(ctx_); }
+		bool preprocess() override;
+		bool render(int num_view, ImageFilm *image_film) override;
+		void cleanup() override {}
+		Rgba integrate(RenderState &, DiffRay &, ColorPasses &, int) const override { return Rgba(0.f); } // never called: render() is overridden
+
+	private:
+		bool fail(const std::string &what)
+		{
+			Y_ERROR << integrator_name_ << ": " << what << (ctx_ ? std::string(" — ") + yafgpu_last_error(ctx_) : std::string()) << YENDL;
+			return false;
+		}
+		bool fillIntegrator(yafgpu_integrator_desc &it, std::string &err) const;
+		bool depositFilm(ImageFilm *film);
+		ParamMap params_;
+		yafgpu_ctx *ctx_ = nullptr;
+		std::vector<float> host_film_;
+};
+
+bool GpuIntegrator::fillIntegrator(yafgpu_integrator_desc &it, std::string &err) const
+{
+	memset(&it, 0, sizeof(it));
+	const ParamMap &p = params_;
+	const std::string type = par<std::string>(p, "type", "");
+	it.raydepth = par<int>(p, "raydepth", 5); it.shadow_depth = par<int>(p, "shadowDepth", 5);
+	it.transp_shad = par<bool>(p, "transpShad", false);
+	it.bg_transp = par<bool>(p, "bg_transp", false); it.bg_transp_refract = par<bool>(p, "bg_transp_refract", false);
+	it.do_ao = par<bool>(p, "do_AO", false); it.ao_samples = par<int>(p, "AO_samples", 32); it.ao_distance = par<float>(p, "AO_distance", 1.f);
+	parCol(p, "AO_color", it.ao_color, 1.f);
+	if(type == "pathtracing")
+	{	// integrator_path_tracer.cc:349-423
+		it.type = YAFGPU_INT_PATHTRACING;
+		it.path_samples = par<int>(p, "path_samples", 32); it.bounces = par<int>(p, "bounces", 3);
+		it.rr_min_bounces = par<int>(p, "russian_roulette_min_bounces", 0); it.no_recursive = par<bool>(p, "no_recursive", false);
+		const std::string c = par<std::string>(p, "caustic_type", "path");
+		if(c == "photon" || c == "both") { err = "caustic photon maps are not implemented on the device"; return false; }
+		it.trace_caustics = c != "none";
+	}
+	else if(type == "directlighting")
+	{	// integrator_direct_light.cc:196-250
+		it.type = YAFGPU_INT_DIRECTLIGHT;
+		if(par<bool>(p, "caustics", false)) { err = "caustic photon maps are not implemented on the device"; return false; }
+	}
+	else { err = "integrator type '" + type + "'"; return false; }
+	it.shadow_bias = scene_->shadow_bias_; it.shadow_bias_auto = scene_->shadow_bias_auto_;
+	it.ray_min_dist = scene_->ray_min_dist_; it.ray_min_dist_auto = scene_->ray_min_dist_auto_;
+	return true;
+}
+
+// Replaces the accelerator-building half of Scene::update() (scene.cc:788-831) for this integrator: flatten what the
+// reference has built (meshes after smoothing, materials, lights, camera, background, film settings) and upload it.
+bool GpuIntegrator::preprocess()
+{
+	std::string err;
+	if(!ctx_)
+	{
+		const char *dev = getenv("YAFGPU_DEVICE");
+		if(yafgpu_create(&ctx_, dev ? atoi(dev) : 0, 0) != YAFGPU_OK) return fail(std::string("cannot create a CUDA context: ") + yafgpu_last_error(nullptr));
+	}
+	yafgpu_scene_desc d;
+	memset(&d, 0, sizeof(d));
+	d.abi_version = YAFGPU_ABI_VERSION;
+
+	// materials in creation order
+	std::vector<yafgpu_material> mats(std::max<size_t>(1, rec().materials.size()));
+	std::map<const Material *, int> mat_index;
+	for(size_t i = 0; i < rec().materials.size(); ++i)
+	{
+		if(!materialRecord(rec().materials[i], mats[i], err)) return fail(err);
+		mat_index[rec().materials[i]] = (int)i;
+	}
+
+	// geometry in the reference's global triangle order: ascending ObjId_t, visible non-base triangle meshes (scene.cc:796-817)
+	std::vector<float> pts, nrm, uvs;
+	std::vector<int32_t> vidx, nidx, uvidx, tmat, tobj;
+	std::vector<yafgpu_object> objs;
+	std::map<int, int> obj_index_of_id;
+	bool any_n = false, any_uv = false;
+	for(auto &kv : scene_->meshes_)
+	{
+		ObjData &dat = kv.second;
+		if(dat.type_ != 0 /* TRIM */) return fail("only triangle meshes (type 0) are implemented on the device");
+		const TriangleObject *o = dat.obj_;
+		if(!o->isVisible() || o->isBaseObject()) continue;
+		const int p_off = (int)(pts.size() / 3), n_off = (int)(nrm.size() / 3), uv_off = (int)(uvs.size() / 2);
+		yafgpu_object rec_o;
+		memset(&rec_o, 0, sizeof(rec_o));
+		rec_o.has_orco = o->has_orco_; rec_o.has_uv = o->has_uv_; rec_o.smooth = o->is_smooth_ || o->normals_exported_; rec_o.light = -1;
+		rec_o.first_tri = (int32_t)tmat.size(); rec_o.n_tris = (int32_t)o->triangles_.size(); rec_o.obj_id = (int32_t)(kv.first & 0x7fffffff);
+		obj_index_of_id[(int)kv.first] = (int)objs.size();
+		for(const Point3 &p : o->points_) { pts.push_back(p.x_); pts.push_back(p.y_); pts.push_back(p.z_); }
+		for(const Normal &n : o->normals_) { nrm.push_back(n.x_); nrm.push_back(n.y_); nrm.push_back(n.z_); }
+		for(const Uv &uv : o->uv_values_) { uvs.push_back(uv.u_); uvs.push_back(uv.v_); }
+		for(const Triangle &t : o->triangles_)
+		{
+			vidx.push_back(t.pa_ + p_off); vidx.push_back(t.pb_ + p_off); vidx.push_back(t.pc_ + p_off);
+			const int na[3] = {t.na_, t.nb_, t.nc_};
+			for(int k = 0; k < 3; ++k) { const bool has = rec_o.smooth && na[k] >= 0; nidx.push_back(has ? na[k] + n_off : -1); any_n |= has; }
+			for(int k = 0; k < 3; ++k)
+			{
+				if(o->has_uv_) { uvidx.push_back(o->uv_offsets_[t.self_index_ * 3 + k] + uv_off); any_uv = true; }
+				else uvidx.push_back(-1);
+			}
+			auto mi = mat_index.find(t.material_);
+			if(mi == mat_index.end()) return fail("a triangle uses a material that was not created through the environment");
+			tmat.push_back(mi->second);
+			tobj.push_back((int32_t)objs.size());
+		}
+		objs.push_back(rec_o);
+	}
+	yafgpu_geometry &g = d.geometry;
+	g.points = pts.data(); g.n_points = pts.size() / 3;
+	g.normals = nrm.data(); g.n_normals = nrm.size() / 3;
+	g.uv = uvs.data(); g.n_uv = uvs.size() / 2;
+	g.tri_vidx = vidx.data(); g.tri_nidx = any_n ? nidx.data() : nullptr; g.tri_uvidx = any_uv ? uvidx.data() : nullptr;
+	g.tri_mat = tmat.data(); g.tri_obj = tobj.data(); g.n_tris = tmat.size();
+	g.objects = objs.data(); g.n_objects = objs.size();
+	d.materials = mats.data(); d.n_materials = rec().materials.size();
+
+	// lights in Scene::lights_ order (the order doLightEstimation's per-light QMC offsets depend on)
+	std::vector<yafgpu_light> lights(std::max<size_t>(1, scene_->lights_.size()));
+	for(size_t i = 0; i < scene_->lights_.size(); ++i)
+		if(!lightRecord(scene_->lights_[i], obj_index_of_id, lights[i], err)) return fail(err);
+	d.lights = lights.data(); d.n_lights = scene_->lights_.size();
+
+	// camera "perspective" (camera_perspective.cc:206-252)
+	{
+		auto it = rec().params.find(scene_->getCamera());
+		if(it == rec().params.end()) return fail("camera was not created through RenderEnvironment::createCamera");
+		const ParamMap &p = it->second;
+		if(par<std::string>(p, "type", "") != "perspective") return fail("camera type '" + par<std::string>(p, "type", "") + "' is not implemented on the device");
+		yafgpu_camera &c = d.camera;
+		c.type = YAFGPU_CAM_PERSPECTIVE; c.resx = par<int>(p, "resx", 320); c.resy = par<int>(p, "resy", 200);
+		par3(p, "from", c.from, 0.f, 1.f, 0.f); par3(p, "to", c.to, 0.f, 0.f, 0.f); par3(p, "up", c.up, 0.f, 1.f, 1.f);
+		c.focal = par<float>(p, "focal", 1.f); c.aperture = par<float>(p, "aperture", 0.f); c.dof_distance = par<float>(p, "dof_distance", 0.f);
+		c.aspect_ratio = par<float>(p, "aspect_ratio", 1.f); c.near_clip = par<float>(p, "nearClip", 0.f); c.far_clip = par<float>(p, "farClip", -1.f);
+		const std::string bt = par<std::string>(p, "bokeh_type", "disk1"), bb = par<std::string>(p, "bokeh_bias", "uniform");
+		c.bokeh_type = bt == "disk2" ? YAFGPU_BK_DISK2 : bt == "triangle" ? YAFGPU_BK_TRI : bt == "square" ? YAFGPU_BK_SQR : bt == "pentagon" ? YAFGPU_BK_PENTA
+		             : bt == "hexagon" ? YAFGPU_BK_HEXA : bt == "ring" ? YAFGPU_BK_RING : YAFGPU_BK_DISK1;
+		c.bokeh_bias = bb == "center" ? YAFGPU_BB_CENTER : bb == "edge" ? YAFGPU_BB_EDGE : YAFGPU_BB_NONE;
+		c.bokeh_rotation = par<float>(p, "bokeh_rotation", 0.f);
+	}
+
+	// background (background_constant.cc:52-86)
+	d.background.type = YAFGPU_BG_NONE;
+	if(const Background *bg = scene_->getBackground())
+	{
+		auto it = rec().params.find(bg);
+		if(it == rec().params.end()) return fail("background was not created through RenderEnvironment::createBackground");
+		const ParamMap &p = it->second;
+		if(par<std::string>(p, "type", "") != "constant") return fail("background type '" + par<std::string>(p, "type", "") + "' is not implemented on the device");
+		d.background.type = YAFGPU_BG_CONSTANT;
+		parCol(p, "color", d.background.color, 0.f);
+		d.background.power = par<float>(p, "power", 1.f); d.background.ibl = par<bool>(p, "ibl", false);
+		d.background.with_caustic = par<bool>(p, "with_caustic", true);
+	}
+
+	// film + AA (environment.cc:456-584, 679-813); the ImageFilm the reference created is the authority for the geometry
+	{
+		const ParamMap &p = rec().film;
+		const ImageFilm *film = scene_->getImageFilm();
+		yafgpu_film_desc &f = d.film;
+		f.width = film->w_; f.height = film->h_; f.xstart = film->cx_0_; f.ystart = film->cy_0_;
+		f.aa_pixelwidth = par<float>(p, "AA_pixelwidth", 1.5f);
+		const std::string ft = par<std::string>(p, "filter_type", "box");
+		f.filter_type = ft == "mitchell" ? YAFGPU_FILTER_MITCHELL : ft == "gauss" ? YAFGPU_FILTER_GAUSS : ft == "lanczos" ? YAFGPU_FILTER_LANCZOS : YAFGPU_FILTER_BOX;
+		f.tile_size = film->getTileSize(); f.premult = par<bool>(p, "premult", false);
+		f.aa_clamp_samples = par<float>(p, "AA_clamp_samples", 0.f); f.aa_clamp_indirect = par<float>(p, "AA_clamp_indirect", 0.f);
+		f.aa_passes = par<int>(p, "AA_passes", 1);
+		f.aa_light_sample_multiplier = f.aa_indirect_sample_multiplier = 1.f;
+		f.base_sampling_offset = film->getBaseSamplingOffset();
+	}
+	if(!fillIntegrator(d.integrator, err)) return fail(err);
+	if(yafgpu_upload_scene(ctx_, &d) != YAFGPU_OK) return fail("scene upload refused");
+	yafgpu_stats st;
+	yafgpu_get_stats(ctx_, &st);
+	Y_INFO << integrator_name_ << ": " << g.n_tris << " triangles, BVH built on the GPU in " << st.ms_build << " ms" << YENDL;
+	return true;
+}
+
+// GPU accumulators -> the reference's film buffers (Pixel{Rgba col_; float weight_}, util_image_buffers.h:36-47), Combined pass
+bool GpuIntegrator::depositFilm(ImageFilm *film)
+{
+	const int w = film->w_, h = film->h_;
+	host_film_.resize((size_t)w * h * 5);
+	if(yafgpu_read_film(ctx_, host_film_.data()) != YAFGPU_OK) return fail("film read-back failed");
+	Rgba2DImageWeighed_t &img = *film->image_passes_[0];
+	for(int y = 0; y < h; ++y) for(int x = 0; x < w; ++x)
+	{
+		const float *s = &host_film_[((size_t)y * w + x) * 5];
+		Pixel &p = img(x, y);
+		p.col_ = Rgba(s[0], s[1], s[2], s[3]);
+		p.weight_ = s[4];
+	}
+	return true;
+}
+
+// The pass schedule of TiledIntegrator::render (integrator_tiled.cc:116-259) with renderPass replaced by yafgpu_render_pass.
+// Adaptive resampling uses the reference's own ImageFilm::nextPass on the deposited film to flag pixels (imagefilm.cc:270-480).
+bool GpuIntegrator::render(int num_view, ImageFilm *film)
+{
+	int aa_samples, aa_passes, aa_inc; float thr, floor_pct, smf, lmf, imf, dark_factor, clamp_s, clamp_i; bool color_noise; DarkDetectionType dark_type; int var_edge, var_pix;
+	scene_->getAaParameters(aa_samples, aa_passes, aa_inc, thr, floor_pct, smf, lmf, imf, color_noise, dark_type, dark_factor, var_edge, var_pix, clamp_s, clamp_i);
+	session__.setStatusTotalPasses(aa_passes);
+	float sample_mult = 1.f, light_mult = 1.f, indirect_mult = 1.f;
+	const int floor_pixels = (int)floorf(floor_pct * (float)film->getTotalPixels() / 100.f);
+	g_timer__.addEvent("rendert");
+	g_timer__.start("rendert");
+	film->init(aa_passes);
+	film->setAaNoiseParams(color_noise, dark_type, dark_factor, var_edge, var_pix, clamp_s);
+	if(yafgpu_film_clear(ctx_) != YAFGPU_OK) return fail("film clear failed");
+	const int w = film->w_, h = film->h_;
+	const unsigned base = film->getBaseSamplingOffset();
+
+	auto pass = [&](int samples, int offset, bool adaptive, int number, const uint8_t *mask) -> bool
+	{
+		yafgpu_pass_desc pd;
+		memset(&pd, 0, sizeof(pd));
+		pd.n_samples = samples; pd.offset = (int32_t)(offset + base); pd.adaptive = adaptive; pd.aa_pass_number = number; pd.resample_mask = mask;
+		session__.setStatusCurrentPass(number + 1);
+		film->setSamplingOffset(offset + samples);
+		if(yafgpu_render_pass(ctx_, &pd) != YAFGPU_OK) return fail("render pass failed");
+		return depositFilm(film);
+	};
+	if(!pass(aa_samples, 0, false, 0, nullptr)) return false;
+	int acum = aa_samples, resampled = 0;
+	bool thr_changed = true;
+	std::vector<uint8_t> mask;
+	for(int i = 1; i < aa_passes; ++i)
+	{
+		if(scene_->getSignals() & Y_SIG_ABORT) break;
+		sample_mult *= smf; light_mult *= lmf; indirect_mult *= imf;
+		yafgpu_set_aa_multipliers(ctx_, light_mult, indirect_mult);
+		film->setAaNoiseParams(color_noise, dark_type, dark_factor, var_edge, var_pix, clamp_s);
+		if(resampled <= 0 && !thr_changed) film->nextPass(num_view, true, integrator_name_, /*skip_next_pass=*/true);
+		else
+		{
+			film->setAaThreshold(thr);
+			resampled = film->nextPass(num_view, true, integrator_name_);
+			thr_changed = false;
+		}
+		const int n = (int)ceilf(aa_inc * sample_mult);
+		if(resampled > 0)
+		{
+			const uint8_t *m = nullptr;
+			if(thr > 0.f)
+			{	// ImageFilm::doMoreSamples (imagefilm.cc:917-920)
+				mask.assign((size_t)w * h, 0);
+				for(int y = 0; y < h; ++y) for(int x = 0; x < w; ++x) mask[(size_t)y * w + x] = film->doMoreSamples(x + film->cx_0_, y + film->cy_0_) ? 1 : 0;
+				m = mask.data();
+			}
+			if(!pass(n, acum, true, i, m)) return false;
+		}
+		acum += n;
+		if(resampled < floor_pixels)
+		{
+			const float ratio = std::min(8.f, (float)floor_pixels / resampled);
+			thr *= (1.f - 0.1f * ratio);
+			if(thr > 0.f) thr_changed = true;
+		}
+	}
+	g_timer__.stop("rendert");
+	session__.setStatusRenderFinished();
+	yafgpu_stats st;
+	yafgpu_get_stats(ctx_, &st);
+	const double rays = (double)(st.rays_camera + st.rays_extension + st.rays_shadow + st.rays_shadow_transp);
+	Y_INFO << integrator_name_ << ": Overall rendertime: " << g_timer__.getTime("rendert") << "s, " << rays / 1e6 << " Mrays, "
+	       << (st.ms_total > 0 ? rays / st.ms_total / 1e3 : 0.0) << " Mrays/s on the device" << YENDL;
+	return true;
+}
+
+END_YAFARAY
+
+// ---- link-time interception (GNU ld --wrap=<mangled name>, see oracle/Makefile `GPU_WRAP`) ----------------------------------
+// `__wrap_X` receives every call to X made from another object file; `__real_X` is the reference's own definition.
+// Member functions are declared as free functions taking `this` first (Itanium C++ ABI: identical calling convention).
+using namespace yafaray4;
+#define YG_STR "NSt7__cxx1112basic_stringIcSt11char_traitsIcESaIcEEE"
+#define YG_ENV "_ZN8yafaray417RenderEnvironment"
+#define YG_SYM_MATERIAL   YG_ENV "14createMaterialERK" YG_STR "RNS_8ParamMapERNS1_4listIS9_SaIS9_EEE"
+#define YG_SYM_LIGHT      YG_ENV "11createLightERK" YG_STR "RNS_8ParamMapE"
+#define YG_SYM_CAMERA     YG_ENV "12createCameraERK" YG_STR "RNS_8ParamMapE"
+#define YG_SYM_BACKGROUND YG_ENV "16createBackgroundERK" YG_STR "RNS_8ParamMapE"
+#define YG_SYM_INTEGRATOR YG_ENV "16createIntegratorERK" YG_STR "RNS_8ParamMapE"
+#define YG_SYM_SETUP      YG_ENV "10setupSceneERNS_5SceneERKNS_8ParamMapERNS_11ColorOutputEPNS_11ProgressBarE"
+
+extern "C" {
+Material *yg_real_material(RenderEnvironment *, const std::string &, ParamMap &, std::list<ParamMap> &) asm("__real_" YG_SYM_MATERIAL);
+Light *yg_real_light(RenderEnvironment *, const std::string &, ParamMap &) asm("__real_" YG_SYM_LIGHT);
+Camera *yg_real_camera(RenderEnvironment *, const std::string &, ParamMap &) asm("__real_" YG_SYM_CAMERA);
+Background *yg_real_background(RenderEnvironment *, const std::string &, ParamMap &) asm("__real_" YG_SYM_BACKGROUND);
+Integrator *yg_real_integrator(RenderEnvironment *, const std::string &, ParamMap &) asm("__real_" YG_SYM_INTEGRATOR);
+bool yg_real_setup(RenderEnvironment *, Scene &, const ParamMap &, ColorOutput &, ProgressBar *) asm("__real_" YG_SYM_SETUP);
+
+Material *yg_wrap_material(RenderEnvironment *, const std::string &, ParamMap &, std::list<ParamMap> &) asm("__wrap_" YG_SYM_MATERIAL);
+Light *yg_wrap_light(RenderEnvironment *, const std::string &, ParamMap &) asm("__wrap_" YG_SYM_LIGHT);
+Camera *yg_wrap_camera(RenderEnvironment *, const std::string &, ParamMap &) asm("__wrap_" YG_SYM_CAMERA);
+Background *yg_wrap_background(RenderEnvironment *, const std::string &, ParamMap &) asm("__wrap_" YG_SYM_BACKGROUND);
+Integrator *yg_wrap_integrator(RenderEnvironment *, const std::string &, ParamMap &) asm("__wrap_" YG_SYM_INTEGRATOR);
+bool yg_wrap_setup(RenderEnvironment *, Scene &, const ParamMap &, ColorOutput &, ProgressBar *) asm("__wrap_" YG_SYM_SETUP);
+}
+
+static void remember(const void *obj, const std::string &name, const ParamMap &p)
+{
+	if(!obj) return;
+	rec().params[obj] = p;
+	rec().names[obj] = name;
+}
+
+Material *yg_wrap_material(RenderEnvironment *env, const std::string &name, ParamMap &p, std::list<ParamMap> &e)
+{
+	const ParamMap copy = p; // factories may edit the map they are given
+	Material *m = yg_real_material(env, name, p, e);
+	if(m) { remember(m, name, copy); rec().materials.push_back(m); }
+	return m;
+}
+Light *yg_wrap_light(RenderEnvironment *env, const std::string &name, ParamMap &p)
+{
+	const ParamMap copy = p;
+	Light *l = yg_real_light(env, name, p);
+	remember(l, name, copy);
+	return l;
+}
+Camera *yg_wrap_camera(RenderEnvironment *env, const std::string &name, ParamMap &p)
+{
+	const ParamMap copy = p;
+	Camera *c = yg_real_camera(env, name, p);
+	remember(c, name, copy);
+	return c;
+}
+Background *yg_wrap_background(RenderEnvironment *env, const std::string &name, ParamMap &p)
+{
+	const ParamMap copy = p;
+	Background *b = yg_real_background(env, name, p);
+	remember(b, name, copy);
+	return b;
+}
+// setupScene receives the <render> block (film size, filter, AA settings): environment.cc:679-813
+bool yg_wrap_setup(RenderEnvironment *env, Scene &scene, const ParamMap &p, ColorOutput &out, ProgressBar *pb)
+{
+	rec().film = p;
+	return yg_real_setup(env, scene, p, out, pb);
+}
+// What Integrator::factory would do with two more `else if` lines (src/integrator/integrator.cc:35-56).
+Integrator *yg_wrap_integrator(RenderEnvironment *env, const std::string &name, ParamMap &p)
+{
+	std::string type;
+	p.getParam("type", type);
+	const char *off = getenv("YAFGPU_DISABLE");
+	bool gpu = !(off && atoi(off) != 0);
+	p.getParam("gpu", gpu);
+	if(!gpu || (type != "pathtracing" && type != "directlighting")) return yg_real_integrator(env, name, p);
+	if(env->integrators_.find(name) != env->integrators_.end()) return nullptr; // same rule as createIntegrator (environment.cc:370-373)
+	Integrator *i = new GpuIntegrator(p);
+	env->integrators_[name] = i;
+	Y_INFO << "Environment: GPU integrator substituted for '" << type << "' (" << name << ")" << YENDL;
+	return i;
+}

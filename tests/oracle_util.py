@@ -51,6 +51,30 @@ def run_reference_render(iface, threads=1, flavour="ieee", timeout=3600):
         return load_film(out), info
 
 
+def gpu_frontend_bin():
+    """The reference front end with the GPU integrator linked in (integration/gpu_integrator.cc, oracle/Makefile `gpu`)."""
+    p = os.path.join(ROOT, "oracle", "_ref", "yaf_xml_gpu")
+    return p if os.path.exists(p) else None
+
+
+def run_gpu_frontend(iface, env=None, timeout=600):
+    """XML -> reference loader -> GpuIntegrator -> C ABI -> GPU -> reference ImageFilm; returns (film, info, completed process)."""
+    exe = gpu_frontend_bin()
+    with tempfile.TemporaryDirectory() as td:
+        xml, out = os.path.join(td, "scene.xml"), os.path.join(td, "out.film")
+        iface.to_xml(xml)
+        e = dict(os.environ)
+        e.update(env or {})
+        r = subprocess.run([exe, "render", xml, out, "1"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=timeout, env=e)
+        film, info = None, {}
+        if r.returncode == 0:
+            film = load_film(out)
+            for line in reversed(r.stdout.decode(errors="replace").strip().splitlines()):
+                if line.startswith("{"):
+                    info = json.loads(line); break
+        return film, info, r
+
+
 def reference_film(iface, key, allow_run=True, write=False):
     """Accumulator film of the reference for `iface`: golden fixture tests/golden/<key>.npz, else the live oracle."""
     path = os.path.join(GOLDEN, key + ".npz")

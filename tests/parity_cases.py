@@ -158,4 +158,10 @@ EXACT["cornell_pt_norr"] = lambda: scenes.cornell_box(160, 90, 16, path_samples=
 EXACT["zoo_pt_mesh_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, rr_min_bounces=99)
 EXACT["zoo_dl_point_free"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3)
 EXACT["zoo_dl_transpshad"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, transp_shad=True)
+
+# rendered only through the reference front end with the GPU integrator linked in (oracle/_ref/yaf_xml_gpu): adaptive AA is
+# driven by the reference's own ImageFilm::nextPass there
+FRONTEND_ONLY = {
+    "cornell_dl_adaptive": lambda: scenes.cornell_box(160, 90, 2, integrator="directlighting", aa_passes=3, AA_threshold=0.02, AA_inc_samples=2),
+}
 CONVERGED["zoo_pt"] = (lambda spp: material_zoo_scene(W, H, spp), 8192)

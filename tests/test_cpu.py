@@ -136,3 +136,19 @@ def test_film_reduce_world2_gloo():
         p.join(120)
         assert p.exitcode == 0
     assert q.get(timeout=5) < 1e-6
+
+
+@pytest.mark.skipif(ou.gpu_frontend_bin() is None, reason="oracle/_ref/yaf_xml_gpu not built")
+def test_gpu_frontend_fails_loudly_without_gpu_and_can_be_disabled():
+    """The reference front end with GpuIntegrator linked in: without a GPU the render FAILS (no CPU fallback); with
+    YAFGPU_DISABLE=1 the reference's own integrator is left in place and reproduces the golden film."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    y = pc.EXACT["simple_dl_gauss"]()
+    film, info, r = ou.run_gpu_frontend(y)
+    assert r.returncode != 0 and b"no CPU fallback" in r.stderr + r.stdout
+    film, info, r = ou.run_gpu_frontend(y, env={"YAFGPU_DISABLE": "1"})
+    assert r.returncode == 0
+    gold = np.load(os.path.join(ou.GOLDEN, "simple_dl_gauss.npz"))["film"]
+    assert np.array_equal(film, gold)

@@ -85,11 +85,7 @@ def test_trace_edge_cases(ctx):
 
 
 # ---- deterministic renders: per-pixel equality with the reference film ------------------------------------------------------
-@pytest.mark.parametrize("name", list(pc.EXACT))
-def test_render_matches_reference_film(ctx, name):
-    from libyafaray_b200 import render_scene
-    gold = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
-    film = render_scene(pc.EXACT[name](), ctx=ctx)
+def _assert_film_matches(film, gold):
     assert film.shape == gold.shape
     # filter weights: same footprints, same table -> equal up to float summation order
     assert np.abs(film[..., 4] - gold[..., 4]).max() <= 1e-5 * gold[..., 4].max()
@@ -105,6 +101,31 @@ def test_render_matches_reference_film(ctx, name):
     # whole image, flipped pixels included: one flipped sample of a 4-spp fixture moves its pixel by up to 25 %
     assert ou.rel_rmse(gi, ri) <= (1e-3 if not flip.any() else 5e-3)
     assert np.abs(gi[..., 3] - ri[..., 3]).max() <= 1e-5
+
+
+@pytest.mark.parametrize("name", list(pc.EXACT))
+def test_render_matches_reference_film(ctx, name):
+    from libyafaray_b200 import render_scene
+    gold = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
+    _assert_film_matches(render_scene(pc.EXACT[name](), ctx=ctx), gold)
+
+
+# ---- the drop-in boundary itself: reference XML loader + Scene + ImageFilm with GpuIntegrator linked in ----------------------
+FRONTEND_CASES = ["simple_dl_gauss", "cornell_dl_glass", "cornell_dl_mitchell", "cornell_pt_norr", "zoo_dl_point_free", "zoo_pt_mesh_norr",
+                  "cornell_dl_adaptive"]
+
+
+@pytest.mark.skipif(ou.gpu_frontend_bin() is None, reason="oracle/_ref/yaf_xml_gpu not built (needs the reference sources)")
+@pytest.mark.parametrize("name", FRONTEND_CASES)
+def test_reference_frontend_with_gpu_integrator(name):
+    """scene.xml -> reference's XML loader -> RenderEnvironment/Scene -> GpuIntegrator (integration/gpu_integrator.cc) -> C ABI ->
+    GPU -> the reference's ImageFilm buffers; compared with the film of the reference's own CPU integrator on the same XML."""
+    build = pc.EXACT.get(name) or pc.FRONTEND_ONLY[name]
+    gold = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
+    film, info, r = ou.run_gpu_frontend(build())
+    assert r.returncode == 0, r.stderr.decode(errors="replace")[-2000:]
+    assert b"GPU integrator substituted" in r.stderr + r.stdout or info.get("rendert_s") is not None
+    _assert_film_matches(film, gold)
 
 
 TOL_CONVERGED = {"cornell_pt": 4e-3, "cornell_pt_noglass": 3e-3, "zoo_pt": 5e-3, "cornell_pt_512k": 1.5e-3}

@@ -19,7 +19,7 @@ def main():
         if a.startswith("--threads="):
             threads = int(a.split("=")[1])
     want = args or ["exact", "hits", "converged"]
-    for name, build in pc.EXACT.items():
+    for name, build in list(pc.EXACT.items()) + list(pc.FRONTEND_ONLY.items()):
         if "exact" in want or name in want:
             t0 = time.time()
             film = ou.reference_film(build(), name, write=True)
