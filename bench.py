@@ -106,7 +106,7 @@ def rays_per_sample_default():
         with open(RAYS_FILE) as fh:
             return float(json.load(fh)["rays_per_camera_sample"])
     except Exception:
-        return 40.0
+        return 11.147  # device-counted rays per camera sample of this workload (profiles/r1_bench_n1.json); the CPU reference has no ray counter
 
 
 def reference_arm(args, rank, world):
