@@ -55,6 +55,23 @@ class ClockSampler(threading.Thread):
         self.index, self.stop_flag, self.rows = index, False, []
 
     def run(self):
+        # NVML in-process (a sample every 10 ms, so that sub-second timed regions are covered); nvidia-smi as the fallback
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            R = pynvml
+            bits = [("hw_slowdown", R.nvmlClocksThrottleReasonHwSlowdown), ("hw_thermal_slowdown", R.nvmlClocksThrottleReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", R.nvmlClocksThrottleReasonSwThermalSlowdown), ("sw_power_cap", R.nvmlClocksThrottleReasonSwPowerCap)]
+            while not self.stop_flag:
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                rs = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append([str(sm), str(mx)] + ["Active" if rs & b else "Not Active" for _, b in bits])
+                time.sleep(0.01)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         while not self.stop_flag:
