@@ -415,7 +415,8 @@ int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
 int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
 
 /* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave, default 2^20),
- * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8). */
+ * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "ray_regeneration" (1: the wavefront
+ * traversal kernels use the warp-persistent schedule with ray regeneration that yafgpu_trace always uses; default 0). */
 int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);
 int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
 int yafgpu_reset_stats(yafgpu_ctx *ctx);

@@ -65,31 +65,35 @@ __global__ void k_tri_shade(int n, const int *__restrict__ vidx, const int *__re
 }
 
 // ---- batch trace kernels (parity probe + microbench) -----------------------------------------------------------------
+struct BatchIO
+{
+	const float4 *rays; float4 *hits; bool shadow;
+	__device__ __forceinline__ void load(int i, V3 &o, V3 &d, float &tmin, float &dist) const
+	{
+		const float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+		o = mk(a.x, a.y, a.z); tmin = a.w; d = mk(b.x, b.y, b.z);
+		dist = (b.w < 0.f) ? __int_as_float(0x7f800000) : b.w;
+		if(shadow)
+		{	// Scene::isShadowed scene.cc:962-970: shift the origin, shorten the segment
+			o = o + d * a.w;
+			if(!(b.w < 0.f)) dist = b.w - 2 * a.w;
+		}
+	}
+	__device__ __forceinline__ void store(int i, const HitD &h, unsigned) const
+	{
+		hits[i] = shadow ? make_float4(h.tri >= 0 ? 1.f : 0.f, 0.f, 0.f, __int_as_float(h.tri)) : make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+	}
+};
+
+// the same warp-persistent traversal the wavefront kernels use, on a caller-supplied ray array (at most 2^31 - 1 rays per call)
 template<bool COUNT>
 __global__ void __launch_bounds__(128) k_trace_batch(Accel acc, const yafgpu_ray *__restrict__ rays, size_t n, yafgpu_hit *__restrict__ hits,
-                                                        int mode, unsigned long long *__restrict__ counters)
+                                                        int mode, int *__restrict__ next, unsigned long long *__restrict__ counters)
 {
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
-	for(size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-	{
-		const float4 a = __ldg((const float4 *)rays + 2 * i), b = __ldg((const float4 *)rays + 2 * i + 1);
-		RayD r; r.o = mk(a.x, a.y, a.z); r.tmin = a.w; r.d = mk(b.x, b.y, b.z); r.tmax = b.w;
-		float4 out;
-		if(mode == YAFGPU_TRACE_CLOSEST)
-		{
-			HitD h = traceClosest<COUNT>(acc, r, &tc);
-			out = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
-		}
-		else
-		{
-			// Scene::isShadowed scene.cc:962-970: shift the origin, shorten the segment
-			V3 o = r.o + r.d * r.tmin;
-			float dist = (r.tmax < 0.f) ? __int_as_float(0x7f800000) : r.tmax - 2 * r.tmin;
-			int blocker = traceShadow<COUNT>(acc, o, r.d, dist, &tc);
-			out = make_float4(blocker >= 0 ? 1.f : 0.f, 0.f, 0.f, __int_as_float(blocker));
-		}
-		((float4 *)hits)[i] = out;
-	}
+	BatchIO io; io.rays = (const float4 *)rays; io.hits = (float4 *)hits; io.shadow = mode != YAFGPU_TRACE_CLOSEST;
+	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, COUNT>(acc, (int)n, next, io, &tc);
+	else traversePersistent<true, COUNT>(acc, (int)n, next, io, &tc);
 	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
 }
 
@@ -125,6 +129,7 @@ int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags)
 	if(e == cudaSuccess) e = cudaMemcpy(c->d_faure, ft, sizeof(FaureTables), cudaMemcpyHostToDevice);
 	delete ft;
 	if(e == cudaSuccess) e = cudaMalloc(&c->d_counters, sizeof(unsigned long long) * CNT_N);
+	if(e == cudaSuccess) e = cudaMalloc(&c->d_fetch, sizeof(int));
 	if(e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * CNT_N);
 	if(e != cudaSuccess) { yafgpu_destroy(c); return cudaErr(nullptr, e, "context allocation"); }
 	*out = c;
@@ -138,7 +143,7 @@ void yafgpu_destroy(yafgpu_ctx *c)
 	if(c->stream) cudaStreamSynchronize(c->stream);
 	freeScene(c);
 	freeWavefront(c);
-	cudaFree(c->d_faure); cudaFree(c->d_counters);
+	cudaFree(c->d_faure); cudaFree(c->d_counters); cudaFree(c->d_fetch);
 	for(cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
 	if(c->ev0) cudaEventDestroy(c->ev0);
 	if(c->ev1) cudaEventDestroy(c->ev1);
@@ -363,12 +368,14 @@ int yafgpu_trace_device(yafgpu_ctx *c, const void *d_rays, size_t n, void *d_hit
 	if(n == 0) return YAFGPU_OK;
 	YG_CUDA(c, cudaSetDevice(c->device));
 	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	if(n > 0x7fffffffu) return setErr(c, YAFGPU_ERR_INVALID, "at most 2^31 - 1 rays per call");
+	YG_CUDA(c, cudaMemsetAsync(c->d_fetch, 0, sizeof(int), c->stream));
 	size_t want = (n + 127) / 128;
 	unsigned grid = (unsigned)(want < (size_t)sms * 16 ? want : (size_t)sms * 16);
 	if(c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL)
-		k_trace_batch<true><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_counters);
+		k_trace_batch<true><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_fetch, c->d_counters);
 	else
-		k_trace_batch<false><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_counters);
+		k_trace_batch<false><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_fetch, c->d_counters);
 	YG_CUDA(c, cudaGetLastError());
 	c->stats.kernel_launches++;
 	if(mode == YAFGPU_TRACE_CLOSEST) c->stats.rays_extension += n; else c->stats.rays_shadow += n;
@@ -461,6 +468,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	if(!c || !name) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
 	const std::string n(name);
 	if(n == "wave_size") { if(value < 1024 || value > (1 << 24)) return setErr(c, YAFGPU_ERR_INVALID, "wave_size out of range"); c->wave_cap_override = (int)value; return YAFGPU_OK; }
+	if(n == "ray_regeneration") { c->ray_regeneration = value != 0; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);
 }

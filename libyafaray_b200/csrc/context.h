@@ -46,6 +46,8 @@ struct yafgpu_ctx
 
 	// stats
 	yafgpu_stats stats;
+	int ray_regeneration = 0;                 // yafgpu_set_option("ray_regeneration"): wavefront trace kernels use the warp-persistent traversal
+	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	std::vector<cudaEvent_t> stage_events; // YAFGPU_FLAG_TIME_STAGES

@@ -159,4 +159,126 @@ YG_D int traceShadow(const Accel &acc, const V3 o, const V3 d, float dist, TravC
 	return -1;
 }
 
+// ---- warp-persistent traversal with ray regeneration ------------------------------------------------------------------------
+// The wavefront kernels do not map ray i to thread i.  Every warp keeps 32 rays in flight; a lane whose ray has finished stores
+// its result and takes the next unprocessed ray from a global counter (one warp-aggregated atomicAdd per refill), so lanes do not
+// idle until the slowest ray of their warp is done.  Inside, traversal is "while-while": all lanes first descend through inner
+// nodes until each holds a leaf (or has nothing left), then all process their leaf together, so the node loop and the
+// Möller–Trumbore loop each run with most lanes active instead of interleaving per lane.
+//
+// IO supplies:  void load(int idx, V3 &o, V3 &d, float &tmin, float &dist)
+//               void store(int idx, const HitD &h, unsigned lanes_storing)   called warp-synchronously by the lanes in `lanes_storing`
+// ANYHIT: Scene::isShadowed semantics (origin already shifted by load, accept t in [0, dist), TRI_VIS_SHADOW, first hit ends the ray);
+// else Scene::intersect semantics (accept t in [tmin, z), TRI_VIS_CAMERA, lowest id at equal t).
+#define YG_EMPTY ((int)0x80000000)
+#ifndef YG_REGEN_THRESH
+#define YG_REGEN_THRESH 22 /* refill as soon as fewer lanes than this are still traversing */
+#endif
+#ifndef YG_REGEN_ROUNDS
+#define YG_REGEN_ROUNDS 6
+#endif
+
+template<bool ANYHIT, bool COUNT, class IO>
+__device__ __forceinline__ void traversePersistent(const Accel &acc, int n, int *__restrict__ next, IO &io, TravCounters *cnt)
+{
+	const unsigned FULL = 0xffffffffu;
+	const int lane = threadIdx.x & 31;
+	const unsigned lt_mask = (1u << lane) - 1u;
+	int ray = -1;          // index of the ray this lane works on, -1 = none
+	int cur = YG_EMPTY;    // node to visit next: >= 0 inner node, < 0 leaf code, YG_EMPTY = traversal finished
+	V3 o = mk(0.f), d = mk(0.f), id = mk(0.f);
+	float tmin = 0.f, z = 0.f, tlo = 0.f;
+	HitD h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.tri = -1;
+	int stack[YG_STACK];
+	int sp = 0;
+	bool exhausted = false; // the global counter has run past n
+	for(;;)
+	{
+		// ---- refill idle lanes (warp-synchronous) ----
+		const unsigned idle = __ballot_sync(FULL, ray < 0);
+		if(idle && !exhausted)
+		{
+			const int want = __popc(idle);
+			int base = 0;
+			if(lane == 0) base = atomicAdd(next, want);
+			base = __shfl_sync(FULL, base, 0);
+			if(base + want >= n) exhausted = true;
+			if(ray < 0)
+			{
+				const int idx = base + __popc(idle & lt_mask);
+				if(idx < n)
+				{
+					float dist;
+					io.load(idx, o, d, tmin, dist);
+					ray = idx;
+					id = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
+					z = dist; tlo = ANYHIT ? 0.f : tmin * 0.99f;
+					h.t = 0.f; h.u = 0.f; h.v = 0.f; h.tri = -1;
+					sp = 0; cur = acc.n_tris != 0 ? acc.root : YG_EMPTY;
+				}
+			}
+		}
+		if(__all_sync(FULL, ray < 0)) { if(exhausted) break; else continue; }
+
+		// ---- a few while-while rounds, then look for lanes to refill ----
+		#pragma unroll 1
+		for(int round = 0; round < YG_REGEN_ROUNDS; ++round)
+		{
+			// node phase: descend until this lane holds a leaf or has finished
+			while(cur >= 0)
+			{
+				const BvhNode *nd = acc.nodes + cur;
+				const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
+				if(COUNT) cnt->nodes++;
+				float ta, tb;
+				const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, tlo, z, ta);
+				const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, tlo, z, tb);
+				const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
+				if(ha && hb)
+				{
+					const bool a_first = ANYHIT ? true : (ta <= tb);
+					cur = a_first ? ca : cb;
+					if(sp < YG_STACK) stack[sp++] = a_first ? cb : ca;
+				}
+				else if(ha) cur = ca;
+				else if(hb) cur = cb;
+				else cur = sp > 0 ? stack[--sp] : YG_EMPTY;
+			}
+			// leaf phase
+			if(cur != YG_EMPTY)
+			{
+				const int code = ~cur;
+				const int first = code >> 3, count = (code & 7) + 1;
+				bool ended = false;
+				for(int k = 0; k < count; ++k)
+				{
+					const TriAccel *tp = acc.tris + first + k;
+					const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
+					if(COUNT) cnt->tris++;
+					float t, u, v;
+					if(!triIntersect(v0e, e1i, e2f, o, d, t, u, v)) continue;
+					const int fl = __float_as_int(e2f.w), id_ = __float_as_int(e1i.w);
+					if(ANYHIT)
+					{
+						if(t < z && t >= 0.f && (fl & TRI_VIS_SHADOW)) { h.tri = id_; h.t = 1.f; ended = true; break; }
+					}
+					else
+					{
+						if(!(fl & TRI_VIS_CAMERA)) continue;
+						if(t >= tmin && (t < z || (t == z && h.tri >= 0 && id_ < h.tri))) { z = t; h.t = t; h.u = u; h.v = v; h.tri = id_; }
+					}
+				}
+				cur = (ended || sp == 0) ? YG_EMPTY : stack[--sp];
+			}
+			// leave early when enough lanes have nothing to do
+			if(__popc(__ballot_sync(FULL, ray >= 0 && cur != YG_EMPTY)) < YG_REGEN_THRESH) break;
+		}
+
+		// ---- store finished rays (warp-synchronous) ----
+		const bool fin = ray >= 0 && cur == YG_EMPTY;
+		const unsigned fin_mask = __ballot_sync(FULL, fin);
+		if(fin) { io.store(ray, h, fin_mask); ray = -1; }
+	}
+}
+
 } // namespace yg

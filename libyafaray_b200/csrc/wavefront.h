@@ -53,6 +53,8 @@ struct WaveCtl // lives in device memory, zeroed at wave start
 {
 	int n_tasks[YG_MAX_ITERS + 2];   // number of tasks queued for iteration i
 	int n_shadow[YG_MAX_ITERS + 2];  // number of shadow rays queued by iteration i
+	int fetch_trace[YG_MAX_ITERS + 2];  // next unclaimed task of iteration i (ray regeneration in k_trace)
+	int fetch_shadow[YG_MAX_ITERS + 2]; // next unclaimed shadow ray of iteration i (k_shadow)
 	int overflow;                     // a queue ran out of capacity: the wave is discarded and retried smaller
 	int pad;
 };

@@ -97,6 +97,9 @@ class Context:
     def set_aa_multipliers(self, light, indirect):
         _check(self.h, capi.lib.yafgpu_set_aa_multipliers(self.h, light, indirect))
 
+    def set_option(self, name, value):
+        _check(self.h, capi.lib.yafgpu_set_option(self.h, name.encode(), int(value)))
+
     def stats(self):
         s = capi.Stats()
         _check(self.h, capi.lib.yafgpu_get_stats(self.h, C.byref(s)))

@@ -170,6 +170,20 @@ def test_film_is_linear_in_sample_ranges_full_size(ctx):
     assert st["camera_samples"] >= 3 * 4 * 1920 * 1080
 
 
+def test_ray_regeneration_schedule_gives_the_same_film(ctx):
+    """The warp-persistent traversal (yafgpu_set_option("ray_regeneration", 1)) changes which lane traces which ray, nothing else."""
+    from libyafaray_b200 import render_scene
+    y = pc.material_zoo_scene(96, 54, 4)
+    a = render_scene(y, ctx=ctx)
+    ctx.set_option("ray_regeneration", 1)
+    try:
+        b = render_scene(y, ctx=ctx)
+    finally:
+        ctx.set_option("ray_regeneration", 0)
+    assert np.array_equal(a[..., 4], b[..., 4])
+    assert np.abs(a[..., :3] - b[..., :3]).max() <= 1e-4 * float(np.abs(a[..., :3]).max())
+
+
 def test_empty_scene_renders_background(ctx):
     from libyafaray_b200 import scenes
     from libyafaray_b200.interface import Interface
