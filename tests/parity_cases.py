@@ -26,6 +26,8 @@ EXACT = {
 CONVERGED = {
     "cornell_pt": (_cornell(path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2), 65536),
     "cornell_pt_noglass": (_cornell(glass=False, path_samples=1, bounces=4, raydepth=4, rr_min_bounces=1), 32768),
+    # same scene as cornell_pt at 8x the samples (reference: 86 CPU-minutes on 6 threads, /tmp script = tools/converged_dump.py)
+    "cornell_pt_512k": (_cornell(path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2), 524288),
 }
 
 
