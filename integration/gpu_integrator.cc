@@ -58,6 +58,9 @@
 #include "light/light.h"
 #include "camera/camera.h"
 #include "background/background.h"
+#include "background/background_texture.h"
+#include "texture/texture_image.h"
+#include "imagehandler/imagehandler.h"
 #include "integrator/integrator.h"
 #undef private
 #undef protected
@@ -222,7 +225,7 @@ bool lightRecord(const Light *l, const std::map<int, int> &obj_index_of_id, yafg
 		out.type = YAFGPU_LIGHT_BACKGROUND;
 		out.samples = par<int>(p, "samples", 16);
 		out.abs_intersect = par<bool>(p, "abs_intersect", false);
-		out.clamp_intersect = 0.f;
+		out.clamp_intersect = l->clamp_intersect_; // set after creation by TextureBackground::factory (background_texture.cc:155-160)
 	}
 	else { err = "light type '" + type + "' is not implemented on the device"; return false; }
 	return true;
@@ -256,7 +259,7 @@ class GpuIntegrator final : public SurfaceIntegrator
 		bool depositFilm(ImageFilm *film);
 		ParamMap params_;
 		yafgpu_ctx *ctx_ = nullptr;
-		std::vector<float> host_film_;
+		std::vector<float> host_film_, bg_texels_;
 };
 
 bool GpuIntegrator::fillIntegrator(yafgpu_integrator_desc &it, std::string &err) const
@@ -390,9 +393,40 @@ bool GpuIntegrator::preprocess()
 		auto it = rec().params.find(bg);
 		if(it == rec().params.end()) return fail("background was not created through RenderEnvironment::createBackground");
 		const ParamMap &p = it->second;
-		if(par<std::string>(p, "type", "") != "constant") return fail("background type '" + par<std::string>(p, "type", "") + "' is not implemented on the device");
-		d.background.type = YAFGPU_BG_CONSTANT;
-		parCol(p, "color", d.background.color, 0.f);
+		const std::string btype = par<std::string>(p, "type", "");
+		if(btype == "constant")
+		{
+			d.background.type = YAFGPU_BG_CONSTANT;
+			parCol(p, "color", d.background.color, 0.f);
+		}
+		else if(btype == "textureback")
+		{	// background_texture.cc:90-165; texels are taken from the reference's own ImageHandler (post load, post colour-space handling)
+			const TextureBackground *tb = static_cast<const TextureBackground *>(bg);
+			const ImageTexture *it_ = dynamic_cast<const ImageTexture *>(tb->tex_);
+			if(!it_) return fail("textureback: only image textures are implemented on the device");
+			if(it_->tex_clip_mode_ != ImageTexture::TexClipMode::Repeat || it_->xrepeat_ != 1 || it_->yrepeat_ != 1 || it_->mirror_x_ || it_->mirror_y_
+			   || it_->cropx_ || it_->cropy_ || it_->rot_90_ || it_->adjustments_set_)
+				return fail("textureback: texture clipping/repeat/mirror/crop/rot90/adjustments are not implemented on the device");
+			const InterpolationType ip = it_->getInterpolationType();
+			if(ip != InterpolationType::Bilinear && ip != InterpolationType::None) return fail("textureback: only 'bilinear' and 'none' texture interpolation are implemented on the device");
+			if(par<float>(p, "smartibl_blur", 0.f) > 0.f) return fail("textureback: smartibl_blur is not implemented on the device");
+			ImageHandler *ih = it_->image_;
+			const int tw = ih->getWidth(), th = ih->getHeight();
+			bg_texels_.resize((size_t)tw * th * 3);
+			for(int y = 0; y < th; ++y) for(int x = 0; x < tw; ++x)
+			{
+				const Rgba c = ih->getPixel(x, y);
+				float *o = &bg_texels_[((size_t)y * tw + x) * 3];
+				o[0] = c.r_; o[1] = c.g_; o[2] = c.b_;
+			}
+			d.background.type = YAFGPU_BG_TEXTURE;
+			d.background.tex_rgb = bg_texels_.data(); d.background.tex_w = tw; d.background.tex_h = th;
+			d.background.tex_interp = ip == InterpolationType::Bilinear;
+			const std::string mapping = par<std::string>(p, "mapping", "");
+			d.background.mapping_angular = mapping == "probe" || mapping == "angular";
+			d.background.rotation = par<float>(p, "rotation", 0.f);
+		}
+		else return fail("background type '" + btype + "' is not implemented on the device");
 		d.background.power = par<float>(p, "power", 1.f); d.background.ibl = par<bool>(p, "ibl", false);
 		d.background.with_caustic = par<bool>(p, "with_caustic", true);
 	}

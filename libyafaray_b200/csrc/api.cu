@@ -230,6 +230,15 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	const yafgpu_background &bg = desc->background;
 	s.bg.type = bg.type;
 	if(bg.type == YAFGPU_BG_CONSTANT) for(int k = 0; k < 3; ++k) s.bg.color[k] = bg.color[k] * bg.power; // background_constant.cc:86
+	else if(bg.type == YAFGPU_BG_TEXTURE)
+	{	// TextureBackground ctor background_texture.cc:32-39
+		if(!bg.tex_rgb || bg.tex_w <= 0 || bg.tex_h <= 0) return setErr(c, YAFGPU_ERR_INVALID, "texture background without texels");
+		s.bg.mapping_angular = bg.mapping_angular; s.bg.power = bg.power; s.bg.tex_interp = bg.tex_interp;
+		s.bg.rotation = 2.0f * bg.rotation / 360.f;
+		s.bg.sin_r = fSin((float)(YG_M_PI * (double)s.bg.rotation)); s.bg.cos_r = fCos((float)(YG_M_PI * (double)s.bg.rotation));
+		s.bg.tex_w = bg.tex_w; s.bg.tex_h = bg.tex_h;
+		s.bg.tex = bg.tex_rgb; // host pointer while the light tables are built below; replaced by the device copy afterwards
+	}
 	else if(bg.type != YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "background type not implemented on the device yet");
 	s.bg.has_ibl = bg.ibl; s.bg.shoots_caustic = bg.with_caustic;
 	// light tables: MeshLight::initIs area CDFs, BackgroundLight::init row/column CDFs
@@ -329,6 +338,11 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, upload(c->d_light_accels, laccels.data(), laccels.size(), st));
 	YG_CUDA(c, upload(c->d_lights, c->h_lights.data(), c->h_lights.size(), st));
 	YG_CUDA(c, upload(c->d_light_tables, light_tab.data(), light_tab.size(), st));
+	if(bg.type == YAFGPU_BG_TEXTURE)
+	{
+		YG_CUDA(c, upload(c->d_bg_tex, bg.tex_rgb, (size_t)3 * bg.tex_w * bg.tex_h, st));
+		s.bg.tex = c->d_bg_tex;
+	}
 	cudaEventRecord(c->ev1, st);
 	cudaError_t e = cudaStreamSynchronize(st);
 	cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj);

@@ -6,6 +6,7 @@
 //   BackgroundLight                  /root/reference/src/light/light_background.cc:122-187
 //   Pdf1D::sample/dSample            /root/reference/include/utility/util_sample.h:125-163
 //   ConstantBackground::eval         /root/reference/src/background/background_constant.cc:41-49
+//   TextureBackground::eval          /root/reference/src/background/background_texture.cc:51-88 (+ ImageTexture::getColor, bilinear)
 //   spheremap__/invSpheremap__       /root/reference/include/texture/texture.h:111-140
 #pragma once
 #include "materials.cuh"
@@ -40,11 +41,81 @@ YG_HD V3 invSpheremap(float u, float v)
 	return mk(sintheta * cosphi, sintheta * sinphi, -costheta);
 }
 
-// Background::eval / operator() for the supported types
+// angmap__ texture.h:83-94
+YG_HD void angmap(V3 p, float &u, float &v)
+{
+	float r = p.x * p.x + p.z * p.z;
+	u = v = 0.f;
+	if(r > 0.f)
+	{
+		const float phi_ratio = (float)(YG_M_1_PI * (double)fAcos(p.y));
+		r = phi_ratio / fSqrt(r);
+		u = p.x * r;
+		v = p.z * r;
+	}
+}
+
+// findTextureInterpolationCoordinates texture_image.cc:231-288, branch repeat = true, mirror = false: the two texel columns
+// (rows) a bilinear lookup blends and the blend factor
+YG_HD void texCoordsRepeat(float cf, int res, int &c1, int &c2, float &frac)
+{
+	c1 = ((int)cf) % res;
+	if(cf > 0.f) { c2 = (c1 + 1) % res; frac = cf - (float)((int)cf); }
+	else { c2 = (res - 1) % res; frac = -cf; }
+}
+
+// ImageTexture::getColor(Point3(u, v, 0)) texture_image.cc:75-87 with the factory defaults the upload insists on (clipping "repeat",
+// xrepeat = yrepeat = 1, no mirror / crop / rot90 / adjustments): doMapping :139-158, then bilinearInterpolation :306-330 or
+// noInterpolation :290-304 ("interpolate" = "none")
+YG_HD Col texLookup(const BackgroundDev &bg, float u, float v)
+{
+	float tx = 0.5f * u + 0.5f, ty = 0.5f * (-v) + 0.5f;
+	if(tx > 1.f) tx -= (float)((int)tx); else if(tx < 0.f) tx += (float)(1 - (int)tx);
+	if(ty > 1.f) ty -= (float)((int)ty); else if(ty < 0.f) ty += (float)(1 - (int)ty);
+	const int resx = bg.tex_w, resy = bg.tex_h;
+	const double fx = (double)tx - floor((double)tx), fy = (double)ty - floor((double)ty);
+	int x1, x2, y1, y2; float dx, dy;
+	if(!bg.tex_interp)
+	{
+		texCoordsRepeat((float)((double)(float)resx * fx), resx, x1, x2, dx);
+		texCoordsRepeat((float)((double)(float)resy * fy), resy, y1, y2, dy);
+		const float *t = bg.tex + 3 * ((size_t)y1 * resx + x1);
+		return mkc(t[0], t[1], t[2]);
+	}
+	texCoordsRepeat((float)((double)(float)resx * fx - 0.5), resx, x1, x2, dx);
+	texCoordsRepeat((float)((double)(float)resy * fy - 0.5), resy, y1, y2, dy);
+	const float *t11 = bg.tex + 3 * ((size_t)y1 * resx + x1), *t21 = bg.tex + 3 * ((size_t)y1 * resx + x2);
+	const float *t12 = bg.tex + 3 * ((size_t)y2 * resx + x1), *t22 = bg.tex + 3 * ((size_t)y2 * resx + x2);
+	const float w11 = (1 - dx) * (1 - dy), w12 = (1 - dx) * dy, w21 = dx * (1 - dy), w22 = dx * dy;
+	return ((w11 * mkc(t11[0], t11[1], t11[2]) + w12 * mkc(t12[0], t12[1], t12[2])) + w21 * mkc(t21[0], t21[1], t21[2])) + w22 * mkc(t22[0], t22[1], t22[2]);
+}
+
+// Background::eval / operator(): ConstantBackground (background_constant.cc:41-49), TextureBackground (background_texture.cc:51-88)
 YG_HD Col bgEval(const BackgroundDev &bg, V3 dir)
 {
-	(void)dir;
-	return mkc(bg.color[0], bg.color[1], bg.color[2]); // constant: col * power
+	if(bg.type != YAFGPU_BG_TEXTURE) return mkc(bg.color[0], bg.color[1], bg.color[2]); // constant: col * power
+	float u = 0.f, v = 0.f;
+	if(bg.mapping_angular)
+	{
+		V3 d = dir;
+		d.x = dir.x * bg.cos_r + dir.y * bg.sin_r;
+		d.y = dir.x * -bg.sin_r + dir.y * bg.cos_r;
+		angmap(d, u, v);
+	}
+	else
+	{
+		spheremap(dir, u, v);
+		u = 2.f * u - 1.f;
+		v = 2.f * v - 1.f;
+		u += bg.rotation;
+		if(u > 1.f) u -= 2.f;
+	}
+	Col ret = texLookup(bg, u, v);
+	const float min_component = 1.0e-5f;
+	if(ret.r < min_component) ret.r = min_component;
+	if(ret.g < min_component) ret.g = min_component;
+	if(ret.b < min_component) ret.b = min_component;
+	return bg.power * ret;
 }
 
 // ---- Pdf1D -------------------------------------------------------------------------------------------------------------

@@ -108,7 +108,10 @@ struct BackgroundDev
 {
 	int type; float color[3]; // constant: col*power
 	int has_ibl, shoots_caustic;
-	int mapping_angular; float rotation, power; const float *tex; int tex_w, tex_h, tex_interp;
+	// texture: background_texture.cc:32-88.  rotation = 2 * rot / 360, sin_r/cos_r = fSin/fCos(pi * rotation); tex = RGB float texels
+	// as ImageHandler::getPixel(x, y) returns them, row y at tex + 3 * y * tex_w (device pointer in kernels, host pointer while the
+	// background-light tables are built)
+	int mapping_angular; float rotation, sin_r, cos_r, power; const float *tex; int tex_w, tex_h, tex_interp;
 };
 
 struct IntegratorDev

@@ -154,6 +154,10 @@ class Interface:
         self.cameras[name] = self._take()[0]
         return name
 
+    def createTexture(self, name):
+        self.textures[name] = self._take()[0]
+        return name
+
     def createBackground(self, name):
         self.backgrounds[name] = self._take()[0]
         return name
@@ -188,6 +192,10 @@ class Interface:
             self.setRenderParams()
         w = []
         w.append('<?xml version="1.0"?>\n<scene type="%s">\n\n' % ("triangle" if self.scene_type == 0 else "universal"))
+        for name, p in self.textures.items():
+            w.append('<texture name="%s">\n' % name)
+            for k, tv in p.items(): w.append(self._xml_param(k, tv))
+            w.append("</texture>\n\n")
         for name, (p, e) in self.materials.items():
             w.append('<material name="%s">\n' % name)
             for k, tv in p.items(): w.append(self._xml_param(k, tv))
@@ -341,6 +349,28 @@ class Interface:
             raise NotImplementedError("light type '%s'" % t)
         return l
 
+    def _background_texels(self, name):
+        """Texels of the image texture `name` as ImageHandler::getPixel(x, y) delivers them (SURVEY App. B #12), float32 [h, w, 3].
+        Only Radiance .hdr files (always linear float storage, texture_image.cc:600-606) with the factory's default mapping
+        (clipping "repeat", no repeat/mirror/crop/rot90/adjustments) are taken; everything else is refused."""
+        if name not in self.textures:
+            raise KeyError("unknown texture '%s'" % name)
+        p, g = self.textures[name], self._g
+        if g(p, "type", "") != "image":
+            raise NotImplementedError("texture type '%s' as a background" % g(p, "type", ""))
+        fn = g(p, "filename", "")
+        if not fn.lower().endswith(".hdr"):
+            raise NotImplementedError("background image '%s': only Radiance .hdr is read by this host mirror" % fn)
+        if g(p, "interpolate", "bilinear") not in ("bilinear", "none"):
+            raise NotImplementedError("texture interpolate '%s'" % g(p, "interpolate", ""))
+        defaults = {"xrepeat": 1, "yrepeat": 1, "cropmin_x": 0.0, "cropmin_y": 0.0, "cropmax_x": 1.0, "cropmax_y": 1.0, "rot90": False,
+                    "mirror_x": False, "mirror_y": False, "clipping": "repeat", "adj_mult_factor_red": 1.0, "adj_mult_factor_green": 1.0,
+                    "adj_mult_factor_blue": 1.0, "adj_intensity": 1.0, "adj_contrast": 1.0, "adj_saturation": 1.0, "adj_hue": 0.0, "adj_clamp": False}
+        for k, d in defaults.items():
+            if g(p, k, d) != d:
+                raise NotImplementedError("texture parameter %s=%r is not implemented on the device" % (k, g(p, k, d)))
+        return read_radiance_hdr(fn)
+
     def scene_desc(self):
         """Flatten to capi.SceneDesc.  Returns (desc, keepalive) — keepalive owns the numpy/ctypes buffers."""
         if self.render_params is None:
@@ -469,10 +499,22 @@ class Interface:
         bname = g(rp, "background_name", None)
         if bname is not None and bname in self.backgrounds:
             bp = self.backgrounds[bname]
-            if g(bp, "type", "") != "constant":
-                raise NotImplementedError("background type '%s'" % g(bp, "type", ""))
-            b.type = capi.BG_CONSTANT
-            b.color = capi.F3(*[np.float32(x) for x in g(bp, "color", (0, 0, 0, 1))[:3]])
+            btype = g(bp, "type", "")
+            if btype == "constant":
+                b.type = capi.BG_CONSTANT
+                b.color = capi.F3(*[np.float32(x) for x in g(bp, "color", (0, 0, 0, 1))[:3]])
+            elif btype == "textureback":  # background_texture.cc:90-165
+                b.type = capi.BG_TEXTURE
+                tex = self._background_texels(g(bp, "texture", ""))
+                keep.append(tex)
+                b.tex_rgb, b.tex_w, b.tex_h = tex.ctypes.data_as(capi.pf), tex.shape[1], tex.shape[0]
+                b.tex_interp = int(g(self.textures[g(bp, "texture", "")], "interpolate", "bilinear") != "none")
+                b.mapping_angular = int(g(bp, "mapping", "") in ("probe", "angular"))
+                b.rotation = g(bp, "rotation", 0.0)
+                if g(bp, "smartibl_blur", 0.0) > 0:
+                    raise NotImplementedError("textureback: smartibl_blur (mipmapped IBL) is not implemented on the device")
+            else:
+                raise NotImplementedError("background type '%s'" % btype)
             b.power, b.ibl, b.with_caustic = g(bp, "power", 1.0), int(g(bp, "ibl", False)), int(g(bp, "with_caustic", True))
             if b.ibl:
                 # ConstantBackground::factory creates and adds a "bglight" AFTER all parsed lights (background_constant.cc:69-83)
@@ -480,7 +522,7 @@ class Interface:
                 bl.type, bl.light_enabled, bl.cast_shadows = capi.LIGHT_BACKGROUND, 1, int(g(bp, "cast_shadows", True))
                 bl.samples, bl.object = int(g(bp, "ibl_samples", 16)), -1
                 bl.shoot_caustic, bl.shoot_diffuse = int(g(bp, "with_caustic", True)), int(g(bp, "with_diffuse", True))
-                bl.abs_intersect, bl.clamp_intersect = 0, 0.0
+                bl.abs_intersect, bl.clamp_intersect = 0, (g(bp, "ibl_clamp_sampling", 0.0) if btype == "textureback" else 0.0)
                 lts.append(bl)
                 larr = (capi.Light * len(lts))(*lts)
                 d.lights, d.n_lights = larr, len(lts)
@@ -525,3 +567,67 @@ class Interface:
         it.shadow_bias_auto, it.shadow_bias = int(g(rp, "adv_auto_shadow_bias_enabled", True)), g(rp, "adv_shadow_bias_value", 0.0005)
         it.ray_min_dist_auto, it.ray_min_dist = int(g(rp, "adv_auto_min_raydist_enabled", True)), g(rp, "adv_min_raydist_value", 0.00005)
         return d, keep
+
+
+def read_radiance_hdr(path):
+    """Radiance RGBE reader matching the reference's HdrHandler (src/imagehandler/imagehandler_hdr.cc, imagehandler_util_hdr.h:88-100):
+    texel = mantissa * 2^(e - 136) (0 when e == 0), standard "-Y h +X w" orientation, flat or new-RLE scanlines.  float32 [h, w, 3]."""
+    with open(path, "rb") as fh:
+        data = fh.read()
+    pos, w, h = 0, None, None
+    while True:
+        end = data.index(b"\n", pos)
+        line = data[pos:end].decode("latin-1").strip()
+        pos = end + 1
+        if line.startswith("-Y") or line.startswith("+Y"):
+            t = line.split()
+            if t[0] != "-Y" or t[2] != "+X":
+                raise NotImplementedError("hdr orientation '%s'" % line)
+            h, w = int(t[1]), int(t[3])
+            break
+    buf = np.frombuffer(data, np.uint8, offset=pos)
+    out = np.zeros((h, w, 4), np.uint8)
+    o = 0
+    for y in range(h):
+        if 8 <= w <= 0x7fff and buf[o] == 2 and buf[o + 1] == 2 and (int(buf[o + 2]) << 8 | int(buf[o + 3])) == w:
+            o += 4
+            for ch in range(4):
+                x = 0
+                while x < w:
+                    c = int(buf[o]); o += 1
+                    if c > 128:
+                        out[y, x:x + c - 128, ch] = buf[o]; o += 1; x += c - 128
+                    else:
+                        out[y, x:x + c, ch] = buf[o:o + c]; o += c; x += c
+        else:
+            # flat / old-RLE scanline.  HdrHandler::readOrle copies only the FIRST pixel of such a scanline into the image
+            # (its store loop steps by max_[1] instead of step_[1], imagehandler_hdr.cc:283-288); runs are not expanded here
+            # because nothing but that pixel is visible to the renderer.  Mirror it: the reference's texels are the definition.
+            out[y, 0] = buf[o:o + 4]; o += 4 * w
+    e = out[..., 3].astype(np.int32)
+    f = np.where(e > 0, np.ldexp(np.float32(1.0), e - 136), np.float32(0.0)).astype(np.float32)
+    return np.ascontiguousarray(out[..., :3].astype(np.float32) * f[..., None])
+
+
+def write_radiance_hdr(path, img):
+    """RGBE writer for test fixtures (new-RLE scanline framing); img float32 [h, w, 3]."""
+    img = np.asarray(img, np.float32)
+    h, w, _ = img.shape
+    m = img.max(axis=2)
+    mant, ex = np.frexp(m)
+    scale = np.where(m > 1e-32, mant * 255.9999 / np.where(m > 1e-32, m, 1), 0).astype(np.float32)
+    rgbe = np.zeros((h, w, 4), np.uint8)
+    rgbe[..., :3] = (img * scale[..., None]).astype(np.uint8)
+    rgbe[..., 3] = np.where(m > 1e-32, ex + 128, 0).astype(np.uint8)
+    with open(path, "wb") as fh:
+        fh.write(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n" % (h, w))
+        if not (8 <= w <= 0x7fff):
+            fh.write(rgbe.tobytes())
+            return
+        for y in range(h):   # new-RLE scanline made of literal chunks only (valid, just not compressed)
+            fh.write(bytes([2, 2, w >> 8, w & 255]))
+            for ch in range(4):
+                row = rgbe[y, :, ch].tobytes()
+                for x in range(0, w, 128):
+                    chunk = row[x:x + 128]
+                    fh.write(bytes([len(chunk)])); fh.write(chunk)

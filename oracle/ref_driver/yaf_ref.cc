@@ -55,6 +55,7 @@
 #include "object_geom/object_geom_mesh.h"
 #include "material/material.h"
 #include "light/light.h"
+#include "background/background.h"
 #include "camera/camera.h"
 #include "integrator/integrator.h"
 #include "output/output.h"
@@ -224,6 +225,32 @@ int cmdHits(int argc, char **argv)
 	return 0;
 }
 
+// yaf_ref bgdump <scene.xml> <dirs.bin> <out.bin>: Background::eval for n directions (3 x float32 each) -> n x rgb float32
+int cmdBgDump(int argc, char **argv)
+{
+	if(argc < 5) { fprintf(stderr, "usage: yaf_ref bgdump scene.xml dirs.bin out.bin\n"); return 2; }
+	Loaded l;
+	if(!loadScene(argv[2], l, 1)) return 1;
+	const Background *bg = l.scene->getBackground();
+	if(!bg) { fprintf(stderr, "no background\n"); return 1; }
+	std::ifstream in(argv[3], std::ios::binary);
+	std::vector<char> raw((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+	const size_t n = raw.size() / 12;
+	const float *d = (const float *)raw.data();
+	std::vector<float> out(n * 3);
+	for(size_t i = 0; i < n; ++i)
+	{
+		Ray ray(Point3(0.f, 0.f, 0.f), Vec3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), 0.f, -1.f, 0.f);
+		const Rgb c = bg->eval(ray, false);
+		out[3 * i] = c.r_; out[3 * i + 1] = c.g_; out[3 * i + 2] = c.b_;
+	}
+	FILE *f = fopen(argv[4], "wb");
+	fwrite(out.data(), sizeof(float), out.size(), f);
+	fclose(f);
+	printf("{\"dirs\": %zu}\n", n);
+	return 0;
+}
+
 } // namespace
 
 #include "kat.h"
@@ -235,6 +262,7 @@ int main(int argc, char **argv)
 	if(cmd == "render") return cmdRender(argc, argv);
 	if(cmd == "hits") return cmdHits(argc, argv);
 	if(cmd == "kat") return cmdKat(argc, argv);
+	if(cmd == "bgdump") return cmdBgDump(argc, argv);
 	fprintf(stderr, "unknown command %s\n", argv[1]);
 	return 2;
 }

@@ -31,6 +31,10 @@ CONVERGED = {
 }
 
 
+import os as _os
+ENV_HDR = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden", "env_64x32.hdr")
+
+
 def trace_rays(n, lo, hi, seed=1, tmin=5e-5):
     """Fixed ray set: origins uniform in the (enlarged) scene bound, isotropic directions, seeded."""
     import numpy as np
@@ -88,7 +92,8 @@ TRACE = {
 TRACE_BOUNDS = {"simple": ((-14, -14, -4), (14, 14, 6)), "cornell": ((-1.4, -1.4, -0.4), (1.4, 1.4, 2.4)), "grid64": ((-5, -5, -1), (5, 5, 2))}
 
 
-def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, only_mat=None, **integ):
+def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, only_mat=None,
+                       hdr_env=None, **integ):
     """Every material and light type of the hot path in one small scene (configs 3/4 in miniature): glossy, coated_glossy,
     rough_glass, blend_mat, mirror, glass and shinydiffuse boxes on a ground quad; sun + mesh light + constant-background IBL."""
     from libyafaray_b200.interface import Interface
@@ -142,7 +147,17 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
     y.paramsClearAll(); y.paramsSetString("type", "perspective")
     y.paramsSetPoint("from", 0.5, -7.5, 4.0); y.paramsSetPoint("to", 0.0, 0.8, 0.6); y.paramsSetPoint("up", 0.5, -7.5, 5.0)
     y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3); y.createCamera("cam")
-    y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.35, 0.45, 0.7); y.paramsSetFloat("power", 0.8)
+    if hdr_env:
+        # equirectangular HDR environment ("textureback" + image texture): hdr_env = {"mapping": ..., "rotation": ..., "interpolate": ...}
+        y.paramsClearAll(); y.paramsSetString("type", "image"); y.paramsSetString("filename", ENV_HDR)
+        y.paramsSetString("interpolate", hdr_env.get("interpolate", "bilinear")); y.createTexture("envtex")
+        y.paramsClearAll(); y.paramsSetString("type", "textureback"); y.paramsSetString("texture", "envtex")
+        y.paramsSetString("mapping", hdr_env.get("mapping", "sphere")); y.paramsSetFloat("rotation", hdr_env.get("rotation", 0.0))
+        y.paramsSetFloat("power", hdr_env.get("power", 0.7))
+        if hdr_env.get("clamp"):
+            y.paramsSetFloat("ibl_clamp_sampling", hdr_env["clamp"])
+    else:
+        y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.35, 0.45, 0.7); y.paramsSetFloat("power", 0.8)
     y.paramsSetBool("ibl", ibl); y.paramsSetInt("ibl_samples", 3); y.createBackground("bg")
     y.paramsClearAll(); y.paramsSetString("type", integrator)
     y.paramsSetInt("raydepth", integ.get("raydepth", 4)); y.paramsSetInt("shadowDepth", 3); y.paramsSetBool("transpShad", transp_shad)
@@ -159,6 +174,9 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
 EXACT["cornell_pt_norr"] = lambda: scenes.cornell_box(160, 90, 16, path_samples=2, bounces=6, raydepth=6, rr_min_bounces=99)
 EXACT["zoo_pt_mesh_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, rr_min_bounces=99)
 EXACT["zoo_dl_point_free"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3)
+EXACT["zoo_dl_hdr_ibl"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, sun=False, meshlight=False,
+                                                     hdr_env={"rotation": 40.0})
+EXACT["zoo_dl_hdr_angular"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=2, sun=False, hdr_env={"mapping": "angular", "rotation": 25.0, "interpolate": "none", "clamp": 4.0})
 EXACT["zoo_dl_transpshad"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, transp_shad=True)
 
 # rendered only through the reference front end with the GPU integrator linked in (oracle/_ref/yaf_xml_gpu): adaptive AA is

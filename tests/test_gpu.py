@@ -112,7 +112,7 @@ def test_render_matches_reference_film(ctx, name):
 
 # ---- the drop-in boundary itself: reference XML loader + Scene + ImageFilm with GpuIntegrator linked in ----------------------
 FRONTEND_CASES = ["simple_dl_gauss", "cornell_dl_glass", "cornell_dl_mitchell", "cornell_pt_norr", "zoo_dl_point_free", "zoo_pt_mesh_norr",
-                  "cornell_dl_adaptive"]
+                  "zoo_dl_hdr_ibl", "zoo_dl_hdr_angular", "cornell_dl_adaptive"]
 
 
 @pytest.mark.skipif(ou.gpu_frontend_bin() is None, reason="oracle/_ref/yaf_xml_gpu not built (needs the reference sources)")
