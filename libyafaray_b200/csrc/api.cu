@@ -213,11 +213,13 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	const yafgpu_integrator_desc &in = desc->integrator;
 	if(in.type != YAFGPU_INT_DIRECTLIGHT && in.type != YAFGPU_INT_PATHTRACING) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "integrator type");
 	if(in.bg_transp || in.bg_transp_refract) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bg_transp / bg_transp_refract (alpha output) not implemented on the device");
-	if(in.do_ao) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "do_AO not implemented on the device");
 	if(in.raydepth + 1 + in.bounces + 8 > YG_MAX_ITERS) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "raydepth + bounces too large for the wavefront schedule");
 	s.integ.type = in.type; s.integ.r_depth = in.raydepth; s.integ.tr_shad = in.transp_shad; s.integ.s_depth = in.shadow_depth;
 	s.integ.n_paths = in.path_samples; s.integ.max_bounces = in.bounces; s.integ.rr_min_bounces = in.rr_min_bounces;
 	s.integ.no_recursive = in.no_recursive; s.integ.trace_caustics = in.trace_caustics;
+	s.integ.do_ao = in.do_ao; s.integ.ao_samples = in.ao_samples; s.integ.ao_dist = in.ao_distance;
+	for(int k = 0; k < 3; ++k) s.integ.ao_col[k] = in.ao_color[k];
+	if(in.do_ao && in.ao_samples < 1) return setErr(c, YAFGPU_ERR_INVALID, "AO_samples must be positive");
 	s.integ.shadow_bias = in.shadow_bias; s.integ.shadow_bias_auto = in.shadow_bias_auto;
 	s.integ.ray_min_dist = in.ray_min_dist; s.integ.ray_min_dist_auto = in.ray_min_dist_auto;
 	s.integ.aa_light_sample_multiplier = desc->film.aa_light_sample_multiplier;

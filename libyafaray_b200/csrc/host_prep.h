@@ -370,7 +370,6 @@ inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
 	vup = vup / (float)c.resy;
 	vright = vright / (float)c.resx;
 	st3(d.pos, pos); st3(d.vright, vright); st3(d.vup, vup); st3(d.vto, vto);
-	if(c.aperture != 0.f && (c.bokeh_type != YAFGPU_BK_DISK1)) { err = "camera: only bokeh_type disk1 is implemented on the device"; return false; }
 	d.bokeh_type = c.bokeh_type; d.bokeh_bias = c.bokeh_bias; d.n_ls = 0;
 	int ns = c.bokeh_type;
 	if(ns >= 3 && ns <= 6)

@@ -113,6 +113,44 @@ __device__ __forceinline__ void samplePos(const WaveParams &wp, const SlotInfo &
 }
 
 // ---- K2: camera rays ---------------------------------------------------------------------------------------------------
+__device__ void shirleyDisk(float r_1, float r_2, float &u, float &v);
+
+// PerspectiveCamera::biasDist / sampleTsd / getLensUv camera_perspective.cc:76-128
+__device__ __forceinline__ float biasDist(int bias, float r)
+{
+	if(bias == YAFGPU_BB_CENTER) return fSqrt(fSqrt(r) * r);
+	if(bias == YAFGPU_BB_EDGE) return fSqrt((float)1.0 - r * r);
+	return fSqrt(r);
+}
+__device__ __forceinline__ void lensUv(const CameraDev &c, float r_1, float r_2, float &u, float &v)
+{
+	switch(c.bokeh_type)
+	{
+		case YAFGPU_BK_TRI: case YAFGPU_BK_SQR: case YAFGPU_BK_PENTA: case YAFGPU_BK_HEXA:
+		{
+			const float fn = (float)c.bokeh_type;
+			int idx = (int)(r_1 * fn);
+			r_1 = (r_1 - ((float)idx) / fn) * fn;
+			r_1 = biasDist(c.bokeh_bias, r_1);
+			const float b_1 = r_1 * r_2, b_0 = r_1 - b_1;
+			idx <<= 1;
+			u = c.ls[idx] * b_0 + c.ls[idx + 2] * b_1;
+			v = c.ls[idx + 1] * b_0 + c.ls[idx + 3] * b_1;
+			break;
+		}
+		case YAFGPU_BK_DISK2: case YAFGPU_BK_RING:
+		{
+			const float w = (float)YG_M_2PI * r_2;
+			if(c.bokeh_type == YAFGPU_BK_RING) r_1 = fSqrt((float)0.707106781 + (float)0.292893218);
+			else r_1 = biasDist(c.bokeh_bias, r_1);
+			u = r_1 * fCos(w);
+			v = r_1 * fSin(w);
+			break;
+		}
+		default: shirleyDisk(r_1, r_2, u, v);
+	}
+}
+
 // shirleyDisk__ util_sample.h (concentric map) used by the default bokeh
 __device__ void shirleyDisk(float r_1, float r_2, float &u, float &v)
 {
@@ -154,7 +192,7 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, cons
 			hv.setStart((uint32_t)wp.pass_offs + si.sampling_offs + (uint32_t)si.sample);
 			const float lu = hu.getNext(), lv = hv.getNext();
 			float u, v;
-			shirleyDisk(lu, lv, u, v); // bokeh disk1 (other bokeh types are refused at upload)
+			lensUv(c, lu, lv, u, v);
 			const V3 li = ldv(c.dof_rt) * u + ldv(c.dof_up) * v;
 			from = from + li;
 			dir = normalize((dir * c.dof_distance) - li);
@@ -465,6 +503,27 @@ __global__ void __launch_bounds__(128, YG_SHADE_MINB) k_shade(const __grid_const
 			if(bsdfs & BsdfDiffuse)
 			{	// estimateAllDirectLight integrator_montecarlo.cc:47-60
 				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation<MT>(cx, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
+				if(ig.type == YAFGPU_INT_DIRECTLIGHT && ig.do_ao)
+				{	// MonteCarloIntegrator::sampleAmbientOcclusion integrator_montecarlo.cc:1030-1088 (only DirectLight calls it, :145)
+					int n = ig.ao_samples;
+					if(ray_division > 1) n = max(1, n / ray_division);
+					const unsigned offs = (unsigned)n * (unsigned)si.pixel_sample + si.sampling_offs;
+					Halton2 hal_2; HaltonB<3> hal_3;
+					hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
+					const float ao_tmin = ig.shadow_bias_auto ? ig.shadow_bias * fmaxf(1.f, length(sp.p)) : ig.shadow_bias;
+					const Col ao_col = mkc(ig.ao_col[0], ig.ao_col[1], ig.ao_col[2]);
+					for(int k = 0; k < n; ++k)
+					{
+						float s_1 = hal_2.getNext(), s_2 = hal_3.getNext();
+						if(ray_division > 1) { s_1 = addMod1(s_1, dcv.x); s_2 = addMod1(s_2, dcv.y); }
+						BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfDiffuse | BsdfReflect; s.pdf = 0.f; s.sampled = BsdfNone;
+						float w = 0.f; V3 adir = mk(0.f);
+						const Col surf_col = matSample<MT>(sc, m, sp, wo, adir, s, w);
+						if(m.bsdf_flags & BsdfEmit) accAdd(acc, slot, W * ((matEmit<MT>(sc, m, sp, wo, true) * s.pdf) / (float)n));
+						const float cosv = fabsf(dot(sp.n, adir));
+						pushShadow(cx, slot, sp.p, ao_tmin, adir, ig.ao_dist, W * ((((ao_col * surf_col) * cosv) * w) / (float)n));
+					}
+				}
 			}
 			if(ig.type == YAFGPU_INT_PATHTRACING)
 			{	// integrator_path_tracer.cc:174-298: first path segment, sampled here; the rest of each path is a TASK_PATH chain

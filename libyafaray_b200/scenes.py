@@ -77,7 +77,7 @@ def _vol_none(y):
 
 def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2,
                 light_samples=4, integrator="pathtracing", glass=True, light_power=30.0, filter_type="box",
-                aa_passes=1, extra_point_light=False, transp_shad=False, no_recursive=False, **render_extra):
+                aa_passes=1, extra_point_light=False, transp_shad=False, no_recursive=False, lens=None, **render_extra):
     """BASELINE config 2: Cornell box, PathIntegrator, area light, ShinyDiffuse + Glass (36 triangles)."""
     y = Interface()
     y.startScene(0)
@@ -133,6 +133,9 @@ def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, ray
     y.paramsSetString("type", "perspective")
     y.paramsSetPoint("from", 0.0, -3.9, 1.0); y.paramsSetPoint("to", 0.0, 0.0, 1.0); y.paramsSetPoint("up", 0.0, -3.9, 2.0)
     y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.1)
+    for k, v in (lens or {}).items():   # thin-lens parameters: aperture, dof_distance, bokeh_type, bokeh_bias, bokeh_rotation
+        if isinstance(v, str): y.paramsSetString(k, v)
+        else: y.paramsSetFloat(k, float(v))
     y.createCamera("cam")
 
     y.paramsClearAll()

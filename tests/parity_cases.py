@@ -164,6 +164,9 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
     if integrator == "pathtracing":
         y.paramsSetInt("path_samples", integ.get("path_samples", 2)); y.paramsSetInt("bounces", integ.get("bounces", 4))
         y.paramsSetInt("russian_roulette_min_bounces", integ.get("rr_min_bounces", 1))
+    if integ.get("do_AO"):
+        y.paramsSetBool("do_AO", True); y.paramsSetInt("AO_samples", integ.get("AO_samples", 8)); y.paramsSetFloat("AO_distance", integ.get("AO_distance", 1.0))
+        y.paramsSetColor("AO_color", 0.9, 0.95, 1.0)
     y.createIntegrator("pt")
     scenes._vol_none(y)
     scenes.render_block(y, width, height, spp)
@@ -177,6 +180,10 @@ EXACT["zoo_dl_point_free"] = lambda: material_zoo_scene(96, 54, 2, integrator="d
 EXACT["zoo_dl_hdr_ibl"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, sun=False, meshlight=False,
                                                      hdr_env={"rotation": 40.0})
 EXACT["zoo_dl_hdr_angular"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=2, sun=False, hdr_env={"mapping": "angular", "rotation": 25.0, "interpolate": "none", "clamp": 4.0})
+for _bk, _bias, _rot in (("disk1", "uniform", 0.0), ("disk2", "edge", 0.0), ("ring", "uniform", 0.0), ("triangle", "center", 15.0), ("hexagon", "uniform", 40.0)):
+    EXACT["cornell_dl_dof_" + _bk] = (lambda bk=_bk, bias=_bias, rot=_rot: scenes.cornell_box(96, 54, 4, integrator="directlighting", lens={
+        "aperture": 0.12, "dof_distance": 3.2, "bokeh_type": bk, "bokeh_bias": bias, "bokeh_rotation": rot}))
+EXACT["zoo_dl_ao"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, sun=False, do_AO=True, AO_samples=4, AO_distance=1.5)
 EXACT["zoo_dl_transpshad"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, transp_shad=True)
 
 # rendered only through the reference front end with the GPU integrator linked in (oracle/_ref/yaf_xml_gpu): adaptive AA is
