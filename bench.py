@@ -171,6 +171,8 @@ def gpu_arm(args, rank, world, local_rank):
     y = build_scene(args.width, args.height, PASS_SPP)
     desc, keep = y.scene_desc()
     ctx = Context(local_rank)
+    if args.wave_size:
+        ctx.set_option("wave_size", args.wave_size)
     ctx.upload(desc, keep)
     S = args.spp_per_step * world
     n_chunks = max(1, PASS_SPP // S)
@@ -227,10 +229,10 @@ def gpu_arm(args, rank, world, local_rank):
     line = {"metric": "Mrays/s", "value": rays / sec / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "samples_per_s": samples / sec, "rays_per_camera_sample": rays / max(1.0, samples), "config": config_dict(args, world),
-            "gpu_launches": int(launches), "clocks": sampler.summary()}
+            "gpu_launches": int(launches), "clocks": sampler.summary(), "waves_per_step": st["waves"] / max(1, args.steps)}
 
     # ---- end-to-end through the public call with host buffers (every step: upload + BVH build, clear, render, film D2H) ----
-    host_film = np.empty((args.height, args.width, 5), np.float32)
+    host_film = torch.empty((args.height, args.width, 5), dtype=torch.float32, pin_memory=True)  # pinned: the D2H of the film runs at PCIe speed
     g = desc.geometry
     h2d = (g.n_points * 12 + g.n_normals * 12 + g.n_uv * 8 + g.n_tris * (12 * 3 + 8) + desc.n_materials * C_sizeof(capi.Material) + desc.n_lights * C_sizeof(capi.Light))
     e2e_steps = max(2, min(args.steps, 8))
@@ -240,7 +242,7 @@ def gpu_arm(args, rank, world, local_rank):
         films.pop(id(ctx), None)  # the film accumulators were re-allocated by the upload
         ctx.film_clear()
         step(i)
-        capi.lib.yafgpu_read_film(ctx.h, host_film.ctypes.data)
+        capi.lib.yafgpu_read_film(ctx.h, host_film.data_ptr())
     e2e_step(0)
     ctx.reset_stats()
     if world > 1:
@@ -256,7 +258,7 @@ def gpu_arm(args, rank, world, local_rank):
     if world > 1:
         t = torch.tensor([t_e2e], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); t_e2e = float(t[0])
         t = torch.tensor([r2], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.SUM); r2 = float(t[0])
-    line["e2e"] = {"value": r2 / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(host_film.nbytes),
+    line["e2e"] = {"value": r2 / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(host_film.numel() * 4),
                    "ms_per_step": t_e2e / e2e_steps * 1e3, "timing": "host wall clock around upload+clear+render+read_film, max over ranks"}
 
     if rank == 0:
@@ -266,6 +268,8 @@ def gpu_arm(args, rank, world, local_rank):
 
         def side_run(flags):
             c2 = Context(local_rank, flags)
+            if args.wave_size:
+                c2.set_option("wave_size", args.wave_size)
             c2.upload(desc, keep)
             c2.film_clear()
             step0(0, c2)
@@ -359,6 +363,7 @@ def main():
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--wave-size", type=int, default=0, help="camera samples per wavefront wave (0 = library default)")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":

@@ -414,7 +414,7 @@ int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
 /* Update per-pass AA multipliers between passes (integrator_tiled.cc:216-218). */
 int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
 
-/* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave, default 2^20),
+/* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^23, limited to a quarter of the free device memory),
  * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "ray_regeneration" (1: the wavefront
  * traversal kernels use the warp-persistent schedule with ray regeneration that yafgpu_trace always uses; default 0). */
 int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);

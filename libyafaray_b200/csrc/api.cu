@@ -304,7 +304,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	if(g.n_tris > 0)
 	{
 		BvhBuildInput bi; bi.n_tris = (int)g.n_tris; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx; bi.tri_mat = c->d_tri_mat;
-		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng;
+		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng; bi.leaf_max = c->leaf_max;
 		BvhBuildOutput bo;
 		cudaError_t e = buildBvh(bi, bo, st);
 		if(e != cudaSuccess) { cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj); return cudaErr(c, e, "buildBvh"); }
@@ -484,6 +484,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	if(!c || !name) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
 	const std::string n(name);
 	if(n == "wave_size") { if(value < 1024 || value > (1 << 24)) return setErr(c, YAFGPU_ERR_INVALID, "wave_size out of range"); c->wave_cap_override = (int)value; return YAFGPU_OK; }
+	if(n == "leaf_size") { if(value < 1 || value > 8) return setErr(c, YAFGPU_ERR_INVALID, "leaf_size must be 1..8"); c->leaf_max = (int)value; return YAFGPU_OK; }
 	if(n == "ray_regeneration") { c->ray_regeneration = value != 0; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);

@@ -98,7 +98,8 @@ __device__ __forceinline__ int deltaFn(const unsigned long long *__restrict__ ke
 }
 
 // one thread per internal node i in [0, n-2]; children: internal k -> k, leaf k -> (n-1)+k in the parent array
-__global__ void k_hierarchy(int n, const unsigned long long *__restrict__ keys, int *__restrict__ left, int *__restrict__ right, int *__restrict__ parent)
+__global__ void k_hierarchy(int n, const unsigned long long *__restrict__ keys, int *__restrict__ left, int *__restrict__ right, int *__restrict__ parent,
+                            int2 *__restrict__ range)
 {
 	int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if(i >= n - 1) return;
@@ -123,6 +124,7 @@ __global__ void k_hierarchy(int n, const unsigned long long *__restrict__ keys, 
 	int lc = (lo == gamma) ? (n - 1) + gamma : gamma;
 	int rc = (hi == gamma + 1) ? (n - 1) + gamma + 1 : gamma + 1;
 	left[i] = lc; right[i] = rc;
+	range[i] = make_int2(lo, hi - lo + 1); // the Morton-ordered triangles this node covers
 	parent[lc] = i; parent[rc] = i;
 	if(i == 0) parent[0] = -1;
 }
@@ -160,10 +162,18 @@ __global__ void k_refit(int n, const int *__restrict__ vals, const float4 *__res
 	}
 }
 
-__device__ __forceinline__ int encodeChild(int c, int n) { return c < n - 1 ? c : ~(((c - (n - 1)) << 3) | 0); }
+// child link: inner node index, or ~((first << 3) | (count - 1)) for a leaf of `count` consecutive TriAccel records.  A subtree
+// that covers at most `leaf_max` triangles is collapsed into one leaf (its box is the subtree's box; the inner nodes below it stay
+// in the array, unreferenced): fewer 64-byte node visits for a few more 48-byte triangle tests.
+__device__ __forceinline__ int encodeChild(int c, int n, const int2 *__restrict__ range, int leaf_max)
+{
+	if(c >= n - 1) return ~(((c - (n - 1)) << 3) | 0);
+	const int2 r = range[c];
+	return r.y <= leaf_max ? ~((r.x << 3) | (r.y - 1)) : c;
+}
 
 __global__ void k_emit_nodes(int n, const int *__restrict__ left, const int *__restrict__ right, const float4 *__restrict__ nmin,
-                             const float4 *__restrict__ nmax, BvhNode *__restrict__ nodes)
+                             const float4 *__restrict__ nmax, const int2 *__restrict__ range, int leaf_max, BvhNode *__restrict__ nodes)
 {
 	int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if(i >= n - 1) return;
@@ -173,7 +183,7 @@ __global__ void k_emit_nodes(int n, const int *__restrict__ left, const int *__r
 	nd.n0 = make_float4(a.x, a.y, a.z, b.x);
 	nd.n1 = make_float4(b.y, b.z, c.x, c.y);
 	nd.n2 = make_float4(c.z, d.x, d.y, d.z);
-	nd.n3 = make_float4(__int_as_float(encodeChild(lc, n)), __int_as_float(encodeChild(rc, n)), 0.f, 0.f);
+	nd.n3 = make_float4(__int_as_float(encodeChild(lc, n, range, leaf_max)), __int_as_float(encodeChild(rc, n, range, leaf_max)), 0.f, 0.f);
 	nodes[i] = nd;
 }
 
@@ -197,6 +207,8 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 	float4 *v0e = nullptr, *e1i = nullptr, *e2f = nullptr, *bmin = nullptr, *bmax = nullptr, *nmin = nullptr, *nmax = nullptr;
 	int *scene_bound = nullptr, *vals = nullptr, *vals_s = nullptr, *left = nullptr, *right = nullptr, *parent = nullptr, *counters = nullptr;
 	unsigned long long *keys = nullptr, *keys_s = nullptr;
+	int2 *range = nullptr;
+	const int leaf_max = in.leaf_max < 1 ? 1 : (in.leaf_max > 8 ? 8 : in.leaf_max);
 	void *cub_tmp = nullptr; size_t cub_bytes = 0;
 	out.nodes = nullptr; out.tris = nullptr; out.n_nodes = 0;
 
@@ -230,16 +242,17 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 		CK(cudaMalloc(&left, sizeof(int) * (n - 1))); CK(cudaMalloc(&right, sizeof(int) * (n - 1)));
 		CK(cudaMalloc(&parent, sizeof(int) * (2 * n - 1))); CK(cudaMalloc(&counters, sizeof(int) * (n - 1)));
 		CK(cudaMalloc(&nmin, sizeof(float4) * (2 * n - 1))); CK(cudaMalloc(&nmax, sizeof(float4) * (2 * n - 1)));
+		CK(cudaMalloc(&range, sizeof(int2) * (n - 1)));
 		CK(cudaMemsetAsync(counters, 0, sizeof(int) * (n - 1), stream));
-		k_hierarchy<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, keys_s, left, right, parent);
+		k_hierarchy<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, keys_s, left, right, parent, range);
 		CK(cudaGetLastError());
 		k_refit<<<G, B, 0, stream>>>(n, vals_s, bmin, bmax, left, right, parent, nmin, nmax, counters);
 		CK(cudaGetLastError());
 		CK(cudaMalloc(&out.nodes, sizeof(BvhNode) * (n - 1)));
-		k_emit_nodes<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, left, right, nmin, nmax, out.nodes);
+		k_emit_nodes<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, left, right, nmin, nmax, range, leaf_max, out.nodes);
 		CK(cudaGetLastError());
 		out.n_nodes = n - 1;
-		out.root = 0;
+		out.root = n <= leaf_max ? ~((0 << 3) | (n - 1)) : 0;
 	}
 	else
 	{
@@ -255,7 +268,7 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 fail:
 	cudaFree(v0e); cudaFree(e1i); cudaFree(e2f); cudaFree(bmin); cudaFree(bmax); cudaFree(nmin); cudaFree(nmax);
 	cudaFree(scene_bound); cudaFree(vals); cudaFree(vals_s); cudaFree(left); cudaFree(right); cudaFree(parent); cudaFree(counters);
-	cudaFree(keys); cudaFree(keys_s); cudaFree(cub_tmp);
+	cudaFree(keys); cudaFree(keys_s); cudaFree(cub_tmp); cudaFree(range);
 	if(err != cudaSuccess) { cudaFree(out.nodes); cudaFree(out.tris); out.nodes = nullptr; out.tris = nullptr; }
 	return err;
 }

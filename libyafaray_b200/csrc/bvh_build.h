@@ -12,6 +12,7 @@ struct BvhBuildInput
 	const int *tri_mat;           // device
 	const unsigned *mat_triflags; // device, per material TRI_* flags
 	float *tri_ng_out;            // device, 3 per triangle: geometric normals (written)
+	int leaf_max = 1;             // subtrees of at most this many triangles become one leaf (1..8)
 };
 
 struct BvhBuildOutput

@@ -1001,8 +1001,27 @@ int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 	const int max_iters = std::min(YG_MAX_ITERS, rdepth + 1 + (ig.type == YAFGPU_INT_PATHTRACING ? ig.max_bounces + 1 : 0));
 
 	// wave sizing: a wave covers `n_pix_w` pixels x `n_smp_w` samples
-	const int wave_cap = c->wave_cap_override > 0 ? c->wave_cap_override : (1 << 20);
 	const int fan = c->task_fan_override > 0 ? c->task_fan_override : 8;
+	int wave_cap = c->wave_cap_override;
+	if(wave_cap <= 0)
+	{	// Default: as large as a quarter of the free HBM allows, at most 2^23 camera samples.  Large waves amortise the thin tail
+		// iterations of a wave (a few thousand tasks per launch at depth 8+): Cornell bench 3.57 -> 4.35 Grays/s from 2^20 to 2^23
+		// (profiles/r1_wave_size.md).  Bytes per camera sample: fan x (2 task queues x 112 B + 48 B shadow record) + 16 B.
+		const size_t pass_samples = n_pix * (size_t)(s_end - s_begin);
+		Wavefront &w0 = c->wf;
+		int want = 1 << 23;
+		while(want > (1 << 16) && (size_t)(want >> 1) >= pass_samples) want >>= 1; // no larger than this call needs
+		if(w0.allocated && w0.wave_cap >= want) wave_cap = w0.wave_cap;               // keep what is there
+		else
+		{
+			size_t free_b = 0, total_b = 0;
+			cudaMemGetInfo(&free_b, &total_b);
+			if(w0.allocated) free_b += (size_t)w0.wave_cap * ((size_t)fan * (2 * 112 + 48) + 16);
+			const size_t per_sample = (size_t)fan * (2 * 112 + 48) + 16;
+			wave_cap = want;
+			while(wave_cap > (1 << 16) && (size_t)wave_cap * per_sample > free_b / 4) wave_cap >>= 1;
+		}
+	}
 	cudaError_t e = allocWavefront(c, wave_cap, wave_cap * fan, wave_cap * fan);
 	if(e != cudaSuccess) return cudaErr(c, e, "wavefront allocation");
 	Wavefront &w = c->wf;

@@ -40,7 +40,7 @@ def main(csv_path, bench_path, tag):
     # one bench step = the launches up to the n-th k_film_add (n = waves per step)
     bench = json.loads(open(bench_path).read().strip().splitlines()[-1])
     samples_step = bench["config"]["camera_samples_per_step"]
-    waves = -(-samples_step // (1 << 20))
+    waves = int(round(bench.get("waves_per_step", -(-samples_step // (1 << 20)))))
     step, films = [], 0
     for i, L in launches.items():
         if "k_tri_setup" in L["name"] or "k_morton" in L["name"] or "cub::" in L["name"] or "k_hierarchy" in L["name"] or "k_refit" in L["name"] \

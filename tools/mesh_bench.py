@@ -12,9 +12,12 @@ spp = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 flags = capi.FLAG_TIME_STAGES | (capi.FLAG_COUNT_TRAVERSAL if "count" in sys.argv else 0)
 t0 = time.time(); y = scenes.procedural_mesh(n_tris, 1920, 1080, 16); desc, keep = y.scene_desc(); t_host = time.time() - t0
 ctx = Context(0, flags)
+for a in sys.argv:
+    if a.startswith("leaf="):
+        ctx.set_option("leaf_size", int(a[5:]))
 t0 = time.time(); ctx.upload(desc, keep); t_up = time.time() - t0
 st = ctx.stats()
-out = {"n_tris": int(desc.geometry.n_tris), "host_scene_s": t_host, "upload_s": t_up, "bvh_build_ms": st["ms_build"], "bvh_nodes": st["bvh_nodes"],
+out = {"argv": sys.argv[1:], "n_tris": int(desc.geometry.n_tris), "host_scene_s": t_host, "upload_s": t_up, "bvh_build_ms": st["ms_build"], "bvh_nodes": st["bvh_nodes"],
        "bvh_mb": st["bvh_bytes"] / 1e6, "tri_mb": st["tri_bytes"] / 1e6}
 # incoherent rays: origins on a plane above the terrain, cosine-ish random directions downwards + random points/dirs inside the bound
 n = 1 << 24
@@ -40,11 +43,11 @@ for mode, key in ((capi.TRACE_CLOSEST, "incoherent_closest"), (capi.TRACE_SHADOW
                 "nodes_per_ray": s2["nodes_visited"] / (reps * n) if s2["nodes_visited"] else None, "tris_per_ray": s2["tris_tested"] / (reps * n) if s2["tris_tested"] else None}
 del rays, hits, o, d
 # wavefront render
-ctx.film_clear(); ctx.render_pass(16, 0, sample_begin=0, sample_end=1); ctx.reset_stats()
-t0 = time.time(); ctx.render_pass(16, 0, sample_begin=1, sample_end=1 + spp); ctx.sync(); t = time.time() - t0
+ctx.film_clear(); ctx.render_pass(16, 0, sample_begin=0, sample_end=spp); ctx.sync(); ctx.reset_stats()   # warm-up: same wave size as the timed call
+t0 = time.time(); ctx.render_pass(16, 0, sample_begin=spp, sample_end=2 * spp); ctx.sync(); t = time.time() - t0
 s = ctx.stats()
 rays_n = s["rays_camera"] + s["rays_extension"] + s["rays_shadow"] + s["rays_shadow_transp"]
-out["render"] = {"spp": spp, "seconds": t, "mrays_s": rays_n / t / 1e6, "samples_s": s["camera_samples"] / t, "rays_per_sample": rays_n / max(1, s["camera_samples"]),
+out["render"] = {"spp": spp, "seconds": t, "mrays_s": rays_n / t / 1e6, "mrays_s_device": rays_n / max(1e-9, s["ms_total"]) / 1e3, "samples_s": s["camera_samples"] / t, "rays_per_sample": rays_n / max(1, s["camera_samples"]),
                  "ms_trace": s["ms_trace"], "ms_shadow": s["ms_shadow"], "ms_shade": s["ms_shade"], "ms_total": s["ms_total"], "waves": s["waves"], "retries": s["wave_retries"],
                  "rays_ext": s["rays_extension"], "rays_shadow": s["rays_shadow"],
                  "nodes_per_ray": s["nodes_visited"] / max(1, rays_n) if s["nodes_visited"] else None, "tris_per_ray": s["tris_tested"] / max(1, rays_n) if s["tris_tested"] else None}
