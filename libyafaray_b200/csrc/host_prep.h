@@ -67,6 +67,8 @@ inline bool prepShinyDiffuse(const yafgpu_material &m, MatDev &d, std::string &e
 		d.bsdf_flags |= BsdfDiffuse | BsdfReflect;
 		d.c_flags[d.n_bsdf] = BsdfDiffuse | BsdfReflect; d.c_index[d.n_bsdf] = 3; ++d.n_bsdf;
 	}
+	// pure Lambert/Oren-Nayar surface: gets its own shading kernel (materials.cuh YG_MAT_SD_LAMBERT); same arithmetic, fewer branches
+	if(d.n_bsdf == 1 && d.is_diffuse && !d.has_fresnel) d.type = YG_MAT_SD_LAMBERT;
 	(void)err;
 	return true;
 }
@@ -156,7 +158,7 @@ inline unsigned triFlagsOf(const MatDev &d)
 	if(d.visibility == YAFGPU_VIS_NORMAL || d.visibility == YAFGPU_VIS_NO_SHADOWS) f |= TRI_VIS_CAMERA;
 	if(d.visibility == YAFGPU_VIS_NORMAL || d.visibility == YAFGPU_VIS_SHADOW_ONLY) f |= TRI_VIS_SHADOW;
 	bool transp = false;
-	if(d.type == YAFGPU_MAT_SHINYDIFFUSE) transp = d.is_transparent;          // material_shiny_diffuse.h:53
+	if(d.type == YAFGPU_MAT_SHINYDIFFUSE || d.type == YG_MAT_SD_LAMBERT) transp = d.is_transparent; // material_shiny_diffuse.h:53
 	if(d.type == YAFGPU_MAT_GLASS || d.type == YAFGPU_MAT_ROUGH_GLASS) transp = d.fake_shadow; // material_glass.h:40
 	if(d.type == YAFGPU_MAT_BLEND) transp = d.is_transparent; // set by finishBlend (material_blend.cc:332-335)
 	if(transp) f |= TRI_TRANSPARENT;
@@ -196,7 +198,7 @@ inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
 
 inline bool matIsTransparent(const MatDev &d)
 {
-	if(d.type == YAFGPU_MAT_SHINYDIFFUSE) return d.is_transparent;
+	if(d.type == YAFGPU_MAT_SHINYDIFFUSE || d.type == YG_MAT_SD_LAMBERT) return d.is_transparent;
 	if(d.type == YAFGPU_MAT_GLASS || d.type == YAFGPU_MAT_ROUGH_GLASS) return d.fake_shadow;
 	return false;
 }

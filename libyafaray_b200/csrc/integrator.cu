@@ -944,7 +944,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		const int *ends = w.hist + YG_MAX_BUCKETS; // the scatter kernel advanced every bucket's offset to its end
 #define YG_SHADE(T) if(c->type_b1[T] >= c->type_b0[T]) { k_shade<T><<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, c->type_b0[T], c->type_b1[T]); ++n_launch; }
 		YG_SHADE(YAFGPU_MAT_SHINYDIFFUSE) YG_SHADE(YAFGPU_MAT_GLOSSY) YG_SHADE(YAFGPU_MAT_COATED_GLOSSY) YG_SHADE(YAFGPU_MAT_GLASS) YG_SHADE(YAFGPU_MAT_ROUGH_GLASS)
-		YG_SHADE(YAFGPU_MAT_BLEND) YG_SHADE(YAFGPU_MAT_MIRROR) YG_SHADE(YAFGPU_MAT_NULL) YG_SHADE(YAFGPU_MAT_LIGHT)
+		YG_SHADE(YAFGPU_MAT_BLEND) YG_SHADE(YAFGPU_MAT_MIRROR) YG_SHADE(YAFGPU_MAT_NULL) YG_SHADE(YAFGPU_MAT_LIGHT) YG_SHADE(YG_MAT_SD_LAMBERT)
 #undef YG_SHADE
 		k_shade<MT_MISS><<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
 		mark();

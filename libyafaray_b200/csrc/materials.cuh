@@ -65,11 +65,13 @@ YG_D void getSurface(const SceneDev &sc, int tri, float b1, float b2, V3 hit, Su
 }
 
 // ---- helpers --------------------------------------------------------------------------------------------------------
+#define YG_SDL(MT) ((MT) == YG_MAT_SD_LAMBERT) /* compile-time: the kernel of the diffuse-only shinydiffuse specialisation */
 
 // ShinyDiffuseMaterial::getFresnel material_shiny_diffuse.cc:120-148
+template<int MT>
 YG_D float sdFresnel(const MatDev &m, V3 wo, V3 n)
 {
-	if(!m.has_fresnel) return 1.f;
+	if(YG_SDL(MT) || !m.has_fresnel) return 1.f;
 	const V3 N = (dot(wo, n) < 0.f) ? -n : n;
 	const float c = dot(wo, N);
 	float g = m.ior_squared + c * c - 1.f;
@@ -88,13 +90,18 @@ YG_D void sdAccumulate(const float *component, float *accum, float kr)
 	acc *= 1.f - component[2];
 	accum[3] = component[3] * acc;
 }
+template<int MT>
 YG_D void sdComponents(const MatDev &m, float *c)
 {	// initBsdf: memset 0 then getComponents without nodes (:98-118,164-183)
-	c[0] = m.is_mirror ? m.mirror_strength : 0.f;
-	c[1] = m.is_transparent ? m.transparency_strength : 0.f;
-	c[2] = m.is_translucent ? m.translucency_strength : 0.f;
-	c[3] = m.is_diffuse ? m.diffuse_strength : 0.f;
+	c[0] = (!YG_SDL(MT) && m.is_mirror) ? m.mirror_strength : 0.f;
+	c[1] = (!YG_SDL(MT) && m.is_transparent) ? m.transparency_strength : 0.f;
+	c[2] = (!YG_SDL(MT) && m.is_translucent) ? m.translucency_strength : 0.f;
+	c[3] = (YG_SDL(MT) || m.is_diffuse) ? m.diffuse_strength : 0.f;
 }
+// component table of config() (:46-92); constants for the Lambert specialisation
+template<int MT> YG_D int sdNBsdf(const MatDev &m) { return YG_SDL(MT) ? 1 : m.n_bsdf; }
+template<int MT> YG_D unsigned sdCFlags(const MatDev &m, int i) { return YG_SDL(MT) ? (unsigned)(BsdfDiffuse | BsdfReflect) : m.c_flags[i]; }
+template<int MT> YG_D int sdCIndex(const MatDev &m, int i) { return YG_SDL(MT) ? 3 : m.c_index[i]; }
 // orenNayar (same code in shiny diffuse :204-241, glossy :74-111, coated glossy :92-128)
 YG_D float orenNayar(float oren_a, float oren_b, V3 wi, V3 wo, V3 n)
 {
@@ -247,7 +254,15 @@ YG_D V3 glassNormal(const SurfPt &sp, V3 wo, bool outside)
 }
 
 // MT >= 0: the material type is a compile-time constant (per-material shading kernels, integrator.cu); MT < 0: read it from the record
-template<int MT> YG_D int mtypeOf(const MatDev &m) { return MT >= 0 ? MT : m.type; }
+// YG_MAT_SD_LAMBERT (internal, host_prep.h): a shinydiffuse material whose only component is diffuse reflection and which has no
+// Fresnel term.  It runs the SAME shinydiffuse code, but the component flags are compile-time constants in its kernel, so the
+// component loops, the Fresnel/accumulate arithmetic on exact zeros and ones, and the dynamically indexed scratch arrays fold away.
+template<int MT> YG_D int mtypeOf(const MatDev &m)
+{
+	const int t = MT >= 0 ? MT : m.type;
+	return t == YG_MAT_SD_LAMBERT ? YAFGPU_MAT_SHINYDIFFUSE : t;
+}
+
 
 template<int MT>
 YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdfs)
@@ -259,11 +274,11 @@ YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdf
 			const float cos_ng_wo = dot(sp.ng, wo), cos_ng_wl = dot(sp.ng, wl);
 			const V3 n = faceForward(sp.ng, sp.n, wo);
 			if(!(bsdfs & m.bsdf_flags & BsdfDiffuse)) return mkc(0.f);
-			float comp[4]; sdComponents(m, comp);
-			const float kr = sdFresnel(m, wo, n);
+			float comp[4]; sdComponents<MT>(m, comp);
+			const float kr = sdFresnel<MT>(m, wo, n);
 			const float m_t = (1.f - kr * comp[0]) * (1.f - comp[1]);
 			const bool transmit = (cos_ng_wo * cos_ng_wl) < 0.f;
-			if(transmit && m.is_translucent) return (comp[2] * m_t) * ldc(m.diffuse_col);
+			if(!YG_SDL(MT) && transmit && m.is_translucent) return (comp[2] * m_t) * ldc(m.diffuse_col);
 			if(dot(n, wl) < 0.0f && !m.flat) return mkc(0.f);
 			float m_d = m_t * (1.f - comp[2]) * comp[3];
 			if(m.use_oren_nayar) m_d *= orenNayar(m.oren_a, m.oren_b, wo, wl, n);
@@ -342,20 +357,20 @@ YG_D float leafPdf(const MatDev &m, const SurfPt &sp, V3 wo, V3 wi, unsigned bsd
 			float pdf = 0.f, accum_c[4], comp[4];
 			const float cos_ng_wo = dot(sp.ng, wo);
 			const V3 n = faceForward(sp.ng, sp.n, wo);
-			sdComponents(m, comp);
-			sdAccumulate(comp, accum_c, sdFresnel(m, wo, n));
+			sdComponents<MT>(m, comp);
+			sdAccumulate(comp, accum_c, sdFresnel<MT>(m, wo, n));
 			float sum = 0.f; int n_match = 0;
-			for(int i = 0; i < m.n_bsdf; ++i)
+			for(int i = 0; i < sdNBsdf<MT>(m); ++i)
 			{
-				if(bsdfs & m.c_flags[i])
+				if(bsdfs & sdCFlags<MT>(m, i))
 				{
-					const float width = accum_c[m.c_index[i]];
+					const float width = accum_c[sdCIndex<MT>(m, i)];
 					sum += width;
-					if(m.c_flags[i] == (BsdfDiffuse | BsdfTransmit))
+					if(sdCFlags<MT>(m, i) == (BsdfDiffuse | BsdfTransmit))
 					{
 						if(cos_ng_wo * dot(sp.ng, wi) < 0) pdf += fabsf(dot(wi, n)) * width;
 					}
-					else if(m.c_flags[i] == (BsdfDiffuse | BsdfReflect)) pdf += fabsf(dot(wi, n)) * width;
+					else if(sdCFlags<MT>(m, i) == (BsdfDiffuse | BsdfReflect)) pdf += fabsf(dot(wi, n)) * width;
 					++n_match;
 				}
 			}
@@ -399,9 +414,9 @@ YG_D float leafPdf(const MatDev &m, const SurfPt &sp, V3 wo, V3 wi, unsigned bsd
 			float accum_c[3], sum = 0.f;
 			accum_c[0] = kr; accum_c[1] = kt * (1.f - m.p_diffuse); accum_c[2] = kt * m.p_diffuse;
 			int n_match = 0;
-			for(int i = 0; i < m.n_bsdf; ++i)
+			for(int i = 0; i < sdNBsdf<MT>(m); ++i)
 			{
-				if((bsdfs & m.c_flags[i]) == m.c_flags[i])
+				if((bsdfs & sdCFlags<MT>(m, i)) == sdCFlags<MT>(m, i))
 				{
 					const float width = accum_c[i];
 					sum += width;
@@ -434,19 +449,19 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 			float accum_c[4], comp[4];
 			const float cos_ng_wo = dot(sp.ng, wo);
 			const V3 n = faceForward(sp.ng, sp.n, wo);
-			sdComponents(m, comp);
-			const float kr = sdFresnel(m, wo, n);
+			sdComponents<MT>(m, comp);
+			const float kr = sdFresnel<MT>(m, wo, n);
 			sdAccumulate(comp, accum_c, kr);
 			float sum = 0.f, val[4], width[4];
 			unsigned choice[4];
 			int n_match = 0, pick = -1;
-			for(int i = 0; i < m.n_bsdf; ++i)
+			for(int i = 0; i < sdNBsdf<MT>(m); ++i)
 			{
-				if((s.flags & m.c_flags[i]) == m.c_flags[i])
+				if((s.flags & sdCFlags<MT>(m, i)) == sdCFlags<MT>(m, i))
 				{
-					width[n_match] = accum_c[m.c_index[i]];
+					width[n_match] = accum_c[sdCIndex<MT>(m, i)];
 					sum += width[n_match];
-					choice[n_match] = m.c_flags[i];
+					choice[n_match] = sdCFlags<MT>(m, i);
 					val[n_match] = sum;
 					++n_match;
 				}
@@ -499,7 +514,7 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 			w = (fabsf(dot(wi, sp.n))) / (s.pdf * 0.99f + 0.01f);
 			// getAlpha :569-597
 			float alpha = 1.f;
-			if(m.is_transparent) alpha = 1.f - (1.f - comp[0] * kr) * comp[1];
+			if(!YG_SDL(MT) && m.is_transparent) alpha = 1.f - (1.f - comp[0] * kr) * comp[1];
 			w = w * (alpha) + 1.f * (1.f - alpha);
 			return scolor;
 		}
@@ -641,9 +656,9 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 			int c_index[3], rc_index[3] = {0, 0, 0};
 			accum_c[0] = kr; accum_c[1] = kt * (1.f - m.p_diffuse); accum_c[2] = kt * m.p_diffuse;
 			int n_match = 0, pick = -1;
-			for(int i = 0; i < m.n_bsdf; ++i)
+			for(int i = 0; i < sdNBsdf<MT>(m); ++i)
 			{
-				if((s.flags & m.c_flags[i]) == m.c_flags[i])
+				if((s.flags & sdCFlags<MT>(m, i)) == sdCFlags<MT>(m, i))
 				{
 					use[i] = true;
 					width[n_match] = accum_c[i];
@@ -870,9 +885,9 @@ YG_D void leafSpecular(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, b
 			const bool backface = dot(wo, sp.ng) < 0.f;
 			const V3 n = backface ? -sp.n : sp.n;
 			const V3 ng = backface ? -sp.ng : sp.ng;
-			float comp[4]; sdComponents(m, comp);
-			const float kr = sdFresnel(m, wo, n);
-			if(m.is_transparent)
+			float comp[4]; sdComponents<MT>(m, comp);
+			const float kr = sdFresnel<MT>(m, wo, n);
+			if(!YG_SDL(MT) && m.is_transparent)
 			{
 				refr = true;
 				dir[1] = -wo;
@@ -881,7 +896,7 @@ YG_D void leafSpecular(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, b
 				col[1] = ((1.f - comp[0] * kr) * comp[1]) * tcol;
 			}
 			else refr = false;
-			if(m.is_mirror)
+			if(!YG_SDL(MT) && m.is_mirror)
 			{
 				refl = true;
 				dir[0] = reflect(wo, n);
@@ -975,10 +990,10 @@ YG_D Col leafTransparency(const MatDev &m, const SurfPt &sp, V3 wo)
 {
 	if(mtypeOf<MT>(m) == YAFGPU_MAT_SHINYDIFFUSE)
 	{	// :530-567
-		if(!m.is_transparent) return mkc(0.f);
+		if(YG_SDL(MT) || !m.is_transparent) return mkc(0.f);
 		float accum = 1.f;
 		const V3 n = faceForward(sp.ng, sp.n, wo);
-		const float kr = sdFresnel(m, wo, n);
+		const float kr = sdFresnel<MT>(m, wo, n);
 		if(m.is_mirror) accum = 1.f - kr * m.mirror_strength;
 		accum *= m.transparency_strength * accum;
 		const float tf = m.transmit_filter_strength;

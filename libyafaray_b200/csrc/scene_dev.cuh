@@ -48,6 +48,9 @@ struct __align__(16) TriShade // 64 B = four 16 B loads
 
 struct ObjDev { int has_orco, has_uv, smooth, light; };
 
+// internal material type (never crosses the C ABI): shinydiffuse with the diffuse-reflection component only, see materials.cuh
+#define YG_MAT_SD_LAMBERT 9
+
 // Material record after the reference constructors' preprocessing (one per yafgpu_material).
 struct MatDev
 {
