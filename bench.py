@@ -173,6 +173,8 @@ def gpu_arm(args, rank, world, local_rank):
     ctx = Context(local_rank)
     if args.wave_size:
         ctx.set_option("wave_size", args.wave_size)
+    for kv in args.option:
+        ctx.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     ctx.upload(desc, keep)
     S = args.spp_per_step * world
     n_chunks = max(1, PASS_SPP // S)
@@ -270,6 +272,8 @@ def gpu_arm(args, rank, world, local_rank):
             c2 = Context(local_rank, flags)
             if args.wave_size:
                 c2.set_option("wave_size", args.wave_size)
+            for kv in args.option:
+                c2.set_option(kv.split("=")[0], int(kv.split("=")[1]))
             c2.upload(desc, keep)
             c2.film_clear()
             step0(0, c2)
@@ -363,6 +367,7 @@ def main():
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--option", action="append", default=[], metavar="NAME=INT", help="yafgpu_set_option knob for A/B runs (e.g. shade_streams=1)")
     ap.add_argument("--wave-size", type=int, default=0, help="camera samples per wavefront wave (0 = library default)")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))

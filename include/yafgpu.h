@@ -416,7 +416,8 @@ int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_
 
 /* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^23, limited to a quarter of the free device memory),
  * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "ray_regeneration" (1: the wavefront
- * traversal kernels use the warp-persistent schedule with ray regeneration that yafgpu_trace always uses; default 0). */
+ * traversal kernels use the warp-persistent schedule with ray regeneration that yafgpu_trace always uses; default 0),
+ * "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3). */
 int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);
 int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
 int yafgpu_reset_stats(yafgpu_ctx *ctx);

@@ -123,6 +123,8 @@ int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags)
 	memset(&c->scene, 0, sizeof(c->scene)); memset(&c->film, 0, sizeof(c->film)); memset(&c->stats, 0, sizeof(c->stats));
 	if((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) { delete c; return cudaErr(nullptr, e, "cudaStreamCreate"); }
 	cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
+	for(int k = 0; k < 2; ++k) { cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking); cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming); }
+	cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
 	FaureTables *ft = new FaureTables();
 	yg_build_faure_tables(*ft);
 	e = cudaMalloc(&c->d_faure, sizeof(FaureTables));
@@ -147,6 +149,8 @@ void yafgpu_destroy(yafgpu_ctx *c)
 	for(cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
 	if(c->ev0) cudaEventDestroy(c->ev0);
 	if(c->ev1) cudaEventDestroy(c->ev1);
+	for(int k = 0; k < 2; ++k) { if(c->side[k]) { cudaStreamSynchronize(c->side[k]); cudaStreamDestroy(c->side[k]); } if(c->ev_join[k]) cudaEventDestroy(c->ev_join[k]); }
+	if(c->ev_fork) cudaEventDestroy(c->ev_fork);
 	if(c->stream) cudaStreamDestroy(c->stream);
 	delete c;
 }
@@ -486,6 +490,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	if(n == "wave_size") { if(value < 1024 || value > (1 << 24)) return setErr(c, YAFGPU_ERR_INVALID, "wave_size out of range"); c->wave_cap_override = (int)value; return YAFGPU_OK; }
 	if(n == "leaf_size") { if(value < 1 || value > 8) return setErr(c, YAFGPU_ERR_INVALID, "leaf_size must be 1..8"); c->leaf_max = (int)value; return YAFGPU_OK; }
 	if(n == "ray_regeneration") { c->ray_regeneration = value != 0; return YAFGPU_OK; }
+	if(n == "shade_streams") { if(value < 1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "shade_streams must be 1..3"); c->shade_streams = (int)value; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);
 }

@@ -51,6 +51,9 @@ struct yafgpu_ctx
 	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	cudaStream_t side[2] = {nullptr, nullptr};   // the per-type shading kernels of one iteration run side by side (integrator.cu)
+	cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+	int shade_streams = 3;                       // yafgpu_set_option("shade_streams", 1..3)
 	std::vector<cudaEvent_t> stage_events; // YAFGPU_FLAG_TIME_STAGES
 };
 

@@ -260,6 +260,17 @@ __global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int
 	const int n = min(*n_tasks, task_cap);
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
 	TraceIO io; io.q = q; io.bins = bins;
+	// bucket counts go to a per-block shared histogram first: with a handful of materials every warp of the grid would otherwise
+	// hit the same few L2 addresses (2.6e5 same-address atomics per 8 M tasks serialise in one L2 slice)
+	extern __shared__ int s_hist[];
+	const int nb = 2 * bins.n_mat + 1;
+	const bool block_hist = nb <= YG_SHARED_BUCKETS;
+	if(block_hist)
+	{
+		for(int b = threadIdx.x; b < nb; b += blockDim.x) s_hist[b] = 0;
+		__syncthreads();
+		io.bins.hist = s_hist;
+	}
 	if(REGEN) traversePersistent<false, COUNT>(acc, n, next, io, &tc);
 	else
 	{
@@ -276,6 +287,11 @@ __global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int
 			r.tmax = dist;
 			io.store(i, traceClosest<COUNT>(acc, r, &tc), vmask);
 		}
+	}
+	if(block_hist)
+	{
+		__syncthreads();
+		for(int b = threadIdx.x; b < nb; b += blockDim.x) if(s_hist[b]) atomicAdd(bins.hist + b, s_hist[b]);
 	}
 	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
 }
@@ -301,7 +317,39 @@ __global__ void __launch_bounds__(1024) k_bin_scan(const int *__restrict__ hist,
 	for(int k = 0; k < per; ++k) if(b0 + k < nb) { offs[b0 + k] = run; run += hist[b0 + k]; }
 }
 
-// scatter: perm[slot in bucket order] = task index
+// scatter: perm[slot in bucket order] = task index.  A block ranks a chunk of YG_SCATTER_PER_THREAD * 256 tasks in shared memory and
+// reserves one range per non-empty bucket, so the global offsets see a few atomics per 4096 tasks instead of one or more per warp.
+#define YG_SCATTER_PER_THREAD 16
+__global__ void __launch_bounds__(256) k_bin_scatter_block(const int *__restrict__ n_tasks, int task_cap, const int *__restrict__ key, int *__restrict__ offs, int *__restrict__ perm, int nb)
+{
+	extern __shared__ int s_cnt[]; // [nb] counts, then [nb] reserved bases
+	int *s_base = s_cnt + nb;
+	const int n = min(*n_tasks, task_cap);
+	const int chunk = YG_SCATTER_PER_THREAD * 256;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	for(int c0 = blockIdx.x * chunk; c0 < n; c0 += gridDim.x * chunk)
+	{
+		for(int b = threadIdx.x; b < nb; b += 256) s_cnt[b] = 0;
+		__syncthreads();
+		int k[YG_SCATTER_PER_THREAD], r[YG_SCATTER_PER_THREAD];
+#pragma unroll
+		for(int j = 0; j < YG_SCATTER_PER_THREAD; ++j)
+		{	// warp w takes 32 consecutive tasks per round: ranks inside a bucket follow queue order up to the warp interleave
+			const int i = c0 + (j * 8 + warp) * 32 + lane;
+			const bool valid = i < n;
+			const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+			k[j] = -1; r[j] = 0;
+			if(valid) { k[j] = key[i]; r[j] = binAdd(s_cnt, k[j], vmask); }
+		}
+		__syncthreads();
+		for(int b = threadIdx.x; b < nb; b += 256) if(s_cnt[b]) s_base[b] = atomicAdd(offs + b, s_cnt[b]);
+		__syncthreads();
+#pragma unroll
+		for(int j = 0; j < YG_SCATTER_PER_THREAD; ++j)
+			if(k[j] >= 0) perm[s_base[k[j]] + r[j]] = c0 + (j * 8 + warp) * 32 + lane;
+		__syncthreads();
+	}
+}
 __global__ void __launch_bounds__(256) k_bin_scatter(const int *__restrict__ n_tasks, int task_cap, const int *__restrict__ key, int *__restrict__ offs, int *__restrict__ perm)
 {
 	const int n = min(*n_tasks, task_cap);
@@ -358,6 +406,9 @@ __device__ __forceinline__ void pushTask(const ShadeCtx &cx, int slot, V3 from, 
 #endif
 #ifndef YG_SHADE_MINB
 #define YG_SHADE_MINB 4
+#endif
+#ifndef YG_SHADE_MINB_L
+#define YG_SHADE_MINB_L 4 /* resident blocks per SM of the diffuse-only kernel (fewer live values than the full BSDFs) */
 #endif
 #if YG_DLE_INLINE
 #define YG_DLE YG_D
@@ -454,7 +505,7 @@ YG_DLE void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, 
 enum { MT_MISS = 100 };
 
 template<int MT>
-__global__ void __launch_bounds__(128, YG_SHADE_MINB) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
+__global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L : YG_SHADE_MINB) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
                                                float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter, const int *__restrict__ perm,
                                                const int *__restrict__ ends, int n_mat, int b0, int b1)
 {
@@ -935,18 +986,27 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		SortBins bins; bins.tri_mat = c->d_tri_mat; bins.mat_bucket = c->d_mat_bucket; bins.n_mat = c->n_mat_buckets; bins.key = w.key; bins.hist = w.hist;
 		const int nb = 2 * c->n_mat_buckets + 1;
 		cudaMemsetAsync(w.hist, 0, sizeof(int) * nb, st);
-#define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, 0, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], c->d_counters)
+		const size_t hist_smem = nb <= YG_SHARED_BUCKETS ? sizeof(int) * nb : 0;
+#define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, hist_smem, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], c->d_counters)
 		if(count) { if(regen) YG_TRACE(true, true); else YG_TRACE(true, false); } else { if(regen) YG_TRACE(false, true); else YG_TRACE(false, false); }
 #undef YG_TRACE
 		mark();
 		k_bin_scan<<<1, 1024, 0, st>>>(w.hist, w.hist + YG_MAX_BUCKETS, nb);
-		k_bin_scatter<<<sms * 4, 256, 0, st>>>(&w.ctl->n_tasks[it], wp.task_cap, w.key, w.hist + YG_MAX_BUCKETS, w.perm);
+		if(nb <= YG_SHARED_BUCKETS) k_bin_scatter_block<<<sms * 4, 256, 2 * sizeof(int) * nb, st>>>(&w.ctl->n_tasks[it], wp.task_cap, w.key, w.hist + YG_MAX_BUCKETS, w.perm, nb);
+		else k_bin_scatter<<<sms * 4, 256, 0, st>>>(&w.ctl->n_tasks[it], wp.task_cap, w.key, w.hist + YG_MAX_BUCKETS, w.perm);
 		const int *ends = w.hist + YG_MAX_BUCKETS; // the scatter kernel advanced every bucket's offset to its end
-#define YG_SHADE(T) if(c->type_b1[T] >= c->type_b0[T]) { k_shade<T><<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, c->type_b0[T], c->type_b1[T]); ++n_launch; }
-		YG_SHADE(YAFGPU_MAT_SHINYDIFFUSE) YG_SHADE(YAFGPU_MAT_GLOSSY) YG_SHADE(YAFGPU_MAT_COATED_GLOSSY) YG_SHADE(YAFGPU_MAT_GLASS) YG_SHADE(YAFGPU_MAT_ROUGH_GLASS)
-		YG_SHADE(YAFGPU_MAT_BLEND) YG_SHADE(YAFGPU_MAT_MIRROR) YG_SHADE(YAFGPU_MAT_NULL) YG_SHADE(YAFGPU_MAT_LIGHT) YG_SHADE(YG_MAT_SD_LAMBERT)
+		// The per-type kernels only share atomically allocated queue slots and atomic accumulators, so they run side by side: the
+		// large one fills the machine, the small ones (glass, emitters, misses) fill its tail instead of each draining the GPU alone.
+		const int n_str = std::max(1, std::min(3, c->shade_streams));
+		if(n_str > 1) { cudaEventRecord(c->ev_fork, st); for(int k = 0; k < n_str - 1; ++k) cudaStreamWaitEvent(c->side[k], c->ev_fork, 0); }
+		int rr = 0;
+		auto shadeStream = [&]() { const int k = rr++ % n_str; return k == 0 ? st : c->side[k - 1]; };
+#define YG_SHADE(T) if(c->type_b1[T] >= c->type_b0[T]) { k_shade<T><<<gs, 128, 0, shadeStream()>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, c->type_b0[T], c->type_b1[T]); ++n_launch; }
+		YG_SHADE(YG_MAT_SD_LAMBERT) YG_SHADE(YAFGPU_MAT_SHINYDIFFUSE) YG_SHADE(YAFGPU_MAT_GLOSSY) YG_SHADE(YAFGPU_MAT_COATED_GLOSSY) YG_SHADE(YAFGPU_MAT_GLASS) YG_SHADE(YAFGPU_MAT_ROUGH_GLASS)
+		YG_SHADE(YAFGPU_MAT_BLEND) YG_SHADE(YAFGPU_MAT_MIRROR) YG_SHADE(YAFGPU_MAT_NULL) YG_SHADE(YAFGPU_MAT_LIGHT)
 #undef YG_SHADE
-		k_shade<MT_MISS><<<gs, 128, 0, st>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
+		k_shade<MT_MISS><<<gs, 128, 0, shadeStream()>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
+		if(n_str > 1) for(int k = 0; k < n_str - 1; ++k) { cudaEventRecord(c->ev_join[k], c->side[k]); cudaStreamWaitEvent(st, c->ev_join[k], 0); }
 		mark();
 #define YG_SHADOW(C, R) k_shadow<C, R><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, &w.ctl->fetch_shadow[it], c->d_counters)
 		if(count) { if(regen) YG_SHADOW(true, true); else YG_SHADOW(true, false); } else { if(regen) YG_SHADOW(false, true); else YG_SHADOW(false, false); }
