@@ -3,6 +3,7 @@
 #include "context.h"
 #include "host_prep.h"
 #include "bvh_build.h"
+#include "dev_pool.h"
 #include "traverse.cuh"
 #include <cstdio>
 #include <cstdlib>
@@ -26,7 +27,7 @@ int cudaErr(yafgpu_ctx *ctx, cudaError_t e, const char *what)
 template<class T> static cudaError_t upload(T *&dst, const T *src, size_t n, cudaStream_t s)
 {
 	dst = nullptr;
-	cudaError_t e = cudaMalloc(&dst, sizeof(T) * (n ? n : 1));
+	cudaError_t e = poolAlloc(&dst, sizeof(T) * n, s);
 	if(e != cudaSuccess) return e;
 	if(n) e = cudaMemcpyAsync(dst, src, sizeof(T) * n, cudaMemcpyHostToDevice, s);
 	return e;
@@ -34,11 +35,11 @@ template<class T> static cudaError_t upload(T *&dst, const T *src, size_t n, cud
 
 static void freeScene(yafgpu_ctx *c)
 {
-	cudaFree(c->d_points); cudaFree(c->d_normals); cudaFree(c->d_uv); cudaFree(c->d_tri_ng); cudaFree(c->d_tri_vidx);
-	cudaFree(c->d_tri_mat); cudaFree(c->d_mat_triflags); cudaFree(c->d_tris); cudaFree(c->d_objects); cudaFree(c->d_mats);
-	cudaFree(c->d_lights); cudaFree(c->d_light_tables); cudaFree(c->d_bg_tex); cudaFree(c->d_nodes); cudaFree(c->d_acc_tris);
-	cudaFree(c->film.pix); cudaFree(c->d_mat_bucket); c->d_mat_bucket = nullptr; cudaFree(c->d_light_accels); c->d_light_accels = nullptr;
-	for(void *q : c->light_bvh_ptrs) cudaFree(q);
+	poolFree(c->d_points, c->stream); poolFree(c->d_normals, c->stream); poolFree(c->d_uv, c->stream); poolFree(c->d_tri_ng, c->stream); poolFree(c->d_tri_vidx, c->stream);
+	poolFree(c->d_tri_mat, c->stream); poolFree(c->d_mat_triflags, c->stream); poolFree(c->d_tris, c->stream); poolFree(c->d_objects, c->stream); poolFree(c->d_mats, c->stream);
+	poolFree(c->d_lights, c->stream); poolFree(c->d_light_tables, c->stream); poolFree(c->d_bg_tex, c->stream); poolFree(c->d_nodes, c->stream); poolFree(c->d_acc_tris, c->stream);
+	poolFree(c->film.pix, c->stream); poolFree(c->d_mat_bucket, c->stream); c->d_mat_bucket = nullptr; poolFree(c->d_light_accels, c->stream); c->d_light_accels = nullptr;
+	for(void *q : c->light_bvh_ptrs) poolFree(q, c->stream);
 	c->light_bvh_ptrs.clear();
 	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
 	c->d_tris = nullptr; c->d_objects = nullptr; c->d_mats = nullptr; c->d_lights = nullptr; c->d_light_tables = nullptr; c->d_bg_tex = nullptr;
@@ -125,6 +126,10 @@ int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags)
 	cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1);
 	for(int k = 0; k < 2; ++k) { cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking); cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming); }
 	cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+	{	// keep freed scene/builder blocks in the stream-ordered pool (dev_pool.h)
+		cudaMemPool_t pool = nullptr;
+		if(cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) { unsigned long long keep = ~0ull; cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep); }
+	}
 	FaureTables *ft = new FaureTables();
 	yg_build_faure_tables(*ft);
 	e = cudaMalloc(&c->d_faure, sizeof(FaureTables));
@@ -144,6 +149,8 @@ void yafgpu_destroy(yafgpu_ctx *c)
 	cudaSetDevice(c->device);
 	if(c->stream) cudaStreamSynchronize(c->stream);
 	freeScene(c);
+	if(c->stream) cudaStreamSynchronize(c->stream);
+	{ cudaMemPool_t pool = nullptr; if(cudaDeviceGetDefaultMemPool(&pool, c->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
 	freeWavefront(c);
 	cudaFree(c->d_faure); cudaFree(c->d_counters); cudaFree(c->d_fetch);
 	for(cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
@@ -295,8 +302,8 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
 	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
-	YG_CUDA(c, cudaMalloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1)));
-	YG_CUDA(c, cudaMalloc(&c->d_tris, sizeof(TriShade) * (g.n_tris ? g.n_tris : 1)));
+	YG_CUDA(c, poolAlloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1), st));
+	YG_CUDA(c, poolAlloc(&c->d_tris, sizeof(TriShade) * (g.n_tris ? g.n_tris : 1), st));
 	if(g.tri_nidx) YG_CUDA(c, upload(d_nidx, g.tri_nidx, g.n_tris * 3, st));
 	if(g.tri_uvidx) YG_CUDA(c, upload(d_uvidx, g.tri_uvidx, g.n_tris * 3, st));
 	YG_CUDA(c, upload(d_obj, g.tri_obj, g.n_tris, st));
@@ -311,7 +318,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng; bi.leaf_max = c->leaf_max;
 		BvhBuildOutput bo;
 		cudaError_t e = buildBvh(bi, bo, st);
-		if(e != cudaSuccess) { cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj); return cudaErr(c, e, "buildBvh"); }
+		if(e != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e, "buildBvh"); }
 		c->d_nodes = bo.nodes; c->d_acc_tris = bo.tris;
 		a.nodes = bo.nodes; a.tris = bo.tris; a.n_nodes = bo.n_nodes; a.root = bo.root;
 		memcpy(c->scene_bound, bo.bound, sizeof(bo.bound));
@@ -334,7 +341,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		bi.tri_mat = c->d_tri_mat + ld.tri_first; bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng + 3 * (size_t)ld.tri_first;
 		BvhBuildOutput bo;
 		cudaError_t e2 = buildBvh(bi, bo, st);
-		if(e2 != cudaSuccess) { cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj); return cudaErr(c, e2, "buildBvh (mesh light)"); }
+		if(e2 != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e2, "buildBvh (mesh light)"); }
 		Accel la; memset(&la, 0, sizeof(la));
 		la.nodes = bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root;
 		c->light_bvh_ptrs.push_back(bo.nodes); c->light_bvh_ptrs.push_back(bo.tris);
@@ -351,7 +358,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	cudaEventRecord(c->ev1, st);
 	cudaError_t e = cudaStreamSynchronize(st);
-	cudaFree(d_nidx); cudaFree(d_uvidx); cudaFree(d_obj);
+	poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream);
 	if(e != cudaSuccess) return cudaErr(c, e, "scene upload");
 	float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->stats.ms_build += ms;
 	c->stats.bvh_nodes = a.n_nodes; c->stats.bvh_bytes = (uint64_t)a.n_nodes * sizeof(BvhNode); c->stats.tri_bytes = (uint64_t)g.n_tris * sizeof(TriAccel);
@@ -364,7 +371,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	c->tile_size = desc->film.tile_size > 0 ? desc->film.tile_size : 32;
 	if(desc->film.width <= 0 || desc->film.height <= 0 || desc->film.width > 65535 || desc->film.height > 65535) return setErr(c, YAFGPU_ERR_INVALID, "film size");
 	if(desc->film.premult) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "premult film not implemented on the device");
-	YG_CUDA(c, cudaMalloc(&c->film.pix, sizeof(float) * 5 * (size_t)c->film.w * c->film.h));
+	YG_CUDA(c, poolAlloc(&c->film.pix, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
 	c->uploaded = true;
@@ -409,9 +416,9 @@ int yafgpu_trace(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_hit *hi
 	if(n == 0) return YAFGPU_OK;
 	YG_CUDA(c, cudaSetDevice(c->device));
 	void *d_r = nullptr, *d_h = nullptr;
-	YG_CUDA(c, cudaMalloc(&d_r, n * sizeof(yafgpu_ray)));
-	cudaError_t e = cudaMalloc(&d_h, n * sizeof(yafgpu_hit));
-	if(e != cudaSuccess) { cudaFree(d_r); return cudaErr(c, e, "cudaMalloc hits"); }
+	YG_CUDA(c, poolAlloc(&d_r, n * sizeof(yafgpu_ray), c->stream));
+	cudaError_t e = poolAlloc(&d_h, n * sizeof(yafgpu_hit), c->stream);
+	if(e != cudaSuccess) { poolFree(d_r, c->stream); return cudaErr(c, e, "device allocation for hits"); }
 	e = cudaMemcpyAsync(d_r, rays, n * sizeof(yafgpu_ray), cudaMemcpyHostToDevice, c->stream);
 	int rc = (e == cudaSuccess) ? yafgpu_trace_device(c, d_r, n, d_h, mode, shadow_depth) : cudaErr(c, e, "H2D rays");
 	if(rc == YAFGPU_OK)
@@ -420,7 +427,7 @@ int yafgpu_trace(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_hit *hi
 		if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
 		if(e != cudaSuccess) rc = cudaErr(c, e, "D2H hits");
 	}
-	cudaFree(d_r); cudaFree(d_h);
+	poolFree(d_r, c->stream); poolFree(d_h, c->stream);
 	return rc;
 }
 

@@ -10,6 +10,7 @@
 //   refit       : bottom-up AABB propagation with one atomic counter per internal node
 //   emit        : 64 B two-child nodes (scene_dev.cuh) + TriAccel records in Morton order
 #include "bvh_build.h"
+#include "dev_pool.h"
 #include <cub/cub.cuh>
 #include <cfloat>
 #include <cstring>
@@ -212,9 +213,9 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 	void *cub_tmp = nullptr; size_t cub_bytes = 0;
 	out.nodes = nullptr; out.tris = nullptr; out.n_nodes = 0;
 
-	CK(cudaMalloc(&v0e, sizeof(float4) * n)); CK(cudaMalloc(&e1i, sizeof(float4) * n)); CK(cudaMalloc(&e2f, sizeof(float4) * n));
-	CK(cudaMalloc(&bmin, sizeof(float4) * n)); CK(cudaMalloc(&bmax, sizeof(float4) * n));
-	CK(cudaMalloc(&scene_bound, sizeof(int) * 6));
+	CK(poolAlloc(&v0e, sizeof(float4) * n, stream)); CK(poolAlloc(&e1i, sizeof(float4) * n, stream)); CK(poolAlloc(&e2f, sizeof(float4) * n, stream));
+	CK(poolAlloc(&bmin, sizeof(float4) * n, stream)); CK(poolAlloc(&bmax, sizeof(float4) * n, stream));
+	CK(poolAlloc(&scene_bound, sizeof(int) * 6, stream));
 	{
 		int flipped[6];
 		for(int k = 0; k < 6; ++k)
@@ -226,29 +227,29 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 	}
 	k_tri_setup<<<G, B, 0, stream>>>(n, in.points, in.tri_vidx, in.tri_mat, in.mat_triflags, v0e, e1i, e2f, bmin, bmax, in.tri_ng_out, scene_bound);
 	CK(cudaGetLastError());
-	CK(cudaMalloc(&keys, sizeof(unsigned long long) * n)); CK(cudaMalloc(&keys_s, sizeof(unsigned long long) * n));
-	CK(cudaMalloc(&vals, sizeof(int) * n)); CK(cudaMalloc(&vals_s, sizeof(int) * n));
+	CK(poolAlloc(&keys, sizeof(unsigned long long) * n, stream)); CK(poolAlloc(&keys_s, sizeof(unsigned long long) * n, stream));
+	CK(poolAlloc(&vals, sizeof(int) * n, stream)); CK(poolAlloc(&vals_s, sizeof(int) * n, stream));
 	k_morton<<<G, B, 0, stream>>>(n, bmin, bmax, scene_bound, keys, vals);
 	CK(cudaGetLastError());
 	CK(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, keys, keys_s, vals, vals_s, n, 0, 63, stream));
-	CK(cudaMalloc(&cub_tmp, cub_bytes ? cub_bytes : 16));
+	CK(poolAlloc(&cub_tmp, cub_bytes ? cub_bytes : 16, stream));
 	CK(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys_s, vals, vals_s, n, 0, 63, stream));
 
-	CK(cudaMalloc(&out.tris, sizeof(TriAccel) * n));
+	CK(poolAlloc(&out.tris, sizeof(TriAccel) * n, stream));
 	k_emit_tris<<<G, B, 0, stream>>>(n, vals_s, v0e, e1i, e2f, out.tris);
 	CK(cudaGetLastError());
 	if(n >= 2)
 	{
-		CK(cudaMalloc(&left, sizeof(int) * (n - 1))); CK(cudaMalloc(&right, sizeof(int) * (n - 1)));
-		CK(cudaMalloc(&parent, sizeof(int) * (2 * n - 1))); CK(cudaMalloc(&counters, sizeof(int) * (n - 1)));
-		CK(cudaMalloc(&nmin, sizeof(float4) * (2 * n - 1))); CK(cudaMalloc(&nmax, sizeof(float4) * (2 * n - 1)));
-		CK(cudaMalloc(&range, sizeof(int2) * (n - 1)));
+		CK(poolAlloc(&left, sizeof(int) * (n - 1), stream)); CK(poolAlloc(&right, sizeof(int) * (n - 1), stream));
+		CK(poolAlloc(&parent, sizeof(int) * (2 * n - 1), stream)); CK(poolAlloc(&counters, sizeof(int) * (n - 1), stream));
+		CK(poolAlloc(&nmin, sizeof(float4) * (2 * n - 1), stream)); CK(poolAlloc(&nmax, sizeof(float4) * (2 * n - 1), stream));
+		CK(poolAlloc(&range, sizeof(int2) * (n - 1), stream));
 		CK(cudaMemsetAsync(counters, 0, sizeof(int) * (n - 1), stream));
 		k_hierarchy<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, keys_s, left, right, parent, range);
 		CK(cudaGetLastError());
 		k_refit<<<G, B, 0, stream>>>(n, vals_s, bmin, bmax, left, right, parent, nmin, nmax, counters);
 		CK(cudaGetLastError());
-		CK(cudaMalloc(&out.nodes, sizeof(BvhNode) * (n - 1)));
+		CK(poolAlloc(&out.nodes, sizeof(BvhNode) * (n - 1), stream));
 		k_emit_nodes<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, left, right, nmin, nmax, range, leaf_max, out.nodes);
 		CK(cudaGetLastError());
 		out.n_nodes = n - 1;
@@ -266,10 +267,10 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 		for(int k = 0; k < 6; ++k) { int i = sb[k]; i = i >= 0 ? i : i ^ 0x7fffffff; memcpy(&out.bound[k], &i, 4); }
 	}
 fail:
-	cudaFree(v0e); cudaFree(e1i); cudaFree(e2f); cudaFree(bmin); cudaFree(bmax); cudaFree(nmin); cudaFree(nmax);
-	cudaFree(scene_bound); cudaFree(vals); cudaFree(vals_s); cudaFree(left); cudaFree(right); cudaFree(parent); cudaFree(counters);
-	cudaFree(keys); cudaFree(keys_s); cudaFree(cub_tmp); cudaFree(range);
-	if(err != cudaSuccess) { cudaFree(out.nodes); cudaFree(out.tris); out.nodes = nullptr; out.tris = nullptr; }
+	poolFree(v0e, stream); poolFree(e1i, stream); poolFree(e2f, stream); poolFree(bmin, stream); poolFree(bmax, stream); poolFree(nmin, stream); poolFree(nmax, stream);
+	poolFree(scene_bound, stream); poolFree(vals, stream); poolFree(vals_s, stream); poolFree(left, stream); poolFree(right, stream); poolFree(parent, stream); poolFree(counters, stream);
+	poolFree(keys, stream); poolFree(keys_s, stream); poolFree(cub_tmp, stream); poolFree(range, stream);
+	if(err != cudaSuccess) { poolFree(out.nodes, stream); poolFree(out.tris, stream); out.nodes = nullptr; out.tris = nullptr; }
 	return err;
 }
 

@@ -71,7 +71,7 @@ def main(csv_path, bench_path, tag):
     with open(os.path.join(ROOT, "profiles", "ncu_traffic.json"), "w") as fh:
         json.dump(out, fh, indent=1)
     tot = sum(v["ns"] for v in byname.values())
-    lines = ["# %s — ncu launch list of one bench step (Cornell 1920x1080, 4 spp per step = 8 waves)" % tag, "",
+    lines = ["# %s — ncu launch list of one bench step (Cornell 1920x1080, 4 spp per step = %d wave%s)" % (tag, waves, "" if waves == 1 else "s"), "",
              "Command: `ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c N --csv python bench.py --steps 1 --warmup 0 --no-cpu`",
              "(per-launch times under ncu are serialised and cold-cache: compare SHARES with bench.py's `roofline.kernels[*].share_of_step`, not absolutes).", "",
              "| kernel | launches | GPU time ms | share | DRAM MB |", "|---|---|---|---|---|"]
