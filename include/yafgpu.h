@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define YAFGPU_ABI_VERSION 1
+#define YAFGPU_ABI_VERSION 2
 
 typedef struct yafgpu_ctx yafgpu_ctx;
 
@@ -200,7 +200,10 @@ typedef enum yafgpu_light_type
 	YAFGPU_LIGHT_SUN = 1,        /* "sunlight"    light_sun.cc:95-125 */
 	YAFGPU_LIGHT_AREA = 2,       /* "arealight"   light_area.cc:174-213 */
 	YAFGPU_LIGHT_MESH = 3,       /* "meshlight"   light_meshlight.cc:228-263 */
-	YAFGPU_LIGHT_BACKGROUND = 4  /* "bglight"     light_background.cc:251-283 (created by a background with ibl=true) */
+	YAFGPU_LIGHT_BACKGROUND = 4, /* "bglight"     light_background.cc:251-283 (created by a background with ibl=true) */
+	YAFGPU_LIGHT_DIRECTIONAL = 5,/* "directional" light_directional.cc:112-158 */
+	YAFGPU_LIGHT_SPOT = 6,       /* "spotlight"   light_spot.cc:251-295 */
+	YAFGPU_LIGHT_SPHERE = 7      /* "spherelight" light_sphere.cc:163-198 (without a linked sphere primitive: "object" must be 0) */
 } yafgpu_light_type;
 
 typedef struct yafgpu_light
@@ -215,19 +218,32 @@ typedef struct yafgpu_light
 	int32_t abs_intersect;   /* bg: "abs_intersect" */
 	float color[3];          /* "color" */
 	float power;             /* "power" */
-	float from[3];           /* point: "from"; sun: "direction"; area: "corner" */
-	float point1[3];         /* area: "point1" */
+	float from[3];           /* point/spot/sphere/finite directional: "from"; sun: "direction"; area: "corner" */
+	float point1[3];         /* area: "point1"; spot: "to"; directional: "direction" */
 	float point2[3];         /* area: "point2" */
 	float angle;             /* sun: "angle" (degrees) */
 	float clamp_intersect;   /* bg: ibl_clamp_sampling */
 	int32_t shoot_caustic;   /* "with_caustic" (bg light: gates caustic-path background hits) */
 	int32_t shoot_diffuse;   /* "with_diffuse" */
-	int32_t reserved[2];
+	float radius;            /* sphere: "radius"; finite directional: "radius" */
+	float cone_angle;        /* spot: "cone_angle" (degrees) */
+	float blend;             /* spot: "blend" */
+	float shadow_fuzzy;      /* spot: "shadowFuzzyness" */
+	int32_t soft_shadows;    /* spot: "soft_shadows" (then it is an area-like light with "samples") */
+	int32_t infinite;        /* directional: "infinite" */
 } yafgpu_light;
 
 /* ---- camera ---------------------------------------------------------------------------- */
 
-typedef enum yafgpu_camera_type { YAFGPU_CAM_PERSPECTIVE = 0 } yafgpu_camera_type;
+typedef enum yafgpu_camera_type
+{
+	YAFGPU_CAM_PERSPECTIVE = 0,     /* "perspective"     camera_perspective.cc */
+	YAFGPU_CAM_ARCHITECT = 1,       /* "architect"       camera_architect.cc (perspective with a vertical image plane) */
+	YAFGPU_CAM_ORTHOGRAPHIC = 2,    /* "orthographic"    camera_orthographic.cc */
+	YAFGPU_CAM_ANGULAR = 3,         /* "angular"         camera_angular.cc */
+	YAFGPU_CAM_EQUIRECTANGULAR = 4  /* "equirectangular" camera_equirectangular.cc */
+} yafgpu_camera_type;
+enum { YAFGPU_AP_EQUIDISTANT = 0, YAFGPU_AP_ORTHOGRAPHIC = 1, YAFGPU_AP_STEREOGRAPHIC = 2, YAFGPU_AP_EQUISOLID = 3, YAFGPU_AP_RECTILINEAR = 4 };
 enum { YAFGPU_BK_DISK1 = 0, YAFGPU_BK_DISK2 = 1, YAFGPU_BK_TRI = 3, YAFGPU_BK_SQR = 4, YAFGPU_BK_PENTA = 5, YAFGPU_BK_HEXA = 6, YAFGPU_BK_RING = 7 };
 enum { YAFGPU_BB_NONE = 0, YAFGPU_BB_CENTER = 1, YAFGPU_BB_EDGE = 2 };
 
@@ -246,6 +262,12 @@ typedef struct yafgpu_camera
 	int32_t bokeh_type;      /* "bokeh_type" */
 	int32_t bokeh_bias;      /* "bokeh_bias" */
 	float bokeh_rotation;    /* "bokeh_rotation" */
+	float scale;             /* orthographic: "scale" */
+	double angle;            /* angular: "angle" (degrees; the factory converts to radians in double, camera_angular.cc:126) */
+	double max_angle;        /* angular: "max_angle" (degrees; the factory defaults it to "angle") */
+	int32_t circular;        /* angular: "circular" */
+	int32_t mirrored;        /* angular: "mirrored" */
+	int32_t projection;      /* angular: "projection" (YAFGPU_AP_*) */
 } yafgpu_camera;
 
 /* ---- background ------------------------------------------------------------------------ */
@@ -254,7 +276,8 @@ typedef enum yafgpu_background_type
 {
 	YAFGPU_BG_NONE = 0,
 	YAFGPU_BG_CONSTANT = 1,   /* "constant"    background_constant.cc:52-86 */
-	YAFGPU_BG_TEXTURE = 2     /* "textureback" background_texture.cc:90-165 (image given as decoded linear float RGB) */
+	YAFGPU_BG_TEXTURE = 2,    /* "textureback" background_texture.cc:90-165 (image given as decoded linear float RGB) */
+	YAFGPU_BG_GRADIENT = 3    /* "gradientback" background_gradient.cc:66-117 */
 } yafgpu_background_type;
 
 typedef struct yafgpu_background
@@ -269,6 +292,9 @@ typedef struct yafgpu_background
 	/* texture: pixels as ImageHandler::getPixel returns them, row-major, y down, RGB float32 */
 	const float *tex_rgb; int32_t tex_w, tex_h;
 	int32_t tex_interp;      /* 0 = none, 1 = bilinear (texture "interpolate") */
+	/* gradient: "horizon_color", "zenith_color", "horizon_ground_color", "zenith_ground_color" (before *power; the factory
+	 * defaults the ground colours to the sky colours) */
+	float horizon_color[3], zenith_color[3], horizon_ground_color[3], zenith_ground_color[3];
 } yafgpu_background;
 
 /* ---- film, AA and integrator settings -------------------------------------------------- */

@@ -227,6 +227,33 @@ bool lightRecord(const Light *l, const std::map<int, int> &obj_index_of_id, yafg
 		out.abs_intersect = par<bool>(p, "abs_intersect", false);
 		out.clamp_intersect = l->clamp_intersect_; // set after creation by TextureBackground::factory (background_texture.cc:155-160)
 	}
+	else if(type == "directional")
+	{	// light_directional.cc:112-158
+		out.type = YAFGPU_LIGHT_DIRECTIONAL;
+		par3(p, "direction", out.point1, 0.f, 0.f, 1.f);
+		out.infinite = par<bool>(p, "infinite", true);
+		if(!out.infinite)
+		{
+			Point3 from(0.f);
+			if(!p.getParam("from", from)) p.getParam("position", from);
+			out.from[0] = from.x_; out.from[1] = from.y_; out.from[2] = from.z_;
+			out.radius = par<float>(p, "radius", 1.f);
+		}
+	}
+	else if(type == "spotlight")
+	{	// light_spot.cc:251-295
+		out.type = YAFGPU_LIGHT_SPOT;
+		par3(p, "from", out.from, 0.f, 0.f, 0.f); par3(p, "to", out.point1, 0.f, 0.f, -1.f);
+		out.cone_angle = par<float>(p, "cone_angle", 45.f); out.blend = par<float>(p, "blend", 0.15f);
+		out.soft_shadows = par<bool>(p, "soft_shadows", false); out.shadow_fuzzy = par<float>(p, "shadowFuzzyness", 1.f);
+		out.samples = par<int>(p, "samples", 8);
+	}
+	else if(type == "spherelight")
+	{	// light_sphere.cc:163-198
+		out.type = YAFGPU_LIGHT_SPHERE;
+		par3(p, "from", out.from, 0.f, 0.f, 0.f); out.radius = par<float>(p, "radius", 1.f);
+		out.object = par<int>(p, "object", 0); // a linked sphere primitive is refused by the library
+	}
 	else { err = "light type '" + type + "' is not implemented on the device"; return false; }
 	return true;
 }
@@ -368,17 +395,31 @@ bool GpuIntegrator::preprocess()
 		if(!lightRecord(scene_->lights_[i], obj_index_of_id, lights[i], err)) return fail(err);
 	d.lights = lights.data(); d.n_lights = scene_->lights_.size();
 
-	// camera "perspective" (camera_perspective.cc:206-252)
+	// camera factories: camera_perspective.cc:206-252, camera_architect.cc:100-133, camera_orthographic.cc:82-106,
+	// camera_angular.cc:100-133, camera_equirectangular.cc:82-108
 	{
 		auto it = rec().params.find(scene_->getCamera());
 		if(it == rec().params.end()) return fail("camera was not created through RenderEnvironment::createCamera");
 		const ParamMap &p = it->second;
-		if(par<std::string>(p, "type", "") != "perspective") return fail("camera type '" + par<std::string>(p, "type", "") + "' is not implemented on the device");
+		const std::string ctype = par<std::string>(p, "type", "");
 		yafgpu_camera &c = d.camera;
-		c.type = YAFGPU_CAM_PERSPECTIVE; c.resx = par<int>(p, "resx", 320); c.resy = par<int>(p, "resy", 200);
+		if(ctype == "perspective") c.type = YAFGPU_CAM_PERSPECTIVE;
+		else if(ctype == "architect") c.type = YAFGPU_CAM_ARCHITECT;
+		else if(ctype == "orthographic") c.type = YAFGPU_CAM_ORTHOGRAPHIC;
+		else if(ctype == "angular") c.type = YAFGPU_CAM_ANGULAR;
+		else if(ctype == "equirectangular") c.type = YAFGPU_CAM_EQUIRECTANGULAR;
+		else return fail("camera type '" + ctype + "' is not implemented on the device");
+		c.resx = par<int>(p, "resx", 320); c.resy = par<int>(p, "resy", 200);
 		par3(p, "from", c.from, 0.f, 1.f, 0.f); par3(p, "to", c.to, 0.f, 0.f, 0.f); par3(p, "up", c.up, 0.f, 1.f, 1.f);
 		c.focal = par<float>(p, "focal", 1.f); c.aperture = par<float>(p, "aperture", 0.f); c.dof_distance = par<float>(p, "dof_distance", 0.f);
-		c.aspect_ratio = par<float>(p, "aspect_ratio", 1.f); c.near_clip = par<float>(p, "nearClip", 0.f); c.far_clip = par<float>(p, "farClip", -1.f);
+		c.aspect_ratio = par<float>(p, "aspect_ratio", 1.f); c.near_clip = par<float>(p, "nearClip", 0.f);
+		c.far_clip = par<float>(p, "farClip", (ctype == "angular" || ctype == "equirectangular") ? -1.0e38f : -1.f);
+		c.scale = par<float>(p, "scale", 1.f);
+		c.angle = par<double>(p, "angle", 90.0); c.max_angle = par<double>(p, "max_angle", c.angle);
+		c.circular = par<bool>(p, "circular", true); c.mirrored = par<bool>(p, "mirrored", false);
+		const std::string proj = par<std::string>(p, "projection", "");
+		c.projection = proj == "orthographic" ? YAFGPU_AP_ORTHOGRAPHIC : proj == "stereographic" ? YAFGPU_AP_STEREOGRAPHIC
+		             : proj == "equisolid_angle" ? YAFGPU_AP_EQUISOLID : proj == "rectilinear" ? YAFGPU_AP_RECTILINEAR : YAFGPU_AP_EQUIDISTANT;
 		const std::string bt = par<std::string>(p, "bokeh_type", "disk1"), bb = par<std::string>(p, "bokeh_bias", "uniform");
 		c.bokeh_type = bt == "disk2" ? YAFGPU_BK_DISK2 : bt == "triangle" ? YAFGPU_BK_TRI : bt == "square" ? YAFGPU_BK_SQR : bt == "pentagon" ? YAFGPU_BK_PENTA
 		             : bt == "hexagon" ? YAFGPU_BK_HEXA : bt == "ring" ? YAFGPU_BK_RING : YAFGPU_BK_DISK1;
@@ -425,6 +466,15 @@ bool GpuIntegrator::preprocess()
 			const std::string mapping = par<std::string>(p, "mapping", "");
 			d.background.mapping_angular = mapping == "probe" || mapping == "angular";
 			d.background.rotation = par<float>(p, "rotation", 0.f);
+		}
+		else if(btype == "gradientback")
+		{	// background_gradient.cc:66-117
+			yafgpu_background &b = d.background;
+			b.type = YAFGPU_BG_GRADIENT;
+			parCol(p, "horizon_color", b.horizon_color, 1.f);
+			{ Rgb z(0.4f, 0.5f, 1.f); p.getParam("zenith_color", z); b.zenith_color[0] = z.r_; b.zenith_color[1] = z.g_; b.zenith_color[2] = z.b_; }
+			{ Rgb c(b.horizon_color[0], b.horizon_color[1], b.horizon_color[2]); p.getParam("horizon_ground_color", c); b.horizon_ground_color[0] = c.r_; b.horizon_ground_color[1] = c.g_; b.horizon_ground_color[2] = c.b_; }
+			{ Rgb c(b.zenith_color[0], b.zenith_color[1], b.zenith_color[2]); p.getParam("zenith_ground_color", c); b.zenith_ground_color[0] = c.r_; b.zenith_ground_color[1] = c.g_; b.zenith_ground_color[2] = c.b_; }
 		}
 		else return fail("background type '" + btype + "' is not implemented on the device");
 		d.background.power = par<float>(p, "power", 1.f); d.background.ibl = par<bool>(p, "ibl", false);

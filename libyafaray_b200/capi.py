@@ -9,18 +9,19 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("YAFGPU_LIB") or os.path.join(_HERE, "libyafgpu.so")  # YAFGPU_LIB: kernel-variant experiments (tools/)
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # enums (include/yafgpu.h)
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE, ERR_NOMEM = range(6)
 VIS_NORMAL, VIS_NO_SHADOWS, VIS_SHADOW_ONLY, VIS_INVISIBLE = range(4)
 (MAT_SHINYDIFFUSE, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_ROUGH_GLASS, MAT_BLEND, MAT_MIRROR, MAT_NULL,
  MAT_LIGHT) = range(9)
-LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND = range(5)
-CAM_PERSPECTIVE = 0
+LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE = range(8)
+CAM_PERSPECTIVE, CAM_ARCHITECT, CAM_ORTHOGRAPHIC, CAM_ANGULAR, CAM_EQUIRECTANGULAR = range(5)
+ANGULAR_PROJECTIONS = {"equidistant": 0, "orthographic": 1, "stereographic": 2, "equisolid_angle": 3, "rectilinear": 4}
 BK = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}
 BB = {"uniform": 0, "center": 1, "edge": 2}
-BG_NONE, BG_CONSTANT, BG_TEXTURE = range(3)
+BG_NONE, BG_CONSTANT, BG_TEXTURE, BG_GRADIENT = range(4)
 FILTERS = {"box": 0, "mitchell": 1, "gauss": 2, "lanczos": 3}
 INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
@@ -85,19 +86,22 @@ class Light(C.Structure):
     _fields_ = [("type", i32), ("light_enabled", i32), ("cast_shadows", i32), ("photon_only", i32), ("samples", i32),
                 ("object", i32), ("double_sided", i32), ("abs_intersect", i32), ("color", F3), ("power", f32),
                 ("from_", F3), ("point1", F3), ("point2", F3), ("angle", f32), ("clamp_intersect", f32),
-                ("shoot_caustic", i32), ("shoot_diffuse", i32), ("reserved", i32 * 2)]
+                ("shoot_caustic", i32), ("shoot_diffuse", i32), ("radius", f32), ("cone_angle", f32), ("blend", f32),
+                ("shadow_fuzzy", f32), ("soft_shadows", i32), ("infinite", i32)]
 
 
 class Camera(C.Structure):
     _fields_ = [("type", i32), ("resx", i32), ("resy", i32), ("from_", F3), ("to", F3), ("up", F3), ("focal", f32),
                 ("aperture", f32), ("dof_distance", f32), ("aspect_ratio", f32), ("near_clip", f32), ("far_clip", f32),
-                ("bokeh_type", i32), ("bokeh_bias", i32), ("bokeh_rotation", f32)]
+                ("bokeh_type", i32), ("bokeh_bias", i32), ("bokeh_rotation", f32), ("scale", f32), ("angle", C.c_double),
+                ("max_angle", C.c_double), ("circular", i32), ("mirrored", i32), ("projection", i32)]
 
 
 class Background(C.Structure):
     _fields_ = [("type", i32), ("color", F3), ("power", f32), ("ibl", i32), ("with_caustic", i32),
                 ("mapping_angular", i32), ("rotation", f32), ("tex_rgb", pf), ("tex_w", i32), ("tex_h", i32),
-                ("tex_interp", i32)]
+                ("tex_interp", i32), ("horizon_color", F3), ("zenith_color", F3), ("horizon_ground_color", F3),
+                ("zenith_ground_color", F3)]
 
 
 class FilmDesc(C.Structure):

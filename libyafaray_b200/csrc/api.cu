@@ -252,8 +252,16 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		s.bg.tex_w = bg.tex_w; s.bg.tex_h = bg.tex_h;
 		s.bg.tex = bg.tex_rgb; // host pointer while the light tables are built below; replaced by the device copy afterwards
 	}
+	else if(bg.type == YAFGPU_BG_GRADIENT)
+	{	// GradientBackground::factory background_gradient.cc:88: every colour * power; the constructor is handed with_caustic = true
+		for(int k = 0; k < 3; ++k)
+		{
+			s.bg.gzenith[k] = bg.zenith_ground_color[k] * bg.power; s.bg.ghoriz[k] = bg.horizon_ground_color[k] * bg.power;
+			s.bg.szenith[k] = bg.zenith_color[k] * bg.power; s.bg.shoriz[k] = bg.horizon_color[k] * bg.power;
+		}
+	}
 	else if(bg.type != YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "background type not implemented on the device yet");
-	s.bg.has_ibl = bg.ibl; s.bg.shoots_caustic = bg.with_caustic;
+	s.bg.has_ibl = bg.ibl; s.bg.shoots_caustic = bg.type == YAFGPU_BG_GRADIENT ? 1 : bg.with_caustic;
 	// light tables: MeshLight::initIs area CDFs, BackgroundLight::init row/column CDFs
 	std::vector<float> light_tab;
 	for(size_t i = 0; i < c->h_lights.size(); ++i)

@@ -222,8 +222,44 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 	d.type = l.type; d.enabled = l.light_enabled; d.cast_shadows = l.cast_shadows; d.photon_only = l.photon_only;
 	d.samples = l.samples; d.object = l.object; d.double_sided = l.double_sided; d.abs_intersect = l.abs_intersect;
 	d.clamp_intersect = l.clamp_intersect; d.shoot_caustic = l.shoot_caustic;
+	d.dirac = l.type == YAFGPU_LIGHT_POINT; d.can_intersect = l.type != YAFGPU_LIGHT_POINT; // sun, area, mesh (tree built), background
 	switch(l.type)
 	{
+		case YAFGPU_LIGHT_DIRECTIONAL: // DirectionalLight::DirectionalLight light_directional.cc:31-42 (+ factory :112-158)
+		{
+			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+			st3(d.fnormal, normalize(ld3(l.point1)));
+			cp3(d.pos, l.from); d.area = l.radius; d.double_sided = !l.infinite;
+			d.dirac = 1; d.can_intersect = 0;
+			return true;
+		}
+		case YAFGPU_LIGHT_SPOT: // SpotLight::SpotLight light_spot.cc:28-69
+		{
+			const V3 from = ld3(l.from), to = ld3(l.point1);
+			const V3 ndir = normalize(from - to), dir = -ndir;
+			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+			V3 du, dv;
+			createCs(dir, du, dv);
+			const double rad_angle = (double)l.cone_angle * 0.01745329251994329576922;
+			const double rad_inner_angle = rad_angle * (double)(1.f - l.blend);
+			d.pdf = fCos((float)rad_inner_angle);   // cos_start_
+			d.cos_angle = fCos((float)rad_angle);   // cos_end_
+			d.invpdf = (float)(1.0 / (double)(d.pdf - d.cos_angle)); // icos_diff_
+			d.area = l.shadow_fuzzy;
+			cp3(d.pos, l.from); st3(d.fnormal, ndir); st3(d.normal, dir); st3(d.du, du); st3(d.dv, dv);
+			d.dirac = !l.soft_shadows; d.can_intersect = l.soft_shadows != 0;
+			return true;
+		}
+		case YAFGPU_LIGHT_SPHERE: // SphereLight::SphereLight light_sphere.cc:31-41
+		{
+			if(l.object > 0) { err = "spherelight linked to a sphere primitive is not supported"; return false; }
+			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+			cp3(d.pos, l.from);
+			d.area = l.radius * l.radius;                           // square_radius_
+			d.inv_area = (float)((double)d.area * 1.000003815);     // square_radius_epsilon_
+			d.dirac = 0; d.can_intersect = 0;
+			return true;
+		}
 		case YAFGPU_LIGHT_POINT: // PointLight::PointLight light_point.cc:29-36
 			for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
 			cp3(d.pos, l.from);
@@ -352,10 +388,13 @@ inline void buildBgLightTables(const BackgroundDev &bg, LightDev &d, std::vector
 inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
 {
 	memset(&d, 0, sizeof(d));
-	if(c.type != YAFGPU_CAM_PERSPECTIVE) { err = "camera type not implemented on the device"; return false; }
+	if(c.type < YAFGPU_CAM_PERSPECTIVE || c.type > YAFGPU_CAM_EQUIRECTANGULAR) { err = "camera type not implemented on the device"; return false; }
+	d.type = c.type;
 	d.resx = c.resx; d.resy = c.resy;
+	// Camera::Camera camera.cc:46-66
 	const V3 pos = ld3(c.from), look = ld3(c.to), up = ld3(c.up);
 	const float aspect_ratio = c.aspect_ratio * (float)c.resy / (float)c.resx;
+	d.aspect_ratio = aspect_ratio;
 	V3 cam_y = up - pos, cam_z = look - pos;
 	V3 cam_x = cross(cam_z, cam_y);
 	cam_y = cross(cam_z, cam_x);
@@ -363,15 +402,46 @@ inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
 	st3(d.near_n, cam_z);
 	st3(d.near_p, pos + cam_z * c.near_clip);
 	st3(d.far_p, pos + cam_z * c.far_clip);
+	st3(d.pos, pos); st3(d.cam_to, cam_z);
+	if(c.type == YAFGPU_CAM_ORTHOGRAPHIC)
+	{	// OrthographicCamera::setAxis camera_orthographic.cc:37-50
+		V3 vright = cam_x, vup = aspect_ratio * cam_y;
+		// pos_ = position_ - 0.5 * scale_ * (vup_ + vright_): (0.5 * scale_) is a double, operator*(float, Vec3) narrows it
+		const V3 p0 = pos - (float)(0.5 * (double)c.scale) * (vup + vright);
+		vup = vup * (c.scale / (float)c.resy);
+		vright = vright * (c.scale / (float)c.resx);
+		st3(d.pos, p0); st3(d.vright, vright); st3(d.vup, vup);
+		return true;
+	}
+	if(c.type == YAFGPU_CAM_ANGULAR)
+	{	// AngularCamera::AngularCamera camera_angular.cc:28-55, factory :100-133
+		const float angle = (float)(c.angle * YG_M_PI / (double)180.f), max_angle = (float)(c.max_angle * YG_M_PI / (double)180.f);
+		d.max_radius = max_angle / angle; d.circular = c.circular; d.projection = c.projection;
+		if(c.projection == YAFGPU_AP_ORTHOGRAPHIC) d.focal_length = 1.f / fSin(angle);
+		else if(c.projection == YAFGPU_AP_STEREOGRAPHIC) d.focal_length = (float)((double)(1.f / 2.f) / tan((double)(angle / 2.f)));
+		else if(c.projection == YAFGPU_AP_EQUISOLID) d.focal_length = 1.f / 2.f / fSin(angle / 2.f);
+		else if(c.projection == YAFGPU_AP_RECTILINEAR) d.focal_length = (float)((double)1.f / tan((double)angle));
+		else d.focal_length = 1.f / angle;
+		V3 vright = cam_x;
+		if(c.mirrored) vright = vright * (float)-1.0;
+		st3(d.vright, vright); st3(d.vup, cam_y);
+		return true;
+	}
+	if(c.type == YAFGPU_CAM_EQUIRECTANGULAR)
+	{	// EquirectangularCamera::setAxis camera_equirectangular.cc:38-48
+		st3(d.vright, cam_x); st3(d.vup, cam_y);
+		return true;
+	}
+	// PerspectiveCamera::PerspectiveCamera / setAxis camera_perspective.cc:29-74; ArchitectCamera::setAxis camera_architect.cc:52-66
 	d.aperture = c.aperture; d.dof_distance = c.dof_distance;
 	st3(d.dof_rt, c.aperture * cam_x); st3(d.dof_up, c.aperture * cam_y);
 	V3 vright = cam_x;
-	V3 vup = aspect_ratio * cam_y;
+	V3 vup = c.type == YAFGPU_CAM_ARCHITECT ? aspect_ratio * mk(0.f, 0.f, -1.f) : aspect_ratio * cam_y;
 	// vto = (camZ * focal) - 0.5 * (vup + vright): 0.5 is double -> operator*(float, Vec3) narrows it to float first
 	V3 vto = (cam_z * c.focal) - 0.5f * (vup + vright);
 	vup = vup / (float)c.resy;
 	vright = vright / (float)c.resx;
-	st3(d.pos, pos); st3(d.vright, vright); st3(d.vup, vup); st3(d.vto, vto);
+	st3(d.vright, vright); st3(d.vup, vup); st3(d.vto, vto);
 	d.bokeh_type = c.bokeh_type; d.bokeh_bias = c.bokeh_bias; d.n_ls = 0;
 	int ns = c.bokeh_type;
 	if(ns >= 3 && ns <= 6)

@@ -176,15 +176,51 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, cons
 		const SlotInfo si = slotInfo(wp, pixels, slot);
 		float dx, dy;
 		samplePos(wp, si, dx, dy);
-		// PerspectiveCamera::shootRay camera_perspective.cc:133-155
 		const CameraDev &c = sc.cam;
 		const float px = (float)si.x + dx, py = (float)si.y + dy;
-		V3 from = ldv(c.pos);
-		V3 dir = normalize((ldv(c.vright) * px + ldv(c.vup) * py) + ldv(c.vto));
+		V3 from = ldv(c.pos), dir;
+		bool dead = false; // Camera::shootRay returned wt = 0: the film gets a black sample (integrator_tiled.cc:412-416)
+		switch(c.type)
+		{
+			case YAFGPU_CAM_ORTHOGRAPHIC: // OrthographicCamera::shootRay camera_orthographic.cc:53-64
+				from = (from + ldv(c.vright) * px) + ldv(c.vup) * py;
+				dir = ldv(c.cam_to);
+				break;
+			case YAFGPU_CAM_ANGULAR: // AngularCamera::shootRay camera_angular.cc:57-85 (asin/atan/atan2 are the double overloads there)
+			{
+				const float u = 1.f - 2.f * (px / (float)c.resx);
+				float v = 2.f * (py / (float)c.resy) - 1.f;
+				v *= c.aspect_ratio;
+				const float radius = fSqrt(u * u + v * v);
+				dir = ldv(c.cam_to);
+				if(c.circular && radius > c.max_radius) { dead = true; break; }
+				float theta = 0.f;
+				if(!((u == 0) && (v == 0))) theta = (float)atan2((double)v, (double)u);
+				float phi;
+				if(c.projection == YAFGPU_AP_ORTHOGRAPHIC) phi = (float)asin((double)(radius / c.focal_length));
+				else if(c.projection == YAFGPU_AP_STEREOGRAPHIC) phi = (float)((double)2.f * atan((double)(radius / (2.f * c.focal_length))));
+				else if(c.projection == YAFGPU_AP_EQUISOLID) phi = (float)((double)2.f * asin((double)(radius / (2.f * c.focal_length))));
+				else if(c.projection == YAFGPU_AP_RECTILINEAR) phi = (float)atan((double)(radius / c.focal_length));
+				else phi = radius / c.focal_length;
+				dir = fSin(phi) * (fCos(theta) * ldv(c.vright) + fSin(theta) * ldv(c.vup)) + fCos(phi) * ldv(c.cam_to);
+				break;
+			}
+			case YAFGPU_CAM_EQUIRECTANGULAR: // EquirectangularCamera::shootRay camera_equirectangular.cc:50-66
+			{
+				const float u = 2.f * px / (float)c.resx - 1.f;
+				const float v = 2.f * py / (float)c.resy - 1.f;
+				const float phi = (float)(YG_M_PI * (double)u);
+				const float theta = (float)(1.57079632679489661923 * (double)v);
+				dir = fCos(theta) * (fCos(phi) * ldv(c.cam_to) + fSin(phi) * ldv(c.vright)) + fSin(theta) * ldv(c.vup);
+				break;
+			}
+			default: // PerspectiveCamera::shootRay camera_perspective.cc:133-155 (ArchitectCamera inherits it)
+				dir = normalize((ldv(c.vright) * px + ldv(c.vup) * py) + ldv(c.vto));
+		}
 		const V3 nn = ldv(c.near_n);
 		// rayPlaneIntersection__ util_geometry.h:34-37 (near and far plane share the normal)
 		const float tmin = dot(nn, ldv(c.near_p) - from) / dot(dir, nn);
-		const float tmax = dot(nn, ldv(c.far_p) - from) / dot(dir, nn);
+		float tmax = dot(nn, ldv(c.far_p) - from) / dot(dir, nn);
 		if(c.aperture != 0)
 		{
 			HaltonB<3> hu; HaltonB<5> hv;
@@ -197,9 +233,12 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, cons
 			from = from + li;
 			dir = normalize((dir * c.dof_distance) - li);
 		}
+		// a dead sample travels as a zero-length ray of zero weight: it misses everything and adds nothing, k_film_add still counts its filter weight
+		const float w0 = dead ? 0.f : 1.f;
+		if(dead) tmax = 0.f;
 		q.ray_o[slot] = make_float4(from.x, from.y, from.z, tmin);
 		q.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, tmax);
-		q.wgt[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+		q.wgt[slot] = make_float4(w0, w0, w0, 0.f);
 		q.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
 		q.st[slot] = make_uint4((unsigned)slot, 0u, packState(TASK_INTEGRATE, 0, 0, 1, 0, 0), 0u);
 		q.dc[slot] = make_float2(0.f, 0.f);
@@ -425,7 +464,7 @@ YG_DLE void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, 
 	const unsigned l_offs = loffs * 4567u;
 	const float plen = length(sp.p);
 	const float sh_tmin = sc.integ.shadow_bias_auto ? sc.integ.shadow_bias * fmaxf(1.f, plen) : sc.integ.shadow_bias;
-	if(lightIsDirac(L.type))
+	if(lightIsDirac(L))
 	{
 		Col lcol; V3 ldir; float tmax;
 		if(lightIlluminate(L, sp, lcol, ldir, tmax))
@@ -442,7 +481,7 @@ YG_DLE void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, 
 	if(ray_division > 1) n = max(1, n / ray_division);
 	const float inv_ns = 1.f / (float)n;
 	const unsigned offs = (unsigned)n * (unsigned)si.pixel_sample + si.sampling_offs + l_offs;
-	const bool can_intersect = lightCanIntersect(L.type) && !(L.type == YAFGPU_LIGHT_MESH && L.accel < 0);
+	const bool can_intersect = lightCanIntersect(L) && !(L.type == YAFGPU_LIGHT_MESH && L.accel < 0);
 	Halton2 hal_2; HaltonB<3> hal_3;
 	hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
 	const double hal_3_start = hal_3.value; // the BSDF loop below restarts both sequences at the same element

@@ -14,8 +14,8 @@
 
 namespace yg {
 
-YG_HD bool lightIsDirac(int type) { return type == YAFGPU_LIGHT_POINT; }
-YG_HD bool lightCanIntersect(int type) { return type != YAFGPU_LIGHT_POINT; } // sun, area, mesh (tree built), background
+YG_HD bool lightIsDirac(const LightDev &L) { return L.dirac != 0; }          // Light::diracLight() (host_prep.h prepLight)
+YG_HD bool lightCanIntersect(const LightDev &L) { return L.can_intersect != 0; } // Light::canIntersect()
 
 // ---- background ------------------------------------------------------------------------------------------------------
 YG_HD void spheremap(V3 p, float &u, float &v)
@@ -93,6 +93,19 @@ YG_HD Col texLookup(const BackgroundDev &bg, float u, float v)
 // Background::eval / operator(): ConstantBackground (background_constant.cc:41-49), TextureBackground (background_texture.cc:51-88)
 YG_HD Col bgEval(const BackgroundDev &bg, V3 dir)
 {
+	if(bg.type == YAFGPU_BG_GRADIENT)
+	{	// GradientBackground::eval background_gradient.cc:39-58
+		Col color;
+		float blend = dir.z;
+		if(blend >= 0.f) color = blend * mkc(bg.szenith[0], bg.szenith[1], bg.szenith[2]) + (1.f - blend) * mkc(bg.shoriz[0], bg.shoriz[1], bg.shoriz[2]);
+		else
+		{
+			blend = -blend;
+			color = blend * mkc(bg.gzenith[0], bg.gzenith[1], bg.gzenith[2]) + (1.f - blend) * mkc(bg.ghoriz[0], bg.ghoriz[1], bg.ghoriz[2]);
+		}
+		if(fminf(color.r, fminf(color.g, color.b)) < 1e-6f) color = mkc(1e-5f);
+		return color;
+	}
 	if(bg.type != YAFGPU_BG_TEXTURE) return mkc(bg.color[0], bg.color[1], bg.color[2]); // constant: col * power
 	float u = 0.f, v = 0.f;
 	if(bg.mapping_angular)
@@ -193,18 +206,67 @@ YG_HD float bgCalcFromDir(const float *tab, const LightDev &L, V3 dir, float &u,
 
 // ---- lights ------------------------------------------------------------------------------------------------------------
 
-// PointLight::illuminate light_point.cc:38-56
+// SpotLight falloff (light_spot.cc:105-114 and :139-148): false outside the cone, else the smoothstep factor (1 inside cos_start_)
+YG_D bool spotFalloff(const LightDev &L, float cosa, float &v, bool &full)
+{
+	if(cosa < L.cos_angle) return false;
+	full = cosa >= L.pdf;
+	if(!full) { v = (cosa - L.cos_angle) * L.invpdf; v = v * v * (3.f - 2.f * v); }
+	return true;
+}
+
+// Light::illuminate of the dirac lights: PointLight light_point.cc:38-56, DirectionalLight light_directional.cc:59-81,
+// SpotLight (soft_shadows off) light_spot.cc:88-120
 YG_D bool lightIlluminate(const LightDev &L, const SurfPt &sp, Col &col, V3 &dir, float &tmax)
 {
 	if(L.photon_only) return false;
+	if(L.type == YAFGPU_LIGHT_DIRECTIONAL)
+	{
+		const V3 direction = ldv(L.fnormal);
+		if(L.double_sided) // finite: inside the illuminated cylinder only
+		{
+			const V3 vec = ldv(L.pos) - sp.p;
+			const float dist = length(cross(direction, vec));
+			if(dist > L.area) return false;
+			tmax = dot(vec, direction);
+			if(tmax <= 0.0f) return false;
+		}
+		else tmax = -1.0f;
+		dir = direction;
+		col = ldc(L.color);
+		return true;
+	}
 	V3 ldir = ldv(L.pos) - sp.p;
 	const float dist_sqr = ldir.x * ldir.x + ldir.y * ldir.y + ldir.z * ldir.z;
 	const float dist = fSqrt(dist_sqr);
 	if(dist == 0.0f) return false;
 	const float idist_sqr = 1.f / dist_sqr;
 	ldir = ldir * (1.f / dist);
+	if(L.type == YAFGPU_LIGHT_SPOT)
+	{
+		float v = 0.f; bool full = false;
+		if(!spotFalloff(L, dot(ldv(L.fnormal), ldir), v, full)) return false;
+		col = full ? ldc(L.color) * idist_sqr : ldc(L.color) * (v * idist_sqr);
+		tmax = dist; dir = ldir;
+		return true;
+	}
 	tmax = dist; dir = ldir;
 	col = ldc(L.color) * idist_sqr;
+	return true;
+}
+
+// sphereIntersect__ light_sphere.cc:56-68: eb, osc and the roots are formed in double (2.0, 4.0 literals)
+YG_D bool sphereIntersect(V3 from, V3 dir, V3 c, float r_2, float &d_1, float &d_2)
+{
+	const V3 vf = from - c;
+	const float ea = dot(dir, dir);
+	const float eb = dot(2.0f * vf, dir);
+	const float ec = dot(vf, vf) - r_2;
+	float osc = (float)((double)(eb * eb) - 4.0 * (double)ea * (double)ec);
+	if(osc < 0) { d_1 = fSqrt(ec / ea); return false; }
+	osc = fSqrt(osc);
+	d_1 = (float)((double)(-eb - osc) / (2.0 * (double)ea));
+	d_2 = (float)((double)(-eb + osc) / (2.0 * (double)ea));
 	return true;
 }
 
@@ -266,6 +328,41 @@ YG_D bool lightIllumSample(const SceneDev &sc, const LightDev &L, const SurfPt &
 			col = ldc(L.color);
 			const float amc = L.area * cos_angle;
 			pdf = (float)((double)dist_sqr * YG_M_PI / (double)((amc == 0.f) ? 1e-8f : amc));
+			return true;
+		}
+		case YAFGPU_LIGHT_SPOT: // SpotLight::illumSample light_spot.cc:122-164
+		{
+			V3 ldir = ldv(L.pos) - sp.p;
+			const float dist_sqr = dot(ldir, ldir);
+			if(dist_sqr == 0.0f) return false;
+			const float dist = fSqrt(dist_sqr);
+			ldir = ldir * (1.f / dist);
+			float v = 0.f; bool full = false;
+			if(!spotFalloff(L, dot(ldv(L.fnormal), ldir), v, full)) return false;
+			tmax = dist;
+			dir = sampleCone(ldir, ldv(L.du), ldv(L.dv), L.cos_angle, s1 * L.area, s2 * L.area);
+			col = full ? ldc(L.color) : ldc(L.color) * v;
+			pdf = dist_sqr;
+			if(pdf < 1.f) { pdf = 1.f; col = col / dist_sqr; }
+			return true;
+		}
+		case YAFGPU_LIGHT_SPHERE: // SphereLight::illumSample light_sphere.cc:70-103
+		{
+			V3 cdir = ldv(L.pos) - sp.p;
+			const float dist_sqr = lengthSqr(cdir);
+			if(dist_sqr <= L.area) return false;
+			const float dist = fSqrt(dist_sqr);
+			const float idist_sqr = 1.f / dist_sqr;
+			const float cos_alpha = fSqrt(1.f - L.area * idist_sqr);
+			cdir = cdir * (1.f / dist);
+			V3 du, dv;
+			createCs(cdir, du, dv);
+			dir = sampleCone(cdir, du, dv, cos_alpha, s1, s2);
+			float d_1, d_2;
+			if(!sphereIntersect(sp.p, dir, ldv(L.pos), L.inv_area, d_1, d_2)) return false;
+			tmax = d_1;
+			pdf = 1.f / (2.f * (1.f - cos_alpha));
+			col = ldc(L.color);
 			return true;
 		}
 		case YAFGPU_LIGHT_BACKGROUND:
@@ -344,6 +441,27 @@ YG_D bool lightIntersect(const SceneDev &sc, const LightDev &L, V3 from, V3 dir,
 			ipdf = idist_sqr * L.area * cos_angle * (float)(1.f / YG_M_PI);
 			col = ldc(L.color);
 			return true;
+		}
+		case YAFGPU_LIGHT_SPOT: // SpotLight::intersect light_spot.cc:215-249 (soft_shadows on)
+		{
+			const V3 sdir = ldv(L.normal);
+			const float cos_a = dot(sdir, dir);
+			if(cos_a == 0.f) return false;
+			t = dot(sdir, ldv(L.pos) - from) / cos_a;
+			if(t < 0.f) return false;
+			const V3 p = from + t * dir;
+			if(dot(sdir, p - ldv(L.pos)) == 0)
+			{
+				if((double)dot(p, p) <= 1e-2) // sic: the hit point's squared distance from the ORIGIN
+				{
+					float v = 0.f; bool full = false;
+					if(!spotFalloff(L, cos_a, v, full)) return false;
+					col = full ? ldc(L.color) : ldc(L.color) * v;
+					ipdf = 1.f / (t * t);
+					return true;
+				}
+			}
+			return false;
 		}
 		case YAFGPU_LIGHT_BACKGROUND:
 		{

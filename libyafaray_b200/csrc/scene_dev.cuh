@@ -96,6 +96,10 @@ struct LightDev
 	int tri_first, tri_count;
 	int accel;          // mesh light: index into SceneDev::light_accels (its own BVH, as MeshLight builds its own kd-tree), -1 = none
 	float clamp_intersect; int shoot_caustic;
+	int dirac, can_intersect;   // Light::diracLight() / canIntersect() (the spot light's depend on "soft_shadows")
+	// directional (pos = position_, fnormal = direction_, area = radius_, double_sided = !infinite_), spot (pos, fnormal = ndir_, normal = dir_,
+	// du/dv, cos_angle = cos_end_, pdf = cos_start_, invpdf = icos_diff_, area = shadow_fuzzy_), sphere (pos = center, area = radius^2,
+	// inv_area = radius^2 * 1.000003815)
 };
 
 struct CameraDev
@@ -105,6 +109,10 @@ struct CameraDev
 	float aperture, dof_distance;
 	int resx, resy, bokeh_type, bokeh_bias, n_ls;
 	float ls[20];
+	int type;                    // yafgpu_camera_type; architect and perspective differ only in the host-side axes
+	float aspect_ratio;          // Camera::aspect_ratio_ = aspect * resy / resx (camera.cc:47)
+	float cam_to[3];             // orthographic / angular / equirectangular: vto_ = cam_z_ (vright/vup hold their own vright_/vup_)
+	float max_radius, focal_length; int circular, projection; // angular (camera_angular.cc:28-42)
 };
 
 struct BackgroundDev
@@ -115,6 +123,7 @@ struct BackgroundDev
 	// as ImageHandler::getPixel(x, y) returns them, row y at tex + 3 * y * tex_w (device pointer in kernels, host pointer while the
 	// background-light tables are built)
 	int mapping_angular; float rotation, sin_r, cos_r, power; const float *tex; int tex_w, tex_h, tex_interp;
+	float gzenith[3], ghoriz[3], szenith[3], shoriz[3]; // gradient: colours * power (background_gradient.cc:88)
 };
 
 struct IntegratorDev

@@ -345,6 +345,19 @@ class Interface:
             l.type = capi.LIGHT_MESH
             l.object = obj_index_of_id(int(g(p, "object", 0)))
             l.double_sided = int(g(p, "double_sided", False))
+        elif t == "directional":  # light_directional.cc:112-158
+            l.type, l.point1, l.infinite = capi.LIGHT_DIRECTIONAL, pt("direction", (0, 0, 1)), int(g(p, "infinite", True))
+            if not l.infinite:
+                l.from_ = pt("from", g(p, "position", (0, 0, 0)))
+                l.radius = g(p, "radius", 1.0)
+        elif t == "spotlight":  # light_spot.cc:251-295
+            l.type, l.from_, l.point1 = capi.LIGHT_SPOT, pt("from", (0, 0, 0)), pt("to", (0, 0, -1))
+            l.cone_angle, l.blend = g(p, "cone_angle", 45.0), g(p, "blend", 0.15)
+            l.soft_shadows, l.shadow_fuzzy, l.samples = int(g(p, "soft_shadows", False)), g(p, "shadowFuzzyness", 1.0), int(g(p, "samples", 8))
+        elif t == "spherelight":  # light_sphere.cc:163-198
+            l.type, l.from_, l.radius = capi.LIGHT_SPHERE, pt("from", (0, 0, 0)), g(p, "radius", 1.0)
+            if int(g(p, "object", 0)) != 0:
+                raise NotImplementedError("spherelight linked to a sphere primitive ('object')")
         else:
             raise NotImplementedError("light type '%s'" % t)
         return l
@@ -479,19 +492,29 @@ class Interface:
         d.lights, d.n_lights = larr, len(lts)
         keep += [mats, objarr, larr]
 
-        # camera "perspective" (camera_perspective.cc:206-252)
+        # cameras (camera_perspective.cc:206-252, camera_architect.cc:100-133, camera_orthographic.cc:82-106,
+        # camera_angular.cc:100-133, camera_equirectangular.cc:82-108)
         cp = self.cameras[g(rp, "camera_name", next(iter(self.cameras)))]
-        if g(cp, "type", "") != "perspective":
-            raise NotImplementedError("camera type '%s'" % g(cp, "type", ""))
+        ctype = g(cp, "type", "")
+        cam_types = {"perspective": capi.CAM_PERSPECTIVE, "architect": capi.CAM_ARCHITECT, "orthographic": capi.CAM_ORTHOGRAPHIC,
+                     "angular": capi.CAM_ANGULAR, "equirectangular": capi.CAM_EQUIRECTANGULAR}
+        if ctype not in cam_types:
+            raise NotImplementedError("camera type '%s'" % ctype)
         c = d.camera
-        c.type, c.resx, c.resy = capi.CAM_PERSPECTIVE, int(g(cp, "resx", 320)), int(g(cp, "resy", 200))
+        c.type, c.resx, c.resy = cam_types[ctype], int(g(cp, "resx", 320)), int(g(cp, "resy", 200))
         c.from_ = capi.F3(*[np.float32(x) for x in g(cp, "from", (0, 1, 0))])
         c.to = capi.F3(*[np.float32(x) for x in g(cp, "to", (0, 0, 0))])
         c.up = capi.F3(*[np.float32(x) for x in g(cp, "up", (0, 1, 1))])
         c.focal, c.aperture, c.dof_distance = g(cp, "focal", 1.0), g(cp, "aperture", 0.0), g(cp, "dof_distance", 0.0)
-        c.aspect_ratio, c.near_clip, c.far_clip = g(cp, "aspect_ratio", 1.0), g(cp, "nearClip", 0.0), g(cp, "farClip", -1.0)
+        c.aspect_ratio, c.near_clip = g(cp, "aspect_ratio", 1.0), g(cp, "nearClip", 0.0)
+        c.far_clip = g(cp, "farClip", -1.0e38 if ctype in ("angular", "equirectangular") else -1.0)
         c.bokeh_type, c.bokeh_bias = capi.BK.get(g(cp, "bokeh_type", "disk1"), 0), capi.BB.get(g(cp, "bokeh_bias", "uniform"), 0)
         c.bokeh_rotation = g(cp, "bokeh_rotation", 0.0)
+        c.scale = g(cp, "scale", 1.0)
+        c.angle = float(g(cp, "angle", 90.0))
+        c.max_angle = float(g(cp, "max_angle", c.angle))
+        c.circular, c.mirrored = int(g(cp, "circular", True)), int(g(cp, "mirrored", False))
+        c.projection = capi.ANGULAR_PROJECTIONS.get(g(cp, "projection", ""), 0)
 
         # background (background_constant.cc:52-86)
         b = d.background
@@ -513,6 +536,12 @@ class Interface:
                 b.rotation = g(bp, "rotation", 0.0)
                 if g(bp, "smartibl_blur", 0.0) > 0:
                     raise NotImplementedError("textureback: smartibl_blur (mipmapped IBL) is not implemented on the device")
+            elif btype == "gradientback":  # background_gradient.cc:66-117
+                b.type = capi.BG_GRADIENT
+                col = lambda key, dflt: capi.F3(*[np.float32(x) for x in g(bp, key, dflt)[:3]])
+                b.horizon_color, b.zenith_color = col("horizon_color", (1, 1, 1, 1)), col("zenith_color", (0.4, 0.5, 1.0, 1))
+                b.horizon_ground_color = col("horizon_ground_color", tuple(b.horizon_color))
+                b.zenith_ground_color = col("zenith_ground_color", tuple(b.zenith_color))
             else:
                 raise NotImplementedError("background type '%s'" % btype)
             b.power, b.ibl, b.with_caustic = g(bp, "power", 1.0), int(g(bp, "ibl", False)), int(g(bp, "with_caustic", True))

@@ -92,8 +92,18 @@ TRACE = {
 TRACE_BOUNDS = {"simple": ((-14, -14, -4), (14, 14, 6)), "cornell": ((-1.4, -1.4, -0.4), (1.4, 1.4, 2.4)), "grid64": ((-5, -5, -1), (5, 5, 2))}
 
 
+def _set_params(y, kw):
+    for k, v in kw.items():
+        if isinstance(v, bool): y.paramsSetBool(k, v)
+        elif isinstance(v, int): y.paramsSetInt(k, v)
+        elif isinstance(v, float): y.paramsSetFloat(k, v)
+        elif isinstance(v, str): y.paramsSetString(k, v)
+        elif len(v) == 3: y.paramsSetPoint(k, *v)
+        else: y.paramsSetColor(k, *v)
+
+
 def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, only_mat=None,
-                       hdr_env=None, **integ):
+                       hdr_env=None, extra_lights=(), camera=None, gradient=None, **integ):
     """Every material and light type of the hot path in one small scene (configs 3/4 in miniature): glossy, coated_glossy,
     rough_glass, blend_mat, mirror, glass and shinydiffuse boxes on a ground quad; sun + mesh light + constant-background IBL."""
     from libyafaray_b200.interface import Interface
@@ -144,10 +154,17 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
     if sun:
         y.paramsClearAll(); y.paramsSetString("type", "sunlight"); y.paramsSetPoint("direction", 0.4, -0.5, 0.8); y.paramsSetFloat("angle", 2.0)
         y.paramsSetColor("color", 1.0, 0.9, 0.8); y.paramsSetFloat("power", 1.2); y.paramsSetInt("samples", 2); y.createLight("sun")
+    for i, lp in enumerate(extra_lights):  # dicts of light parameters; 3-tuples are points, 4-tuples colours
+        y.paramsClearAll(); _set_params(y, lp); y.createLight("extra%d" % i)
     y.paramsClearAll(); y.paramsSetString("type", "perspective")
     y.paramsSetPoint("from", 0.5, -7.5, 4.0); y.paramsSetPoint("to", 0.0, 0.8, 0.6); y.paramsSetPoint("up", 0.5, -7.5, 5.0)
-    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3); y.createCamera("cam")
-    if hdr_env:
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3)
+    if camera:
+        _set_params(y, camera)
+    y.createCamera("cam")
+    if gradient is not None:
+        y.paramsClearAll(); y.paramsSetString("type", "gradientback"); _set_params(y, gradient)
+    elif hdr_env:
         # equirectangular HDR environment ("textureback" + image texture): hdr_env = {"mapping": ..., "rotation": ..., "interpolate": ...}
         y.paramsClearAll(); y.paramsSetString("type", "image"); y.paramsSetString("filename", ENV_HDR)
         y.paramsSetString("interpolate", hdr_env.get("interpolate", "bilinear")); y.createTexture("envtex")
@@ -185,6 +202,33 @@ for _bk, _bias, _rot in (("disk1", "uniform", 0.0), ("disk2", "edge", 0.0), ("ri
         "aperture": 0.12, "dof_distance": 3.2, "bokeh_type": bk, "bokeh_bias": bias, "bokeh_rotation": rot}))
 EXACT["zoo_dl_ao"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, sun=False, do_AO=True, AO_samples=4, AO_distance=1.5)
 EXACT["zoo_dl_transpshad"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, transp_shad=True)
+
+# §8f rank 2: the remaining light types, camera types and the gradient background
+_ZOO_DL = dict(integrator="directlighting", raydepth=3, sun=False, meshlight=False, ibl=False)
+EXACT["zoo_dl_directional"] = lambda: material_zoo_scene(96, 54, 2, extra_lights=[
+    {"type": "directional", "direction": (0.3, -0.4, 0.85), "color": (1.0, 0.95, 0.9, 1.0), "power": 1.1},
+    {"type": "directional", "direction": (-0.5, 0.2, 0.8), "infinite": False, "from": (-1.5, 0.5, 0.0), "radius": 2.2, "color": (0.4, 0.6, 1.0, 1.0), "power": 2.0}], **_ZOO_DL)
+EXACT["zoo_dl_spot"] = lambda: material_zoo_scene(96, 54, 2, extra_lights=[
+    {"type": "spotlight", "from": (-2.0, -3.0, 5.0), "to": (-0.5, 0.8, 0.0), "cone_angle": 28.0, "blend": 0.4, "color": (1.0, 0.9, 0.7, 1.0), "power": 40.0},
+    {"type": "spotlight", "from": (0.3, 0.2, 0.6), "to": (2.0, 1.0, 0.0), "cone_angle": 50.0, "blend": 0.1, "color": (0.5, 0.7, 1.0, 1.0), "power": 1.5}], **_ZOO_DL)
+EXACT["zoo_dl_spot_soft"] = lambda: material_zoo_scene(96, 54, 2, extra_lights=[
+    {"type": "spotlight", "from": (2.5, -2.0, 4.5), "to": (0.5, 1.0, 0.0), "cone_angle": 35.0, "blend": 0.3, "soft_shadows": True, "shadowFuzzyness": 0.8,
+     "samples": 3, "color": (1.0, 1.0, 0.9, 1.0), "power": 35.0}], **_ZOO_DL)
+EXACT["zoo_dl_sphere"] = lambda: material_zoo_scene(96, 54, 2, extra_lights=[
+    {"type": "spherelight", "from": (0.5, 0.0, 3.0), "radius": 0.45, "samples": 3, "color": (1.0, 0.9, 0.8, 1.0), "power": 12.0}], **_ZOO_DL)
+EXACT["zoo_pt_sphere_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, meshlight=False, rr_min_bounces=99, extra_lights=[
+    {"type": "spherelight", "from": (0.5, 0.0, 3.0), "radius": 0.45, "samples": 2, "color": (1.0, 0.9, 0.8, 1.0), "power": 12.0}])
+EXACT["zoo_dl_gradient_ibl"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, sun=False, meshlight=False, ibl=True, gradient={
+    "horizon_color": (0.9, 0.8, 0.7, 1.0), "zenith_color": (0.2, 0.4, 0.9, 1.0), "horizon_ground_color": (0.3, 0.25, 0.2, 1.0),
+    "zenith_ground_color": (0.05, 0.05, 0.04, 1.0), "power": 1.3})
+_CAM_LIGHT = dict(integrator="directlighting", raydepth=3, ibl=False)
+EXACT["zoo_dl_cam_ortho"] = lambda: material_zoo_scene(96, 54, 2, camera={"type": "orthographic", "scale": 9.5}, **_CAM_LIGHT)
+EXACT["zoo_dl_cam_architect"] = lambda: material_zoo_scene(96, 54, 2, camera={"type": "architect", "focal": 1.1, "aperture": 0.05, "dof_distance": 8.0,
+                                                                             "bokeh_type": "pentagon", "bokeh_rotation": 10.0}, **_CAM_LIGHT)
+EXACT["zoo_dl_cam_angular"] = lambda: material_zoo_scene(96, 54, 2, camera={"type": "angular", "angle": 55.0, "max_angle": 50.0, "circular": True}, **_CAM_LIGHT)
+EXACT["zoo_dl_cam_angular_stereo"] = lambda: material_zoo_scene(96, 54, 2, camera={"type": "angular", "angle": 70.0, "circular": False, "mirrored": True,
+                                                                                  "projection": "stereographic"}, **_CAM_LIGHT)
+EXACT["zoo_dl_cam_equirect"] = lambda: material_zoo_scene(96, 48, 2, camera={"type": "equirectangular"}, **_CAM_LIGHT)
 
 # rendered only through the reference front end with the GPU integrator linked in (oracle/_ref/yaf_xml_gpu): adaptive AA is
 # driven by the reference's own ImageFilm::nextPass there
