@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define YAFGPU_ABI_VERSION 2
+#define YAFGPU_ABI_VERSION 3
 
 typedef struct yafgpu_ctx yafgpu_ctx;
 
@@ -108,6 +108,101 @@ typedef enum yafgpu_material_type
 	YAFGPU_MAT_LIGHT = 8          /* "light_mat"        material_simple.cc:38-73 */
 } yafgpu_material_type;
 
+/* ---- textures and shader nodes ------------------------------------- */
+
+/* ImageTexture, /root/reference/src/texture/texture_image.cc:560-720 (factory), :75-230 (getColor, doMapping), :231-375 (interpolation).
+ * Texels are handed over as ImageHandler::getPixel(x, y) returns them — linear RGB float after the handler's colour-space
+ * decode and texture "optimization" storage round trip — so no image codec lives on this side of the ABI. */
+typedef enum yafgpu_texture_type { YAFGPU_TEX_IMAGE = 0 } yafgpu_texture_type;
+enum { YAFGPU_TEXINTERP_NONE = 0, YAFGPU_TEXINTERP_BILINEAR = 1, YAFGPU_TEXINTERP_BICUBIC = 2 }; /* "interpolate"; mipmap_* are refused */
+enum { YAFGPU_TEXCLIP_EXTEND = 0, YAFGPU_TEXCLIP_CLIP = 1, YAFGPU_TEXCLIP_CLIPCUBE = 2, YAFGPU_TEXCLIP_REPEAT = 3, YAFGPU_TEXCLIP_CHECKER = 4 }; /* ImageTexture::TexClipMode */
+enum { YAFGPU_CS_RAW_MANUAL_GAMMA = 1, YAFGPU_CS_LINEAR_RGB = 2, YAFGPU_CS_SRGB = 3, YAFGPU_CS_XYZ_D65 = 4 }; /* ColorSpace, include/common/color.h:33-39 */
+
+typedef struct yafgpu_texture
+{
+	int32_t type;            /* yafgpu_texture_type */
+	int32_t width, height;   /* ImageHandler::getWidth/getHeight */
+	const float *rgba;       /* width*height*4 floats: getPixel(x, y) at rgba + 4 * (y * width + x) */
+	int32_t interpolate;     /* YAFGPU_TEXINTERP_* */
+	int32_t clip_mode;       /* "clipping" (YAFGPU_TEXCLIP_*; the factory's fallback for unknown strings is repeat) */
+	int32_t xrepeat, yrepeat;/* "xrepeat", "yrepeat" */
+	int32_t mirror_x, mirror_y; /* "mirror_x", "mirror_y" */
+	int32_t rot90;           /* "rot90" */
+	float cropmin_x, cropmin_y, cropmax_x, cropmax_y; /* "cropmin_x" ... (narrowed to float by setCrop) */
+	int32_t checker_even, checker_odd; /* "even_tiles", "odd_tiles" */
+	float checker_dist;      /* "checker_dist" */
+	int32_t normalmap;       /* "normalmap" */
+	int32_t color_space;     /* YAFGPU_CS_* the handler decoded from (HDR/EXR: linear); used by getRawColor to re-encode */
+	float gamma;             /* "gamma" */
+	float adj_intensity, adj_contrast, adj_saturation; /* "adj_intensity", "adj_contrast", "adj_saturation" */
+	float adj_hue;           /* "adj_hue" / 60.f in float, i.e. Texture::adj_hue_ as setAdjustments stores it (texture.h:154) */
+	float adj_mult_red, adj_mult_green, adj_mult_blue;
+	int32_t adj_clamp;       /* "adj_clamp" */
+} yafgpu_texture;
+
+typedef enum yafgpu_node_type
+{
+	YAFGPU_NODE_TEXTURE_MAPPER = 0, /* "texture_mapper" shader_node_basic.cc:28-420 */
+	YAFGPU_NODE_VALUE = 1,          /* "value"          shader_node_basic.cc:426-446 */
+	YAFGPU_NODE_MIX = 2,            /* "mix"            shader_node_basic.cc:452-705 (mode picks Mix/Add/Mult/Sub/Screen/Diff/Dark/Light/Overlay) */
+	YAFGPU_NODE_LAYER = 3           /* "layer"          shader_node_layer.cc:25-244 */
+} yafgpu_node_type;
+enum { YAFGPU_TEXCO_UV = 0, YAFGPU_TEXCO_GLOBAL = 1, YAFGPU_TEXCO_ORCO = 2, YAFGPU_TEXCO_TRANSFORMED = 3, YAFGPU_TEXCO_NORMAL = 4,
+       YAFGPU_TEXCO_REFLECT = 5, YAFGPU_TEXCO_WINDOW = 6, YAFGPU_TEXCO_STICK = 7, YAFGPU_TEXCO_STRESS = 8, YAFGPU_TEXCO_TANGENT = 9 }; /* TextureMapperNode::Coords */
+enum { YAFGPU_TEXPROJ_PLAIN = 0, YAFGPU_TEXPROJ_CUBE = 1, YAFGPU_TEXPROJ_TUBE = 2, YAFGPU_TEXPROJ_SPHERE = 3 };                   /* TextureMapperNode::Projection */
+/* MixModes, include/shader/shader_node.h:66 */
+enum { YAFGPU_MIX_MIX = 0, YAFGPU_MIX_ADD, YAFGPU_MIX_MULT, YAFGPU_MIX_SUB, YAFGPU_MIX_SCREEN, YAFGPU_MIX_DIV, YAFGPU_MIX_DIFF, YAFGPU_MIX_DARK, YAFGPU_MIX_LIGHT, YAFGPU_MIX_OVERLAY };
+
+/* One <list_element element="shader_node">.  Fields are the values the node factories / configInputs read (after defaults). */
+typedef struct yafgpu_shader_node
+{
+	int32_t type;            /* yafgpu_node_type */
+	/* inputs: index into the owning material's node list, -1 = the parameter is absent.
+	 *   mix:   input1 = "input1", input2 = "input2", factor = "factor"
+	 *   layer: input1 = "input",  input2 = "upper_layer" */
+	int32_t input1, input2, factor;
+	int32_t mode;            /* mix, layer: "mode" */
+	/* texture_mapper (factory shader_node_basic.cc:344-420) */
+	int32_t texture;         /* index into yafgpu_scene_desc.textures ("texture") */
+	int32_t texco;           /* "texco"   (YAFGPU_TEXCO_*, default global) */
+	int32_t mapping;         /* "mapping" (YAFGPU_TEXPROJ_*, default plain; only honoured for discrete textures) */
+	int32_t proj_x, proj_y, proj_z; /* "proj_x/y/z" (clamped to 0..3 by the factory) */
+	float scale[3];          /* "scale" */
+	float offset[3];         /* "offset" (as given; the factory doubles it) */
+	float bump_strength;     /* "bump_strength" */
+	int32_t do_scalar;       /* "do_scalar" */
+	float transform[16];     /* "transform", row-major Matrix4 (identity by default) */
+	/* value: color = "color" + "alpha", scalar = "scalar".  mix: color = "color1", color2 = "color2", scalar = "value"
+	 * (constant inputs of a mix node have no scalar part in the reference — val_1_/val_2_ are never set — it is taken as 0).
+	 * layer: color = "def_col" (alpha 1), color2 = "upper_color", scalar = "def_val", scalar2 = "upper_value" */
+	float color[4], color2[4];
+	float scalar, scalar2;
+	/* layer (factory shader_node_layer.cc:203-244) */
+	float colfac, valfac;    /* "colfac", "valfac" */
+	int32_t do_color, layer_do_scalar, color_input, use_alpha; /* "do_color", "do_scalar", "color_input", "use_alpha" */
+	int32_t no_rgb, stencil, negative;                         /* "noRGB", "stencil", "negative" */
+} yafgpu_shader_node;
+
+/* "<slot>_shader" material parameters (e.g. material_shiny_diffuse.cc:696-724, material_glossy.cc, material_coated_glossy.cc,
+ * material_glass.cc, material_rough_glass.cc, material_blend.cc) */
+enum { YAFGPU_SLOT_DIFFUSE = 0,       /* "diffuse_shader" */
+       YAFGPU_SLOT_MIRROR_COLOR = 1,  /* "mirror_color_shader" */
+       YAFGPU_SLOT_BUMP = 2,          /* "bump_shader" */
+       YAFGPU_SLOT_MIRROR = 3,        /* "mirror_shader" */
+       YAFGPU_SLOT_TRANSPARENCY = 4,  /* "transparency_shader" */
+       YAFGPU_SLOT_TRANSLUCENCY = 5,  /* "translucency_shader" */
+       YAFGPU_SLOT_SIGMA_OREN = 6,    /* "sigma_oren_shader" */
+       YAFGPU_SLOT_DIFFUSE_REFL = 7,  /* "diffuse_refl_shader" */
+       YAFGPU_SLOT_IOR = 8,           /* "IOR_shader" */
+       YAFGPU_SLOT_WIREFRAME = 9,     /* "wireframe_shader" */
+       YAFGPU_SLOT_GLOSSY = 10,       /* "glossy_shader" */
+       YAFGPU_SLOT_GLOSSY_REFLECT = 11, /* "glossy_reflect_shader" */
+       YAFGPU_SLOT_EXPONENT = 12,     /* "exponent_shader" */
+       YAFGPU_SLOT_FILTER_COLOR = 13, /* "filter_color_shader" */
+       YAFGPU_SLOT_ROUGHNESS = 14,    /* "roughness_shader" */
+       YAFGPU_SLOT_BLEND = 15,        /* blend_mat "mask" */
+       YAFGPU_N_SLOTS = 16 };
+
 typedef struct yafgpu_mat_shinydiffuse
 {
 	float color[3];          /* "color" */
@@ -180,7 +275,14 @@ typedef struct yafgpu_material
 	int32_t transparent_bias_multiply_raydepth; /* "transparentbias_multiply_raydepth" */
 	float sampling_factor;        /* "samplingfactor" */
 	int32_t mat_pass_index;       /* "mat_pass_index" */
-	int32_t reserved[3];
+	/* shader nodes of this material (NodeMaterial::loadNodes material_node.cc:140-214): nodes[node_first .. node_first+node_count)
+	 * of yafgpu_scene_desc.nodes, in DECLARATION order (the <list_element> order); the library derives the evaluation order
+	 * (solveNodesOrder material_node.cc:85-103) and the colour / bump node lists the material factories build.  node_count = 0:
+	 * no nodes (also what the reference is left with when loadNodes fails, e.g. on a texture that could not be loaded). */
+	int32_t node_first, node_count;
+	int32_t reserved;
+	/* "<slot>_shader" parameters: index into this material's node list, -1 = not given (YAFGPU_SLOT_*) */
+	int32_t shader[YAFGPU_N_SLOTS];
 	union
 	{
 		yafgpu_mat_shinydiffuse shinydiffuse;
@@ -352,6 +454,8 @@ typedef struct yafgpu_scene_desc
 	yafgpu_geometry geometry;
 	const yafgpu_material *materials; size_t n_materials;
 	const yafgpu_light *lights;       size_t n_lights;   /* in Scene::lights_ order */
+	const yafgpu_texture *textures;   size_t n_textures; /* referenced by texture_mapper nodes */
+	const yafgpu_shader_node *nodes;  size_t n_nodes;    /* all materials' nodes; yafgpu_material.node_first/node_count slice it */
 	yafgpu_camera camera;
 	yafgpu_background background;
 	yafgpu_film_desc film;

@@ -55,6 +55,7 @@
 #include "common/monitor.h"
 #include "object_geom/object_geom_mesh.h"
 #include "material/material.h"
+#include "material/material_node.h"
 #include "light/light.h"
 #include "camera/camera.h"
 #include "background/background.h"
@@ -77,6 +78,8 @@ struct Recorded
 	std::map<const void *, ParamMap> params;     // object -> the ParamMap it was created from
 	std::map<const void *, std::string> names;
 	std::vector<const Material *> materials;     // creation order = material index on the device
+	std::map<const void *, std::list<ParamMap>> eparams; // material -> its <list_element> maps (shader nodes)
+	RenderEnvironment *env = nullptr;
 	ParamMap film;                               // the <render> block as setupScene saw it
 	ParamMap integrator;
 	std::string background_name;
@@ -107,14 +110,172 @@ bool hasShaderNodes(const ParamMap &p)
 }
 
 // ---- ParamMap -> C ABI records (same keys and in-code defaults as the reference factories) ------------------------------
-bool materialRecord(const Material *m, yafgpu_material &out, std::string &err)
+// Scene-wide node and texture tables handed to yafgpu_upload_scene (include/yafgpu.h: yafgpu_shader_node, yafgpu_texture)
+struct NodePool
+{
+	std::vector<yafgpu_shader_node> nodes;
+	std::vector<yafgpu_texture> textures;
+	std::map<const Texture *, int> tex_index;
+	std::list<std::vector<float>> texels; // stable storage behind yafgpu_texture::rgba
+};
+
+// ImageTexture -> yafgpu_texture: parameters from the constructed object (the factory's results, texture_image.cc:560-720), texels
+// from the reference's own ImageHandler::getPixel — whatever format the reference could load, colour-space decode included
+bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &err)
+{
+	auto f = pool.tex_index.find(t);
+	if(f != pool.tex_index.end()) { index = f->second; return true; }
+	const ImageTexture *it = dynamic_cast<const ImageTexture *>(t);
+	if(!it) { err = "only image textures are implemented on the device (procedural textures are not)"; return false; }
+	yafgpu_texture r;
+	memset(&r, 0, sizeof(r));
+	r.type = YAFGPU_TEX_IMAGE;
+	ImageHandler *ih = it->image_;
+	r.width = ih->getWidth(); r.height = ih->getHeight();
+	pool.texels.emplace_back((size_t)r.width * r.height * 4);
+	std::vector<float> &px = pool.texels.back();
+	for(int y = 0; y < r.height; ++y) for(int x = 0; x < r.width; ++x)
+	{
+		const Rgba c = ih->getPixel(x, y);
+		float *o = &px[((size_t)y * r.width + x) * 4];
+		o[0] = c.r_; o[1] = c.g_; o[2] = c.b_; o[3] = c.a_;
+	}
+	r.rgba = px.data();
+	switch(it->getInterpolationType())
+	{
+		case InterpolationType::None: r.interpolate = YAFGPU_TEXINTERP_NONE; break;
+		case InterpolationType::Bilinear: r.interpolate = YAFGPU_TEXINTERP_BILINEAR; break;
+		case InterpolationType::Bicubic: r.interpolate = YAFGPU_TEXINTERP_BICUBIC; break;
+		default: err = "texture interpolation mipmap_trilinear / mipmap_ewa (ray differentials) is not implemented on the device"; return false;
+	}
+	r.clip_mode = (int)it->tex_clip_mode_; // same enumerator order as YAFGPU_TEXCLIP_*
+	r.xrepeat = it->xrepeat_; r.yrepeat = it->yrepeat_; r.mirror_x = it->mirror_x_; r.mirror_y = it->mirror_y_; r.rot90 = it->rot_90_;
+	r.cropmin_x = it->cropminx_; r.cropmin_y = it->cropminy_; r.cropmax_x = it->cropmaxx_; r.cropmax_y = it->cropmaxy_;
+	r.checker_even = it->checker_even_; r.checker_odd = it->checker_odd_; r.checker_dist = it->checker_dist_;
+	r.normalmap = it->normalmap_; r.color_space = (int)it->color_space_; r.gamma = it->gamma_;
+	r.adj_intensity = it->adj_intensity_; r.adj_contrast = it->adj_contrast_; r.adj_saturation = it->adj_saturation_;
+	r.adj_hue = it->adj_hue_;        // already "adj_hue" / 60.f (setAdjustments, texture.h:154), which is what the ABI field holds
+	r.adj_mult_red = it->adj_mult_factor_red_; r.adj_mult_green = it->adj_mult_factor_green_; r.adj_mult_blue = it->adj_mult_factor_blue_;
+	r.adj_clamp = it->adj_clamp_;
+	index = (int)pool.textures.size();
+	pool.textures.push_back(r);
+	pool.tex_index[t] = index;
+	return true;
+}
+
+// NodeMaterial::loadNodes / parseNodes (material_node.cc:140-237) restated on the recorded <list_element> maps: the nodes in declaration
+// order and the "<slot>_shader" bindings.  When the reference itself ended up without nodes (loadNodes failed, e.g. an image the build
+// has no decoder for) the material has none here either.
+bool nodeRecords(const Material *m, const ParamMap &p, const std::string &name, yafgpu_material &out, NodePool &pool, std::string &err)
+{
+	for(int s = 0; s < YAFGPU_N_SLOTS; ++s) out.shader[s] = -1;
+	out.node_first = (int32_t)pool.nodes.size(); out.node_count = 0;
+	const NodeMaterial *nm = dynamic_cast<const NodeMaterial *>(m);
+	if(!nm || nm->m_shaders_table_.empty()) return true;
+	auto ep = rec().eparams.find(m);
+	if(ep == rec().eparams.end()) return true;
+	std::vector<const ParamMap *> elems;
+	for(const ParamMap &e : ep->second)
+	{
+		std::string element;
+		if(e.getParam("element", element) && element != "shader_node") continue;
+		elems.push_back(&e);
+	}
+	std::map<std::string, int> idx;
+	for(size_t i = 0; i < elems.size(); ++i) idx[par<std::string>(*elems[i], "name", "")] = (int)i;
+	auto ref = [&](const ParamMap &e, const char *key) -> int
+	{
+		std::string n;
+		if(!e.getParam(key, n)) return -1;
+		auto f = idx.find(n);
+		return f == idx.end() ? -1 : f->second;
+	};
+	auto col4 = [&](const ParamMap &e, const char *key, float *o)
+	{
+		Rgba c(0.f, 0.f, 0.f, 1.f);
+		e.getParam(key, c);
+		o[0] = c.r_; o[1] = c.g_; o[2] = c.b_; o[3] = c.a_;
+	};
+	for(const ParamMap *ee : elems)
+	{
+		const ParamMap &e = *ee;
+		const std::string type = par<std::string>(e, "type", "");
+		yafgpu_shader_node r;
+		memset(&r, 0, sizeof(r));
+		r.input1 = r.input2 = r.factor = r.texture = -1;
+		if(type == "texture_mapper")
+		{	// shader_node_basic.cc:344-420
+			r.type = YAFGPU_NODE_TEXTURE_MAPPER;
+			const Texture *tex = rec().env ? rec().env->getTexture(par<std::string>(e, "texture", "")) : nullptr;
+			if(!tex) { err = "material '" + name + "': texture of a texture_mapper node not found"; return false; }
+			int ti = -1;
+			if(!textureRecord(tex, pool, ti, err)) { err = "material '" + name + "': " + err; return false; }
+			r.texture = ti;
+			const std::string tc = par<std::string>(e, "texco", "global"), mp = par<std::string>(e, "mapping", "plain");
+			r.texco = tc == "uv" ? YAFGPU_TEXCO_UV : tc == "orco" ? YAFGPU_TEXCO_ORCO : tc == "transformed" ? YAFGPU_TEXCO_TRANSFORMED : tc == "window" ? YAFGPU_TEXCO_WINDOW
+			        : tc == "normal" ? YAFGPU_TEXCO_NORMAL : tc == "reflect" ? YAFGPU_TEXCO_REFLECT : tc == "stick" ? YAFGPU_TEXCO_STICK : tc == "stress" ? YAFGPU_TEXCO_STRESS
+			        : tc == "tangent" ? YAFGPU_TEXCO_TANGENT : YAFGPU_TEXCO_GLOBAL;
+			r.mapping = mp == "cube" ? YAFGPU_TEXPROJ_CUBE : mp == "tube" ? YAFGPU_TEXPROJ_TUBE : mp == "sphere" ? YAFGPU_TEXPROJ_SPHERE : YAFGPU_TEXPROJ_PLAIN;
+			r.proj_x = par<int>(e, "proj_x", 1); r.proj_y = par<int>(e, "proj_y", 2); r.proj_z = par<int>(e, "proj_z", 3);
+			par3(e, "scale", r.scale, 1.f, 1.f, 1.f); par3(e, "offset", r.offset, 0.f, 0.f, 0.f);
+			r.bump_strength = par<float>(e, "bump_strength", 1.f); r.do_scalar = par<bool>(e, "do_scalar", true);
+			Matrix4 mtx(1);
+			e.getParam("transform", mtx);
+			for(int a = 0; a < 4; ++a) for(int b = 0; b < 4; ++b) r.transform[4 * a + b] = mtx[a][b];
+		}
+		else if(type == "value")
+		{
+			r.type = YAFGPU_NODE_VALUE;
+			Rgb c(1.f);
+			e.getParam("color", c);
+			r.color[0] = c.r_; r.color[1] = c.g_; r.color[2] = c.b_; r.color[3] = par<float>(e, "alpha", 1.f);
+			r.scalar = par<float>(e, "scalar", 1.f);
+		}
+		else if(type == "mix")
+		{
+			r.type = YAFGPU_NODE_MIX; r.mode = par<int>(e, "mode", 0);
+			r.input1 = ref(e, "input1"); r.input2 = ref(e, "input2"); r.factor = ref(e, "factor");
+			col4(e, "color1", r.color); col4(e, "color2", r.color2);
+			r.scalar = par<float>(e, "value", 0.f);
+		}
+		else if(type == "layer")
+		{	// shader_node_layer.cc:160-244
+			r.type = YAFGPU_NODE_LAYER; r.mode = par<int>(e, "mode", 0);
+			r.input1 = ref(e, "input"); r.input2 = ref(e, "upper_layer");
+			Rgb dc(1.f);
+			e.getParam("def_col", dc);
+			r.color[0] = dc.r_; r.color[1] = dc.g_; r.color[2] = dc.b_; r.color[3] = 1.f;
+			col4(e, "upper_color", r.color2);
+			r.scalar = (float)par<double>(e, "def_val", 1.0); r.scalar2 = par<float>(e, "upper_value", 0.f);
+			r.colfac = (float)par<double>(e, "colfac", 1.0); r.valfac = (float)par<double>(e, "valfac", 1.0);
+			r.do_color = par<bool>(e, "do_color", true); r.layer_do_scalar = par<bool>(e, "do_scalar", false);
+			r.color_input = par<bool>(e, "color_input", true); r.use_alpha = par<bool>(e, "use_alpha", false);
+			r.no_rgb = par<bool>(e, "noRGB", false); r.stencil = par<bool>(e, "stencil", false); r.negative = par<bool>(e, "negative", false);
+		}
+		else { err = "material '" + name + "': shader node type '" + type + "' is not implemented on the device"; return false; }
+		pool.nodes.push_back(r);
+	}
+	out.node_count = (int32_t)elems.size();
+	static const char *slot_keys[YAFGPU_N_SLOTS] = {"diffuse_shader", "mirror_color_shader", "bump_shader", "mirror_shader", "transparency_shader", "translucency_shader",
+		"sigma_oren_shader", "diffuse_refl_shader", "IOR_shader", "wireframe_shader", "glossy_shader", "glossy_reflect_shader", "exponent_shader", "filter_color_shader",
+		"roughness_shader", "mask"};
+	const std::string mtype = par<std::string>(p, "type", "");
+	for(int s = 0; s < YAFGPU_N_SLOTS; ++s)
+	{
+		if(s == YAFGPU_SLOT_BLEND && mtype != "blend_mat") continue;
+		out.shader[s] = ref(p, slot_keys[s]);
+	}
+	return true;
+}
+
+bool materialRecord(const Material *m, yafgpu_material &out, NodePool &pool, std::string &err)
 {
 	memset(&out, 0, sizeof(out));
 	auto it = rec().params.find(m);
 	if(it == rec().params.end()) { err = "material was not created through RenderEnvironment::createMaterial"; return false; }
 	const ParamMap &p = it->second;
 	const std::string name = rec().names[m];
-	if(hasShaderNodes(p)) { err = "material '" + name + "': shader nodes are not implemented on the device"; return false; }
+	if(!nodeRecords(m, p, name, out, pool, err)) return false;
 	const std::string type = par<std::string>(p, "type", "");
 	const std::string vis = par<std::string>(p, "visibility", "normal");     // material factories: e.g. material_shiny_diffuse.cc:626-649
 	out.visibility = vis == "no_shadows" ? YAFGPU_VIS_NO_SHADOWS : vis == "shadow_only" ? YAFGPU_VIS_SHADOW_ONLY : vis == "invisible" ? YAFGPU_VIS_INVISIBLE : YAFGPU_VIS_NORMAL;
@@ -336,9 +497,10 @@ bool GpuIntegrator::preprocess()
 	// materials in creation order
 	std::vector<yafgpu_material> mats(std::max<size_t>(1, rec().materials.size()));
 	std::map<const Material *, int> mat_index;
+	NodePool pool;
 	for(size_t i = 0; i < rec().materials.size(); ++i)
 	{
-		if(!materialRecord(rec().materials[i], mats[i], err)) return fail(err);
+		if(!materialRecord(rec().materials[i], mats[i], pool, err)) return fail(err);
 		mat_index[rec().materials[i]] = (int)i;
 	}
 
@@ -388,6 +550,8 @@ bool GpuIntegrator::preprocess()
 	g.tri_mat = tmat.data(); g.tri_obj = tobj.data(); g.n_tris = tmat.size();
 	g.objects = objs.data(); g.n_objects = objs.size();
 	d.materials = mats.data(); d.n_materials = rec().materials.size();
+	d.nodes = pool.nodes.data(); d.n_nodes = pool.nodes.size();
+	d.textures = pool.textures.data(); d.n_textures = pool.textures.size();
 
 	// lights in Scene::lights_ order (the order doLightEstimation's per-light QMC offsets depend on)
 	std::vector<yafgpu_light> lights(std::max<size_t>(1, scene_->lights_.size()));
@@ -637,7 +801,7 @@ Material *yg_wrap_material(RenderEnvironment *env, const std::string &name, Para
 {
 	const ParamMap copy = p; // factories may edit the map they are given
 	Material *m = yg_real_material(env, name, p, e);
-	if(m) { remember(m, name, copy); rec().materials.push_back(m); }
+	if(m) { remember(m, name, copy); rec().materials.push_back(m); rec().eparams[m] = e; rec().env = env; }
 	return m;
 }
 Light *yg_wrap_light(RenderEnvironment *env, const std::string &name, ParamMap &p)

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("YAFGPU_LIB") or os.path.join(_HERE, "libyafgpu.so")  # YAFGPU_LIB: kernel-variant experiments (tools/)
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # enums (include/yafgpu.h)
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE, ERR_NOMEM = range(6)
@@ -26,6 +26,18 @@ FILTERS = {"box": 0, "mitchell": 1, "gauss": 2, "lanczos": 3}
 INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
 FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES = 1, 2
+TEX_IMAGE = 0
+TEXINTERP = {"none": 0, "bilinear": 1, "bicubic": 2}
+TEXCLIP = {"extend": 0, "clip": 1, "clipcube": 2, "repeat": 3, "checker": 4}
+CS = {"Raw_Manual_Gamma": 1, "LinearRGB": 2, "sRGB": 3, "XYZ": 4}
+NODE_TEXTURE_MAPPER, NODE_VALUE, NODE_MIX, NODE_LAYER = range(4)
+TEXCO = {"uv": 0, "global": 1, "orco": 2, "transformed": 3, "normal": 4, "reflect": 5, "window": 6, "stick": 7, "stress": 8, "tangent": 9}
+TEXPROJ = {"plain": 0, "cube": 1, "tube": 2, "sphere": 3}
+SLOTS = {"diffuse_shader": 0, "mirror_color_shader": 1, "bump_shader": 2, "mirror_shader": 3, "transparency_shader": 4,
+         "translucency_shader": 5, "sigma_oren_shader": 6, "diffuse_refl_shader": 7, "IOR_shader": 8, "wireframe_shader": 9,
+         "glossy_shader": 10, "glossy_reflect_shader": 11, "exponent_shader": 12, "filter_color_shader": 13,
+         "roughness_shader": 14, "mask": 15}
+N_SLOTS = 16
 
 f32, i32, u32, u64 = C.c_float, C.c_int32, C.c_uint32, C.c_uint64
 F3 = f32 * 3
@@ -79,7 +91,26 @@ class Material(C.Structure):
     _fields_ = [("type", i32), ("visibility", i32), ("receive_shadows", i32), ("flat_material", i32),
                 ("additional_depth", i32), ("transparent_bias_factor", f32),
                 ("transparent_bias_multiply_raydepth", i32), ("sampling_factor", f32), ("mat_pass_index", i32),
-                ("reserved", i32 * 3), ("u", MatUnion)]
+                ("node_first", i32), ("node_count", i32), ("reserved", i32), ("shader", i32 * N_SLOTS), ("u", MatUnion)]
+
+
+class Texture(C.Structure):
+    _fields_ = [("type", i32), ("width", i32), ("height", i32), ("rgba", pf), ("interpolate", i32), ("clip_mode", i32),
+                ("xrepeat", i32), ("yrepeat", i32), ("mirror_x", i32), ("mirror_y", i32), ("rot90", i32),
+                ("cropmin_x", f32), ("cropmin_y", f32), ("cropmax_x", f32), ("cropmax_y", f32),
+                ("checker_even", i32), ("checker_odd", i32), ("checker_dist", f32), ("normalmap", i32),
+                ("color_space", i32), ("gamma", f32), ("adj_intensity", f32), ("adj_contrast", f32),
+                ("adj_saturation", f32), ("adj_hue", f32), ("adj_mult_red", f32), ("adj_mult_green", f32),
+                ("adj_mult_blue", f32), ("adj_clamp", i32)]
+
+
+class ShaderNode(C.Structure):
+    _fields_ = [("type", i32), ("input1", i32), ("input2", i32), ("factor", i32), ("mode", i32), ("texture", i32),
+                ("texco", i32), ("mapping", i32), ("proj_x", i32), ("proj_y", i32), ("proj_z", i32), ("scale", F3),
+                ("offset", F3), ("bump_strength", f32), ("do_scalar", i32), ("transform", f32 * 16),
+                ("color", f32 * 4), ("color2", f32 * 4), ("scalar", f32), ("scalar2", f32), ("colfac", f32),
+                ("valfac", f32), ("do_color", i32), ("layer_do_scalar", i32), ("color_input", i32), ("use_alpha", i32),
+                ("no_rgb", i32), ("stencil", i32), ("negative", i32)]
 
 
 class Light(C.Structure):
@@ -122,6 +153,8 @@ class IntegratorDesc(C.Structure):
 class SceneDesc(C.Structure):
     _fields_ = [("abi_version", u32), ("geometry", Geometry), ("materials", C.POINTER(Material)),
                 ("n_materials", C.c_size_t), ("lights", C.POINTER(Light)), ("n_lights", C.c_size_t),
+                ("textures", C.POINTER(Texture)), ("n_textures", C.c_size_t),
+                ("nodes", C.POINTER(ShaderNode)), ("n_nodes", C.c_size_t),
                 ("camera", Camera), ("background", Background), ("film", FilmDesc), ("integrator", IntegratorDesc)]
 
 

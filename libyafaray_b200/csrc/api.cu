@@ -41,6 +41,9 @@ static void freeScene(yafgpu_ctx *c)
 	poolFree(c->film.pix, c->stream); poolFree(c->d_mat_bucket, c->stream); c->d_mat_bucket = nullptr; poolFree(c->d_light_accels, c->stream); c->d_light_accels = nullptr;
 	for(void *q : c->light_bvh_ptrs) poolFree(q, c->stream);
 	c->light_bvh_ptrs.clear();
+	for(void *q : c->tex_ptrs) poolFree(q, c->stream);
+	c->tex_ptrs.clear();
+	poolFree(c->d_textures, c->stream); c->d_textures = nullptr; poolFree(c->d_shader_nodes, c->stream); c->d_shader_nodes = nullptr;
 	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
 	c->d_tris = nullptr; c->d_objects = nullptr; c->d_mats = nullptr; c->d_lights = nullptr; c->d_light_tables = nullptr; c->d_bg_tex = nullptr;
 	c->d_nodes = nullptr; c->d_acc_tris = nullptr; c->film.pix = nullptr;
@@ -192,9 +195,17 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	// materials / lights / camera / film: reference constructors restated on the host (host_prep.h)
 	c->h_mats.assign(desc->n_materials, MatDev());
 	std::vector<unsigned> triflags(desc->n_materials ? desc->n_materials : 1, 0u);
+	std::vector<TexDev> h_tex(desc->n_textures);
+	for(size_t i = 0; i < desc->n_textures; ++i)
+	{
+		std::string err;
+		if(!desc->textures || !prepTexture(desc->textures[i], h_tex[i], err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "texture " + std::to_string(i) + ": " + err);
+	}
+	std::vector<NodeDev> h_nodes;
 	for(size_t i = 0; i < desc->n_materials; ++i)
 	{
 		std::string err;
+		if(!prepNodes(desc->materials[i], *desc, h_tex, c->h_mats[i], h_nodes, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
 		if(!prepMaterial(desc->materials[i], c->h_mats[i], err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
 	}
 	for(size_t i = 0; i < desc->n_materials; ++i)
@@ -203,6 +214,15 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		if(c->h_mats[i].type == YAFGPU_MAT_BLEND && !finishBlend(c->h_mats, i, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
 	}
 	for(size_t i = 0; i < desc->n_materials; ++i) triflags[i] = triFlagsOf(c->h_mats[i]);
+	for(size_t i = 0; i < desc->n_materials; ++i)
+	{	// Scene::isShadowed calls Material::getTransparency without initBsdf (kdtree_triangle.cc:1106-1124): with shader nodes it would read
+		// the node stack of whatever material was shaded last.  Not reproducible, so the combination is refused.
+		const MatDev &md = c->h_mats[i];
+		const bool transp_nodes = md.node_count > 0 && md.is_transparent;
+		const bool blend_child_nodes = md.type == YAFGPU_MAT_BLEND && (c->h_mats[md.mat1].node_count > 0 || c->h_mats[md.mat2].node_count > 0);
+		if(blend_child_nodes) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": blend_mat of materials with shader nodes is not implemented on the device");
+		if(transp_nodes && desc->integrator.transp_shad) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": transparent shadows through a material with shader nodes");
+	}
 	c->h_lights.clear();
 	std::vector<size_t> light_src; // descriptor index of every kept light; disabled lights are never added (Scene::addLight scene.cc:688-698)
 	for(size_t i = 0; i < desc->n_lights; ++i)
@@ -294,14 +314,15 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	{	// sort buckets of the shading kernel: materials ranked by (type, index) so that equal code paths are adjacent
 		std::vector<int> order(c->h_mats.size()), bucket(c->h_mats.size() ? c->h_mats.size() : 1, 0);
 		for(size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
-		std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return c->h_mats[a].type < c->h_mats[b].type; });
+		auto ktype = [&](int i) { return c->h_mats[i].node_count > 0 ? YG_MAT_NODES : c->h_mats[i].type; }; // kernel that shades the material
+		std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return ktype(a) < ktype(b); });
 		// one bucket per material while they fit, else one per type: a bucket never mixes types (per-type shading kernels)
 		const bool per_mat = order.size() <= 4096;
 		c->n_mat_buckets = per_mat ? (int)std::max<size_t>(order.size(), 1) : YG_N_MAT_TYPES;
 		for(int t = 0; t < YG_N_MAT_TYPES; ++t) { c->type_b0[t] = 0; c->type_b1[t] = -1; }
 		for(size_t r = 0; r < order.size(); ++r)
 		{
-			const int t = c->h_mats[order[r]].type, b = per_mat ? (int)r : t;
+			const int t = ktype(order[r]), b = per_mat ? (int)r : t;
 			bucket[order[r]] = b;
 			if(c->type_b1[t] < 0) c->type_b0[t] = b;
 			c->type_b1[t] = b;
@@ -310,6 +331,15 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
 	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
+	for(size_t i = 0; i < h_tex.size(); ++i)
+	{
+		float4 *d_px = nullptr;
+		YG_CUDA(c, upload(d_px, (const float4 *)desc->textures[i].rgba, (size_t)h_tex[i].w * h_tex[i].h, st));
+		c->tex_ptrs.push_back(d_px);
+		h_tex[i].tex = d_px;
+	}
+	YG_CUDA(c, upload(c->d_textures, h_tex.data(), h_tex.size(), st));
+	YG_CUDA(c, upload(c->d_shader_nodes, h_nodes.data(), h_nodes.size(), st));
 	YG_CUDA(c, poolAlloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1), st));
 	YG_CUDA(c, poolAlloc(&c->d_tris, sizeof(TriShade) * (g.n_tris ? g.n_tris : 1), st));
 	if(g.tri_nidx) YG_CUDA(c, upload(d_nidx, g.tri_nidx, g.n_tris * 3, st));
@@ -373,6 +403,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 
 	s.points = c->d_points; s.normals = c->d_normals; s.uv = c->d_uv; s.tris = c->d_tris; s.objects = c->d_objects;
 	s.materials = c->d_mats; s.lights = c->d_lights; s.n_lights = (int)c->h_lights.size(); s.light_tables = c->d_light_tables; s.light_accels = c->d_light_accels; s.faure = c->d_faure;
+	s.textures = c->d_textures; s.nodes = c->d_shader_nodes;
 
 	// film (ImageFilm ctor + init)
 	prepFilm(desc->film, c->film);

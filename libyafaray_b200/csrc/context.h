@@ -28,6 +28,8 @@ struct yafgpu_ctx
 	yg::Accel *d_light_accels = nullptr;
 	std::vector<void *> light_bvh_ptrs; // node/triangle arrays of the mesh-light accelerators
 	float *d_bg_tex = nullptr;
+	yg::TexDev *d_textures = nullptr; yg::NodeDev *d_shader_nodes = nullptr; // image textures and shader nodes (nodes.cuh)
+	std::vector<void *> tex_ptrs;                                            // texel arrays of d_textures
 	yg::FaureTables *d_faure = nullptr;
 	yg::BvhNode *d_nodes = nullptr;
 	yg::TriAccel *d_acc_tris = nullptr;

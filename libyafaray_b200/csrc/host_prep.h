@@ -7,6 +7,8 @@
 #include <string>
 #include <vector>
 #include <cstring>
+#include <functional>
+#include <algorithm>
 
 namespace yg {
 
@@ -37,27 +39,29 @@ inline bool prepShinyDiffuse(const yafgpu_material &m, MatDev &d, std::string &e
 		d.oren_b = (float)(0.45 * s2 / (s2 + 0.09));
 		d.use_oren_nayar = 1;
 	}
-	// config() :46-92 without shader nodes
+	// config() :46-92; a bound "<component>_shader" switches the component on whatever its constant strength is
+	const bool sh_mirror = d.slot[YAFGPU_SLOT_MIRROR] >= 0, sh_transp = d.slot[YAFGPU_SLOT_TRANSPARENCY] >= 0, sh_transl = d.slot[YAFGPU_SLOT_TRANSLUCENCY] >= 0;
+	d.diffuse_refl_mul = 1.f;
 	d.n_bsdf = 0; d.is_mirror = d.is_transparent = d.is_translucent = d.is_diffuse = 0;
 	float acc = 1.f;
-	if(d.mirror_strength > 0.00001f)
+	if(d.mirror_strength > 0.00001f || sh_mirror)
 	{
 		d.is_mirror = 1;
-		if(!d.has_fresnel) acc = 1.f - d.mirror_strength;
+		if(sh_mirror) {} else if(!d.has_fresnel) acc = 1.f - d.mirror_strength;
 		d.bsdf_flags |= BsdfSpecular | BsdfReflect;
 		d.c_flags[d.n_bsdf] = BsdfSpecular | BsdfReflect; d.c_index[d.n_bsdf] = 0; ++d.n_bsdf;
 	}
-	if(d.transparency_strength * acc > 0.00001f)
+	if(d.transparency_strength * acc > 0.00001f || sh_transp)
 	{
 		d.is_transparent = 1;
-		acc *= 1.f - d.transparency_strength;
+		if(!sh_transp) acc *= 1.f - d.transparency_strength;
 		d.bsdf_flags |= BsdfTransmit | BsdfFilter;
 		d.c_flags[d.n_bsdf] = BsdfTransmit | BsdfFilter; d.c_index[d.n_bsdf] = 1; ++d.n_bsdf;
 	}
-	if(d.translucency_strength * acc > 0.00001f)
+	if(d.translucency_strength * acc > 0.00001f || sh_transl)
 	{
 		d.is_translucent = 1;
-		acc *= 1.f - d.transparency_strength; // sic: the reference multiplies by (1 - transparency) here as well (:78)
+		if(!sh_transl) acc *= 1.f - d.transparency_strength; // sic: the reference multiplies by (1 - transparency) here as well (:78)
 		d.bsdf_flags |= BsdfDiffuse | BsdfTransmit;
 		d.c_flags[d.n_bsdf] = BsdfDiffuse | BsdfTransmit; d.c_index[d.n_bsdf] = 2; ++d.n_bsdf;
 	}
@@ -68,7 +72,8 @@ inline bool prepShinyDiffuse(const yafgpu_material &m, MatDev &d, std::string &e
 		d.c_flags[d.n_bsdf] = BsdfDiffuse | BsdfReflect; d.c_index[d.n_bsdf] = 3; ++d.n_bsdf;
 	}
 	// pure Lambert/Oren-Nayar surface: gets its own shading kernel (materials.cuh YG_MAT_SD_LAMBERT); same arithmetic, fewer branches
-	if(d.n_bsdf == 1 && d.is_diffuse && !d.has_fresnel) d.type = YG_MAT_SD_LAMBERT;
+	if(d.n_bsdf == 1 && d.is_diffuse && !d.has_fresnel && d.node_count == 0) d.type = YG_MAT_SD_LAMBERT;
+	if(d.slot[YAFGPU_SLOT_WIREFRAME] >= 0) { err = "shinydiffusemat: wireframe_shader is not implemented on the device"; return false; }
 	(void)err;
 	return true;
 }
@@ -165,9 +170,123 @@ inline unsigned triFlagsOf(const MatDev &d)
 	return f;
 }
 
-inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
+// ---- shader nodes ------------------------------------------------------------------------------------------------------
+// ImageTexture after its factory, texture_image.cc:560-720 and Texture::setAdjustments texture.h:147-201
+inline bool prepTexture(const yafgpu_texture &t, TexDev &d, std::string &err)
 {
 	memset(&d, 0, sizeof(d));
+	if(t.type != YAFGPU_TEX_IMAGE) { err = "texture type " + std::to_string(t.type) + " is not implemented on the device"; return false; }
+	if(!t.rgba || t.width <= 0 || t.height <= 0) { err = "image texture without texels"; return false; }
+	if(t.interpolate < YAFGPU_TEXINTERP_NONE || t.interpolate > YAFGPU_TEXINTERP_BICUBIC) { err = "texture interpolation (mipmap_trilinear / mipmap_ewa need ray differentials) is not implemented on the device"; return false; }
+	if(t.clip_mode < YAFGPU_TEXCLIP_EXTEND || t.clip_mode > YAFGPU_TEXCLIP_CHECKER) { err = "texture clip mode"; return false; }
+	d.w = t.width; d.h = t.height; d.interp = t.interpolate; d.clip = t.clip_mode;
+	d.xrepeat = t.xrepeat; d.yrepeat = t.yrepeat; d.mirror_x = t.mirror_x ? 1 : 0; d.mirror_y = t.mirror_y ? 1 : 0; d.rot90 = t.rot90 ? 1 : 0;
+	// setCrop :224-229
+	d.cropminx = t.cropmin_x; d.cropmaxx = t.cropmax_x; d.cropminy = t.cropmin_y; d.cropmaxy = t.cropmax_y;
+	d.cropx = ((double)d.cropminx != 0.0) || ((double)d.cropmaxx != 1.0);
+	d.cropy = ((double)d.cropminy != 0.0) || ((double)d.cropmaxy != 1.0);
+	d.checker_even = t.checker_even ? 1 : 0; d.checker_odd = t.checker_odd ? 1 : 0; d.checker_dist = t.checker_dist;
+	d.normalmap = t.normalmap ? 1 : 0; d.color_space = t.color_space; d.gamma = t.gamma;
+	d.adj_intensity = t.adj_intensity; d.adj_contrast = t.adj_contrast; d.adj_saturation = t.adj_saturation; d.adj_hue = t.adj_hue;
+	d.adj_clamp = t.adj_clamp ? 1 : 0; d.adj_mult[0] = t.adj_mult_red; d.adj_mult[1] = t.adj_mult_green; d.adj_mult[2] = t.adj_mult_blue;
+	d.adj_set = (t.adj_intensity != 1.f || t.adj_contrast != 1.f || t.adj_saturation != 1.f || t.adj_hue != 0.f || t.adj_mult_red != 1.f ||
+	             t.adj_mult_green != 1.f || t.adj_mult_blue != 1.f || t.adj_clamp) ? 1 : 0;
+	return true;
+}
+
+// NodeMaterial::loadNodes / solveNodesOrder / getNodeList (material_node.cc:46-119,140-214) for one material: appends the material's
+// reachable nodes to `out` in a dependency order (the reference's order is one particular depth-first order; node results do not depend
+// on which topological order is used), and fills the node fields of `d`.
+inline bool prepNodes(const yafgpu_material &m, const yafgpu_scene_desc &sd, const std::vector<TexDev> &tex, MatDev &d, std::vector<NodeDev> &out, std::string &err)
+{
+	for(int s = 0; s < YAFGPU_N_SLOTS; ++s) d.slot[s] = -1;
+	d.node_first = (int)out.size(); d.node_count = 0; d.color_mask = d.bump_mask = 0u;
+	const int n = m.node_count;
+	if(n <= 0) return true;
+	if(m.node_first < 0 || (size_t)m.node_first + (size_t)n > sd.n_nodes || !sd.nodes) { err = "shader node range out of bounds"; return false; }
+	const yafgpu_shader_node *nd = sd.nodes + m.node_first;
+	auto deps = [&](int i, int *dp) { int k = 0; const yafgpu_shader_node &q = nd[i];
+		if(q.type == YAFGPU_NODE_MIX) { if(q.input1 >= 0) dp[k++] = q.input1; if(q.input2 >= 0) dp[k++] = q.input2; if(q.factor >= 0) dp[k++] = q.factor; }
+		else if(q.type == YAFGPU_NODE_LAYER) { if(q.input1 >= 0) dp[k++] = q.input1; if(q.input2 >= 0) dp[k++] = q.input2; }
+		return k; };
+	for(int i = 0; i < n; ++i)
+	{
+		int dp[3]; const int k = deps(i, dp);
+		for(int j = 0; j < k; ++j) if(dp[j] >= n) { err = "shader node input index out of range"; return false; }
+		if(nd[i].type == YAFGPU_NODE_LAYER && nd[i].input1 < 0) { err = "layer node without input"; return false; }
+		if(nd[i].type < YAFGPU_NODE_TEXTURE_MAPPER || nd[i].type > YAFGPU_NODE_LAYER) { err = "shader node type " + std::to_string(nd[i].type) + " is not implemented on the device"; return false; }
+	}
+	std::vector<int> pos(n, -1), state(n, 0), order;
+	bool cyc = false;
+	std::function<void(int)> visit = [&](int i) { // recursiveSolver__ :46-58
+		if(state[i] == 2) return;
+		if(state[i] == 1) { cyc = true; return; }
+		state[i] = 1;
+		int dp[3]; const int k = deps(i, dp);
+		for(int j = 0; j < k; ++j) visit(dp[j]);
+		state[i] = 2; pos[i] = (int)order.size(); order.push_back(i); };
+	for(int s = 0; s < YAFGPU_N_SLOTS; ++s)
+	{
+		if(m.shader[s] < 0) continue;
+		if(m.shader[s] >= n) { err = "shader slot index out of range"; return false; }
+		visit(m.shader[s]);
+	}
+	if(cyc) { err = "shader node graph has a cycle"; return false; }
+	if(order.empty()) return true; // nodes declared but none bound: nothing is ever evaluated
+	if(order.size() > YG_MAX_NODES) { err = "more than " + std::to_string(YG_MAX_NODES) + " shader nodes in one material"; return false; }
+	std::function<void(int, unsigned &)> mark = [&](int i, unsigned &mask) { // recursiveFinder__ :60-72
+		if(mask >> pos[i] & 1u) return;
+		mask |= 1u << pos[i];
+		int dp[3]; const int k = deps(i, dp);
+		for(int j = 0; j < k; ++j) mark(dp[j], mask); };
+	for(int s = 0; s < YAFGPU_N_SLOTS; ++s)
+	{
+		if(m.shader[s] < 0) continue;
+		d.slot[s] = pos[m.shader[s]];
+		mark(m.shader[s], s == YAFGPU_SLOT_BUMP ? d.bump_mask : d.color_mask);
+	}
+	d.node_count = (int)order.size();
+	for(int i : order)
+	{
+		const yafgpu_shader_node &q = nd[i];
+		NodeDev o; memset(&o, 0, sizeof(o));
+		o.type = q.type; o.mode = q.mode;
+		o.in1 = q.input1 >= 0 ? pos[q.input1] : -1; o.in2 = q.input2 >= 0 ? pos[q.input2] : -1; o.fac = q.factor >= 0 ? pos[q.factor] : -1;
+		for(int k = 0; k < 4; ++k) { o.col[k] = q.color[k]; o.col2[k] = q.color2[k]; }
+		o.f1 = q.scalar; o.f2 = q.scalar2;
+		if(q.type == YAFGPU_NODE_TEXTURE_MAPPER)
+		{	// TextureMapperNode::factory :344-420 and setup() :33-55
+			if(q.texture < 0 || (size_t)q.texture >= tex.size()) { err = "texture_mapper: texture index out of range"; return false; }
+			const TexDev &t = tex[q.texture];
+			o.tex = q.texture; o.coords = q.texco; o.proj = q.mapping; // image textures are discrete(): the "mapping" is honoured
+			if(q.texco == YAFGPU_TEXCO_WINDOW || q.texco == YAFGPU_TEXCO_NORMAL) { err = "texture_mapper: texco window / normal (camera dependent) is not implemented on the device"; return false; }
+			if(q.texco < 0 || q.texco > YAFGPU_TEXCO_TANGENT || q.mapping < 0 || q.mapping > YAFGPU_TEXPROJ_SPHERE) { err = "texture_mapper: texco / mapping"; return false; }
+			o.map_x = std::min(3, std::max(0, q.proj_x)); o.map_y = std::min(3, std::max(0, q.proj_y)); o.map_z = std::min(3, std::max(0, q.proj_z));
+			for(int k = 0; k < 3; ++k) { o.scale[k] = q.scale[k]; o.offset[k] = 2 * q.offset[k]; }
+			o.do_scalar = q.do_scalar ? 1 : 0;
+			for(int k = 0; k < 12; ++k) o.mtx[k] = q.transform[k];
+			o.d_u = 1.f / (float)t.w; o.d_v = 1.f / (float)t.h;
+			o.bump_str = q.bump_strength / length(mk(o.scale[0], o.scale[1], o.scale[2]));
+			if(!t.normalmap) o.bump_str /= 100.0f;
+		}
+		else if(q.type == YAFGPU_NODE_LAYER)
+		{	// LayerNode::factory :203-244 (colfac / valfac / def_val are read as doubles and narrowed by the constructor)
+			o.colfac = q.colfac; o.valfac = q.valfac;
+			o.texflag = (q.no_rgb ? 1u : 0u) | (q.stencil ? 2u : 0u) | (q.negative ? 4u : 0u) | (q.use_alpha ? 8u : 0u);
+			o.do_color = q.do_color ? 1 : 0; o.do_scalar_l = q.layer_do_scalar ? 1 : 0; o.color_input = q.color_input ? 1 : 0; o.use_alpha = q.use_alpha ? 1 : 0;
+			o.col[3] = 1.f; // Rgba(def_col)
+		}
+		out.push_back(o);
+	}
+	return true;
+}
+
+inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
+{
+	// node fields (node_first .. slot[]) were filled by prepNodes and are kept
+	{ MatDev keep = d; memset(&d, 0, sizeof(d)); d.node_first = keep.node_first; d.node_count = keep.node_count; d.color_mask = keep.color_mask; d.bump_mask = keep.bump_mask; memcpy(d.slot, keep.slot, sizeof(d.slot)); }
+	d.diffuse_refl_mul = 1.f;
+	if(d.node_count > 0 && m.type != YAFGPU_MAT_SHINYDIFFUSE) { err = "shader nodes on this material type are not implemented on the device yet"; return false; }
 	d.type = m.type; d.visibility = m.visibility; d.receive_shadows = m.receive_shadows; d.flat = m.flat_material;
 	d.additional_depth = m.additional_depth; d.transp_bias_factor = m.transparent_bias_factor;
 	d.transp_bias_mult = m.transparent_bias_multiply_raydepth; d.sampling_factor = m.sampling_factor;

@@ -21,6 +21,7 @@
 //     path of a sibling subtree wrote, integrator_path_tracer.cc:212,253).
 #include "context.h"
 #include "lights.cuh"
+#include "nodes.cuh"
 #include <algorithm>
 #include <cstdio>
 
@@ -455,11 +456,10 @@ __device__ __forceinline__ void pushTask(const ShadeCtx &cx, int slot, V3 from, 
 #define YG_DLE YG_DN
 #endif
 template<int MT>
-YG_DLE void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, int li, const SurfPt &sp, V3 wo, unsigned loffs, int ray_division, Col W)
+YG_DLE void doLightEstimation(const ShadeCtx &cx, const MatDev &m, int slot, const SlotInfo &si, int li, const SurfPt &sp, V3 wo, unsigned loffs, int ray_division, Col W)
 {
 	const SceneDev &sc = *cx.sc;
 	const LightDev &L = sc.lights[li];
-	const MatDev &m = sc.materials[sp.mat];
 	const bool cast_shadows = L.cast_shadows && m.receive_shadows;
 	const unsigned l_offs = loffs * 4567u;
 	const float plen = length(sp.p);
@@ -541,7 +541,7 @@ YG_DLE void doLightEstimation(const ShadeCtx &cx, int slot, const SlotInfo &si, 
 // scatter kernel leaves behind, [b0, b1] is the bucket range of the type inside one kind (host-known), so a launch needs no
 // host-side knowledge of the counts.  Compiling the material code in per type keeps each kernel's instruction footprint
 // (and register allocation) to what that BSDF needs: the single generic kernel was 278 k SASS instructions.
-enum { MT_MISS = 100 };
+enum { MT_MISS = 100, MT_NODES = -2 /* negative: the material type is read from the record, as for blend children */ };
 
 template<int MT>
 __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L : YG_SHADE_MINB) k_shade(const __grid_constant__ SceneDev sc, WaveParams wp, const uint32_t *__restrict__ pixels, TaskQueue in, TaskQueue out, ShadowQueue sq,
@@ -582,7 +582,12 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			}
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp); // Point3 h = ray.from_ + z * ray.dir_ (scene.cc:908)
-			const MatDev &m = sc.materials[sp.mat];
+			// materials with shader nodes (kernel class YG_MAT_NODES): the node pass of initBsdf() resolves the bound shaders into a
+			// thread-local copy of the record (nodes.cuh); every other kernel reads the record in place
+			const MatDev *mp = &sc.materials[sp.mat];
+			MatDev ml;
+			if(MT == MT_NODES) { ml = *mp; evalMaterialNodes(sc, ml, sp, tri, hh.y, hh.z); mp = &ml; }
+			const MatDev &m = *mp;
 			matInitBsdf<MT>(m, sp);
 			const unsigned bsdfs = m.bsdf_flags;
 			const V3 wo = -dir;
@@ -592,7 +597,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit<MT>(sc, m, sp, wo, true));
 			if(bsdfs & BsdfDiffuse)
 			{	// estimateAllDirectLight integrator_montecarlo.cc:47-60
-				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation<MT>(cx, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
+				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation<MT>(cx, m, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
 				if(ig.type == YAFGPU_INT_DIRECTLIGHT && ig.do_ao)
 				{	// MonteCarloIntegrator::sampleAmbientOcclusion integrator_montecarlo.cc:1030-1088 (only DirectLight calls it, :145)
 					int n = ig.ao_samples;
@@ -724,7 +729,12 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			}
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp);
-			const MatDev &m = sc.materials[sp.mat];
+			// materials with shader nodes (kernel class YG_MAT_NODES): the node pass of initBsdf() resolves the bound shaders into a
+			// thread-local copy of the record (nodes.cuh); every other kernel reads the record in place
+			const MatDev *mp = &sc.materials[sp.mat];
+			MatDev ml;
+			if(MT == MT_NODES) { ml = *mp; evalMaterialNodes(sc, ml, sp, tri, hh.y, hh.z); mp = &ml; }
+			const MatDev &m = *mp;
 			matInitBsdf<MT>(m, sp);
 			const unsigned bsdfs = m.bsdf_flags;
 			const V3 pwo = -dir;
@@ -745,7 +755,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			{	// estimateOneDirectLight integrator_montecarlo.cc:62-76 (a material without diffuse/glossy lobes evaluates to black)
 				const float u = hashRand(wp.seed + 0x51ED270Bu + (unsigned)(wp.pix_base + slot), offs, (unsigned)depth);
 				const int lnum = min((int)(u * (float)sc.n_lights), sc.n_lights - 1);
-				doLightEstimation<MT>(cx, slot, si, lnum, sp, pwo, (unsigned)lnum, ray_division, Wp * (float)sc.n_lights);
+				doLightEstimation<MT>(cx, m, slot, si, lnum, sp, pwo, (unsigned)lnum, ray_division, Wp * (float)sc.n_lights);
 			}
 			if(bsdfs & BsdfEmit)
 			{
@@ -1044,6 +1054,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		YG_SHADE(YG_MAT_SD_LAMBERT) YG_SHADE(YAFGPU_MAT_SHINYDIFFUSE) YG_SHADE(YAFGPU_MAT_GLOSSY) YG_SHADE(YAFGPU_MAT_COATED_GLOSSY) YG_SHADE(YAFGPU_MAT_GLASS) YG_SHADE(YAFGPU_MAT_ROUGH_GLASS)
 		YG_SHADE(YAFGPU_MAT_BLEND) YG_SHADE(YAFGPU_MAT_MIRROR) YG_SHADE(YAFGPU_MAT_NULL) YG_SHADE(YAFGPU_MAT_LIGHT)
 #undef YG_SHADE
+		if(c->type_b1[YG_MAT_NODES] >= c->type_b0[YG_MAT_NODES]) { k_shade<MT_NODES><<<gs, 128, 0, shadeStream()>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, c->type_b0[YG_MAT_NODES], c->type_b1[YG_MAT_NODES]); ++n_launch; }
 		k_shade<MT_MISS><<<gs, 128, 0, shadeStream()>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
 		if(n_str > 1) for(int k = 0; k < n_str - 1; ++k) { cudaEventRecord(c->ev_join[k], c->side[k]); cudaStreamWaitEvent(st, c->ev_join[k], 0); }
 		mark();

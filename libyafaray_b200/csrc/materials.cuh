@@ -128,6 +128,34 @@ YG_D float orenNayar(float oren_a, float oren_b, V3 wi, V3 wo, V3 n)
 	return fminf(1.f, fmaxf(0.f, oren_a + oren_b * maxcos_f * sin_alpha * tan_beta));
 }
 
+// ShinyDiffuseMaterial::orenNayar with use_texture_sigma (material_shiny_diffuse.cc:229-236): coefficients and the final sum in double
+YG_D float orenNayarTex(float sigma, V3 wi, V3 wo, V3 n)
+{
+	const float cos_ti = fmaxf(-1.f, fminf(1.f, dot(n, wi)));
+	const float cos_to = fmaxf(-1.f, fminf(1.f, dot(n, wo)));
+	float maxcos_f = 0.f;
+	if(cos_ti < 0.9999f && cos_to < 0.9999f)
+	{
+		const V3 v1 = normalize(wi - n * cos_ti);
+		const V3 v2 = normalize(wo - n * cos_to);
+		maxcos_f = fmaxf(0.f, dot(v1, v2));
+	}
+	float sin_alpha, tan_beta;
+	if(cos_to >= cos_ti)
+	{
+		sin_alpha = fSqrt(1.f - cos_ti * cos_ti);
+		tan_beta = fSqrt(1.f - cos_to * cos_to) / ((cos_to == 0.f) ? 1e-8f : cos_to);
+	}
+	else
+	{
+		sin_alpha = fSqrt(1.f - cos_to * cos_to);
+		tan_beta = fSqrt(1.f - cos_ti * cos_ti) / ((cos_ti == 0.f) ? 1e-8f : cos_ti);
+	}
+	const double s2 = (double)sigma * (double)sigma;
+	const double a = 1.0 - 0.5 * (s2 / (s2 + 0.33)), b = 0.45 * s2 / (s2 + 0.09);
+	return fminf(1.f, fmaxf(0.f, (float)(a + b * (double)maxcos_f * (double)sin_alpha * (double)tan_beta)));
+}
+
 // microfacet helpers, material_utils_microfacet.h
 YG_D float pdfDivisor(float c) { return (float)((double)8.f * YG_M_PI * (double)(c * 0.99f + 0.04f)); }
 YG_D float asDivisor(float c1, float ci, float co) { return (float)((double)8.f * YG_M_PI * (double)((c1 * fmaxf(ci, co)) * 0.99f + 0.04f)); }
@@ -281,7 +309,8 @@ YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdf
 			if(!YG_SDL(MT) && transmit && m.is_translucent) return (comp[2] * m_t) * ldc(m.diffuse_col);
 			if(dot(n, wl) < 0.0f && !m.flat) return mkc(0.f);
 			float m_d = m_t * (1.f - comp[2]) * comp[3];
-			if(m.use_oren_nayar) m_d *= orenNayar(m.oren_a, m.oren_b, wo, wl, n);
+			if(m.use_oren_nayar) m_d *= (MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wo, wl, n) : orenNayar(m.oren_a, m.oren_b, wo, wl, n);
+			if(MT < 0) m_d *= m.diffuse_refl_mul; // "diffuse_refl_shader" (:285); 1 when absent.  Only the generic instantiation can see nodes.
 			return m_d * ldc(m.diffuse_col);
 		}
 		case YAFGPU_MAT_GLOSSY:
@@ -506,7 +535,7 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 				default:
 					wi = sampleCosHemisphere(n, sp.nu, sp.nv, s_1, s.s2);
 					if(cos_ng_wo * dot(sp.ng, wi) > 0) scolor = accum_c[3] * ldc(m.diffuse_col);
-					if(m.use_oren_nayar) scolor = scolor * orenNayar(m.oren_a, m.oren_b, wo, wi, n);
+					if(m.use_oren_nayar) scolor = scolor * ((MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wo, wi, n) : orenNayar(m.oren_a, m.oren_b, wo, wi, n));
 					s.pdf = fabsf(dot(wi, n)) * width[pick];
 					break;
 			}

@@ -1,5 +1,6 @@
 // HBM layout of the flattened scene.  Plain-old-data views handed to every kernel by value.
 #pragma once
+#include "../../include/yafgpu.h"
 #include "dev_math.cuh"
 #include "dev_qmc.cuh"
 
@@ -50,6 +51,8 @@ struct ObjDev { int has_orco, has_uv, smooth, light; };
 
 // internal material type (never crosses the C ABI): shinydiffuse with the diffuse-reflection component only, see materials.cuh
 #define YG_MAT_SD_LAMBERT 9
+// kernel class (never a MatDev::type) of every material that carries shader nodes: generic type dispatch + node evaluation, nodes.cuh
+#define YG_MAT_NODES 10
 
 // Material record after the reference constructors' preprocessing (one per yafgpu_material).
 struct MatDev
@@ -78,6 +81,37 @@ struct MatDev
 	int mat1, mat2; float blend_val;
 	// simple (light_mat / mirror)
 	float simple_col[3]; int double_sided;
+	// shader nodes (nodes.cuh): this material's nodes are SceneDev::nodes[node_first .. node_first + node_count) in evaluation order
+	// (stack index = position); bit i of color_mask / bump_mask = node i is in the colour / bump node list; slot[] = stack index of the
+	// node bound to each "<slot>_shader" parameter, -1 = none.  Filled per hit from the node results (evalMaterialNodes):
+	int node_first, node_count; unsigned color_mask, bump_mask; int slot[YAFGPU_N_SLOTS];
+	float diffuse_refl_mul;              // shinydiffuse "diffuse_refl_shader" (1 without it: the reference then does not multiply)
+	int oren_tex; float oren_sigma;      // "sigma_oren_shader": Oren-Nayar coefficients from the textured sigma, in double (material_shiny_diffuse.cc:231-236)
+};
+
+#define YG_MAX_NODES 16 /* nodes per material (per-thread node stack: 20 B each) */
+
+// ImageTexture after its factory (texture_image.cc:560-720); texels as ImageHandler::getPixel returns them, RGBA float
+struct TexDev
+{
+	const float4 *tex; int w, h;
+	int interp, clip, xrepeat, yrepeat, mirror_x, mirror_y, rot90, cropx, cropy;
+	float cropminx, cropminy, cropmaxx, cropmaxy;
+	int checker_even, checker_odd; float checker_dist;
+	int normalmap, color_space; float gamma;
+	int adj_set, adj_clamp; float adj_intensity, adj_contrast, adj_saturation, adj_hue, adj_mult[3]; // adj_hue already / 60 (texture.h:154)
+};
+
+// One shader node after its factory + configInputs; in1/in2/fac are stack indices (-1 = constant input)
+struct NodeDev
+{
+	int type, in1, in2, fac, mode;
+	// texture mapper after setup() (shader_node_basic.cc:33-55): offset doubled, bump_str scaled, d_u/d_v = 1 / resolution
+	int tex, coords, proj, map_x, map_y, map_z, do_scalar;
+	float scale[3], offset[3], bump_str, d_u, d_v;
+	float mtx[12];
+	float col[4], col2[4], f1, f2;   // value: colour, scalar; mix: color1, color2, cfactor; layer: def_col, upper_col, def_val, upper_val
+	float colfac, valfac; unsigned texflag; int do_color, do_scalar_l, color_input, use_alpha;
 };
 
 // Light record after constructor preprocessing.
@@ -155,6 +189,8 @@ struct SceneDev
 	const float *light_tables;
 	const Accel *light_accels;
 	const FaureTables *faure;
+	const TexDev *textures;
+	const NodeDev *nodes;
 	CameraDev cam;
 	BackgroundDev bg;
 	IntegratorDev integ;

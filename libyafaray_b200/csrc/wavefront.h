@@ -46,7 +46,7 @@ enum { CNT_RAYS_CAMERA = 0, CNT_RAYS_EXTENSION, CNT_RAYS_SHADOW, CNT_RAYS_SHADOW
        CNT_CAMERA_SAMPLES, CNT_NODES, CNT_TRIS, CNT_N };
 
 #define YG_MAX_ITERS 96
-#define YG_N_MAT_TYPES 10  /* yafgpu_material_type values 0..8 + YG_MAT_SD_LAMBERT */
+#define YG_N_MAT_TYPES 11  /* yafgpu_material_type values 0..8 + YG_MAT_SD_LAMBERT + YG_MAT_NODES */
 #define YG_MAX_BUCKETS 8200 /* 2 task kinds x up to 4096 material buckets + miss */
 #define YG_SHARED_BUCKETS 2048 /* up to this many buckets the histogram and the scatter ranks are staged per block in shared memory */
 

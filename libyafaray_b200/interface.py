@@ -15,6 +15,7 @@ import ctypes as C
 import numpy as np
 
 from . import capi
+from .capi import f32
 
 
 class _Mesh:
@@ -267,9 +268,7 @@ class Interface:
         m.transparent_bias_multiply_raydepth = int(g(p, "transparentbias_multiply_raydepth", False))
         m.sampling_factor = g(p, "samplingfactor", 1.0)
         m.mat_pass_index = int(g(p, "mat_pass_index", 0))
-        for k in p:
-            if k.endswith("_shader"):
-                raise NotImplementedError("material '%s': shader nodes (%s) are not implemented on the device" % (name, k))
+        self._node_records(name, m)
         col = lambda key, d: capi.F3(*[np.float32(x) for x in g(p, key, d)[:3]])
         if t == "shinydiffusemat":  # material_shiny_diffuse.cc:599-688
             m.type = capi.MAT_SHINYDIFFUSE
@@ -320,6 +319,130 @@ class Interface:
         else:
             raise NotImplementedError("material type '%s'" % t)
         return m
+
+    # ---- shader nodes and textures (material_node.cc:140-237, shader_node_basic.cc:344-420, shader_node_layer.cc:160-244) ----------
+    def _node_records(self, name, m):
+        """Appends this material's <list_element element="shader_node"> entries to self._nodes (declaration order) and binds the
+        "<slot>_shader" parameters, exactly what NodeMaterial::loadNodes / parseNodes read.  A texture_mapper whose texture does not
+        exist makes loadNodes fail in the reference, which then leaves the material without any node: mirrored."""
+        p, elems = self.materials[name]
+        g = self._g
+        for s in range(capi.N_SLOTS):
+            m.shader[s] = -1
+        m.node_first, m.node_count = len(self._nodes), 0
+        elems = [e for e in elems if g(e, "element", "shader_node") == "shader_node"]
+        if not elems:
+            return
+        names = [g(e, "name", None) for e in elems]
+        if None in names or len(set(names)) != len(names):
+            return  # loadNodes error -> no nodes
+        idx = {n: i for i, n in enumerate(names)}
+        recs = []
+        for e in elems:
+            t = g(e, "type", None)
+            r = capi.ShaderNode()
+            r.input1 = r.input2 = r.factor = r.texture = -1
+
+            def ref(key):
+                if key not in e:
+                    return -1
+                n = g(e, key, "")
+                if n not in idx:
+                    raise KeyError("shader node '%s': input '%s' does not exist" % (g(e, "name", ""), n))
+                return idx[n]
+            col4 = lambda key, d: (f32 * 4)(*[np.float32(x) for x in g(e, key, d)])
+            if t == "texture_mapper":
+                r.type = capi.NODE_TEXTURE_MAPPER
+                tn = g(e, "texture", None)
+                if tn is None or tn not in self.textures:
+                    return  # "texture does not exist" -> factory returns nullptr -> loadNodes fails -> the material has no nodes
+                r.texture = self._texture_index(tn)
+                r.texco = capi.TEXCO.get(g(e, "texco", "global"), capi.TEXCO["global"])
+                r.mapping = capi.TEXPROJ.get(g(e, "mapping", "plain"), 0)
+                r.proj_x, r.proj_y, r.proj_z = int(g(e, "proj_x", 1)), int(g(e, "proj_y", 2)), int(g(e, "proj_z", 3))
+                r.scale = capi.F3(*[np.float32(x) for x in g(e, "scale", (1, 1, 1))])
+                r.offset = capi.F3(*[np.float32(x) for x in g(e, "offset", (0, 0, 0))])
+                r.bump_strength, r.do_scalar = g(e, "bump_strength", 1.0), int(g(e, "do_scalar", True))
+                if "transform" in e:
+                    raise NotImplementedError("texture_mapper 'transform' matrices are not passed by this host mirror")
+                r.transform = (f32 * 16)(1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1)
+            elif t == "value":
+                r.type = capi.NODE_VALUE
+                c = g(e, "color", (1, 1, 1, 1))
+                r.color = (f32 * 4)(np.float32(c[0]), np.float32(c[1]), np.float32(c[2]), np.float32(g(e, "alpha", 1.0)))
+                r.scalar = g(e, "scalar", 1.0)
+            elif t == "mix":
+                r.type, r.mode = capi.NODE_MIX, int(g(e, "mode", 0))
+                r.input1, r.input2, r.factor = ref("input1"), ref("input2"), ref("factor")
+                if (r.input1 < 0 and "color1" not in e) or (r.input2 < 0 and "color2" not in e) or (r.factor < 0 and "value" not in e):
+                    return  # configInputs fails -> no nodes
+                r.color, r.color2 = col4("color1", (0, 0, 0, 1)), col4("color2", (0, 0, 0, 1))
+                r.scalar = g(e, "value", 0.0)
+            elif t == "layer":
+                r.type, r.mode = capi.NODE_LAYER, int(g(e, "mode", 0))
+                r.input1, r.input2 = ref("input"), ref("upper_layer")
+                if r.input1 < 0:
+                    return
+                dc = g(e, "def_col", (1, 1, 1, 1))
+                r.color = (f32 * 4)(np.float32(dc[0]), np.float32(dc[1]), np.float32(dc[2]), 1.0)
+                r.color2 = col4("upper_color", (0, 0, 0, 1))
+                r.scalar, r.scalar2 = g(e, "def_val", 1.0), g(e, "upper_value", 0.0)
+                r.colfac, r.valfac = g(e, "colfac", 1.0), g(e, "valfac", 1.0)
+                r.do_color, r.layer_do_scalar = int(g(e, "do_color", True)), int(g(e, "do_scalar", False))
+                r.color_input, r.use_alpha = int(g(e, "color_input", True)), int(g(e, "use_alpha", False))
+                r.no_rgb, r.stencil, r.negative = int(g(e, "noRGB", False)), int(g(e, "stencil", False)), int(g(e, "negative", False))
+            else:
+                raise NotImplementedError("shader node type '%s'" % t)
+            recs.append(r)
+        mtype = g(p, "type", "")
+        for key, slot in capi.SLOTS.items():
+            if key == "mask" and mtype != "blend_mat":
+                continue
+            if key in p:
+                n = g(p, key, "")
+                if n in idx:   # parseNodes only warns about a missing node (material_node.cc:216-235)
+                    m.shader[slot] = idx[n]
+        self._nodes += recs
+        m.node_count = len(recs)
+
+    def _texture_index(self, name):
+        if name in self._tex_index:
+            return self._tex_index[name]
+        p, g = self.textures[name], self._g
+        if g(p, "type", "") != "image":
+            raise NotImplementedError("texture type '%s' (only image textures are implemented on the device)" % g(p, "type", ""))
+        fn = g(p, "filename", "")
+        if isinstance(fn, str) and fn.lower().endswith(".hdr"):
+            rgb = read_radiance_hdr(fn)   # HDR: always linear, never "optimized" (texture_image.cc:600-606)
+            cs = capi.CS["LinearRGB"]
+        else:
+            raise NotImplementedError("image texture '%s': only Radiance .hdr is decoded by this host mirror (the C++ adaptor "
+                                      "takes any format the reference's image handlers load)" % fn)
+        rgba = np.ones(rgb.shape[:2] + (4,), np.float32)
+        rgba[..., :3] = rgb
+        rgba = np.ascontiguousarray(rgba)
+        t = capi.Texture()
+        t.type, t.width, t.height, t.rgba = capi.TEX_IMAGE, rgba.shape[1], rgba.shape[0], rgba.ctypes.data_as(capi.pf)
+        interp = g(p, "interpolate", "bilinear")
+        if interp in ("mipmap_trilinear", "mipmap_ewa"):
+            raise NotImplementedError("texture interpolate '%s' (ray differentials) is not implemented on the device" % interp)
+        t.interpolate = capi.TEXINTERP.get(interp, 1)
+        t.clip_mode = capi.TEXCLIP.get(g(p, "clipping", "repeat"), capi.TEXCLIP["repeat"])  # string2Cliptype__: unknown -> repeat
+        t.xrepeat, t.yrepeat = int(g(p, "xrepeat", 1)), int(g(p, "yrepeat", 1))
+        t.mirror_x, t.mirror_y, t.rot90 = int(g(p, "mirror_x", False)), int(g(p, "mirror_y", False)), int(g(p, "rot90", False))
+        t.cropmin_x, t.cropmin_y = g(p, "cropmin_x", 0.0), g(p, "cropmin_y", 0.0)
+        t.cropmax_x, t.cropmax_y = g(p, "cropmax_x", 1.0), g(p, "cropmax_y", 1.0)
+        t.checker_even, t.checker_odd = int(g(p, "even_tiles", False)), int(g(p, "odd_tiles", True))
+        t.checker_dist = g(p, "checker_dist", 0.0)
+        t.normalmap, t.color_space, t.gamma = int(g(p, "normalmap", False)), cs, g(p, "gamma", 1.0)
+        t.adj_intensity, t.adj_contrast = g(p, "adj_intensity", 1.0), g(p, "adj_contrast", 1.0)
+        t.adj_saturation, t.adj_hue = g(p, "adj_saturation", 1.0), float(np.float32(g(p, "adj_hue", 0.0)) / np.float32(60.0))
+        t.adj_mult_red, t.adj_mult_green, t.adj_mult_blue = g(p, "adj_mult_factor_red", 1.0), g(p, "adj_mult_factor_green", 1.0), g(p, "adj_mult_factor_blue", 1.0)
+        t.adj_clamp = int(g(p, "adj_clamp", False))
+        self._tex_index[name] = len(self._texs)
+        self._texs.append(t)
+        self._tex_keep.append(rgba)
+        return self._tex_index[name]
 
     def _light_record(self, p, obj_index_of_id):
         g = self._g
@@ -398,6 +521,7 @@ class Interface:
                 raise KeyError("unknown material '%s'" % n)
             return mat_index[n]
         mats = (capi.Material * max(1, len(mat_names)))()
+        self._nodes, self._texs, self._tex_index, self._tex_keep = [], [], {}, []
         for i, n in enumerate(mat_names):
             mats[i] = self._material_record(n, index_of)
 
@@ -484,6 +608,10 @@ class Interface:
         ge.tri_uvidx = pin(A_u) if any_uv else None
         ge.objects, ge.n_objects = objarr, len(objs)
         d.materials, d.n_materials = mats, len(mat_names)
+        narr = (capi.ShaderNode * max(1, len(self._nodes)))(*self._nodes)
+        tarr = (capi.Texture * max(1, len(self._texs)))(*self._texs)
+        d.nodes, d.n_nodes, d.textures, d.n_textures = narr, len(self._nodes), tarr, len(self._texs)
+        keep += [narr, tarr, self._tex_keep]
 
         def obj_index_of_id(oid):
             return obj_index.get(oid, -1) if oid else -1

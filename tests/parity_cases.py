@@ -236,3 +236,166 @@ FRONTEND_ONLY = {
     "cornell_dl_adaptive": lambda: scenes.cornell_box(160, 90, 2, integrator="directlighting", aa_passes=3, AA_threshold=0.02, AA_inc_samples=2),
 }
 CONVERGED["zoo_pt"] = (lambda spp: material_zoo_scene(W, H, spp), 8192)
+
+
+# ---- §8f rank 1: shader-node graphs and image textures ---------------------------------------------------------------------
+TEX_HDR = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden", "tex_48x40.hdr")
+
+
+def make_tex_hdr(path=TEX_HDR):
+    """The texture fixture (written once by tools/make_golden.py): smooth colour ramps, a diagonal stripe pattern and a few bright texels;
+    non-square and not a power of two so that row/column mix-ups show."""
+    import numpy as np
+    from libyafaray_b200.interface import write_radiance_hdr
+    h, w = 40, 48
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    img = np.zeros((h, w, 3), np.float32)
+    img[..., 0] = 0.15 + 0.8 * xx / (w - 1)
+    img[..., 1] = 0.1 + 0.85 * yy / (h - 1)
+    img[..., 2] = 0.5 + 0.45 * np.sin(0.9 * xx + 0.6 * yy)
+    stripe = ((xx + 2 * yy).astype(np.int32) // 5) % 2 == 0
+    img[stripe] *= 0.35
+    img[5:9, 30:36] = (1.6, 0.2, 0.1)
+    write_radiance_hdr(path, img)
+    return path
+
+
+def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=None, variant="basic", **integ):
+    """Ground quad with uv coordinates and six boxes (three of them with orco coordinates) whose shinydiffuse materials read their
+    colours / component strengths / bump from node graphs: texture_mapper (uv, orco, global, transformed; plain, cube, tube, sphere),
+    layer (all blend modes, stencil, negative, noRGB), mix (all modes) and value nodes over an image texture."""
+    from libyafaray_b200.interface import Interface
+    y = Interface(); y.startScene(0)
+    tex = dict(tex or {})
+    y.paramsClearAll(); y.paramsSetString("type", "image"); y.paramsSetString("filename", TEX_HDR)
+    _set_params(y, tex); y.createTexture("tex")
+    y.paramsClearAll(); y.paramsSetString("type", "image"); y.paramsSetString("filename", ENV_HDR); y.paramsSetString("interpolate", "bicubic")
+    y.paramsSetString("clipping", "extend"); y.createTexture("tex2")
+
+    def node(**kw):
+        y.paramsPushList(); y.paramsSetString("element", "shader_node"); _set_params(y, kw)
+
+    def mapper(name, texture="tex", **kw):
+        node(type="texture_mapper", name=name, texture=texture, **kw)
+
+    def layer(name, inp, **kw):
+        d = dict(type="layer", name=name, input=inp, mode=0, colfac=1.0, def_col=(1.0, 0.0, 1.0, 1.0), def_val=1.0, do_color=True, do_scalar=False,
+                 color_input=True, negative=False, noRGB=False, stencil=False, use_alpha=False, upper_color=(0.9, 0.9, 0.9, 1.0), upper_value=0.0)
+        d.update(kw)
+        node(**d)
+
+    def sd(name, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", "shinydiffusemat"); _set_params(y, kw)
+
+    modes = {"basic": (0, 2, 4), "modes_b": (1, 3, 6), "modes_c": (5, 7, 8)}.get(variant, (0, 2, 4))
+    # ground: uv-mapped, repeated 3x2, plain projection
+    sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
+    layer("gl", "gm", mode=modes[0], colfac=0.9)
+    mapper("gm", texco="uv", mapping="plain", scale=(3.0, 2.0, 1.0), offset=(0.1, 0.05, 0.0))
+    y.createMaterial("ground")
+    # box 0: orco + cube projection (the test01 setup), with emission from the textured colour
+    sd("b0", color=(0.9, 0.9, 0.9, 1.0), diffuse_reflect=0.8, emit=0.05, diffuse_shader="l0")
+    layer("l0", "m0", mode=modes[1], colfac=0.8)
+    mapper("m0", texco="orco", mapping="cube", proj_x=1, proj_y=2, proj_z=3)
+    y.createMaterial("b0")
+    # box 1: global coordinates + tube projection; mirror strength and mirror colour from nodes; Fresnel with a textured IOR
+    sd("b1", color=(0.8, 0.6, 0.4, 1.0), specular_reflect=0.2, fresnel_effect=True, IOR=1.5, mirror_shader="l1s", mirror_color_shader="l1c", diffuse_shader="l1c",
+       IOR_shader="l1i")
+    layer("l1s", "m1", do_color=False, do_scalar=True, color_input=False, def_val=0.6, upper_value=0.1, mode=modes[2], valfac=0.9)
+    layer("l1c", "m1", mode=0, colfac=0.7, upper_color=(0.3, 0.5, 0.9, 1.0))
+    layer("l1i", "m1", do_color=False, do_scalar=True, color_input=True, def_val=0.4, upper_value=0.05, noRGB=False)
+    mapper("m1", texco="global", mapping="tube", scale=(1.0, 1.0, 0.7))
+    y.createMaterial("b1")
+    # box 2: transformed... kept as global + sphere projection; transparency and translucency from nodes, stencil + negative layers stacked
+    sd("b2", color=(0.5, 0.8, 0.5, 1.0), transparency=0.1, translucency=0.1, transmit_filter=0.7, transparency_shader="l2t", translucency_shader="l2u", diffuse_shader="l2b")
+    layer("l2t", "m2", do_color=False, do_scalar=True, color_input=True, noRGB=True, def_val=0.5, upper_value=0.0)
+    layer("l2u", "m2", do_color=False, do_scalar=True, color_input=False, def_val=0.3, upper_value=0.05, negative=True)
+    layer("l2a", "m2", mode=0, stencil=True, colfac=1.0, upper_color=(0.9, 0.2, 0.2, 1.0))
+    layer("l2b", "m2b", upper_layer="l2a", mode=modes[0], colfac=0.6, negative=True)
+    mapper("m2", texco="global", mapping="sphere", proj_x=2, proj_y=3, proj_z=1)
+    mapper("m2b", texture="tex2", texco="orco", mapping="plain", scale=(0.8, 0.8, 0.8))
+    y.createMaterial("b2")
+    # box 3: mix / value nodes: diffuse = mix_k(texture, value); Oren-Nayar with a textured sigma; diffuse_refl_shader
+    sd("b3", color=(0.8, 0.8, 0.8, 1.0), diffuse_brdf="oren_nayar", sigma=0.3, diffuse_shader="x3", sigma_oren_shader="l3s", diffuse_refl_shader="l3r")
+    node(type="mix", name="x3", input1="m3", input2="v3", factor="l3s", mode={"basic": 0, "modes_b": 4, "modes_c": 8}.get(variant, 0))
+    node(type="mix", name="x3b", input1="m3", color2=(0.2, 0.3, 0.9, 1.0), value=0.4, mode={"basic": 1, "modes_b": 6, "modes_c": 7}.get(variant, 1))
+    node(type="value", name="v3", color=(0.9, 0.7, 0.2, 1.0), alpha=0.8, scalar=0.35)
+    layer("l3s", "m3", do_color=False, do_scalar=True, color_input=True, def_val=0.8, upper_value=0.1)
+    layer("l3r", "x3b", do_color=False, do_scalar=True, color_input=True, def_val=0.9, upper_value=0.2)
+    mapper("m3", texco="orco", mapping="cube", proj_x=3, proj_y=1, proj_z=2, scale=(1.5, 1.5, 1.5))
+    y.createMaterial("b3")
+    # box 4: bump mapping from the texture through orco coordinates (the non-uv derivative path) + a coloured layer
+    sd("b4", color=(0.7, 0.7, 0.9, 1.0), specular_reflect=0.15, bump_shader="l4b", diffuse_shader="l4c")
+    layer("l4b", "m4", do_color=False, do_scalar=True, color_input=False)
+    layer("l4c", "m4", mode=2, colfac=0.5)
+    mapper("m4", texco="orco", mapping="cube", bump_strength=3.0, scale=(2.0, 2.0, 2.0))
+    y.createMaterial("b4")
+    # box 5 (has uv): bump through uv coordinates (the uv derivative path), two stacked bump layers
+    sd("b5", color=(0.9, 0.8, 0.6, 1.0), bump_shader="l5b2", diffuse_shader="l5c")
+    layer("l5b1", "m5", do_color=False, do_scalar=True, color_input=False)
+    layer("l5b2", "m5b", upper_layer="l5b1", do_color=False, do_scalar=True, color_input=False, negative=True)
+    layer("l5c", "m5", mode=0, colfac=0.85)
+    mapper("m5", texco="uv", mapping="plain", bump_strength=2.0)
+    mapper("m5b", texture="tex2", texco="uv", mapping="plain", bump_strength=0.5, scale=(2.0, 2.0, 1.0))
+    y.createMaterial("b5")
+
+    def box(oid, lo, hi, mat, orco=False, uv=False, rot=0.0):
+        import math
+        cx, cy = 0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1])
+        c, s = math.cos(math.radians(rot)), math.sin(math.radians(rot))
+        y.startTriMesh(oid, 8, 12, orco, uv, 0)
+        vs = []
+        for k in range(8):
+            px, py, pz = (hi if k & 1 else lo)[0], (hi if k & 2 else lo)[1], (hi if k & 4 else lo)[2]
+            rx, ry = cx + c * (px - cx) - s * (py - cy), cy + s * (px - cx) + c * (py - cy)
+            if orco:
+                vs.append(y.addVertex(rx, ry, pz, 2.0 * (k & 1) - 1.0, 2.0 * ((k >> 1) & 1) - 1.0, 2.0 * ((k >> 2) & 1) - 1.0))
+            else:
+                vs.append(y.addVertex(rx, ry, pz))
+        if uv:
+            uvs = [y.addUv(0.0, 0.0), y.addUv(1.0, 0.0), y.addUv(1.0, 1.0), y.addUv(0.0, 1.0)]
+        for q in ((0, 2, 3, 1), (4, 5, 7, 6), (0, 1, 5, 4), (2, 6, 7, 3), (0, 4, 6, 2), (1, 3, 7, 5)):
+            a, b, cc, d = (vs[i] for i in q)
+            if uv:
+                y.addTriangle(a, b, cc, uvs[0], uvs[1], uvs[2], mat); y.addTriangle(a, cc, d, uvs[0], uvs[2], uvs[3], mat)
+            else:
+                y.addTriangle(a, b, cc, mat); y.addTriangle(a, cc, d, mat)
+        y.endTriMesh()
+
+    y.startGeometry()
+    y.startTriMesh(1, 4, 2, False, True, 0)
+    a, b, c, d = y.addVertex(-8, -8, 0), y.addVertex(8, -8, 0), y.addVertex(8, 8, 0), y.addVertex(-8, 8, 0)
+    u0, u1, u2, u3 = y.addUv(0.0, 0.0), y.addUv(1.0, 0.0), y.addUv(1.0, 1.0), y.addUv(0.0, 1.0)
+    y.addTriangle(a, b, c, u0, u1, u2, "ground"); y.addTriangle(a, c, d, u0, u2, u3, "ground")
+    y.endTriMesh()
+    for i, (m, orco, uv) in enumerate((("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))):
+        x0, y0 = -3.3 + 2.3 * (i % 3), -0.6 + 2.5 * (i // 3)
+        box(2 + i, (x0, y0, 0.003), (x0 + 1.5, y0 + 1.5, 1.1 + 0.2 * i), m, orco, uv, rot=13.0 * i)
+    y.endGeometry()
+    y.paramsClearAll(); y.paramsSetString("type", "pointlight"); y.paramsSetPoint("from", -2.0, -5.0, 6.0)
+    y.paramsSetColor("color", 1.0, 0.95, 0.9); y.paramsSetFloat("power", 60.0); y.createLight("L")
+    if integ.get("area_light"):
+        y.paramsClearAll(); y.paramsSetString("type", "arealight"); y.paramsSetPoint("corner", 2.0, -2.0, 5.0); y.paramsSetPoint("point1", 3.0, -2.0, 5.0)
+        y.paramsSetPoint("point2", 2.0, -1.0, 5.0); y.paramsSetColor("color", 0.8, 0.9, 1.0); y.paramsSetFloat("power", 25.0); y.paramsSetInt("samples", 2); y.createLight("A")
+    y.paramsClearAll(); y.paramsSetString("type", "perspective")
+    y.paramsSetPoint("from", 0.5, -7.5, 4.5); y.paramsSetPoint("to", 0.0, 1.0, 0.6); y.paramsSetPoint("up", 0.5, -7.5, 5.5)
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3); y.createCamera("cam")
+    y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.3, 0.4, 0.6); y.paramsSetFloat("power", 0.7); y.createBackground("bg")
+    y.paramsClearAll(); y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", integ.get("raydepth", 3)); y.paramsSetInt("shadowDepth", 3)
+    if integrator == "pathtracing":
+        y.paramsSetInt("path_samples", integ.get("path_samples", 2)); y.paramsSetInt("bounces", integ.get("bounces", 4))
+        y.paramsSetInt("russian_roulette_min_bounces", integ.get("rr_min_bounces", 99))
+    y.createIntegrator("pt")
+    scenes._vol_none(y)
+    scenes.render_block(y, width, height, spp)
+    return y
+
+
+EXACT["tex_dl_basic"] = lambda: textured_scene(96, 54, 2)
+EXACT["tex_dl_modes_b"] = lambda: textured_scene(96, 54, 2, variant="modes_b", tex={"interpolate": "none", "clipping": "extend"})
+EXACT["tex_dl_modes_c"] = lambda: textured_scene(96, 54, 2, variant="modes_c", tex={"interpolate": "bicubic", "mirror_x": True, "mirror_y": True, "xrepeat": 2, "yrepeat": 3})
+EXACT["tex_dl_adjust"] = lambda: textured_scene(96, 54, 2, tex={"adj_contrast": 1.3, "adj_intensity": 0.9, "adj_saturation": 1.4, "adj_hue": 40.0, "adj_clamp": True,
+                                                                "adj_mult_factor_red": 0.9, "adj_mult_factor_blue": 1.2, "rot90": True, "cropmin_x": 0.1, "cropmax_x": 0.8, "cropmax_y": 0.9})
+EXACT["tex_dl_checker"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "checker", "even_tiles": True, "odd_tiles": False, "checker_dist": 0.2, "xrepeat": 2})
+EXACT["tex_dl_clip"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "clip", "cropmin_y": 0.2})
+EXACT["tex_pt_norr"] = lambda: textured_scene(96, 54, 4, integrator="pathtracing")

@@ -113,7 +113,8 @@ def test_render_matches_reference_film(ctx, name):
 # ---- the drop-in boundary itself: reference XML loader + Scene + ImageFilm with GpuIntegrator linked in ----------------------
 FRONTEND_CASES = ["simple_dl_gauss", "cornell_dl_glass", "cornell_dl_mitchell", "cornell_pt_norr", "zoo_dl_point_free", "zoo_pt_mesh_norr",
                   "zoo_dl_hdr_ibl", "zoo_dl_hdr_angular", "cornell_dl_adaptive", "zoo_dl_directional", "zoo_dl_spot_soft", "zoo_dl_sphere",
-                  "zoo_dl_gradient_ibl", "zoo_dl_cam_ortho", "zoo_dl_cam_architect", "zoo_dl_cam_angular_stereo", "zoo_dl_cam_equirect"]
+                  "zoo_dl_gradient_ibl", "zoo_dl_cam_ortho", "zoo_dl_cam_architect", "zoo_dl_cam_angular_stereo", "zoo_dl_cam_equirect",
+                  "tex_dl_basic", "tex_dl_modes_c", "tex_dl_adjust", "tex_pt_norr"]
 
 
 @pytest.mark.skipif(ou.gpu_frontend_bin() is None, reason="oracle/_ref/yaf_xml_gpu not built (needs the reference sources)")
@@ -127,6 +128,29 @@ def test_reference_frontend_with_gpu_integrator(name):
     assert r.returncode == 0, r.stderr.decode(errors="replace")[-2000:]
     assert b"GPU integrator substituted" in r.stderr + r.stdout or info.get("rendert_s") is not None
     _assert_film_matches(film, gold)
+
+
+TEST01 = os.path.join(ROOT, "oracle", "_ref", "test01")
+
+
+@pytest.mark.skipif(ou.gpu_frontend_bin() is None or ou.ref_bin() is None or not os.path.exists(os.path.join(TEST01, "test01.xml")),
+                    reason="needs oracle/_ref (yaf_xml_gpu, yaf_ref_ieee and the staged tests/test01 scene)")
+def test_config0_reference_test01_scene_through_the_frontend():
+    """BASELINE.json configs[0]: the reference's own tests/test01/test01.xml (480x270, DirectLight, gauss filter, shinydiffuse materials whose
+    colours come from layer + texture_mapper (orco, cube) nodes over TGA / HDR images), loaded by the reference's XML loader and image
+    handlers, rendered by the GPU integrator, compared with the reference's CPU integrator run live on the same file."""
+    import subprocess, tempfile
+    with tempfile.TemporaryDirectory() as td:
+        films = []
+        for exe in (ou.ref_bin(), ou.gpu_frontend_bin()):
+            out = os.path.join(td, os.path.basename(exe) + ".film")
+            r = subprocess.run([exe, "render", "test01.xml", out, "1"], cwd=TEST01, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=900)
+            assert r.returncode == 0, r.stderr.decode(errors="replace")[-2000:]
+            if exe == ou.gpu_frontend_bin():
+                assert b"GPU integrator substituted" in r.stderr + r.stdout
+            films.append(ou.load_film(out))
+    assert films[0].shape == (270, 480, 5)
+    _assert_film_matches(films[1], films[0])
 
 
 TOL_CONVERGED = {"cornell_pt": 4e-3, "cornell_pt_noglass": 3e-3, "zoo_pt": 5e-3, "cornell_pt_512k": 1.5e-3}
