@@ -73,7 +73,6 @@ inline bool prepShinyDiffuse(const yafgpu_material &m, MatDev &d, std::string &e
 	}
 	// pure Lambert/Oren-Nayar surface: gets its own shading kernel (materials.cuh YG_MAT_SD_LAMBERT); same arithmetic, fewer branches
 	if(d.n_bsdf == 1 && d.is_diffuse && !d.has_fresnel && d.node_count == 0) d.type = YG_MAT_SD_LAMBERT;
-	if(d.slot[YAFGPU_SLOT_WIREFRAME] >= 0) { err = "shinydiffusemat: wireframe_shader is not implemented on the device"; return false; }
 	(void)err;
 	return true;
 }
@@ -286,7 +285,23 @@ inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
 	// node fields (node_first .. slot[]) were filled by prepNodes and are kept
 	{ MatDev keep = d; memset(&d, 0, sizeof(d)); d.node_first = keep.node_first; d.node_count = keep.node_count; d.color_mask = keep.color_mask; d.bump_mask = keep.bump_mask; memcpy(d.slot, keep.slot, sizeof(d.slot)); }
 	d.diffuse_refl_mul = 1.f;
-	if(d.node_count > 0 && m.type != YAFGPU_MAT_SHINYDIFFUSE) { err = "shader nodes on this material type are not implemented on the device yet"; return false; }
+	if(d.node_count > 0)
+	{	// which "<slot>_shader" parameters each factory looks up (material_*.cc node_list[...]); a slot the type does not have is ignored there
+		static const unsigned allowed[9] = {
+			/* shinydiffuse */ 1u << YAFGPU_SLOT_DIFFUSE | 1u << YAFGPU_SLOT_MIRROR_COLOR | 1u << YAFGPU_SLOT_BUMP | 1u << YAFGPU_SLOT_MIRROR | 1u << YAFGPU_SLOT_TRANSPARENCY |
+			                   1u << YAFGPU_SLOT_TRANSLUCENCY | 1u << YAFGPU_SLOT_SIGMA_OREN | 1u << YAFGPU_SLOT_DIFFUSE_REFL | 1u << YAFGPU_SLOT_IOR | 1u << YAFGPU_SLOT_WIREFRAME,
+			/* glossy */       1u << YAFGPU_SLOT_DIFFUSE | 1u << YAFGPU_SLOT_GLOSSY | 1u << YAFGPU_SLOT_GLOSSY_REFLECT | 1u << YAFGPU_SLOT_BUMP | 1u << YAFGPU_SLOT_SIGMA_OREN |
+			                   1u << YAFGPU_SLOT_EXPONENT | 1u << YAFGPU_SLOT_WIREFRAME | 1u << YAFGPU_SLOT_DIFFUSE_REFL,
+			/* coated */       1u << YAFGPU_SLOT_DIFFUSE | 1u << YAFGPU_SLOT_GLOSSY | 1u << YAFGPU_SLOT_GLOSSY_REFLECT | 1u << YAFGPU_SLOT_BUMP | 1u << YAFGPU_SLOT_SIGMA_OREN |
+			                   1u << YAFGPU_SLOT_EXPONENT | 1u << YAFGPU_SLOT_WIREFRAME | 1u << YAFGPU_SLOT_DIFFUSE_REFL | 1u << YAFGPU_SLOT_MIRROR | 1u << YAFGPU_SLOT_MIRROR_COLOR | 1u << YAFGPU_SLOT_IOR,
+			/* glass */        1u << YAFGPU_SLOT_MIRROR_COLOR | 1u << YAFGPU_SLOT_BUMP | 1u << YAFGPU_SLOT_FILTER_COLOR | 1u << YAFGPU_SLOT_IOR | 1u << YAFGPU_SLOT_WIREFRAME,
+			/* rough glass */  1u << YAFGPU_SLOT_MIRROR_COLOR | 1u << YAFGPU_SLOT_BUMP | 1u << YAFGPU_SLOT_FILTER_COLOR | 1u << YAFGPU_SLOT_IOR | 1u << YAFGPU_SLOT_WIREFRAME | 1u << YAFGPU_SLOT_ROUGHNESS,
+			/* blend */        1u << YAFGPU_SLOT_BLEND,
+			0u, 0u, 0u };
+		if(m.type < 0 || m.type > 8 || allowed[m.type] == 0u) { err = "shader nodes on this material type are not implemented on the device"; return false; }
+		for(int s = 0; s < YAFGPU_N_SLOTS; ++s) if(d.slot[s] >= 0 && !(allowed[m.type] >> s & 1u)) { err = "shader slot " + std::to_string(s) + " does not exist on material type " + std::to_string(m.type); return false; }
+		if(d.slot[YAFGPU_SLOT_WIREFRAME] >= 0) { err = "wireframe_shader is not implemented on the device"; return false; }
+	}
 	d.type = m.type; d.visibility = m.visibility; d.receive_shadows = m.receive_shadows; d.flat = m.flat_material;
 	d.additional_depth = m.additional_depth; d.transp_bias_factor = m.transparent_bias_factor;
 	d.transp_bias_mult = m.transparent_bias_multiply_raydepth; d.sampling_factor = m.sampling_factor;

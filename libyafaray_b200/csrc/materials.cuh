@@ -336,7 +336,8 @@ YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdf
 			if(m.with_diffuse && diffuse_flag)
 			{
 				Col add_col = (m.gl_diffuse * (1.f - m.gl_glossy)) * ldc(m.diff_col);
-				if(m.gl_oren_nayar) add_col = add_col * orenNayar(m.gl_oren_a, m.gl_oren_b, wl, wo, n);
+				if(MT < 0) add_col = add_col * m.diffuse_refl_mul; // "diffuse_refl_shader"; 1 when absent
+				if(m.gl_oren_nayar) add_col = add_col * ((MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wl, wo, n) : orenNayar(m.gl_oren_a, m.gl_oren_b, wl, wo, n));
 				col = col + add_col;
 			}
 			return col;
@@ -366,7 +367,8 @@ YG_D Col leafEval(const MatDev &m, const SurfPt &sp, V3 wo, V3 wl, unsigned bsdf
 			if(m.with_diffuse && diffuse_flag)
 			{
 				Col add_col = ((m.gl_diffuse * (1.f - m.gl_glossy)) * ldc(m.diff_col)) * kt;
-				if(m.gl_oren_nayar) add_col = add_col * orenNayar(m.gl_oren_a, m.gl_oren_b, wl, wo, n);
+				if(MT < 0) add_col = add_col * m.diffuse_refl_mul; // "diffuse_refl_shader"; 1 when absent
+				if(m.gl_oren_nayar) add_col = add_col * ((MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wl, wo, n) : orenNayar(m.gl_oren_a, m.gl_oren_b, wl, wo, n));
 				col = col + add_col;
 			}
 			return col;
@@ -630,7 +632,8 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 					scolor = glossy * ldc(m.gloss_col);
 					{
 						Col add_col = diffuseReflect(wi_n, wo_n, m.gl_glossy, m.gl_diffuse, ldc(m.diff_col));
-						if(m.gl_oren_nayar) add_col = add_col * orenNayar(m.gl_oren_a, m.gl_oren_b, wi, wo, n);
+						if(MT < 0) add_col = add_col * m.diffuse_refl_mul; // "diffuse_refl_shader"; 1 when absent
+						if(m.gl_oren_nayar) add_col = add_col * ((MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wi, wo, n) : orenNayar(m.gl_oren_a, m.gl_oren_b, wi, wo, n));
 						scolor = scolor + add_col;
 					}
 					w = wi_n / (s.pdf * 0.99f + 0.01f);
@@ -665,7 +668,8 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 			if(use_diffuse)
 			{
 				Col add_col = diffuseReflect(wi_n, wo_n, m.gl_glossy, m.gl_diffuse, ldc(m.diff_col));
-				if(m.gl_oren_nayar) add_col = add_col * orenNayar(m.gl_oren_a, m.gl_oren_b, wi, wo, n);
+				if(MT < 0) add_col = add_col * m.diffuse_refl_mul; // "diffuse_refl_shader"; 1 when absent
+				if(m.gl_oren_nayar) add_col = add_col * ((MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wi, wo, n) : orenNayar(m.gl_oren_a, m.gl_oren_b, wi, wo, n));
 				s.pdf = wi_n * cur_p_diffuse + s.pdf * (1.f - cur_p_diffuse);
 				scolor = scolor + add_col;
 			}
@@ -769,7 +773,8 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 				if(use[2])
 				{
 					Col add_col = kt * diffuseReflect(wi_n, wo_n, m.gl_glossy, m.gl_diffuse, ldc(m.diff_col));
-					if(m.gl_oren_nayar) add_col = add_col * orenNayar(m.gl_oren_a, m.gl_oren_b, wi, wo, n);
+					if(MT < 0) add_col = add_col * m.diffuse_refl_mul; // "diffuse_refl_shader"; 1 when absent
+					if(m.gl_oren_nayar) add_col = add_col * ((MT < 0 && m.oren_tex) ? orenNayarTex(m.oren_sigma, wi, wo, n) : orenNayar(m.gl_oren_a, m.gl_oren_b, wi, wo, n));
 					scolor = scolor + add_col;
 					s.pdf += wi_n * width[rc_index[2]];
 				}

@@ -687,6 +687,40 @@ YG_DN void evalMaterialNodes(const SceneDev &sc, MatDev &ml, SurfPt &sp, int tri
 			if(YG_SLOT(SIGMA_OREN) >= 0) { ml.oren_tex = 1; ml.oren_sigma = stack[YG_SLOT(SIGMA_OREN)].f; }
 			break;
 		}
+		case YAFGPU_MAT_GLOSSY:
+		case YAFGPU_MAT_COATED_GLOSSY:
+		{	// material_glossy.cc:51-64,113-173,175-357; material_coated_glossy.cc:67-80,130-185,187-369,430-463
+			if(YG_SLOT(DIFFUSE) >= 0) { const Rgba4 c = stack[YG_SLOT(DIFFUSE)].col; ml.diff_col[0] = c.r; ml.diff_col[1] = c.g; ml.diff_col[2] = c.b; }
+			if(YG_SLOT(GLOSSY) >= 0) { const Rgba4 c = stack[YG_SLOT(GLOSSY)].col; ml.gloss_col[0] = c.r; ml.gloss_col[1] = c.g; ml.gloss_col[2] = c.b; }
+			if(YG_SLOT(GLOSSY_REFLECT) >= 0)
+			{	// initBsdf: m_glossy_ from the node, p_diffuse_ recomputed from it
+				ml.gl_glossy = stack[YG_SLOT(GLOSSY_REFLECT)].f;
+				ml.p_diffuse = fminf(0.6f, 1.f - (ml.gl_glossy / (ml.gl_glossy + (1.f - ml.gl_glossy) * ml.gl_diffuse)));
+			}
+			if(YG_SLOT(EXPONENT) >= 0) ml.gl_exponent = stack[YG_SLOT(EXPONENT)].f;
+			if(YG_SLOT(DIFFUSE_REFL) >= 0) ml.diffuse_refl_mul = stack[YG_SLOT(DIFFUSE_REFL)].f;
+			if(YG_SLOT(SIGMA_OREN) >= 0) { ml.oren_tex = 1; ml.oren_sigma = stack[YG_SLOT(SIGMA_OREN)].f; }
+			if(ml.type == YAFGPU_MAT_COATED_GLOSSY)
+			{
+				if(YG_SLOT(MIRROR_COLOR) >= 0) { const Rgba4 c = stack[YG_SLOT(MIRROR_COLOR)].col; ml.gl_mirror_col[0] = c.r; ml.gl_mirror_col[1] = c.g; ml.gl_mirror_col[2] = c.b; }
+				if(YG_SLOT(MIRROR) >= 0) ml.gl_mirror_strength = stack[YG_SLOT(MIRROR)].f;
+				if(YG_SLOT(IOR) >= 0) ml.ior = ml.ior + stack[YG_SLOT(IOR)].f;
+			}
+			break;
+		}
+		case YAFGPU_MAT_GLASS:
+		case YAFGPU_MAT_ROUGH_GLASS:
+		{	// material_glass.cc:63-215,250-309; material_rough_glass.cc:60-170,172-290 (getTransparency reads the IOR node differently,
+			// :223 / :298, but is only reached through transparent shadows, which are refused for node materials)
+			if(YG_SLOT(FILTER_COLOR) >= 0) { const Rgba4 c = stack[YG_SLOT(FILTER_COLOR)].col; ml.filter_col[0] = c.r; ml.filter_col[1] = c.g; ml.filter_col[2] = c.b; }
+			if(YG_SLOT(MIRROR_COLOR) >= 0) { const Rgba4 c = stack[YG_SLOT(MIRROR_COLOR)].col; ml.spec_refl_col[0] = c.r; ml.spec_refl_col[1] = c.g; ml.spec_refl_col[2] = c.b; }
+			if(YG_SLOT(IOR) >= 0) ml.ior = ml.ior + stack[YG_SLOT(IOR)].f;
+			if(ml.type == YAFGPU_MAT_ROUGH_GLASS && YG_SLOT(ROUGHNESS) >= 0) ml.alpha_rough = stack[YG_SLOT(ROUGHNESS)].f + 0.001f; // alpha_2 = alpha_texture^2 (:69-70)
+			break;
+		}
+		case YAFGPU_MAT_BLEND: // BlendMaterial::getBlendVal material_blend.cc:57-75
+			if(YG_SLOT(BLEND) >= 0) ml.blend_val = stack[YG_SLOT(BLEND)].f;
+			break;
 		default: break;
 	}
 #undef YG_SLOT

@@ -288,6 +288,86 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
         y.paramsClearAll(); y.paramsSetString("type", "shinydiffusemat"); _set_params(y, kw)
 
     modes = {"basic": (0, 2, 4), "modes_b": (1, 3, 6), "modes_c": (5, 7, 8)}.get(variant, (0, 2, 4))
+    if variant == "materials":
+        _textured_other_materials(y, sd, node, mapper, layer)
+        box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
+    else:
+        _textured_shinydiffuse_materials(y, sd, node, mapper, layer, modes, variant)
+        box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
+    _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, integ)
+    return y
+
+
+def _textured_other_materials(y, sd, node, mapper, layer):
+    """glossy, coated_glossy, glass, rough_glass and blend_mat with every "<slot>_shader" those factories know."""
+    def mat(typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ); _set_params(y, kw)
+    sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
+    layer("gl", "gm", mode=0, colfac=0.9)
+    mapper("gm", texco="uv", mapping="plain", scale=(3.0, 2.0, 1.0))
+    y.createMaterial("ground")
+    # glossy: glossy / diffuse colours, reflectivity, exponent, diffuse_refl and a textured Oren-Nayar sigma
+    mat("glossy", color=(0.9, 0.6, 0.2, 1.0), diffuse_color=(0.5, 0.3, 0.1, 1.0), diffuse_reflect=0.5, glossy_reflect=0.7, exponent=120.0, as_diffuse=False,
+        diffuse_brdf="Oren-Nayar", sigma=0.2, glossy_shader="g_c", diffuse_shader="g_d", glossy_reflect_shader="g_r", exponent_shader="g_e",
+        diffuse_refl_shader="g_f", sigma_oren_shader="g_s")
+    layer("g_c", "g_m", mode=0, colfac=0.6, upper_color=(0.9, 0.6, 0.2, 1.0))
+    layer("g_d", "g_m", mode=2, colfac=0.8, upper_color=(0.5, 0.4, 0.3, 1.0))
+    layer("g_r", "g_m", do_color=False, do_scalar=True, color_input=True, def_val=0.9, upper_value=0.3)
+    layer("g_e", "g_m", do_color=False, do_scalar=True, color_input=True, def_val=300.0, upper_value=20.0)
+    layer("g_f", "g_m", do_color=False, do_scalar=True, color_input=False, def_val=0.9, upper_value=0.4)
+    layer("g_s", "g_m", do_color=False, do_scalar=True, color_input=True, def_val=0.7, upper_value=0.05)
+    mapper("g_m", texco="orco", mapping="cube", scale=(1.3, 1.3, 1.3))
+    y.createMaterial("b0")
+    # coated glossy: + mirror strength / colour and IOR from nodes, bump
+    mat("coated_glossy", color=(0.2, 0.5, 0.9, 1.0), diffuse_color=(0.1, 0.2, 0.5, 1.0), diffuse_reflect=0.5, glossy_reflect=0.6, exponent=60.0, IOR=1.6, as_diffuse=False,
+        mirror_color=(1.0, 1.0, 1.0, 1.0), specular_reflect=0.8, glossy_shader="c_c", diffuse_shader="c_d", mirror_shader="c_ms", mirror_color_shader="c_mc",
+        IOR_shader="c_i", bump_shader="c_b", exponent_shader="c_e")
+    layer("c_c", "c_m", mode=0, colfac=0.5, upper_color=(0.2, 0.5, 0.9, 1.0))
+    layer("c_d", "c_m", mode=4, colfac=0.7, upper_color=(0.3, 0.3, 0.6, 1.0))
+    layer("c_ms", "c_m", do_color=False, do_scalar=True, color_input=True, def_val=1.0, upper_value=0.3)
+    layer("c_mc", "c_m", mode=0, colfac=0.4, upper_color=(1.0, 0.9, 0.8, 1.0))
+    layer("c_i", "c_m", do_color=False, do_scalar=True, color_input=True, def_val=0.5, upper_value=0.0)
+    layer("c_b", "c_m", do_color=False, do_scalar=True, color_input=False)
+    layer("c_e", "c_m", do_color=False, do_scalar=True, color_input=False, def_val=200.0, upper_value=30.0)
+    mapper("c_m", texco="global", mapping="plain", scale=(0.9, 0.9, 0.9), bump_strength=2.0)
+    y.createMaterial("b1")
+    # glass: filter and mirror colours, IOR, bump
+    mat("glass", IOR=1.45, filter_color=(1.0, 0.9, 0.9, 1.0), transmit_filter=0.8, mirror_color=(1.0, 1.0, 1.0, 1.0), filter_color_shader="q_f", mirror_color_shader="q_m",
+        IOR_shader="q_i", bump_shader="q_b")
+    layer("q_f", "q_t", mode=0, colfac=0.5, upper_color=(0.95, 0.95, 0.95, 1.0))
+    layer("q_m", "q_t", mode=0, colfac=0.3, upper_color=(1.0, 1.0, 1.0, 1.0))
+    layer("q_i", "q_t", do_color=False, do_scalar=True, color_input=True, def_val=0.3, upper_value=0.0)
+    layer("q_b", "q_t", do_color=False, do_scalar=True, color_input=False)
+    mapper("q_t", texco="orco", mapping="cube", bump_strength=1.5)
+    y.createMaterial("b2")
+    # rough glass: + roughness
+    mat("rough_glass", IOR=1.5, alpha=0.3, filter_color=(0.9, 1.0, 0.9, 1.0), transmit_filter=1.0, filter_color_shader="r_f", mirror_color_shader="r_m", roughness_shader="r_r",
+        IOR_shader="r_i")
+    layer("r_f", "r_t", mode=0, colfac=0.4, upper_color=(0.9, 1.0, 0.9, 1.0))
+    layer("r_m", "r_t", mode=0, colfac=0.2, upper_color=(1.0, 1.0, 1.0, 1.0))
+    layer("r_r", "r_t", do_color=False, do_scalar=True, color_input=True, def_val=0.4, upper_value=0.05)
+    layer("r_i", "r_t", do_color=False, do_scalar=True, color_input=True, def_val=0.2, upper_value=0.0)
+    mapper("r_t", texco="orco", mapping="sphere")
+    y.createMaterial("b3")
+    # blend_mat with a textured mask between two plain materials
+    mat("glossy", color=(0.9, 0.8, 0.3, 1.0), diffuse_color=(0.4, 0.3, 0.1, 1.0), diffuse_reflect=0.4, glossy_reflect=0.8, exponent=200.0, as_diffuse=False)
+    y.createMaterial("bl_a")
+    mat("shinydiffusemat", color=(0.2, 0.3, 0.8, 1.0), specular_reflect=0.3, diffuse_reflect=0.9)
+    y.createMaterial("bl_b")
+    mat("blend_mat", material1="bl_a", material2="bl_b", blend_value=0.5, mask="k_l")
+    layer("k_l", "k_m", do_color=False, do_scalar=True, color_input=True, def_val=1.0, upper_value=0.0)
+    mapper("k_m", texco="orco", mapping="cube", scale=(1.2, 1.2, 1.2))
+    y.createMaterial("b4")
+    # glossy, anisotropic, as_diffuse, uv bump
+    mat("glossy", color=(0.8, 0.8, 0.8, 1.0), diffuse_color=(0.3, 0.3, 0.3, 1.0), diffuse_reflect=0.3, anisotropic=True, exp_u=20.0, exp_v=800.0, as_diffuse=True,
+        bump_shader="a_b", diffuse_shader="a_d")
+    layer("a_b", "a_m", do_color=False, do_scalar=True, color_input=False)
+    layer("a_d", "a_m", mode=0, colfac=0.9)
+    mapper("a_m", texco="uv", mapping="plain", bump_strength=1.0)
+    y.createMaterial("b5")
+
+
+def _textured_shinydiffuse_materials(y, sd, node, mapper, layer, modes, variant):
     # ground: uv-mapped, repeated 3x2, plain projection
     sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
     layer("gl", "gm", mode=modes[0], colfac=0.9)
@@ -339,6 +419,9 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
     mapper("m5b", texture="tex2", texco="uv", mapping="plain", bump_strength=0.5, scale=(2.0, 2.0, 1.0))
     y.createMaterial("b5")
 
+
+
+def _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, integ):
     def box(oid, lo, hi, mat, orco=False, uv=False, rot=0.0):
         import math
         cx, cy = 0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1])
@@ -368,7 +451,7 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
     u0, u1, u2, u3 = y.addUv(0.0, 0.0), y.addUv(1.0, 0.0), y.addUv(1.0, 1.0), y.addUv(0.0, 1.0)
     y.addTriangle(a, b, c, u0, u1, u2, "ground"); y.addTriangle(a, c, d, u0, u2, u3, "ground")
     y.endTriMesh()
-    for i, (m, orco, uv) in enumerate((("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))):
+    for i, (m, orco, uv) in enumerate(box_mats):
         x0, y0 = -3.3 + 2.3 * (i % 3), -0.6 + 2.5 * (i // 3)
         box(2 + i, (x0, y0, 0.003), (x0 + 1.5, y0 + 1.5, 1.1 + 0.2 * i), m, orco, uv, rot=13.0 * i)
     y.endGeometry()
@@ -399,3 +482,5 @@ EXACT["tex_dl_adjust"] = lambda: textured_scene(96, 54, 2, tex={"adj_contrast": 
 EXACT["tex_dl_checker"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "checker", "even_tiles": True, "odd_tiles": False, "checker_dist": 0.2, "xrepeat": 2})
 EXACT["tex_dl_clip"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "clip", "cropmin_y": 0.2})
 EXACT["tex_pt_norr"] = lambda: textured_scene(96, 54, 4, integrator="pathtracing")
+EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
+EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)
