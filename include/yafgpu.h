@@ -245,9 +245,10 @@ typedef struct yafgpu_mat_glass /* glass and rough_glass */
 	float dispersion_power;  /* "dispersion_power" */
 	int32_t fake_shadows;    /* "fake_shadows" */
 	float alpha;             /* rough_glass only: "alpha" */
-	int32_t has_absorption;  /* "absorption" given and < 1 in some channel */
+	int32_t has_absorption;  /* the factory created the Beer volume handler (Material::vol_i_): "absorption" given and < 1 in some channel AND the
+	                          * material's ParamMap carries a "name" parameter (material_glass.cc:376-399); without it "absorption" has no effect */
 	float absorption[3];     /* "absorption" */
-	float absorption_dist;   /* "absorption_dist" */
+	float absorption_dist;   /* "absorption_dist" (1 when absent) */
 } yafgpu_mat_glass;
 
 typedef struct yafgpu_mat_blend

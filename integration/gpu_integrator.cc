@@ -312,7 +312,7 @@ bool materialRecord(const Material *m, yafgpu_material &out, NodePool &pool, std
 		s.fake_shadows = par<bool>(p, "fake_shadows", false); s.alpha = par<float>(p, "alpha", 0.5f);
 		Rgb absorb(1.f);
 		const bool has = p.getParam("absorption", absorb);
-		s.has_absorption = has && (absorb.r_ < 1.f || absorb.g_ < 1.f || absorb.b_ < 1.f);
+		s.has_absorption = has && (absorb.r_ < 1.f || absorb.g_ < 1.f || absorb.b_ < 1.f) && m->vol_i_ != nullptr; // the factory made a Beer handler (needs "name")
 		s.absorption[0] = absorb.r_; s.absorption[1] = absorb.g_; s.absorption[2] = absorb.b_;
 		s.absorption_dist = par<float>(p, "absorption_dist", 1.f);
 	}

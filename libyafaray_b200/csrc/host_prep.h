@@ -77,6 +77,20 @@ inline bool prepShinyDiffuse(const yafgpu_material &m, MatDev &d, std::string &e
 	return true;
 }
 
+// BeerVolumeHandler ctor volumehandler_beer.cc:27-34 (the handler the glass factories create for "absorption" when the material's ParamMap
+// also carries a "name": material_glass.cc:376-399, material_rough_glass.cc:382-409); log() on floats is the C double function
+inline void prepBeer(const yafgpu_mat_glass &p, MatDev &d)
+{
+	d.absorb = 0;
+	if(!p.has_absorption) return;
+	const float maxlog = (float)log(1e38);
+	for(int k = 0; k < 3; ++k) d.beer_sigma_a[k] = ((double)p.absorption[k] > 1e-38) ? (float)(-log((double)p.absorption[k])) : maxlog;
+	const double dist = (double)p.absorption_dist;
+	if(dist != 0.0) { const float f = (float)(1.0 / dist); for(int k = 0; k < 3; ++k) d.beer_sigma_a[k] *= f; }
+	d.absorb = 1;
+	d.bsdf_flags |= BsdfVolumetric;
+}
+
 // GlassMaterial ctor + factory: material_glass.cc:32-49,311-379
 inline bool prepGlass(const yafgpu_material &m, MatDev &d, std::string &err)
 {
@@ -92,8 +106,7 @@ inline bool prepGlass(const yafgpu_material &m, MatDev &d, std::string &err)
 	d.tm_flags = d.fake_shadow ? (BsdfFilter | BsdfTransmit) : (BsdfSpecular | BsdfTransmit);
 	d.disperse = 0;
 	if(p.dispersion_power > 0.f) { err = "glass: dispersion_power > 0 (spectral dispersion) is not implemented on the device"; return false; }
-	d.absorb = 0;
-	if(p.has_absorption) { err = "glass: Beer absorption volume handler is not implemented on the device"; return false; }
+	prepBeer(p, d);
 	return true;
 }
 
@@ -152,7 +165,7 @@ inline bool prepRoughGlass(const yafgpu_material &m, MatDev &d, std::string &err
 	d.bsdf_flags = BsdfAllGlossy;
 	if(d.fake_shadow) d.bsdf_flags |= BsdfFilter;
 	if(p.dispersion_power > 0.f) { err = "rough_glass: dispersion_power > 0 (spectral dispersion) is not implemented on the device"; return false; }
-	if(p.has_absorption) { err = "rough_glass: Beer absorption volume handler is not implemented on the device"; return false; }
+	prepBeer(p, d);
 	return true;
 }
 
@@ -346,6 +359,7 @@ inline bool finishBlend(std::vector<MatDev> &mats, size_t i, std::string &err)
 	d.bsdf_flags = a.bsdf_flags | b.bsdf_flags;
 	d.additional_depth = a.additional_depth > b.additional_depth ? a.additional_depth : b.additional_depth;
 	d.is_transparent = (matIsTransparent(a) || matIsTransparent(b)) ? 1 : 0;
+	if(a.absorb || b.absorb) { err = "blend_mat of a glass with Beer absorption is not implemented on the device"; return false; }
 	return true;
 }
 

@@ -289,7 +289,8 @@ class Interface:
             s.fake_shadows = int(g(p, "fake_shadows", False))
             s.alpha = g(p, "alpha", 0.5)
             ab = g(p, "absorption", (1, 1, 1, 1))
-            s.has_absorption = int("absorption" in p and min(ab[:3]) < 1.0)
+            # the Beer volume handler only exists when the material's own ParamMap has a "name" (material_glass.cc:390-398)
+            s.has_absorption = int("absorption" in p and min(ab[:3]) < 1.0 and "name" in p)
             s.absorption = capi.F3(*[np.float32(x) for x in ab[:3]])
             s.absorption_dist = g(p, "absorption_dist", 1.0)
         elif t in ("glossy", "coated_glossy"):  # material_glossy.cc:407-480, material_coated_glossy.cc:465-545

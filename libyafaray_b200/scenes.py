@@ -196,7 +196,7 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
 
 
 def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=12345, bounces=8, raydepth=8, path_samples=1,
-                    rr_min_bounces=2, integrator="pathtracing", smooth=True):
+                    rr_min_bounces=2, integrator="pathtracing", smooth=True, ibl_hdr=None, mesh_lights=0, blend=False):
     """BASELINE config 3: procedural displaced-grid terrain of ~n_tris triangles (2*n^2) with materials cycling over
     glossy / coated_glossy / rough_glass / shinydiffuse in 16x16-quad patches, a sun and an area light, path depth 8.
     Built through the bulk mesh call (numpy arrays); value-noise displacement from a seeded generator."""
@@ -222,6 +222,12 @@ def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=123
         mat("gloss_b", "glossy", color=(0.8, 0.8, 0.8), diffuse_color=(0.4, 0.5, 0.3), diffuse_reflect=0.7, glossy_reflect=0.4, exponent=50.0, as_diffuse=True),
         mat("coat_b", "coated_glossy", color=(0.9, 0.3, 0.3), diffuse_color=(0.6, 0.2, 0.2), diffuse_reflect=0.7, glossy_reflect=0.5, exponent=2000.0, IOR=1.8, as_diffuse=False),
     ]
+    if blend:
+        # BASELINE config 4: blend_mat of glossy / shinydiffuse with blend_value 0.3 / 0.5 / 0.7 in the material cycle
+        for k, bv in enumerate((0.3, 0.5, 0.7)):
+            y.paramsClearAll(); y.paramsSetString("type", "blend_mat"); y.paramsSetString("material1", "gloss_a" if k != 1 else "gloss_b")
+            y.paramsSetString("material2", "diff_a"); y.paramsSetFloat("blend_value", bv)
+            names.append(y.createMaterial("blend_%d" % k))
     # value noise: three octaves of bilinearly interpolated random lattices
     xs = np.linspace(0.0, 1.0, n + 1, dtype=np.float32)
     h = np.zeros((n + 1, n + 1), np.float32)
@@ -255,7 +261,23 @@ def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=123
     z = 6.0
     _quad(y, (-2, -2, z), (-2, 2, z), (2, 2, z), (2, -2, z), lm)
     y.endTriMesh()
+    for k in range(mesh_lights):
+        # config 4: mesh lights of ~10^3 triangles each (a 22 x 23 grid of quads = 1012 triangles), facing down
+        gx, gy = 22, 23
+        cx, cy, cz = -5.0 + 5.0 * k, 2.0 - 2.0 * k, 5.0 + 0.5 * k
+        ux = np.linspace(-0.8, 0.8, gx + 1, dtype=np.float32); uy = np.linspace(-0.8, 0.8, gy + 1, dtype=np.float32)
+        LX, LY = np.meshgrid(ux + cx, uy + cy)
+        LP = np.stack([LX, LY, np.full_like(LX, cz) + 0.1 * np.sin(3.0 * LX) * np.cos(3.0 * LY)], axis=-1).reshape(-1, 3).astype(np.float32)
+        jj, ii = np.meshgrid(np.arange(gy, dtype=np.int32), np.arange(gx, dtype=np.int32), indexing="ij")
+        aa = (jj * (gx + 1) + ii).reshape(-1)
+        LF = np.empty((2 * gx * gy, 3), np.int32)
+        LF[0::2] = np.stack([aa, aa + gx + 2, aa + 1], axis=1)      # wound so that the geometric normal points down (-z)
+        LF[1::2] = np.stack([aa, aa + gx + 1, aa + gx + 2], axis=1)
+        y.addTriMeshArrays(10 + k, LP, LF, "lightmat")
     y.endGeometry()
+    for k in range(mesh_lights):
+        y.paramsClearAll(); y.paramsSetString("type", "meshlight"); y.paramsSetInt("object", 10 + k); y.paramsSetColor("color", 1.0, 0.9 - 0.1 * k, 0.7 + 0.1 * k)
+        y.paramsSetFloat("power", 12.0); y.paramsSetInt("samples", 1); y.createLight("mesh%d" % k)
     y.paramsClearAll(); y.paramsSetString("type", "arealight"); y.paramsSetPoint("corner", -2, -2, z); y.paramsSetPoint("point1", -2, 2, z)
     y.paramsSetPoint("point2", 2, -2, z); y.paramsSetColor("color", 1.0, 1.0, 1.0); y.paramsSetFloat("power", 40.0)
     y.paramsSetInt("samples", 1); y.paramsSetInt("object", 2); y.createLight("area")
@@ -264,7 +286,13 @@ def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=123
     y.paramsClearAll(); y.paramsSetString("type", "perspective")
     y.paramsSetPoint("from", 0.0, -13.0, 7.0); y.paramsSetPoint("to", 0.0, 0.0, 0.8); y.paramsSetPoint("up", 0.0, -13.0, 8.0)
     y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.4); y.createCamera("cam")
-    y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.4, 0.5, 0.7); y.paramsSetFloat("power", 1.0)
+    if ibl_hdr:
+        # config 4: equirectangular HDR "textureback" with ibl true, ibl_samples 16
+        y.paramsClearAll(); y.paramsSetString("type", "image"); y.paramsSetString("filename", ibl_hdr); y.createTexture("envtex")
+        y.paramsClearAll(); y.paramsSetString("type", "textureback"); y.paramsSetString("texture", "envtex"); y.paramsSetString("mapping", "sphere")
+        y.paramsSetFloat("power", 1.0); y.paramsSetBool("ibl", True); y.paramsSetInt("ibl_samples", 16)
+    else:
+        y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.4, 0.5, 0.7); y.paramsSetFloat("power", 1.0)
     y.createBackground("bg")
     y.paramsClearAll(); y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", raydepth); y.paramsSetInt("shadowDepth", 2)
     if integrator == "pathtracing":

@@ -103,13 +103,13 @@ def _set_params(y, kw):
 
 
 def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, only_mat=None,
-                       hdr_env=None, extra_lights=(), camera=None, gradient=None, **integ):
+                       hdr_env=None, extra_lights=(), camera=None, gradient=None, beer=False, **integ):
     """Every material and light type of the hot path in one small scene (configs 3/4 in miniature): glossy, coated_glossy,
     rough_glass, blend_mat, mirror, glass and shinydiffuse boxes on a ground quad; sun + mesh light + constant-background IBL."""
     from libyafaray_b200.interface import Interface
     y = Interface(); y.startScene(0)
 
-    def mat(name, typ, **kw):
+    def mat(mname, typ, **kw):
         y.paramsClearAll(); y.paramsSetString("type", typ)
         for k, v in kw.items():
             if isinstance(v, bool): y.paramsSetBool(k, v)
@@ -117,15 +117,17 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
             elif isinstance(v, float): y.paramsSetFloat(k, v)
             elif isinstance(v, str): y.paramsSetString(k, v)
             else: y.paramsSetColor(k, *v)
-        return y.createMaterial(name)
+        return y.createMaterial(mname)
     ground = mat("ground", "shinydiffusemat", color=(0.7, 0.7, 0.65))
     mats = [
         mat("gloss", "glossy", color=(0.9, 0.6, 0.2), diffuse_color=(0.5, 0.3, 0.1), diffuse_reflect=0.4, glossy_reflect=0.8, exponent=200.0, as_diffuse=False),
         mat("coated", "coated_glossy", color=(0.2, 0.5, 0.9), diffuse_color=(0.1, 0.2, 0.5), diffuse_reflect=0.5, glossy_reflect=0.7, exponent=80.0, IOR=1.8, as_diffuse=False),
-        mat("rough", "rough_glass", IOR=1.5, alpha=0.3, filter_color=(0.9, 1.0, 0.9), transmit_filter=1.0),
+        mat("rough", "rough_glass", IOR=1.5, alpha=0.3, filter_color=(0.9, 1.0, 0.9), transmit_filter=1.0,
+            **({"name": "rough", "absorption": (0.9, 0.5, 0.6, 1.0), "absorption_dist": 0.8} if beer else {})),
         mat("aniso", "glossy", color=(0.8, 0.8, 0.8), diffuse_color=(0.3, 0.3, 0.3), diffuse_reflect=0.3, anisotropic=True, exp_u=20.0, exp_v=800.0, as_diffuse=True),
         mat("mirr", "shinydiffusemat", color=(0.6, 0.2, 0.2), specular_reflect=0.5, mirror_color=(1.0, 1.0, 1.0), fresnel_effect=True, IOR=1.6, diffuse_reflect=0.9),
-        mat("glas", "glass", IOR=1.45, filter_color=(1.0, 0.9, 0.9), transmit_filter=0.8, fake_shadows=transp_shad),
+        mat("glas", "glass", IOR=1.45, filter_color=(1.0, 0.9, 0.9), transmit_filter=0.8, fake_shadows=transp_shad,
+            **({"name": "glas", "absorption": (0.4, 0.7, 0.9, 1.0), "absorption_dist": 0.5} if beer else {})),
         mat("sd_on", "shinydiffusemat", color=(0.3, 0.7, 0.3), diffuse_brdf="oren_nayar", sigma=0.4, transparency=0.3, translucency=0.2),
     ]
     y.paramsClearAll(); y.paramsSetString("type", "blend_mat"); y.paramsSetString("material1", "gloss"); y.paramsSetString("material2", "mirr")
@@ -474,6 +476,9 @@ def _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, int
     return y
 
 
+# Beer absorption inside glass / rough glass (the volume handler the factories create when the material has a "name" parameter)
+EXACT["zoo_dl_beer"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=5, beer=True)
+EXACT["zoo_pt_beer_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, rr_min_bounces=99, beer=True, raydepth=5)
 EXACT["tex_dl_basic"] = lambda: textured_scene(96, 54, 2)
 EXACT["tex_dl_modes_b"] = lambda: textured_scene(96, 54, 2, variant="modes_b", tex={"interpolate": "none", "clipping": "extend"})
 EXACT["tex_dl_modes_c"] = lambda: textured_scene(96, 54, 2, variant="modes_c", tex={"interpolate": "bicubic", "mirror_x": True, "mirror_y": True, "xrepeat": 2, "yrepeat": 3})
