@@ -241,6 +241,9 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		std::string err;
 		if(!prepCamera(desc->camera, s.cam, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, err);
 	}
+	for(const NodeDev &nd : h_nodes)
+		if(nd.type == YAFGPU_NODE_TEXTURE_MAPPER && nd.coords == YAFGPU_TEXCO_WINDOW && desc->camera.type != YAFGPU_CAM_PERSPECTIVE)
+			return setErr(c, YAFGPU_ERR_UNSUPPORTED, "texture_mapper texco window is implemented for the perspective camera only");
 	const yafgpu_integrator_desc &in = desc->integrator;
 	if(in.type != YAFGPU_INT_DIRECTLIGHT && in.type != YAFGPU_INT_PATHTRACING) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "integrator type");
 	if(in.bg_transp || in.bg_transp_refract) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bg_transp / bg_transp_refract (alpha output) not implemented on the device");

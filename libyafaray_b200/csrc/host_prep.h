@@ -271,7 +271,6 @@ inline bool prepNodes(const yafgpu_material &m, const yafgpu_scene_desc &sd, con
 			if(q.texture < 0 || (size_t)q.texture >= tex.size()) { err = "texture_mapper: texture index out of range"; return false; }
 			const TexDev &t = tex[q.texture];
 			o.tex = q.texture; o.coords = q.texco; o.proj = q.mapping; // image textures are discrete(): the "mapping" is honoured
-			if(q.texco == YAFGPU_TEXCO_WINDOW || q.texco == YAFGPU_TEXCO_NORMAL) { err = "texture_mapper: texco window / normal (camera dependent) is not implemented on the device"; return false; }
 			if(q.texco < 0 || q.texco > YAFGPU_TEXCO_TANGENT || q.mapping < 0 || q.mapping > YAFGPU_TEXPROJ_SPHERE) { err = "texture_mapper: texco / mapping"; return false; }
 			o.map_x = std::min(3, std::max(0, q.proj_x)); o.map_y = std::min(3, std::max(0, q.proj_y)); o.map_z = std::min(3, std::max(0, q.proj_z));
 			for(int k = 0; k < 3; ++k) { o.scale[k] = q.scale[k]; o.offset[k] = 2 * q.offset[k]; }
@@ -551,6 +550,7 @@ inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
 	st3(d.near_p, pos + cam_z * c.near_clip);
 	st3(d.far_p, pos + cam_z * c.far_clip);
 	st3(d.pos, pos); st3(d.cam_to, cam_z);
+	st3(d.axis_x, cam_x); st3(d.axis_y, cam_y); st3(d.axis_z, cam_z); d.focal = c.focal; // Camera::getAxis / screenproject (texture_mapper texco normal / window)
 	if(c.type == YAFGPU_CAM_ORTHOGRAPHIC)
 	{	// OrthographicCamera::setAxis camera_orthographic.cc:37-50
 		V3 vright = cam_x, vup = aspect_ratio * cam_y;

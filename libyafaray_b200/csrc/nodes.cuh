@@ -353,8 +353,8 @@ YG_D V3 mapperDoMapping(const NodeDev &nd, V3 p, V3 n)
 	}
 	return mk(t.x * nd.scale[0], t.y * nd.scale[1], t.z * nd.scale[2]) + mk(nd.offset[0], nd.offset[1], nd.offset[2]);
 }
-// getCoords :159-186 (window / normal coordinates are refused at upload; the "not implemented yet" modes map to global as there)
-YG_D void mapperGetCoords(const NodeDev &nd, const SurfPt &sp, const SurfTex &sx, V3 &texpt, V3 &ng)
+// getCoords :159-186 (the "not implemented yet" modes map to global as there)
+YG_D void mapperGetCoords(const CameraDev &cam, const NodeDev &nd, const SurfPt &sp, const SurfTex &sx, V3 &texpt, V3 &ng)
 {
 	switch(nd.coords)
 	{
@@ -367,6 +367,17 @@ YG_D void mapperGetCoords(const NodeDev &nd, const SurfPt &sp, const SurfTex &sx
 			ng = mk((m[0] * sp.ng.x + m[1] * sp.ng.y) + m[2] * sp.ng.z, (m[4] * sp.ng.x + m[5] * sp.ng.y) + m[6] * sp.ng.z, (m[8] * sp.ng.x + m[9] * sp.ng.y) + m[10] * sp.ng.z);
 			break;
 		}
+		case YAFGPU_TEXCO_WINDOW:
+		{	// PerspectiveCamera::screenproject camera_perspective.cc:158-173 (other camera types are refused at upload)
+			const V3 dir = sp.p - ldv(cam.pos);
+			const float dx = dot(dir, ldv(cam.axis_x)), dy = dot(dir, ldv(cam.axis_y)), dz = dot(dir, ldv(cam.axis_z));
+			texpt = mk(2.0f * dx * cam.focal / dz, -2.0f * dy * cam.focal / (dz * cam.aspect_ratio), 0.f);
+			ng = sp.ng;
+			break;
+		}
+		case YAFGPU_TEXCO_NORMAL: // Camera::getAxis; sp.n is the (possibly bumped) shading normal at this point of initBsdf
+			texpt = mk(dot(sp.n, ldv(cam.axis_x)), -dot(sp.n, ldv(cam.axis_y)), 0.f); ng = sp.ng;
+			break;
 		default: texpt = sp.p; ng = sp.ng; break;
 	}
 }
@@ -374,7 +385,7 @@ YG_D void mapperGetCoords(const NodeDev &nd, const SurfPt &sp, const SurfTex &sx
 YG_D NodeRes mapperEval(const SceneDev &sc, const NodeDev &nd, const SurfPt &sp, const SurfTex &sx)
 {
 	V3 texpt, ng;
-	mapperGetCoords(nd, sp, sx, texpt, ng);
+	mapperGetCoords(sc.cam, nd, sp, sx, texpt, ng);
 	texpt = mapperDoMapping(nd, texpt, ng);
 	const TexDev &t = sc.textures[nd.tex];
 	NodeRes r;
@@ -387,7 +398,7 @@ YG_D NodeRes mapperEvalDerivative(const SceneDev &sc, const NodeDev &nd, const S
 {
 	V3 texpt, ng;
 	float du = 0.0f, dv = 0.0f;
-	mapperGetCoords(nd, sp, sx, texpt, ng);
+	mapperGetCoords(sc.cam, nd, sp, sx, texpt, ng);
 	const TexDev &t = sc.textures[nd.tex];
 	if(sx.has_uv && nd.coords == YAFGPU_TEXCO_UV)
 	{

@@ -412,6 +412,18 @@ def _textured_shinydiffuse_materials(y, sd, node, mapper, layer, modes, variant)
     layer("l4c", "m4", mode=2, colfac=0.5)
     mapper("m4", texco="orco", mapping="cube", bump_strength=3.0, scale=(2.0, 2.0, 2.0))
     y.createMaterial("b4")
+    if variant == "camera_coords":
+        # camera-dependent texture coordinates on two of the boxes: "window" (Camera::screenproject) and "normal" (Camera::getAxis)
+        sd("b3", color=(0.8, 0.8, 0.8, 1.0), diffuse_shader="w_l")
+        layer("w_l", "w_m", mode=0, colfac=0.9)
+        mapper("w_m", texco="window", mapping="plain", scale=(1.5, 1.5, 1.0))
+        y.createMaterial("b3")
+        sd("b4", color=(0.7, 0.7, 0.9, 1.0), diffuse_shader="n_l", bump_shader="n_b")
+        layer("n_l", "n_m", mode=0, colfac=0.9)
+        layer("n_b", "n_m2", do_color=False, do_scalar=True, color_input=False)
+        mapper("n_m", texco="normal", mapping="plain")
+        mapper("n_m2", texco="orco", mapping="cube", bump_strength=2.0)
+        y.createMaterial("b4")
     # box 5 (has uv): bump through uv coordinates (the uv derivative path), two stacked bump layers
     sd("b5", color=(0.9, 0.8, 0.6, 1.0), bump_shader="l5b2", diffuse_shader="l5c")
     layer("l5b1", "m5", do_color=False, do_scalar=True, color_input=False)
@@ -487,5 +499,6 @@ EXACT["tex_dl_adjust"] = lambda: textured_scene(96, 54, 2, tex={"adj_contrast": 
 EXACT["tex_dl_checker"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "checker", "even_tiles": True, "odd_tiles": False, "checker_dist": 0.2, "xrepeat": 2})
 EXACT["tex_dl_clip"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "clip", "cropmin_y": 0.2})
 EXACT["tex_pt_norr"] = lambda: textured_scene(96, 54, 4, integrator="pathtracing")
+EXACT["tex_dl_camera_coords"] = lambda: textured_scene(96, 54, 2, variant="camera_coords")
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)

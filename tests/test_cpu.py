@@ -30,12 +30,12 @@ def test_library_exports_every_declared_symbol():
 def test_struct_sizes_match_header():
     """ctypes mirrors vs the C compiler's view of include/yafgpu.h."""
     from libyafaray_b200 import capi
-    src = '#include "yafgpu.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(yafgpu_material), sizeof(yafgpu_light), sizeof(yafgpu_scene_desc), sizeof(yafgpu_pass_desc), sizeof(yafgpu_stats), sizeof(yafgpu_camera), sizeof(yafgpu_object));return 0;}\n'
+    src = '#include "yafgpu.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(yafgpu_material), sizeof(yafgpu_light), sizeof(yafgpu_scene_desc), sizeof(yafgpu_pass_desc), sizeof(yafgpu_stats), sizeof(yafgpu_camera), sizeof(yafgpu_object), sizeof(yafgpu_texture), sizeof(yafgpu_shader_node));return 0;}\n'
     with tempfile.TemporaryDirectory() as td:
         open(os.path.join(td, "a.c"), "w").write(src)
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), os.path.join(td, "a.c"), "-o", os.path.join(td, "a")])
         out = subprocess.check_output([os.path.join(td, "a")]).decode().split()
-    want = [ctypes.sizeof(t) for t in (capi.Material, capi.Light, capi.SceneDesc, capi.PassDesc, capi.Stats, capi.Camera, capi.Object)]
+    want = [ctypes.sizeof(t) for t in (capi.Material, capi.Light, capi.SceneDesc, capi.PassDesc, capi.Stats, capi.Camera, capi.Object, capi.Texture, capi.ShaderNode)]
     assert [int(x) for x in out] == want
 
 
