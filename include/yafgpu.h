@@ -105,7 +105,10 @@ typedef enum yafgpu_material_type
 	YAFGPU_MAT_BLEND = 5,         /* "blend_mat"        material_blend.cc:464-518 */
 	YAFGPU_MAT_MIRROR = 6,        /* "mirror"           material_glass.cc (MirrorMaterial) */
 	YAFGPU_MAT_NULL = 7,          /* "null"             material_glass.cc (NullMaterial) */
-	YAFGPU_MAT_LIGHT = 8          /* "light_mat"        material_simple.cc:38-73 */
+	YAFGPU_MAT_LIGHT = 8,         /* "light_mat"        material_simple.cc:38-73 */
+	/* 9 and 10 are kernel classes internal to the library */
+	YAFGPU_MAT_MASK = 11          /* "mask_mat"         material_mask.cc:30-198: u.blend.material1 / material2, blend_value = "threshold"; the "mask"
+	                               * shader (YAFGPU_SLOT_BLEND) picks material2 where its scalar > threshold, else material1 */
 } yafgpu_material_type;
 
 /* ---- textures and shader nodes ------------------------------------- */
@@ -200,7 +203,7 @@ enum { YAFGPU_SLOT_DIFFUSE = 0,       /* "diffuse_shader" */
        YAFGPU_SLOT_EXPONENT = 12,     /* "exponent_shader" */
        YAFGPU_SLOT_FILTER_COLOR = 13, /* "filter_color_shader" */
        YAFGPU_SLOT_ROUGHNESS = 14,    /* "roughness_shader" */
-       YAFGPU_SLOT_BLEND = 15,        /* blend_mat "mask" */
+       YAFGPU_SLOT_BLEND = 15,        /* blend_mat / mask_mat "mask" */
        YAFGPU_N_SLOTS = 16 };
 
 typedef struct yafgpu_mat_shinydiffuse
@@ -255,7 +258,7 @@ typedef struct yafgpu_mat_blend
 {
 	int32_t material1;       /* index of "material1" */
 	int32_t material2;       /* index of "material2" */
-	float blend_value;       /* "blend_value" */
+	float blend_value;       /* blend_mat "blend_value"; mask_mat "threshold" */
 } yafgpu_mat_blend;
 
 typedef struct yafgpu_mat_simple /* mirror: color*reflect; light_mat: color*power, double_sided */
@@ -306,7 +309,10 @@ typedef enum yafgpu_light_type
 	YAFGPU_LIGHT_BACKGROUND = 4, /* "bglight"     light_background.cc:251-283 (created by a background with ibl=true) */
 	YAFGPU_LIGHT_DIRECTIONAL = 5,/* "directional" light_directional.cc:112-158 */
 	YAFGPU_LIGHT_SPOT = 6,       /* "spotlight"   light_spot.cc:251-295 */
-	YAFGPU_LIGHT_SPHERE = 7      /* "spherelight" light_sphere.cc:163-198 (without a linked sphere primitive: "object" must be 0) */
+	YAFGPU_LIGHT_SPHERE = 7,     /* "spherelight" light_sphere.cc:163-198 (without a linked sphere primitive: "object" must be 0) */
+	YAFGPU_LIGHT_BGPORTAL = 8    /* "bgPortalLight" light_background_portal.cc:236-266: the mesh "object" is a window that radiates the background
+	                              * (colour = Background::eval(direction) * power); the mesh must be present in the geometry — the reference's
+	                              * kd-tree is built before the light's init() hides it (scene.cc:788-831 precede the light loop) */
 } yafgpu_light_type;
 
 typedef struct yafgpu_light

@@ -262,7 +262,7 @@ bool nodeRecords(const Material *m, const ParamMap &p, const std::string &name, 
 	const std::string mtype = par<std::string>(p, "type", "");
 	for(int s = 0; s < YAFGPU_N_SLOTS; ++s)
 	{
-		if(s == YAFGPU_SLOT_BLEND && mtype != "blend_mat") continue;
+		if(s == YAFGPU_SLOT_BLEND && mtype != "blend_mat" && mtype != "mask_mat") continue;
 		out.shader[s] = ref(p, slot_keys[s]);
 	}
 	return true;
@@ -328,6 +328,16 @@ bool materialRecord(const Material *m, yafgpu_material &out, NodePool &pool, std
 		s.as_diffuse = par<bool>(p, "as_diffuse", true); s.anisotropic = par<bool>(p, "anisotropic", false);
 		s.oren_nayar = par<std::string>(p, "diffuse_brdf", "") == "Oren-Nayar"; s.sigma = par<float>(p, "sigma", 0.1f);
 	}
+	else if(type == "mask_mat")
+	{	// material_mask.cc:150-198
+		out.type = YAFGPU_MAT_MASK;
+		// the mask factory reads nothing but threshold, the two children, receive_shadows and visibility: the rest stays at Material's defaults
+		out.flat_material = 0; out.additional_depth = 0; out.transparent_bias_factor = 0.f; out.transparent_bias_multiply_raydepth = 0;
+		out.sampling_factor = 1.f; out.mat_pass_index = 0;
+		out.u.blend.material1 = indexOf(par<std::string>(p, "material1", ""));
+		out.u.blend.material2 = indexOf(par<std::string>(p, "material2", ""));
+		out.u.blend.blend_value = (float)par<double>(p, "threshold", 0.5);
+	}
 	else if(type == "blend_mat")
 	{	// material_blend.cc:464-518
 		out.type = YAFGPU_MAT_BLEND;
@@ -373,6 +383,11 @@ bool lightRecord(const Light *l, const std::map<int, int> &obj_index_of_id, yafg
 	{	// light_area.cc:174-213
 		out.type = YAFGPU_LIGHT_AREA;
 		par3(p, "corner", out.from, 0.f, 0.f, 0.f); par3(p, "point1", out.point1, 0.f, 0.f, 0.f); par3(p, "point2", out.point2, 0.f, 0.f, 0.f);
+		out.object = objectOf();
+	}
+	else if(type == "bgPortalLight")
+	{	// light_background_portal.cc:236-266
+		out.type = YAFGPU_LIGHT_BGPORTAL;
 		out.object = objectOf();
 	}
 	else if(type == "meshlight")
@@ -510,12 +525,20 @@ bool GpuIntegrator::preprocess()
 	std::vector<yafgpu_object> objs;
 	std::map<int, int> obj_index_of_id;
 	bool any_n = false, any_uv = false;
+	// BackgroundPortalLight::init hides its mesh (light_background_portal.cc:90), but only after Scene::update has put it into the kd-tree this
+	// render uses (scene.cc:788-831 run before the light loop): the portal meshes are part of the geometry
+	std::set<int> portal_objects;
+	for(const Light *l : scene_->lights_)
+	{
+		auto it = rec().params.find(l);
+		if(it != rec().params.end() && par<std::string>(it->second, "type", "") == "bgPortalLight") portal_objects.insert(par<int>(it->second, "object", 0));
+	}
 	for(auto &kv : scene_->meshes_)
 	{
 		ObjData &dat = kv.second;
 		if(dat.type_ != 0 /* TRIM */) return fail("only triangle meshes (type 0) are implemented on the device");
 		const TriangleObject *o = dat.obj_;
-		if(!o->isVisible() || o->isBaseObject()) continue;
+		if((!o->isVisible() && !portal_objects.count((int)kv.first)) || o->isBaseObject()) continue;
 		const int p_off = (int)(pts.size() / 3), n_off = (int)(nrm.size() / 3), uv_off = (int)(uvs.size() / 2);
 		yafgpu_object rec_o;
 		memset(&rec_o, 0, sizeof(rec_o));

@@ -16,7 +16,8 @@ OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE, ERR_NOMEM = range(6)
 VIS_NORMAL, VIS_NO_SHADOWS, VIS_SHADOW_ONLY, VIS_INVISIBLE = range(4)
 (MAT_SHINYDIFFUSE, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_ROUGH_GLASS, MAT_BLEND, MAT_MIRROR, MAT_NULL,
  MAT_LIGHT) = range(9)
-LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE = range(8)
+MAT_MASK = 11
+LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE, LIGHT_BGPORTAL = range(9)
 CAM_PERSPECTIVE, CAM_ARCHITECT, CAM_ORTHOGRAPHIC, CAM_ANGULAR, CAM_EQUIRECTANGULAR = range(5)
 ANGULAR_PROJECTIONS = {"equidistant": 0, "orthographic": 1, "stereographic": 2, "equisolid_angle": 3, "rectilinear": 4}
 BK = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}

@@ -211,8 +211,9 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	for(size_t i = 0; i < desc->n_materials; ++i)
 	{
 		std::string err;
-		if(c->h_mats[i].type == YAFGPU_MAT_BLEND && !finishBlend(c->h_mats, i, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
+		if((c->h_mats[i].type == YAFGPU_MAT_BLEND || c->h_mats[i].type == YAFGPU_MAT_MASK) && !finishBlend(c->h_mats, i, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
 	}
+	for(size_t i = 0; i < desc->n_materials; ++i) { c->h_mats[i].obj_flags = c->h_mats[i].bsdf_flags; c->h_mats[i].is_mask = 0; }
 	for(size_t i = 0; i < desc->n_materials; ++i) triflags[i] = triFlagsOf(c->h_mats[i]);
 	for(size_t i = 0; i < desc->n_materials; ++i)
 	{	// Scene::isShadowed calls Material::getTransparency without initBsdf (kdtree_triangle.cc:1106-1124): with shader nodes it would read
@@ -232,7 +233,8 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		LightDev ld;
 		if(!prepLight(desc->lights[i], ld, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "light " + std::to_string(i) + ": " + err);
 		if(ld.object >= (int)g.n_objects) return setErr(c, YAFGPU_ERR_INVALID, "light object index out of range");
-		if(ld.type == YAFGPU_LIGHT_MESH && ld.object < 0) return setErr(c, YAFGPU_ERR_INVALID, "meshlight without a valid object");
+		if((ld.type == YAFGPU_LIGHT_MESH || ld.type == YAFGPU_LIGHT_BGPORTAL) && ld.object < 0) return setErr(c, YAFGPU_ERR_INVALID, "meshlight / bgPortalLight without a valid object");
+		if(ld.type == YAFGPU_LIGHT_BGPORTAL && desc->background.type == YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_INVALID, "bgPortalLight without a background");
 		c->h_lights.push_back(ld); light_src.push_back(i);
 	}
 	SceneDev &s = c->scene;
@@ -290,7 +292,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	for(size_t i = 0; i < c->h_lights.size(); ++i)
 	{
 		LightDev &ld = c->h_lights[i];
-		if(ld.type == YAFGPU_LIGHT_MESH) buildMeshLightTables(g, g.objects[ld.object], ld, light_tab);
+		if(ld.type == YAFGPU_LIGHT_MESH || ld.type == YAFGPU_LIGHT_BGPORTAL) buildMeshLightTables(g, g.objects[ld.object], ld, light_tab);
 		else if(ld.type == YAFGPU_LIGHT_BACKGROUND)
 		{
 			if(bg.type == YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_INVALID, "bglight without a background");
@@ -302,7 +304,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	std::vector<ObjDev> objs(g.n_objects ? g.n_objects : 1);
 	for(size_t i = 0; i < g.n_objects; ++i) { objs[i].has_orco = g.objects[i].has_orco; objs[i].has_uv = g.objects[i].has_uv; objs[i].smooth = g.objects[i].smooth; objs[i].light = g.objects[i].light; }
 	for(size_t i = 0; i < c->h_lights.size(); ++i)
-		if((c->h_lights[i].type == YAFGPU_LIGHT_AREA || c->h_lights[i].type == YAFGPU_LIGHT_MESH) && c->h_lights[i].object >= 0) objs[c->h_lights[i].object].light = (int)i;
+		if((c->h_lights[i].type == YAFGPU_LIGHT_AREA || c->h_lights[i].type == YAFGPU_LIGHT_MESH || c->h_lights[i].type == YAFGPU_LIGHT_BGPORTAL) && c->h_lights[i].object >= 0) objs[c->h_lights[i].object].light = (int)i;
 
 	cudaStream_t st = c->stream;
 	c->n_tris = g.n_tris; c->n_points = g.n_points; c->n_normals = g.n_normals; c->n_uv = g.n_uv; c->n_objects = g.n_objects;
@@ -377,7 +379,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	for(size_t i = 0; i < c->h_lights.size(); ++i)
 	{
 		LightDev &ld = c->h_lights[i];
-		if(ld.type != YAFGPU_LIGHT_MESH || ld.tri_count <= 0) continue;
+		if((ld.type != YAFGPU_LIGHT_MESH && ld.type != YAFGPU_LIGHT_BGPORTAL) || ld.tri_count <= 0) continue;
 		BvhBuildInput bi; bi.n_tris = ld.tri_count; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx + 3 * (size_t)ld.tri_first;
 		bi.tri_mat = c->d_tri_mat + ld.tri_first; bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng + 3 * (size_t)ld.tri_first;
 		BvhBuildOutput bo;

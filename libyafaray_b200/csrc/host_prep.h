@@ -177,7 +177,7 @@ inline unsigned triFlagsOf(const MatDev &d)
 	bool transp = false;
 	if(d.type == YAFGPU_MAT_SHINYDIFFUSE || d.type == YG_MAT_SD_LAMBERT) transp = d.is_transparent; // material_shiny_diffuse.h:53
 	if(d.type == YAFGPU_MAT_GLASS || d.type == YAFGPU_MAT_ROUGH_GLASS) transp = d.fake_shadow; // material_glass.h:40
-	if(d.type == YAFGPU_MAT_BLEND) transp = d.is_transparent; // set by finishBlend (material_blend.cc:332-335)
+	if(d.type == YAFGPU_MAT_BLEND || d.type == YAFGPU_MAT_MASK) transp = d.is_transparent; // set by finishBlend (material_blend.cc:332-335, material_mask.cc:88-91)
 	if(transp) f |= TRI_TRANSPARENT;
 	return f;
 }
@@ -310,8 +310,9 @@ inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
 			/* rough glass */  1u << YAFGPU_SLOT_MIRROR_COLOR | 1u << YAFGPU_SLOT_BUMP | 1u << YAFGPU_SLOT_FILTER_COLOR | 1u << YAFGPU_SLOT_IOR | 1u << YAFGPU_SLOT_WIREFRAME | 1u << YAFGPU_SLOT_ROUGHNESS,
 			/* blend */        1u << YAFGPU_SLOT_BLEND,
 			0u, 0u, 0u };
-		if(m.type < 0 || m.type > 8 || allowed[m.type] == 0u) { err = "shader nodes on this material type are not implemented on the device"; return false; }
-		for(int s = 0; s < YAFGPU_N_SLOTS; ++s) if(d.slot[s] >= 0 && !(allowed[m.type] >> s & 1u)) { err = "shader slot " + std::to_string(s) + " does not exist on material type " + std::to_string(m.type); return false; }
+		const unsigned allow = m.type == YAFGPU_MAT_MASK ? 1u << YAFGPU_SLOT_BLEND : (m.type < 0 || m.type > 8) ? 0u : allowed[m.type];
+		if(allow == 0u) { err = "shader nodes on this material type are not implemented on the device"; return false; }
+		for(int s = 0; s < YAFGPU_N_SLOTS; ++s) if(d.slot[s] >= 0 && !(allow >> s & 1u)) { err = "shader slot " + std::to_string(s) + " does not exist on material type " + std::to_string(m.type); return false; }
 		if(d.slot[YAFGPU_SLOT_WIREFRAME] >= 0) { err = "wireframe_shader is not implemented on the device"; return false; }
 	}
 	d.type = m.type; d.visibility = m.visibility; d.receive_shadows = m.receive_shadows; d.flat = m.flat_material;
@@ -332,6 +333,10 @@ inline bool prepMaterial(const yafgpu_material &m, MatDev &d, std::string &err)
 		case YAFGPU_MAT_MIRROR: // MirrorMaterial material_glass.h:79-84
 			for(int k = 0; k < 3; ++k) d.simple_col[k] = m.u.simple.color[k] * m.u.simple.strength;
 			d.bsdf_flags = BsdfSpecular;
+			return true;
+		case YAFGPU_MAT_MASK: // MaskMaterial ctor + factory material_mask.cc:30-37,150-198; flags resolved by finishBlend() once all materials exist
+			d.mat1 = m.u.blend.material1; d.mat2 = m.u.blend.material2; d.blend_val = (float)(double)m.u.blend.blend_value;
+			if(d.slot[YAFGPU_SLOT_BLEND] < 0) { err = "mask_mat without a \"mask\" shader node"; return false; }
 			return true;
 		case YAFGPU_MAT_BLEND: // BlendMaterial ctor material_blend.cc:37-49; flags/additional depth resolved by finishBlend() once all materials exist
 			d.mat1 = m.u.blend.material1; d.mat2 = m.u.blend.material2; d.blend_val = m.u.blend.blend_value;
@@ -354,6 +359,14 @@ inline bool finishBlend(std::vector<MatDev> &mats, size_t i, std::string &err)
 	MatDev &d = mats[i];
 	if(d.mat1 < 0 || d.mat2 < 0 || (size_t)d.mat1 >= mats.size() || (size_t)d.mat2 >= mats.size()) { err = "blend_mat: child index out of range"; return false; }
 	const MatDev &a = mats[d.mat1], &b = mats[d.mat2];
+	if(d.type == YAFGPU_MAT_MASK)
+	{	// the chosen child's record replaces the mask's per hit (nodes.cuh), so children are plain materials (a blend_mat of plain materials included)
+		if(a.type == YAFGPU_MAT_MASK || b.type == YAFGPU_MAT_MASK || a.node_count > 0 || b.node_count > 0) { err = "mask_mat of materials with shader nodes is not implemented on the device"; return false; }
+		d.bsdf_flags = a.bsdf_flags | b.bsdf_flags;
+		d.is_transparent = (matIsTransparent(a) || matIsTransparent(b)) ? 1 : 0;
+		return true;
+	}
+	if(a.type == YAFGPU_MAT_MASK || b.type == YAFGPU_MAT_MASK) { err = "blend_mat of mask_mat is not implemented on the device"; return false; }
 	if(a.type == YAFGPU_MAT_BLEND || b.type == YAFGPU_MAT_BLEND) { err = "blend_mat of blend_mat is not implemented on the device"; return false; }
 	d.bsdf_flags = a.bsdf_flags | b.bsdf_flags;
 	d.additional_depth = a.additional_depth > b.additional_depth ? a.additional_depth : b.additional_depth;
@@ -446,6 +459,9 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 		case YAFGPU_LIGHT_MESH: // MeshLight::factory light_meshlight.cc:251: color * (float)power * M_PI; tables/BVH built by the caller (initIs)
 			for(int k = 0; k < 3; ++k) d.color[k] = (l.color[k] * l.power) * (float)YG_M_PI;
 			d.accel = -1;
+			return true;
+		case YAFGPU_LIGHT_BGPORTAL: // BackgroundPortalLight ctor + factory light_background_portal.cc:34-44,236-266; tables/BVH as for the mesh light (initIs :58-78)
+			d.power = l.power; d.accel = -1; d.double_sided = 0; d.clamp_intersect = 0.f;
 			return true;
 		case YAFGPU_LIGHT_BACKGROUND: // BackgroundLight ctor light_background.cc:56-65; tables built by buildBgLightTables (init)
 			return true;

@@ -489,7 +489,7 @@ YG_DLE void doLightEstimation(const ShadeCtx &cx, const MatDev &m, int slot, con
 	if(ray_division > 1) n = max(1, n / ray_division);
 	const float inv_ns = 1.f / (float)n;
 	const unsigned offs = (unsigned)n * (unsigned)si.pixel_sample + si.sampling_offs + l_offs;
-	const bool can_intersect = lightCanIntersect(L) && !(L.type == YAFGPU_LIGHT_MESH && L.accel < 0);
+	const bool can_intersect = lightCanIntersect(L) && !((L.type == YAFGPU_LIGHT_MESH || L.type == YAFGPU_LIGHT_BGPORTAL) && L.accel < 0);
 	Halton2 hal_2; HaltonB<3> hal_3;
 	hal_2.setStart(offs - 1u); hal_3.setStart(offs - 1u);
 	const double hal_3_start = hal_3.value; // the BSDF loop below restarts both sequences at the same element
@@ -633,7 +633,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 						BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfDiffuse | BsdfReflect; s.pdf = 0.f; s.sampled = BsdfNone;
 						float w = 0.f; V3 adir = mk(0.f);
 						const Col surf_col = matSample<MT>(sc, m, sp, wo, adir, s, w);
-						if(m.bsdf_flags & BsdfEmit) accAdd(acc, slot, W * ((matEmit<MT>(sc, m, sp, wo, true) * s.pdf) / (float)n));
+						if((MT == MT_NODES ? m.obj_flags : m.bsdf_flags) & BsdfEmit) accAdd(acc, slot, W * ((matEmit<MT>(sc, m, sp, wo, true) * s.pdf) / (float)n));
 						const float cosv = fabsf(dot(sp.n, adir));
 						pushShadow(cx, slot, sp.p, ao_tmin, adir, ig.ao_dist, W * ((((ao_col * surf_col) * cosv) * w) / (float)n));
 					}
@@ -686,9 +686,11 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 						++branch;
 						const float s_1 = hal_2.getNext(), s_2 = hal_3.getNext();
 						const unsigned child = packState(TASK_INTEGRATE, rl, 0, new_division, 0, additional_depth);
-						if(m.bsdf_flags & BsdfGlossy)
+						// material->getFlags() here, not the flags initBsdf returned (integrator_montecarlo.cc:895-919): they differ under a mask_mat
+						const unsigned oflags = MT == MT_NODES ? m.obj_flags : m.bsdf_flags;
+						if(oflags & BsdfGlossy)
 						{
-							if((m.bsdf_flags & BsdfReflect) && !(m.bsdf_flags & BsdfTransmit))
+							if((oflags & BsdfReflect) && !(oflags & BsdfTransmit))
 							{
 								BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfReflect; s.pdf = 0.f; s.sampled = BsdfNone;
 								float w = 0.f; V3 wi = mk(0.f);
@@ -696,7 +698,8 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 								const Col f = (mcol * w) * d_1;
 								if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2, beerOf(m, sp, wi));
 							}
-							else if((m.bsdf_flags & BsdfReflect) && (m.bsdf_flags & BsdfTransmit))
+							else if(MT == MT_NODES && m.is_mask) {} // MaskMaterial inherits the two-lobe Material::sample, which returns black and samples nothing
+							else if((oflags & BsdfReflect) && (oflags & BsdfTransmit))
 							{
 								BSample s; s.s1 = s_1; s.s2 = s_2; s.flags = BsdfGlossy | BsdfAllGlossy; s.pdf = 0.f; s.sampled = BsdfNone;
 								Col mcol[2] = {mkc(0.f), mkc(0.f)}; float w[2] = {0.f, 0.f}; V3 d2[2] = {mk(0.f), mk(0.f)};

@@ -297,9 +297,10 @@ YG_D bool lightIllumSample(const SceneDev &sc, const LightDev &L, const SurfPt &
 			pdf = (float)((double)dist_sqr * YG_M_PI / (double)(L.area * cos_angle));
 			return true;
 		}
-		case YAFGPU_LIGHT_MESH:
+		case YAFGPU_LIGHT_BGPORTAL: // BackgroundPortalLight::illumSample light_background_portal.cc:118-150: the mesh light's sampling, single sided,
+		case YAFGPU_LIGHT_MESH:     // colour = the background seen along the light direction
 		{
-			// sampleSurface light_meshlight.cc:87-106
+			// sampleSurface light_meshlight.cc:87-106 / light_background_portal.cc:80-97
 			const float *cdf = sc.light_tables + L.cdf_offset; // cdf[count+1]
 			const int prim = pdf1dDSample(cdf, L.cdf_count, s1);
 			if(prim >= L.cdf_count) return false;
@@ -325,8 +326,14 @@ YG_D bool lightIllumSample(const SceneDev &sc, const LightDev &L, const SurfPt &
 				else return false;
 			}
 			tmax = dist; dir = ldir;
-			col = ldc(L.color);
 			const float amc = L.area * cos_angle;
+			if(L.type == YAFGPU_LIGHT_BGPORTAL)
+			{
+				col = bgEval(sc.bg, ldir) * L.power;
+				pdf = (float)((double)dist_sqr * YG_M_PI / (double)amc);
+				return true;
+			}
+			col = ldc(L.color);
 			pdf = (float)((double)dist_sqr * YG_M_PI / (double)((amc == 0.f) ? 1e-8f : amc));
 			return true;
 		}
@@ -423,6 +430,7 @@ YG_D bool lightIntersect(const SceneDev &sc, const LightDev &L, V3 from, V3 dir,
 			ipdf = (float)((double)(1.f / (t * t) * L.area * cos_angle) * YG_M_1_PI);
 			return true;
 		}
+		case YAFGPU_LIGHT_BGPORTAL: // BackgroundPortalLight::intersect light_background_portal.cc:188-212 (clamp_intersect_ keeps its default 0)
 		case YAFGPU_LIGHT_MESH:
 		{
 			if(L.accel < 0) return false;
@@ -439,7 +447,7 @@ YG_D bool lightIntersect(const SceneDev &sc, const LightDev &L, V3 from, V3 dir,
 			}
 			const float idist_sqr = 1.f / (t * t);
 			ipdf = idist_sqr * L.area * cos_angle * (float)(1.f / YG_M_PI);
-			col = ldc(L.color);
+			col = L.type == YAFGPU_LIGHT_BGPORTAL ? bgEval(sc.bg, dir) * L.power : ldc(L.color);
 			return true;
 		}
 		case YAFGPU_LIGHT_SPOT: // SpotLight::intersect light_spot.cc:215-249 (soft_shadows on)

@@ -729,6 +729,19 @@ YG_DN void evalMaterialNodes(const SceneDev &sc, MatDev &ml, SurfPt &sp, int tri
 			if(ml.type == YAFGPU_MAT_ROUGH_GLASS && YG_SLOT(ROUGHNESS) >= 0) ml.alpha_rough = stack[YG_SLOT(ROUGHNESS)].f + 0.001f; // alpha_2 = alpha_texture^2 (:69-70)
 			break;
 		}
+		case YAFGPU_MAT_MASK:
+		{	// MaskMaterial::initBsdf material_mask.cc:40-51: every later call goes to the chosen child, so its record takes the mask's place;
+			// what the integrator asks the *mask* object itself stays (visibility, shadow reception, additional depth, bias, sampling factor)
+			const MatDev &ch = sc.materials[stack[YG_SLOT(BLEND)].f > ml.blend_val ? ml.mat2 : ml.mat1];
+			const int vis = ml.visibility, rs = ml.receive_shadows, ad = ml.additional_depth, tbm = ml.transp_bias_mult;
+			const float tbf = ml.transp_bias_factor, sf = ml.sampling_factor;
+			const unsigned uni = ml.bsdf_flags; // MaskMaterial ctor: union of the children's flags
+			ml = ch;
+			ml.obj_flags = uni; ml.is_mask = 1;
+			ml.absorb = 0; // MaskMaterial does not forward getVolumeHandler (the base class returns its own, unset, handlers)
+			ml.visibility = vis; ml.receive_shadows = rs; ml.additional_depth = ad; ml.transp_bias_mult = tbm; ml.transp_bias_factor = tbf; ml.sampling_factor = sf;
+			break;
+		}
 		case YAFGPU_MAT_BLEND: // BlendMaterial::getBlendVal material_blend.cc:57-75
 			if(YG_SLOT(BLEND) >= 0) ml.blend_val = stack[YG_SLOT(BLEND)].f;
 			break;

@@ -85,6 +85,8 @@ struct MatDev
 	// (stack index = position); bit i of color_mask / bump_mask = node i is in the colour / bump node list; slot[] = stack index of the
 	// node bound to each "<slot>_shader" parameter, -1 = none.  Filled per hit from the node results (evalMaterialNodes):
 	int node_first, node_count; unsigned color_mask, bump_mask; int slot[YAFGPU_N_SLOTS];
+	unsigned obj_flags; int is_mask;     // Material::getFlags() of the object the integrator holds: equal to bsdf_flags except under a mask_mat, where
+	                                     // bsdf_flags is the chosen child's (what initBsdf returns) and obj_flags the union of both children
 	float diffuse_refl_mul;              // shinydiffuse "diffuse_refl_shader" (1 without it: the reference then does not multiply)
 	int oren_tex; float oren_sigma;      // "sigma_oren_shader": Oren-Nayar coefficients from the textured sigma, in double (material_shiny_diffuse.cc:231-236)
 };
@@ -130,6 +132,7 @@ struct LightDev
 	int tri_first, tri_count;
 	int accel;          // mesh light: index into SceneDev::light_accels (its own BVH, as MeshLight builds its own kd-tree), -1 = none
 	float clamp_intersect; int shoot_caustic;
+	float power;        // background portal: colour = Background::eval(dir) * power_
 	int dirac, can_intersect;   // Light::diracLight() / canIntersect() (the spot light's depend on "soft_shadows")
 	// directional (pos = position_, fnormal = direction_, area = radius_, double_sided = !infinite_), spot (pos, fnormal = ndir_, normal = dir_,
 	// du/dv, cos_angle = cos_end_, pdf = cos_start_, invpdf = icos_diff_, area = shadow_fuzzy_), sphere (pos = center, area = radius^2,

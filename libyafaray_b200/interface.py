@@ -305,6 +305,14 @@ class Interface:
             s.as_diffuse, s.anisotropic = int(g(p, "as_diffuse", True)), int(g(p, "anisotropic", False))
             s.oren_nayar = int(g(p, "diffuse_brdf", "") == "Oren-Nayar")
             s.sigma = g(p, "sigma", 0.1)
+        elif t == "mask_mat":  # material_mask.cc:150-198
+            m.type = capi.MAT_MASK
+            # the mask factory reads nothing but threshold, the two children, receive_shadows and visibility: the rest stays at Material's defaults
+            m.flat_material, m.additional_depth, m.transparent_bias_factor, m.transparent_bias_multiply_raydepth = 0, 0, 0.0, 0
+            m.sampling_factor, m.mat_pass_index = 1.0, 0
+            m.u.blend.material1 = index_of(g(p, "material1", ""))
+            m.u.blend.material2 = index_of(g(p, "material2", ""))
+            m.u.blend.blend_value = g(p, "threshold", 0.5)
         elif t == "blend_mat":  # material_blend.cc:464-518
             m.type = capi.MAT_BLEND
             m.u.blend.material1 = index_of(g(p, "material1", ""))
@@ -397,7 +405,7 @@ class Interface:
             recs.append(r)
         mtype = g(p, "type", "")
         for key, slot in capi.SLOTS.items():
-            if key == "mask" and mtype != "blend_mat":
+            if key == "mask" and mtype not in ("blend_mat", "mask_mat"):
                 continue
             if key in p:
                 n = g(p, key, "")
@@ -469,6 +477,9 @@ class Interface:
             l.type = capi.LIGHT_MESH
             l.object = obj_index_of_id(int(g(p, "object", 0)))
             l.double_sided = int(g(p, "double_sided", False))
+        elif t == "bgPortalLight":  # light_background_portal.cc:236-266
+            l.type = capi.LIGHT_BGPORTAL
+            l.object = obj_index_of_id(int(g(p, "object", 0)))
         elif t == "directional":  # light_directional.cc:112-158
             l.type, l.point1, l.infinite = capi.LIGHT_DIRECTIONAL, pt("direction", (0, 0, 1)), int(g(p, "infinite", True))
             if not l.infinite:

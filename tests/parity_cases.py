@@ -103,7 +103,7 @@ def _set_params(y, kw):
 
 
 def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl=True, sun=True, meshlight=True, transp_shad=False, only_mat=None,
-                       hdr_env=None, extra_lights=(), camera=None, gradient=None, beer=False, **integ):
+                       hdr_env=None, extra_lights=(), camera=None, gradient=None, beer=False, portal=False, **integ):
     """Every material and light type of the hot path in one small scene (configs 3/4 in miniature): glossy, coated_glossy,
     rough_glass, blend_mat, mirror, glass and shinydiffuse boxes on a ground quad; sun + mesh light + constant-background IBL."""
     from libyafaray_b200.interface import Interface
@@ -149,7 +149,17 @@ def material_zoo_scene(width=64, height=36, spp=4, integrator="pathtracing", ibl
         y.startTriMesh(30, 4, 2, False, False, 0)
         scenes._quad(y, (-1.0, 0.5, 3.5), (-1.0, 1.5, 3.5), (1.0, 1.5, 3.5), (1.0, 0.5, 3.5), lm)   # normal -z
         y.endTriMesh()
+    if portal:
+        # a "window" of four triangles the background shines through (bgPortalLight); its own material is an ordinary diffuse one
+        y.startTriMesh(31, 5, 4, False, False, 0)
+        pa, pb, pc, pd, pe = (y.addVertex(-3.0, 3.2, 0.5), y.addVertex(3.0, 3.2, 0.5), y.addVertex(3.0, 3.6, 3.0), y.addVertex(-3.0, 3.6, 3.0), y.addVertex(0.0, 3.5, 1.75))
+        for q in ((pa, pb, pe), (pb, pc, pe), (pc, pd, pe), (pd, pa, pe)):   # wound so that the normals face the boxes (-y)
+            y.addTriangle(q[0], q[1], q[2], ground)
+        y.endTriMesh()
     y.endGeometry()
+    if portal:
+        y.paramsClearAll(); y.paramsSetString("type", "bgPortalLight"); y.paramsSetInt("object", 31); y.paramsSetFloat("power", 2.5); y.paramsSetInt("samples", 3)
+        y.createLight("portal")
     if meshlight:
         y.paramsClearAll(); y.paramsSetString("type", "meshlight"); y.paramsSetInt("object", 30); y.paramsSetColor("color", 1.0, 0.95, 0.8)
         y.paramsSetFloat("power", 6.0); y.paramsSetInt("samples", 2); y.createLight("ml")
@@ -290,7 +300,11 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
         y.paramsClearAll(); y.paramsSetString("type", "shinydiffusemat"); _set_params(y, kw)
 
     modes = {"basic": (0, 2, 4), "modes_b": (1, 3, 6), "modes_c": (5, 7, 8)}.get(variant, (0, 2, 4))
-    if variant == "materials":
+    if variant == "mask":
+        _textured_shinydiffuse_materials(y, sd, node, mapper, layer, modes, variant)
+        _textured_mask_materials(y, sd, node, mapper, layer)
+        box_mats = (("mb0", True, False), ("mb1", False, False), ("b2", True, False), ("mb3", True, False), ("b4", True, False), ("b5", False, True))
+    elif variant == "materials":
         _textured_other_materials(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     else:
@@ -298,6 +312,36 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, integ)
     return y
+
+
+def _textured_mask_materials(y, sd, node, mapper, layer):
+    """mask_mat (material_mask.cc): a textured scalar against a threshold picks one of two materials per hit; used on boxes 0, 1 and 3."""
+    # MaskMaterial::initBsdf evaluates all_nodes_ in DECLARATION order (material_mask.cc:43), not in dependency order: a node declared before its
+    # input reads whatever the previous hit left in the stack.  The nodes are therefore declared inputs first (the device always uses dependency order).
+    def mat(typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ); _set_params(y, kw)
+    mat("glossy", color=(0.9, 0.8, 0.3, 1.0), diffuse_color=(0.4, 0.3, 0.1, 1.0), diffuse_reflect=0.4, glossy_reflect=0.8, exponent=200.0, as_diffuse=False)
+    y.createMaterial("mk_a")
+    mat("shinydiffusemat", color=(0.2, 0.3, 0.8, 1.0), specular_reflect=0.3, diffuse_reflect=0.9)
+    y.createMaterial("mk_b")
+    mat("glass", IOR=1.5, filter_color=(0.9, 1.0, 0.9, 1.0), transmit_filter=0.9)
+    y.createMaterial("mk_g")
+    mat("shinydiffusemat", color=(0.8, 0.25, 0.2, 1.0), diffuse_brdf="oren_nayar", sigma=0.3)
+    y.createMaterial("mk_l")
+    mat("blend_mat", material1="mk_a", material2="mk_l", blend_value=0.4)
+    y.createMaterial("mk_bl")
+    mat("mask_mat", material1="mk_a", material2="mk_b", threshold=0.45, mask="k0_l")
+    mapper("k0_m", texco="orco", mapping="cube", scale=(1.2, 1.2, 1.2))
+    layer("k0_l", "k0_m", do_color=False, do_scalar=True, color_input=True, def_val=1.0, upper_value=0.0)
+    y.createMaterial("mb0")
+    mat("mask_mat", material1="mk_g", material2="mk_bl", threshold=0.35, mask="k1_l", additionaldepth=1)
+    mapper("k1_m", texco="global", mapping="tube")
+    layer("k1_l", "k1_m", do_color=False, do_scalar=True, color_input=False, def_val=1.0, upper_value=0.0)
+    y.createMaterial("mb1")
+    mat("mask_mat", material1="mk_l", material2="mk_a", threshold=0.5, mask="k3_l", receive_shadows=False)
+    mapper("k3_m", texco="orco", mapping="sphere")
+    layer("k3_l", "k3_m", do_color=False, do_scalar=True, color_input=True, def_val=1.0, upper_value=0.0, negative=True)
+    y.createMaterial("mb3")
 
 
 def _textured_other_materials(y, sd, node, mapper, layer):
@@ -491,6 +535,11 @@ def _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, int
 # Beer absorption inside glass / rough glass (the volume handler the factories create when the material has a "name" parameter)
 EXACT["zoo_dl_beer"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=5, beer=True)
 EXACT["zoo_pt_beer_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, rr_min_bounces=99, beer=True, raydepth=5)
+# bgPortalLight: a window mesh that radiates the (HDR / gradient) background
+EXACT["zoo_dl_portal_hdr"] = lambda: material_zoo_scene(96, 54, 2, integrator="directlighting", raydepth=3, sun=False, meshlight=False, ibl=False, portal=True,
+                                                        hdr_env={"rotation": 15.0})
+EXACT["zoo_pt_portal_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, meshlight=False, ibl=False, portal=True, rr_min_bounces=99, gradient={
+    "horizon_color": (0.9, 0.8, 0.7, 1.0), "zenith_color": (0.2, 0.4, 0.9, 1.0), "power": 1.5})
 EXACT["tex_dl_basic"] = lambda: textured_scene(96, 54, 2)
 EXACT["tex_dl_modes_b"] = lambda: textured_scene(96, 54, 2, variant="modes_b", tex={"interpolate": "none", "clipping": "extend"})
 EXACT["tex_dl_modes_c"] = lambda: textured_scene(96, 54, 2, variant="modes_c", tex={"interpolate": "bicubic", "mirror_x": True, "mirror_y": True, "xrepeat": 2, "yrepeat": 3})
@@ -500,5 +549,7 @@ EXACT["tex_dl_checker"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "ch
 EXACT["tex_dl_clip"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "clip", "cropmin_y": 0.2})
 EXACT["tex_pt_norr"] = lambda: textured_scene(96, 54, 4, integrator="pathtracing")
 EXACT["tex_dl_camera_coords"] = lambda: textured_scene(96, 54, 2, variant="camera_coords")
+EXACT["tex_dl_mask"] = lambda: textured_scene(96, 54, 2, variant="mask", raydepth=4)
+EXACT["tex_pt_mask_norr"] = lambda: textured_scene(96, 54, 4, variant="mask", integrator="pathtracing", raydepth=4)
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)
