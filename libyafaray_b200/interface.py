@@ -134,6 +134,12 @@ class Interface:
         self.meshes[id] = m
         return True
 
+    def addInstance(self, base_object_id, obj_to_world):
+        # TriangleObjectInstance::getPrimitives is declared non-const (object_geom_mesh.h:124) and so does not override the const virtual that
+        # Scene::update calls (scene.cc:816): the reference counts an instance's triangles but never hands them to the kd-tree builder, which then
+        # reads uninitialised pointers (it crashes on every scene with an <instance>).  There is no reference behaviour to reproduce.
+        raise NotImplementedError("addInstance: instances do not render in the reference (Scene::update never collects their triangles)")
+
     def smoothMesh(self, id, angle):
         raise NotImplementedError("smoothMesh: pass explicit vertex normals (addNormal); the reference-side adaptor "
                                   "exports the normals Scene::smoothMesh produced (scene.cc:420-539)")
