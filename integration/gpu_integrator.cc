@@ -721,9 +721,22 @@ bool GpuIntegrator::render(int num_view, ImageFilm *film)
 	g_timer__.start("rendert");
 	film->init(aa_passes);
 	film->setAaNoiseParams(color_noise, dark_type, dark_factor, var_edge, var_pix, clamp_s);
-	if(yafgpu_film_clear(ctx_) != YAFGPU_OK) return fail("film clear failed");
 	const int w = film->w_, h = film->h_;
 	const unsigned base = film->getBaseSamplingOffset();
+	if(session__.renderResumed())
+	{	// film_save_load "load-save": ImageFilm::init has summed the YAF_FILMv1 files of the output folder into the film (imagefilm.cc:1467-1558):
+		// the device continues from those accumulators
+		host_film_.resize((size_t)w * h * 5);
+		const Rgba2DImageWeighed_t &img = *film->image_passes_[0];
+		for(int y = 0; y < h; ++y) for(int x = 0; x < w; ++x)
+		{
+			const Pixel &p = img(x, y);
+			float *o = &host_film_[((size_t)y * w + x) * 5];
+			o[0] = p.col_.r_; o[1] = p.col_.g_; o[2] = p.col_.b_; o[3] = p.col_.a_; o[4] = p.weight_;
+		}
+		if(yafgpu_write_film(ctx_, host_film_.data()) != YAFGPU_OK) return fail("film upload failed");
+	}
+	else if(yafgpu_film_clear(ctx_) != YAFGPU_OK) return fail("film clear failed");
 
 	auto pass = [&](int samples, int offset, bool adaptive, int number, const uint8_t *mask) -> bool
 	{
@@ -735,8 +748,14 @@ bool GpuIntegrator::render(int num_view, ImageFilm *film)
 		if(yafgpu_render_pass(ctx_, &pd) != YAFGPU_OK) return fail("render pass failed");
 		return depositFilm(film);
 	};
-	if(!pass(aa_samples, 0, false, 0, nullptr)) return false;
 	int acum = aa_samples, resampled = 0;
+	if(session__.renderResumed())
+	{	// "skipping pass 1": renderPass(0 samples, offset = the loaded film's sampling offset) (integrator_tiled.cc:198-202)
+		acum = (int)film->getSamplingOffset();
+		session__.setStatusCurrentPass(1);
+		film->setSamplingOffset(acum);
+	}
+	else if(!pass(aa_samples, 0, false, 0, nullptr)) return false;
 	bool thr_changed = true;
 	std::vector<uint8_t> mask;
 	for(int i = 1; i < aa_passes; ++i)

@@ -8,5 +8,6 @@ loudly when it is missing — there is no CPU fallback.
 from . import capi  # noqa: F401  (dlopens libyafgpu.so, raises ImportError when it is not built)
 from .interface import Interface  # noqa: F401
 from .render import Context, render_scene, load_film, film_to_image  # noqa: F401
+from . import film_io  # noqa: F401
 
-__all__ = ["capi", "Interface", "Context", "render_scene", "load_film", "film_to_image"]
+__all__ = ["capi", "Interface", "Context", "render_scene", "load_film", "film_to_image", "film_io"]

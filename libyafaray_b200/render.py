@@ -7,6 +7,7 @@ flagging) is evaluated on the host film between passes when AA_threshold > 0.
 """
 import ctypes as C
 import math
+import os
 import struct
 
 import numpy as np
@@ -127,8 +128,14 @@ def load_film(path):
         return np.frombuffer(fh.read(), np.float32).reshape(h, w, 5).copy()
 
 
-def render_scene(iface, output=None, device=0, ctx=None):
-    """TiledIntegrator::render pass schedule (integrator_tiled.cc:116-259) driving the GPU passes. Returns the film."""
+def render_scene(iface, output=None, device=0, ctx=None, image_output_path=None):
+    """TiledIntegrator::render pass schedule (integrator_tiled.cc:116-259) driving the GPU passes. Returns the film.
+
+    `image_output_path` plays the role of yafaray-xml's output image path for the <render> parameter `film_save_load`
+    (environment.cc:499,524-526): "save" writes "<path> - node NNNN.film" after the render, "load-save" first sums every matching
+    film of that folder into the accumulators and continues from the loaded sampling offset, skipping pass 1
+    (imagefilm.cc:262-267,1467-1558; integrator_tiled.cc:174-202).  The files are the reference's YAF_FILMv1 format (film_io.py)."""
+    from . import film_io
     g, rp = iface._g, iface.render_params
     desc, keep = iface.scene_desc()
     own = ctx is None
@@ -141,10 +148,25 @@ def render_scene(iface, output=None, device=0, ctx=None):
     lmf = np.float32(g(rp, "AA_light_sample_multiplier_factor", 1.0))
     imf = np.float32(g(rp, "AA_indirect_sample_multiplier_factor", 1.0))
     threshold = g(rp, "AA_threshold", 0.05)
-    base = desc.film.base_sampling_offset
-    ctx.film_clear()
-    ctx.render_pass(aa_samples, 0 + base, False, 0)
-    acum = aa_samples
+    fsl = g(rp, "film_save_load", "none") if image_output_path is not None else "none"
+    node, base_raw = int(g(rp, "adv_computer_node", 0)), int(g(rp, "adv_base_sampling_offset", 0))
+    loaded = None
+    if fsl == "load-save":
+        loaded, _paths = film_io.load_films_in_folder(image_output_path, (desc.film.height, desc.film.width))
+        if loaded is not None:
+            base_raw = max(base_raw, loaded.base_sampling_offset)
+    if fsl in ("save", "load-save"):
+        fp = film_io.film_path(image_output_path, node)
+        if os.path.exists(fp):   # imageFilmFileBackup (imagefilm.cc:1659-1690)
+            os.replace(fp, fp + "-previous.bak")
+    base = base_raw + node * 100000   # ImageFilm::getBaseSamplingOffset (imagefilm.h:124)
+    if loaded is not None:
+        ctx.write_film(loaded.film)
+        acum = sampling_offset = loaded.sampling_offset
+    else:
+        ctx.film_clear()
+        ctx.render_pass(aa_samples, 0 + base, False, 0)
+        acum = sampling_offset = aa_samples
     sm, lm, im = np.float32(1), np.float32(1), np.float32(1)
     for i in range(1, aa_passes):
         sm, lm, im = np.float32(sm * smf), np.float32(lm * lmf), np.float32(im * imf)
@@ -153,9 +175,13 @@ def render_scene(iface, output=None, device=0, ctx=None):
         if threshold > 0:
             raise NotImplementedError("adaptive AA (AA_threshold > 0 with AA_passes > 1): set AA_threshold 0")
         ctx.render_pass(n, acum + base, True, i)  # threshold 0: doMoreSamples() is true for every pixel (imagefilm.cc:917-920)
+        sampling_offset = acum + n                # ImageFilm::setSamplingOffset(offset + samples) (integrator_tiled.cc:270)
         acum += n
     ctx.sync()
     film = ctx.read_film()
+    if fsl in ("save", "load-save"):
+        film_io.write_film_file(film_io.film_path(image_output_path, node), film, sampling_offset, base_raw, node,
+                                int(g(rp, "xstart", 0)), int(g(rp, "ystart", 0)))
     if output is not None:
         output(film)
     if own:

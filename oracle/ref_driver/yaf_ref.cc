@@ -78,6 +78,9 @@ class NullOutput : public ColorOutput
 		bool putPixel(int, int, int, const RenderPasses *, const std::vector<Rgba> &, bool) override { return true; }
 		void flush(int, const RenderPasses *) override {}
 		void flushArea(int, int, int, int, int, const RenderPasses *) override {}
+		// ImageFilm::flush saves the "YAF_FILMv1" file only for an image output (imagefilm.cc:900-906); YAF_REF_FILM_PATH plays the role of
+		// yafaray-xml's output path (output_image.cc:36), so `film_save_load` in the <render> block works as it does there
+		bool isImageOutput() override { return getenv("YAF_REF_FILM_PATH") != nullptr; }
 };
 
 struct Loaded
@@ -99,6 +102,7 @@ bool loadScene(const char *xml, Loaded &l, int threads)
 	if(threads >= -1) l.render["threads"] = threads;
 	l.render["logging_saveLog"] = false;
 	l.render["logging_saveHTML"] = false;
+	if(const char *fp = getenv("YAF_REF_FILM_PATH")) session__.setPathImageOutput(fp);
 	if(!l.env->setupScene(*l.scene, l.render, l.out)) return false;
 	session__.setInteractive(false);
 	return true;

@@ -21,8 +21,8 @@ def ref_bin(flavour="ieee"):
     return p if os.path.exists(p) else None
 
 
-def _run(args, timeout=3600):
-    r = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=timeout)
+def _run(args, timeout=3600, env=None):
+    r = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=timeout, env=env)
     if r.returncode != 0:
         raise RuntimeError("oracle failed: %s\n%s" % (" ".join(args), r.stderr.decode(errors="replace")[-2000:]))
     out = r.stdout.decode(errors="replace").strip().splitlines()
@@ -39,15 +39,16 @@ def load_film(path):
         return np.frombuffer(fh.read(), np.float32).reshape(h, w, 5).copy()
 
 
-def run_reference_render(iface, threads=1, flavour="ieee", timeout=3600):
-    """Render `iface` with the reference CPU code; returns (film[h,w,5], info dict)."""
+def run_reference_render(iface, threads=1, flavour="ieee", timeout=3600, film_path=None):
+    """Render `iface` with the reference CPU code; returns (film[h,w,5], info dict).  `film_path` = the image output path that the
+    <render> parameter film_save_load refers to (YAF_REF_FILM_PATH of oracle/ref_driver/yaf_ref.cc)."""
     exe = ref_bin(flavour)
     if exe is None:
         return None, None
     with tempfile.TemporaryDirectory() as td:
         xml, out = os.path.join(td, "scene.xml"), os.path.join(td, "out.film")
         iface.to_xml(xml)
-        info = _run([exe, "render", xml, out, str(threads)], timeout)
+        info = _run([exe, "render", xml, out, str(threads)], timeout, env=None if film_path is None else dict(os.environ, YAF_REF_FILM_PATH=film_path))
         return load_film(out), info
 
 

@@ -553,3 +553,20 @@ EXACT["tex_dl_mask"] = lambda: textured_scene(96, 54, 2, variant="mask", raydept
 EXACT["tex_pt_mask_norr"] = lambda: textured_scene(96, 54, 4, variant="mask", integrator="pathtracing", raydepth=4)
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)
+
+
+def film_io_scene(aa_passes, film_save_load, width=32, height=18, inc=3):
+    """Cornell box for the YAF_FILMv1 tests: `aa_passes` passes (2 samples, then `inc` per pass, no adaptive threshold), computer node 3,
+    base sampling offset 17, the given film_save_load mode."""
+    y = scenes.cornell_box(width, height, 2, path_samples=2, bounces=5, raydepth=5, rr_min_bounces=99)   # no roulette: no rand()-seeded prng
+    if y.render_params is None:
+        y.setRenderParams()
+    rp = y.render_params
+    rp["AA_passes"], rp["AA_inc_samples"], rp["AA_threshold"] = ("int", aa_passes), ("int", inc), ("float", 0.0)
+    rp["adv_computer_node"], rp["adv_base_sampling_offset"] = ("int", 3), ("int", 17)
+    rp["film_save_load"] = ("string", film_save_load)
+    return y
+
+
+# three AA passes without adaptive threshold on computer node 3 with a base sampling offset
+EXACT["cornell_pt_3pass_node3"] = lambda: film_io_scene(3, "none")

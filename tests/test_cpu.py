@@ -152,3 +152,77 @@ def test_gpu_frontend_fails_loudly_without_gpu_and_can_be_disabled():
     assert r.returncode == 0
     gold = np.load(os.path.join(ou.GOLDEN, "simple_dl_gauss.npz"))["film"]
     assert np.array_equal(film, gold)
+
+
+# ---- YAF_FILMv1: the reference's on-disk film format (imagefilm.cc:1340-1465,1560-1657) -------------------------------------
+REF_FILM = os.path.join(ou.GOLDEN, "ref_cornell_32x18.film")
+
+
+def test_film_file_reader_and_writer_against_a_film_saved_by_the_reference():
+    """tests/golden/ref_cornell_32x18.film was written by the reference's own ImageFilm::imageFilmSave (tools/make_film_golden.py); the
+    .npz beside it is the raw accumulator dump of the same render."""
+    from libyafaray_b200 import film_io
+    raw = np.load(os.path.join(ou.GOLDEN, "ref_cornell_32x18.npz"))["film"]
+    f = film_io.read_film_file(REF_FILM, expect_shape=raw.shape[:2])
+    assert (f.computer_node, f.base_sampling_offset, f.sampling_offset, f.cx0, f.cy0) == (3, 17, 2, 0, 0)
+    assert len(f.passes) == 1 and len(f.aux_passes) == 0
+    assert np.array_equal(f.film, raw)
+    with tempfile.TemporaryDirectory() as td:
+        p = film_io.write_film_file(os.path.join(td, "w.film"), raw, sampling_offset=2, base_sampling_offset=17, computer_node=3)
+        assert open(p, "rb").read() == open(REF_FILM, "rb").read()          # byte for byte what the reference wrote
+    assert film_io.film_path("/x/img.tga", 3) == "/x/img.tga - node 0003.film"
+
+
+def test_film_file_reader_refuses_what_the_reference_refuses():
+    from libyafaray_b200 import film_io
+    data = open(REF_FILM, "rb").read()
+    with tempfile.TemporaryDirectory() as td:
+        bad = os.path.join(td, "bad.film")
+        open(bad, "wb").write(b"YAF_FILMv2" + data[10:])
+        with pytest.raises(ValueError):
+            film_io.read_film_file(bad)                                      # header check (imagefilm.cc:1352-1358)
+        open(bad, "wb").write(data[:-8])
+        with pytest.raises(ValueError):
+            film_io.read_film_file(bad)                                      # truncated pixel data
+        with pytest.raises(ValueError):
+            film_io.read_film_file(REF_FILM, expect_shape=(18, 33))          # "film check failed. Image width" (:1364-1369)
+
+
+def test_films_of_a_folder_are_summed_like_imageFilmLoadAllInFolder():
+    from libyafaray_b200 import film_io
+    raw = np.load(os.path.join(ou.GOLDEN, "ref_cornell_32x18.npz"))["film"]
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "img.tga")
+        film_io.write_film_file(film_io.film_path(out, 0), raw, sampling_offset=2, base_sampling_offset=5)
+        film_io.write_film_file(film_io.film_path(out, 1), raw * np.float32(0.5), sampling_offset=9, base_sampling_offset=1, computer_node=1)
+        film_io.write_film_file(os.path.join(td, "other - node 0000.film"), raw)            # other base name: ignored
+        film_io.write_film_file(os.path.join(td, "img_small.film"), raw[:9])                # wrong size: skipped with a warning
+        total, loaded = film_io.load_films_in_folder(out, raw.shape[:2])
+        assert [os.path.basename(p) for p in loaded] == ["img.tga - node 0000.film", "img.tga - node 0001.film"]
+        assert np.array_equal(total.film, raw + raw * np.float32(0.5))
+        assert (total.sampling_offset, total.base_sampling_offset) == (9, 5)
+        assert film_io.load_films_in_folder(os.path.join(td, "nothing.tga"), raw.shape[:2])[0] is None
+
+
+@pytest.mark.skipif(ou.ref_bin() is None, reason="live oracle not available")
+def test_reference_resumes_from_a_film_written_by_our_writer():
+    """ImageFilm::imageFilmLoadAllInFolder of the reference reads a file produced by film_io.write_film_file and continues the render
+    from it: same final film as when it resumes from the file it saved itself."""
+    from libyafaray_b200 import film_io
+    finals = []
+    for ours in (False, True):
+        with tempfile.TemporaryDirectory() as td:
+            out = os.path.join(td, "img.tga")
+            first, _ = ou.run_reference_render(pc.film_io_scene(1, "save"), film_path=out)
+            fp = film_io.film_path(out, 3)
+            if ours:
+                f = film_io.read_film_file(fp)
+                os.remove(fp)
+                film_io.write_film_file(fp, first, f.sampling_offset, f.base_sampling_offset, f.computer_node)
+            final, _ = ou.run_reference_render(pc.film_io_scene(3, "load-save"), film_path=out)
+            saved = film_io.read_film_file(fp)
+            assert np.array_equal(saved.film, final) and saved.sampling_offset == 2 + 3 + 3
+            assert os.path.exists(fp + "-previous.bak")
+            finals.append(final)
+    assert np.array_equal(finals[0], finals[1])
+    assert not np.array_equal(finals[0], first) and finals[0][..., 4].min() > first[..., 4].max() * 2

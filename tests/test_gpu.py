@@ -1,6 +1,7 @@
 """GPU parity tests (`-m gpu`): the CUDA path, called through the C ABI (libyafgpu.so via ctypes), against the oracle —
 golden fixtures generated from the reference's own CPU code, and the live oracle binary when it travelled with the snapshot."""
 import os
+import tempfile
 import sys
 
 import numpy as np
@@ -241,3 +242,42 @@ def test_all_material_and_light_types_render_finite(ctx):
     y = pc.material_zoo_scene(64, 36, 4)
     img = _img(render_scene(y, ctx=ctx))
     assert np.isfinite(img).all() and img[..., :3].mean() > 1e-3
+
+
+# ---- YAF_FILMv1 either side of the path: films saved by the reference are resumed on the GPU and the other way round ------------
+@pytest.mark.skipif(ou.gpu_frontend_bin() is None or ou.ref_bin() is None, reason="oracle/_ref binaries not built")
+def test_frontend_resumes_on_the_gpu_from_a_film_saved_by_the_cpu_integrator():
+    """film_save_load: the reference's CPU integrator renders pass 1 and saves "img.tga - node 0003.film"; the reference front end with the
+    GPU integrator loads it (ImageFilm::init -> imageFilmLoadAllInFolder), uploads the accumulators and renders passes 2 and 3.
+    Result = what the CPU integrator reaches when it resumes from the same file (tests/golden/ref_cornell_32x18_resumed.npz); the film it saves is readable and equal to what it returned."""
+    from libyafaray_b200 import film_io
+    gold = np.load(os.path.join(ou.GOLDEN, "ref_cornell_32x18_resumed.npz"))["film"]
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "img.tga")
+        ou.run_reference_render(pc.film_io_scene(1, "save"), film_path=out)
+        film, info, r = ou.run_gpu_frontend(pc.film_io_scene(3, "load-save"), env={"YAF_REF_FILM_PATH": out})
+        assert r.returncode == 0, r.stderr.decode(errors="replace")[-2000:]
+        _assert_film_matches(film, gold)
+        saved = film_io.read_film_file(film_io.film_path(out, 3))
+        assert np.array_equal(saved.film, film) and (saved.sampling_offset, saved.base_sampling_offset, saved.computer_node) == (8, 17, 3)
+
+
+@pytest.mark.skipif(ou.ref_bin() is None, reason="live oracle not available")
+def test_film_saved_by_the_gpu_is_resumed_by_the_reference_and_by_the_gpu(ctx):
+    from libyafaray_b200 import render_scene, film_io
+    gold = np.load(os.path.join(ou.GOLDEN, "ref_cornell_32x18_resumed.npz"))["film"]
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "img.tga")
+        first = render_scene(pc.film_io_scene(1, "save"), ctx=ctx, image_output_path=out)
+        fp = film_io.film_path(out, 3)
+        f = film_io.read_film_file(fp, expect_shape=first.shape[:2])
+        assert np.array_equal(f.film, first) and (f.sampling_offset, f.base_sampling_offset, f.computer_node) == (2, 17, 3)
+        keep = open(fp, "rb").read()
+        final_ref, _ = ou.run_reference_render(pc.film_io_scene(3, "load-save"), film_path=out)   # CPU integrator continues the GPU film
+        _assert_film_matches(final_ref, gold)
+        for n in os.listdir(td):
+            os.remove(os.path.join(td, n))
+        open(fp, "wb").write(keep)
+        final_gpu = render_scene(pc.film_io_scene(3, "load-save"), ctx=ctx, image_output_path=out)  # and so does the GPU
+        _assert_film_matches(final_gpu, gold)
+        assert film_io.read_film_file(fp).sampling_offset == 8 and os.path.exists(fp + "-previous.bak")
