@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define YAFGPU_ABI_VERSION 3
+#define YAFGPU_ABI_VERSION 4
 
 typedef struct yafgpu_ctx yafgpu_ctx;
 
@@ -310,6 +310,10 @@ typedef enum yafgpu_light_type
 	YAFGPU_LIGHT_DIRECTIONAL = 5,/* "directional" light_directional.cc:112-158 */
 	YAFGPU_LIGHT_SPOT = 6,       /* "spotlight"   light_spot.cc:251-295 */
 	YAFGPU_LIGHT_SPHERE = 7,     /* "spherelight" light_sphere.cc:163-198 (without a linked sphere primitive: "object" must be 0) */
+	YAFGPU_LIGHT_IES = 9,        /* "ieslight"    light_ies.cc:184-233: a point source whose intensity follows the photometric web of an IESNA LM-63 file;
+	                              * the caller passes the FILE CONTENTS (ies_data / ies_size), the library parses them as IesData::parseIesFile does
+	                              * (include/utility/util_ies.h:131-379).  A file the reference's parser rejects makes its factory return no light at
+	                              * all: such a light must not be passed (upload fails with YAFGPU_ERR_INVALID) */
 	YAFGPU_LIGHT_BGPORTAL = 8    /* "bgPortalLight" light_background_portal.cc:236-266: the mesh "object" is a window that radiates the background
 	                              * (colour = Background::eval(direction) * power); the mesh must be present in the geometry — the reference's
 	                              * kd-tree is built before the light's init() hides it (scene.cc:788-831 precede the light loop) */
@@ -327,8 +331,8 @@ typedef struct yafgpu_light
 	int32_t abs_intersect;   /* bg: "abs_intersect" */
 	float color[3];          /* "color" */
 	float power;             /* "power" */
-	float from[3];           /* point/spot/sphere/finite directional: "from"; sun: "direction"; area: "corner" */
-	float point1[3];         /* area: "point1"; spot: "to"; directional: "direction" */
+	float from[3];           /* point/spot/sphere/ies/finite directional: "from"; sun: "direction"; area: "corner" */
+	float point1[3];         /* area: "point1"; spot, ies: "to"; directional: "direction" */
 	float point2[3];         /* area: "point2" */
 	float angle;             /* sun: "angle" (degrees) */
 	float clamp_intersect;   /* bg: ibl_clamp_sampling */
@@ -338,8 +342,10 @@ typedef struct yafgpu_light
 	float cone_angle;        /* spot: "cone_angle" (degrees) */
 	float blend;             /* spot: "blend" */
 	float shadow_fuzzy;      /* spot: "shadowFuzzyness" */
-	int32_t soft_shadows;    /* spot: "soft_shadows" (then it is an area-like light with "samples") */
+	int32_t soft_shadows;    /* spot, ies: "soft_shadows" (then it is an area-like light with "samples") */
 	int32_t infinite;        /* directional: "infinite" */
+	const char *ies_data;    /* ies: contents of the file named by "file" (need not be NUL terminated) */
+	size_t ies_size;
 } yafgpu_light;
 
 /* ---- camera ---------------------------------------------------------------------------- */

@@ -27,6 +27,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
 #include <iomanip>
 #include <iostream>
 #include <limits>
@@ -83,6 +84,7 @@ struct Recorded
 	ParamMap film;                               // the <render> block as setupScene saw it
 	ParamMap integrator;
 	std::string background_name;
+	std::list<std::string> ies_texts;            // contents of the IES files of the scene's ieslights (kept alive across yafgpu_upload_scene)
 };
 Recorded &rec() { static Recorded r; return r; }
 
@@ -424,6 +426,18 @@ bool lightRecord(const Light *l, const std::map<int, int> &obj_index_of_id, yafg
 		out.soft_shadows = par<bool>(p, "soft_shadows", false); out.shadow_fuzzy = par<float>(p, "shadowFuzzyness", 1.f);
 		out.samples = par<int>(p, "samples", 8);
 	}
+	else if(type == "ieslight")
+	{	// light_ies.cc:184-233; the library parses the file contents as IesData::parseIesFile does (the light exists, so the reference's parse succeeded)
+		out.type = YAFGPU_LIGHT_IES;
+		par3(p, "from", out.from, 0.f, 0.f, 0.f); par3(p, "to", out.point1, 0.f, 0.f, -1.f);
+		out.soft_shadows = par<bool>(p, "soft_shadows", false); out.samples = par<int>(p, "samples", 16);
+		const std::string file = par<std::string>(p, "file", "");
+		std::ifstream fin(file.c_str(), std::ios::in | std::ios::binary);
+		if(!fin) { err = "cannot read the IES file '" + file + "'"; return false; }
+		std::stringstream ss; ss << fin.rdbuf();
+		rec().ies_texts.push_back(ss.str());
+		out.ies_data = rec().ies_texts.back().data(); out.ies_size = rec().ies_texts.back().size();
+	}
 	else if(type == "spherelight")
 	{	// light_sphere.cc:163-198
 		out.type = YAFGPU_LIGHT_SPHERE;
@@ -577,6 +591,7 @@ bool GpuIntegrator::preprocess()
 	d.textures = pool.textures.data(); d.n_textures = pool.textures.size();
 
 	// lights in Scene::lights_ order (the order doLightEstimation's per-light QMC offsets depend on)
+	rec().ies_texts.clear();
 	std::vector<yafgpu_light> lights(std::max<size_t>(1, scene_->lights_.size()));
 	for(size_t i = 0; i < scene_->lights_.size(); ++i)
 		if(!lightRecord(scene_->lights_[i], obj_index_of_id, lights[i], err)) return fail(err);

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("YAFGPU_LIB") or os.path.join(_HERE, "libyafgpu.so")  # YAFGPU_LIB: kernel-variant experiments (tools/)
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # enums (include/yafgpu.h)
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE, ERR_NOMEM = range(6)
@@ -17,7 +17,7 @@ VIS_NORMAL, VIS_NO_SHADOWS, VIS_SHADOW_ONLY, VIS_INVISIBLE = range(4)
 (MAT_SHINYDIFFUSE, MAT_GLOSSY, MAT_COATED_GLOSSY, MAT_GLASS, MAT_ROUGH_GLASS, MAT_BLEND, MAT_MIRROR, MAT_NULL,
  MAT_LIGHT) = range(9)
 MAT_MASK = 11
-LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE, LIGHT_BGPORTAL = range(9)
+LIGHT_POINT, LIGHT_SUN, LIGHT_AREA, LIGHT_MESH, LIGHT_BACKGROUND, LIGHT_DIRECTIONAL, LIGHT_SPOT, LIGHT_SPHERE, LIGHT_BGPORTAL, LIGHT_IES = range(10)
 CAM_PERSPECTIVE, CAM_ARCHITECT, CAM_ORTHOGRAPHIC, CAM_ANGULAR, CAM_EQUIRECTANGULAR = range(5)
 ANGULAR_PROJECTIONS = {"equidistant": 0, "orthographic": 1, "stereographic": 2, "equisolid_angle": 3, "rectilinear": 4}
 BK = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}
@@ -119,7 +119,7 @@ class Light(C.Structure):
                 ("object", i32), ("double_sided", i32), ("abs_intersect", i32), ("color", F3), ("power", f32),
                 ("from_", F3), ("point1", F3), ("point2", F3), ("angle", f32), ("clamp_intersect", f32),
                 ("shoot_caustic", i32), ("shoot_diffuse", i32), ("radius", f32), ("cone_angle", f32), ("blend", f32),
-                ("shadow_fuzzy", f32), ("soft_shadows", i32), ("infinite", i32)]
+                ("shadow_fuzzy", f32), ("soft_shadows", i32), ("infinite", i32), ("ies_data", C.c_char_p), ("ies_size", C.c_size_t)]
 
 
 class Camera(C.Structure):

@@ -293,6 +293,11 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	{
 		LightDev &ld = c->h_lights[i];
 		if(ld.type == YAFGPU_LIGHT_MESH || ld.type == YAFGPU_LIGHT_BGPORTAL) buildMeshLightTables(g, g.objects[ld.object], ld, light_tab);
+		else if(ld.type == YAFGPU_LIGHT_IES)
+		{
+			std::string ies_err;
+			if(!buildIesTables(desc->lights[i], ld, light_tab, ies_err)) return setErr(c, YAFGPU_ERR_INVALID, ies_err.c_str());
+		}
 		else if(ld.type == YAFGPU_LIGHT_BACKGROUND)
 		{
 			if(bg.type == YAFGPU_BG_NONE) return setErr(c, YAFGPU_ERR_INVALID, "bglight without a background");

@@ -9,6 +9,8 @@
 #include <cstring>
 #include <functional>
 #include <algorithm>
+#include <sstream>
+#include <limits>
 
 namespace yg {
 
@@ -410,6 +412,9 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 			d.dirac = !l.soft_shadows; d.can_intersect = l.soft_shadows != 0;
 			return true;
 		}
+		case YAFGPU_LIGHT_IES: // finished by buildIesTables (needs the table vector)
+			d.dirac = !l.soft_shadows; d.can_intersect = 0;
+			return true;
 		case YAFGPU_LIGHT_SPHERE: // SphereLight::SphereLight light_sphere.cc:31-41
 		{
 			if(l.object > 0) { err = "spherelight linked to a sphere primitive is not supported"; return false; }
@@ -473,6 +478,90 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 
 
 // MeshLight::initIs light_meshlight.cc:55-73 + Pdf1D/cumulateStep1DDf__ util_sample.h:89-124: appends cdf[count+1] to `tab`
+// IesLight::IesLight (light_ies.cc:30-50) + IesData::parseIesFile (util_ies.h:131-379) on the file CONTENTS.  The parser is the reference's token
+// stream, restated with the same iostream extractions (so malformed numbers behave alike); its console prints are dropped.  Differences, all on
+// input the reference mishandles: a file without any "TILT=" token loops forever there and is rejected here; and getRadiance's interval search reads
+// one element past each angle map (util_ies.h:94-111).  That element is allocator slack or the next chunk's header (zero or a denormal), never
+// greater than an angle that has reached the last map entry, so for such an angle no interval matches, the index stays 0 and the reference
+// EXTRAPOLATES from the first cell (often to a negative radiance, which doLightEstimation then drops through its pdf test).  The sampled direction of
+// a soft-shadow ieslight is not unit length, so this happens routinely (world z >= 1 and y < 0 give a horizontal angle of exactly 360).
+// The horizontal map carries -INF in that slot, which reproduces exactly that (pinned by the soft-shadow parity renders).  The vertical map can only
+// be overrun in the thin ring where the fast-cosine cut-off lets the angle pass its last entry; there the reference's result depends on heap contents
+// (its golden renders behave as if the element were large: the last cell is kept), so that slot carries +INF.
+inline bool buildIesTables(const yafgpu_light &l, LightDev &d, std::vector<float> &tab, std::string &err)
+{
+	if(!l.ies_data || l.ies_size < 7) { err = "ieslight: IES file missing or too small"; return false; }
+	const std::string text(l.ies_data, l.ies_size);
+	if(text.compare(0, 6, "IESNA:") != 0) { err = "ieslight: wrong file format, first characters are not \"IESNA:\""; return false; }
+	std::istringstream fin(text);
+	std::string line;
+	fin >> line;
+	while(line.find("TILT=") == std::string::npos)
+	{
+		if(!(fin >> line)) { err = "ieslight: no TILT= entry in the IES file"; return false; }
+	}
+	if(line == "TILT=INCLUDE")
+	{
+		int pairs = 0;
+		fin >> line;
+		fin >> pairs;
+		for(int i = 0; i < (pairs * 2); i++) fin >> line;
+	}
+	float candela_mult = 0.f;
+	int nv = 0, nh = 0, type = 0;
+	fin >> line; fin >> line;
+	fin >> candela_mult;
+	fin >> nv; fin >> nh;
+	fin >> type;
+	fin >> line;
+	float w = 0.f, lg = 0.f, h = 0.f;
+	fin >> w; fin >> lg; fin >> h;
+	fin >> line; fin >> line; fin >> line;
+	if(nv < 1 || nh < 1 || nv > (1 << 16) || nh > (1 << 16)) { err = "ieslight: implausible angle counts in the IES file"; return false; }
+	std::vector<float> vert((size_t)nv, 0.f);
+	float max_v = 0.f;
+	for(int i = 0; i < nv; ++i) { fin >> vert[i]; if(max_v < vert[i]) max_v = vert[i]; }
+	if(vert[0] > 0.f)
+	{
+		const float minus = vert[0];
+		max_v -= minus;
+		for(int i = 0; i < nv; ++i) vert[i] -= minus;
+	}
+	max_v = (float)((double)max_v * 0.01745329251994329576922); // DEG_TO_RAD: float * double
+	bool h_adjust = false;
+	if(type == 1 /* TypeC */ && nh == 1) { nh++; h_adjust = true; }
+	std::vector<float> hor((size_t)nh, 0.f);
+	for(int i = 0; i < nh; ++i)
+	{
+		if(i == nh - 1 && h_adjust) hor[i] = 180.f;
+		else fin >> hor[i];
+	}
+	float max_rad = 0.f;
+	std::vector<float> rad((size_t)nh * nv, 0.f);
+	for(int i = 0; i < nh; ++i) for(int j = 0; j < nv; ++j)
+	{
+		if(i == nh - 1 && h_adjust) rad[(size_t)i * nv + j] = rad[(size_t)(i - 1) * nv + j];
+		else fin >> rad[(size_t)i * nv + j];
+		if(max_rad < rad[(size_t)i * nv + j]) max_rad = rad[(size_t)i * nv + j];
+	}
+	max_rad = 1.f / max_rad;
+	d.cdf_offset = (int)tab.size(); d.cdf_count = nv + 1 + nh + 1 + nh * nv;
+	d.ies_nv = nv; d.ies_nh = nh; d.ies_type = type; d.ies_max_rad = max_rad;
+	tab.insert(tab.end(), vert.begin(), vert.end()); tab.push_back(std::numeric_limits<float>::infinity());
+	tab.insert(tab.end(), hor.begin(), hor.end()); tab.push_back(-std::numeric_limits<float>::infinity());
+	tab.insert(tab.end(), rad.begin(), rad.end());
+	// constructor: ndir_ = (from - to).normalize(), dir_ = -ndir_, createCs__(dir_, du_, dv_), cos_end_ = fCos__(max vertical angle), color_ = col * power
+	const V3 from = ld3(l.from), to = ld3(l.point1);
+	const V3 ndir = normalize(from - to), dir = -ndir;
+	V3 du, dv;
+	createCs(dir, du, dv);
+	d.cos_angle = fCos(max_v);
+	for(int k = 0; k < 3; ++k) d.color[k] = l.color[k] * l.power;
+	cp3(d.pos, l.from); st3(d.fnormal, ndir); st3(d.normal, dir); st3(d.du, du); st3(d.dv, dv);
+	d.dirac = !l.soft_shadows; d.can_intersect = 0;
+	return true;
+}
+
 inline void buildMeshLightTables(const yafgpu_geometry &g, const yafgpu_object &o, LightDev &d, std::vector<float> &tab)
 {
 	const int n = o.n_tris;

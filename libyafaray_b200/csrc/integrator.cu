@@ -475,7 +475,7 @@ YG_DLE void doLightEstimation(const ShadeCtx &cx, const MatDev &m, int slot, con
 	if(lightIsDirac(L))
 	{
 		Col lcol; V3 ldir; float tmax;
-		if(lightIlluminate(L, sp, lcol, ldir, tmax))
+		if(lightIlluminate(sc, L, sp, lcol, ldir, tmax))
 		{
 			const float angle = m.flat ? 1.f : fabsf(dot(sp.n, ldir));
 			const Col surf_col = matEval<MT>(sc, m, sp, wo, ldir, BsdfAll);

@@ -215,9 +215,46 @@ YG_D bool spotFalloff(const LightDev &L, float cosa, float &v, bool &full)
 	return true;
 }
 
+// IesLight::getAngles light_ies.cc:52-63 (u from the WORLD z of the direction, as the reference has it) and IesData::getRadiance util_ies.h:67-128.
+// Table layout at L.cdf_offset: vert angles [nv], +INF, hor angles [nh], -INF, rad_map [nh][nv] (host_prep.h buildIesTables explains the -INF).
+YG_D float iesRadiance(const float *__restrict__ tab, const LightDev &L, V3 dir, float costheta)
+{
+	float u = (dir.z >= 1.f) ? 0.f : (float)((double)fAcos(dir.z) * 57.29577951308232087684636);
+	if(dir.y < 0) u = 360.f - u;
+	const float v = (costheta >= 1.f) ? 0.f : (float)((double)fAcos(costheta) * 57.29577951308232087684636);
+	const int nv = L.ies_nv, nh = L.ies_nh;
+	const float *vert = tab + L.cdf_offset, *hor = vert + nv + 1, *rad = hor + nh + 1;
+	float ang_1, ang_2;
+	if(L.ies_type == 1) { ang_1 = u; ang_2 = v; }
+	else
+	{
+		ang_1 = v; ang_2 = u;
+		if(L.ies_type == 2) { ang_1 += 90; if(ang_1 > 360.f) ang_1 -= 360.f; }
+	}
+	if(ang_1 > 180.f && hor[nh - 1] <= 180.f) ang_1 = 360.f - ang_1;
+	if(ang_1 > 90.f && hor[nh - 1] <= 90.f) ang_1 -= 90.f;
+	if(ang_2 > 90.f && vert[nv - 1] <= 90.f) ang_2 -= 90.f;
+	int x = 0, y = 0;
+	for(int i = 0; i < nh; i++) if(hor[i] <= ang_1 && hor[i + 1] > ang_1) x = i;
+	for(int i = 0; i < nv; i++) if(vert[i] <= ang_2 && vert[i + 1] > ang_2) { y = i; break; }
+	float r;
+	if(ang_1 == hor[x] && ang_2 == vert[y]) r = rad[x * nv + y];
+	else
+	{
+		// a horizontal angle at or beyond the last map entry leaves x at 0 and extrapolates, as the reference does; a vertical one keeps the last cell
+		const int x_2 = x + 1 < nh ? x + 1 : x, y_2 = y + 1 < nv ? y + 1 : y;
+		const float d_x = x_2 == x ? 0.f : (ang_1 - hor[x]) / (hor[x_2] - hor[x]);
+		const float d_y = y_2 == y ? 0.f : (ang_2 - vert[y]) / (vert[y_2] - vert[y]);
+		const float rx_1 = ((1.f - d_x) * rad[x * nv + y]) + (d_x * rad[x_2 * nv + y]);
+		const float rx_2 = ((1.f - d_x) * rad[x * nv + y_2]) + (d_x * rad[x_2 * nv + y_2]);
+		r = ((1.f - d_y) * rx_1) + (d_y * rx_2);
+	}
+	return r * L.ies_max_rad;
+}
+
 // Light::illuminate of the dirac lights: PointLight light_point.cc:38-56, DirectionalLight light_directional.cc:59-81,
 // SpotLight (soft_shadows off) light_spot.cc:88-120
-YG_D bool lightIlluminate(const LightDev &L, const SurfPt &sp, Col &col, V3 &dir, float &tmax)
+YG_D bool lightIlluminate(const SceneDev &sc, const LightDev &L, const SurfPt &sp, Col &col, V3 &dir, float &tmax)
 {
 	if(L.photon_only) return false;
 	if(L.type == YAFGPU_LIGHT_DIRECTIONAL)
@@ -247,6 +284,14 @@ YG_D bool lightIlluminate(const LightDev &L, const SurfPt &sp, Col &col, V3 &dir
 		float v = 0.f; bool full = false;
 		if(!spotFalloff(L, dot(ldv(L.fnormal), ldir), v, full)) return false;
 		col = full ? ldc(L.color) * idist_sqr : ldc(L.color) * (v * idist_sqr);
+		tmax = dist; dir = ldir;
+		return true;
+	}
+	if(L.type == YAFGPU_LIGHT_IES) // IesLight::illuminate light_ies.cc:65-93
+	{
+		const float cosa = dot(ldv(L.fnormal), ldir);
+		if(cosa < L.cos_angle) return false;
+		col = (ldc(L.color) * iesRadiance(sc.light_tables, L, ldir, cosa)) * idist_sqr;
 		tmax = dist; dir = ldir;
 		return true;
 	}
@@ -351,6 +396,24 @@ YG_D bool lightIllumSample(const SceneDev &sc, const LightDev &L, const SurfPt &
 			col = full ? ldc(L.color) : ldc(L.color) * v;
 			pdf = dist_sqr;
 			if(pdf < 1.f) { pdf = 1.f; col = col / dist_sqr; }
+			return true;
+		}
+		case YAFGPU_LIGHT_IES: // IesLight::illumSample light_ies.cc:95-128 (soft_shadows on): a cone of half-angle acos(cosa) around the direction to the light
+		{
+			V3 ldir = ldv(L.pos) - sp.p;
+			const float dist_sqr = lengthSqr(ldir);
+			const float dist = fSqrt(dist_sqr);
+			const float idist_sqr = 1.f / dist_sqr;
+			if(dist == 0.0f) return false;
+			ldir = ldir * (1.f / dist);
+			const float cosa = dot(ldv(L.fnormal), ldir);
+			if(cosa < L.cos_angle) return false;
+			tmax = dist;
+			dir = sampleCone(ldir, ldv(L.du), ldv(L.dv), cosa, s1, s2);
+			const float r = iesRadiance(sc.light_tables, L, dir, cosa);
+			if(r == 0.f) return false;
+			col = ldc(L.color) * idist_sqr;
+			pdf = 1.f / r;
 			return true;
 		}
 		case YAFGPU_LIGHT_SPHERE: // SphereLight::illumSample light_sphere.cc:70-103

@@ -134,6 +134,7 @@ struct LightDev
 	float clamp_intersect; int shoot_caustic;
 	float power;        // background portal: colour = Background::eval(dir) * power_
 	int dirac, can_intersect;   // Light::diracLight() / canIntersect() (the spot light's depend on "soft_shadows")
+	int ies_nv, ies_nh, ies_type; float ies_max_rad; // ies: IesData (util_ies.h:33-56); tables at cdf_offset: vert angles [nv] -INF, hor angles [nh] -INF, rad_map [nh][nv]
 	// directional (pos = position_, fnormal = direction_, area = radius_, double_sided = !infinite_), spot (pos, fnormal = ndir_, normal = dir_,
 	// du/dv, cos_angle = cos_end_, pdf = cos_start_, invpdf = icos_diff_, area = shadow_fuzzy_), sphere (pos = center, area = radius^2,
 	// inv_area = radius^2 * 1.000003815)

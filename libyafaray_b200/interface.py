@@ -495,6 +495,13 @@ class Interface:
             l.type, l.from_, l.point1 = capi.LIGHT_SPOT, pt("from", (0, 0, 0)), pt("to", (0, 0, -1))
             l.cone_angle, l.blend = g(p, "cone_angle", 45.0), g(p, "blend", 0.15)
             l.soft_shadows, l.shadow_fuzzy, l.samples = int(g(p, "soft_shadows", False)), g(p, "shadowFuzzyness", 1.0), int(g(p, "samples", 8))
+        elif t == "ieslight":  # light_ies.cc:184-233; the library parses the file contents as IesData::parseIesFile does
+            l.type, l.from_, l.point1 = capi.LIGHT_IES, pt("from", (0, 0, 0)), pt("to", (0, 0, -1))
+            l.soft_shadows, l.samples = int(g(p, "soft_shadows", False)), int(g(p, "samples", 16))
+            with open(g(p, "file", ""), "rb") as fh:   # a missing file: the reference's factory returns no light and the scene load fails
+                data = fh.read()
+            self._ies_keep.append(data)
+            l.ies_data, l.ies_size = data, len(data)
         elif t == "spherelight":  # light_sphere.cc:163-198
             l.type, l.from_, l.radius = capi.LIGHT_SPHERE, pt("from", (0, 0, 0)), g(p, "radius", 1.0)
             if int(g(p, "object", 0)) != 0:
@@ -633,7 +640,9 @@ class Interface:
 
         def obj_index_of_id(oid):
             return obj_index.get(oid, -1) if oid else -1
+        self._ies_keep = []
         lts = [self._light_record(p, obj_index_of_id) for p in self.lights.values()]
+        keep.append(self._ies_keep)
         larr = (capi.Light * max(1, len(lts)))(*lts)
         d.lights, d.n_lights = larr, len(lts)
         keep += [mats, objarr, larr]

@@ -570,3 +570,19 @@ def film_io_scene(aa_passes, film_save_load, width=32, height=18, inc=3):
 
 # three AA passes without adaptive threshold on computer node 3 with a base sampling offset
 EXACT["cornell_pt_3pass_node3"] = lambda: film_io_scene(3, "none")
+
+
+# ieslight (light_ies.cc, util_ies.h): synthetic photometric webs written by hand (tests/golden/*.ies) — a full-sphere type C web with nine
+# horizontal planes, and an axially symmetric downlight (one horizontal angle, TILT=INCLUDE block, 70 degree cut-off)
+IES_WEB = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden", "web_typeC.ies")
+IES_DOWN = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden", "downlight_axial.ies")
+EXACT["zoo_dl_ies"] = lambda: material_zoo_scene(96, 54, 2, extra_lights=[
+    {"type": "ieslight", "file": IES_WEB, "from": (-1.0, -1.5, 3.5), "to": (-0.6, 0.4, 0.0), "color": (1.0, 0.95, 0.85, 1.0), "power": 30.0},
+    {"type": "ieslight", "file": IES_DOWN, "from": (2.2, 0.5, 3.0), "to": (2.0, 0.8, 0.0), "color": (0.6, 0.8, 1.0, 1.0), "power": 25.0}], **_ZOO_DL)
+EXACT["zoo_dl_ies_soft"] = lambda: material_zoo_scene(96, 54, 2, extra_lights=[
+    {"type": "ieslight", "file": IES_WEB, "from": (0.5, -2.0, 4.0), "to": (0.2, 0.5, 0.0), "soft_shadows": True, "samples": 3, "color": (1.0, 0.9, 0.8, 1.0), "power": 30.0}], **_ZOO_DL)
+# path tracing picks ONE light per vertex from a schedule-dependent counter (integrator_montecarlo.cc:62-76): exact parity needs a single light
+EXACT["zoo_pt_ies_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, meshlight=False, rr_min_bounces=99, extra_lights=[
+    {"type": "ieslight", "file": IES_WEB, "from": (-1.0, -2.0, 3.0), "to": (0.0, 0.0, 0.5), "soft_shadows": True, "samples": 2, "color": (0.9, 0.9, 1.0, 1.0), "power": 30.0}])
+EXACT["zoo_pt_ies_down_norr"] = lambda: material_zoo_scene(96, 54, 4, sun=False, ibl=False, meshlight=False, rr_min_bounces=99, extra_lights=[
+    {"type": "ieslight", "file": IES_DOWN, "from": (0.5, 0.0, 3.2), "to": (0.4, 0.3, 0.0), "color": (1.0, 0.9, 0.8, 1.0), "power": 30.0}])
