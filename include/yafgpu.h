@@ -116,7 +116,15 @@ typedef enum yafgpu_material_type
 /* ImageTexture, /root/reference/src/texture/texture_image.cc:560-720 (factory), :75-230 (getColor, doMapping), :231-375 (interpolation).
  * Texels are handed over as ImageHandler::getPixel(x, y) returns them — linear RGB float after the handler's colour-space
  * decode and texture "optimization" storage round trip — so no image codec lives on this side of the ABI. */
-typedef enum yafgpu_texture_type { YAFGPU_TEX_IMAGE = 0 } yafgpu_texture_type;
+typedef enum yafgpu_texture_type
+{
+	YAFGPU_TEX_IMAGE = 0,
+	YAFGPU_TEX_BLEND = 1,    /* "blend"    texture_basic.cc:680-779: a gradient of the texture point (blend_type, use_flip_axis); a colour ramp is refused.
+	                          * Its factory sets no adjustments. */
+	YAFGPU_TEX_RGB_CUBE = 2  /* "rgb_cube" texture_basic.cc:347-386: colour = the texture point clamped to [0,1]^3, with the adj_* adjustments */
+} yafgpu_texture_type;
+enum { YAFGPU_TEXBLEND_LINEAR = 0, YAFGPU_TEXBLEND_QUADRATIC = 1, YAFGPU_TEXBLEND_EASING = 2, YAFGPU_TEXBLEND_DIAGONAL = 3, YAFGPU_TEXBLEND_SPHERICAL = 4,
+       YAFGPU_TEXBLEND_QUADRATIC_SPHERE = 5, YAFGPU_TEXBLEND_RADIAL = 6 }; /* BlendTexture::ProgressionType ("stype" lin/quad/ease/diag/sphere/halo|quad_sphere/radial) */
 enum { YAFGPU_TEXINTERP_NONE = 0, YAFGPU_TEXINTERP_BILINEAR = 1, YAFGPU_TEXINTERP_BICUBIC = 2 }; /* "interpolate"; mipmap_* are refused */
 enum { YAFGPU_TEXCLIP_EXTEND = 0, YAFGPU_TEXCLIP_CLIP = 1, YAFGPU_TEXCLIP_CLIPCUBE = 2, YAFGPU_TEXCLIP_REPEAT = 3, YAFGPU_TEXCLIP_CHECKER = 4 }; /* ImageTexture::TexClipMode */
 enum { YAFGPU_CS_RAW_MANUAL_GAMMA = 1, YAFGPU_CS_LINEAR_RGB = 2, YAFGPU_CS_SRGB = 3, YAFGPU_CS_XYZ_D65 = 4 }; /* ColorSpace, include/common/color.h:33-39 */
@@ -137,10 +145,12 @@ typedef struct yafgpu_texture
 	int32_t normalmap;       /* "normalmap" */
 	int32_t color_space;     /* YAFGPU_CS_* the handler decoded from (HDR/EXR: linear); used by getRawColor to re-encode */
 	float gamma;             /* "gamma" */
-	float adj_intensity, adj_contrast, adj_saturation; /* "adj_intensity", "adj_contrast", "adj_saturation" */
+	float adj_intensity, adj_contrast, adj_saturation; /* "adj_intensity", "adj_contrast", "adj_saturation" (image, rgb_cube) */
 	float adj_hue;           /* "adj_hue" / 60.f in float, i.e. Texture::adj_hue_ as setAdjustments stores it (texture.h:154) */
 	float adj_mult_red, adj_mult_green, adj_mult_blue;
 	int32_t adj_clamp;       /* "adj_clamp" */
+	int32_t blend_type;      /* blend: YAFGPU_TEXBLEND_* */
+	int32_t use_flip_axis;   /* blend: "use_flip_axis" */
 } yafgpu_texture;
 
 typedef enum yafgpu_node_type

@@ -62,6 +62,7 @@
 #include "background/background.h"
 #include "background/background_texture.h"
 #include "texture/texture_image.h"
+#include "texture/texture_basic.h"
 #include "imagehandler/imagehandler.h"
 #include "integrator/integrator.h"
 #undef private
@@ -127,10 +128,25 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 {
 	auto f = pool.tex_index.find(t);
 	if(f != pool.tex_index.end()) { index = f->second; return true; }
-	const ImageTexture *it = dynamic_cast<const ImageTexture *>(t);
-	if(!it) { err = "only image textures are implemented on the device (procedural textures are not)"; return false; }
 	yafgpu_texture r;
 	memset(&r, 0, sizeof(r));
+	const BlendTexture *bt = dynamic_cast<const BlendTexture *>(t);
+	const RgbCubeTexture *ct = dynamic_cast<const RgbCubeTexture *>(t);
+	if(bt || ct)
+	{	// texture_basic.cc:680-779, 347-386: fields of the constructed objects
+		if(bt && bt->color_ramp_) { err = "a blend texture with a colour ramp is not implemented on the device"; return false; }
+		r.type = bt ? YAFGPU_TEX_BLEND : YAFGPU_TEX_RGB_CUBE;
+		if(bt) { r.blend_type = (int)bt->progression_type_; r.use_flip_axis = bt->use_flip_axis_; } // same enumerator order as YAFGPU_TEXBLEND_*
+		r.adj_intensity = t->adj_intensity_; r.adj_contrast = t->adj_contrast_; r.adj_saturation = t->adj_saturation_; r.adj_hue = t->adj_hue_;
+		r.adj_mult_red = t->adj_mult_factor_red_; r.adj_mult_green = t->adj_mult_factor_green_; r.adj_mult_blue = t->adj_mult_factor_blue_;
+		r.adj_clamp = t->adj_clamp_;
+		index = (int)pool.textures.size();
+		pool.textures.push_back(r);
+		pool.tex_index[t] = index;
+		return true;
+	}
+	const ImageTexture *it = dynamic_cast<const ImageTexture *>(t);
+	if(!it) { err = "this procedural texture type is not implemented on the device (image, blend and rgb_cube are)"; return false; }
 	r.type = YAFGPU_TEX_IMAGE;
 	ImageHandler *ih = it->image_;
 	r.width = ih->getWidth(); r.height = ih->getHeight();

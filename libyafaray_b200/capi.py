@@ -27,7 +27,8 @@ FILTERS = {"box": 0, "mitchell": 1, "gauss": 2, "lanczos": 3}
 INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
 FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES = 1, 2
-TEX_IMAGE = 0
+TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE = range(3)
+TEXBLEND = {"lin": 0, "quad": 1, "ease": 2, "diag": 3, "sphere": 4, "halo": 5, "quad_sphere": 5, "radial": 6}
 TEXINTERP = {"none": 0, "bilinear": 1, "bicubic": 2}
 TEXCLIP = {"extend": 0, "clip": 1, "clipcube": 2, "repeat": 3, "checker": 4}
 CS = {"Raw_Manual_Gamma": 1, "LinearRGB": 2, "sRGB": 3, "XYZ": 4}
@@ -102,7 +103,7 @@ class Texture(C.Structure):
                 ("checker_even", i32), ("checker_odd", i32), ("checker_dist", f32), ("normalmap", i32),
                 ("color_space", i32), ("gamma", f32), ("adj_intensity", f32), ("adj_contrast", f32),
                 ("adj_saturation", f32), ("adj_hue", f32), ("adj_mult_red", f32), ("adj_mult_green", f32),
-                ("adj_mult_blue", f32), ("adj_clamp", i32)]
+                ("adj_mult_blue", f32), ("adj_clamp", i32), ("blend_type", i32), ("use_flip_axis", i32)]
 
 
 class ShaderNode(C.Structure):

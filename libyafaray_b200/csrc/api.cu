@@ -344,6 +344,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	for(size_t i = 0; i < h_tex.size(); ++i)
 	{
 		float4 *d_px = nullptr;
+		if(h_tex[i].type != YAFGPU_TEX_IMAGE) { h_tex[i].tex = nullptr; continue; } // procedural: no texels
 		YG_CUDA(c, upload(d_px, (const float4 *)desc->textures[i].rgba, (size_t)h_tex[i].w * h_tex[i].h, st));
 		c->tex_ptrs.push_back(d_px);
 		h_tex[i].tex = d_px;

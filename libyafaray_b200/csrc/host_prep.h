@@ -189,10 +189,19 @@ inline unsigned triFlagsOf(const MatDev &d)
 inline bool prepTexture(const yafgpu_texture &t, TexDev &d, std::string &err)
 {
 	memset(&d, 0, sizeof(d));
-	if(t.type != YAFGPU_TEX_IMAGE) { err = "texture type " + std::to_string(t.type) + " is not implemented on the device"; return false; }
+	d.type = t.type;
+	if(t.type == YAFGPU_TEX_BLEND)
+	{	// BlendTexture::factory texture_basic.cc:759-776: setAdjustments is called with the neutral values, whatever the parameters say
+		if(t.blend_type < YAFGPU_TEXBLEND_LINEAR || t.blend_type > YAFGPU_TEXBLEND_RADIAL) { err = "blend texture: progression type"; return false; }
+		d.blend_type = t.blend_type; d.flip = t.use_flip_axis ? 1 : 0;
+		d.adj_intensity = d.adj_contrast = d.adj_saturation = 1.f; d.adj_mult[0] = d.adj_mult[1] = d.adj_mult[2] = 1.f;
+		return true;
+	}
+	if(t.type != YAFGPU_TEX_IMAGE && t.type != YAFGPU_TEX_RGB_CUBE) { err = "texture type " + std::to_string(t.type) + " is not implemented on the device"; return false; }
+	if(t.type == YAFGPU_TEX_IMAGE)
 	if(!t.rgba || t.width <= 0 || t.height <= 0) { err = "image texture without texels"; return false; }
-	if(t.interpolate < YAFGPU_TEXINTERP_NONE || t.interpolate > YAFGPU_TEXINTERP_BICUBIC) { err = "texture interpolation (mipmap_trilinear / mipmap_ewa need ray differentials) is not implemented on the device"; return false; }
-	if(t.clip_mode < YAFGPU_TEXCLIP_EXTEND || t.clip_mode > YAFGPU_TEXCLIP_CHECKER) { err = "texture clip mode"; return false; }
+	if(t.type == YAFGPU_TEX_IMAGE && (t.interpolate < YAFGPU_TEXINTERP_NONE || t.interpolate > YAFGPU_TEXINTERP_BICUBIC)) { err = "texture interpolation (mipmap_trilinear / mipmap_ewa need ray differentials) is not implemented on the device"; return false; }
+	if(t.type == YAFGPU_TEX_IMAGE && (t.clip_mode < YAFGPU_TEXCLIP_EXTEND || t.clip_mode > YAFGPU_TEXCLIP_CHECKER)) { err = "texture clip mode"; return false; }
 	d.w = t.width; d.h = t.height; d.interp = t.interpolate; d.clip = t.clip_mode;
 	d.xrepeat = t.xrepeat; d.yrepeat = t.yrepeat; d.mirror_x = t.mirror_x ? 1 : 0; d.mirror_y = t.mirror_y ? 1 : 0; d.rot90 = t.rot90 ? 1 : 0;
 	// setCrop :224-229
@@ -272,13 +281,15 @@ inline bool prepNodes(const yafgpu_material &m, const yafgpu_scene_desc &sd, con
 		{	// TextureMapperNode::factory :344-420 and setup() :33-55
 			if(q.texture < 0 || (size_t)q.texture >= tex.size()) { err = "texture_mapper: texture index out of range"; return false; }
 			const TexDev &t = tex[q.texture];
-			o.tex = q.texture; o.coords = q.texco; o.proj = q.mapping; // image textures are discrete(): the "mapping" is honoured
+			o.tex = q.texture; o.coords = q.texco; o.discrete = t.type == YAFGPU_TEX_IMAGE;
+			o.proj = o.discrete ? q.mapping : YAFGPU_TEXPROJ_PLAIN; // the factory honours "mapping" for discrete() textures only (shader_node_basic.cc:381)
 			if(q.texco < 0 || q.texco > YAFGPU_TEXCO_TANGENT || q.mapping < 0 || q.mapping > YAFGPU_TEXPROJ_SPHERE) { err = "texture_mapper: texco / mapping"; return false; }
 			o.map_x = std::min(3, std::max(0, q.proj_x)); o.map_y = std::min(3, std::max(0, q.proj_y)); o.map_z = std::min(3, std::max(0, q.proj_z));
 			for(int k = 0; k < 3; ++k) { o.scale[k] = q.scale[k]; o.offset[k] = 2 * q.offset[k]; }
 			o.do_scalar = q.do_scalar ? 1 : 0;
 			for(int k = 0; k < 12; ++k) o.mtx[k] = q.transform[k];
-			o.d_u = 1.f / (float)t.w; o.d_v = 1.f / (float)t.h;
+			if(o.discrete) { o.d_u = 1.f / (float)t.w; o.d_v = 1.f / (float)t.h; }
+			else o.d_u = o.d_v = 0.0002f;
 			o.bump_str = q.bump_strength / length(mk(o.scale[0], o.scale[1], o.scale[2]));
 			if(!t.normalmap) o.bump_str /= 100.0f;
 		}

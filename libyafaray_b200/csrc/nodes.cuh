@@ -290,17 +290,62 @@ YG_D Rgba4 imgInterpolate(const TexDev &t, float px, float py)
 	return ((w11 * c11 + w12 * c12) + w21 * c21) + w22 * c22;
 }
 
-// ImageTexture::getColor(Point3) :75-87
+// BlendTexture::getFloat texture_basic.cc:698-751 (its factory leaves the adjustments unset)
+YG_D float blendTexFloat(const TexDev &t, V3 p)
+{
+	float blend = 0.f;
+	const float coord_1 = t.flip ? p.y : p.x, coord_2 = t.flip ? p.x : p.y;
+	switch(t.blend_type)
+	{
+		case YAFGPU_TEXBLEND_QUADRATIC:
+			blend = 0.5f * (coord_1 + 1.f);
+			if(blend < 0.f) blend = 0.f; else blend *= blend;
+			break;
+		case YAFGPU_TEXBLEND_EASING:
+			blend = 0.5f * (coord_1 + 1.f);
+			if(blend <= 0.f) blend = 0.f;
+			else if(blend >= 1.f) blend = 1.f;
+			else blend = (3.f * blend * blend - 2.f * blend * blend * blend);
+			break;
+		case YAFGPU_TEXBLEND_DIAGONAL: blend = 0.25f * (2.f + coord_1 + coord_2); break;
+		case YAFGPU_TEXBLEND_SPHERICAL: case YAFGPU_TEXBLEND_QUADRATIC_SPHERE:
+			blend = 1.f - fSqrt(coord_1 * coord_1 + coord_2 * coord_2 + p.z * p.z);
+			if(blend < 0.f) blend = 0.f;
+			if(t.blend_type == YAFGPU_TEXBLEND_QUADRATIC_SPHERE) blend *= blend;
+			break;
+		case YAFGPU_TEXBLEND_RADIAL: blend = (atan2f(coord_2, coord_1) / (float)(2.f * 3.14159265358979323846) + 0.5f); break;
+		default: blend = 0.5f * (coord_1 + 1.f); break;
+	}
+	return fmaxf(0.f, fminf(blend, 1.f));
+}
+
+// ImageTexture::getColor(Point3) :75-87; BlendTexture::getColor texture_basic.cc:753-757 (no colour ramp); RgbCubeTexture::getColor :347-354
 YG_D Rgba4 texGetColor(const TexDev &t, V3 p)
 {
+	if(t.type == YAFGPU_TEX_BLEND) { const float f = blendTexFloat(t, p); return mk4(f, f, f, 1.f); }
+	if(t.type == YAFGPU_TEX_RGB_CUBE)
+	{
+		Rgba4 c = mk4(fmaxf(0.f, fminf(1.f, p.x)), fmaxf(0.f, fminf(1.f, p.y)), fmaxf(0.f, fminf(1.f, p.z)), 1.f);
+		return t.adj_set ? texAdjust(t, c) : c;
+	}
 	float x = p.x, y = -p.y, z = p.z;
 	if(imgDoMapping(t, x, y, z)) return mk4(0.f, 0.f, 0.f, 0.f);
 	return texAdjust(t, imgInterpolate(t, x, y));
 }
 // ImageTexture::getRawColor(Point3) :89-103
-YG_D Rgba4 texGetRawColor(const TexDev &t, V3 p) { return colorSpaceFromLinear(texGetColor(t, p), t.color_space, t.gamma); }
-// Texture::getFloat texture.h:51
-YG_D float texGetFloat(const TexDev &t, V3 p) { return texAdjustFloat(t, col2Bri(texGetRawColor(t, p))); }
+YG_D Rgba4 texGetRawColor(const TexDev &t, V3 p)
+{
+	if(t.type != YAFGPU_TEX_IMAGE) return texGetColor(t, p); // Texture::getRawColor texture.h:48
+	return colorSpaceFromLinear(texGetColor(t, p), t.color_space, t.gamma);
+}
+// Texture::getFloat texture.h:51; RgbCubeTexture::getFloat texture_basic.cc:356-361 (Rgb::energy = (r + g + b) * 0.333333f)
+YG_D float texGetFloat(const TexDev &t, V3 p)
+{
+	if(t.type == YAFGPU_TEX_BLEND) return blendTexFloat(t, p);
+	if(t.type == YAFGPU_TEX_RGB_CUBE)
+		return texAdjustFloat(t, (fmaxf(0.f, fminf(1.f, p.x)) + fmaxf(0.f, fminf(1.f, p.y)) + fmaxf(0.f, fminf(1.f, p.z))) * 0.333333f);
+	return texAdjustFloat(t, col2Bri(texGetRawColor(t, p)));
+}
 
 // ---- TextureMapperNode ------------------------------------------------------------------------------------------------------
 // doMapping shader_node_basic.cc:122-152 with tubemap__/spheremap__/cubemap__ :57-113
@@ -393,14 +438,14 @@ YG_D NodeRes mapperEval(const SceneDev &sc, const NodeDev &nd, const SurfPt &sp,
 	r.f = nd.do_scalar ? texGetFloat(t, texpt) : 0.f;
 	return r;
 }
-// evalDerivative :241-342 (image textures: discrete() is true)
+// evalDerivative :241-342
 YG_D NodeRes mapperEvalDerivative(const SceneDev &sc, const NodeDev &nd, const SurfPt &sp, const SurfTex &sx)
 {
 	V3 texpt, ng;
 	float du = 0.0f, dv = 0.0f;
 	mapperGetCoords(sc.cam, nd, sp, sx, texpt, ng);
 	const TexDev &t = sc.textures[nd.tex];
-	if(sx.has_uv && nd.coords == YAFGPU_TEXCO_UV)
+	if(nd.discrete && sx.has_uv && nd.coords == YAFGPU_TEXCO_UV)
 	{
 		texpt = mapperDoMapping(nd, texpt, ng);
 		V3 norm;

@@ -101,6 +101,7 @@ struct TexDev
 	float cropminx, cropminy, cropmaxx, cropmaxy;
 	int checker_even, checker_odd; float checker_dist;
 	int normalmap, color_space; float gamma;
+	int type, blend_type, flip;  // yafgpu_texture_type; blend: progression type, use_flip_axis
 	int adj_set, adj_clamp; float adj_intensity, adj_contrast, adj_saturation, adj_hue, adj_mult[3]; // adj_hue already / 60 (texture.h:154)
 };
 
@@ -111,6 +112,7 @@ struct NodeDev
 	// texture mapper after setup() (shader_node_basic.cc:33-55): offset doubled, bump_str scaled, d_u/d_v = 1 / resolution
 	int tex, coords, proj, map_x, map_y, map_z, do_scalar;
 	float scale[3], offset[3], bump_str, d_u, d_v;
+	int discrete;                    // Texture::discrete(): image textures; procedural ones take the 3-D finite-difference bump (shader_node_basic.cc:240,320-338)
 	float mtx[12];
 	float col[4], col2[4], f1, f2;   // value: colour, scalar; mix: color1, color2, cfactor; layer: def_col, upper_col, def_val, upper_val
 	float colfac, valfac; unsigned texflag; int do_color, do_scalar_l, color_input, use_alpha;
@@ -134,7 +136,7 @@ struct LightDev
 	float clamp_intersect; int shoot_caustic;
 	float power;        // background portal: colour = Background::eval(dir) * power_
 	int dirac, can_intersect;   // Light::diracLight() / canIntersect() (the spot light's depend on "soft_shadows")
-	int ies_nv, ies_nh, ies_type; float ies_max_rad; // ies: IesData (util_ies.h:33-56); tables at cdf_offset: vert angles [nv] -INF, hor angles [nh] -INF, rad_map [nh][nv]
+	int ies_nv, ies_nh, ies_type; float ies_max_rad; // ies: IesData (util_ies.h:33-56); tables at cdf_offset: vert angles [nv] +INF, hor angles [nh] -INF, rad_map [nh][nv]
 	// directional (pos = position_, fnormal = direction_, area = radius_, double_sided = !infinite_), spot (pos, fnormal = ndir_, normal = dir_,
 	// du/dv, cos_angle = cos_end_, pdf = cos_start_, invpdf = icos_diff_, area = shadow_fuzzy_), sphere (pos = center, area = radius^2,
 	// inv_area = radius^2 * 1.000003815)

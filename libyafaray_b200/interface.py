@@ -424,8 +424,26 @@ class Interface:
         if name in self._tex_index:
             return self._tex_index[name]
         p, g = self.textures[name], self._g
-        if g(p, "type", "") != "image":
-            raise NotImplementedError("texture type '%s' (only image textures are implemented on the device)" % g(p, "type", ""))
+        ttype = g(p, "type", "")
+        if ttype in ("blend", "rgb_cube"):   # texture_basic.cc:759-776, 363-386
+            t = capi.Texture()
+            t.adj_intensity = t.adj_contrast = t.adj_saturation = t.adj_mult_red = t.adj_mult_green = t.adj_mult_blue = 1.0
+            if ttype == "blend":
+                if g(p, "use_color_ramp", False):
+                    raise NotImplementedError("blend texture with a colour ramp is not implemented on the device")
+                t.type, t.blend_type = capi.TEX_BLEND, capi.TEXBLEND.get(g(p, "stype", ""), 0)   # unknown strings: linear
+                t.use_flip_axis = int(g(p, "use_flip_axis", False))
+            else:
+                t.type = capi.TEX_RGB_CUBE
+                t.adj_intensity, t.adj_contrast = g(p, "adj_intensity", 1.0), g(p, "adj_contrast", 1.0)
+                t.adj_saturation, t.adj_hue = g(p, "adj_saturation", 1.0), float(np.float32(g(p, "adj_hue", 0.0)) / np.float32(60.0))
+                t.adj_mult_red, t.adj_mult_green, t.adj_mult_blue = g(p, "adj_mult_factor_red", 1.0), g(p, "adj_mult_factor_green", 1.0), g(p, "adj_mult_factor_blue", 1.0)
+                t.adj_clamp = int(g(p, "adj_clamp", False))
+            self._tex_index[name] = len(self._texs)
+            self._texs.append(t)
+            return self._tex_index[name]
+        if ttype != "image":
+            raise NotImplementedError("texture type '%s' (image, blend and rgb_cube textures are implemented on the device)" % ttype)
         fn = g(p, "filename", "")
         if isinstance(fn, str) and fn.lower().endswith(".hdr"):
             rgb = read_radiance_hdr(fn)   # HDR: always linear, never "optimized" (texture_image.cc:600-606)

@@ -304,6 +304,9 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
         _textured_shinydiffuse_materials(y, sd, node, mapper, layer, modes, variant)
         _textured_mask_materials(y, sd, node, mapper, layer)
         box_mats = (("mb0", True, False), ("mb1", False, False), ("b2", True, False), ("mb3", True, False), ("b4", True, False), ("b5", False, True))
+    elif variant == "procedural":
+        _textured_procedural_materials(y, sd, node, mapper, layer)
+        box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     elif variant == "materials":
         _textured_other_materials(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
@@ -312,6 +315,55 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, integ)
     return y
+
+
+def _textured_procedural_materials(y, sd, node, mapper, layer):
+    """The procedural textures without a noise basis: "blend" (all seven progressions, flipped axis) and "rgb_cube" (with adjustments), read through
+    colour layers, scalar layers and as bump maps (the three-dimensional finite-difference branch of TextureMapperNode::evalDerivative)."""
+    def tex(name, typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ); _set_params(y, kw); y.createTexture(name)
+    for st in ("lin", "quad", "ease", "diag", "sphere", "halo", "radial"):
+        tex("p_" + st, "blend", stype=st)
+    tex("p_flip", "blend", stype="diag", use_flip_axis=True)
+    tex("p_cube", "rgb_cube")
+    tex("p_cube_adj", "rgb_cube", adj_intensity=1.1, adj_contrast=1.4, adj_saturation=0.7, adj_hue=25.0, adj_mult_factor_red=0.9, adj_mult_factor_blue=1.2, adj_clamp=True)
+    sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
+    layer("gl", "gm", mode=0, colfac=0.8, upper_color=(0.3, 0.5, 0.8, 1.0))
+    mapper("gm", texture="p_radial", texco="uv", mapping="cube", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0))   # "mapping" is ignored for procedurals
+    y.createMaterial("ground")
+    sd("b0", color=(0.9, 0.9, 0.9, 1.0), diffuse_shader="l0")
+    layer("l0", "m0", mode=0, colfac=0.9)
+    mapper("m0", texture="p_cube_adj", texco="orco", scale=(0.5, 0.5, 0.5), offset=(0.25, 0.25, 0.25))
+    y.createMaterial("b0")
+    sd("b1", color=(0.8, 0.6, 0.4, 1.0), specular_reflect=0.3, mirror_shader="l1s", diffuse_shader="l1c")
+    layer("l1s", "m1", do_color=False, do_scalar=True, color_input=False, def_val=0.6, upper_value=0.1)
+    layer("l1c", "m1b", mode=2, colfac=0.7, upper_color=(0.9, 0.8, 0.3, 1.0))
+    mapper("m1", texture="p_ease", texco="global", scale=(0.6, 0.6, 0.6))
+    mapper("m1b", texture="p_quad", texco="global", scale=(0.4, 0.4, 0.4), offset=(0.3, 0.0, 0.0))
+    y.createMaterial("b1")
+    sd("b2", color=(0.5, 0.8, 0.5, 1.0), transparency=0.1, transmit_filter=0.7, transparency_shader="l2t", diffuse_shader="l2b")
+    layer("l2t", "m2", do_color=False, do_scalar=True, color_input=True, def_val=0.5, upper_value=0.0)
+    layer("l2b", "m2b", mode=0, colfac=0.8)
+    mapper("m2", texture="p_sphere", texco="orco")
+    mapper("m2b", texture="p_cube", texco="orco", scale=(0.5, 0.5, 0.5), offset=(0.25, 0.25, 0.25))
+    y.createMaterial("b2")
+    sd("b3", color=(0.8, 0.8, 0.8, 1.0), diffuse_shader="x3")
+    node(type="mix", name="x3", input1="m3", input2="m3b", value=0.5, mode=0)
+    mapper("m3", texture="p_halo", texco="orco", scale=(0.8, 0.8, 0.8))
+    mapper("m3b", texture="p_flip", texco="orco")
+    y.createMaterial("b3")
+    sd("b4", color=(0.7, 0.7, 0.9, 1.0), specular_reflect=0.15, bump_shader="l4b", diffuse_shader="l4c")
+    layer("l4b", "m4", do_color=False, do_scalar=True, color_input=False)
+    layer("l4c", "m4c", mode=0, colfac=0.5, upper_color=(0.9, 0.4, 0.3, 1.0))
+    mapper("m4", texture="p_sphere", texco="orco", scale=(1.5, 1.5, 1.5), bump_strength=3.0)
+    mapper("m4c", texture="p_lin", texco="orco")
+    y.createMaterial("b4")
+    sd("b5", color=(0.9, 0.8, 0.6, 1.0), bump_shader="l5b", diffuse_shader="l5c")
+    layer("l5b", "m5", do_color=False, do_scalar=True, color_input=False)
+    layer("l5c", "m5c", mode=0, colfac=0.8)
+    mapper("m5", texture="p_halo", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0), bump_strength=2.0)   # uv coordinates, yet the non-discrete bump branch
+    mapper("m5c", texture="p_diag", texco="uv")
+    y.createMaterial("b5")
 
 
 def _textured_mask_materials(y, sd, node, mapper, layer):
@@ -551,6 +603,8 @@ EXACT["tex_pt_norr"] = lambda: textured_scene(96, 54, 4, integrator="pathtracing
 EXACT["tex_dl_camera_coords"] = lambda: textured_scene(96, 54, 2, variant="camera_coords")
 EXACT["tex_dl_mask"] = lambda: textured_scene(96, 54, 2, variant="mask", raydepth=4)
 EXACT["tex_pt_mask_norr"] = lambda: textured_scene(96, 54, 4, variant="mask", integrator="pathtracing", raydepth=4)
+EXACT["tex_dl_procedural"] = lambda: textured_scene(96, 54, 2, variant="procedural")
+EXACT["tex_pt_procedural_norr"] = lambda: textured_scene(96, 54, 4, variant="procedural", integrator="pathtracing")
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)
 
