@@ -568,8 +568,9 @@ int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
 int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
 
 /* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^23, limited to a quarter of the free device memory),
- * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "ray_regeneration" (1: the wavefront
- * traversal kernels use the warp-persistent schedule with ray regeneration that yafgpu_trace always uses; default 0),
+ * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "ray_regeneration" (the wavefront traversal kernels use the
+ * warp-persistent schedule with ray regeneration that yafgpu_trace always uses: 0 = off, 1 = both kernels, 2 = closest-hit kernel only, 3 = shadow kernel only;
+ * default -1 = the closest-hit kernel when the scene has at most 4096 triangles),
  * "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3). */
 int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);
 int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);

@@ -546,7 +546,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	const std::string n(name);
 	if(n == "wave_size") { if(value < 1024 || value > (1 << 24)) return setErr(c, YAFGPU_ERR_INVALID, "wave_size out of range"); c->wave_cap_override = (int)value; return YAFGPU_OK; }
 	if(n == "leaf_size") { if(value < 1 || value > 8) return setErr(c, YAFGPU_ERR_INVALID, "leaf_size must be 1..8"); c->leaf_max = (int)value; return YAFGPU_OK; }
-	if(n == "ray_regeneration") { c->ray_regeneration = value != 0; return YAFGPU_OK; }
+	if(n == "ray_regeneration") { if(value < -1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "ray_regeneration: -1..3"); c->ray_regeneration = value; return YAFGPU_OK; }
 	if(n == "shade_streams") { if(value < 1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "shade_streams must be 1..3"); c->shade_streams = (int)value; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);

@@ -49,7 +49,7 @@ struct yafgpu_ctx
 	// stats
 	yafgpu_stats stats;
 	int leaf_max = 1;                         // yafgpu_set_option("leaf_size"): BVH leaf collapse threshold used by the NEXT upload
-	int ray_regeneration = 0;                 // yafgpu_set_option("ray_regeneration"): wavefront trace kernels use the warp-persistent traversal
+	int ray_regeneration = -1;                // yafgpu_set_option("ray_regeneration"): wavefront trace kernels use the warp-persistent traversal
 	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -1042,7 +1042,10 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 {
 	Wavefront &w = c->wf;
 	cudaStream_t st = c->stream;
-	const bool count = (c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL) != 0, regen = c->ray_regeneration != 0;
+	const bool count = (c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL) != 0, regen_s = c->ray_regeneration == 1 || c->ray_regeneration == 3;
+	// auto (-1): the closest-hit kernel regenerates rays when the whole BVH is cache resident — there lane divergence (12.5 of 32 lanes per instruction
+	// on the Cornell bench), not memory coherence, is what limits it: +1.8 % on the bench, neutral at 10^7 triangles, -6 % on config 4 (profiles/r1n_regen_ab.log)
+	const bool regen_t = c->ray_regeneration >= 0 ? (c->ray_regeneration == 1 || c->ray_regeneration == 2) : c->scene.accel.n_tris <= 4096;
 	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
 	YG_CUDA(c, cudaMemsetAsync(w.ctl, 0, sizeof(WaveCtl), st));
 	YG_CUDA(c, cudaMemsetAsync(w.acc, 0, sizeof(float4) * (size_t)wp.n_slots, st));
@@ -1064,7 +1067,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		cudaMemsetAsync(w.hist, 0, sizeof(int) * nb, st);
 		const size_t hist_smem = nb <= YG_SHARED_BUCKETS ? sizeof(int) * nb : 0;
 #define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, hist_smem, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], c->d_counters)
-		if(count) { if(regen) YG_TRACE(true, true); else YG_TRACE(true, false); } else { if(regen) YG_TRACE(false, true); else YG_TRACE(false, false); }
+		if(count) { if(regen_t) YG_TRACE(true, true); else YG_TRACE(true, false); } else { if(regen_t) YG_TRACE(false, true); else YG_TRACE(false, false); }
 #undef YG_TRACE
 		mark();
 		k_bin_scan<<<1, 1024, 0, st>>>(w.hist, w.hist + YG_MAX_BUCKETS, nb);
@@ -1092,7 +1095,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		if(n_str > 1) for(int k = 0; k < n_str - 1; ++k) { cudaEventRecord(c->ev_join[k], c->side[k]); cudaStreamWaitEvent(st, c->ev_join[k], 0); }
 		mark();
 #define YG_SHADOW(C, R) k_shadow<C, R><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, &w.ctl->fetch_shadow[it], c->d_counters)
-		if(count) { if(regen) YG_SHADOW(true, true); else YG_SHADOW(true, false); } else { if(regen) YG_SHADOW(false, true); else YG_SHADOW(false, false); }
+		if(count) { if(regen_s) YG_SHADOW(true, true); else YG_SHADOW(true, false); } else { if(regen_s) YG_SHADOW(false, true); else YG_SHADOW(false, false); }
 #undef YG_SHADOW
 		mark();
 		c->stats.kernel_launches += 4 + n_launch;

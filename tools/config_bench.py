@@ -61,6 +61,8 @@ def main():
     desc, keep = y.scene_desc()
     ctx = Context(local, capi.FLAG_TIME_STAGES)
     ctx.upload(desc, keep)
+    if "ray_regeneration" in cfg:   # A/B knob: python tools/config_bench.py c3 4 2 ray_regeneration=2
+        ctx.set_option("ray_regeneration", cfg["ray_regeneration"])
     st0 = ctx.stats()
     S = cfg["spp"] * world
     n_chunks = max(1, cfg["pass_spp"] // S)
