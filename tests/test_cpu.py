@@ -63,6 +63,37 @@ def test_interface_xml_and_descriptor():
     assert txt.count("<f ") == 36 and 'sval="pathtracing"' in txt
 
 
+def test_descriptor_of_ies_lights_and_procedural_textures():
+    """Host mirror only (no device call): an ieslight carries the file CONTENTS across the ABI, blend / rgb_cube textures carry their
+    factory parameters, mask_mat keeps only what its factory reads, and what the device refuses is refused here too."""
+    from libyafaray_b200 import capi
+    y = pc.EXACT["zoo_dl_ies_soft"]()
+    d, keep = y.scene_desc()
+    ies = [d.lights[i] for i in range(d.n_lights) if d.lights[i].type == capi.LIGHT_IES]
+    assert len(ies) == 1 and ies[0].soft_shadows == 1 and ies[0].samples == 3
+    data = open(pc.IES_WEB, "rb").read()
+    assert ies[0].ies_size == len(data) and C_string(ies[0].ies_data, ies[0].ies_size) == data
+    y = pc.EXACT["tex_dl_procedural"]()
+    d, keep = y.scene_desc()
+    tex = [d.textures[i] for i in range(d.n_textures)]
+    kinds = sorted((t.type, t.blend_type, t.use_flip_axis) for t in tex)
+    assert (capi.TEX_BLEND, capi.TEXBLEND["radial"], 0) in kinds and (capi.TEX_BLEND, capi.TEXBLEND["diag"], 1) in kinds
+    cube = [t for t in tex if t.type == capi.TEX_RGB_CUBE and t.adj_clamp]
+    assert len(cube) == 1 and abs(cube[0].adj_hue - 25.0 / 60.0) < 1e-6 and abs(cube[0].adj_contrast - 1.4) < 1e-6
+    y = pc.EXACT["tex_dl_mask"]()
+    d, keep = y.scene_desc()
+    masks = [d.materials[i] for i in range(d.n_materials) if d.materials[i].type == capi.MAT_MASK]
+    assert len(masks) == 3 and all(m.additional_depth == 0 and m.sampling_factor == 1.0 for m in masks)   # the factory reads neither
+    from libyafaray_b200.interface import Interface
+    z = Interface()
+    with pytest.raises(NotImplementedError):
+        z.addInstance(1, np.eye(4))
+
+
+def C_string(ptr, n):
+    return ctypes.string_at(ptr, n)
+
+
 def test_golden_fixtures_present_and_sane():
     for name in pc.EXACT:
         f = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
