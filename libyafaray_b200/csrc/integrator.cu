@@ -311,7 +311,8 @@ __global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int
 		__syncthreads();
 		io.bins.hist = s_hist;
 	}
-	if(REGEN) traversePersistent<false, COUNT>(acc, n, next, io, &tc);
+	// refill threshold 14 instead of 22: this schedule is only the default on cache-resident scenes, where the plateau is 8..16 (profiles/r1n_regen_ab.log)
+	if(REGEN) traversePersistent<false, COUNT>(acc, n, next, io, &tc, 14);
 	else
 	{
 		const int stride = gridDim.x * blockDim.x;
