@@ -24,6 +24,20 @@ int cudaErr(yafgpu_ctx *ctx, cudaError_t e, const char *what)
 	return setErr(ctx, YAFGPU_ERR_CUDA, std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what);
 }
 
+int faultCheck(yafgpu_ctx *c, bool fetch)
+{
+	if(fetch)
+	{
+		cudaError_t e = cudaMemcpyAsync(c->h_fault, c->d_fault, sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+		if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+		if(e != cudaSuccess) return cudaErr(c, e, "traversal fault word");
+	}
+	if(*c->h_fault == 0) return YAFGPU_OK;
+	*c->h_fault = 0;
+	cudaMemsetAsync(c->d_fault, 0, sizeof(int), c->stream);
+	return setErr(c, YAFGPU_ERR_CUDA, "BVH traversal stack overflow: a subtree was skipped, the result is discarded (tree deeper than the traversal stack)");
+}
+
 template<class T> static cudaError_t upload(T *&dst, const T *src, size_t n, cudaStream_t s)
 {
 	dst = nullptr;
@@ -140,6 +154,10 @@ int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags)
 	delete ft;
 	if(e == cudaSuccess) e = cudaMalloc(&c->d_counters, sizeof(unsigned long long) * CNT_N);
 	if(e == cudaSuccess) e = cudaMalloc(&c->d_fetch, sizeof(int));
+	if(e == cudaSuccess) e = cudaMalloc(&c->d_fault, sizeof(int));
+	if(e == cudaSuccess) e = cudaMemset(c->d_fault, 0, sizeof(int));
+	if(e == cudaSuccess) e = cudaMallocHost(&c->h_fault, sizeof(int));
+	if(e == cudaSuccess) *c->h_fault = 0;
 	if(e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * CNT_N);
 	if(e != cudaSuccess) { yafgpu_destroy(c); return cudaErr(nullptr, e, "context allocation"); }
 	*out = c;
@@ -155,7 +173,7 @@ void yafgpu_destroy(yafgpu_ctx *c)
 	if(c->stream) cudaStreamSynchronize(c->stream);
 	{ cudaMemPool_t pool = nullptr; if(cudaDeviceGetDefaultMemPool(&pool, c->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
 	freeWavefront(c);
-	cudaFree(c->d_faure); cudaFree(c->d_counters); cudaFree(c->d_fetch);
+	cudaFree(c->d_faure); cudaFree(c->d_counters); cudaFree(c->d_fetch); cudaFree(c->d_fault); if(c->h_fault) cudaFreeHost(c->h_fault);
 	for(cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
 	if(c->ev0) cudaEventDestroy(c->ev0);
 	if(c->ev1) cudaEventDestroy(c->ev1);
@@ -361,6 +379,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	cudaEventRecord(c->ev0, st);
 	Accel &a = s.accel;
 	a.n_tris = (int)g.n_tris;
+	a.fault = c->d_fault; a.stack_limit = c->stack_limit > 0 ? c->stack_limit : YG_STACK;
 	if(g.n_tris > 0)
 	{
 		BvhBuildInput bi; bi.n_tris = (int)g.n_tris; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx; bi.tri_mat = c->d_tri_mat;
@@ -392,7 +411,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		cudaError_t e2 = buildBvh(bi, bo, st);
 		if(e2 != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e2, "buildBvh (mesh light)"); }
 		Accel la; memset(&la, 0, sizeof(la));
-		la.nodes = bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root;
+		la.nodes = bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root; la.fault = c->d_fault; la.stack_limit = a.stack_limit;
 		c->light_bvh_ptrs.push_back(bo.nodes); c->light_bvh_ptrs.push_back(bo.tris);
 		ld.accel = (int)laccels.size();
 		laccels.push_back(la);
@@ -501,8 +520,7 @@ int yafgpu_sync(yafgpu_ctx *c)
 {
 	if(!c) return YAFGPU_ERR_INVALID;
 	YG_CUDA(c, cudaSetDevice(c->device));
-	YG_CUDA(c, cudaStreamSynchronize(c->stream));
-	return YAFGPU_OK;
+	return faultCheck(c, true);
 }
 
 int yafgpu_read_film(yafgpu_ctx *c, float *out)
@@ -548,6 +566,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	if(n == "leaf_size") { if(value < 1 || value > 8) return setErr(c, YAFGPU_ERR_INVALID, "leaf_size must be 1..8"); c->leaf_max = (int)value; return YAFGPU_OK; }
 	if(n == "ray_regeneration") { if(value < -1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "ray_regeneration: -1..3"); c->ray_regeneration = value; return YAFGPU_OK; }
 	if(n == "shade_streams") { if(value < 1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "shade_streams must be 1..3"); c->shade_streams = (int)value; return YAFGPU_OK; }
+	if(n == "debug_stack_limit") { if(value < 0 || value > YG_STACK) return setErr(c, YAFGPU_ERR_INVALID, "debug_stack_limit: 0..96"); c->stack_limit = (int)value; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);
 }

@@ -50,6 +50,8 @@ struct yafgpu_ctx
 	yafgpu_stats stats;
 	int leaf_max = 1;                         // yafgpu_set_option("leaf_size"): BVH leaf collapse threshold used by the NEXT upload
 	int ray_regeneration = -1;                // yafgpu_set_option("ray_regeneration"): wavefront trace kernels use the warp-persistent traversal
+	int *d_fault = nullptr, *h_fault = nullptr; // traversal-stack fault word (Accel::fault) and its pinned mirror
+	int stack_limit = 0;                      // yafgpu_set_option("debug_stack_limit"): 0 = YG_STACK
 	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -64,6 +66,7 @@ int setErr(yafgpu_ctx *ctx, int code, const std::string &msg);
 int cudaErr(yafgpu_ctx *ctx, cudaError_t e, const char *what);
 int renderPass(yafgpu_ctx *ctx, const yafgpu_pass_desc *pass); // integrator.cu
 void freeWavefront(yafgpu_ctx *ctx);
+int faultCheck(yafgpu_ctx *ctx, bool fetch); // api.cu: YAFGPU_ERR_CUDA when a traversal stack overflowed since the last check (fetch: copy the word first)
 }
 
 #define YG_CUDA(ctx, call) do { cudaError_t e__ = (call); if(e__ != cudaSuccess) return yg::cudaErr(ctx, e__, #call); } while(0)

@@ -830,7 +830,7 @@ __device__ bool traceShadowTransp(const SceneDev &sc, V3 o, V3 d, float tmin, fl
 			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, 0.f, dist, ta);
 			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, 0.f, dist, tb);
 			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-			if(ha && hb) { cur = ca; if(sp_ < YG_STACK) stack[sp_++] = cb; continue; }
+			if(ha && hb) { cur = ca; if(sp_ < acc.stack_limit) stack[sp_++] = cb; else stackFault(acc); continue; }
 			if(ha) { cur = ca; continue; }
 			if(hb) { cur = cb; continue; }
 		}
@@ -1105,7 +1105,9 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	c->stats.kernel_launches += 2;
 	YG_CUDA(c, cudaGetLastError());
 	YG_CUDA(c, cudaMemcpyAsync(w.h_ctl, w.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
+	YG_CUDA(c, cudaMemcpyAsync(c->h_fault, c->d_fault, sizeof(int), cudaMemcpyDeviceToHost, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
+	if(int rc = faultCheck(c, false)) return rc;
 	overflow = w.h_ctl->overflow != 0;
 	c->stats.waves++;
 	if(timed && !overflow)

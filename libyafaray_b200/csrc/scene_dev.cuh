@@ -33,6 +33,8 @@ struct Accel
 	int n_nodes, n_tris;
 	int root;          // encoded like a child (a 1-triangle scene has a leaf root)
 	float bmin[3], bmax[3]; // tree bound grown by 0.1 % as TriKdTree does (kdtree_triangle.cc:112-116)
+	int stack_limit;   // entries of the per-thread traversal stack in use (YG_STACK; lower only through the debug option that tests the fault path)
+	int *fault;        // device word raised by a traversal whose stack overflowed (traverse.cuh stackFault); owned by the context
 };
 
 // ---- shading data (global triangle order) ---------------------------------------------------------------------------

@@ -56,6 +56,11 @@ YG_D bool slab(float bx0, float by0, float bz0, float bx1, float by1, float bz1,
 
 struct TravCounters { unsigned long long nodes, tris; };
 
+// A traversal stack that is full cannot take the far child: the subtree would be skipped and the image silently wrong.  The entry is
+// still dropped (no memory is touched out of bounds) but the accelerator's fault word is raised; every host entry point that
+// synchronises (yafgpu_trace, yafgpu_render_pass, yafgpu_sync) reads it and fails with YAFGPU_ERR_CUDA instead of returning the result.
+YG_D void stackFault(const Accel &acc) { if(acc.fault) *acc.fault = 1; }
+
 // Closest hit. `dist` = ray.tmax < 0 ? inf : ray.tmax (scene.cc:900-901).
 template<bool COUNT>
 YG_D HitD traceClosest(const Accel &acc, const RayD &r, TravCounters *cnt)
@@ -83,7 +88,7 @@ YG_D HitD traceClosest(const Accel &acc, const RayD &r, TravCounters *cnt)
 			{
 				const bool a_first = ta <= tb;
 				cur = a_first ? ca : cb;
-				if(sp < YG_STACK) stack[sp++] = a_first ? cb : ca;
+				if(sp < acc.stack_limit) stack[sp++] = a_first ? cb : ca; else stackFault(acc);
 				continue;
 			}
 			if(ha) { cur = ca; continue; }
@@ -135,7 +140,7 @@ YG_D int traceShadow(const Accel &acc, const V3 o, const V3 d, float dist, TravC
 			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, 0.f, dist, ta);
 			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, 0.f, dist, tb);
 			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-			if(ha && hb) { cur = ca; if(sp < YG_STACK) stack[sp++] = cb; continue; }
+			if(ha && hb) { cur = ca; if(sp < acc.stack_limit) stack[sp++] = cb; else stackFault(acc); continue; }
 			if(ha) { cur = ca; continue; }
 			if(hb) { cur = cb; continue; }
 		}
@@ -238,7 +243,7 @@ __device__ __forceinline__ void traversePersistent(const Accel &acc, int n, int 
 				{
 					const bool a_first = ANYHIT ? true : (ta <= tb);
 					cur = a_first ? ca : cb;
-					if(sp < YG_STACK) stack[sp++] = a_first ? cb : ca;
+					if(sp < acc.stack_limit) stack[sp++] = a_first ? cb : ca; else stackFault(acc);
 				}
 				else if(ha) cur = ca;
 				else if(hb) cur = cb;

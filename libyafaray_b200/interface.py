@@ -195,61 +195,96 @@ class Interface:
         raise ValueError(t)
 
     def to_xml(self, path):
+        """Streams the scene to `path`.  Bulk meshes (addTriMeshArrays) are written in chunks, so a 10^7-triangle mesh costs no
+        more host memory than the arrays it is made of; floats are printed with 9 significant digits, which round-trips float32
+        through the reference's atof() -> float (import_xml.cc:92-121)."""
         if self.render_params is None:
             self.setRenderParams()
-        w = []
-        w.append('<?xml version="1.0"?>\n<scene type="%s">\n\n' % ("triangle" if self.scene_type == 0 else "universal"))
-        for name, p in self.textures.items():
-            w.append('<texture name="%s">\n' % name)
-            for k, tv in p.items(): w.append(self._xml_param(k, tv))
-            w.append("</texture>\n\n")
-        for name, (p, e) in self.materials.items():
-            w.append('<material name="%s">\n' % name)
-            for k, tv in p.items(): w.append(self._xml_param(k, tv))
-            for le in e:
-                w.append("\t<list_element>\n")
-                for k, tv in le.items(): w.append(self._xml_param(k, tv, "\t\t"))
-                w.append("\t</list_element>\n")
-            w.append("</material>\n\n")
-        for tag, table in (("light", self.lights), ("camera", self.cameras), ("background", self.backgrounds),
-                           ("integrator", self.integrators)):
-            for name, p in table.items():
-                w.append('<%s name="%s">\n' % (tag, name))
-                for k, tv in p.items(): w.append(self._xml_param(k, tv))
-                w.append("</%s>\n\n" % tag)
-        for oid in sorted(self.meshes):
-            m = self.meshes[oid]
-            if m.np_faces is not None:
-                raise NotImplementedError("bulk meshes are not exported to XML (use startTriMesh/addVertex for oracle scenes)")
-            nv = len(m.points) // 2 if m.has_orco else len(m.points)
-            w.append('<mesh id="%d" vertices="%d" faces="%d" has_orco="%s" has_uv="%s" type="%d" obj_pass_index="%d">\n'
-                     % (oid, nv, len(m.faces), "true" if m.has_orco else "false", "true" if m.has_uv else "false", m.type, m.pass_index))
-            for i in range(nv):
-                if m.has_orco:
-                    p, o = m.points[2 * i], m.points[2 * i + 1]
-                    w.append('\t<p x="%r" y="%r" z="%r" ox="%r" oy="%r" oz="%r"/>\n' % (p[0], p[1], p[2], o[0], o[1], o[2]))
-                else:
-                    p = m.points[i]
-                    w.append('\t<p x="%r" y="%r" z="%r"/>\n' % (p[0], p[1], p[2]))
-                if m.normals_exported:
-                    n = m.normals[i]
-                    w.append('\t<n x="%r" y="%r" z="%r"/>\n' % (n[0], n[1], n[2]))
-            for u, v in m.uvs:
-                w.append('\t<uv u="%r" v="%r"/>\n' % (u, v))
-            cur = None
-            for f, uv, mat in zip(m.faces, m.face_uv, m.face_mat):
-                if mat != cur:
-                    w.append('\t<set_material sval="%s"/>\n' % mat)
-                    cur = mat
-                if uv is None: w.append('\t<f a="%d" b="%d" c="%d"/>\n' % f)
-                else: w.append('\t<f a="%d" b="%d" c="%d" uv_a="%d" uv_b="%d" uv_c="%d"/>\n' % (f + uv))
-            w.append("</mesh>\n\n")
-        w.append("<render>\n")
-        for k, tv in self.render_params.items(): w.append(self._xml_param(k, tv))
-        w.append("</render>\n</scene>\n")
-        with open(path, "w") as fh:
-            fh.write("".join(w))
+        with open(path, "w", buffering=1 << 22) as fh:
+            w = fh.write
+            w('<?xml version="1.0"?>\n<scene type="%s">\n\n' % ("triangle" if self.scene_type == 0 else "universal"))
+            for name, p in self.textures.items():
+                w('<texture name="%s">\n' % name)
+                for k, tv in p.items(): w(self._xml_param(k, tv))
+                w("</texture>\n\n")
+            for name, (p, e) in self.materials.items():
+                w('<material name="%s">\n' % name)
+                for k, tv in p.items(): w(self._xml_param(k, tv))
+                for le in e:
+                    w("\t<list_element>\n")
+                    for k, tv in le.items(): w(self._xml_param(k, tv, "\t\t"))
+                    w("\t</list_element>\n")
+                w("</material>\n\n")
+            for tag, table in (("light", self.lights), ("camera", self.cameras), ("background", self.backgrounds),
+                               ("integrator", self.integrators)):
+                for name, p in table.items():
+                    w('<%s name="%s">\n' % (tag, name))
+                    for k, tv in p.items(): w(self._xml_param(k, tv))
+                    w("</%s>\n\n" % tag)
+            for oid in sorted(self.meshes):
+                m = self.meshes[oid]
+                if m.np_faces is not None:
+                    self._xml_bulk_mesh(w, oid, m)
+                    continue
+                nv = len(m.points) // 2 if m.has_orco else len(m.points)
+                w('<mesh id="%d" vertices="%d" faces="%d" has_orco="%s" has_uv="%s" type="%d" obj_pass_index="%d">\n'
+                  % (oid, nv, len(m.faces), "true" if m.has_orco else "false", "true" if m.has_uv else "false", m.type, m.pass_index))
+                for i in range(nv):
+                    if m.has_orco:
+                        p, o = m.points[2 * i], m.points[2 * i + 1]
+                        w('\t<p x="%r" y="%r" z="%r" ox="%r" oy="%r" oz="%r"/>\n' % (p[0], p[1], p[2], o[0], o[1], o[2]))
+                    else:
+                        p = m.points[i]
+                        w('\t<p x="%r" y="%r" z="%r"/>\n' % (p[0], p[1], p[2]))
+                    if m.normals_exported:
+                        n = m.normals[i]
+                        w('\t<n x="%r" y="%r" z="%r"/>\n' % (n[0], n[1], n[2]))
+                for u, v in m.uvs:
+                    w('\t<uv u="%r" v="%r"/>\n' % (u, v))
+                cur = None
+                for f, uv, mat in zip(m.faces, m.face_uv, m.face_mat):
+                    if mat != cur:
+                        w('\t<set_material sval="%s"/>\n' % mat)
+                        cur = mat
+                    if uv is None: w('\t<f a="%d" b="%d" c="%d"/>\n' % f)
+                    else: w('\t<f a="%d" b="%d" c="%d" uv_a="%d" uv_b="%d" uv_c="%d"/>\n' % (f + uv))
+                w("</mesh>\n\n")
+            w("<render>\n")
+            for k, tv in self.render_params.items(): w(self._xml_param(k, tv))
+            w("</render>\n</scene>\n")
         return path
+
+    @staticmethod
+    def _xml_bulk_mesh(w, oid, m, chunk=1 << 16):
+        """A mesh given as arrays, in the element order the reference's mesh state expects (import_xml.cc:401-416 opens it,
+        :550-630 reads `p` [+ `n` for the vertex just added, Scene::addNormal scene.cc:236-262], `set_material`, `f`)."""
+        P, F, N = m.np_points, m.np_faces, m.np_normals
+        nv, nt = len(P), len(F)
+        w('<mesh id="%d" vertices="%d" faces="%d" has_orco="false" has_uv="false" type="%d" obj_pass_index="%d">\n' % (oid, nv, nt, m.type, m.pass_index))
+        for s in range(0, nv, chunk):
+            if N is None:
+                w("".join(['\t<p x="%.9g" y="%.9g" z="%.9g"/>\n' % tuple(r) for r in P[s:s + chunk].tolist()]))
+            else:
+                rows = np.concatenate([P[s:s + chunk], N[s:s + chunk]], axis=1).tolist()
+                w("".join(['\t<p x="%.9g" y="%.9g" z="%.9g"/>\n\t<n x="%.9g" y="%.9g" z="%.9g"/>\n' % tuple(r) for r in rows]))
+        if isinstance(m.np_mat, str):
+            names, per_tri = [m.np_mat], np.zeros(nt, np.int32)
+        else:
+            names, per_tri = m.np_mat
+            per_tri = np.asarray(per_tri)
+        # runs of equal material: one <set_material> per run
+        starts = np.concatenate([[0], np.flatnonzero(per_tri[1:] != per_tri[:-1]) + 1, [nt]]) if nt else np.array([0, 0])
+        buf, pending = [], 0
+        for k in range(len(starts) - 1):
+            a, b = int(starts[k]), int(starts[k + 1])
+            if b <= a: continue
+            buf.append('\t<set_material sval="%s"/>\n' % names[int(per_tri[a])])
+            buf.extend(['\t<f a="%d" b="%d" c="%d"/>\n' % tuple(r) for r in F[a:b].tolist()])
+            pending += b - a
+            if pending >= chunk:
+                w("".join(buf)); buf, pending = [], 0
+        w("".join(buf))
+        w("</mesh>\n\n")
 
     # ---- flattening to the C ABI descriptor ----------------------------------------------------------------------
     @staticmethod

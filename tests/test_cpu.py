@@ -257,3 +257,69 @@ def test_reference_resumes_from_a_film_written_by_our_writer():
             finals.append(final)
     assert np.array_equal(finals[0], finals[1])
     assert not np.array_equal(finals[0], first) and finals[0][..., 4].min() > first[..., 4].max() * 2
+
+
+@pytest.mark.skipif(ou.ref_bin() is None, reason="oracle not built")
+def test_mwc_restatement_matches_the_references_generator():
+    """tests/ray_sets.py draws the scale ray sets from a restatement of Random (util_mcqmc.h:173-190): pinned on the KAT dump."""
+    from tests import ray_sets as rs
+    with tempfile.TemporaryDirectory() as td:
+        p = os.path.join(td, "kat.bin")
+        subprocess.check_call([ou.ref_bin(), "kat", p], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        k = ou.read_kat(p)["random"]
+    for i, s in enumerate((0, 1, 123, (1804289383 + 123) & 0xffffffff)):
+        assert np.array_equal(k[64 * i:64 * i + 64], rs.mwc_stream(s, 64))
+        assert np.array_equal(k[64 * i:64 * i + 64], rs.mwc_reference_loop(s, 64))
+
+
+@pytest.mark.skipif(ou.ref_bin() is None, reason="oracle not built")
+def test_bulk_mesh_xml_export_reaches_the_references_loader():
+    """addTriMeshArrays meshes are streamed to XML (to_xml) and load through the reference's unchanged mesh state
+    (import_xml.cc:401-416,550-630): same triangle count, float32 coordinates survive the text round trip (the hits of a ray set
+    equal those of the same mesh entered vertex by vertex), per-triangle material runs become <set_material> elements."""
+    from libyafaray_b200 import scenes
+    from libyafaray_b200.interface import Interface
+    y = scenes.procedural_mesh(5000, 32, 18, 1, integrator="directlighting", mesh_lights=1, blend=True)
+    rays = pc.trace_rays(4096, (-10, -10, 0.5), (10, 10, 8), seed=4)
+    rays[:, 6] = -np.abs(rays[:, 6]) - 0.2
+    with tempfile.TemporaryDirectory() as td:
+        xml = y.to_xml(os.path.join(td, "s.xml"))
+        txt = open(xml).read()
+        assert txt.count("<set_material") > 10 and txt.count("<f a=") == sum(m.n_tris() for m in y.meshes.values())
+        assert txt.count("<n x=") == len(y.meshes[1].np_points)
+    h = ou.reference_hits(y, rays, 0)
+    assert (h["tri"] >= 0).mean() > 0.3
+    # the same geometry through startTriMesh/addVertex/addTriangle: identical hits
+    y2 = Interface()
+    y2.materials, y2.lights, y2.cameras, y2.backgrounds, y2.integrators = y.materials, y.lights, y.cameras, y.backgrounds, y.integrators
+    y2.render_params = y.render_params
+    y2.startGeometry()
+    for oid in sorted(y.meshes):
+        m = y.meshes[oid]
+        if m.np_faces is None:
+            y2.meshes[oid] = m
+            continue
+        names, per_tri = ([m.np_mat], np.zeros(len(m.np_faces), np.int32)) if isinstance(m.np_mat, str) else m.np_mat
+        y2.startTriMesh(oid, len(m.np_points), len(m.np_faces), False, False, 0)
+        for k, p in enumerate(m.np_points.tolist()):
+            y2.addVertex(*p)
+            if m.np_normals is not None:
+                y2.addNormal(*m.np_normals[k].tolist())
+        for f, t in zip(m.np_faces.tolist(), per_tri):
+            y2.addTriangle(f[0], f[1], f[2], names[int(t)])
+        y2.endTriMesh()
+    y2.endGeometry()
+    h2 = ou.reference_hits(y2, rays, 0)
+    assert np.array_equal(h.view(np.uint8), h2.view(np.uint8))
+
+
+def test_scale_golden_subsets_are_consistent_with_the_ray_generator():
+    """The committed subset of the reference's answers at 10^6 triangles belongs to the ray set the generator produces today."""
+    from tests import ray_sets as rs
+    z = np.load(os.path.join(ou.GOLDEN, "scale_hits_c4.npz"))
+    y = rs.scale_scene("c4")
+    rays = rs.scale_rays("c4", y)
+    assert len(rays) == 2 << 20 and np.isfinite(rays).all()
+    assert bytes(z["digest"]).decode() == rs.rays_digest(rays)
+    h = z["hits"].view(ou.HIT_DTYPE).reshape(-1)
+    assert len(h) == len(z["index"]) and 0.3 < (h["tri"] >= 0).mean() < 0.95
