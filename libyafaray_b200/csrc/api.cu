@@ -493,8 +493,10 @@ int yafgpu_trace(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_hit *hi
 	if(rc == YAFGPU_OK)
 	{
 		e = cudaMemcpyAsync(hits, d_h, n * sizeof(yafgpu_hit), cudaMemcpyDeviceToHost, c->stream);
+		if(e == cudaSuccess) e = cudaMemcpyAsync(c->h_fault, c->d_fault, sizeof(int), cudaMemcpyDeviceToHost, c->stream);
 		if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
 		if(e != cudaSuccess) rc = cudaErr(c, e, "D2H hits");
+		else rc = faultCheck(c, false);
 	}
 	poolFree(d_r, c->stream); poolFree(d_h, c->stream);
 	return rc;

@@ -181,3 +181,34 @@ def scale_reference_hits(name, iface, rays, allow_run=True):
     except OSError:
         pass
     return h, "live"
+
+
+def triangle_intersect_f32(points, faces, rays, tri):
+    """Triangle::intersect (/root/reference/include/common/triangle.h:223-259) restated on float32 numpy arrays with the reference's
+    operation order (no fused multiply-add): returns (ok, t, u, v) for ray i against triangle tri[i].  Used to certify that a
+    triangle the GPU reports is a hit under the reference's own arithmetic."""
+    f = np.float32
+    o, d = rays[:, 0:3].astype(f), rays[:, 4:7].astype(f)
+    a, b, c = (points[faces[tri][:, k]].astype(f) for k in range(3))
+    e1, e2 = b - a, c - a
+
+    def cross(x, y):
+        return np.stack([x[:, 1] * y[:, 2] - x[:, 2] * y[:, 1], x[:, 2] * y[:, 0] - x[:, 0] * y[:, 2], x[:, 0] * y[:, 1] - x[:, 1] * y[:, 0]], axis=1)
+
+    def dot(x, y):
+        return (x[:, 0] * y[:, 0] + x[:, 1] * y[:, 1]) + x[:, 2] * y[:, 2]
+
+    def length(x):
+        return np.sqrt(dot(x, x))
+    eps = ((np.float64(f(0.1)) * 0.00005) * np.maximum(length(e1), length(e2)).astype(np.float64)).astype(f)  # triangle.h:206
+    pvec = cross(d, e2)
+    det = dot(e1, pvec)
+    with np.errstate(all="ignore"):
+        inv = f(1.0) / det
+        tvec = o - a
+        u = dot(tvec, pvec) * inv
+        qvec = cross(tvec, e1)
+        v = dot(d, qvec) * inv
+        t = dot(e2, qvec) * inv
+    ok = ~((det > -eps) & (det < eps)) & ~((u < 0) | (u > 1)) & ~((v < 0) | ((u + v) > 1)) & ~(t < eps)
+    return ok, t, u, v

@@ -323,3 +323,18 @@ def test_scale_golden_subsets_are_consistent_with_the_ray_generator():
     assert bytes(z["digest"]).decode() == rs.rays_digest(rays)
     h = z["hits"].view(ou.HIT_DTYPE).reshape(-1)
     assert len(h) == len(z["index"]) and 0.3 < (h["tri"] >= 0).mean() < 0.95
+
+
+def test_triangle_intersect_restatement_reproduces_the_references_hits():
+    """tests/ray_sets.py triangle_intersect_f32 (the certificate behind the epsilon-tie rule of the scale tests) returns the reference's
+    own t,u,v bit for bit on every hit of the committed 10^6-triangle subset."""
+    from tests import ray_sets as rs
+    z = np.load(os.path.join(ou.GOLDEN, "scale_hits_c4.npz"))
+    y = rs.scale_scene("c4")
+    rays = rs.scale_rays("c4", y)[z["index"]]
+    h = z["hits"].view(ou.HIT_DTYPE).reshape(-1)
+    m = h["tri"] >= 0
+    ok, t, u, v = rs.triangle_intersect_f32(*rs.scene_triangles(y), rays[m], h["tri"][m])
+    assert ok.all() and m.sum() > 5000
+    for a, b in ((t, "t"), (u, "u"), (v, "v")):
+        assert np.array_equal(a.view(np.uint32), h[b][m].view(np.uint32)), b

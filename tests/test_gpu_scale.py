@@ -17,17 +17,40 @@ from tests import oracle_util as ou, ray_sets as rs  # noqa: E402
 pytestmark = pytest.mark.gpu
 
 
-def check_hits(g, h):
-    """Vectorised form of test_gpu._check_hits: ids equal except exact-t ties, t/u/v bit-equal where ids agree."""
+def check_hits(g, h, rays=None, geom=None, tag=None):
+    """Vectorised form of test_gpu._check_hits.  Ids must be equal except
+      * exact-t ties: both sides hit at bit-equal t (shared edge / coplanar faces; the kd-tree keeps the first triangle it visits,
+        the BVH the lower id), and
+      * epsilon ties (needs `rays` and `geom`): the ray crosses an edge shared by two triangles and both are hit, at distances one
+        or two ulps apart because each triangle computes t from its own edge vectors.  TriKdTree::intersect returns as soon as the
+        current leaf cell holds a hit (kdtree_triangle.cc:812-826), so it can keep the farther of the two; the BVH keeps the
+        nearer.  Accepted only when the GPU's t is the smaller one by at most 64 ulps (7.6e-6 relative; measured: 1-6), both hit
+        points lie within 1e-2 (barycentric) of a triangle edge, AND the GPU's triangle is certified as a hit with exactly that
+        t,u,v by the float32 restatement of Triangle::intersect (the reference's own test would accept it too).
+    t, u, v must be bit-equal wherever the ids agree.  Returns (exact ties, epsilon ties)."""
     same = g["tri"] == h["tri"]
     bad = ~same
     tie = bad & (g["tri"] >= 0) & (h["tri"] >= 0) & (g["t"].view(np.uint32) == h["t"].view(np.uint32))
-    not_tie = np.flatnonzero(bad & ~tie)
-    assert len(not_tie) == 0, (len(not_tie), not_tie[:8], g[not_tie[:8]], h[not_tie[:8]])
+    rest = np.flatnonzero(bad & ~tie)
+    n_eps = 0
+    if len(rest) and rays is not None:
+        P, F = geom
+        gi, hi = g[rest], h[rest]
+        both = (gi["tri"] >= 0) & (hi["tri"] >= 0)
+        ulps = hi["t"].view(np.int32).astype(np.int64) - gi["t"].view(np.int32).astype(np.int64)   # positive floats: ulp distance
+        ok, t, u, v = rs.triangle_intersect_f32(P, F, rays[rest], np.maximum(gi["tri"], 0))
+        certified = ok & (t.view(np.uint32) == gi["t"].view(np.uint32)) & (u.view(np.uint32) == gi["u"].view(np.uint32)) & (v.view(np.uint32) == gi["v"].view(np.uint32))
+        edge = lambda r: np.minimum(np.minimum(r["u"], r["v"]), 1.0 - r["u"] - r["v"]) < 1e-2
+        eps_tie = both & (ulps > 0) & (ulps <= 64) & certified & edge(gi) & edge(hi)
+        if tag and os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+            np.savez(os.path.join(ROOT, "gpurun_out", "hit_mismatch_%s.npz" % tag), index=rest, gpu=gi, ref=hi, ulps=ulps, certified=certified)
+        n_eps = int(eps_tie.sum())
+        rest = rest[~eps_tie]
+    assert len(rest) == 0, (len(rest), rest[:8], g[rest[:8]], h[rest[:8]])
     ok = same & (h["tri"] >= 0)
     for f in ("t", "u", "v"):
         assert np.array_equal(g[f][ok].view(np.uint32), h[f][ok].view(np.uint32)), f
-    return int(bad.sum())
+    return int(tie.sum()), n_eps
 
 
 @pytest.fixture(scope="module")
@@ -51,15 +74,16 @@ def test_closest_hit_ids_match_reference_at_scale(big_ctx, name):
     z = np.load(os.path.join(ou.GOLDEN, "scale_hits_%s.npz" % name))
     assert bytes(z["digest"]).decode() == rs.rays_digest(rays), "the fixed ray set changed: regenerate with tools/make_scale_hits.py"
     sub = z["index"]
-    check_hits(g[sub], z["hits"].view(ou.HIT_DTYPE).reshape(-1))
+    geom = rs.scene_triangles(y)
+    check_hits(g[sub], z["hits"].view(ou.HIT_DTYPE).reshape(-1), rays[sub], geom)
     h, how = rs.scale_reference_hits(name, y, rays)
     if h is None:
         pytest.skip("neither the cached reference answer nor the oracle binary is present; the committed subset passed")
-    ties = check_hits(g, h)
+    ties, eps_ties = check_hits(g, h, rays, geom, tag=name)
     n = len(rays) // 2
-    print("%s: %d rays, reference answer from %s, %d exact-t ties, hit fraction cam %.3f surf %.3f"
-          % (name, len(rays), how, ties, (h["tri"][:n] >= 0).mean(), (h["tri"][n:] >= 0).mean()))
-    assert ties <= len(rays) // 1000
+    print("%s: %d rays, reference answer from %s, %d exact-t ties, %d epsilon ties, hit fraction cam %.3f surf %.3f"
+          % (name, len(rays), how, ties, eps_ties, (h["tri"][:n] >= 0).mean(), (h["tri"][n:] >= 0).mean()))
+    assert ties <= len(rays) // 1000 and eps_ties <= len(rays) // 10000
     assert (h["tri"][:n] >= 0).mean() > 0.5 and (h["tri"][n:] >= 0).mean() > 0.05
 
 
