@@ -550,6 +550,17 @@ int yafgpu_scene_bound(yafgpu_ctx *ctx, float *bound6);
 int yafgpu_trace(yafgpu_ctx *ctx, const yafgpu_ray *rays, size_t n, yafgpu_hit *hits, int mode, int shadow_depth);
 /* Same with device pointers (no copies): for microbenchmarks that keep rays resident in HBM. */
 int yafgpu_trace_device(yafgpu_ctx *ctx, const void *d_rays, size_t n, void *d_hits, int mode, int shadow_depth);
+/* yafgpu_trace for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same results as yafgpu_trace
+ * for YAFGPU_TRACE_CLOSEST / YAFGPU_TRACE_SHADOW, but the device copies of `rays` and `hits` and the kernel's work counter live in
+ * a file-scope device array of the library (3 MiB + 256 B per GPU that loads it, held until the process exits) instead of the
+ * memory pool: the call performs no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library routine.
+ * At most YAFGPU_TRACE_STATIC_MAX_RAYS rays per call (more: YAFGPU_ERR_INVALID, nothing is traced).  All calls on one GPU share the
+ * array, which keeps the last call's contents; callers inside one process are serialised by the library, but work that overlaps on
+ * the GPU from elsewhere (another host process driving the same array is impossible, each has its own copy; a caller that bypasses this
+ * entry point is not) would race.  Synchronous like yafgpu_trace: returns with `hits` filled. */
+#define YAFGPU_TRACE_STATIC_MAX_RAYS 65536
+int yafgpu_trace_static(yafgpu_ctx *ctx, const yafgpu_ray *rays, size_t n, yafgpu_hit *hits, int mode);
 
 /* ImageFilm::init (imagefilm.cc:219-268): zero the film accumulators. */
 int yafgpu_film_clear(yafgpu_ctx *ctx);

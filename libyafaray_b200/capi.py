@@ -26,6 +26,7 @@ BG_NONE, BG_CONSTANT, BG_TEXTURE, BG_GRADIENT = range(4)
 FILTERS = {"box": 0, "mitchell": 1, "gauss": 2, "lanczos": 3}
 INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
+TRACE_STATIC_MAX_RAYS = 65536  # YAFGPU_TRACE_STATIC_MAX_RAYS
 FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES = 1, 2
 TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE = range(3)
 TEXBLEND = {"lin": 0, "quad": 1, "ease": 2, "diag": 3, "sphere": 4, "halo": 5, "quad_sphere": 5, "radial": 6}
@@ -186,6 +187,7 @@ SYMBOLS = {
     "yafgpu_scene_bound": (C.c_int, [C.c_void_p, pf]),
     "yafgpu_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
     "yafgpu_trace_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]),
+    "yafgpu_trace_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]),
     "yafgpu_film_clear": (C.c_int, [C.c_void_p]),
     "yafgpu_render_pass": (C.c_int, [C.c_void_p, C.POINTER(PassDesc)]),
     "yafgpu_sync": (C.c_int, [C.c_void_p]),

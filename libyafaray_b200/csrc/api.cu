@@ -9,6 +9,9 @@
 #include <cstdlib>
 #include <algorithm>
 #include <new>
+#include <mutex>
+
+#define YG_MAX_DEVICES 64 /* per-device tables of yafgpu_trace_static */
 
 static std::string g_create_err;
 
@@ -113,6 +116,31 @@ __global__ void __launch_bounds__(128) k_trace_batch(Accel acc, const yafgpu_ray
 	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, COUNT>(acc, (int)n, next, io, &tc);
 	else traversePersistent<true, COUNT>(acc, (int)n, next, io, &tc);
 	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+}
+
+// ---- allocation-free batch trace (yafgpu_trace_static) ---------------------------------------------------------------------
+// The batch trace needs device scratch: a copy of the caller's rays, room for the hit records and the ray-regeneration counter of
+// traversePersistent.  yafgpu_trace takes it from the stream-ordered pool; callers that may not allocate get the same kernel over a
+// file-scope array instead.  One array per GPU that loads the library, held until the process exits:
+//   [0, 256)                                  int: next unclaimed ray (must be zero when the kernel starts)
+//   [256, 256 + 32 n_max)                     yafgpu_ray[n_max]
+//   [256 + 32 n_max, 256 + 48 n_max)          yafgpu_hit[n_max]
+#define YG_STATIC_SCRATCH_BYTES (256 + (size_t)YAFGPU_TRACE_STATIC_MAX_RAYS * (sizeof(yafgpu_ray) + sizeof(yafgpu_hit)))
+static __device__ __align__(256) unsigned char g_trace_static_scratch[YG_STATIC_SCRATCH_BYTES];
+
+// Variant of k_trace_batch whose ray, hit and counter storage is carved out of one scratch block.  `scratch` is the DEVICE address of
+// g_trace_static_scratch as cudaGetSymbolAddress reports it for the current device (staticScratch below).  In host code the symbol
+// itself is only a stand-in, never an address a kernel may be given.
+__global__ void __launch_bounds__(128) k_trace_batch_static(Accel acc, unsigned char *__restrict__ scratch, int n, int mode)
+{
+	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	int *next = (int *)scratch;
+	BatchIO io;
+	io.rays = (const float4 *)(scratch + 256);
+	io.hits = (float4 *)(scratch + 256 + (size_t)YAFGPU_TRACE_STATIC_MAX_RAYS * sizeof(yafgpu_ray));
+	io.shadow = mode != YAFGPU_TRACE_CLOSEST;
+	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, false>(acc, n, next, io, &tc);
+	else traversePersistent<true, false>(acc, n, next, io, &tc);
 }
 
 } // namespace yg
@@ -500,6 +528,55 @@ int yafgpu_trace(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_hit *hi
 	}
 	poolFree(d_r, c->stream); poolFree(d_h, c->stream);
 	return rc;
+}
+
+// Device address of the static scratch array on `device` (which must be current): looked up once per device.
+static std::mutex g_static_mutex[YG_MAX_DEVICES];
+static unsigned char *g_static_ptr[YG_MAX_DEVICES];
+static cudaError_t staticScratch(int device, unsigned char **out)
+{
+	if(!g_static_ptr[device])
+	{
+		void *p = nullptr;
+		cudaError_t e = cudaGetSymbolAddress(&p, g_trace_static_scratch);
+		if(e != cudaSuccess) return e;
+		g_static_ptr[device] = (unsigned char *)p;
+	}
+	*out = g_static_ptr[device];
+	return cudaSuccess;
+}
+
+int yafgpu_trace_static(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_hit *hits, int mode)
+{
+	if(!c || (n && (!rays || !hits))) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	if(mode != YAFGPU_TRACE_CLOSEST && mode != YAFGPU_TRACE_SHADOW) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "yafgpu_trace_static: mode must be YAFGPU_TRACE_CLOSEST or YAFGPU_TRACE_SHADOW");
+	if(n > (size_t)YAFGPU_TRACE_STATIC_MAX_RAYS)
+		return setErr(c, YAFGPU_ERR_INVALID, "yafgpu_trace_static: " + std::to_string(n) + " rays exceed the static scratch capacity of " + std::to_string(YAFGPU_TRACE_STATIC_MAX_RAYS) +
+		              " rays per call (YAFGPU_TRACE_STATIC_MAX_RAYS); split the batch or use yafgpu_trace");
+	if(n == 0) return YAFGPU_OK;
+	if(c->device < 0 || c->device >= YG_MAX_DEVICES) return setErr(c, YAFGPU_ERR_INVALID, "yafgpu_trace_static: device index beyond the per-device table");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	// every call on this device shares the one array: callers of this process are serialised here, through the final synchronise
+	std::lock_guard<std::mutex> lock(g_static_mutex[c->device]);
+	unsigned char *scratch = nullptr;
+	YG_CUDA(c, staticScratch(c->device, &scratch));
+	unsigned char *d_rays = scratch + 256, *d_hits = scratch + 256 + (size_t)YAFGPU_TRACE_STATIC_MAX_RAYS * sizeof(yafgpu_ray);
+	// the array keeps the previous call's contents: the fetch counter must start at zero; rays [0, n) are overwritten and every hit
+	// record in [0, n) is written by the kernel, nothing beyond n is read
+	YG_CUDA(c, cudaMemsetAsync(scratch, 0, 256, c->stream));
+	YG_CUDA(c, cudaMemcpyAsync(d_rays, rays, n * sizeof(yafgpu_ray), cudaMemcpyHostToDevice, c->stream));
+	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	const size_t want = (n + 127) / 128;
+	const unsigned grid = (unsigned)(want < (size_t)sms * 16 ? want : (size_t)sms * 16);
+	k_trace_batch_static<<<grid, 128, 0, c->stream>>>(c->scene.accel, scratch, (int)n, mode);
+	YG_CUDA(c, cudaGetLastError());
+	YG_CUDA(c, cudaMemcpyAsync(hits, d_hits, n * sizeof(yafgpu_hit), cudaMemcpyDeviceToHost, c->stream));
+	YG_CUDA(c, cudaMemcpyAsync(c->h_fault, c->d_fault, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+	YG_CUDA(c, cudaStreamSynchronize(c->stream));
+	c->stats.kernel_launches++;
+	if(mode == YAFGPU_TRACE_CLOSEST) c->stats.rays_extension += n; else c->stats.rays_shadow += n;
+	return faultCheck(c, false);
 }
 
 int yafgpu_film_clear(yafgpu_ctx *c)

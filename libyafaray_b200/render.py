@@ -62,6 +62,13 @@ class Context:
         _check(self.h, capi.lib.yafgpu_trace(self.h, rays.ctypes.data, len(rays), hits.ctypes.data, mode, shadow_depth))
         return hits
 
+    def trace_static(self, rays, mode=capi.TRACE_CLOSEST):
+        """yafgpu_trace_static: the same trace without any device allocation (static scratch, at most capi.TRACE_STATIC_MAX_RAYS rays)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.zeros(len(rays), dtype=[("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("tri", "<i4")])
+        _check(self.h, capi.lib.yafgpu_trace_static(self.h, rays.ctypes.data, len(rays), hits.ctypes.data, mode))
+        return hits
+
     def trace_device(self, d_rays_ptr, n, d_hits_ptr, mode=capi.TRACE_CLOSEST, shadow_depth=2):
         _check(self.h, capi.lib.yafgpu_trace_device(self.h, d_rays_ptr, n, d_hits_ptr, mode, shadow_depth))
 
