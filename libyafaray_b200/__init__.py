@@ -5,7 +5,11 @@ built in-tree into libyafgpu.so), `capi` (ctypes binding), `interface` (host mir
 `render` (host mirror of TiledIntegrator::render's pass loop).  Importing the package loads libyafgpu.so and fails
 loudly when it is missing — there is no CPU fallback.
 """
-from . import capi  # noqa: F401  (dlopens libyafgpu.so, raises ImportError when it is not built)
+import os as _os
+
+from . import capi  # noqa: F401
+if _os.environ.get("LIBYAFARAY_B200_HOST_ONLY") != "1":
+    capi.lib.load()  # dlopens libyafgpu.so, raises ImportError when it is not built (host-only processes defer this to the first device call)
 from .interface import Interface  # noqa: F401
 from .render import Context, render_scene, load_film, film_to_image  # noqa: F401
 from . import film_io  # noqa: F401

@@ -223,4 +223,20 @@ def load():
     return lib
 
 
-lib = load()
+class _Lib:
+    """`capi.lib`: binds libyafgpu.so on first use.  The package import (libyafaray_b200/__init__.py) forces the load right away, so
+    a missing library still fails loudly at import; only a process that declares itself host-only (LIBYAFARAY_B200_HOST_ONLY=1:
+    scene description and XML export for the reference arm of bench.py, which must not map the product library) defers it — and
+    even there the first device call loads the library or raises, there is no fallback."""
+    _lib = None
+
+    def load(self):
+        if _Lib._lib is None:
+            _Lib._lib = load()
+        return _Lib._lib
+
+    def __getattr__(self, name):
+        return getattr(self.load(), name)
+
+
+lib = _Lib()

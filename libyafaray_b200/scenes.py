@@ -196,10 +196,12 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
 
 
 def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=12345, bounces=8, raydepth=8, path_samples=1,
-                    rr_min_bounces=2, integrator="pathtracing", smooth=True, ibl_hdr=None, mesh_lights=0, blend=False):
+                    rr_min_bounces=2, integrator="pathtracing", smooth=True, ibl_hdr=None, mesh_lights=0, blend=False, crop=None, threads=1):
     """BASELINE config 3: procedural displaced-grid terrain of ~n_tris triangles (2*n^2) with materials cycling over
     glossy / coated_glossy / rough_glass / shinydiffuse in 16x16-quad patches, a sun and an area light, path depth 8.
-    Built through the bulk mesh call (numpy arrays); value-noise displacement from a seeded generator."""
+    Built through the bulk mesh call (numpy arrays); value-noise displacement from a seeded generator.
+    `crop` = (xstart, ystart, width, height): render only that window of the width x height camera image (the <render> block's
+    xstart/ystart/width/height, environment.cc:456-470)."""
     n = max(2, int(round((n_tris / 2) ** 0.5)))
     rng = np.random.default_rng(seed)
     y = Interface()
@@ -300,5 +302,8 @@ def procedural_mesh(n_tris=10_000_000, width=1920, height=1080, spp=16, seed=123
         y.paramsSetInt("russian_roulette_min_bounces", rr_min_bounces)
     y.createIntegrator("pt")
     _vol_none(y)
-    render_block(y, width, height, spp)
+    if crop is None:
+        render_block(y, width, height, spp, threads=threads)
+    else:
+        render_block(y, crop[2], crop[3], spp, threads=threads, xstart=int(crop[0]), ystart=int(crop[1]))
     return y

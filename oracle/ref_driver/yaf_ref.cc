@@ -11,6 +11,11 @@
 //   yaf_ref hits <scene.xml> <rays.bin> <hits.bin> [mode] [shadow_depth]
 //                                                     Scene::intersect / Scene::isShadowed (scene.cc:896-1035) per ray,
 //                                                     global triangle ids in the order of scene.cc:807-817.
+//   yaf_ref bench <scene.xml> <threads> <warmup> <steps> [spp]
+//                                                     CPU baseline of bench.py: loads the scene ONCE (XML parse and Scene::update, i.e. the kd-tree
+//                                                     build, timed separately), then calls Scene::render() warmup + steps times; every call is one
+//                                                     full-frame render at `spp` samples per pixel (AA_minsamples override) and reports the
+//                                                     reference's own "rendert" timer.
 //   yaf_ref kat <out.bin>                             known-answer vectors of the QMC / fast-math / filter helpers.
 //
 // File formats (little endian): rays.bin = n x {from[3], tmin, dir[3], tmax} float32 (yafgpu_ray);
@@ -143,6 +148,48 @@ int cmdRender(int argc, char **argv)
 	return 0;
 }
 
+int cmdBench(int argc, char **argv)
+{
+	if(argc < 6) { fprintf(stderr, "usage: yaf_ref bench scene.xml threads warmup steps [spp]\n"); return 2; }
+	const int threads = atoi(argv[3]), warmup = atoi(argv[4]), steps = atoi(argv[5]);
+	const int spp = argc > 6 ? atoi(argv[6]) : 0;
+	Loaded l;
+	logger__.setConsoleMasterVerbosity("warning");
+	logger__.setLogMasterVerbosity("mute");
+	l.env = new RenderEnvironment();
+	l.scene = new Scene(l.env);
+	l.env->setScene(l.scene);
+	auto t0 = std::chrono::steady_clock::now();
+	if(!parseXmlFile__(argv[2], l.scene, l.env, l.render, "LinearRGB", 1.f)) return 1;
+	auto t1 = std::chrono::steady_clock::now();
+	l.render["threads"] = threads;
+	l.render["logging_saveLog"] = false;
+	l.render["logging_saveHTML"] = false;
+	if(spp > 0) { l.render["AA_minsamples"] = spp; l.render["AA_passes"] = 1; }
+	if(!l.env->setupScene(*l.scene, l.render, l.out)) return 1;
+	session__.setInteractive(false);
+	const std::map<std::string, Camera *> *cams = l.env->getCameraTable();
+	if(cams->empty()) { fprintf(stderr, "no camera\n"); return 1; }
+	l.scene->setCamera(cams->begin()->second);
+	auto t2 = std::chrono::steady_clock::now();
+	if(!l.scene->update()) { fprintf(stderr, "scene update failed\n"); return 1; }   // kd-tree build (kdtree_triangle.cc:76-157) + Light::init
+	auto t3 = std::chrono::steady_clock::now();
+	std::vector<double> rendert;
+	session__.setStatusRenderStarted();
+	for(int i = 0; i < warmup + steps; ++i)
+	{
+		if(!l.scene->render()) { fprintf(stderr, "yaf_ref: render failed\n"); return 1; }
+		if(i >= warmup) rendert.push_back(g_timer__.getTime("rendert"));
+	}
+	ImageFilm *film = l.scene->getImageFilm();
+	printf("{\"width\": %d, \"height\": %d, \"threads\": %d, \"spp\": %d, \"ntris\": %d, \"xml_parse_s\": %.3f, \"scene_update_s\": %.3f, \"rendert_s\": [",
+	       film->w_, film->h_, l.scene->getNumThreads(), spp, l.scene->tree_ ? (int)l.scene->tree_->total_prims_ : 0,
+	       std::chrono::duration<double>(t1 - t0).count(), std::chrono::duration<double>(t3 - t2).count());
+	for(size_t i = 0; i < rendert.size(); ++i) printf("%s%.6f", i ? ", " : "", rendert[i]);
+	printf("]}\n");
+	return 0;
+}
+
 struct MeshRange { const Triangle *base; size_t count; size_t offset; };
 
 int cmdHits(int argc, char **argv)
@@ -265,6 +312,7 @@ int main(int argc, char **argv)
 	std::string cmd = argv[1];
 	if(cmd == "render") return cmdRender(argc, argv);
 	if(cmd == "hits") return cmdHits(argc, argv);
+	if(cmd == "bench") return cmdBench(argc, argv);
 	if(cmd == "kat") return cmdKat(argc, argv);
 	if(cmd == "bgdump") return cmdBgDump(argc, argv);
 	fprintf(stderr, "unknown command %s\n", argv[1]);
