@@ -335,23 +335,27 @@ def gpu_arm(args, rank, world, local_rank):
         ctx.close(); ctx = None                     # HBM for the side contexts
         s2 = side_run(capi.FLAG_TIME_STAGES)        # kernel durations (CUDA events around every launch, no counting code)
         s3 = side_run(capi.FLAG_COUNT_TRAVERSAL)    # nodes visited / triangles tested on the same steps
-        s2["nodes_visited"], s2["tris_tested"] = s3["nodes_visited"], s3["tris_tested"]
+        for k in ("nodes_visited", "tris_tested", "nodes_visited_shadow", "tris_tested_shadow"):
+            s2[k] = s3[k]
         line["wave0_tasks"], line["wave0_shadow"] = s2["last_wave_tasks"], s2["last_wave_shadow"]
         peak, how = hbm_peak()
         n_trace, n_shadow = s2["rays_in_timed_trace"], s2["rays_in_timed_shadow"]
         ms_tr, ms_sh, ms_shd = s2["ms_trace"], s2["ms_shadow"], s2["ms_shade"]
         # Algorithmic bytes.  Traversal: 48 B ray+hit record, node_bytes per node visited, 48 B per
-        # triangle tested (the counters cover closest-hit AND shadow rays; they are split by ray count).  Shading: per task 108 B queue
-        # record in (ray_o, ray_d, hit, wgt, thr|dc, st, perm), 104 B per task spawned, 48 B per shadow ray queued, 136 B of
-        # triangle/vertex/normal data per hit (the scene exceeds the caches).
-        node_b, tri_b = float(s2.get("bvh_node_bytes", 0) or 64), 48.0
+        # triangle tested, closest-hit and shadow rays counted separately.  Shading: per task 108 B queue record in (ray_o, ray_d, hit,
+        # wgt, thr|dc, st, perm), 104 B per task spawned, 48 B per shadow ray queued, 136 B of triangle/vertex/normal data per hit
+        # (the scene exceeds the caches).
+        node_b, tri_b = float(s2["bvh_node_bytes"]), 48.0
         n_rays = max(1, n_trace + n_shadow)
-        per_ray = (node_b * s2["nodes_visited"] + tri_b * s2["tris_tested"]) / n_rays
+        per_ray_c = (node_b * s2["nodes_visited"] + tri_b * s2["tris_tested"]) / max(1, n_trace)
+        per_ray_s = (node_b * s2["nodes_visited_shadow"] + tri_b * s2["tris_tested_shadow"]) / max(1, n_shadow)
         spawned = max(0, n_trace - s2["camera_samples"])
         alg_shade = (108.0 + 136.0) * n_trace + 104.0 * spawned + 48.0 * n_shadow
         kern = {
-            "k_trace": {"ms": ms_tr, "launches": s2["launches_trace"], "alg_bytes": (48.0 + per_ray) * n_trace, "units": n_trace, "unit": "ray"},
-            "k_shadow": {"ms": ms_sh, "launches": s2["launches_shadow"], "alg_bytes": (48.0 + per_ray) * n_shadow, "units": n_shadow, "unit": "ray"},
+            "k_trace": {"ms": ms_tr, "launches": s2["launches_trace"], "alg_bytes": (48.0 + per_ray_c) * n_trace, "units": n_trace, "unit": "ray",
+                        "nodes_per_ray": s2["nodes_visited"] / max(1, n_trace), "tris_per_ray": s2["tris_tested"] / max(1, n_trace)},
+            "k_shadow": {"ms": ms_sh, "launches": s2["launches_shadow"], "alg_bytes": (48.0 + per_ray_s) * n_shadow, "units": n_shadow, "unit": "ray",
+                         "nodes_per_ray": s2["nodes_visited_shadow"] / max(1, n_shadow), "tris_per_ray": s2["tris_tested_shadow"] / max(1, n_shadow)},
             "k_shade": {"ms": ms_shd, "launches": s2["launches_shade"], "alg_bytes": alg_shade, "units": n_trace, "unit": "task"},
         }
         dom = max(kern, key=lambda k: kern[k]["ms"])
@@ -372,12 +376,11 @@ def gpu_arm(args, rank, world, local_rank):
         d = kern[dom]
         line["roofline"] = {"bound": "hbm", "achieved": d["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": d["frac"], "traffic": traffic,
                             "peak_source": how, "kernel": dom, "algorithmic_bytes_per_launch": d["alg_bytes"] / max(1, d["launches"]),
-                            "avg_launch_ms": d["avg_launch_ms"], "kernels": kern, "node_bytes": node_b,
-                            "nodes_per_ray": s2["nodes_visited"] / n_rays, "tris_per_ray": s2["tris_tested"] / n_rays,
+                            "avg_launch_ms": d["avg_launch_ms"], "kernels": kern, "node_bytes": node_b, "bvh_width": s2["bvh_width"],
+                            "nodes_per_ray": (s2["nodes_visited"] + s2["nodes_visited_shadow"]) / n_rays, "tris_per_ray": (s2["tris_tested"] + s2["tris_tested_shadow"]) / n_rays,
                             "stage_ms": {"trace": ms_tr, "shadow": ms_sh, "shade": ms_shd, "total": s2["ms_total"]},
                             "note": "durations: CUDA events around every launch in a TIME_STAGES context on the context's own stream; node/triangle "
-                                    "counts: a COUNT_TRAVERSAL context on the same steps (closest-hit and shadow rays share the counters: bytes per ray "
-                                    "are their common mean); k_shade = the per-material shading kernels of one iteration incl. the 2 sort kernels"}
+                                    "counts: a COUNT_TRAVERSAL context on the same steps; k_shade = the per-material shading kernels of one iteration incl. the 2 sort kernels"}
         # ---- CPU baseline (bounded sample): the reference arm's result when it ran on this box just before, else a 1-step run ----
         if not args.no_cpu:
             info = None

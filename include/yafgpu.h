@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define YAFGPU_ABI_VERSION 4
+#define YAFGPU_ABI_VERSION 5
 
 typedef struct yafgpu_ctx yafgpu_ctx;
 
@@ -528,6 +528,10 @@ typedef struct yafgpu_stats
 	uint64_t rays_in_timed_trace, rays_in_timed_shadow;
 	/* queue lengths of the most recent wave, per wavefront iteration (first 16): tasks traced+shaded, shadow rays traced */
 	uint32_t last_wave_tasks[16], last_wave_shadow[16];
+	/* accelerator shape: bytes per node (64: 4-wide, 96: 8-wide), children per node, levels of the wide tree */
+	uint32_t bvh_node_bytes, bvh_width, bvh_levels, reserved0;
+	/* COUNT_TRAVERSAL: nodes_visited / tris_tested above cover closest-hit rays, these the shadow (any-hit) rays */
+	uint64_t nodes_visited_shadow, tris_tested_shadow;
 } yafgpu_stats;
 
 enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2 };
@@ -579,10 +583,9 @@ int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
 int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
 
 /* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^23, limited to a quarter of the free device memory),
- * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "ray_regeneration" (the wavefront traversal kernels use the
- * warp-persistent schedule with ray regeneration that yafgpu_trace always uses: 0 = off, 1 = both kernels, 2 = closest-hit kernel only, 3 = shadow kernel only;
- * default -1 = the closest-hit kernel when the scene has at most 4096 triangles),
- * "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3). */
+ * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "leaf_size" (triangles per leaf link of the BVH built by
+ * the NEXT upload, 1..8), "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3),
+ * "debug_stack_limit" (traversal stack entries in use, only to exercise the overflow error path). */
 int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);
 int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
 int yafgpu_reset_stats(yafgpu_ctx *ctx);

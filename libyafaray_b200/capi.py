@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("YAFGPU_LIB") or os.path.join(_HERE, "libyafgpu.so")  # YAFGPU_LIB: kernel-variant experiments (tools/)
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 # enums (include/yafgpu.h)
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_STATE, ERR_NOMEM = range(6)
@@ -174,7 +174,9 @@ class Stats(C.Structure):
                 ("ms_build", C.c_double), ("ms_trace", C.c_double), ("ms_shade", C.c_double), ("ms_film", C.c_double),
                 ("ms_total", C.c_double), ("waves", u64), ("wave_retries", u64), ("ms_shadow", C.c_double),
                 ("launches_trace", u64), ("launches_shadow", u64), ("launches_shade", u64), ("rays_in_timed_trace", u64),
-                ("rays_in_timed_shadow", u64), ("last_wave_tasks", C.c_uint32 * 16), ("last_wave_shadow", C.c_uint32 * 16)]
+                ("rays_in_timed_shadow", u64), ("last_wave_tasks", C.c_uint32 * 16), ("last_wave_shadow", C.c_uint32 * 16),
+                ("bvh_node_bytes", C.c_uint32), ("bvh_width", C.c_uint32), ("bvh_levels", C.c_uint32), ("reserved0", C.c_uint32),
+                ("nodes_visited_shadow", u64), ("tris_tested_shadow", u64)]
 
 
 # every entry point include/yafgpu.h declares: name -> (restype, argtypes)

@@ -106,16 +106,19 @@ struct BatchIO
 	}
 };
 
-// the same warp-persistent traversal the wavefront kernels use, on a caller-supplied ray array (at most 2^31 - 1 rays per call)
+// the warp-persistent traversal with ray regeneration the wavefront kernels use, on a caller-supplied ray array (at most 2^31 - 1 rays
+// per call); `next` = the global fetch counter, zero at launch
 template<bool COUNT>
 __global__ void __launch_bounds__(128) k_trace_batch(Accel acc, const yafgpu_ray *__restrict__ rays, size_t n, yafgpu_hit *__restrict__ hits,
-                                                        int mode, int *__restrict__ next, unsigned long long *__restrict__ counters)
+                                                        int mode, int *__restrict__ next, int refill_below, unsigned long long *__restrict__ counters)
 {
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	__shared__ uint2 s_stack[YG_STACK_SHARED * 128];
+	TravStack<YG_STACK_SHARED> st; bindSharedStack(st, s_stack);
 	BatchIO io; io.rays = (const float4 *)rays; io.hits = (float4 *)hits; io.shadow = mode != YAFGPU_TRACE_CLOSEST;
-	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, COUNT>(acc, (int)n, next, io, &tc);
-	else traversePersistent<true, COUNT>(acc, (int)n, next, io, &tc);
-	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, COUNT>(acc, (int)n, next, io, st, &tc, refill_below);
+	else traversePersistent<true, COUNT>(acc, (int)n, next, io, st, &tc, refill_below);
+	if(COUNT) { atomicAdd(&counters[mode == YAFGPU_TRACE_CLOSEST ? CNT_NODES : CNT_NODES_SHADOW], tc.nodes); atomicAdd(&counters[mode == YAFGPU_TRACE_CLOSEST ? CNT_TRIS : CNT_TRIS_SHADOW], tc.tris); }
 }
 
 // ---- allocation-free batch trace (yafgpu_trace_static) ---------------------------------------------------------------------
@@ -131,16 +134,18 @@ static __device__ __align__(256) unsigned char g_trace_static_scratch[YG_STATIC_
 // Variant of k_trace_batch whose ray, hit and counter storage is carved out of one scratch block.  `scratch` is the DEVICE address of
 // g_trace_static_scratch as cudaGetSymbolAddress reports it for the current device (staticScratch below).  In host code the symbol
 // itself is only a stand-in, never an address a kernel may be given.
-__global__ void __launch_bounds__(128) k_trace_batch_static(Accel acc, unsigned char *__restrict__ scratch, int n, int mode)
+__global__ void __launch_bounds__(128) k_trace_batch_static(Accel acc, unsigned char *__restrict__ scratch, int n, int mode, int refill_below)
 {
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	__shared__ uint2 s_stack[YG_STACK_SHARED * 128];
+	TravStack<YG_STACK_SHARED> st; bindSharedStack(st, s_stack);
 	int *next = (int *)scratch;
 	BatchIO io;
 	io.rays = (const float4 *)(scratch + 256);
 	io.hits = (float4 *)(scratch + 256 + (size_t)YAFGPU_TRACE_STATIC_MAX_RAYS * sizeof(yafgpu_ray));
 	io.shadow = mode != YAFGPU_TRACE_CLOSEST;
-	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, false>(acc, n, next, io, &tc);
-	else traversePersistent<true, false>(acc, n, next, io, &tc);
+	if(mode == YAFGPU_TRACE_CLOSEST) traversePersistent<false, false>(acc, n, next, io, st, &tc, refill_below);
+	else traversePersistent<true, false>(acc, n, next, io, st, &tc, refill_below);
 }
 
 } // namespace yg
@@ -184,8 +189,8 @@ int yafgpu_create(yafgpu_ctx **out, int device, unsigned flags)
 	if(e == cudaSuccess) e = cudaMalloc(&c->d_fetch, sizeof(int));
 	if(e == cudaSuccess) e = cudaMalloc(&c->d_fault, sizeof(int));
 	if(e == cudaSuccess) e = cudaMemset(c->d_fault, 0, sizeof(int));
-	if(e == cudaSuccess) e = cudaMallocHost(&c->h_fault, sizeof(int));
-	if(e == cudaSuccess) *c->h_fault = 0;
+	if(e == cudaSuccess) e = cudaMallocHost(&c->h_fault, 2 * sizeof(int)); // [0] fault word mirror, [1] control word of yafgpu_trace_static
+	if(e == cudaSuccess) { c->h_fault[0] = 0; c->h_fault[1] = 0; }
 	if(e == cudaSuccess) e = cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * CNT_N);
 	if(e != cudaSuccess) { yafgpu_destroy(c); return cudaErr(nullptr, e, "context allocation"); }
 	*out = c;
@@ -411,12 +416,13 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	if(g.n_tris > 0)
 	{
 		BvhBuildInput bi; bi.n_tris = (int)g.n_tris; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx; bi.tri_mat = c->d_tri_mat;
-		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng; bi.leaf_max = c->leaf_max;
+		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng; bi.leaf_max = c->leaf_max; bi.width = YG_BVH_WIDTH;
 		BvhBuildOutput bo;
 		cudaError_t e = buildBvh(bi, bo, st);
 		if(e != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e, "buildBvh"); }
 		c->d_nodes = bo.nodes; c->d_acc_tris = bo.tris;
-		a.nodes = bo.nodes; a.tris = bo.tris; a.n_nodes = bo.n_nodes; a.root = bo.root;
+		a.nodes = (const uint4 *)bo.nodes; a.tris = bo.tris; a.n_nodes = bo.n_nodes; a.root = bo.root; a.width = YG_BVH_WIDTH;
+		c->stats.bvh_node_bytes = (uint32_t)bo.node_bytes; c->stats.bvh_width = YG_BVH_WIDTH; c->stats.bvh_levels = (uint32_t)bo.levels;
 		memcpy(c->scene_bound, bo.bound, sizeof(bo.bound));
 		// tree bound grown by 0.1 % per axis (kdtree_triangle.cc:112-116; double arithmetic on float members)
 		for(int k = 0; k < 3; ++k)
@@ -434,12 +440,12 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		LightDev &ld = c->h_lights[i];
 		if((ld.type != YAFGPU_LIGHT_MESH && ld.type != YAFGPU_LIGHT_BGPORTAL) || ld.tri_count <= 0) continue;
 		BvhBuildInput bi; bi.n_tris = ld.tri_count; bi.points = c->d_points; bi.tri_vidx = c->d_tri_vidx + 3 * (size_t)ld.tri_first;
-		bi.tri_mat = c->d_tri_mat + ld.tri_first; bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng + 3 * (size_t)ld.tri_first;
+		bi.tri_mat = c->d_tri_mat + ld.tri_first; bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng + 3 * (size_t)ld.tri_first; bi.leaf_max = c->leaf_max; bi.width = YG_BVH_WIDTH;
 		BvhBuildOutput bo;
 		cudaError_t e2 = buildBvh(bi, bo, st);
 		if(e2 != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e2, "buildBvh (mesh light)"); }
 		Accel la; memset(&la, 0, sizeof(la));
-		la.nodes = bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root; la.fault = c->d_fault; la.stack_limit = a.stack_limit;
+		la.nodes = (const uint4 *)bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root; la.width = YG_BVH_WIDTH; la.fault = c->d_fault; la.stack_limit = a.stack_limit;
 		c->light_bvh_ptrs.push_back(bo.nodes); c->light_bvh_ptrs.push_back(bo.tris);
 		ld.accel = (int)laccels.size();
 		laccels.push_back(la);
@@ -457,7 +463,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream);
 	if(e != cudaSuccess) return cudaErr(c, e, "scene upload");
 	float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->stats.ms_build += ms;
-	c->stats.bvh_nodes = a.n_nodes; c->stats.bvh_bytes = (uint64_t)a.n_nodes * sizeof(BvhNode); c->stats.tri_bytes = (uint64_t)g.n_tris * sizeof(TriAccel);
+	c->stats.bvh_nodes = a.n_nodes; c->stats.bvh_bytes = (uint64_t)a.n_nodes * c->stats.bvh_node_bytes; c->stats.tri_bytes = (uint64_t)g.n_tris * sizeof(TriAccel);
 
 	s.points = c->d_points; s.normals = c->d_normals; s.uv = c->d_uv; s.tris = c->d_tris; s.objects = c->d_objects;
 	s.materials = c->d_mats; s.lights = c->d_lights; s.n_lights = (int)c->h_lights.size(); s.light_tables = c->d_light_tables; s.light_accels = c->d_light_accels; s.faure = c->d_faure;
@@ -497,9 +503,9 @@ int yafgpu_trace_device(yafgpu_ctx *c, const void *d_rays, size_t n, void *d_hit
 	size_t want = (n + 127) / 128;
 	unsigned grid = (unsigned)(want < (size_t)sms * 16 ? want : (size_t)sms * 16);
 	if(c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL)
-		k_trace_batch<true><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_fetch, c->d_counters);
+		k_trace_batch<true><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_fetch, c->regen_threshold, c->d_counters);
 	else
-		k_trace_batch<false><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_fetch, c->d_counters);
+		k_trace_batch<false><<<grid, 128, 0, c->stream>>>(c->scene.accel, (const yafgpu_ray *)d_rays, n, (yafgpu_hit *)d_hits, mode, c->d_fetch, c->regen_threshold, c->d_counters);
 	YG_CUDA(c, cudaGetLastError());
 	c->stats.kernel_launches++;
 	if(mode == YAFGPU_TRACE_CLOSEST) c->stats.rays_extension += n; else c->stats.rays_shadow += n;
@@ -569,13 +575,16 @@ int yafgpu_trace_static(yafgpu_ctx *c, const yafgpu_ray *rays, size_t n, yafgpu_
 	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
 	const size_t want = (n + 127) / 128;
 	const unsigned grid = (unsigned)(want < (size_t)sms * 16 ? want : (size_t)sms * 16);
-	k_trace_batch_static<<<grid, 128, 0, c->stream>>>(c->scene.accel, scratch, (int)n, mode);
+	k_trace_batch_static<<<grid, 128, 0, c->stream>>>(c->scene.accel, scratch, (int)n, mode, c->regen_threshold);
 	YG_CUDA(c, cudaGetLastError());
 	YG_CUDA(c, cudaMemcpyAsync(hits, d_hits, n * sizeof(yafgpu_hit), cudaMemcpyDeviceToHost, c->stream));
 	YG_CUDA(c, cudaMemcpyAsync(c->h_fault, c->d_fault, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+	YG_CUDA(c, cudaMemcpyAsync(c->h_fault + 1, scratch, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
 	YG_CUDA(c, cudaStreamSynchronize(c->stream));
 	c->stats.kernel_launches++;
 	if(mode == YAFGPU_TRACE_CLOSEST) c->stats.rays_extension += n; else c->stats.rays_shadow += n;
+	// every warp reserves rays until the counter passes n: a final value below n means somebody else reset it under the kernel
+	if((size_t)c->h_fault[1] < n) return setErr(c, YAFGPU_ERR_CUDA, "yafgpu_trace_static: the static scratch was disturbed while the call ran (fetch counter " + std::to_string(c->h_fault[1]) + " < " + std::to_string(n) + " rays): overlapping use of the array");
 	return faultCheck(c, false);
 }
 
@@ -643,8 +652,9 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	const std::string n(name);
 	if(n == "wave_size") { if(value < 1024 || value > (1 << 24)) return setErr(c, YAFGPU_ERR_INVALID, "wave_size out of range"); c->wave_cap_override = (int)value; return YAFGPU_OK; }
 	if(n == "leaf_size") { if(value < 1 || value > 8) return setErr(c, YAFGPU_ERR_INVALID, "leaf_size must be 1..8"); c->leaf_max = (int)value; return YAFGPU_OK; }
-	if(n == "ray_regeneration") { if(value < -1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "ray_regeneration: -1..3"); c->ray_regeneration = value; return YAFGPU_OK; }
 	if(n == "shade_streams") { if(value < 1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "shade_streams must be 1..3"); c->shade_streams = (int)value; return YAFGPU_OK; }
+	if(n == "ray_regeneration") { if(value < -1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "ray_regeneration: -1..3"); c->ray_regeneration = (int)value; return YAFGPU_OK; }
+	if(n == "regen_threshold") { if(value < 1 || value > 32) return setErr(c, YAFGPU_ERR_INVALID, "regen_threshold: 1..32"); c->regen_threshold = (int)value; return YAFGPU_OK; }
 	if(n == "debug_stack_limit") { if(value < 0 || value > YG_STACK) return setErr(c, YAFGPU_ERR_INVALID, "debug_stack_limit: 0..96"); c->stack_limit = (int)value; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);
@@ -661,6 +671,7 @@ int yafgpu_get_stats(yafgpu_ctx *c, yafgpu_stats *out)
 	out->rays_camera += h[CNT_RAYS_CAMERA]; out->rays_extension += h[CNT_RAYS_EXTENSION]; out->rays_shadow += h[CNT_RAYS_SHADOW];
 	out->rays_shadow_transp += h[CNT_RAYS_SHADOW_TRANSP]; out->rays_light_probe += h[CNT_RAYS_LIGHT_PROBE];
 	out->camera_samples += h[CNT_CAMERA_SAMPLES]; out->nodes_visited = h[CNT_NODES]; out->tris_tested = h[CNT_TRIS];
+	out->nodes_visited_shadow = h[CNT_NODES_SHADOW]; out->tris_tested_shadow = h[CNT_TRIS_SHADOW];
 	return YAFGPU_OK;
 }
 
@@ -669,9 +680,10 @@ int yafgpu_reset_stats(yafgpu_ctx *c)
 	if(!c) return YAFGPU_ERR_INVALID;
 	YG_CUDA(c, cudaSetDevice(c->device));
 	YG_CUDA(c, cudaStreamSynchronize(c->stream));
-	uint64_t nodes = c->stats.bvh_nodes, nb = c->stats.bvh_bytes, tb = c->stats.tri_bytes; double mb = c->stats.ms_build;
+	const yafgpu_stats old = c->stats;
 	memset(&c->stats, 0, sizeof(c->stats));
-	c->stats.bvh_nodes = nodes; c->stats.bvh_bytes = nb; c->stats.tri_bytes = tb; c->stats.ms_build = mb;
+	c->stats.bvh_nodes = old.bvh_nodes; c->stats.bvh_bytes = old.bvh_bytes; c->stats.tri_bytes = old.tri_bytes; c->stats.ms_build = old.ms_build;
+	c->stats.bvh_node_bytes = old.bvh_node_bytes; c->stats.bvh_width = old.bvh_width; c->stats.bvh_levels = old.bvh_levels;
 	YG_CUDA(c, cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * CNT_N));
 	return YAFGPU_OK;
 }

@@ -8,7 +8,14 @@
 //   sort        : cub::DeviceRadixSort (library primitive; everything else here is hand-written)
 //   hierarchy   : Karras 2012 "Maximizing parallelism in the construction of BVHs", index-augmented keys for duplicates
 //   refit       : bottom-up AABB propagation with one atomic counter per internal node
-//   emit        : 64 B two-child nodes (scene_dev.cuh) + TriAccel records in Morton order
+//   collapse    : the binary hierarchy is collapsed top-down, level by level, into W-wide nodes (W = 4 or 8): a wide node starts from
+//                 the two children of its binary node and repeatedly opens the child with the largest surface area until it holds W
+//                 children (the SAH-greedy collapse of Wald et al. 2008 / Ylitie et al. 2017); subtrees of at most `leaf_max`
+//                 triangles become leaf links
+//   emit        : W-wide nodes with float32 child planes in structure-of-arrays form (scene_dev.cuh) + TriAccel records in Morton order.
+//                 (An 8-bit quantised node was built and measured first: the traversal kernel is bound by instruction issue — 68 %
+//                 issue-slot utilisation at 10.5 of 32 lanes, DRAM at 4 % — so the byte->float conversions cost more than the smaller
+//                 nodes saved: profiles/r2b_*.)
 #include "bvh_build.h"
 #include "dev_pool.h"
 #include <cub/cub.cuh>
@@ -78,9 +85,11 @@ __global__ void k_morton(int n, const float4 *__restrict__ bmin, const float4 *_
 	float4 lo = bmin[i], hi = bmax[i];
 	float c[3] = {0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z)};
 	unsigned long long q[3];
+	// cubic cells: every axis is scaled by the LARGEST extent, so a flat scene (a terrain) spends its code bits on the two long axes
+	// instead of splitting its thin axis as often as the others
+	const float ext = fmaxf(fmaxf(sh[0] - sl[0], sh[1] - sl[1]), sh[2] - sl[2]);
 	for(int k = 0; k < 3; ++k)
 	{
-		float ext = sh[k] - sl[k];
 		float t = ext > 0.f ? (c[k] - sl[k]) / ext : 0.f;
 		t = fminf(fmaxf(t, 0.f), 1.f);
 		q[k] = (unsigned long long)fminf(t * 2097152.f, 2097151.f);
@@ -163,29 +172,95 @@ __global__ void k_refit(int n, const int *__restrict__ vals, const float4 *__res
 	}
 }
 
-// child link: inner node index, or ~((first << 3) | (count - 1)) for a leaf of `count` consecutive TriAccel records.  A subtree
-// that covers at most `leaf_max` triangles is collapsed into one leaf (its box is the subtree's box; the inner nodes below it stay
-// in the array, unreferenced): fewer 64-byte node visits for a few more 48-byte triangle tests.
-__device__ __forceinline__ int encodeChild(int c, int n, const int2 *__restrict__ range, int leaf_max)
+// ---- collapse to W-wide quantised nodes ------------------------------------------------------------------------------------------
+// A binary node id is: k in [0, n-1) internal node k, (n-1)+k leaf k (triangle at Morton position k).
+struct CollapseItem { int node2; int slot; };   // binary node to expand -> wide node index to write
+
+__device__ __forceinline__ float boxArea(const float4 lo, const float4 hi)
 {
-	if(c >= n - 1) return ~(((c - (n - 1)) << 3) | 0);
-	const int2 r = range[c];
-	return r.y <= leaf_max ? ~((r.x << 3) | (r.y - 1)) : c;
+	const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+	return dx * dy + dy * dz + dz * dx;
 }
 
-__global__ void k_emit_nodes(int n, const int *__restrict__ left, const int *__restrict__ right, const float4 *__restrict__ nmin,
-                             const float4 *__restrict__ nmax, const int2 *__restrict__ range, int leaf_max, BvhNode *__restrict__ nodes)
+// triangles under binary node c (1 for a leaf)
+__device__ __forceinline__ int trisUnder(int c, int n, const int2 *__restrict__ range) { return c >= n - 1 ? 1 : range[c].y; }
+
+template<int W>
+__global__ void k_collapse(int n, int n_items, const CollapseItem *__restrict__ items, const int *__restrict__ left, const int *__restrict__ right,
+                           const float4 *__restrict__ nmin, const float4 *__restrict__ nmax, const int2 *__restrict__ range, int leaf_max,
+                           uint4 *__restrict__ nodes, CollapseItem *__restrict__ next_items, int *__restrict__ counters /* [0] wide nodes, [1] next queue length */)
 {
-	int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if(i >= n - 1) return;
-	const int lc = left[i], rc = right[i];
-	float4 a = nmin[lc], b = nmax[lc], c = nmin[rc], d = nmax[rc];
-	BvhNode nd;
-	nd.n0 = make_float4(a.x, a.y, a.z, b.x);
-	nd.n1 = make_float4(b.y, b.z, c.x, c.y);
-	nd.n2 = make_float4(c.z, d.x, d.y, d.z);
-	nd.n3 = make_float4(__int_as_float(encodeChild(lc, n, range, leaf_max)), __int_as_float(encodeChild(rc, n, range, leaf_max)), 0.f, 0.f);
-	nodes[i] = nd;
+	const int it = blockIdx.x * blockDim.x + threadIdx.x;
+	if(it >= n_items) return;
+	const CollapseItem item = items[it];
+	int ch[W]; float area[W];   // area < 0: not openable (leaf link)
+	int cnt = 2;
+	ch[0] = left[item.node2]; ch[1] = right[item.node2];
+#pragma unroll
+	for(int k = 0; k < W; ++k)
+	{
+		if(k < 2) area[k] = trisUnder(ch[k], n, range) > leaf_max ? boxArea(nmin[ch[k]], nmax[ch[k]]) : -1.f;
+		else { ch[k] = -1; area[k] = -1.f; }
+	}
+	while(cnt < W)
+	{
+		int best = -1; float ba = -1.f;
+#pragma unroll
+		for(int k = 0; k < W; ++k) if(k < cnt && area[k] > ba) { ba = area[k]; best = k; }   // area >= 0 only for openable children
+		if(best < 0) break;
+		int c = -1;
+#pragma unroll
+		for(int k = 0; k < W; ++k) if(k == best) c = ch[k];
+		const int l = left[c], r = right[c];
+		const float al = trisUnder(l, n, range) > leaf_max ? boxArea(nmin[l], nmax[l]) : -1.f;
+		const float ar = trisUnder(r, n, range) > leaf_max ? boxArea(nmin[r], nmax[r]) : -1.f;
+#pragma unroll
+		for(int k = 0; k < W; ++k)
+		{
+			if(k == best) { ch[k] = l; area[k] = al; }
+			if(k == cnt) { ch[k] = r; area[k] = ar; }
+		}
+		++cnt;
+	}
+	// inner children get consecutive wide-node slots
+	int n_inner = 0;
+#pragma unroll
+	for(int k = 0; k < W; ++k) if(k < cnt && area[k] >= 0.f) ++n_inner;
+	int slot0 = 0, q0 = 0;
+	if(n_inner) { slot0 = atomicAdd(&counters[0], n_inner); q0 = atomicAdd(&counters[1], n_inner); }
+	// node (scene_dev.cuh): six planes of W floats (lo x,y,z, hi x,y,z), then W links, padded to 128 B (W = 4) / 256 B (W = 8)
+	float pl[6][W]; int link[W];
+	int ii = 0;
+#pragma unroll
+	for(int k = 0; k < W; ++k)
+	{
+		if(k >= cnt)
+		{	// no child: inverted box, never hit
+			for(int a = 0; a < 3; ++a) { pl[a][k] = FLT_MAX; pl[3 + a][k] = -FLT_MAX; }
+			link[k] = (int)0x80000000;
+			continue;
+		}
+		const int c = ch[k];
+		const float4 lo = nmin[c], hi = nmax[c];
+		pl[0][k] = lo.x; pl[1][k] = lo.y; pl[2][k] = lo.z; pl[3][k] = hi.x; pl[4][k] = hi.y; pl[5][k] = hi.z;
+		if(area[k] >= 0.f)
+		{
+			link[k] = slot0 + ii;
+			next_items[q0 + ii] = CollapseItem{c, slot0 + ii};
+			++ii;
+		}
+		else if(c >= n - 1) link[k] = ~(((c - (n - 1)) << 3) | 0);
+		else { const int2 r = range[c]; link[k] = ~((r.x << 3) | (r.y - 1)); }
+	}
+	float4 *out = (float4 *)(nodes + (size_t)item.slot * (W == 4 ? 8 : 16));
+#pragma unroll
+	for(int a = 0; a < 6; ++a)
+#pragma unroll
+		for(int v = 0; v < W / 4; ++v) out[a * (W / 4) + v] = make_float4(pl[a][4 * v], pl[a][4 * v + 1], pl[a][4 * v + 2], pl[a][4 * v + 3]);
+#pragma unroll
+	for(int v = 0; v < W / 4; ++v)
+		out[6 * (W / 4) + v] = make_float4(__int_as_float(link[4 * v]), __int_as_float(link[4 * v + 1]), __int_as_float(link[4 * v + 2]), __int_as_float(link[4 * v + 3]));
+	out[7 * (W / 4)] = make_float4(__int_as_float(cnt), 0.f, 0.f, 0.f);
 }
 
 __global__ void k_emit_tris(int n, const int *__restrict__ vals, const float4 *__restrict__ v0e, const float4 *__restrict__ e1i,
@@ -196,6 +271,15 @@ __global__ void k_emit_tris(int n, const int *__restrict__ vals, const float4 *_
 	const int t = vals[k];
 	TriAccel ta; ta.v0e = v0e[t]; ta.e1i = e1i[t]; ta.e2f = e2f[t];
 	out[k] = ta;
+}
+
+__global__ void k_pad_boxes(int n_boxes, float4 *__restrict__ nmin, float4 *__restrict__ nmax, float pad)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n_boxes) return;
+	float4 a = nmin[i], b = nmax[i];
+	a.x -= pad; a.y -= pad; a.z -= pad; b.x += pad; b.y += pad; b.z += pad;
+	nmin[i] = a; nmax[i] = b;
 }
 
 #define CK(x) do { cudaError_t e_ = (x); if(e_ != cudaSuccess) { err = e_; goto fail; } } while(0)
@@ -209,9 +293,10 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 	int *scene_bound = nullptr, *vals = nullptr, *vals_s = nullptr, *left = nullptr, *right = nullptr, *parent = nullptr, *counters = nullptr;
 	unsigned long long *keys = nullptr, *keys_s = nullptr;
 	int2 *range = nullptr;
+	CollapseItem *items[2] = {nullptr, nullptr}; int *ccount = nullptr;
 	const int leaf_max = in.leaf_max < 1 ? 1 : (in.leaf_max > 8 ? 8 : in.leaf_max);
 	void *cub_tmp = nullptr; size_t cub_bytes = 0;
-	out.nodes = nullptr; out.tris = nullptr; out.n_nodes = 0;
+	out.nodes = nullptr; out.tris = nullptr; out.n_nodes = 0; out.node_bytes = in.width == 4 ? 128 : 256; out.levels = 0;
 
 	CK(poolAlloc(&v0e, sizeof(float4) * n, stream)); CK(poolAlloc(&e1i, sizeof(float4) * n, stream)); CK(poolAlloc(&e2f, sizeof(float4) * n, stream));
 	CK(poolAlloc(&bmin, sizeof(float4) * n, stream)); CK(poolAlloc(&bmax, sizeof(float4) * n, stream));
@@ -249,11 +334,45 @@ cudaError_t buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t 
 		CK(cudaGetLastError());
 		k_refit<<<G, B, 0, stream>>>(n, vals_s, bmin, bmax, left, right, parent, nmin, nmax, counters);
 		CK(cudaGetLastError());
-		CK(poolAlloc(&out.nodes, sizeof(BvhNode) * (n - 1), stream));
-		k_emit_nodes<<<(n - 1 + B - 1) / B, B, 0, stream>>>(n, left, right, nmin, nmax, range, leaf_max, out.nodes);
-		CK(cudaGetLastError());
-		out.n_nodes = n - 1;
-		out.root = n <= leaf_max ? ~((0 << 3) | (n - 1)) : 0;
+		// pad every box by 2^-19 of the scene's largest coordinate: the traversal tests the planes in t-space with fused arithmetic
+		// whose rounding differs from Moeller-Trumbore's by a few ulps of the coordinates involved
+		{
+			int sb[6];
+			CK(cudaMemcpyAsync(sb, scene_bound, sizeof(sb), cudaMemcpyDeviceToHost, stream));
+			CK(cudaStreamSynchronize(stream));
+			float mx = 0.f;
+			for(int k = 0; k < 6; ++k) { int i = sb[k]; i = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &i, 4); mx = fmaxf(mx, fabsf(f)); }
+			const float pad = mx * 1.9073486328125e-06f + 1e-30f;
+			k_pad_boxes<<<(2 * n - 1 + B - 1) / B, B, 0, stream>>>(2 * n - 1, nmin, nmax, pad);
+			CK(cudaGetLastError());
+		}
+		const int W = in.width == 4 ? 4 : 8;
+		const size_t node_u4 = W == 4 ? 8 : 16;
+		out.node_bytes = (int)(node_u4 * sizeof(uint4));
+		if(n <= leaf_max) { out.n_nodes = 0; out.root = ~((0 << 3) | (n - 1)); }
+		else
+		{
+			CK(poolAlloc(&out.nodes, sizeof(uint4) * node_u4 * (size_t)(n - 1), stream));
+			CK(poolAlloc(&items[0], sizeof(CollapseItem) * (size_t)n, stream)); CK(poolAlloc(&items[1], sizeof(CollapseItem) * (size_t)n, stream));
+			CK(poolAlloc(&ccount, sizeof(int) * 2, stream));
+			const CollapseItem root_item = {0, 0};
+			int hc[2] = {1, 0};
+			CK(cudaMemcpyAsync(items[0], &root_item, sizeof(root_item), cudaMemcpyHostToDevice, stream));
+			CK(cudaMemcpyAsync(ccount, hc, sizeof(hc), cudaMemcpyHostToDevice, stream));
+			int n_items = 1, cur = 0, levels = 0;
+			while(n_items > 0)
+			{
+				const int g = (n_items + 127) / 128;
+				if(W == 4) k_collapse<4><<<g, 128, 0, stream>>>(n, n_items, items[cur], left, right, nmin, nmax, range, leaf_max, (uint4 *)out.nodes, items[cur ^ 1], ccount);
+				else k_collapse<8><<<g, 128, 0, stream>>>(n, n_items, items[cur], left, right, nmin, nmax, range, leaf_max, (uint4 *)out.nodes, items[cur ^ 1], ccount);
+				CK(cudaGetLastError());
+				CK(cudaMemcpyAsync(hc, ccount, sizeof(hc), cudaMemcpyDeviceToHost, stream));
+				CK(cudaMemsetAsync(ccount + 1, 0, sizeof(int), stream));
+				CK(cudaStreamSynchronize(stream));
+				n_items = hc[1]; cur ^= 1; ++levels;
+			}
+			out.n_nodes = hc[0]; out.root = 0; out.levels = levels;
+		}
 	}
 	else
 	{
@@ -270,6 +389,7 @@ fail:
 	poolFree(v0e, stream); poolFree(e1i, stream); poolFree(e2f, stream); poolFree(bmin, stream); poolFree(bmax, stream); poolFree(nmin, stream); poolFree(nmax, stream);
 	poolFree(scene_bound, stream); poolFree(vals, stream); poolFree(vals_s, stream); poolFree(left, stream); poolFree(right, stream); poolFree(parent, stream); poolFree(counters, stream);
 	poolFree(keys, stream); poolFree(keys_s, stream); poolFree(cub_tmp, stream); poolFree(range, stream);
+	poolFree(items[0], stream); poolFree(items[1], stream); poolFree(ccount, stream);
 	if(err != cudaSuccess) { poolFree(out.nodes, stream); poolFree(out.tris, stream); out.nodes = nullptr; out.tris = nullptr; }
 	return err;
 }

@@ -13,11 +13,13 @@ struct BvhBuildInput
 	const unsigned *mat_triflags; // device, per material TRI_* flags
 	float *tri_ng_out;            // device, 3 per triangle: geometric normals (written)
 	int leaf_max = 1;             // subtrees of at most this many triangles become one leaf (1..8)
+	int width = 8;                // children per node: 4 (64 B nodes) or 8 (96 B nodes)
 };
 
 struct BvhBuildOutput
 {
-	BvhNode *nodes; int n_nodes;
+	void *nodes; int n_nodes;     // quantised wide nodes (scene_dev.cuh)
+	int node_bytes, levels;
 	TriAccel *tris;
 	int root;
 	float bound[6]; // exact scene bound: min xyz, max xyz

@@ -6,6 +6,13 @@
 #include <string>
 #include <vector>
 
+#ifndef YG_DEFAULT_REGEN
+#define YG_DEFAULT_REGEN 1
+#endif
+#ifndef YG_DEFAULT_LEAF
+#define YG_DEFAULT_LEAF 2 /* triangles per leaf link of the wide BVH unless yafgpu_set_option("leaf_size") says otherwise */
+#endif
+
 struct yafgpu_ctx
 {
 	int device = 0;
@@ -31,7 +38,7 @@ struct yafgpu_ctx
 	yg::TexDev *d_textures = nullptr; yg::NodeDev *d_shader_nodes = nullptr; // image textures and shader nodes (nodes.cuh)
 	std::vector<void *> tex_ptrs;                                            // texel arrays of d_textures
 	yg::FaureTables *d_faure = nullptr;
-	yg::BvhNode *d_nodes = nullptr;
+	void *d_nodes = nullptr;
 	yg::TriAccel *d_acc_tris = nullptr;
 	size_t n_tris = 0, n_points = 0, n_normals = 0, n_uv = 0, n_objects = 0, n_mats = 0, n_lights = 0;
 
@@ -48,11 +55,12 @@ struct yafgpu_ctx
 
 	// stats
 	yafgpu_stats stats;
-	int leaf_max = 1;                         // yafgpu_set_option("leaf_size"): BVH leaf collapse threshold used by the NEXT upload
-	int ray_regeneration = -1;                // yafgpu_set_option("ray_regeneration"): wavefront trace kernels use the warp-persistent traversal
+	int leaf_max = YG_DEFAULT_LEAF;                         // yafgpu_set_option("leaf_size"): BVH leaf collapse threshold used by the NEXT upload
+	int ray_regeneration = -1;                // yafgpu_set_option("ray_regeneration"): -1 = library default (YG_DEFAULT_REGEN), 0 none, 1 both kernels, 2 closest-hit only, 3 shadow only
+	int regen_threshold = 20;                 // yafgpu_set_option("regen_threshold"): refill a warp as soon as fewer lanes than this are busy
+	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	int *d_fault = nullptr, *h_fault = nullptr; // traversal-stack fault word (Accel::fault) and its pinned mirror
 	int stack_limit = 0;                      // yafgpu_set_option("debug_stack_limit"): 0 = YG_STACK
-	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	cudaStream_t side[2] = {nullptr, nullptr};   // the per-type shading kernels of one iteration run side by side (integrator.cu)

@@ -289,17 +289,18 @@ struct TraceIO
 	}
 };
 
-// REGEN = false: task i -> thread i (grid-stride), the warp's 32 consecutive tasks stay together — the default, because queue
-//                order is spatially coherent (tile order, then per-material runs) and that coherence is worth more than full lanes;
-// REGEN = true : warp-persistent traversal with ray regeneration (traverse.cuh) — faster on uncorrelated rays (+9 % closest,
-//                +16 % any-hit on 2^24 random rays in the 10^7-triangle mesh), slower on the wavefront queues (profiles/r1_traversal.md).
+// task i -> thread i (grid-stride): the warp's 32 consecutive tasks stay together — queue order is spatially coherent (tile order, then
+// per-material runs), which is worth more than full lanes once the BVH exceeds the caches (profiles/r1_traversal.md).
+// REGEN: warp-persistent schedule with ray regeneration (traverse.cuh traversePersistent) instead of task i -> thread i.
 template<bool COUNT, bool REGEN>
-__global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int *__restrict__ n_tasks, int task_cap, SortBins bins, int *__restrict__ next,
+__global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int *__restrict__ n_tasks, int task_cap, SortBins bins, int *__restrict__ next, int refill_below,
                                                unsigned long long *__restrict__ counters)
 {
 	const int n = min(*n_tasks, task_cap);
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
 	TraceIO io; io.q = q; io.bins = bins;
+	__shared__ uint2 s_stack[YG_STACK_SHARED * 128];
+	TravStack<YG_STACK_SHARED> st; bindSharedStack(st, s_stack);
 	// bucket counts go to a per-block shared histogram first: with a handful of materials every warp of the grid would otherwise
 	// hit the same few L2 addresses (2.6e5 same-address atomics per 8 M tasks serialise in one L2 slice)
 	extern __shared__ int s_hist[];
@@ -311,8 +312,7 @@ __global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int
 		__syncthreads();
 		io.bins.hist = s_hist;
 	}
-	// refill threshold 14 instead of 22: this schedule is only the default on cache-resident scenes, where the plateau is 8..16 (profiles/r1n_regen_ab.log)
-	if(REGEN) traversePersistent<false, COUNT>(acc, n, next, io, &tc, 14);
+	if(REGEN) traversePersistent<false, COUNT>(acc, n, next, io, st, &tc, refill_below);
 	else
 	{
 		const int stride = gridDim.x * blockDim.x;
@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int
 			float dist;
 			io.load(i, r.o, r.d, r.tmin, dist);
 			r.tmax = dist;
-			io.store(i, traceClosest<COUNT>(acc, r, &tc), vmask);
+			io.store(i, traceClosestS<COUNT>(acc, r, st, &tc), vmask);
 		}
 	}
 	if(block_hist)
@@ -812,52 +812,30 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 // TriKdTree::intersectTs kdtree_triangle.cc:983-1162: every shadow-visible triangle in (tmin, dist); opaque -> blocked;
 // transparent -> filt *= getTransparency, at most max_depth of them (a BVH holds each triangle once, so the reference's
 // std::set of already-filtered triangles is implicit).
-__device__ bool traceShadowTransp(const SceneDev &sc, V3 o, V3 d, float tmin, float dist, int max_depth, Col &filt)
+struct TranspF
 {
-	const Accel &acc = sc.accel;
-	filt = mkc(1.f);
-	if(acc.n_tris == 0) return false;
-	const V3 id = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
-	int stack[YG_STACK];
-	int sp_ = 0, cur = acc.root, depth = 0;
-	for(;;)
+	const SceneDev *sc; V3 o, d; float tmin; int max_depth, depth; Col filt; bool blocked;
+	__device__ __forceinline__ bool operator()(const float4 e1i, const float4 e2f, float t, float u, float v, float &z)
 	{
-		if(cur >= 0)
-		{
-			const BvhNode *nd = acc.nodes + cur;
-			const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
-			float ta, tb;
-			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, 0.f, dist, ta);
-			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, 0.f, dist, tb);
-			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-			if(ha && hb) { cur = ca; if(sp_ < acc.stack_limit) stack[sp_++] = cb; else stackFault(acc); continue; }
-			if(ha) { cur = ca; continue; }
-			if(hb) { cur = cb; continue; }
-		}
-		else
-		{
-			const int code = ~cur;
-			const int first = code >> 3, count = (code & 7) + 1;
-			for(int k = 0; k < count; ++k)
-			{
-				const TriAccel *tp = acc.tris + first + k;
-				const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
-				float t, u, v;
-				if(!triIntersect(v0e, e1i, e2f, o, d, t, u, v)) continue;
-				const int fl = __float_as_int(e2f.w);
-				if(!(t < dist && t >= tmin && (fl & TRI_VIS_SHADOW))) continue;
-				if(!(fl & TRI_TRANSPARENT)) return true;
-				if(depth >= max_depth) return true;
-				SurfPt sp;
-				getSurface(sc, __float_as_int(e1i.w), u, v, o + t * d, sp);
-				filt = filt * matTransparency(sc, sc.materials[sp.mat], sp, d);
-				++depth;
-			}
-		}
-		if(sp_ == 0) break;
-		cur = stack[--sp_];
+		const int fl = __float_as_int(e2f.w);
+		if(!(t < z && t >= tmin && (fl & TRI_VIS_SHADOW))) return false;
+		if(!(fl & TRI_TRANSPARENT) || depth >= max_depth) { blocked = true; return true; }
+		SurfPt sp;
+		getSurface(*sc, __float_as_int(e1i.w), u, v, o + t * d, sp);
+		filt = filt * matTransparency(*sc, sc->materials[sp.mat], sp, d);
+		++depth;
+		return false;
 	}
-	return false;
+};
+
+template<int NS>
+__device__ bool traceShadowTransp(const SceneDev &sc, V3 o, V3 d, float tmin, float dist, int max_depth, Col &filt, TravStack<NS> &st)
+{
+	TranspF f; f.sc = &sc; f.o = o; f.d = d; f.tmin = tmin; f.max_depth = max_depth; f.depth = 0; f.filt = mkc(1.f); f.blocked = false;
+	float z = dist;
+	traverseWide<false, false, NS>(sc.accel, o, d, 0.f, z, st, f, nullptr);
+	filt = f.filt;
+	return f.blocked;
 }
 
 struct ShadowIO
@@ -882,36 +860,36 @@ struct ShadowIO
 // opaque shadows: any-hit traversal (REGEN as in k_trace); transparent shadows (transpShad): filter accumulation along the segment
 template<bool COUNT, bool REGEN>
 __global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ SceneDev sc, ShadowQueue sq, const int *__restrict__ n_shadow, int shadow_cap, float4 *__restrict__ acc,
-                                                int *__restrict__ next, unsigned long long *__restrict__ counters)
+                                                int *__restrict__ next, int refill_below, unsigned long long *__restrict__ counters)
 {
 	const int n = min(*n_shadow, shadow_cap);
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
+	__shared__ uint2 s_stack[YG_STACK_SHARED * 128];
+	TravStack<YG_STACK_SHARED> st; bindSharedStack(st, s_stack);
 	if(REGEN && !sc.integ.tr_shad)
 	{
 		ShadowIO io; io.sq = sq; io.acc = acc;
-		traversePersistent<true, COUNT>(sc.accel, n, next, io, &tc);
+		traversePersistent<true, COUNT>(sc.accel, n, next, io, st, &tc, refill_below);
 	}
 	else
+	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
 	{
-		for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+		const float4 a = sq.ray_o[i], b = sq.ray_d[i], c = sq.contrib[i];
+		const V3 dir = mk(b.x, b.y, b.z);
+		// Scene::isShadowed scene.cc:965-970: shift the origin by tmin, shorten the segment by 2 tmin
+		const V3 o = mk(a.x, a.y, a.z) + dir * a.w;
+		const float dist = (b.w < 0.f) ? __int_as_float(0x7f800000) : b.w - 2 * a.w;
+		Col contrib = mkc(c.x, c.y, c.z);
+		if(sc.integ.tr_shad)
 		{
-			const float4 a = sq.ray_o[i], b = sq.ray_d[i], c = sq.contrib[i];
-			const V3 dir = mk(b.x, b.y, b.z);
-			// Scene::isShadowed scene.cc:965-970: shift the origin by tmin, shorten the segment by 2 tmin
-			const V3 o = mk(a.x, a.y, a.z) + dir * a.w;
-			const float dist = (b.w < 0.f) ? __int_as_float(0x7f800000) : b.w - 2 * a.w;
-			Col contrib = mkc(c.x, c.y, c.z);
-			if(sc.integ.tr_shad)
-			{
-				Col filt;
-				if(traceShadowTransp(sc, o, dir, a.w, dist, sc.integ.s_depth, filt)) continue;
-				contrib = contrib * filt;
-			}
-			else if(traceShadow<COUNT>(sc.accel, o, dir, dist, &tc) >= 0) continue;
-			accAdd(acc, __float_as_int(c.w), contrib);
+			Col filt;
+			if(traceShadowTransp(sc, o, dir, a.w, dist, sc.integ.s_depth, filt, st)) continue;
+			contrib = contrib * filt;
 		}
+		else if(traceShadowS<COUNT>(sc.accel, o, dir, dist, st, &tc) >= 0) continue;
+		accAdd(acc, __float_as_int(c.w), contrib);
 	}
-	if(COUNT) { atomicAdd(&counters[CNT_NODES], tc.nodes); atomicAdd(&counters[CNT_TRIS], tc.tris); }
+	if(COUNT) { atomicAdd(&counters[CNT_NODES_SHADOW], tc.nodes); atomicAdd(&counters[CNT_TRIS_SHADOW], tc.tris); }
 }
 
 // ---- K9: ImageFilm::addSample imagefilm.cc:925-1015 (Combined pass) --------------------------------------------------------
@@ -1043,10 +1021,10 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 {
 	Wavefront &w = c->wf;
 	cudaStream_t st = c->stream;
-	const bool count = (c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL) != 0, regen_s = c->ray_regeneration == 1 || c->ray_regeneration == 3;
-	// auto (-1): the closest-hit kernel regenerates rays when the whole BVH is cache resident — there lane divergence (12.5 of 32 lanes per instruction
-	// on the Cornell bench), not memory coherence, is what limits it: +1.8 % on the bench, neutral at 10^7 triangles, -6 % on config 4 (profiles/r1n_regen_ab.log)
-	const bool regen_t = c->ray_regeneration >= 0 ? (c->ray_regeneration == 1 || c->ray_regeneration == 2) : c->scene.accel.n_tris <= 4096;
+	const bool count = (c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL) != 0;
+	const int rr = c->ray_regeneration >= 0 ? c->ray_regeneration : YG_DEFAULT_REGEN;
+	const bool regen_t = rr == 1 || rr == 2, regen_s = rr == 1 || rr == 3;
+	const int refill = c->regen_threshold;
 	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
 	YG_CUDA(c, cudaMemsetAsync(w.ctl, 0, sizeof(WaveCtl), st));
 	YG_CUDA(c, cudaMemsetAsync(w.acc, 0, sizeof(float4) * (size_t)wp.n_slots, st));
@@ -1067,7 +1045,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		const int nb = 2 * c->n_mat_buckets + 1;
 		cudaMemsetAsync(w.hist, 0, sizeof(int) * nb, st);
 		const size_t hist_smem = nb <= YG_SHARED_BUCKETS ? sizeof(int) * nb : 0;
-#define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, hist_smem, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], c->d_counters)
+#define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, hist_smem, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], refill, c->d_counters)
 		if(count) { if(regen_t) YG_TRACE(true, true); else YG_TRACE(true, false); } else { if(regen_t) YG_TRACE(false, true); else YG_TRACE(false, false); }
 #undef YG_TRACE
 		mark();
@@ -1095,7 +1073,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		k_shade<MT_MISS, 2><<<gs, 128, 0, shadeStream()>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
 		if(n_str > 1) for(int k = 0; k < n_str - 1; ++k) { cudaEventRecord(c->ev_join[k], c->side[k]); cudaStreamWaitEvent(st, c->ev_join[k], 0); }
 		mark();
-#define YG_SHADOW(C, R) k_shadow<C, R><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, &w.ctl->fetch_shadow[it], c->d_counters)
+#define YG_SHADOW(C, R) k_shadow<C, R><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, &w.ctl->fetch_shadow[it], refill, c->d_counters)
 		if(count) { if(regen_s) YG_SHADOW(true, true); else YG_SHADOW(true, false); } else { if(regen_s) YG_SHADOW(false, true); else YG_SHADOW(false, false); }
 #undef YG_SHADOW
 		mark();

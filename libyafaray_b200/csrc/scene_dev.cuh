@@ -18,22 +18,24 @@ enum { TRI_VIS_CAMERA = 1,  // visibility in {Normal, VisibleNoShadows}      kdt
        TRI_TRANSPARENT = 4  // Material::isTransparent()                     kdtree_triangle.cc:1106
 };
 
-// BVH2 node, 64 B = one 4 x float4 burst (two 32 B sectors):
-//   n0 = (c0.min.x, c0.min.y, c0.min.z, c0.max.x)
-//   n1 = (c0.max.y, c0.max.z, c1.min.x, c1.min.y)
-//   n2 = (c1.min.z, c1.max.x, c1.max.y, c1.max.z)
-//   n3 = (bits child0, bits child1, unused, unused)
-// child >= 0: internal node index; child < 0: leaf, ~child = (first << 3) | (count - 1) into the TriAccel array.
-struct BvhNode { float4 n0, n1, n2, n3; };
+// W-wide BVH node, W = 4 (128 B = one cache line) or W = 8 (256 B), float32 child planes in structure-of-arrays form so that one
+// 16-byte load fetches the same plane of four children and the ray's direction signs pick the near / far plane by ADDRESS:
+//   plane a (a = 0..5: lo.x, lo.y, lo.z, hi.x, hi.y, hi.z) of children 4v..4v+3 = float4 at index a * (W/4) + v
+//   links of children 4v..4v+3 = int4 at index 6 * (W/4) + v:  >= 0 inner node index; < 0 leaf, ~link = (first << 3) | (count - 1)
+//   into the TriAccel array; 0x80000000 = no child (its box is inverted, lo = +FLT_MAX > hi, so the box test alone rejects it)
+//   float4 at index 7 * (W/4): child count (rest of the node is padding)
+// The TriAccel records stay full float32: the boxes only cull, Triangle::intersect decides.
+#define YG_NO_CHILD ((int)0x80000000)
 
 struct Accel
 {
-	const BvhNode *nodes;
+	const uint4 *nodes;
 	const TriAccel *tris;
 	int n_nodes, n_tris;
-	int root;          // encoded like a child (a 1-triangle scene has a leaf root)
+	int root;          // encoded like a link (a scene of up to leaf_max triangles has a leaf root)
+	int width;         // 4 or 8
 	float bmin[3], bmax[3]; // tree bound grown by 0.1 % as TriKdTree does (kdtree_triangle.cc:112-116)
-	int stack_limit;   // entries of the per-thread traversal stack in use (YG_STACK; lower only through the debug option that tests the fault path)
+	int stack_limit;   // traversal stack entries in use (YG_STACK; lower only through the debug option that tests the fault path)
 	int *fault;        // device word raised by a traversal whose stack overflowed (traverse.cuh stackFault); owned by the context
 };
 

@@ -1,4 +1,4 @@
-// K3/K4 device traversal: closest hit and any hit over the BVH2 of scene_dev.cuh.
+// K3/K4 device traversal: closest hit and any hit over the W-wide BVH of scene_dev.cuh.
 //
 // Semantics follow the reference, not a generic ray tracer:
 //   closest : Scene::intersect -> TriKdTree::intersect (/root/reference/src/common/scene.cc:896-927, kdtree_triangle.cc:684-837)
@@ -10,6 +10,15 @@
 //             a, edge_1, edge_2, eps, same operation order, no FMA contraction (-fmad=false).
 // Equal-t candidates: the kd-tree keeps the first one it visits (strict <); a BVH visits in another order, so the tie is
 // broken deterministically towards the LOWER global triangle id (documented tie rule).
+//
+// Only the triangle test is parity-critical; the box tests merely cull and are free to be fast: the near / far plane of every child
+// is fetched by address from the direction signs and tested in t-space with one fused multiply-add (t = plane / d - o / d), children
+// are visited nearest first, the rest pushed farthest first with their entry distance so that a popped entry beyond the current hit
+// costs no node fetch.  The loop is "while-while" (Aila & Laine 2009): all lanes first descend through inner nodes until each holds
+// a leaf, then run Möller–Trumbore together — the kernel is bound by instruction issue at ~10 of 32 active lanes (profiles/r2b_*),
+// so keeping the two code paths apart is worth more than anything that saves bytes.
+// The first YG_STACK_SHARED entries of the per-ray stack live in shared memory (one 8-byte column per thread), the tail in local
+// memory; a full stack raises Accel::fault (the host turns it into an error) instead of dropping the subtree silently.
 #pragma once
 #include "scene_dev.cuh"
 
@@ -18,7 +27,14 @@ namespace yg {
 struct RayD { V3 o; float tmin; V3 d; float tmax; };
 struct HitD { float t, u, v; int tri; };
 
-#define YG_STACK 96
+#ifndef YG_BVH_WIDTH
+#define YG_BVH_WIDTH 4
+#endif
+#define YG_STACK 64          /* entries per ray: link + entry distance, 8 B each */
+#ifndef YG_STACK_SHARED
+#define YG_STACK_SHARED 16   /* of which in shared memory in the kernels that provide it (16 x 8 B x 128 threads = 16 KB per block) */
+#endif
+#define YG_NODE_U4 (YG_BVH_WIDTH == 4 ? 8 : 16)
 
 // Möller–Trumbore exactly as triangle.h:223-259. Returns true and t,u,v when the reference would return true.
 YG_D bool triIntersect(const float4 v0e, const float4 e1i, const float4 e2f, const V3 o, const V3 d, float &t, float &u, float &v)
@@ -40,162 +56,270 @@ YG_D bool triIntersect(const float4 v0e, const float4 e1i, const float4 e2f, con
 	return true;
 }
 
-// slab test of one child box against [tlo, thi]; conservative (NaN-safe min/max, far side widened by 2 ulp-ish)
-YG_D bool slab(float bx0, float by0, float bz0, float bx1, float by1, float bz1, const V3 o, const V3 id, float tlo, float thi, float &tnear)
-{
-	float t0 = (bx0 - o.x) * id.x, t1 = (bx1 - o.x) * id.x;
-	float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
-	t0 = (by0 - o.y) * id.y; t1 = (by1 - o.y) * id.y;
-	tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
-	t0 = (bz0 - o.z) * id.z; t1 = (bz1 - o.z) * id.z;
-	tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
-	tf *= 1.0000004f;
-	tnear = tn;
-	return tn <= tf && tf >= tlo && tn <= thi;
-}
-
 struct TravCounters { unsigned long long nodes, tris; };
 
-// A traversal stack that is full cannot take the far child: the subtree would be skipped and the image silently wrong.  The entry is
+// A traversal stack that is full cannot take another child: the subtree would be skipped and the image silently wrong.  The entry is
 // still dropped (no memory is touched out of bounds) but the accelerator's fault word is raised; every host entry point that
 // synchronises (yafgpu_trace, yafgpu_render_pass, yafgpu_sync) reads it and fails with YAFGPU_ERR_CUDA instead of returning the result.
 YG_D void stackFault(const Accel &acc) { if(acc.fault) *acc.fault = 1; }
 
-// Closest hit. `dist` = ray.tmax < 0 ? inf : ray.tmax (scene.cc:900-901).
-template<bool COUNT>
-YG_D HitD traceClosest(const Accel &acc, const RayD &r, TravCounters *cnt)
+// Per-ray stack: entries [0, NS) in shared memory (column of this thread: s[i * stride]), the rest in local memory.  NS = 0: all local.
+template<int NS>
+struct TravStack
 {
-	HitD h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.tri = -1;
-	float z = (r.tmax < 0.f) ? __int_as_float(0x7f800000) : r.tmax;
-	const V3 id = mk(1.f / r.d.x, 1.f / r.d.y, 1.f / r.d.z);
-	const float tlo = r.tmin * 0.99f;
-	int stack[YG_STACK];
-	int sp = 0;
-	int cur = acc.root;
-	if(acc.n_tris == 0) return h;
+	uint2 *s; int stride;
+	uint2 l[YG_STACK - NS];
+	__device__ __forceinline__ void put(int i, uint2 v) { if(NS > 0 && i < NS) s[i * stride] = v; else l[i - NS] = v; }
+	__device__ __forceinline__ uint2 get(int i) const { return (NS > 0 && i < NS) ? s[i * stride] : l[i - NS]; }
+};
+
+// 1/d for the box tests only: a zero component becomes +-1e-30 so that no inf/NaN enters the fused arithmetic (the box of a ray
+// parallel to an axis is then tested with slopes of 1e30, which decides "inside the slab or not" exactly as it should)
+__device__ __forceinline__ float safeInv(float d) { return 1.f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
+
+__device__ __forceinline__ float comp4(const float4 v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
+
+// Per-ray traversal state: the constants of the box test, the search interval and the stack position.
+struct TravRay
+{
+	V3 o, d;
+	float idx, idy, idz, ox, oy, oz;   // 1/d (safe) and -o/d
+	int nx, ny, nz;                    // float4 index of the near plane of each axis inside a node (far = 3V / 5V / 7V - near)
+	float tlo, z;                      // box tests clip to [tlo, z]; z is the far limit of the search (the closest hit so far)
+	int cur, sp;
+	__device__ __forceinline__ void start(const Accel &acc, const V3 o_, const V3 d_, float tlo_, float z_)
+	{
+		constexpr int V = YG_BVH_WIDTH / 4;
+		o = o_; d = d_;
+		idx = safeInv(d.x); idy = safeInv(d.y); idz = safeInv(d.z);
+		ox = -o.x * idx; oy = -o.y * idy; oz = -o.z * idz;
+		nx = idx >= 0.f ? 0 : 3 * V; ny = idy >= 0.f ? V : 4 * V; nz = idz >= 0.f ? 2 * V : 5 * V;
+		tlo = fmaxf(tlo_, 0.f); z = z_;
+		sp = 0; cur = acc.n_tris != 0 ? acc.root : YG_NO_CHILD;
+	}
+};
+
+// nearest pending subtree that can still hold something closer than z, or YG_NO_CHILD
+template<int NS>
+__device__ __forceinline__ int popNext(TravRay &r, const TravStack<NS> &st)
+{
+	while(r.sp > 0)
+	{
+		const uint2 e = st.get(--r.sp);
+		if(__uint_as_float(e.y) <= r.z * 1.0000004f) return (int)e.x;
+	}
+	return YG_NO_CHILD;
+}
+
+// One inner node (r.cur >= 0): box tests of its W children; r.cur becomes the nearest hit child (ORDERED) or the first one, the others
+// are pushed (farthest first when ORDERED); with no child hit the next pending subtree is popped.
+// The ordering is branch-free: (entry distance | slot, link) pairs go through a sorting network, misses sort last, then W - 1
+// predicated pushes.  (A loop "extract the farthest, push it" ran at 3.3 of 32 lanes and took 17 % of the kernel's issue slots,
+// profiles/r2c_ncu_k_trace_bvh4_fp32_regen.txt.)
+#define YG_CX(a, b) { const bool sw_ = key[b] < key[a]; const unsigned ka_ = sw_ ? key[b] : key[a], kb_ = sw_ ? key[a] : key[b]; \
+                      const int la_ = sw_ ? link[b] : link[a], lb_ = sw_ ? link[a] : link[b]; key[a] = ka_; key[b] = kb_; link[a] = la_; link[b] = lb_; }
+template<bool ORDERED, bool COUNT, int NS>
+__device__ __forceinline__ void nodeStep(const Accel &acc, TravRay &r, TravStack<NS> &st, TravCounters *cnt)
+{
+	constexpr int W = YG_BVH_WIDTH, V = W / 4;
+	const float4 *nd = (const float4 *)acc.nodes + (size_t)r.cur * YG_NODE_U4;
+	if(COUNT) cnt->nodes++;
+	const float zf = r.z * 1.0000004f;
+	const int fx = 3 * V - r.nx, fy = 5 * V - r.ny, fz = 7 * V - r.nz;
+	const int limit = acc.stack_limit;
+	unsigned key[W];   // entry distance bits with the slot in the low 3 bits; 0xffffffff = missed
+	int link[W];
+#pragma unroll
+	for(int v = 0; v < V; ++v)
+	{
+		const float4 pnx = __ldg(nd + r.nx + v), pny = __ldg(nd + r.ny + v), pnz = __ldg(nd + r.nz + v);
+		const float4 pfx = __ldg(nd + fx + v), pfy = __ldg(nd + fy + v), pfz = __ldg(nd + fz + v);
+		const float4 lk = __ldg(nd + 6 * V + v);
+#pragma unroll
+		for(int j = 0; j < 4; ++j)
+		{
+			const int k = 4 * v + j;
+			const float tn = fmaxf(fmaxf(fmaf(comp4(pnx, j), r.idx, r.ox), fmaf(comp4(pny, j), r.idy, r.oy)), fmaxf(fmaf(comp4(pnz, j), r.idz, r.oz), r.tlo));
+			const float tf = fminf(fminf(fmaf(comp4(pfx, j), r.idx, r.ox), fmaf(comp4(pfy, j), r.idy, r.oy)), fminf(fmaf(comp4(pfz, j), r.idz, r.oz), zf));
+			link[k] = __float_as_int(comp4(lk, j));
+			// the boxes carry an absolute pad of 2^-19 of the scene size (bvh_build.cu), which covers the rounding of these six products;
+			// an absent child has an inverted box and fails here
+			key[k] = (tn <= tf) ? ((__float_as_uint(tn) & ~7u) | (unsigned)k) : 0xffffffffu;
+		}
+	}
+	if(ORDERED)
+	{
+		if(W == 4) { YG_CX(0, 1) YG_CX(2, 3) YG_CX(0, 2) YG_CX(1, 3) YG_CX(1, 2) }
+		else
+		{	// 19-comparator network for 8 keys
+			YG_CX(0, 1) YG_CX(2, 3) YG_CX(W - 4, W - 3) YG_CX(W - 2, W - 1) YG_CX(0, 2) YG_CX(1, 3) YG_CX(W - 4, W - 2) YG_CX(W - 3, W - 1) YG_CX(1, 2) YG_CX(W - 3, W - 2)
+			YG_CX(0, W - 4) YG_CX(1, W - 3) YG_CX(2, W - 2) YG_CX(3, W - 1) YG_CX(2, W - 4) YG_CX(3, W - 3) YG_CX(1, 2) YG_CX(3, W - 4) YG_CX(W - 3, W - 2)
+		}
+#pragma unroll
+		for(int k = W - 1; k >= 1; --k)
+			if(key[k] != 0xffffffffu) { if(r.sp < limit) st.put(r.sp++, make_uint2((unsigned)link[k], key[k] & ~7u)); else stackFault(acc); }
+		r.cur = key[0] != 0xffffffffu ? link[0] : popNext(r, st);
+	}
+	else
+	{
+		int next = YG_NO_CHILD;
+#pragma unroll
+		for(int k = 0; k < W; ++k)
+		{
+			if(key[k] == 0xffffffffu) continue;
+			if(next == YG_NO_CHILD) next = link[k];
+			else if(r.sp < limit) st.put(r.sp++, make_uint2((unsigned)link[k], key[k] & ~7u)); else stackFault(acc);
+		}
+		r.cur = next != YG_NO_CHILD ? next : popNext(r, st);
+	}
+}
+#undef YG_CX
+
+// One leaf link (< 0, not YG_NO_CHILD): Triangle::intersect on its triangles; f decides.  Returns true when f ended the search.
+template<bool COUNT, class F>
+__device__ __forceinline__ bool leafTest(const Accel &acc, TravRay &r, int link, F &f, TravCounters *cnt)
+{
+	const int code = ~link;
+	const int first = code >> 3, count = (code & 7) + 1;
+	for(int k = 0; k < count; ++k)
+	{
+		const TriAccel *tp = acc.tris + first + k;
+		const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
+		if(COUNT) cnt->tris++;
+		float t, u, v;
+		if(!triIntersect(v0e, e1i, e2f, r.o, r.d, t, u, v)) continue;
+		if(f(e1i, e2f, t, u, v, r.z)) return true;
+	}
+	return false;
+}
+
+// Node phase of one lane: descend until the lane is blocked on a leaf.  With POSTPONE the first leaf met is set aside (`stash`) and the
+// descent goes on with the next pending subtree, so that the lane stays in the node loop with the rest of its warp instead of idling
+// until every other lane has found a leaf of its own (the node loop ran at 11.5 of 32 lanes without this, profiles/r2c_*); the leaf
+// test is order-independent (the closest hit is the minimum over all accepted triangles), only the shrinking of z is delayed.
+#ifndef YG_POSTPONE
+#define YG_POSTPONE 1
+#endif
+template<bool ORDERED, bool COUNT, bool POSTPONE, int NS>
+__device__ __forceinline__ void nodePhase(const Accel &acc, TravRay &r, int &stash, TravStack<NS> &st, TravCounters *cnt)
+{
 	for(;;)
 	{
-		if(cur >= 0)
-		{
-			const BvhNode *nd = acc.nodes + cur;
-			const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
-			if(COUNT) cnt->nodes++;
-			float ta, tb;
-			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, r.o, id, tlo, z, ta);
-			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, r.o, id, tlo, z, tb);
-			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-			if(ha && hb)
-			{
-				const bool a_first = ta <= tb;
-				cur = a_first ? ca : cb;
-				if(sp < acc.stack_limit) stack[sp++] = a_first ? cb : ca; else stackFault(acc);
-				continue;
-			}
-			if(ha) { cur = ca; continue; }
-			if(hb) { cur = cb; continue; }
-		}
-		else
-		{
-			const int code = ~cur;
-			const int first = code >> 3, count = (code & 7) + 1;
-			for(int k = 0; k < count; ++k)
-			{
-				const TriAccel *tp = acc.tris + first + k;
-				const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
-				if(COUNT) cnt->tris++;
-				float t, u, v;
-				if(!triIntersect(v0e, e1i, e2f, r.o, r.d, t, u, v)) continue;
-				if(!(__float_as_int(e2f.w) & TRI_VIS_CAMERA)) continue;
-				const int id_ = __float_as_int(e1i.w);
-				if(t >= r.tmin && (t < z || (t == z && h.tri >= 0 && id_ < h.tri)))
-				{
-					z = t; h.t = t; h.u = u; h.v = v; h.tri = id_;
-				}
-			}
-		}
-		if(sp == 0) break;
-		cur = stack[--sp];
+		if(r.cur >= 0) nodeStep<ORDERED, COUNT>(acc, r, st, cnt);
+		else if(POSTPONE && r.cur != YG_NO_CHILD && stash == YG_NO_CHILD) { stash = r.cur; r.cur = popNext(r, st); }
+		else break;
 	}
-	return h;
+}
+
+// Leaf phase of one lane: the postponed leaf, then the one in hand.  Returns true when f ended the search.
+template<bool COUNT, int NS, class F>
+__device__ __forceinline__ bool leafPhase(const Accel &acc, TravRay &r, int &stash, TravStack<NS> &st, F &f, TravCounters *cnt)
+{
+	if(stash != YG_NO_CHILD)
+	{
+		const int l = stash; stash = YG_NO_CHILD;
+		if(leafTest<COUNT>(acc, r, l, f, cnt)) { r.cur = YG_NO_CHILD; return true; }
+	}
+	if(r.cur != YG_NO_CHILD && r.cur < 0)
+	{
+		if(leafTest<COUNT>(acc, r, r.cur, f, cnt)) { r.cur = YG_NO_CHILD; return true; }
+		r.cur = popNext(r, st);
+	}
+	return false;
+}
+
+// One ray, start to finish ("while-while").  F: bool f(e1i, e2f, t, u, v, float &z) — called for every triangle Triangle::intersect
+// accepts; may lower z; returns true to end the traversal.  ORDERED: visit children nearest first (closest hit); else in slot order.
+template<bool ORDERED, bool COUNT, int NS, class F>
+__device__ __forceinline__ void traverseWide(const Accel &acc, const V3 o, const V3 d, float tlo, float &z, TravStack<NS> &st, F &f, TravCounters *cnt)
+{
+	TravRay r;
+	r.start(acc, o, d, tlo, z);
+	int stash = YG_NO_CHILD;
+	while(r.cur != YG_NO_CHILD)
+	{
+		nodePhase<ORDERED, COUNT, ORDERED && YG_POSTPONE>(acc, r, stash, st, cnt);
+		if(leafPhase<COUNT>(acc, r, stash, st, f, cnt)) break;
+	}
+	z = r.z;
+}
+
+// ---- the two searches of the reference --------------------------------------------------------------------------------------------
+struct ClosestF
+{
+	float tmin; HitD h;
+	__device__ __forceinline__ bool operator()(const float4 e1i, const float4 e2f, float t, float u, float v, float &z)
+	{
+		if(!(__float_as_int(e2f.w) & TRI_VIS_CAMERA)) return false;
+		const int id_ = __float_as_int(e1i.w);
+		if(t >= tmin && (t < z || (t == z && h.tri >= 0 && id_ < h.tri))) { z = t; h.t = t; h.u = u; h.v = v; h.tri = id_; }
+		return false;
+	}
+};
+
+struct AnyF
+{
+	int tri;
+	__device__ __forceinline__ bool operator()(const float4 e1i, const float4 e2f, float t, float, float, float &z)
+	{
+		if(t < z && t >= 0.f && (__float_as_int(e2f.w) & TRI_VIS_SHADOW)) { tri = __float_as_int(e1i.w); return true; }
+		return false;
+	}
+};
+
+// Closest hit. `dist` = ray.tmax < 0 ? inf : ray.tmax (scene.cc:900-901).
+template<bool COUNT, int NS>
+__device__ __forceinline__ HitD traceClosestS(const Accel &acc, const RayD &r, TravStack<NS> &st, TravCounters *cnt)
+{
+	ClosestF f; f.tmin = r.tmin; f.h.t = 0.f; f.h.u = 0.f; f.h.v = 0.f; f.h.tri = -1;
+	float z = (r.tmax < 0.f) ? __int_as_float(0x7f800000) : r.tmax;
+	traverseWide<true, COUNT, NS>(acc, r.o, r.d, r.tmin * 0.99f, z, st, f, cnt);
+	return f.h;
 }
 
 // Any hit for opaque shadows. The caller passes the ALREADY SHIFTED origin and dist (scene.cc:965-970).
 // Returns the global id of a blocker (any), or -1.
-template<bool COUNT>
-YG_D int traceShadow(const Accel &acc, const V3 o, const V3 d, float dist, TravCounters *cnt)
+template<bool COUNT, int NS>
+__device__ __forceinline__ int traceShadowS(const Accel &acc, const V3 o, const V3 d, float dist, TravStack<NS> &st, TravCounters *cnt)
 {
-	if(acc.n_tris == 0) return -1;
-	const V3 id = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
-	int stack[YG_STACK];
-	int sp = 0;
-	int cur = acc.root;
-	for(;;)
-	{
-		if(cur >= 0)
-		{
-			const BvhNode *nd = acc.nodes + cur;
-			const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
-			if(COUNT) cnt->nodes++;
-			float ta, tb;
-			const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, 0.f, dist, ta);
-			const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, 0.f, dist, tb);
-			const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-			if(ha && hb) { cur = ca; if(sp < acc.stack_limit) stack[sp++] = cb; else stackFault(acc); continue; }
-			if(ha) { cur = ca; continue; }
-			if(hb) { cur = cb; continue; }
-		}
-		else
-		{
-			const int code = ~cur;
-			const int first = code >> 3, count = (code & 7) + 1;
-			for(int k = 0; k < count; ++k)
-			{
-				const TriAccel *tp = acc.tris + first + k;
-				const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
-				if(COUNT) cnt->tris++;
-				float t, u, v;
-				if(!triIntersect(v0e, e1i, e2f, o, d, t, u, v)) continue;
-				if(t < dist && t >= 0.f && (__float_as_int(e2f.w) & TRI_VIS_SHADOW)) return __float_as_int(e1i.w);
-			}
-		}
-		if(sp == 0) break;
-		cur = stack[--sp];
-	}
-	return -1;
+	AnyF f; f.tri = -1;
+	float z = dist;
+	traverseWide<false, COUNT, NS>(acc, o, d, 0.f, z, st, f, cnt);
+	return f.tri;
+}
+
+// all-local-stack flavours for code that runs outside the traversal kernels (mesh-light intersection inside the shading kernels)
+template<bool COUNT>
+YG_D HitD traceClosest(const Accel &acc, const RayD &r, TravCounters *cnt)
+{
+	TravStack<0> st; st.s = nullptr; st.stride = 0;
+	return traceClosestS<COUNT, 0>(acc, r, st, cnt);
 }
 
 // ---- warp-persistent traversal with ray regeneration ------------------------------------------------------------------------
-// The wavefront kernels do not map ray i to thread i.  Every warp keeps 32 rays in flight; a lane whose ray has finished stores
-// its result and takes the next unprocessed ray from a global counter (one warp-aggregated atomicAdd per refill), so lanes do not
-// idle until the slowest ray of their warp is done.  Inside, traversal is "while-while": all lanes first descend through inner
-// nodes until each holds a leaf (or has nothing left), then all process their leaf together, so the node loop and the
-// Möller–Trumbore loop each run with most lanes active instead of interleaving per lane.
+// The kernel is bound by instruction issue, and a warp that maps ray i to lane i issues for as long as its SLOWEST ray lives (node
+// visits per ray spread from a handful to ~100).  Here every warp keeps 32 rays in flight instead: a lane whose ray has finished
+// stores its result and takes the next unprocessed ray from a global counter (one warp-aggregated atomicAdd per refill), as soon as
+// fewer than `refill_below` lanes are still busy.  Inside, the loop is the same while-while as traverseWide.
 //
 // IO supplies:  void load(int idx, V3 &o, V3 &d, float &tmin, float &dist)
 //               void store(int idx, const HitD &h, unsigned lanes_storing)   called warp-synchronously by the lanes in `lanes_storing`
-// ANYHIT: Scene::isShadowed semantics (origin already shifted by load, accept t in [0, dist), TRI_VIS_SHADOW, first hit ends the ray);
-// else Scene::intersect semantics (accept t in [tmin, z), TRI_VIS_CAMERA, lowest id at equal t).
-#define YG_EMPTY ((int)0x80000000)
-#ifndef YG_REGEN_THRESH
-#define YG_REGEN_THRESH 22 /* refill as soon as fewer lanes than this are still traversing (tuned on random rays in the 10^7-triangle mesh) */
-#endif
+// ANYHIT: Scene::isShadowed semantics (origin already shifted by load, accept t in [0, dist), TRI_VIS_SHADOW, first hit ends the ray;
+// a blocked ray reports h.tri >= 0); else Scene::intersect semantics.
 #ifndef YG_REGEN_ROUNDS
-#define YG_REGEN_ROUNDS 6
+#define YG_REGEN_ROUNDS 4
 #endif
-
-template<bool ANYHIT, bool COUNT, class IO>
-__device__ __forceinline__ void traversePersistent(const Accel &acc, int n, int *__restrict__ next, IO &io, TravCounters *cnt, const int refill_below = YG_REGEN_THRESH)
+template<bool ANYHIT, bool COUNT, int NS, class IO>
+__device__ __forceinline__ void traversePersistent(const Accel &acc, int n, int *__restrict__ next, IO &io, TravStack<NS> &st, TravCounters *cnt, const int refill_below)
 {
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x & 31;
 	const unsigned lt_mask = (1u << lane) - 1u;
 	int ray = -1;          // index of the ray this lane works on, -1 = none
-	int cur = YG_EMPTY;    // node to visit next: >= 0 inner node, < 0 leaf code, YG_EMPTY = traversal finished
-	V3 o = mk(0.f), d = mk(0.f), id = mk(0.f);
-	float tmin = 0.f, z = 0.f, tlo = 0.f;
-	HitD h; h.t = 0.f; h.u = 0.f; h.v = 0.f; h.tri = -1;
-	int stack[YG_STACK];
-	int sp = 0;
+	int stash = YG_NO_CHILD;
+	TravRay r; r.cur = YG_NO_CHILD; r.sp = 0;
+	ClosestF fc; fc.tmin = 0.f; fc.h.t = 0.f; fc.h.u = 0.f; fc.h.v = 0.f; fc.h.tri = -1;
+	AnyF fa; fa.tri = -1;
 	bool exhausted = false; // the global counter has run past n
 	for(;;)
 	{
@@ -213,77 +337,39 @@ __device__ __forceinline__ void traversePersistent(const Accel &acc, int n, int 
 				const int idx = base + __popc(idle & lt_mask);
 				if(idx < n)
 				{
-					float dist;
+					V3 o, d; float tmin, dist;
 					io.load(idx, o, d, tmin, dist);
 					ray = idx;
-					id = mk(1.f / d.x, 1.f / d.y, 1.f / d.z);
-					z = dist; tlo = ANYHIT ? 0.f : tmin * 0.99f;
-					h.t = 0.f; h.u = 0.f; h.v = 0.f; h.tri = -1;
-					sp = 0; cur = acc.n_tris != 0 ? acc.root : YG_EMPTY;
+					r.start(acc, o, d, ANYHIT ? 0.f : tmin * 0.99f, dist);
+					fc.tmin = tmin; fc.h.t = 0.f; fc.h.u = 0.f; fc.h.v = 0.f; fc.h.tri = -1; fa.tri = -1;
 				}
 			}
 		}
 		if(__all_sync(FULL, ray < 0)) { if(exhausted) break; else continue; }
 
 		// ---- a few while-while rounds, then look for lanes to refill ----
-		#pragma unroll 1
+#pragma unroll 1
 		for(int round = 0; round < YG_REGEN_ROUNDS; ++round)
 		{
-			// node phase: descend until this lane holds a leaf or has finished
-			while(cur >= 0)
-			{
-				const BvhNode *nd = acc.nodes + cur;
-				const float4 n0 = __ldg(&nd->n0), n1 = __ldg(&nd->n1), n2 = __ldg(&nd->n2), n3 = __ldg(&nd->n3);
-				if(COUNT) cnt->nodes++;
-				float ta, tb;
-				const bool ha = slab(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, id, tlo, z, ta);
-				const bool hb = slab(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, id, tlo, z, tb);
-				const int ca = __float_as_int(n3.x), cb = __float_as_int(n3.y);
-				if(ha && hb)
-				{
-					const bool a_first = ANYHIT ? true : (ta <= tb);
-					cur = a_first ? ca : cb;
-					if(sp < acc.stack_limit) stack[sp++] = a_first ? cb : ca; else stackFault(acc);
-				}
-				else if(ha) cur = ca;
-				else if(hb) cur = cb;
-				else cur = sp > 0 ? stack[--sp] : YG_EMPTY;
-			}
-			// leaf phase
-			if(cur != YG_EMPTY)
-			{
-				const int code = ~cur;
-				const int first = code >> 3, count = (code & 7) + 1;
-				bool ended = false;
-				for(int k = 0; k < count; ++k)
-				{
-					const TriAccel *tp = acc.tris + first + k;
-					const float4 v0e = __ldg(&tp->v0e), e1i = __ldg(&tp->e1i), e2f = __ldg(&tp->e2f);
-					if(COUNT) cnt->tris++;
-					float t, u, v;
-					if(!triIntersect(v0e, e1i, e2f, o, d, t, u, v)) continue;
-					const int fl = __float_as_int(e2f.w), id_ = __float_as_int(e1i.w);
-					if(ANYHIT)
-					{
-						if(t < z && t >= 0.f && (fl & TRI_VIS_SHADOW)) { h.tri = id_; h.t = 1.f; ended = true; break; }
-					}
-					else
-					{
-						if(!(fl & TRI_VIS_CAMERA)) continue;
-						if(t >= tmin && (t < z || (t == z && h.tri >= 0 && id_ < h.tri))) { z = t; h.t = t; h.u = u; h.v = v; h.tri = id_; }
-					}
-				}
-				cur = (ended || sp == 0) ? YG_EMPTY : stack[--sp];
-			}
-			// leave early when enough lanes have nothing to do
-			if(__popc(__ballot_sync(FULL, ray >= 0 && cur != YG_EMPTY)) < refill_below) break;
+			nodePhase<!ANYHIT, COUNT, !ANYHIT && YG_POSTPONE>(acc, r, stash, st, cnt);
+			if(ANYHIT) leafPhase<COUNT>(acc, r, stash, st, fa, cnt); else leafPhase<COUNT>(acc, r, stash, st, fc, cnt);
+			if(__popc(__ballot_sync(FULL, ray >= 0 && r.cur != YG_NO_CHILD)) < refill_below) break;
 		}
 
 		// ---- store finished rays (warp-synchronous) ----
-		const bool fin = ray >= 0 && cur == YG_EMPTY;
+		const bool fin = ray >= 0 && r.cur == YG_NO_CHILD;
 		const unsigned fin_mask = __ballot_sync(FULL, fin);
-		if(fin) { io.store(ray, h, fin_mask); ray = -1; }
+		if(fin)
+		{
+			HitD h = fc.h;
+			if(ANYHIT) { h.tri = fa.tri; h.t = fa.tri >= 0 ? 1.f : 0.f; }
+			io.store(ray, h, fin_mask);
+			ray = -1;
+		}
 	}
 }
+
+// this thread's column of a block-wide shared stack area of YG_STACK_SHARED * blockDim.x entries
+__device__ __forceinline__ void bindSharedStack(TravStack<YG_STACK_SHARED> &st, uint2 *area) { st.s = area + threadIdx.x; st.stride = blockDim.x; }
 
 } // namespace yg

@@ -195,16 +195,16 @@ def test_film_is_linear_in_sample_ranges_full_size(ctx):
     assert st["camera_samples"] >= 3 * 4 * 1920 * 1080
 
 
-def test_ray_regeneration_schedule_gives_the_same_film(ctx):
-    """The warp-persistent traversal (yafgpu_set_option("ray_regeneration", 1)) changes which lane traces which ray, nothing else."""
+def test_leaf_size_changes_the_tree_not_the_film(ctx):
+    """yafgpu_set_option("leaf_size") changes how many triangles a leaf link of the wide BVH holds, nothing else."""
     from libyafaray_b200 import render_scene
     y = pc.material_zoo_scene(96, 54, 4)
     a = render_scene(y, ctx=ctx)
-    ctx.set_option("ray_regeneration", 1)
+    ctx.set_option("leaf_size", 4)
     try:
         b = render_scene(y, ctx=ctx)
     finally:
-        ctx.set_option("ray_regeneration", 0)
+        ctx.set_option("leaf_size", 2)
     assert np.array_equal(a[..., 4], b[..., 4])
     assert np.abs(a[..., :3] - b[..., :3]).max() <= 1e-4 * float(np.abs(a[..., :3]).max())
 

@@ -61,8 +61,8 @@ def main():
     desc, keep = y.scene_desc()
     ctx = Context(local, capi.FLAG_TIME_STAGES)
     ctx.upload(desc, keep)
-    if "ray_regeneration" in cfg:   # A/B knob: python tools/config_bench.py c3 4 2 ray_regeneration=2
-        ctx.set_option("ray_regeneration", cfg["ray_regeneration"])
+    if "leaf_size" in cfg:   # A/B knob: python tools/config_bench.py c3 4 2 leaf_size=4 (before the upload below? no: re-upload)
+        ctx.set_option("leaf_size", cfg["leaf_size"]); ctx.upload(desc, keep)
     st0 = ctx.stats()
     S = cfg["spp"] * world
     n_chunks = max(1, cfg["pass_spp"] // S)

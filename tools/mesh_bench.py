@@ -15,6 +15,8 @@ ctx = Context(0, flags)
 for a in sys.argv:
     if a.startswith("leaf="):
         ctx.set_option("leaf_size", int(a[5:]))
+    if a.startswith("opt:"):
+        ctx.set_option(a[4:].split("=")[0], int(a.split("=")[1]))
 t0 = time.time(); ctx.upload(desc, keep); t_up = time.time() - t0
 st = ctx.stats()
 out = {"argv": sys.argv[1:], "n_tris": int(desc.geometry.n_tris), "host_scene_s": t_host, "upload_s": t_up, "bvh_build_ms": st["ms_build"], "bvh_nodes": st["bvh_nodes"],
@@ -40,7 +42,8 @@ for mode, key in ((capi.TRACE_CLOSEST, "incoherent_closest"), (capi.TRACE_SHADOW
     ms = e0.elapsed_time(e1) / reps
     s2 = ctx.stats()
     out[key] = {"rays": n, "ms": ms, "mrays_s": n / ms / 1e3, "hit_frac": float((hits[:, 3].view(torch.int32) >= 0).float().mean()) if mode == 0 else float((hits[:, 0] > 0).float().mean()),
-                "nodes_per_ray": s2["nodes_visited"] / (reps * n) if s2["nodes_visited"] else None, "tris_per_ray": s2["tris_tested"] / (reps * n) if s2["tris_tested"] else None}
+                "nodes_per_ray": (s2["nodes_visited"] + s2["nodes_visited_shadow"]) / (reps * n) if s2["nodes_visited"] + s2["nodes_visited_shadow"] else None,
+                "tris_per_ray": (s2["tris_tested"] + s2["tris_tested_shadow"]) / (reps * n) if s2["tris_tested"] + s2["tris_tested_shadow"] else None}
 del rays, hits, o, d
 # wavefront render
 ctx.film_clear(); ctx.render_pass(16, 0, sample_begin=0, sample_end=spp); ctx.sync(); ctx.reset_stats()   # warm-up: same wave size as the timed call
@@ -50,7 +53,12 @@ rays_n = s["rays_camera"] + s["rays_extension"] + s["rays_shadow"] + s["rays_sha
 out["render"] = {"spp": spp, "seconds": t, "mrays_s": rays_n / t / 1e6, "mrays_s_device": rays_n / max(1e-9, s["ms_total"]) / 1e3, "samples_s": s["camera_samples"] / t, "rays_per_sample": rays_n / max(1, s["camera_samples"]),
                  "ms_trace": s["ms_trace"], "ms_shadow": s["ms_shadow"], "ms_shade": s["ms_shade"], "ms_total": s["ms_total"], "waves": s["waves"], "retries": s["wave_retries"],
                  "rays_ext": s["rays_extension"], "rays_shadow": s["rays_shadow"],
-                 "nodes_per_ray": s["nodes_visited"] / max(1, rays_n) if s["nodes_visited"] else None, "tris_per_ray": s["tris_tested"] / max(1, rays_n) if s["tris_tested"] else None}
+                 "nodes_per_ray": (s["nodes_visited"] + s["nodes_visited_shadow"]) / max(1, rays_n) if s["nodes_visited"] else None,
+                 "tris_per_ray": (s["tris_tested"] + s["tris_tested_shadow"]) / max(1, rays_n) if s["tris_tested"] else None,
+                 "closest_nodes_per_ray": s["nodes_visited"] / max(1, s["rays_camera"] + s["rays_extension"]) if s["nodes_visited"] else None,
+                 "closest_tris_per_ray": s["tris_tested"] / max(1, s["rays_camera"] + s["rays_extension"]) if s["nodes_visited"] else None,
+                 "shadow_nodes_per_ray": s["nodes_visited_shadow"] / max(1, s["rays_shadow"]) if s["nodes_visited_shadow"] else None,
+                 "bvh_width": s["bvh_width"], "bvh_node_bytes": s["bvh_node_bytes"], "bvh_levels": s["bvh_levels"]}
 img = ctx.read_film()
 out["render"]["finite"] = bool(np.isfinite(img).all()); out["render"]["mean"] = float((img[..., :3].sum(axis=(0, 1)) / img[..., 4].sum()).mean())
 print(json.dumps(out))
