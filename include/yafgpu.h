@@ -532,9 +532,13 @@ typedef struct yafgpu_stats
 	uint32_t bvh_node_bytes, bvh_width, bvh_levels, reserved0;
 	/* COUNT_TRAVERSAL: nodes_visited / tris_tested above cover closest-hit rays, these the shadow (any-hit) rays */
 	uint64_t nodes_visited_shadow, tris_tested_shadow;
+	/* yafgpu_group_get_stats only: film reductions queued so far and the duration of the most recent one that was read back */
+	uint64_t film_reduces; double ms_film_reduce;
 } yafgpu_stats;
 
-enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2 };
+enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2,
+       YAFGPU_FLAG_SHARE_DEVICE = 4 /* yafgpu_group_create only: the device list may name a GPU more than once (several members share it; exercises the
+                                       partition + film-sum path on a single-GPU box) */ };
 
 /* ---- entry points ---------------------------------------------------------------------- */
 
@@ -591,6 +595,30 @@ int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
 int yafgpu_reset_stats(yafgpu_ctx *ctx);
 /* Raw CUDA stream handle of the context (cudaStream_t), so callers can time with events on the launching stream. */
 void *yafgpu_stream(yafgpu_ctx *ctx);
+
+/* ---- multi-GPU: one scene on N GPUs of one box ------------------------------------------------------------------------
+ * Replaces, for a single 8-GPU node, what the reference does with worker threads pulling tiles from ImageSplitter
+ * (integrator_tiled.cc:223-259, imagesplitter.cc:37-50) and, across machines, with the sum of accumulator films
+ * (ImageFilm::imageFilmLoadAllInFolder, imagefilm.cc:1506-1535): the scene is replicated, member k of N renders the
+ * tile_size x tile_size raster tiles t with t mod N == k of every pass, and after each pass the members' films are summed on the
+ * first device (peer copies over NVLink + an add kernel, asynchronous to the host).  Every call mirrors the single-context call of the
+ * same name; `yafgpu_group_read_film` returns the SUMMED film.  A group of one device behaves exactly like a plain context. */
+typedef struct yafgpu_group yafgpu_group;
+/* devices == NULL or n_devices <= 0: all GPUs of the box */
+int yafgpu_group_create(yafgpu_group **out, const int *devices, int n_devices, unsigned flags);
+void yafgpu_group_destroy(yafgpu_group *g);
+const char *yafgpu_group_last_error(const yafgpu_group *g); /* g may be NULL: error of the last failed yafgpu_group_create */
+int yafgpu_group_size(const yafgpu_group *g);
+yafgpu_ctx *yafgpu_group_ctx(yafgpu_group *g, int member);  /* member context (owned by the group): per-device stats, device pointers */
+int yafgpu_group_upload_scene(yafgpu_group *g, const yafgpu_scene_desc *desc);
+int yafgpu_group_film_clear(yafgpu_group *g);
+int yafgpu_group_write_film(yafgpu_group *g, const float *rgbaw); /* resume: the first member takes the film, the others start from zero */
+int yafgpu_group_render_pass(yafgpu_group *g, const yafgpu_pass_desc *pass); /* part_index / part_count are set per member */
+int yafgpu_group_read_film(yafgpu_group *g, float *rgbaw);
+int yafgpu_group_sync(yafgpu_group *g); /* yafgpu_sync on every member (the first member's stream also carries the film sum) */
+int yafgpu_group_set_aa_multipliers(yafgpu_group *g, float light_mult, float indirect_mult);
+int yafgpu_group_set_option(yafgpu_group *g, const char *name, long long value);
+int yafgpu_group_get_stats(yafgpu_group *g, yafgpu_stats *out); /* counts summed over the members, times of the slowest */
 
 #ifdef __cplusplus
 }

@@ -476,7 +476,7 @@ class GpuIntegrator final : public SurfaceIntegrator
 			integrator_name_ = "GPU " + par<std::string>(params, "type", "");
 			integrator_short_name_ = "GPU";
 		}
-		~GpuIntegrator() override { if(ctx_) yafgpu_destroy(ctx_); }
+		~GpuIntegrator() override { if(grp_) yafgpu_group_destroy(grp_); }
 		bool preprocess() override;
 		bool render(int num_view, ImageFilm *image_film) override;
 		void cleanup() override {}
@@ -485,13 +485,13 @@ class GpuIntegrator final : public SurfaceIntegrator
 	private:
 		bool fail(const std::string &what)
 		{
-			Y_ERROR << integrator_name_ << ": " << what << (ctx_ ? std::string(" — ") + yafgpu_last_error(ctx_) : std::string()) << YENDL;
+			Y_ERROR << integrator_name_ << ": " << what << (grp_ ? std::string(" — ") + yafgpu_group_last_error(grp_) : std::string()) << YENDL;
 			return false;
 		}
 		bool fillIntegrator(yafgpu_integrator_desc &it, std::string &err) const;
 		bool depositFilm(ImageFilm *film);
 		ParamMap params_;
-		yafgpu_ctx *ctx_ = nullptr;
+		yafgpu_group *grp_ = nullptr;   // the GPUs that render this scene: YAFGPU_DEVICES="0,1,2,3" | "all", else YAFGPU_DEVICE (one GPU, default 0)
 		std::vector<float> host_film_, bg_texels_;
 };
 
@@ -530,10 +530,21 @@ bool GpuIntegrator::fillIntegrator(yafgpu_integrator_desc &it, std::string &err)
 bool GpuIntegrator::preprocess()
 {
 	std::string err;
-	if(!ctx_)
-	{
-		const char *dev = getenv("YAFGPU_DEVICE");
-		if(yafgpu_create(&ctx_, dev ? atoi(dev) : 0, 0) != YAFGPU_OK) return fail(std::string("cannot create a CUDA context: ") + yafgpu_last_error(nullptr));
+	if(!grp_)
+	{	// device list: integrator parameter "gpu_devices" (string) or YAFGPU_DEVICES, "all" = every GPU of the box; else one GPU (YAFGPU_DEVICE, default 0)
+		std::string list = par<std::string>(params_, "gpu_devices", "");
+		if(const char *env = getenv("YAFGPU_DEVICES")) list = env;
+		std::vector<int> devs;
+		bool all = list == "all";
+		if(!all && !list.empty())
+		{
+			std::stringstream ss(list);
+			std::string tok;
+			while(std::getline(ss, tok, ',')) if(!tok.empty()) devs.push_back(atoi(tok.c_str()));
+		}
+		if(!all && devs.empty()) { const char *dev = getenv("YAFGPU_DEVICE"); devs.push_back(dev ? atoi(dev) : 0); }
+		if(yafgpu_group_create(&grp_, all ? nullptr : devs.data(), all ? 0 : (int)devs.size(), 0) != YAFGPU_OK)
+			return fail(std::string("cannot create the CUDA contexts: ") + yafgpu_group_last_error(nullptr));
 	}
 	yafgpu_scene_desc d;
 	memset(&d, 0, sizeof(d));
@@ -715,10 +726,10 @@ bool GpuIntegrator::preprocess()
 		f.base_sampling_offset = film->getBaseSamplingOffset();
 	}
 	if(!fillIntegrator(d.integrator, err)) return fail(err);
-	if(yafgpu_upload_scene(ctx_, &d) != YAFGPU_OK) return fail("scene upload refused");
+	if(yafgpu_group_upload_scene(grp_, &d) != YAFGPU_OK) return fail("scene upload refused");
 	yafgpu_stats st;
-	yafgpu_get_stats(ctx_, &st);
-	Y_INFO << integrator_name_ << ": " << g.n_tris << " triangles, BVH built on the GPU in " << st.ms_build << " ms" << YENDL;
+	yafgpu_group_get_stats(grp_, &st);
+	Y_INFO << integrator_name_ << ": " << g.n_tris << " triangles on " << yafgpu_group_size(grp_) << " GPU(s), BVH built on the GPU in " << st.ms_build << " ms" << YENDL;
 	return true;
 }
 
@@ -727,7 +738,7 @@ bool GpuIntegrator::depositFilm(ImageFilm *film)
 {
 	const int w = film->w_, h = film->h_;
 	host_film_.resize((size_t)w * h * 5);
-	if(yafgpu_read_film(ctx_, host_film_.data()) != YAFGPU_OK) return fail("film read-back failed");
+	if(yafgpu_group_read_film(grp_, host_film_.data()) != YAFGPU_OK) return fail("film read-back failed");
 	Rgba2DImageWeighed_t &img = *film->image_passes_[0];
 	for(int y = 0; y < h; ++y) for(int x = 0; x < w; ++x)
 	{
@@ -765,9 +776,9 @@ bool GpuIntegrator::render(int num_view, ImageFilm *film)
 			float *o = &host_film_[((size_t)y * w + x) * 5];
 			o[0] = p.col_.r_; o[1] = p.col_.g_; o[2] = p.col_.b_; o[3] = p.col_.a_; o[4] = p.weight_;
 		}
-		if(yafgpu_write_film(ctx_, host_film_.data()) != YAFGPU_OK) return fail("film upload failed");
+		if(yafgpu_group_write_film(grp_, host_film_.data()) != YAFGPU_OK) return fail("film upload failed");
 	}
-	else if(yafgpu_film_clear(ctx_) != YAFGPU_OK) return fail("film clear failed");
+	else if(yafgpu_group_film_clear(grp_) != YAFGPU_OK) return fail("film clear failed");
 
 	auto pass = [&](int samples, int offset, bool adaptive, int number, const uint8_t *mask) -> bool
 	{
@@ -776,7 +787,7 @@ bool GpuIntegrator::render(int num_view, ImageFilm *film)
 		pd.n_samples = samples; pd.offset = (int32_t)(offset + base); pd.adaptive = adaptive; pd.aa_pass_number = number; pd.resample_mask = mask;
 		session__.setStatusCurrentPass(number + 1);
 		film->setSamplingOffset(offset + samples);
-		if(yafgpu_render_pass(ctx_, &pd) != YAFGPU_OK) return fail("render pass failed");
+		if(yafgpu_group_render_pass(grp_, &pd) != YAFGPU_OK) return fail("render pass failed");
 		return depositFilm(film);
 	};
 	int acum = aa_samples, resampled = 0;
@@ -793,7 +804,7 @@ bool GpuIntegrator::render(int num_view, ImageFilm *film)
 	{
 		if(scene_->getSignals() & Y_SIG_ABORT) break;
 		sample_mult *= smf; light_mult *= lmf; indirect_mult *= imf;
-		yafgpu_set_aa_multipliers(ctx_, light_mult, indirect_mult);
+		yafgpu_group_set_aa_multipliers(grp_, light_mult, indirect_mult);
 		film->setAaNoiseParams(color_noise, dark_type, dark_factor, var_edge, var_pix, clamp_s);
 		if(resampled <= 0 && !thr_changed) film->nextPass(num_view, true, integrator_name_, /*skip_next_pass=*/true);
 		else
@@ -825,7 +836,7 @@ bool GpuIntegrator::render(int num_view, ImageFilm *film)
 	g_timer__.stop("rendert");
 	session__.setStatusRenderFinished();
 	yafgpu_stats st;
-	yafgpu_get_stats(ctx_, &st);
+	yafgpu_group_get_stats(grp_, &st);
 	const double rays = (double)(st.rays_camera + st.rays_extension + st.rays_shadow + st.rays_shadow_transp);
 	Y_INFO << integrator_name_ << ": Overall rendertime: " << g_timer__.getTime("rendert") << "s, " << rays / 1e6 << " Mrays, "
 	       << (st.ms_total > 0 ? rays / st.ms_total / 1e3 : 0.0) << " Mrays/s on the device" << YENDL;

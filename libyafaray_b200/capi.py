@@ -27,7 +27,7 @@ FILTERS = {"box": 0, "mitchell": 1, "gauss": 2, "lanczos": 3}
 INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
 TRACE_STATIC_MAX_RAYS = 65536  # YAFGPU_TRACE_STATIC_MAX_RAYS
-FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES = 1, 2
+FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES, FLAG_SHARE_DEVICE = 1, 2, 4
 TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE = range(3)
 TEXBLEND = {"lin": 0, "quad": 1, "ease": 2, "diag": 3, "sphere": 4, "halo": 5, "quad_sphere": 5, "radial": 6}
 TEXINTERP = {"none": 0, "bilinear": 1, "bicubic": 2}
@@ -176,7 +176,7 @@ class Stats(C.Structure):
                 ("launches_trace", u64), ("launches_shadow", u64), ("launches_shade", u64), ("rays_in_timed_trace", u64),
                 ("rays_in_timed_shadow", u64), ("last_wave_tasks", C.c_uint32 * 16), ("last_wave_shadow", C.c_uint32 * 16),
                 ("bvh_node_bytes", C.c_uint32), ("bvh_width", C.c_uint32), ("bvh_levels", C.c_uint32), ("reserved0", C.c_uint32),
-                ("nodes_visited_shadow", u64), ("tris_tested_shadow", u64)]
+                ("nodes_visited_shadow", u64), ("tris_tested_shadow", u64), ("film_reduces", u64), ("ms_film_reduce", C.c_double)]
 
 
 # every entry point include/yafgpu.h declares: name -> (restype, argtypes)
@@ -201,6 +201,20 @@ SYMBOLS = {
     "yafgpu_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "yafgpu_reset_stats": (C.c_int, [C.c_void_p]),
     "yafgpu_stream": (C.c_void_p, [C.c_void_p]),
+    "yafgpu_group_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.c_uint]),
+    "yafgpu_group_destroy": (None, [C.c_void_p]),
+    "yafgpu_group_last_error": (C.c_char_p, [C.c_void_p]),
+    "yafgpu_group_size": (C.c_int, [C.c_void_p]),
+    "yafgpu_group_ctx": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "yafgpu_group_upload_scene": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc)]),
+    "yafgpu_group_film_clear": (C.c_int, [C.c_void_p]),
+    "yafgpu_group_write_film": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "yafgpu_group_render_pass": (C.c_int, [C.c_void_p, C.POINTER(PassDesc)]),
+    "yafgpu_group_read_film": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "yafgpu_group_sync": (C.c_int, [C.c_void_p]),
+    "yafgpu_group_set_aa_multipliers": (C.c_int, [C.c_void_p, f32, f32]),
+    "yafgpu_group_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),
+    "yafgpu_group_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
 }
 
 

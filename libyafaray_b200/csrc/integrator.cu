@@ -773,7 +773,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			}
 			if(depth >= 1 && depth > ig.rr_min_bounces)
 			{	// Russian roulette :282-288
-				const float random_value = hashRand(wp.seed ^ (unsigned)(wp.pix_base + slot), offs, (unsigned)depth);
+				const float random_value = hashRand(wp.seed ^ ((unsigned)si.x | ((unsigned)si.y << 16)), offs, (unsigned)depth);   // (pass, pixel | sample, path via offs | depth): independent of wave and partition
 				const float probability = maxc(thr);
 				if(probability <= 0.f || probability < random_value) continue;
 				const float ip = 1.f / probability;
@@ -781,7 +781,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			}
 			if(direct && sc.n_lights > 0 && (bsdfs & (BsdfDiffuse | BsdfGlossy)))
 			{	// estimateOneDirectLight integrator_montecarlo.cc:62-76 (a material without diffuse/glossy lobes evaluates to black)
-				const float u = hashRand(wp.seed + 0x51ED270Bu + (unsigned)(wp.pix_base + slot), offs, (unsigned)depth);
+				const float u = hashRand((wp.seed + 0x51ED270Bu) ^ ((unsigned)si.x | ((unsigned)si.y << 16)), offs, (unsigned)depth);
 				const int lnum = min((int)(u * (float)sc.n_lights), sc.n_lights - 1);
 				doLightEstimation<MT>(cx, m, slot, si, lnum, sp, pwo, (unsigned)lnum, ray_division, Wp * (float)sc.n_lights);
 			}
@@ -1176,7 +1176,7 @@ int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 		wp.sample_base = s_begin + smp0;
 		wp.n_samples_pass = p->n_samples; wp.pass_offs = p->offset; wp.aa_passes = c->film.aa_passes;
 		wp.task_cap = w.task_cap; wp.shadow_cap = w.shadow_cap;
-		wp.seed = hashSeed((unsigned)p->offset, (unsigned)wp.sample_base, (unsigned)p->aa_pass_number);
+		wp.seed = hashSeed((unsigned)p->offset, 0x2545F491u, (unsigned)p->aa_pass_number);   // per pass, NOT per wave: a sample's random numbers must not depend on how the pass is cut into waves
 		bool overflow = false;
 		rc = runWave(c, wp, max_iters, overflow);
 		if(rc != YAFGPU_OK) return rc;

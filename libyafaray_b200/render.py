@@ -120,6 +120,89 @@ class Context:
         return capi.lib.yafgpu_stream(self.h)
 
 
+class Group:
+    """N GPUs of one box rendering one scene (yafgpu_group, include/yafgpu.h): the scene is replicated, every pass is split by
+    interleaved tiles, `read_film` returns the summed film.  Same methods as `Context`, so `render_scene(..., ctx=Group([0, 1]))` works."""
+
+    def __init__(self, devices=None, flags=0):
+        h = C.c_void_p()
+        n = 0 if devices is None else len(devices)
+        arr = (C.c_int * max(1, n))(*(devices or [0]))
+        rc = capi.lib.yafgpu_group_create(C.byref(h), arr if n else None, n, flags)
+        if rc != capi.OK:
+            msg = capi.lib.yafgpu_group_last_error(None)
+            raise capi.YafGpuError(rc, msg.decode() if msg else "?")
+        self.h = h
+        self.width = self.height = 0
+        self._keep = None
+
+    def _check(self, rc):
+        if rc != capi.OK:
+            msg = capi.lib.yafgpu_group_last_error(self.h)
+            raise capi.YafGpuError(rc, msg.decode() if msg else "?")
+
+    def size(self):
+        return capi.lib.yafgpu_group_size(self.h)
+
+    def close(self):
+        if self.h:
+            capi.lib.yafgpu_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, desc, keep=None):
+        self._keep = keep
+        self._check(capi.lib.yafgpu_group_upload_scene(self.h, C.byref(desc)))
+        self.width, self.height = desc.film.width, desc.film.height
+
+    def film_clear(self):
+        self._check(capi.lib.yafgpu_group_film_clear(self.h))
+
+    def render_pass(self, n_samples, offset=0, adaptive=False, aa_pass_number=0, mask=None, sample_begin=0, sample_end=0, part_index=0, part_count=1):
+        p = capi.PassDesc()
+        p.n_samples, p.offset, p.adaptive, p.aa_pass_number = n_samples, offset, int(adaptive), aa_pass_number
+        p.sample_begin, p.sample_end = sample_begin, sample_end   # the partition fields belong to the group
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, np.uint8)
+            p.resample_mask = mask.ctypes.data_as(C.POINTER(C.c_uint8))
+        self._check(capi.lib.yafgpu_group_render_pass(self.h, C.byref(p)))
+
+    def read_film(self):
+        out = np.empty((self.height, self.width, 5), np.float32)
+        self._check(capi.lib.yafgpu_group_read_film(self.h, out.ctypes.data))
+        return out
+
+    def read_film_into(self, ptr):
+        self._check(capi.lib.yafgpu_group_read_film(self.h, ptr))
+
+    def sync(self):
+        self._check(capi.lib.yafgpu_group_sync(self.h))
+
+    def write_film(self, film):
+        film = np.ascontiguousarray(film, np.float32)
+        self._check(capi.lib.yafgpu_group_write_film(self.h, film.ctypes.data))
+
+    def set_aa_multipliers(self, light, indirect):
+        self._check(capi.lib.yafgpu_group_set_aa_multipliers(self.h, light, indirect))
+
+    def set_option(self, name, value):
+        self._check(capi.lib.yafgpu_group_set_option(self.h, name.encode(), int(value)))
+
+    def stats(self):
+        s = capi.Stats()
+        self._check(capi.lib.yafgpu_group_get_stats(self.h, C.byref(s)))
+        return {k: (list(getattr(s, k)) if hasattr(getattr(s, k), "__len__") else getattr(s, k)) for k, _ in capi.Stats._fields_}
+
+    def reset_stats(self):
+        for k in range(self.size()):
+            _check(None, capi.lib.yafgpu_reset_stats(capi.lib.yafgpu_group_ctx(self.h, k)))
+
+
 def film_to_image(film):
     """Pixel::normalized (util_image_buffers.h:39-43): col / weight when weight != 0."""
     w = film[..., 4:5]

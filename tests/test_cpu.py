@@ -17,8 +17,8 @@ from tests import oracle_util as ou, parity_cases as pc, qmc_ref  # noqa: E402
 
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "yafgpu.h")).read()
-    names = set(re.findall(r"^(?:int|void|const char \*|void \*)\s*\*?(yafgpu_\w+)\(", hdr, re.M))
-    assert len(names) >= 18
+    names = set(re.findall(r"^(?:int|void|const char \*|void \*|yafgpu_ctx \*)\s*\*?(yafgpu_\w+)\(", hdr, re.M))
+    assert len(names) >= 32
     lib = ctypes.CDLL(os.path.join(ROOT, "libyafaray_b200", "libyafgpu.so"))
     for n in names:
         assert hasattr(lib, n), n
