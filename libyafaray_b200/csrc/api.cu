@@ -225,6 +225,12 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, cudaSetDevice(c->device));
 	YG_CUDA(c, cudaStreamSynchronize(c->stream));
 	freeScene(c);
+	{	// film first: bad input must not pay for the upload and the BVH build.  Pixel coordinates travel as x | y << 16 (integrator.cu buildPixelList)
+		const yafgpu_film_desc &f = desc->film;
+		if(f.width <= 0 || f.height <= 0 || f.xstart < 0 || f.ystart < 0 || (long long)f.xstart + f.width > 65535 || (long long)f.ystart + f.height > 65535)
+			return setErr(c, YAFGPU_ERR_INVALID, "film size: width, height > 0 and xstart + width, ystart + height <= 65535");
+		if(f.premult) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "premult film not implemented on the device");
+	}
 	const yafgpu_geometry &g = desc->geometry;
 	if(g.n_tris > 0 && (!g.points || !g.tri_vidx || !g.tri_mat || !g.tri_obj || !g.objects))
 		return setErr(c, YAFGPU_ERR_INVALID, "geometry arrays missing");
@@ -299,11 +305,18 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 			return setErr(c, YAFGPU_ERR_UNSUPPORTED, "texture_mapper texco window is implemented for the perspective camera only");
 	const yafgpu_integrator_desc &in = desc->integrator;
 	if(in.type != YAFGPU_INT_DIRECTLIGHT && in.type != YAFGPU_INT_PATHTRACING) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "integrator type");
-	if(in.bg_transp || in.bg_transp_refract) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bg_transp / bg_transp_refract (alpha output) not implemented on the device");
-	if(in.raydepth + 1 + in.bounces + 8 > YG_MAX_ITERS) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "raydepth + bounces too large for the wavefront schedule");
+	// bg_transp: the alpha of a camera sample is 0 when its primary ray leaves the scene, 1 otherwise (integrator_path_tracer.cc:122-123,324;
+	// integrator_direct_light.cc likewise).  bg_transp_refract needs Material::getAlpha along the refraction chain and stays refused.
+	if(in.bg_transp_refract) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bg_transp_refract (alpha through refractions) not implemented on the device");
+	// the packed task state holds the path depth in 6 bits (integrator.cu packState); the recursion level never passes 19 — the reference's own
+	// `raylevel_ < 20` guards (integrator_montecarlo.cc:862,921) — so the wavefront needs at most 20 + bounces + 1 iterations
+	if(in.bounces > 63) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bounces > 63: the wavefront task state holds the path depth in 6 bits");
+	if(in.raydepth < 0 || in.bounces < 0) return setErr(c, YAFGPU_ERR_INVALID, "negative raydepth / bounces");
+	if(std::min(in.raydepth + 31, 19) + 1 + in.bounces + 1 > YG_MAX_ITERS) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "raydepth + bounces too large for the wavefront schedule");
 	s.integ.type = in.type; s.integ.r_depth = in.raydepth; s.integ.tr_shad = in.transp_shad; s.integ.s_depth = in.shadow_depth;
 	s.integ.n_paths = in.path_samples; s.integ.max_bounces = in.bounces; s.integ.rr_min_bounces = in.rr_min_bounces;
 	s.integ.no_recursive = in.no_recursive; s.integ.trace_caustics = in.trace_caustics;
+	s.integ.transp_bg = in.bg_transp ? 1 : 0; s.integ.transp_refr_bg = 0;
 	s.integ.do_ao = in.do_ao; s.integ.ao_samples = in.ao_samples; s.integ.ao_dist = in.ao_distance;
 	for(int k = 0; k < 3; ++k) s.integ.ao_col[k] = in.ao_color[k];
 	if(in.do_ao && in.ao_samples < 1) return setErr(c, YAFGPU_ERR_INVALID, "AO_samples must be positive");
@@ -365,7 +378,13 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	cudaStream_t st = c->stream;
 	c->n_tris = g.n_tris; c->n_points = g.n_points; c->n_normals = g.n_normals; c->n_uv = g.n_uv; c->n_objects = g.n_objects;
 	c->n_mats = desc->n_materials; c->n_lights = c->h_lights.size();
-	int *d_nidx = nullptr, *d_uvidx = nullptr, *d_obj = nullptr;
+	struct TmpIdx   // index arrays only k_tri_shade needs: released on every way out of this function
+	{
+		int *nidx = nullptr, *uvidx = nullptr, *obj = nullptr; cudaStream_t s;
+		~TmpIdx() { poolFree(nidx, s); poolFree(uvidx, s); poolFree(obj, s); }
+	} tmp;
+	tmp.s = st;
+	int *&d_nidx = tmp.nidx, *&d_uvidx = tmp.uvidx, *&d_obj = tmp.obj;
 	YG_CUDA(c, upload(c->d_points, g.points, g.n_points * 3, st));
 	YG_CUDA(c, upload(c->d_normals, g.normals, g.n_normals * 3, st));
 	YG_CUDA(c, upload(c->d_uv, g.uv, g.n_uv * 2, st));
@@ -419,7 +438,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng; bi.leaf_max = c->leaf_max; bi.width = YG_BVH_WIDTH;
 		BvhBuildOutput bo;
 		cudaError_t e = buildBvh(bi, bo, st);
-		if(e != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e, "buildBvh"); }
+		if(e != cudaSuccess) return cudaErr(c, e, "buildBvh");
 		c->d_nodes = bo.nodes; c->d_acc_tris = bo.tris;
 		a.nodes = (const uint4 *)bo.nodes; a.tris = bo.tris; a.n_nodes = bo.n_nodes; a.root = bo.root; a.width = YG_BVH_WIDTH;
 		c->stats.bvh_node_bytes = (uint32_t)bo.node_bytes; c->stats.bvh_width = YG_BVH_WIDTH; c->stats.bvh_levels = (uint32_t)bo.levels;
@@ -443,7 +462,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		bi.tri_mat = c->d_tri_mat + ld.tri_first; bi.mat_triflags = c->d_mat_triflags; bi.tri_ng_out = c->d_tri_ng + 3 * (size_t)ld.tri_first; bi.leaf_max = c->leaf_max; bi.width = YG_BVH_WIDTH;
 		BvhBuildOutput bo;
 		cudaError_t e2 = buildBvh(bi, bo, st);
-		if(e2 != cudaSuccess) { poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream); return cudaErr(c, e2, "buildBvh (mesh light)"); }
+		if(e2 != cudaSuccess) return cudaErr(c, e2, "buildBvh (mesh light)");
 		Accel la; memset(&la, 0, sizeof(la));
 		la.nodes = (const uint4 *)bo.nodes; la.tris = bo.tris; la.n_nodes = bo.n_nodes; la.n_tris = ld.tri_count; la.root = bo.root; la.width = YG_BVH_WIDTH; la.fault = c->d_fault; la.stack_limit = a.stack_limit;
 		c->light_bvh_ptrs.push_back(bo.nodes); c->light_bvh_ptrs.push_back(bo.tris);
@@ -460,7 +479,6 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	cudaEventRecord(c->ev1, st);
 	cudaError_t e = cudaStreamSynchronize(st);
-	poolFree(d_nidx, c->stream); poolFree(d_uvidx, c->stream); poolFree(d_obj, c->stream);
 	if(e != cudaSuccess) return cudaErr(c, e, "scene upload");
 	float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1); c->stats.ms_build += ms;
 	c->stats.bvh_nodes = a.n_nodes; c->stats.bvh_bytes = (uint64_t)a.n_nodes * c->stats.bvh_node_bytes; c->stats.tri_bytes = (uint64_t)g.n_tris * sizeof(TriAccel);
@@ -471,12 +489,12 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 
 	// film (ImageFilm ctor + init)
 	prepFilm(desc->film, c->film);
+	c->film.transp_bg = s.integ.transp_bg;
 	c->tile_size = desc->film.tile_size > 0 ? desc->film.tile_size : 32;
-	if(desc->film.width <= 0 || desc->film.height <= 0 || desc->film.width > 65535 || desc->film.height > 65535) return setErr(c, YAFGPU_ERR_INVALID, "film size");
-	if(desc->film.premult) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "premult film not implemented on the device");
 	YG_CUDA(c, poolAlloc(&c->film.pix, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
+	c->wave_cur_cap = 0;
 	c->uploaded = true;
 	return YAFGPU_OK;
 }

@@ -48,6 +48,7 @@ struct yafgpu_ctx
 	std::vector<yg::MatDev> h_mats;
 	std::vector<yg::LightDev> h_lights;
 	int tile_size = 32;
+	int wave_cur_cap = 0;                             // wave size after queue overflows on the current scene (0 = none yet); reset by every upload
 	int wave_cap_override = 0, task_fan_override = 0; // yafgpu_set_option
 
 	// wavefront state

@@ -294,8 +294,9 @@ struct TraceIO
 // REGEN: warp-persistent schedule with ray regeneration (traverse.cuh traversePersistent) instead of task i -> thread i.
 template<bool COUNT, bool REGEN>
 __global__ void __launch_bounds__(128) k_trace(Accel acc, TaskQueue q, const int *__restrict__ n_tasks, int task_cap, SortBins bins, int *__restrict__ next, int refill_below,
-                                               unsigned long long *__restrict__ counters)
+                                               unsigned long long *__restrict__ counters, const WaveCtl *__restrict__ ctl)
 {
+	if(ctl->overflow) return;   // a queue ran over earlier in this wave: the wave is discarded, do not pay for the rest of it
 	const int n = min(*n_tasks, task_cap);
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
 	TraceIO io; io.q = q; io.bins = bins;
@@ -559,6 +560,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
                                                float4 *__restrict__ acc, WaveCtl *__restrict__ ctl, int iter, const int *__restrict__ perm,
                                                const int *__restrict__ ends, int n_mat, int b0, int b1)
 {
+	if(ctl->overflow) return;
 	ShadeCtx cx; cx.sc = &sc; cx.wp = wp; cx.out = out; cx.sq = sq; cx.acc = acc; cx.ctl = ctl; cx.iter = iter;
 	const IntegratorDev &ig = sc.integ;
 	// runs of this type: kind 0 buckets [b0, b1], kind 1 buckets [n_mat + b0, n_mat + b1]; the miss bucket is 2 * n_mat
@@ -598,6 +600,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			if(MT == MT_MISS || tri < 0)
 			{
 				if(sc.bg.type != YAFGPU_BG_NONE) accAdd(acc, slot, W * bgEval(sc.bg, dir));
+				if(ig.transp_bg && stRaylevel(packed) == 0) ((float *)(acc + slot))[3] = 1.f;   // primary ray missed: alpha stays at its initial 0 (integrator_path_tracer.cc:122)
 				continue;
 			}
 			SurfPt sp;
@@ -860,8 +863,9 @@ struct ShadowIO
 // opaque shadows: any-hit traversal (REGEN as in k_trace); transparent shadows (transpShad): filter accumulation along the segment
 template<bool COUNT, bool REGEN>
 __global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ SceneDev sc, ShadowQueue sq, const int *__restrict__ n_shadow, int shadow_cap, float4 *__restrict__ acc,
-                                                int *__restrict__ next, int refill_below, unsigned long long *__restrict__ counters)
+                                                int *__restrict__ next, int refill_below, unsigned long long *__restrict__ counters, const WaveCtl *__restrict__ ctl)
 {
+	if(ctl->overflow) return;
 	const int n = min(*n_shadow, shadow_cap);
 	TravCounters tc; tc.nodes = 0; tc.tris = 0;
 	__shared__ uint2 s_stack[YG_STACK_SHARED * 128];
@@ -905,7 +909,7 @@ __global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, c
 		samplePos(wp, si, dx, dy);
 		const float4 a = acc[slot];
 		Col col = clampProportional(mkc(a.x, a.y, a.z), film.clamp_samples);
-		const float alpha = 1.f;
+		const float alpha = (film.transp_bg && a.w != 0.f) ? 0.f : 1.f;
 		const int x = si.x, y = si.y;
 		const double fw = (double)film.filterw;
 		const int dx_0 = max(film.cx0 - x, round2Int((double)dx - fw));
@@ -1043,9 +1047,9 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		TaskQueue &in = w.q[it & 1], &out = w.q[(it + 1) & 1];
 		SortBins bins; bins.tri_mat = c->d_tri_mat; bins.mat_bucket = c->d_mat_bucket; bins.n_mat = c->n_mat_buckets; bins.key = w.key; bins.hist = w.hist;
 		const int nb = 2 * c->n_mat_buckets + 1;
-		cudaMemsetAsync(w.hist, 0, sizeof(int) * nb, st);
+		YG_CUDA(c, cudaMemsetAsync(w.hist, 0, sizeof(int) * nb, st));
 		const size_t hist_smem = nb <= YG_SHARED_BUCKETS ? sizeof(int) * nb : 0;
-#define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, hist_smem, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], refill, c->d_counters)
+#define YG_TRACE(C, R) k_trace<C, R><<<gt, 128, hist_smem, st>>>(c->scene.accel, in, &w.ctl->n_tasks[it], wp.task_cap, bins, &w.ctl->fetch_trace[it], refill, c->d_counters, w.ctl)
 		if(count) { if(regen_t) YG_TRACE(true, true); else YG_TRACE(true, false); } else { if(regen_t) YG_TRACE(false, true); else YG_TRACE(false, false); }
 #undef YG_TRACE
 		mark();
@@ -1073,7 +1077,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		k_shade<MT_MISS, 2><<<gs, 128, 0, shadeStream()>>>(c->scene, wp, w.pixels, in, out, w.sq, w.acc, w.ctl, it, w.perm, ends, c->n_mat_buckets, 0, 0); ++n_launch;
 		if(n_str > 1) for(int k = 0; k < n_str - 1; ++k) { cudaEventRecord(c->ev_join[k], c->side[k]); cudaStreamWaitEvent(st, c->ev_join[k], 0); }
 		mark();
-#define YG_SHADOW(C, R) k_shadow<C, R><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, &w.ctl->fetch_shadow[it], refill, c->d_counters)
+#define YG_SHADOW(C, R) k_shadow<C, R><<<gt, 128, 0, st>>>(c->scene, w.sq, &w.ctl->n_shadow[it], wp.shadow_cap, w.acc, &w.ctl->fetch_shadow[it], refill, c->d_counters, w.ctl)
 		if(count) { if(regen_s) YG_SHADOW(true, true); else YG_SHADOW(true, false); } else { if(regen_s) YG_SHADOW(false, true); else YG_SHADOW(false, false); }
 #undef YG_SHADOW
 		mark();
@@ -1112,7 +1116,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 {
 	if(p->n_samples <= 0) return setErr(c, YAFGPU_ERR_INVALID, "n_samples must be positive");
-	if(p->adaptive && p->resample_mask == nullptr && false) return setErr(c, YAFGPU_ERR_INVALID, "adaptive pass without mask");
+	// an adaptive pass without a mask resamples every pixel: ImageFilm::doMoreSamples is true everywhere while AA_threshold is 0 (imagefilm.cc:917-920)
 	int s_begin = p->sample_begin, s_end = p->sample_end;
 	if(s_begin == 0 && s_end == 0) s_end = p->n_samples;
 	if(s_begin < 0 || s_end > p->n_samples || s_begin >= s_end) return setErr(c, YAFGPU_ERR_INVALID, "sample range");
@@ -1127,29 +1131,45 @@ int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 	const int rdepth = std::min(ig.r_depth + max_add, 19);
 	const int max_iters = std::min(YG_MAX_ITERS, rdepth + 1 + (ig.type == YAFGPU_INT_PATHTRACING ? ig.max_bounces + 1 : 0));
 
-	// wave sizing: a wave covers `n_pix_w` pixels x `n_smp_w` samples
-	const int fan = c->task_fan_override > 0 ? c->task_fan_override : 8;
+	// Queue capacities per camera sample ("fans").  Tasks: the widest step of the recursion tree is the glossy x8 fan of recursiveRaytrace
+	// plus the two specular children, or n_paths first path segments.  Shadow rays: one integrate() task queues, per light, ceil(samples x
+	// multiplier) rays, twice that for lights that also take the BSDF-sampling half of the MIS estimator (doLightEstimation), plus the AO
+	// samples; a scene with a 16-sample IBL light and a few mesh lights needs ~40 per task, and with the fixed fan of 8 used before every
+	// pass first rendered and discarded whole waves (~55 % of config 4's time).
+	int task_fan = 8, shadow_fan = 8;
+	{
+		if(ig.type == YAFGPU_INT_PATHTRACING) task_fan = std::max(task_fan, std::min(ig.n_paths + 2, 64));
+		int s_int = (ig.type == YAFGPU_INT_DIRECTLIGHT && ig.do_ao) ? ig.ao_samples : 0;
+		for(const LightDev &L : c->h_lights)
+		{
+			if(L.dirac) { s_int += 1; continue; }
+			const int n = std::max(1, (int)ceilf((float)L.samples * ig.aa_light_sample_multiplier));
+			s_int += n * (L.can_intersect ? 2 : 1);
+		}
+		shadow_fan = std::max(8, std::min(s_int + 4, 128));
+	}
+	if(c->task_fan_override > 0) { task_fan = c->task_fan_override; shadow_fan = std::max(shadow_fan, c->task_fan_override); }
+	const size_t per_sample = (size_t)task_fan * (2 * 112) + (size_t)shadow_fan * 48 + 16;
 	int wave_cap = c->wave_cap_override;
 	if(wave_cap <= 0)
 	{	// Default: as large as a quarter of the free HBM allows, at most 2^23 camera samples.  Large waves amortise the thin tail
 		// iterations of a wave (a few thousand tasks per launch at depth 8+): Cornell bench 3.57 -> 4.35 Grays/s from 2^20 to 2^23
-		// (profiles/r1_wave_size.md).  Bytes per camera sample: fan x (2 task queues x 112 B + 48 B shadow record) + 16 B.
+		// (profiles/r1_wave_size.md).
 		const size_t pass_samples = n_pix * (size_t)(s_end - s_begin);
 		Wavefront &w0 = c->wf;
 		int want = 1 << 23;
 		while(want > (1 << 16) && (size_t)(want >> 1) >= pass_samples) want >>= 1; // no larger than this call needs
-		if(w0.allocated && w0.wave_cap >= want) wave_cap = w0.wave_cap;               // keep what is there
+		if(w0.allocated && w0.wave_cap >= want && w0.task_cap == w0.wave_cap * task_fan && w0.shadow_cap == w0.wave_cap * shadow_fan) wave_cap = w0.wave_cap;   // keep what is there
 		else
 		{
 			size_t free_b = 0, total_b = 0;
 			cudaMemGetInfo(&free_b, &total_b);
-			if(w0.allocated) free_b += (size_t)w0.wave_cap * ((size_t)fan * (2 * 112 + 48) + 16);
-			const size_t per_sample = (size_t)fan * (2 * 112 + 48) + 16;
+			if(w0.allocated) free_b += (size_t)w0.task_cap * (2 * 112) + (size_t)w0.shadow_cap * 48 + (size_t)w0.wave_cap * 16;
 			wave_cap = want;
 			while(wave_cap > (1 << 16) && (size_t)wave_cap * per_sample > free_b / 4) wave_cap >>= 1;
 		}
 	}
-	cudaError_t e = allocWavefront(c, wave_cap, wave_cap * fan, wave_cap * fan);
+	cudaError_t e = allocWavefront(c, wave_cap, wave_cap * task_fan, wave_cap * shadow_fan);
 	if(e != cudaSuccess) return cudaErr(c, e, "wavefront allocation");
 	Wavefront &w = c->wf;
 
@@ -1157,7 +1177,8 @@ int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 	const int n_smp = s_end - s_begin;
 	size_t pix0 = 0;
 	int smp0 = 0;
-	int cur_cap = wave_cap;
+	// a wave size that overflowed once on this scene is not tried again (the scene decides the fan-out, not the pass)
+	int cur_cap = (c->wave_cur_cap > 0 && c->wave_cur_cap < wave_cap) ? c->wave_cur_cap : wave_cap;
 	while(smp0 < n_smp)
 	{
 		WaveParams wp;
@@ -1184,6 +1205,7 @@ int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 		{
 			if(cur_cap <= 1024) return setErr(c, YAFGPU_ERR_NOMEM, "wavefront queues overflow even at the smallest wave size");
 			cur_cap /= 2;
+			c->wave_cur_cap = cur_cap;
 			continue; // retry the same range with a smaller wave
 		}
 		const int ns_done = wp.n_slots / wp.n_pix;

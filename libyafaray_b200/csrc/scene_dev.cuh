@@ -185,6 +185,7 @@ struct FilmDev
 	int w, h, cx0, cy0, cx1, cy1;
 	float filterw, table_scale, clamp_samples;
 	int premult, aa_passes;
+	int transp_bg;      // "bg_transp": a camera sample whose primary ray left the scene has alpha 0 (acc[slot].w carries the mark)
 	unsigned base_sampling_offset;
 	float table[256];   // 16x16 filter table, imagefilm.cc:167-174
 };

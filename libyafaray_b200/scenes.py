@@ -154,7 +154,7 @@ def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, ray
     return y
 
 
-def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting", filter_type="gauss"):
+def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting", filter_type="gauss", bg_transp=False):
     """Small DirectLight + point-light scene in the spirit of BASELINE config 1 (tests/test01 geometry is 6 cubes on
     a ground quad lit by one point light; its textures are 'next' scope, so flat colours are used)."""
     y = Interface()
@@ -187,6 +187,8 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
     y.createBackground("bg")
     y.paramsClearAll()
     y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", 8); y.paramsSetInt("shadowDepth", 2)
+    if bg_transp:
+        y.paramsSetBool("bg_transp", True)
     if integrator == "pathtracing":
         y.paramsSetInt("path_samples", 2); y.paramsSetInt("bounces", 3); y.paramsSetInt("russian_roulette_min_bounces", 8)
     y.createIntegrator("pt")

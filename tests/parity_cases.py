@@ -20,6 +20,13 @@ EXACT = {
     "cornell_dl_noglass": lambda: scenes.cornell_box(160, 90, 4, integrator="directlighting", glass=False),
     "cornell_dl_glass": lambda: scenes.cornell_box(160, 90, 4, integrator="directlighting"),
     "cornell_dl_mitchell": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", filter_type="mitchell", aa_passes=2),
+    # round 2: the filter and clamp corners of ImageFilm::addSample (imagefilm.cc:60-122,925-1015) and the bg_transp alpha channel
+    "cornell_dl_lanczos": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", filter_type="lanczos"),
+    "cornell_dl_lanczos_wide": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", filter_type="lanczos", pixelwidth=3.0),
+    "cornell_dl_clamp": lambda: scenes.cornell_box(96, 54, 4, integrator="directlighting", AA_clamp_samples=0.7, AA_clamp_indirect=0.3),
+    "cornell_pt_clamp_norr": lambda: scenes.cornell_box(96, 54, 4, path_samples=2, bounces=3, raydepth=3, rr_min_bounces=8, AA_clamp_samples=0.5, AA_clamp_indirect=0.2),
+    "simple_dl_bgtransp": lambda: scenes.simple_point_scene(160, 90, 2, filter_type="box", bg_transp=True),
+    "simple_pt_bgtransp": lambda: scenes.simple_point_scene(160, 90, 4, integrator="pathtracing", filter_type="box", bg_transp=True),
 }
 
 # name -> (builder(spp), converged spp of the golden reference)
