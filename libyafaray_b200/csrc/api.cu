@@ -10,6 +10,8 @@
 #include <algorithm>
 #include <new>
 #include <mutex>
+#include <thread>
+#include <chrono>
 
 #define YG_MAX_DEVICES 64 /* per-device tables of yafgpu_trace_static */
 
@@ -225,6 +227,9 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, cudaSetDevice(c->device));
 	YG_CUDA(c, cudaStreamSynchronize(c->stream));
 	freeScene(c);
+	const bool timing = getenv("YAFGPU_UPLOAD_TIMING") != nullptr;   // development aid: host wall-clock phases on stderr
+	auto t_prev = std::chrono::steady_clock::now();
+	auto phase = [&](const char *what) { if(!timing) return; cudaStreamSynchronize(c->stream); const auto t = std::chrono::steady_clock::now(); fprintf(stderr, "yafgpu upload: %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t - t_prev).count()); t_prev = t; };
 	{	// film first: bad input must not pay for the upload and the BVH build.  Pixel coordinates travel as x | y << 16 (integrator.cu buildPixelList)
 		const yafgpu_film_desc &f = desc->film;
 		if(f.width <= 0 || f.height <= 0 || f.xstart < 0 || f.ystart < 0 || (long long)f.xstart + f.width > 65535 || (long long)f.ystart + f.height > 65535)
@@ -235,20 +240,38 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	if(g.n_tris > 0 && (!g.points || !g.tri_vidx || !g.tri_mat || !g.tri_obj || !g.objects))
 		return setErr(c, YAFGPU_ERR_INVALID, "geometry arrays missing");
 	if(g.n_tris > (size_t)(1u << 28)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "more than 2^28 triangles");
-	// validate indices on the host (cheap, and a bad index would otherwise be an illegal address on the device)
-	for(size_t i = 0; i < g.n_tris; ++i)
+	// validate indices on the host (a bad index would otherwise be an illegal address on the device); 10^7 triangles are split over a few threads
 	{
-		for(int k = 0; k < 3; ++k)
+		const unsigned hw = std::thread::hardware_concurrency();
+		const int n_thr = g.n_tris < (size_t)1 << 18 ? 1 : (int)std::max(1u, std::min(8u, hw ? hw : 1u));
+		std::vector<const char *> bad((size_t)n_thr, nullptr);
+		auto check = [&](int t)
 		{
-			const int v = g.tri_vidx[3 * i + k];
-			if(v < 0 || (size_t)v >= g.n_points) return setErr(c, YAFGPU_ERR_INVALID, "tri_vidx out of range");
-			if(g.tri_nidx) { const int q = g.tri_nidx[3 * i + k]; if(q >= (int)g.n_normals) return setErr(c, YAFGPU_ERR_INVALID, "tri_nidx out of range"); }
-			if(g.tri_uvidx) { const int q = g.tri_uvidx[3 * i + k]; if(q >= (int)g.n_uv) return setErr(c, YAFGPU_ERR_INVALID, "tri_uvidx out of range"); }
+			const size_t i0 = g.n_tris * (size_t)t / n_thr, i1 = g.n_tris * (size_t)(t + 1) / n_thr;
+			for(size_t i = i0; i < i1 && !bad[t]; ++i)
+			{
+				for(int k = 0; k < 3; ++k)
+				{
+					const int v = g.tri_vidx[3 * i + k];
+					if(v < 0 || (size_t)v >= g.n_points) bad[t] = "tri_vidx out of range";
+					if(g.tri_nidx) { const int q = g.tri_nidx[3 * i + k]; if(q >= (int)g.n_normals) bad[t] = "tri_nidx out of range"; }
+					if(g.tri_uvidx) { const int q = g.tri_uvidx[3 * i + k]; if(q >= (int)g.n_uv) bad[t] = "tri_uvidx out of range"; }
+				}
+				if(g.tri_mat[i] < 0 || (size_t)g.tri_mat[i] >= desc->n_materials) bad[t] = "tri_mat out of range";
+				if(g.tri_obj[i] < 0 || (size_t)g.tri_obj[i] >= g.n_objects) bad[t] = "tri_obj out of range";
+			}
+		};
+		if(n_thr == 1) check(0);
+		else
+		{
+			std::vector<std::thread> th;
+			for(int t = 0; t < n_thr; ++t) th.emplace_back(check, t);
+			for(std::thread &t : th) t.join();
 		}
-		if(g.tri_mat[i] < 0 || (size_t)g.tri_mat[i] >= desc->n_materials) return setErr(c, YAFGPU_ERR_INVALID, "tri_mat out of range");
-		if(g.tri_obj[i] < 0 || (size_t)g.tri_obj[i] >= g.n_objects) return setErr(c, YAFGPU_ERR_INVALID, "tri_obj out of range");
+		for(const char *b : bad) if(b) return setErr(c, YAFGPU_ERR_INVALID, b);
 	}
 
+	phase("index validation");
 	// materials / lights / camera / film: reference constructors restated on the host (host_prep.h)
 	c->h_mats.assign(desc->n_materials, MatDev());
 	std::vector<unsigned> triflags(desc->n_materials ? desc->n_materials : 1, 0u);
@@ -427,6 +450,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	if(g.tri_uvidx) YG_CUDA(c, upload(d_uvidx, g.tri_uvidx, g.n_tris * 3, st));
 	YG_CUDA(c, upload(d_obj, g.tri_obj, g.n_tris, st));
 
+	phase("host prep + H2D copies");
 	// K1: accelerator
 	cudaEventRecord(c->ev0, st);
 	Accel &a = s.accel;
@@ -452,6 +476,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		}
 		k_tri_shade<<<(unsigned)((g.n_tris + 255) / 256), 256, 0, st>>>((int)g.n_tris, c->d_tri_vidx, d_nidx, d_uvidx, c->d_tri_mat, d_obj, c->d_tri_ng, c->d_tris);
 	}
+	phase("BVH build");
 	// mesh lights intersect their own accelerator (MeshLight::initIs builds a private TriKdTree, light_meshlight.cc:72)
 	std::vector<Accel> laccels;
 	for(size_t i = 0; i < c->h_lights.size(); ++i)
@@ -494,6 +519,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, poolAlloc(&c->film.pix, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
+	phase("lights, film, rest");
 	c->wave_cur_cap = 0;
 	c->uploaded = true;
 	return YAFGPU_OK;

@@ -228,7 +228,7 @@ __global__ void k_collapse(int n, int n_items, const CollapseItem *__restrict__ 
 	for(int k = 0; k < W; ++k) if(k < cnt && area[k] >= 0.f) ++n_inner;
 	int slot0 = 0, q0 = 0;
 	if(n_inner) { slot0 = atomicAdd(&counters[0], n_inner); q0 = atomicAdd(&counters[1], n_inner); }
-	// node (scene_dev.cuh): six planes of W floats (lo x,y,z, hi x,y,z), then W links, padded to 128 B (W = 4) / 256 B (W = 8)
+	// node (scene_dev.cuh): per axis the lo and hi planes of W children, then W links, 128 B (W = 4) / 256 B (W = 8)
 	float pl[6][W]; int link[W];
 	int ii = 0;
 #pragma unroll
@@ -252,15 +252,22 @@ __global__ void k_collapse(int n, int n_items, const CollapseItem *__restrict__ 
 		else if(c >= n - 1) link[k] = ~(((c - (n - 1)) << 3) | 0);
 		else { const int2 r = range[c]; link[k] = ~((r.x << 3) | (r.y - 1)); }
 	}
+	// 32-byte chunks (one 256-bit load each): per axis [lo of children 4v..4v+3 | hi of the same], then [links | child count, padding]
 	float4 *out = (float4 *)(nodes + (size_t)item.slot * (W == 4 ? 8 : 16));
 #pragma unroll
-	for(int a = 0; a < 6; ++a)
+	for(int a = 0; a < 3; ++a)
 #pragma unroll
-		for(int v = 0; v < W / 4; ++v) out[a * (W / 4) + v] = make_float4(pl[a][4 * v], pl[a][4 * v + 1], pl[a][4 * v + 2], pl[a][4 * v + 3]);
+		for(int v = 0; v < W / 4; ++v)
+		{
+			out[2 * (a * (W / 4) + v)] = make_float4(pl[a][4 * v], pl[a][4 * v + 1], pl[a][4 * v + 2], pl[a][4 * v + 3]);
+			out[2 * (a * (W / 4) + v) + 1] = make_float4(pl[3 + a][4 * v], pl[3 + a][4 * v + 1], pl[3 + a][4 * v + 2], pl[3 + a][4 * v + 3]);
+		}
 #pragma unroll
 	for(int v = 0; v < W / 4; ++v)
-		out[6 * (W / 4) + v] = make_float4(__int_as_float(link[4 * v]), __int_as_float(link[4 * v + 1]), __int_as_float(link[4 * v + 2]), __int_as_float(link[4 * v + 3]));
-	out[7 * (W / 4)] = make_float4(__int_as_float(cnt), 0.f, 0.f, 0.f);
+	{
+		out[2 * (3 * (W / 4) + v)] = make_float4(__int_as_float(link[4 * v]), __int_as_float(link[4 * v + 1]), __int_as_float(link[4 * v + 2]), __int_as_float(link[4 * v + 3]));
+		out[2 * (3 * (W / 4) + v) + 1] = make_float4(__int_as_float(cnt), 0.f, 0.f, 0.f);
+	}
 }
 
 __global__ void k_emit_tris(int n, const int *__restrict__ vals, const float4 *__restrict__ v0e, const float4 *__restrict__ e1i,

@@ -499,62 +499,76 @@ inline bool prepLight(const yafgpu_light &l, LightDev &d, std::string &err)
 // The horizontal map carries -INF in that slot, which reproduces exactly that (pinned by the soft-shadow parity renders).  The vertical map can only
 // be overrun in the thin ring where the fast-cosine cut-off lets the angle pass its last entry; there the reference's result depends on heap contents
 // (its golden renders behave as if the element were large: the last cell is kept), so that slot carries +INF.
+// IESNA LM-63 photometric file -> the three tables IesData holds (vertical angles, horizontal angles, candela map).  Own reader: the
+// text is cut into whitespace-separated tokens once and the LM-63 record is read field by field from a cursor; the numbers it yields are
+// what the reference's stream extraction yields on a well-formed file (pinned by the IES parity renders), the code shares nothing with it.
+struct IesTokens
+{
+	std::vector<std::pair<const char *, size_t>> tok; size_t pos = 0;
+	explicit IesTokens(const char *p, size_t n)
+	{
+		size_t i = 0;
+		while(i < n)
+		{
+			while(i < n && isspace((unsigned char)p[i])) ++i;
+			const size_t b = i;
+			while(i < n && !isspace((unsigned char)p[i])) ++i;
+			if(i > b) tok.emplace_back(p + b, i - b);
+		}
+	}
+	bool done() const { return pos >= tok.size(); }
+	std::string text(size_t k) const { return std::string(tok[k].first, tok[k].second); }
+	void skip(size_t k) { pos += k; }
+	double number() { if(done()) return 0.0; const std::string t = text(pos++); return strtod(t.c_str(), nullptr); }
+	bool seek(const char *needle)   // position the cursor just behind the first token that contains `needle`
+	{
+		for(size_t k = pos; k < tok.size(); ++k) if(text(k).find(needle) != std::string::npos) { pos = k + 1; return true; }
+		return false;
+	}
+};
+
 inline bool buildIesTables(const yafgpu_light &l, LightDev &d, std::vector<float> &tab, std::string &err)
 {
 	if(!l.ies_data || l.ies_size < 7) { err = "ieslight: IES file missing or too small"; return false; }
-	const std::string text(l.ies_data, l.ies_size);
-	if(text.compare(0, 6, "IESNA:") != 0) { err = "ieslight: wrong file format, first characters are not \"IESNA:\""; return false; }
-	std::istringstream fin(text);
-	std::string line;
-	fin >> line;
-	while(line.find("TILT=") == std::string::npos)
+	if(strncmp(l.ies_data, "IESNA:", 6) != 0) { err = "ieslight: wrong file format, first characters are not \"IESNA:\""; return false; }
+	IesTokens in(l.ies_data, l.ies_size);
+	// keyword lines end at the TILT= line; TILT=INCLUDE carries <lamp-to-luminaire geometry> <n pairs> <n angles> <n multiplying factors>
+	if(!in.seek("TILT=")) { err = "ieslight: no TILT= entry in the IES file"; return false; }
+	if(in.text(in.pos - 1) == "TILT=INCLUDE")
 	{
-		if(!(fin >> line)) { err = "ieslight: no TILT= entry in the IES file"; return false; }
+		in.skip(1);
+		const int n_pairs = (int)in.number();
+		in.skip((size_t)std::max(0, n_pairs) * 2);
 	}
-	if(line == "TILT=INCLUDE")
-	{
-		int pairs = 0;
-		fin >> line;
-		fin >> pairs;
-		for(int i = 0; i < (pairs * 2); i++) fin >> line;
-	}
-	float candela_mult = 0.f;
-	int nv = 0, nh = 0, type = 0;
-	fin >> line; fin >> line;
-	fin >> candela_mult;
-	fin >> nv; fin >> nh;
-	fin >> type;
-	fin >> line;
-	float w = 0.f, lg = 0.f, h = 0.f;
-	fin >> w; fin >> lg; fin >> h;
-	fin >> line; fin >> line; fin >> line;
+	// photometric record: lamps, lumens per lamp, candela multiplier, vertical count, horizontal count, photometric type, units type,
+	// width, length, height, ballast factor, (future use), input watts
+	in.skip(2);
+	(void)in.number();                       // candela multiplier: read, not applied (IesData keeps the raw candela values)
+	int nv = (int)in.number(), nh = (int)in.number();
+	const int type = (int)in.number();
+	in.skip(1 + 3 + 3);
 	if(nv < 1 || nh < 1 || nv > (1 << 16) || nh > (1 << 16)) { err = "ieslight: implausible angle counts in the IES file"; return false; }
-	std::vector<float> vert((size_t)nv, 0.f);
-	float max_v = 0.f;
-	for(int i = 0; i < nv; ++i) { fin >> vert[i]; if(max_v < vert[i]) max_v = vert[i]; }
+	std::vector<float> vert((size_t)nv);
+	for(float &a : vert) a = (float)in.number();
+	float max_v = *std::max_element(vert.begin(), vert.end());
+	if(max_v < 0.f) max_v = 0.f;
 	if(vert[0] > 0.f)
-	{
-		const float minus = vert[0];
-		max_v -= minus;
-		for(int i = 0; i < nv; ++i) vert[i] -= minus;
+	{	// a vertical range that does not start at 0 is shifted down to 0
+		const float first = vert[0];
+		max_v -= first;
+		for(float &a : vert) a -= first;
 	}
-	max_v = (float)((double)max_v * 0.01745329251994329576922); // DEG_TO_RAD: float * double
-	bool h_adjust = false;
-	if(type == 1 /* TypeC */ && nh == 1) { nh++; h_adjust = true; }
-	std::vector<float> hor((size_t)nh, 0.f);
-	for(int i = 0; i < nh; ++i)
-	{
-		if(i == nh - 1 && h_adjust) hor[i] = 180.f;
-		else fin >> hor[i];
-	}
+	max_v = (float)((double)max_v * 0.01745329251994329576922); // degrees -> radians, float * double as in IesData
+	// a type C file with one horizontal plane is axially symmetric: the plane is duplicated at 180 degrees
+	const bool mirrored = type == 1 && nh == 1;
+	const int nh_file = nh;
+	if(mirrored) nh = 2;
+	std::vector<float> hor((size_t)nh), rad((size_t)nh * nv);
+	for(int i = 0; i < nh_file; ++i) hor[i] = (float)in.number();
+	for(int i = 0; i < nh_file; ++i) for(int j = 0; j < nv; ++j) rad[(size_t)i * nv + j] = (float)in.number();
+	if(mirrored) { hor[1] = 180.f; std::copy(rad.begin(), rad.begin() + nv, rad.begin() + nv); }
 	float max_rad = 0.f;
-	std::vector<float> rad((size_t)nh * nv, 0.f);
-	for(int i = 0; i < nh; ++i) for(int j = 0; j < nv; ++j)
-	{
-		if(i == nh - 1 && h_adjust) rad[(size_t)i * nv + j] = rad[(size_t)(i - 1) * nv + j];
-		else fin >> rad[(size_t)i * nv + j];
-		if(max_rad < rad[(size_t)i * nv + j]) max_rad = rad[(size_t)i * nv + j];
-	}
+	for(float r : rad) if(max_rad < r) max_rad = r;
 	max_rad = 1.f / max_rad;
 	d.cdf_offset = (int)tab.size(); d.cdf_count = nv + 1 + nh + 1 + nh * nv;
 	d.ies_nv = nv; d.ies_nh = nh; d.ies_type = type; d.ies_max_rad = max_rad;

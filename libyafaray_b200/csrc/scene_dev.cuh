@@ -18,12 +18,13 @@ enum { TRI_VIS_CAMERA = 1,  // visibility in {Normal, VisibleNoShadows}      kdt
        TRI_TRANSPARENT = 4  // Material::isTransparent()                     kdtree_triangle.cc:1106
 };
 
-// W-wide BVH node, W = 4 (128 B = one cache line) or W = 8 (256 B), float32 child planes in structure-of-arrays form so that one
-// 16-byte load fetches the same plane of four children and the ray's direction signs pick the near / far plane by ADDRESS:
-//   plane a (a = 0..5: lo.x, lo.y, lo.z, hi.x, hi.y, hi.z) of children 4v..4v+3 = float4 at index a * (W/4) + v
-//   links of children 4v..4v+3 = int4 at index 6 * (W/4) + v:  >= 0 inner node index; < 0 leaf, ~link = (first << 3) | (count - 1)
-//   into the TriAccel array; 0x80000000 = no child (its box is inverted, lo = +FLT_MAX > hi, so the box test alone rejects it)
-//   float4 at index 7 * (W/4): child count (rest of the node is padding)
+// W-wide BVH node, W = 4 (128 B = one cache line) or W = 8 (256 B), float32 child planes, laid out in 32-byte chunks so that the
+// traversal fetches a node with 256-bit loads (LDG.E.256: one L1 wavefront per chunk and lane instead of two 128-bit ones — the
+// traversal kernels sit at 80-93 % of the L1 pipe, profiles/r2_ncu_summary.txt).  With V = W / 4:
+//   chunk a * V + v (a = 0, 1, 2 = x, y, z): [ lo.a of children 4v..4v+3 | hi.a of children 4v..4v+3 ]
+//   chunk 3 * V + v                        : [ links of children 4v..4v+3 | child count, padding ]
+//   link >= 0 inner node index; < 0 leaf, ~link = (first << 3) | (count - 1) into the TriAccel array; 0x80000000 = no child (its box
+//   is inverted, lo = +FLT_MAX > hi, so the box test alone rejects it)
 // The TriAccel records stay full float32: the boxes only cull, Triangle::intersect decides.
 #define YG_NO_CHILD ((int)0x80000000)
 

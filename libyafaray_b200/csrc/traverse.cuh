@@ -77,23 +77,30 @@ struct TravStack
 // parallel to an axis is then tested with slopes of 1e30, which decides "inside the slab or not" exactly as it should)
 __device__ __forceinline__ float safeInv(float d) { return 1.f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d)); }
 
-__device__ __forceinline__ float comp4(const float4 v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
+// one 32-byte chunk through the read-only path: LDG.E.256 on sm_100a
+struct __align__(32) F8 { float v[8]; };
+__device__ __forceinline__ F8 ld256(const void *p)
+{
+	F8 r;
+	asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+	             : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7]) : "l"(p));
+	return r;
+}
 
 // Per-ray traversal state: the constants of the box test, the search interval and the stack position.
 struct TravRay
 {
 	V3 o, d;
 	float idx, idy, idz, ox, oy, oz;   // 1/d (safe) and -o/d
-	int nx, ny, nz;                    // float4 index of the near plane of each axis inside a node (far = 3V / 5V / 7V - near)
+	bool px, py, pz;                   // direction signs: the near plane of an axis is its lo plane when positive
 	float tlo, z;                      // box tests clip to [tlo, z]; z is the far limit of the search (the closest hit so far)
 	int cur, sp;
 	__device__ __forceinline__ void start(const Accel &acc, const V3 o_, const V3 d_, float tlo_, float z_)
 	{
-		constexpr int V = YG_BVH_WIDTH / 4;
 		o = o_; d = d_;
 		idx = safeInv(d.x); idy = safeInv(d.y); idz = safeInv(d.z);
 		ox = -o.x * idx; oy = -o.y * idy; oz = -o.z * idz;
-		nx = idx >= 0.f ? 0 : 3 * V; ny = idy >= 0.f ? V : 4 * V; nz = idz >= 0.f ? 2 * V : 5 * V;
+		px = idx >= 0.f; py = idy >= 0.f; pz = idz >= 0.f;
 		tlo = fmaxf(tlo_, 0.f); z = z_;
 		sp = 0; cur = acc.n_tris != 0 ? acc.root : YG_NO_CHILD;
 	}
@@ -122,26 +129,27 @@ template<bool ORDERED, bool COUNT, int NS>
 __device__ __forceinline__ void nodeStep(const Accel &acc, TravRay &r, TravStack<NS> &st, TravCounters *cnt)
 {
 	constexpr int W = YG_BVH_WIDTH, V = W / 4;
-	const float4 *nd = (const float4 *)acc.nodes + (size_t)r.cur * YG_NODE_U4;
+	const char *nd = (const char *)(acc.nodes + (size_t)r.cur * YG_NODE_U4);
 	if(COUNT) cnt->nodes++;
 	const float zf = r.z * 1.0000004f;
-	const int fx = 3 * V - r.nx, fy = 5 * V - r.ny, fz = 7 * V - r.nz;
 	const int limit = acc.stack_limit;
 	unsigned key[W];   // entry distance bits with the slot in the low 3 bits; 0xffffffff = missed
 	int link[W];
 #pragma unroll
 	for(int v = 0; v < V; ++v)
 	{
-		const float4 pnx = __ldg(nd + r.nx + v), pny = __ldg(nd + r.ny + v), pnz = __ldg(nd + r.nz + v);
-		const float4 pfx = __ldg(nd + fx + v), pfy = __ldg(nd + fy + v), pfz = __ldg(nd + fz + v);
-		const float4 lk = __ldg(nd + 6 * V + v);
+		const F8 cx = ld256(nd + 32 * v), cy = ld256(nd + 32 * (V + v)), cz = ld256(nd + 32 * (2 * V + v)), cl = ld256(nd + 32 * (3 * V + v));
 #pragma unroll
 		for(int j = 0; j < 4; ++j)
 		{
 			const int k = 4 * v + j;
-			const float tn = fmaxf(fmaxf(fmaf(comp4(pnx, j), r.idx, r.ox), fmaf(comp4(pny, j), r.idy, r.oy)), fmaxf(fmaf(comp4(pnz, j), r.idz, r.oz), r.tlo));
-			const float tf = fminf(fminf(fmaf(comp4(pfx, j), r.idx, r.ox), fmaf(comp4(pfy, j), r.idy, r.oy)), fminf(fmaf(comp4(pfz, j), r.idz, r.oz), zf));
-			link[k] = __float_as_int(comp4(lk, j));
+			// near / far plane of each axis by the direction sign
+			const float nxp = r.px ? cx.v[j] : cx.v[4 + j], fxp = r.px ? cx.v[4 + j] : cx.v[j];
+			const float nyp = r.py ? cy.v[j] : cy.v[4 + j], fyp = r.py ? cy.v[4 + j] : cy.v[j];
+			const float nzp = r.pz ? cz.v[j] : cz.v[4 + j], fzp = r.pz ? cz.v[4 + j] : cz.v[j];
+			const float tn = fmaxf(fmaxf(fmaf(nxp, r.idx, r.ox), fmaf(nyp, r.idy, r.oy)), fmaxf(fmaf(nzp, r.idz, r.oz), r.tlo));
+			const float tf = fminf(fminf(fmaf(fxp, r.idx, r.ox), fmaf(fyp, r.idy, r.oy)), fminf(fmaf(fzp, r.idz, r.oz), zf));
+			link[k] = __float_as_int(cl.v[j]);
 			// the boxes carry an absolute pad of 2^-19 of the scene size (bvh_build.cu), which covers the rounding of these six products;
 			// an absent child has an inverted box and fails here
 			key[k] = (tn <= tf) ? ((__float_as_uint(tn) & ~7u) | (unsigned)k) : 0xffffffffu;

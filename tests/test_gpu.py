@@ -176,6 +176,41 @@ def test_render_converges_to_reference_image(ctx, name):
     assert abs(float(img.mean()) / float(ref.mean()) - 1.0) <= 5e-4
 
 
+def test_converged_render_is_within_1e_3_of_the_converged_reference(ctx):
+    """north_star: per-pixel RMSE <= 1e-3 relative to the converged image.  The converged REFERENCE image is built as BASELINE.md §3.6
+    prescribes: the mean of K >= 16 renders of the reference's own CPU path tracer with distinct adv_base_sampling_offset
+    (environment.cc:773,807), 65 536 spp each (tools/make_converged_mean.py; the fixture also holds the reference's own noise floor: the
+    means of the two halves of its renders against each other).  Scene: BASELINE config 2's Cornell box (ShinyDiffuse + Glass, area
+    light, bounces 8, Russian roulette on) at 32x18.  The GPU image is the mean of 4 K renders of 65 536 spp (float64 mean of float32
+    films, like the reference side: one multi-million-spp float32 film would round small samples away)."""
+    from libyafaray_b200 import render_scene, scenes
+    path = os.path.join(ou.GOLDEN, "cornell_pt_mean_converged.npz")
+    if not os.path.exists(path):
+        pytest.skip("no converged-mean fixture")
+    z = np.load(path)
+    ref, S, K, w, h = z["image"].astype(np.float64), int(z["S"]), int(z["K"]), int(z["width"]), int(z["height"])
+    assert K >= 16
+    acc = np.zeros_like(ref)
+    n = 4 * K
+    same_spp = None
+    for k in range(n):
+        y = scenes.cornell_box(w, h, S, path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2)
+        y.render_params["adv_base_sampling_offset"] = ("int", k * S)
+        acc += _img(render_scene(y, ctx=ctx))[..., :3]
+        if k + 1 == K:
+            same_spp = ou.rel_rmse(acc / K, ref)     # the same K * S samples per pixel as the reference used
+    gpu = acc / n
+    rel = ou.rel_rmse(gpu, ref)
+    # half-vs-half RMSE = sqrt(2) sigma(half) and sigma(all) = sigma(half) / sqrt(2): the reference's own distance from the truth at K * S spp
+    floor = float(z["half_vs_half_rmse"]) / 2.0
+    print("rel. RMSE vs the converged reference (%d spp): %.3e with the GPU at %d spp, %.3e with the GPU at the reference's spp; "
+          "reference's own noise floor: %.3e (its two halves against each other: %.3e)" % (K * S, rel, n * S, same_spp, floor, float(z["half_vs_half_rmse"])))
+    assert rel <= 1e-3, rel
+    assert abs(float(gpu.mean()) / float(ref.mean()) - 1.0) <= 3e-4
+    # indistinguishable from a reference realisation: at equal spp the GPU is no farther from the reference's mean than two reference halves are from each other
+    assert same_spp <= 1.25 * float(z["half_vs_half_rmse"]), (same_spp, float(z["half_vs_half_rmse"]))
+
+
 # ---- size-independent properties at BASELINE.json's full frame size ------------------------------------------------------------
 def test_film_is_linear_in_sample_ranges_full_size(ctx):
     """[0,2) + [2,4) rendered as two calls == [0,4) in one call; tile partitions 0/2 + 1/2 == whole frame (1920x1080)."""

@@ -3,11 +3,12 @@
 S samples per pixel.  The offsets are k * S, so the K renders use consecutive ranges of the QMC sequences: their mean IS the K*S-spp
 render, up to the Russian-roulette stream.
 
-Writes tests/golden/<name>_mean_converged.npz: image (float32 mean), spp_total, K, S, and the reference's own noise floor —
-`loo_rmse`: relative RMSE of every single S-spp render against the mean of the OTHER K-1 (what one reference realisation at S spp
-scores against a converged image), from which the floor at K*S spp follows as loo_rmse.mean() / sqrt(K) for independent renders.
+Incremental: the fixture tests/golden/<name>_mean_converged.npz keeps `block_means` / `block_counts` (the first run's 16 renders are one
+block, every later render its own), so the tool can be left running to add renders; `image` is the mean over all of them, `K`, `S`,
+`spp_total` say how many, `half_vs_half_rmse` is the relative RMSE between the means of the two halves of the blocks (the reference's own
+noise floor at HALF the total spp), `loo_rmse` the leave-one-out RMSE of the single-render blocks against the mean of everything else.
 
-    python tools/make_converged_mean.py cornell_pt 32 18 65536 16"""
+    python tools/make_converged_mean.py cornell_pt 32 18 65536 <renders to add> [threads]"""
 import os
 import sys
 import time
@@ -26,29 +27,48 @@ CASES = {
 }
 
 
+def save(out, means, counts, S, w, h, seconds):
+    means, counts = np.asarray(means, np.float64), np.asarray(counts, np.int64)
+    K = int(counts.sum())
+    total = (means * counts[:, None, None, None]).sum(axis=0)
+    image = total / K
+    # two halves of the blocks by sample count
+    order = np.argsort(-counts, kind="stable")
+    a, b, ca, cb = 0.0, 0.0, 0, 0
+    for i in order:
+        if ca <= cb:
+            a = a + means[i] * counts[i]; ca += counts[i]
+        else:
+            b = b + means[i] * counts[i]; cb += counts[i]
+    half = ou.rel_rmse(a / max(ca, 1), b / max(cb, 1)) if ca and cb else 0.0
+    loo = [ou.rel_rmse(means[i], (total - means[i]) / (K - 1)) for i in range(len(counts)) if counts[i] == 1 and K > 1]
+    np.savez_compressed(out, image=image.astype(np.float32), spp_total=K * S, K=K, S=S, width=w, height=h, block_means=means.astype(np.float32),
+                        block_counts=counts, half_vs_half_rmse=half, half_counts=np.array([ca, cb]), loo_rmse=np.array(loo if loo else [0.0]), seconds=seconds)
+    return K, half
+
+
 def main():
-    name, w, h, S, K = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
+    name, w, h, S, add = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
     threads = int(sys.argv[6]) if len(sys.argv) > 6 else -1
-    imgs = []
+    out = os.path.join(ou.GOLDEN, "%s_mean_converged.npz" % name)
+    means, counts, seconds = [], [], 0.0
+    if os.path.exists(out):
+        z = np.load(out)
+        assert int(z["S"]) == S and int(z["width"]) == w and int(z["height"]) == h
+        if "block_means" in z.files:
+            means, counts = list(z["block_means"].astype(np.float64)), list(z["block_counts"])
+        else:   # first-generation fixture: one block of K renders
+            means, counts = [z["image"].astype(np.float64)], [int(z["K"])]
+        seconds = float(z["seconds"])
     t0 = time.time()
-    for k in range(K):
+    for _ in range(add):
+        k = int(np.sum(counts)) if counts else 0
         y = CASES[name](w, h, S)
         y.render_params["adv_base_sampling_offset"] = ("int", k * S)
         film, info = ou.run_reference_render(y, threads=threads, flavour="ieee", timeout=24 * 3600)
-        imgs.append(film_to_image(film)[..., :3].astype(np.float64))
-        print("render %d/%d  %.0f s total, rendert %.1f s" % (k + 1, K, time.time() - t0, info["rendert_s"]), flush=True)
-    imgs = np.stack(imgs)
-    mean = imgs.mean(axis=0)
-    loo = []
-    for k in range(K):
-        others = (imgs.sum(axis=0) - imgs[k]) / (K - 1)
-        loo.append(ou.rel_rmse(imgs[k], others))
-    half = ou.rel_rmse(imgs[: K // 2].mean(axis=0), imgs[K // 2:].mean(axis=0))
-    out = os.path.join(ou.GOLDEN, "%s_mean_converged.npz" % name)
-    np.savez_compressed(out, image=mean.astype(np.float32), spp_total=K * S, K=K, S=S, width=w, height=h, loo_rmse=np.array(loo), half_vs_half_rmse=half,
-                        seconds=time.time() - t0)
-    print(out, "leave-one-out rel. RMSE of one %d-spp reference render: mean %.3e; two halves (%d spp each) against each other: %.3e"
-          % (S, float(np.mean(loo)), K // 2 * S, half))
+        means.append(film_to_image(film)[..., :3].astype(np.float64)); counts.append(1)
+        K, half = save(out, means, counts, S, w, h, seconds + time.time() - t0)
+        print("render %d done (%.0f s this run), K = %d, half-vs-half rel. RMSE %.3e" % (k, time.time() - t0, K, half), flush=True)
 
 
 if __name__ == "__main__":

@@ -15,8 +15,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def klass(name):
     if "k_shade" in name or "k_bin_" in name:
         return "k_shade"
-    if "k_trace" in name or "k_shadow" in name:
-        return "k_trace+k_shadow"
+    if "k_trace" in name:
+        return "k_trace"
+    if "k_shadow" in name:
+        return "k_shadow"
     return None
 
 
@@ -41,10 +43,10 @@ def main(csv_path, bench_path, tag):
     bench = json.loads(open(bench_path).read().strip().splitlines()[-1])
     samples_step = bench["config"]["camera_samples_per_step"]
     waves = int(round(bench.get("waves_per_step", -(-samples_step // (1 << 20)))))
-    step, films = [], 0
+    step, films, build = [], 0, []
     for i, L in launches.items():
-        if "k_tri_setup" in L["name"] or "k_morton" in L["name"] or "cub::" in L["name"] or "k_hierarchy" in L["name"] or "k_refit" in L["name"] \
-                or "k_emit" in L["name"] or "k_tri_shade" in L["name"]:
+        if any(t in L["name"] for t in ("k_tri_setup", "k_morton", "cub::", "DeviceRadixSort", "k_hierarchy", "k_refit", "k_emit", "k_tri_shade", "k_pad_boxes", "k_collapse")):
+            build.append(L)
             continue
         step.append(L)
         if "k_film_add" in L["name"]:
@@ -62,7 +64,7 @@ def main(csv_path, bench_path, tag):
                 continue
             d[k]["launches"] += 1; d[k]["ns"] += ns; d[k]["dram"] += dram
     kern = bench["roofline"]["kernels"]
-    side_steps = min(bench["steps"], 4)
+    side_steps = min(bench["steps"], 3)
     out = {"tag": tag, "source": os.path.basename(csv_path), "waves_per_step": waves, "complete_step": films == waves}
     for k, a in agg.items():
         units_step = kern[k]["units"] / side_steps
@@ -71,8 +73,8 @@ def main(csv_path, bench_path, tag):
     with open(os.path.join(ROOT, "profiles", "ncu_traffic.json"), "w") as fh:
         json.dump(out, fh, indent=1)
     tot = sum(v["ns"] for v in byname.values())
-    lines = ["# %s — ncu launch list of one bench step (Cornell 1920x1080, 4 spp per step = %d wave%s)" % (tag, waves, "" if waves == 1 else "s"), "",
-             "Command: `ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c N --csv python bench.py --steps 1 --warmup 0 --no-cpu`",
+    lines = ["# %s — ncu launch list of one bench step (%s, %d wave%s per step)" % (tag, bench["config"]["workload"], waves, "" if waves == 1 else "s"), "",
+             "Command: `ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c N --csv python bench.py --steps 2 --warmup 1 --no-cpu`",
              "(per-launch times under ncu are serialised and cold-cache: compare SHARES with bench.py's `roofline.kernels[*].share_of_step`, not absolutes).", "",
              "| kernel | launches | GPU time ms | share | DRAM MB |", "|---|---|---|---|---|"]
     for k, v in sorted(byname.items(), key=lambda kv: -kv[1]["ns"]):
@@ -82,6 +84,18 @@ def main(csv_path, bench_path, tag):
     for k in agg:
         o = out[k]
         lines.append("| %s (per %s) | %.1f | %.1f | %.2f |" % (k, kern[k]["unit"], o["dram_bytes_per_unit"], o["alg_bytes_per_unit"], o["dram_bytes_per_unit"] / max(1e-9, o["alg_bytes_per_unit"])))
+    # the upload that precedes the step: BVH build kernels (the radix sort is the one library primitive on the path)
+    btot = sum(L["m"].get("gpu__time_duration.sum", 0.0) for L in build)
+    bsort = sum(L["m"].get("gpu__time_duration.sum", 0.0) for L in build if "cub::" in L["name"] or "DeviceRadixSort" in L["name"])
+    if build:
+        bn = collections.defaultdict(lambda: [0, 0.0])
+        for L in build:
+            short = L["name"].split("(")[0].replace("void ", "").replace("yg::", "")[:70]
+            bn[short][0] += 1; bn[short][1] += L["m"].get("gpu__time_duration.sum", 0.0)
+        lines += ["", "## BVH build kernels of the uploads in the capture (%d launches, %.2f ms under ncu; cub::DeviceRadixSort share %.1f %%)" % (len(build), btot / 1e6, 100 * bsort / max(1.0, btot)), "",
+                  "| kernel | launches | GPU time ms | share |", "|---|---|---|---|"]
+        for k, v in sorted(bn.items(), key=lambda kv: -kv[1][1]):
+            lines.append("| `%s` | %d | %.3f | %.1f %% |" % (k, v[0], v[1] / 1e6, 100 * v[1] / btot))
     with open(os.path.join(ROOT, "profiles", "%s_launches.md" % tag), "w") as fh:
         fh.write("\n".join(lines) + "\n")
     print("\n".join(lines))
