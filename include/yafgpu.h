@@ -483,6 +483,10 @@ typedef struct yafgpu_scene_desc
 	yafgpu_background background;
 	yafgpu_film_desc film;
 	yafgpu_integrator_desc integrator;
+	/* CIE 1931 colour matching functions, 471 rows (360..830 nm, 1 nm) of x, y, z — the table behind wl2RgbFromCie__ (spectrum.cc:276-289).
+	 * Needed only when a glass / rough_glass material has dispersion_power > 0 (upload fails without it); the reference-side adaptor fills it
+	 * from the reference's own wl2Xyz__, the Python mirror from libyafaray_b200/data/cie_xyz_360_830.npy (tools/make_cie_table.py). */
+	const float *cie_xyz; size_t n_cie_rows;
 } yafgpu_scene_desc;
 
 /* ---- rays and hits (parity probe + traversal microbench) -------------------------------- */

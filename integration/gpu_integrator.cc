@@ -37,6 +37,7 @@
 #include <mutex>
 #include <set>
 #include <sstream>
+#include "common/spectrum.h"
 #include <string>
 #include <thread>
 #include <vector>
@@ -726,6 +727,12 @@ bool GpuIntegrator::preprocess()
 		f.base_sampling_offset = film->getBaseSamplingOffset();
 	}
 	if(!fillIntegrator(d.integrator, err)) return fail(err);
+	// CIE table for dispersive glass: rows 360..829 nm are wl2Xyz__ at integer wavelengths (the interpolation weights are 1 and 0 there), row 830
+	// follows from the midpoint 829.5 nm; only 400..700 nm is ever looked up (spectrum.h:41-46)
+	std::vector<float> cie(471 * 3, 0.f);
+	for(int i = 0; i < 470; ++i) { const Rgb c = wl2Xyz__(360.f + (float)i); cie[3 * i] = c.r_; cie[3 * i + 1] = c.g_; cie[3 * i + 2] = c.b_; }
+	{ const Rgb c = wl2Xyz__(829.5f); cie[3 * 470] = 2.f * c.r_ - cie[3 * 469]; cie[3 * 470 + 1] = 2.f * c.g_ - cie[3 * 469 + 1]; cie[3 * 470 + 2] = 2.f * c.b_ - cie[3 * 469 + 2]; }
+	d.cie_xyz = cie.data(); d.n_cie_rows = 471;
 	if(yafgpu_group_upload_scene(grp_, &d) != YAFGPU_OK) return fail("scene upload refused");
 	yafgpu_stats st;
 	yafgpu_group_get_stats(grp_, &st);

@@ -158,7 +158,8 @@ class SceneDesc(C.Structure):
                 ("n_materials", C.c_size_t), ("lights", C.POINTER(Light)), ("n_lights", C.c_size_t),
                 ("textures", C.POINTER(Texture)), ("n_textures", C.c_size_t),
                 ("nodes", C.POINTER(ShaderNode)), ("n_nodes", C.c_size_t),
-                ("camera", Camera), ("background", Background), ("film", FilmDesc), ("integrator", IntegratorDesc)]
+                ("camera", Camera), ("background", Background), ("film", FilmDesc), ("integrator", IntegratorDesc),
+                ("cie_xyz", C.POINTER(C.c_float)), ("n_cie_rows", C.c_size_t)]
 
 
 class PassDesc(C.Structure):

@@ -62,6 +62,7 @@ static void freeScene(yafgpu_ctx *c)
 	c->light_bvh_ptrs.clear();
 	for(void *q : c->tex_ptrs) poolFree(q, c->stream);
 	c->tex_ptrs.clear();
+	poolFree(c->d_cie, c->stream); c->d_cie = nullptr;
 	poolFree(c->d_textures, c->stream); c->d_textures = nullptr; poolFree(c->d_shader_nodes, c->stream); c->d_shader_nodes = nullptr;
 	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
 	c->d_tris = nullptr; c->d_objects = nullptr; c->d_mats = nullptr; c->d_lights = nullptr; c->d_light_tables = nullptr; c->d_bg_tex = nullptr;
@@ -294,6 +295,19 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		if((c->h_mats[i].type == YAFGPU_MAT_BLEND || c->h_mats[i].type == YAFGPU_MAT_MASK) && !finishBlend(c->h_mats, i, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": " + err);
 	}
 	for(size_t i = 0; i < desc->n_materials; ++i) { c->h_mats[i].obj_flags = c->h_mats[i].bsdf_flags; c->h_mats[i].is_mask = 0; }
+	bool any_dispersion = false;
+	for(size_t i = 0; i < desc->n_materials; ++i)
+	{
+		const MatDev &md = c->h_mats[i];
+		if(!md.disperse) continue;
+		any_dispersion = true;
+		// with an IOR shader the reference recomputes the Cauchy coefficients per hit (material_glass.cc:92-95)
+		if(md.node_count > 0 && md.slot[YAFGPU_SLOT_IOR] >= 0) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": dispersion together with an IOR shader is not implemented on the device");
+	}
+	for(size_t i = 0; i < desc->n_materials; ++i)
+		if((c->h_mats[i].type == YAFGPU_MAT_BLEND || c->h_mats[i].type == YAFGPU_MAT_MASK) && (c->h_mats[c->h_mats[i].mat1].disperse || c->h_mats[c->h_mats[i].mat2].disperse))
+			return setErr(c, YAFGPU_ERR_UNSUPPORTED, "material " + std::to_string(i) + ": blend / mask over a dispersive glass is not implemented on the device");
+	if(any_dispersion && (!desc->cie_xyz || desc->n_cie_rows < 471)) return setErr(c, YAFGPU_ERR_INVALID, "a material has dispersion_power > 0 but yafgpu_scene_desc.cie_xyz (471 rows) is missing");
 	for(size_t i = 0; i < desc->n_materials; ++i) triflags[i] = triFlagsOf(c->h_mats[i]);
 	for(size_t i = 0; i < desc->n_materials; ++i)
 	{	// Scene::isShadowed calls Material::getTransparency without initBsdf (kdtree_triangle.cc:1106-1124): with shader nodes it would read
@@ -444,6 +458,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	YG_CUDA(c, upload(c->d_textures, h_tex.data(), h_tex.size(), st));
 	YG_CUDA(c, upload(c->d_shader_nodes, h_nodes.data(), h_nodes.size(), st));
+	if(any_dispersion) YG_CUDA(c, upload(c->d_cie, desc->cie_xyz, (size_t)471 * 3, st));
 	YG_CUDA(c, poolAlloc(&c->d_tri_ng, sizeof(float) * 3 * (g.n_tris ? g.n_tris : 1), st));
 	YG_CUDA(c, poolAlloc(&c->d_tris, sizeof(TriShade) * (g.n_tris ? g.n_tris : 1), st));
 	if(g.tri_nidx) YG_CUDA(c, upload(d_nidx, g.tri_nidx, g.n_tris * 3, st));
@@ -510,7 +525,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 
 	s.points = c->d_points; s.normals = c->d_normals; s.uv = c->d_uv; s.tris = c->d_tris; s.objects = c->d_objects;
 	s.materials = c->d_mats; s.lights = c->d_lights; s.n_lights = (int)c->h_lights.size(); s.light_tables = c->d_light_tables; s.light_accels = c->d_light_accels; s.faure = c->d_faure;
-	s.textures = c->d_textures; s.nodes = c->d_shader_nodes;
+	s.textures = c->d_textures; s.nodes = c->d_shader_nodes; s.cie_xyz = c->d_cie; s.n_cie = c->d_cie ? 471 : 0;
 
 	// film (ImageFilm ctor + init)
 	prepFilm(desc->film, c->film);

@@ -93,6 +93,23 @@ inline void prepBeer(const yafgpu_mat_glass &p, MatDev &d)
 	d.bsdf_flags |= BsdfVolumetric;
 }
 
+// cauchyCoefficients__ (spectrum.cc:330-342) as the glass constructors call it (material_glass.cc:41-46, material_rough_glass.cc:40-45):
+// float members, the Fraunhofer-line squares are double products narrowed to float, (ior - 1.0) is a double expression
+inline void prepDispersion(const yafgpu_mat_glass &p, MatDev &d)
+{
+	d.disperse = 0; d.cauchy_a = 0.f; d.cauchy_b = 0.f;
+	if(!(p.dispersion_power > 0.f)) return;
+	d.disperse = 1;
+	d.bsdf_flags |= BsdfDispersive;
+	const float ior = p.ior, disp_pw = p.dispersion_power;
+	const float l_f_2 = (float)(486.13 * 486.13), ld_2 = (float)(587.56 * 587.56), l_c_2 = (float)(656.27 * 656.27);
+	const float vd = (float)(((double)ior - 1.0) / (double)disp_pw);   // Abbe number
+	float cauchy_b = (l_c_2 - l_f_2) * vd;
+	if(cauchy_b != 0.0) cauchy_b = (float)(((double)(l_f_2 * l_c_2) * ((double)ior - 1.0)) / (double)cauchy_b);
+	d.cauchy_b = cauchy_b;
+	d.cauchy_a = ior - cauchy_b / ld_2;
+}
+
 // GlassMaterial ctor + factory: material_glass.cc:32-49,311-379
 inline bool prepGlass(const yafgpu_material &m, MatDev &d, std::string &err)
 {
@@ -106,9 +123,9 @@ inline bool prepGlass(const yafgpu_material &m, MatDev &d, std::string &err)
 	d.bsdf_flags = BsdfAllSpecular;
 	if(d.fake_shadow) d.bsdf_flags |= BsdfFilter;
 	d.tm_flags = d.fake_shadow ? (BsdfFilter | BsdfTransmit) : (BsdfSpecular | BsdfTransmit);
-	d.disperse = 0;
-	if(p.dispersion_power > 0.f) { err = "glass: dispersion_power > 0 (spectral dispersion) is not implemented on the device"; return false; }
+	prepDispersion(p, d);
 	prepBeer(p, d);
+	if(d.disperse && d.absorb) { err = "glass: dispersion together with absorption is not implemented on the device (the reference applies the LAST wavelength sample's Beer transmittance to all of them, integrator_montecarlo.cc:841-845)"; return false; }
 	return true;
 }
 
@@ -166,8 +183,9 @@ inline bool prepRoughGlass(const yafgpu_material &m, MatDev &d, std::string &err
 	d.fake_shadow = p.fake_shadows ? 1 : 0;
 	d.bsdf_flags = BsdfAllGlossy;
 	if(d.fake_shadow) d.bsdf_flags |= BsdfFilter;
-	if(p.dispersion_power > 0.f) { err = "rough_glass: dispersion_power > 0 (spectral dispersion) is not implemented on the device"; return false; }
+	prepDispersion(p, d);
 	prepBeer(p, d);
+	if(d.disperse && d.absorb) { err = "rough_glass: dispersion together with absorption is not implemented on the device"; return false; }
 	return true;
 }
 

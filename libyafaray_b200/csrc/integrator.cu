@@ -52,6 +52,12 @@ __device__ __forceinline__ int stDepth(unsigned p) { return (p >> 6) & 63; }
 __device__ __forceinline__ int stDivision(unsigned p) { return (p >> 12) & 255; }
 __device__ __forceinline__ int stCaustic(unsigned p) { return (p >> 22) & 1; }
 __device__ __forceinline__ int stAddDepth(unsigned p) { return (p >> 23) & 31; }
+// bit 20: RenderState::chromatic_ == false — the task carries ONE wavelength (st.y of a TASK_INTEGRATE holds its bits), set by the dispersive
+// branch of recursiveRaytrace and inherited by everything below it
+#define YG_ST_MONO (1u << 20)
+// bit 21: this integrate() was called by the dispersive branch, which sets RenderState::include_lights_ = false for its children
+// (integrator_montecarlo.cc:799 "debatable..."); the glossy / specular branches set it back to true for theirs (:864,977)
+#define YG_ST_NOLIGHTS (1u << 21)
 
 // warp-aggregated queue slot allocation
 __device__ __forceinline__ int allocSlot(int *counter)
@@ -605,6 +611,9 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			}
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp); // Point3 h = ray.from_ + z * ray.dir_ (scene.cc:908)
+			const unsigned mono = packed & YG_ST_MONO;
+			sp.chromatic = mono ? 0 : 1; sp.wavelength = mono ? __uint_as_float(st.y) : 0.f;
+
 			// materials with shader nodes (kernel class YG_MAT_NODES): the node pass of initBsdf() resolves the bound shaders into a
 			// thread-local copy of the record (nodes.cuh); every other kernel reads the record in place
 			const MatDev *mp = &sc.materials[sp.mat];
@@ -617,7 +626,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			const int raylevel = stRaylevel(packed);
 			const int additional_depth = max(stAddDepth(packed), m.additional_depth);
 			const float2 dcv = in.dc[i];
-			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit<MT>(sc, m, sp, wo, true));
+			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit<MT>(sc, m, sp, wo, !(packed & YG_ST_NOLIGHTS)));
 			if(bsdfs & BsdfDiffuse)
 			{	// estimateAllDirectLight integrator_montecarlo.cc:47-60
 				for(int l = 0; l < sc.n_lights; ++l) doLightEstimation<MT>(cx, m, slot, si, l, sp, wo, (unsigned)l, ray_division, W);
@@ -654,6 +663,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 					for(int k = 0; k < n_samples; ++k)
 					{
 						const unsigned offs = (unsigned)ig.n_paths * (unsigned)si.pixel_sample + si.sampling_offs + (unsigned)k;
+						if(sp.chromatic) sp.wavelength = riS(offs);   // integrator_path_tracer.cc:196-197
 						float s_1 = riVdC(offs);
 						float s_2 = (float)scrHaltonT(*sc.faure, 2, offs);
 						if(ray_division > 1) { s_1 = addMod1(s_1, dcv.x); s_2 = addMod1(s_2, dcv.y); }
@@ -663,7 +673,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 						scol = scol * w;
 						if(isBlack(scol) || s.sampled == BsdfNone) continue; // contributes exactly zero in the reference as well
 						pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, (W * scol) * inv_n, scol, offs,
-						         packState(TASK_PATH, raylevel, 0, ray_division, 0, 0), 0u, 0.f, 0.f);
+						         packState(TASK_PATH, raylevel, 0, ray_division, 0, 0) | mono, 0u, 0.f, 0.f);
 					}
 				}
 			}
@@ -671,6 +681,38 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			const int rl = raylevel + 1;
 			if(rl <= ig.r_depth + additional_depth)
 			{
+				const unsigned child_wl = mono ? st.y : 0u;   // a single-wavelength task hands its wavelength down
+				if((bsdfs & BsdfDispersive) && sp.chromatic)
+				{	// dispersive branch, integrator_montecarlo.cc:796-858: 8 wavelengths (fewer below a ray division), each refracted with its own IOR
+					// and traced as a single-wavelength integrate() whose result is tinted by the wavelength's colour
+					int dsam = 8;
+					const int old_division = ray_division, old_offset = (int)st.w;
+					if(old_division > 1) dsam = max(1, dsam / old_division);
+					const int new_division = old_division * dsam;
+					int branch = new_division * old_offset;
+					const float d_1 = 1.f / (float)dsam;
+					const float ss_1 = riS((uint32_t)si.pixel_sample + si.sampling_offs);
+					for(int ns = 0; ns < dsam; ++ns)
+					{
+						float wl = ((float)ns + ss_1) * d_1;
+						const float dc1 = (float)scrHaltonT(*sc.faure, 2 * rl + 1, (unsigned)branch + si.sampling_offs);
+						const float dc2 = (float)scrHaltonT(*sc.faure, 2 * rl + 2, (unsigned)branch + si.sampling_offs);
+						if(old_division > 1) wl = addMod1(wl, dcv.x);
+						const unsigned ray_offset = (unsigned)branch;
+						++branch;
+						sp.wavelength = wl;   // stays set after the loop: getSpecular below reads the LAST sample's wavelength, as the reference's state does
+						BSample s; s.s1 = 0.5f; s.s2 = 0.5f; s.flags = BsdfReflect | BsdfTransmit | BsdfDispersive; s.pdf = 0.f; s.sampled = BsdfNone;
+						float w = 0.f; V3 wi = mk(0.f);
+						const Col mcol = matSample<MT>(sc, m, sp, wo, wi, s, w);
+						if(s.pdf > 1.0e-6f && (s.sampled & BsdfDispersive))
+						{
+							const Col f = ((mcol * wl2Rgb(sc, wl)) * w) * d_1;
+							if(!isBlack(f))
+								pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, W * f, mkc(1.f), __float_as_uint(wl),
+								         packState(TASK_INTEGRATE, rl, 0, new_division, 0, additional_depth) | YG_ST_MONO | YG_ST_NOLIGHTS, ray_offset, dc1, dc2);
+						}
+					}
+				}
 				if((bsdfs & BsdfGlossy) && rl < 20)
 				{
 					int gsam = 8;
@@ -689,7 +731,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 						const unsigned ray_offset = (unsigned)branch;
 						++branch;
 						const float s_1 = hal_2.getNext(), s_2 = hal_3.getNext();
-						const unsigned child = packState(TASK_INTEGRATE, rl, 0, new_division, 0, additional_depth);
+						const unsigned child = packState(TASK_INTEGRATE, rl, 0, new_division, 0, additional_depth) | mono;
 						// material->getFlags() here, not the flags initBsdf returned (integrator_montecarlo.cc:895-919): they differ under a mask_mat
 						const unsigned oflags = MT == MT_NODES ? m.obj_flags : m.bsdf_flags;
 						if(oflags & BsdfGlossy)
@@ -700,7 +742,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 								float w = 0.f; V3 wi = mk(0.f);
 								const Col mcol = matSample<MT>(sc, m, sp, wo, wi, s, w);
 								const Col f = (mcol * w) * d_1;
-								if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2, beerOf(m, sp, wi));
+								if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, W * f, mkc(1.f), child_wl, child, ray_offset, dc1, dc2, beerOf(m, sp, wi));
 							}
 							else if(MT == MT_NODES && m.is_mask) {} // MaskMaterial inherits the two-lobe Material::sample, which returns black and samples nothing
 							else if((oflags & BsdfReflect) && (oflags & BsdfTransmit))
@@ -711,12 +753,12 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 								if((s.sampled & BsdfReflect) && !(s.sampled & BsdfDispersive))
 								{
 									const Col f = (mcol[0] * w[0]) * d_1;
-									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[0]));
+									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * f, mkc(1.f), child_wl, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[0]));
 								}
 								if(s.sampled & BsdfTransmit)
 								{
 									const Col f = (mcol[1] * w[1]) * d_1;
-									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[1], W * f, mkc(1.f), 0u, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[1]));
+									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[1], W * f, mkc(1.f), child_wl, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[1]));
 								}
 							}
 						}
@@ -727,8 +769,8 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 					bool refl = false, refr = false;
 					V3 d2[2]; Col rcol[2];
 					matSpecular<MT>(sc, m, sp, wo, rl, refl, refr, d2, rcol);
-					const unsigned child = packState(TASK_INTEGRATE, rl, 0, ray_division, 0, additional_depth);
-					if(refl && !isBlack(rcol[0])) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * rcol[0], mkc(1.f), 0u, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[0]));
+					const unsigned child = packState(TASK_INTEGRATE, rl, 0, ray_division, 0, additional_depth) | mono;
+					if(refl && !isBlack(rcol[0])) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * rcol[0], mkc(1.f), child_wl, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[0]));
 					if(refr && !isBlack(rcol[1]))
 					{
 						V3 o = sp.p;
@@ -738,7 +780,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 							if(m.transp_bias_mult) tb *= (float)rl;
 							o = sp.p + d2[1] * tb;
 						}
-						pushTask(cx, slot, o, ig.ray_min_dist, d2[1], W * rcol[1], mkc(1.f), 0u, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[1]));
+						pushTask(cx, slot, o, ig.ray_min_dist, d2[1], W * rcol[1], mkc(1.f), child_wl, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[1]));
 					}
 				}
 			}
@@ -755,6 +797,8 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			}
 			SurfPt sp;
 			getSurface(sc, tri, hh.y, hh.z, from + hh.x * dir, sp);
+			const unsigned mono = packed & YG_ST_MONO;
+			sp.chromatic = mono ? 0 : 1; sp.wavelength = mono ? 0.f : riS(st.y);   // the path keeps the wavelength of its first segment (integrator_path_tracer.cc:196-197)
 			// materials with shader nodes (kernel class YG_MAT_NODES): the node pass of initBsdf() resolves the bound shaders into a
 			// thread-local copy of the record (nodes.cuh); every other kernel reads the record in place
 			const MatDev *mp = &sc.materials[sp.mat];
@@ -805,7 +849,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 				if(isBlack(scol)) continue;
 				const bool ncaustic = ig.trace_caustics && (s.sampled & (BsdfSpecular | BsdfGlossy | BsdfFilter));
 				pushTask(cx, slot, sp.p, ig.ray_min_dist, wi, Wp * scol, thr * scol, offs,
-				         packState(TASK_PATH, stRaylevel(packed), nd, ray_division, ncaustic ? 1 : 0, 0), 0u, 0.f, 0.f);
+				         packState(TASK_PATH, stRaylevel(packed), nd, ray_division, ncaustic ? 1 : 0, 0) | mono, 0u, 0.f, 0.f);
 			}
 		}
 	}

@@ -32,9 +32,40 @@ struct SurfPt
 	int mat;    // material index
 	int light;  // light index the hit object is tagged with (ObjectGeometric::light_), -1 = none
 	int tri;    // global triangle id
+	// RenderState::chromatic_ / wavelength_ (scene.h:97-99) of the task being shaded: only dispersive glass reads them
+	int chromatic; float wavelength;
 };
 
+// getIor__ (spectrum.h:35-39): wl = 300.0 * w + 400.0 is a double expression narrowed to float
+YG_D float cauchyIor(float w, float cauchy_a, float cauchy_b)
+{
+	const float wl = (float)(300.0 * (double)w + 400.0);
+	return cauchy_a + cauchy_b / (wl * wl);
+}
+// IOR the glass materials use at this hit: the Cauchy value at the task's wavelength while the full spectrum is still being carried
+// (disperse_ && state.chromatic_, material_glass.cc:83-96,148-155,267-274, material_rough_glass.cc:85-92,199-206), else ior_
+#define YG_IOR(m, sp) (((m).disperse && (sp).chromatic) ? cauchyIor((sp).wavelength, (m).cauchy_a, (m).cauchy_b) : (m).ior)
+
 struct BSample { float s1, s2, pdf; unsigned flags, sampled; };
+
+// wl2Rgb__ (spectrum.h:41-46) = wl2RgbFromCie__ (spectrum.cc:276-289: linear interpolation in the CIE 1931 table) + xyzToRgb__ (:264-273)
+YG_D Col wl2Rgb(const SceneDev &sc, float w)
+{
+	const float wl = (float)(300.0 * (double)w + 400.0);
+	float fr = wl - 360.f;
+	const int p_1 = (int)fr;
+	if(p_1 < 0 || p_1 + 1 > 470 || !sc.cie_xyz) return mkc(0.f);
+	fr -= floorf(fr);
+	const float fr_2 = 1.f - fr;
+	const float *a = sc.cie_xyz + 3 * p_1, *b = a + 3;
+	const float x = fr_2 * __ldg(a) + fr * __ldg(b), y = fr_2 * __ldg(a + 1) + fr * __ldg(b + 1), z = fr_2 * __ldg(a + 2) + fr * __ldg(b + 2);
+	Col c = mkc((2.28783848734076f * x - 0.833367677835217f * y) - 0.454470795871421f * z,
+	            (-0.511651380743862f * x + 1.42275837632178f * y) + 0.0888930017552939f * z,
+	            (0.00572040983140966f * x - 0.0159068485104036f * y) + 1.0101864083734f * z);
+	const float wt = fminf(c.r, fminf(c.g, c.b));
+	if(wt < 0.f) c = mkc(c.r - wt, c.g - wt, c.b - wt);
+	return c * 2.214032659670777114f;
+}
 
 YG_HD V3 ldv(const float *p) { return mk(p[0], p[1], p[2]); }
 YG_HD Col ldc(const float *p) { return mkc(p[0], p[1], p[2]); }
@@ -61,7 +92,7 @@ YG_D void getSurface(const SceneDev &sc, int tri, float b1, float b2, V3 hit, Su
 	else sp.n = sp.ng;
 	sp.p = hit;
 	createCs(sp.n, sp.nu, sp.nv);
-	sp.mat = mat; sp.light = ob.light; sp.tri = tri;
+	sp.mat = mat; sp.light = ob.light; sp.tri = tri; sp.chromatic = 1; sp.wavelength = 0.f;
 }
 
 // ---- helpers --------------------------------------------------------------------------------------------------------
@@ -550,29 +581,57 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 			return scolor;
 		}
 		case YAFGPU_MAT_GLASS:
-		{	// material_glass.cc:64-216 without dispersion (refused at upload)
-			if(!(s.flags & BsdfSpecular)) { s.pdf = 0.f; return mkc(0.f); }
+		{	// material_glass.cc:64-216
+			if(!(s.flags & BsdfSpecular) && !((s.flags & m.bsdf_flags & BsdfDispersive) && sp.chromatic)) { s.pdf = 0.f; return mkc(0.f); }
 			const bool outside = dot(sp.ng, wo) > 0;
 			const V3 n = glassNormal(sp, wo, outside);
 			s.pdf = 1.f;
 			V3 refdir;
-			if(refract(n, wo, refdir, m.ior))
+			const float cur_ior = YG_IOR(m, sp);
+			const bool spec_refl = (s.flags & (BsdfSpecular | BsdfReflect)) == (BsdfSpecular | BsdfReflect);
+			if(m.disperse && sp.chromatic)
+			{	// :83-138 the dispersion has to be sampled: the refracted direction belongs to one wavelength
+				if(refract(n, wo, refdir, cur_ior))
+				{
+					float kr, kt;
+					fresnel(wo, n, cur_ior, kr, kt);
+					const float p_kr = (float)(0.01 + 0.99 * (double)kr), p_kt = (float)(0.01 + 0.99 * (double)kt);
+					if(!(s.flags & BsdfSpecular) || s.s1 < p_kt)
+					{
+						wi = refdir; s.pdf = spec_refl ? p_kt : 1.f; s.sampled = BsdfDispersive | BsdfTransmit; w = 1.f;
+						return ldc(m.filter_col);
+					}
+					else if(spec_refl)
+					{
+						wi = reflect(wo, n); s.pdf = p_kr; s.sampled = BsdfSpecular | BsdfReflect; w = 1.f;
+						return ldc(m.spec_refl_col);
+					}
+				}
+				else if(spec_refl)
+				{
+					wi = reflect(wo, n); s.sampled = BsdfSpecular | BsdfReflect; w = 1.f;
+					return mkc(1.f);
+				}
+				s.pdf = 0.f;
+				return mkc(0.f);
+			}
+			if(refract(n, wo, refdir, cur_ior))
 			{
 				float kr, kt;
-				fresnel(wo, n, m.ior, kr, kt);
+				fresnel(wo, n, cur_ior, kr, kt);
 				const float p_kr = (float)(0.01 + 0.99 * (double)kr), p_kt = (float)(0.01 + 0.99 * (double)kt);
 				if(s.s1 < p_kt && ((s.flags & m.tm_flags) == m.tm_flags))
 				{
 					wi = refdir; s.pdf = p_kt; s.sampled = m.tm_flags; w = 1.f;
 					return ldc(m.filter_col);
 				}
-				else if((s.flags & (BsdfSpecular | BsdfReflect)) == (BsdfSpecular | BsdfReflect))
+				else if(spec_refl)
 				{
 					wi = reflect(wo, n); s.pdf = p_kr; s.sampled = BsdfSpecular | BsdfReflect; w = 1.f;
 					return ldc(m.spec_refl_col);
 				}
 			}
-			else if((s.flags & (BsdfSpecular | BsdfReflect)) == (BsdfSpecular | BsdfReflect))
+			else if(spec_refl)
 			{
 				wi = reflect(wo, n); s.sampled = BsdfSpecular | BsdfReflect; w = 1.f;
 				return mkc(1.f);
@@ -785,14 +844,14 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 			return scolor;
 		}
 		case YAFGPU_MAT_ROUGH_GLASS:
-		{	// material_rough_glass.cc:61-172 without dispersion
+		{	// material_rough_glass.cc:61-172
 			const V3 n = faceForward(sp.ng, sp.n, wo);
 			const bool outside = dot(sp.ng, wo) > 0.f;
 			s.pdf = 1.f;
 			const float alpha_2 = m.alpha_rough * m.alpha_rough;
 			V3 h = ggxSample(alpha_2, s.s1, s.s2);
 			h = normalize((h.x * sp.nu + h.y * sp.nv) + h.z * n);
-			const float cur_ior = m.ior;
+			const float cur_ior = YG_IOR(m, sp);
 			float glossy, glossy_d = 0.f, glossy_g = 0.f, wi_n, wi_h, jacobian;
 			const float cos_theta = dot(h, n);
 			const float cos_theta_2 = cos_theta * cos_theta;
@@ -813,7 +872,7 @@ YG_D Col leafSample(const MatDev &m, const SurfPt &sp, V3 wo, V3 &wi, BSample &s
 					jacobian = (ior_wi * ior_wi) / fmaxf(1.0e-8f, ht * ht);
 					glossy = fabsf((wo_h * wi_h) / (wi_n * wo_n)) * kt * glossy_g * glossy_d * jacobian;
 					s.pdf = glossy_d * cos_theta * (jacobian * fabsf(wi_h));
-					s.sampled = BsdfGlossy | BsdfTransmit;
+					s.sampled = ((m.disperse && sp.chromatic) ? BsdfDispersive : BsdfGlossy) | BsdfTransmit;
 					ret = glossy * ldc(m.filter_col);
 					w = fabsf(wi_n) / fmaxf(0.1f, s.pdf);
 				}
@@ -857,7 +916,7 @@ YG_D Col leafSample2(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tco
 	const float alpha_2 = m.alpha_rough * m.alpha_rough;
 	V3 h = ggxSample(alpha_2, s.s1, s.s2), wi;
 	h = normalize((h.x * sp.nu + h.y * sp.nv) + h.z * n);
-	const float cur_ior = m.ior;
+	const float cur_ior = YG_IOR(m, sp);
 	float glossy, glossy_d = 0.f, glossy_g = 0.f, wi_n, wi_h, jacobian;
 	const float cos_theta = dot(h, n);
 	const float cos_theta_2 = cos_theta * cos_theta;
@@ -879,7 +938,7 @@ YG_D Col leafSample2(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tco
 			jacobian = (ior_wi * ior_wi) / fmaxf(1.0e-8f, ht * ht);
 			glossy = fabsf((wo_h * wi_h) / (wi_n * wo_n)) * kt * glossy_g * glossy_d * jacobian;
 			s.pdf = glossy_d * cos_theta * (jacobian * fabsf(wi_h));
-			s.sampled = BsdfGlossy | BsdfTransmit;
+			s.sampled = ((m.disperse && sp.chromatic) ? BsdfDispersive : BsdfGlossy) | BsdfTransmit;
 			ret = glossy * ldc(m.filter_col);
 			w[0] = fabsf(wi_n) / fmaxf(0.1f, s.pdf);
 			dir[0] = wi;
@@ -950,13 +1009,18 @@ YG_D void leafSpecular(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, b
 			const bool outside = dot(sp.ng, wo) > 0;
 			const V3 n = glassNormal(sp, wo, outside);
 			V3 refdir;
-			if(refract(n, wo, refdir, m.ior))
+			const float cur_ior = YG_IOR(m, sp);
+			if(refract(n, wo, refdir, cur_ior))
 			{
 				float kr, kt;
-				fresnel(wo, n, m.ior, kr, kt);
-				col[1] = kt * ldc(m.filter_col);
-				dir[1] = refdir;
-				refr = true;
+				fresnel(wo, n, cur_ior, kr, kt);
+				if(!sp.chromatic || !m.disperse)
+				{
+					col[1] = kt * ldc(m.filter_col);
+					dir[1] = refdir;
+					refr = true;
+				}
+				else refr = false; // the refraction is sampled per wavelength by the dispersive branch of recursiveRaytrace, not specular here
 				if(outside || raylevel < 3)
 				{
 					dir[0] = reflect(wo, n);

@@ -204,6 +204,7 @@ struct SceneDev
 	const FaureTables *faure;
 	const TexDev *textures;
 	const NodeDev *nodes;
+	const float *cie_xyz; int n_cie;   // CIE 1931 colour matching functions, rows of x,y,z from 360 nm in 1 nm steps (dispersion only)
 	CameraDev cam;
 	BackgroundDev bg;
 	IntegratorDev integ;

@@ -803,6 +803,12 @@ class Interface:
         it.ao_color = capi.F3(*[np.float32(x) for x in g(ip, "AO_color", (1, 1, 1, 1))[:3]])
         it.shadow_bias_auto, it.shadow_bias = int(g(rp, "adv_auto_shadow_bias_enabled", True)), g(rp, "adv_shadow_bias_value", 0.0005)
         it.ray_min_dist_auto, it.ray_min_dist = int(g(rp, "adv_auto_min_raydist_enabled", True)), g(rp, "adv_min_raydist_value", 0.00005)
+        if any(m.type in (capi.MAT_GLASS, capi.MAT_ROUGH_GLASS) and m.u.glass.dispersion_power > 0 for m in mats):
+            # CIE 1931 colour matching functions for wl2RgbFromCie__ (spectrum.cc:276-289): data dumped from the reference by tools/make_cie_table.py
+            import os
+            cie = np.ascontiguousarray(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "cie_xyz_360_830.npy")), np.float32).reshape(-1, 3)
+            keep.append(cie)
+            d.cie_xyz, d.n_cie_rows = cie.ctypes.data_as(C.POINTER(C.c_float)), len(cie)
         return d, keep
 
 

@@ -77,7 +77,7 @@ def _vol_none(y):
 
 def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, raydepth=8, rr_min_bounces=2,
                 light_samples=4, integrator="pathtracing", glass=True, light_power=30.0, filter_type="box",
-                aa_passes=1, extra_point_light=False, transp_shad=False, no_recursive=False, lens=None, **render_extra):
+                aa_passes=1, extra_point_light=False, transp_shad=False, no_recursive=False, lens=None, dispersion=0.0, rough_glass=False, **render_extra):
     """BASELINE config 2: Cornell box, PathIntegrator, area light, ShinyDiffuse + Glass (36 triangles)."""
     y = Interface()
     y.startScene(0)
@@ -86,8 +86,12 @@ def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, ray
     green = _shiny(y, "green", (0.14, 0.45, 0.09))
     y.paramsClearAll()
     if glass:
-        y.paramsSetString("type", "glass"); y.paramsSetFloat("IOR", 1.5)
+        y.paramsSetString("type", "rough_glass" if rough_glass else "glass"); y.paramsSetFloat("IOR", 1.5)
         y.paramsSetColor("filter_color", 1.0, 1.0, 1.0); y.paramsSetColor("mirror_color", 1.0, 1.0, 1.0)
+        if rough_glass:
+            y.paramsSetFloat("alpha", 0.3)
+        if dispersion > 0:
+            y.paramsSetFloat("dispersion_power", dispersion)
         gl = y.createMaterial("glassmat")
     else:
         gl = _shiny(y, "glassmat", (0.3, 0.3, 0.7))

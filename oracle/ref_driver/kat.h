@@ -76,6 +76,23 @@ static int cmdKat(int argc, char **argv)
 		for(uint32_t s : seeds) { Random r(s); for(int i = 0; i < 64; ++i) v.push_back(r()); }
 		w.f64("random", v);
 	}
+	{	// CIE 1931 colour matching functions as the reference tabulates them (spectrum.cc): wl2Xyz__ at the integer wavelengths 360..829 nm
+		// returns the table rows themselves (fr = 0); row 470 (830 nm) is recovered from the midpoint 829.5 nm.  Also a few wl2Rgb__ / getIor__ /
+		// cauchyCoefficients__ known answers for the dispersion code.
+		std::vector<float> t(471 * 3, 0.f);
+		for(int i = 0; i < 470; ++i) { const Rgb c = wl2Xyz__(360.f + (float)i); t[3 * i] = c.r_; t[3 * i + 1] = c.g_; t[3 * i + 2] = c.b_; }
+		{ const Rgb c = wl2Xyz__(829.5f); for(int k = 0; k < 3; ++k) t[3 * 470 + k] = 2.f * (k == 0 ? c.r_ : k == 1 ? c.g_ : c.b_) - t[3 * 469 + k]; }
+		w.f32("cie_xyz", t);
+		std::vector<float> v;
+		for(int i = 0; i < 64; ++i)
+		{
+			const float wl = (float)i / 64.f + 0.0078125f;
+			Rgb c; wl2Rgb__(wl, c);
+			float ca, cb; cauchyCoefficients__(1.3f + 0.01f * (float)i, 5.f + (float)i, ca, cb);
+			v.push_back(c.r_); v.push_back(c.g_); v.push_back(c.b_); v.push_back(ca); v.push_back(cb); v.push_back(getIor__(wl, ca, cb));
+		}
+		w.f32("dispersion_kat", v);
+	}
 	{	// fast math (util_math_optimizations.h:116-270)
 		std::vector<float> fsin(n), fcos(n), fexp(n), flog(n), fpow(n), fexp2(n), flog2(n), facos(n), fasin(n), fsqrt(n);
 		uint32_t s = 12345u;

@@ -57,6 +57,7 @@
 #include "common/triangle.h"
 #include "common/kdtree_triangle.h"
 #include "common/scr_halton.h"
+#include "common/spectrum.h"
 #include "object_geom/object_geom_mesh.h"
 #include "material/material.h"
 #include "light/light.h"

@@ -25,6 +25,13 @@ EXACT = {
     "cornell_dl_lanczos_wide": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", filter_type="lanczos", pixelwidth=3.0),
     "cornell_dl_clamp": lambda: scenes.cornell_box(96, 54, 4, integrator="directlighting", AA_clamp_samples=0.7, AA_clamp_indirect=0.3),
     "cornell_pt_clamp_norr": lambda: scenes.cornell_box(96, 54, 4, path_samples=2, bounces=3, raydepth=3, rr_min_bounces=8, AA_clamp_samples=0.5, AA_clamp_indirect=0.2),
+    # glass / rough-glass dispersion: the dispersive branch of recursiveRaytrace (integrator_montecarlo.cc:796-858), Cauchy IOR per wavelength
+    # (material_glass.cc:64-216,242-309, material_rough_glass.cc:61-172), wl2Rgb__ through the CIE table
+    "cornell_dl_dispersion": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", dispersion=20.0, raydepth=4),
+    "cornell_pt_dispersion_norr": lambda: scenes.cornell_box(96, 54, 2, path_samples=2, bounces=3, raydepth=3, rr_min_bounces=8, dispersion=20.0),
+    # rough glass is glossy AND dispersive: its glossy-branch samples read RenderState::wavelength_, which the previous sibling's subtree
+    # overwrites in the reference (a leftover of its depth-first order, like include_lights_); exact only while the children cannot recurse
+    "cornell_dl_rough_dispersion": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", dispersion=30.0, rough_glass=True, raydepth=1),
     "simple_dl_bgtransp": lambda: scenes.simple_point_scene(160, 90, 2, filter_type="box", bg_transp=True),
     "simple_pt_bgtransp": lambda: scenes.simple_point_scene(160, 90, 4, integrator="pathtracing", filter_type="box", bg_transp=True),
 }
