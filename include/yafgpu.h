@@ -532,12 +532,14 @@ typedef struct yafgpu_stats
 	uint64_t rays_in_timed_trace, rays_in_timed_shadow;
 	/* queue lengths of the most recent wave, per wavefront iteration (first 16): tasks traced+shaded, shadow rays traced */
 	uint32_t last_wave_tasks[16], last_wave_shadow[16];
-	/* accelerator shape: bytes per node (64: 4-wide, 96: 8-wide), children per node, levels of the wide tree */
+	/* accelerator shape: bytes per node (128: 4-wide fp32 boxes), children per node, levels of the wide tree */
 	uint32_t bvh_node_bytes, bvh_width, bvh_levels, reserved0;
 	/* COUNT_TRAVERSAL: nodes_visited / tris_tested above cover closest-hit rays, these the shadow (any-hit) rays */
 	uint64_t nodes_visited_shadow, tris_tested_shadow;
 	/* yafgpu_group_get_stats only: film reductions queued so far and the duration of the most recent one that was read back */
 	uint64_t film_reduces; double ms_film_reduce;
+	/* camera samples whose radiance came back NaN/Inf and were left out of the film (see option "keep_nonfinite_samples") */
+	uint64_t nonfinite_samples;
 } yafgpu_stats;
 
 enum { YAFGPU_FLAG_COUNT_TRAVERSAL = 1, YAFGPU_FLAG_TIME_STAGES = 2,
@@ -593,7 +595,9 @@ int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_
 /* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^23, limited to a quarter of the free device memory),
  * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "leaf_size" (triangles per leaf link of the BVH built by
  * the NEXT upload, 1..8), "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3),
- * "debug_stack_limit" (traversal stack entries in use, only to exercise the overflow error path). */
+ * "debug_stack_limit" (traversal stack entries in use, only to exercise the overflow error path),
+ * "keep_nonfinite_samples" (0, default: a camera sample whose radiance is NaN/Inf is left out of the film and counted in yafgpu_stats.nonfinite_samples;
+ * 1: it is splatted as the reference's ImageFilm::addSample does, imagefilm.cc, and the pixels its filter footprint covers stay NaN). */
 int yafgpu_set_option(yafgpu_ctx *ctx, const char *name, long long value);
 int yafgpu_get_stats(yafgpu_ctx *ctx, yafgpu_stats *out);
 int yafgpu_reset_stats(yafgpu_ctx *ctx);

@@ -177,7 +177,7 @@ class Stats(C.Structure):
                 ("launches_trace", u64), ("launches_shadow", u64), ("launches_shade", u64), ("rays_in_timed_trace", u64),
                 ("rays_in_timed_shadow", u64), ("last_wave_tasks", C.c_uint32 * 16), ("last_wave_shadow", C.c_uint32 * 16),
                 ("bvh_node_bytes", C.c_uint32), ("bvh_width", C.c_uint32), ("bvh_levels", C.c_uint32), ("reserved0", C.c_uint32),
-                ("nodes_visited_shadow", u64), ("tris_tested_shadow", u64), ("film_reduces", u64), ("ms_film_reduce", C.c_double)]
+                ("nodes_visited_shadow", u64), ("tris_tested_shadow", u64), ("film_reduces", u64), ("ms_film_reduce", C.c_double), ("nonfinite_samples", u64)]
 
 
 # every entry point include/yafgpu.h declares: name -> (restype, argtypes)

@@ -715,6 +715,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	if(n == "ray_regeneration") { if(value < -1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "ray_regeneration: -1..3"); c->ray_regeneration = (int)value; return YAFGPU_OK; }
 	if(n == "regen_threshold") { if(value < 1 || value > 32) return setErr(c, YAFGPU_ERR_INVALID, "regen_threshold: 1..32"); c->regen_threshold = (int)value; return YAFGPU_OK; }
 	if(n == "debug_stack_limit") { if(value < 0 || value > YG_STACK) return setErr(c, YAFGPU_ERR_INVALID, "debug_stack_limit: 0..96"); c->stack_limit = (int)value; return YAFGPU_OK; }
+	if(n == "keep_nonfinite_samples") { c->keep_nonfinite = value != 0; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);
 }
@@ -730,7 +731,7 @@ int yafgpu_get_stats(yafgpu_ctx *c, yafgpu_stats *out)
 	out->rays_camera += h[CNT_RAYS_CAMERA]; out->rays_extension += h[CNT_RAYS_EXTENSION]; out->rays_shadow += h[CNT_RAYS_SHADOW];
 	out->rays_shadow_transp += h[CNT_RAYS_SHADOW_TRANSP]; out->rays_light_probe += h[CNT_RAYS_LIGHT_PROBE];
 	out->camera_samples += h[CNT_CAMERA_SAMPLES]; out->nodes_visited = h[CNT_NODES]; out->tris_tested = h[CNT_TRIS];
-	out->nodes_visited_shadow = h[CNT_NODES_SHADOW]; out->tris_tested_shadow = h[CNT_TRIS_SHADOW];
+	out->nodes_visited_shadow = h[CNT_NODES_SHADOW]; out->tris_tested_shadow = h[CNT_TRIS_SHADOW]; out->nonfinite_samples = h[CNT_NONFINITE];
 	return YAFGPU_OK;
 }
 

@@ -281,7 +281,7 @@ int yafgpu_group_get_stats(yafgpu_group *g, yafgpu_stats *out)
 			out->rays_camera += s.rays_camera; out->rays_extension += s.rays_extension; out->rays_shadow += s.rays_shadow; out->rays_shadow_transp += s.rays_shadow_transp;
 			out->rays_light_probe += s.rays_light_probe; out->camera_samples += s.camera_samples; out->kernel_launches += s.kernel_launches;
 			out->nodes_visited += s.nodes_visited; out->tris_tested += s.tris_tested; out->nodes_visited_shadow += s.nodes_visited_shadow; out->tris_tested_shadow += s.tris_tested_shadow;
-			out->waves += s.waves; out->wave_retries += s.wave_retries;
+			out->waves += s.waves; out->wave_retries += s.wave_retries; out->nonfinite_samples += s.nonfinite_samples;
 			out->ms_total = s.ms_total > out->ms_total ? s.ms_total : out->ms_total; out->ms_build = s.ms_build > out->ms_build ? s.ms_build : out->ms_build;
 		}
 	}

@@ -82,8 +82,15 @@ __device__ __forceinline__ unsigned hash3(unsigned a, unsigned b, unsigned c)
 }
 __device__ __forceinline__ float hashRand(unsigned a, unsigned b, unsigned c) { return (float)((double)hash3(a, b, c) * YG_MULT_RATIO); } // Random::operator() is x * 2^-32
 
+#ifdef YG_NAN_TRAP   // diagnosis build (tools/nan_probe.py): name the source line of a non-finite contribution
+#define accAdd(a, s, c) accAddAt(a, s, c, __LINE__)
+__device__ __forceinline__ void accAddAt(float4 *acc, int slot, Col c, int line)
+{
+	if(!(isfinite(c.r) && isfinite(c.g) && isfinite(c.b))) printf("non-finite contribution at integrator.cu:%d slot %d (%g %g %g)\n", line, slot, c.r, c.g, c.b);
+#else
 __device__ __forceinline__ void accAdd(float4 *acc, int slot, Col c)
 {
+#endif
 	float *p = (float *)(acc + slot);
 	if(c.r != 0.f) atomicAdd(p, c.r);
 	if(c.g != 0.f) atomicAdd(p + 1, c.g);
@@ -436,8 +443,16 @@ __device__ __forceinline__ void pushShadow(const ShadeCtx &cx, int slot, V3 from
 
 // `beer`: 1 + index of the absorbing material whose Beer transmittance over the traced segment multiplies everything the child task returns
 // (recursiveRaytrace: `integ *= vcol` after integrate(), integrator_montecarlo.cc:841-845,912-915,991-994,1019-1022); 0 = none
+#ifdef YG_NAN_TRAP
+#define pushTask(cx, slot, from, tmin, dir, wgt, ...) pushTaskAt(__LINE__, cx, slot, from, tmin, dir, wgt, __VA_ARGS__)
+__device__ __forceinline__ void pushTaskAt(int line, const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2, int beer = 0)
+{
+	if(!(isfinite(wgt.r) && isfinite(wgt.g) && isfinite(wgt.b) && isfinite(thr.r) && isfinite(thr.g) && isfinite(thr.b) && isfinite(dir.x + dir.y + dir.z) && isfinite(from.x + from.y + from.z)))
+		printf("non-finite task pushed at integrator.cu:%d slot %d wgt (%g %g %g) thr (%g %g %g) dir (%g %g %g) from (%g %g %g) packed %08x\n", line, slot, wgt.r, wgt.g, wgt.b, thr.r, thr.g, thr.b, dir.x, dir.y, dir.z, from.x, from.y, from.z, packed);
+#else
 __device__ __forceinline__ void pushTask(const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2, int beer = 0)
 {
+#endif
 	const int k = allocSlot(&cx.ctl->n_tasks[cx.iter + 1]);
 	if(k >= cx.wp.task_cap) { cx.ctl->overflow = 1; return; }
 	cx.out.ray_o[k] = make_float4(from.x, from.y, from.z, tmin);
@@ -943,7 +958,8 @@ __global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ SceneDev
 // ---- K9: ImageFilm::addSample imagefilm.cc:925-1015 (Combined pass) --------------------------------------------------------
 __device__ __forceinline__ int round2Int(double v) { return (int)(v + (.5 - 1.4e-11)); } // util_math.h:34-43 (FAST_INT off)
 
-__global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, const uint32_t *__restrict__ pixels, const float4 *__restrict__ acc, const WaveCtl *__restrict__ ctl)
+__global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, const uint32_t *__restrict__ pixels, const float4 *__restrict__ acc, const WaveCtl *__restrict__ ctl,
+                                                  int keep_nonfinite, unsigned long long *__restrict__ counters)
 {
 	if(ctl->overflow) return; // the wave is discarded and re-rendered in smaller pieces
 	for(int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < wp.n_slots; slot += gridDim.x * blockDim.x)
@@ -952,6 +968,10 @@ __global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, c
 		float dx, dy;
 		samplePos(wp, si, dx, dy);
 		const float4 a = acc[slot];
+		// A path can return NaN/Inf where the reference's own arithmetic does (e.g. RoughGlassMaterial::sample, material_rough_glass.cc:225: |wo_h wi_h / (wi_n wo_n)| * G
+		// with wo_n == 0 and G == 0 is inf * 0; about one camera sample in 10^9 of the bench scene).  The reference splats it and the pixel stays NaN for good; here the
+		// sample is left out (colour AND weight) and counted in yafgpu_stats.nonfinite_samples, unless option "keep_nonfinite_samples" asks for the reference's behaviour.
+		if(!keep_nonfinite && !(isfinite(a.x) && isfinite(a.y) && isfinite(a.z))) { atomicAdd(&counters[CNT_NONFINITE], 1ull); continue; }
 		Col col = clampProportional(mkc(a.x, a.y, a.z), film.clamp_samples);
 		const float alpha = (film.transp_bg && a.w != 0.f) ? 0.f : 1.f;
 		const int x = si.x, y = si.y;
@@ -1127,7 +1147,7 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		mark();
 		c->stats.kernel_launches += 4 + n_launch;
 	}
-	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl);
+	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl, c->keep_nonfinite, c->d_counters);
 	c->stats.kernel_launches += 2;
 	YG_CUDA(c, cudaGetLastError());
 	YG_CUDA(c, cudaMemcpyAsync(w.h_ctl, w.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));

@@ -942,6 +942,10 @@ YG_D Col leafSample2(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &tco
 			ret = glossy * ldc(m.filter_col);
 			w[0] = fabsf(wi_n) / fmaxf(0.1f, s.pdf);
 			dir[0] = wi;
+#ifdef YG_NAN_TRAP
+			if(!isfinite(glossy) || !isfinite(w[0])) printf("rough glass transmit lobe: glossy %g w %g pdf %g | wo_h %g wi_h %g wi_n %g wo_n %g kt %g G %g D %g jac %g ht %g cos_theta %g tan2 %g s1 %g s2 %g h (%g %g %g) n (%g %g %g) nu (%g %g %g) nv (%g %g %g)\n",
+				glossy, w[0], s.pdf, wo_h, wi_h, wi_n, wo_n, kt, glossy_g, glossy_d, jacobian, ht, cos_theta, tan_theta_2, s.s1, s.s2, h.x, h.y, h.z, n.x, n.y, n.z, sp.nu.x, sp.nu.y, sp.nu.z, sp.nv.x, sp.nv.y, sp.nv.z);
+#endif
 		}
 		if(s.flags & BsdfReflect)
 		{

@@ -43,7 +43,7 @@ struct ShadowQueue
 };
 
 enum { CNT_RAYS_CAMERA = 0, CNT_RAYS_EXTENSION, CNT_RAYS_SHADOW, CNT_RAYS_SHADOW_TRANSP, CNT_RAYS_LIGHT_PROBE,
-       CNT_CAMERA_SAMPLES, CNT_NODES, CNT_TRIS, CNT_NODES_SHADOW, CNT_TRIS_SHADOW, CNT_N };
+       CNT_CAMERA_SAMPLES, CNT_NODES, CNT_TRIS, CNT_NODES_SHADOW, CNT_TRIS_SHADOW, CNT_NONFINITE, CNT_N };
 
 #define YG_MAX_ITERS 96
 #define YG_N_MAT_TYPES 11  /* yafgpu_material_type values 0..8 + YG_MAT_SD_LAMBERT + YG_MAT_NODES */

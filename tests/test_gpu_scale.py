@@ -137,3 +137,38 @@ def test_traversal_stack_overflow_is_an_error_not_a_wrong_image():
         assert (c.trace(rays, 0)["tri"] >= 0).any()
     finally:
         c.close()
+
+
+def test_non_finite_camera_sample_is_dropped_and_counted():
+    """RoughGlassMaterial::sample (material_rough_glass.cc:218-229) evaluates |wo_h wi_h / (wi_n wo_n)| * kt * G * D * J; with wo_n == 0 and
+    G == 0 that is inf * 0.  In the bench scene (BASELINE configs[2]) pixel (836, 415), pass offset 640, sample 12 is such a path
+    (found by tools/nan_probe.py; about 3 camera samples in 2 * 10^9).  The reference has no guard on this path and would splat NaN
+    into the film for good; the library leaves the sample out and counts it, unless "keep_nonfinite_samples" asks for the NaN."""
+    import bench
+    from libyafaray_b200 import Context
+
+    class A:
+        tris, width, height = bench.N_TRIS, bench.WIDTH, bench.HEIGHT
+    px, py, off, smp = 836, 415, 640, 12
+    desc, keep = bench.build_scene(A, 128).scene_desc()
+    mask = np.zeros((A.height, A.width), np.uint8); mask[py, px] = 1
+    c = Context(0)
+    try:
+        c.upload(desc, keep)
+        films = {}
+        for keep_nan in (1, 0):
+            c.set_option("keep_nonfinite_samples", keep_nan)
+            c.film_clear(); c.reset_stats()
+            c.render_pass(128, off, adaptive=True, mask=mask, sample_begin=smp, sample_end=smp + 1)
+            films[keep_nan] = (c.read_film(), c.stats()["nonfinite_samples"])
+        f, n = films[1]
+        assert np.isnan(f[py, px, :3]).all() and f[py, px, 4] == 1.0 and n == 0
+        f, n = films[0]
+        assert np.isfinite(f).all() and not f.any() and n == 1
+        # a neighbouring sample of the same pixel is untouched by the guard
+        c.film_clear(); c.reset_stats()
+        c.render_pass(128, off, adaptive=True, mask=mask, sample_begin=smp + 1, sample_end=smp + 2)
+        f = c.read_film()
+        assert np.isfinite(f).all() and f[py, px, 4] == 1.0 and f[py, px, :3].sum() > 0 and c.stats()["nonfinite_samples"] == 0
+    finally:
+        c.close()

@@ -6,6 +6,8 @@ import os
 import sys
 import time
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
@@ -23,7 +25,9 @@ def main():
     S = bench.FRAME_SPP * n
     y = bench.build_scene(A, S)
     desc, keep = y.scene_desc()
-    g = Group(list(range(n)))
+    share = "share" in sys.argv   # n members on GPU 0 (the partition + film-sum path on a one-GPU box)
+    from libyafaray_b200 import capi
+    g = Group([0] * n, capi.FLAG_SHARE_DEVICE) if share else Group(list(range(n)))
     t0 = time.perf_counter(); g.upload(desc, keep); t_up = time.perf_counter() - t0
     g.film_clear()
     for i in range(warmup):
@@ -38,8 +42,19 @@ def main():
     rays = bench.total_rays(st)
     print(json.dumps({"path": "yafgpu_group (in-process)", "n_gpus": n, "steps": steps, "warmup": warmup, "ms_per_step": t / steps * 1e3, "value_mrays_s": rays / t / 1e6,
                       "samples_per_s": st["camera_samples"] / t, "upload_s": t_up, "film_reduces": st["film_reduces"], "ms_last_film_reduce": st["ms_film_reduce"],
-                      "timing": "host wall clock around `steps` group passes + the final film read-back", "finite": bool((film == film).all()),
+                      "timing": "host wall clock around `steps` group passes + the final film read-back", "finite": bool(np.isfinite(film).all()), "non_finite_pixels": int((~np.isfinite(film).all(axis=2)).sum()), "first_bad": np.argwhere(~np.isfinite(film).all(axis=2))[:4].tolist(),
                       "workload": bench.config_dict(A, n, bench.FRAME_SPP)["workload"]}))
+    if "members" in sys.argv:   # diagnosis: each member's own film next to the sum
+        g.sync()
+        tot = np.zeros_like(film, np.float64)
+        for k in range(g.size()):
+            m = np.empty_like(film)
+            assert capi.lib.yafgpu_read_film(capi.lib.yafgpu_group_ctx(g.h, k), m.ctypes.data) == 0
+            bad = ~np.isfinite(m).all(axis=2)
+            print(f"member {k}: non-finite pixels {int(bad.sum())} first {np.argwhere(bad)[:3].tolist()} weight sum {float(m[..., 4][~bad].sum()):.1f}", file=sys.stderr)
+            tot += np.nan_to_num(m.astype(np.float64), nan=0.0, posinf=0.0, neginf=0.0)
+        ok = np.isfinite(film).all(axis=2)
+        print("sum of member films vs reduced film (finite pixels): max |d| =", float(np.abs(tot[ok] - film[ok]).max()), file=sys.stderr)
     g.close()
 
 
