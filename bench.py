@@ -269,6 +269,8 @@ def gpu_arm(args, rank, world, local_rank):
 
     # ---- end-to-end through the public call with host buffers (every step: upload + BVH build, clear, render, film D2H) ----
     host_film = torch.empty((args.height, args.width, 5), dtype=torch.float32, pin_memory=True)  # pinned: the D2H of the film runs at PCIe speed
+    from libyafaray_b200 import pin_host_arrays
+    pinned = pin_host_arrays(keep) if not args.pageable else []   # once, outside the timed region: the step's inputs come from pinned host memory
     g = desc.geometry
     h2d = (g.n_points * 12 + g.n_normals * 12 + g.n_uv * 8 + g.n_tris * (12 * (1 + (1 if g.n_normals else 0) + (1 if g.n_uv else 0)) + 8)
            + desc.n_materials * C_sizeof(capi.Material) + desc.n_lights * C_sizeof(capi.Light))
@@ -313,6 +315,7 @@ def gpu_arm(args, rank, world, local_rank):
     line["e2e"] = {"value": r2 / t_e2e / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(host_film.numel() * 4),
                    "ms_per_step": t_e2e / e2e_steps * 1e3, "steps": e2e_steps, "phases_ms_per_step_rank0": {k: v / e2e_steps for k, v in phases.items()},
                    "bvh_build_ms": (st2["ms_build"] - build0) / max(1, e2e_steps),
+                   "host_buffers": "pageable" if args.pageable else "pinned once before the timed steps (yafgpu_host_register, %d arrays)" % len(pinned),
                    "timing": "host wall clock around yafgpu_upload_scene (H2D + BVH build) + film clear + render of the frame + film read-back, every step, max over ranks"}
 
     if rank == 0:
@@ -403,6 +406,8 @@ def gpu_arm(args, rank, world, local_rank):
         print(json.dumps(line))
     if ctx is not None:
         ctx.close()
+    from libyafaray_b200 import unpin_host_arrays
+    unpin_host_arrays(pinned)
     if world > 1:
         dist.destroy_process_group()
 
@@ -425,6 +430,7 @@ def main():
     ap.add_argument("--tris", type=int, default=N_TRIS)
     ap.add_argument("--ref-crop", action="store_true", help="CPU sample = centred half-size window instead of the full frame")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--pageable", action="store_true", help="e2e leg: leave the scene arrays pageable (A/B against the default, yafgpu_host_register once before the timed steps)")
     ap.add_argument("--option", action="append", default=[], metavar="NAME=INT", help="yafgpu_set_option knob for A/B runs (e.g. shade_streams=1)")
     ap.add_argument("--wave-size", type=int, default=0, help="camera samples per wavefront wave (0 = library default)")
     args = ap.parse_args()

@@ -11,7 +11,7 @@ from . import capi  # noqa: F401
 if _os.environ.get("LIBYAFARAY_B200_HOST_ONLY") != "1":
     capi.lib.load()  # dlopens libyafgpu.so, raises ImportError when it is not built (host-only processes defer this to the first device call)
 from .interface import Interface  # noqa: F401
-from .render import Context, Group, render_scene, load_film, film_to_image  # noqa: F401
+from .render import Context, Group, render_scene, pin_host_arrays, unpin_host_arrays, load_film, film_to_image  # noqa: F401
 from . import film_io  # noqa: F401
 
-__all__ = ["capi", "Interface", "Context", "Group", "render_scene", "load_film", "film_to_image", "film_io"]
+__all__ = ["capi", "Interface", "Context", "Group", "render_scene", "pin_host_arrays", "unpin_host_arrays", "load_film", "film_to_image", "film_io"]

@@ -194,6 +194,8 @@ SYMBOLS = {
     "yafgpu_film_clear": (C.c_int, [C.c_void_p]),
     "yafgpu_render_pass": (C.c_int, [C.c_void_p, C.POINTER(PassDesc)]),
     "yafgpu_sync": (C.c_int, [C.c_void_p]),
+    "yafgpu_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
+    "yafgpu_host_unregister": (C.c_int, [C.c_void_p]),
     "yafgpu_read_film": (C.c_int, [C.c_void_p, C.c_void_p]),
     "yafgpu_film_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "yafgpu_write_film": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -343,8 +343,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	const yafgpu_integrator_desc &in = desc->integrator;
 	if(in.type != YAFGPU_INT_DIRECTLIGHT && in.type != YAFGPU_INT_PATHTRACING) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "integrator type");
 	// bg_transp: the alpha of a camera sample is 0 when its primary ray leaves the scene, 1 otherwise (integrator_path_tracer.cc:122-123,324;
-	// integrator_direct_light.cc likewise).  bg_transp_refract needs Material::getAlpha along the refraction chain and stays refused.
-	if(in.bg_transp_refract) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bg_transp_refract (alpha through refractions) not implemented on the device");
+	// integrator_direct_light.cc likewise).  bg_transp_refract folds Material::getAlpha along the refraction chain (YG_ST_ALPHA in integrator.cu).
 	// the packed task state holds the path depth in 6 bits (integrator.cu packState); the recursion level never passes 19 — the reference's own
 	// `raylevel_ < 20` guards (integrator_montecarlo.cc:862,921) — so the wavefront needs at most 20 + bounces + 1 iterations
 	if(in.bounces > 63) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "bounces > 63: the wavefront task state holds the path depth in 6 bits");
@@ -353,7 +352,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	s.integ.type = in.type; s.integ.r_depth = in.raydepth; s.integ.tr_shad = in.transp_shad; s.integ.s_depth = in.shadow_depth;
 	s.integ.n_paths = in.path_samples; s.integ.max_bounces = in.bounces; s.integ.rr_min_bounces = in.rr_min_bounces;
 	s.integ.no_recursive = in.no_recursive; s.integ.trace_caustics = in.trace_caustics;
-	s.integ.transp_bg = in.bg_transp ? 1 : 0; s.integ.transp_refr_bg = 0;
+	s.integ.transp_bg = in.bg_transp ? 1 : 0; s.integ.transp_refr_bg = in.bg_transp_refract ? 1 : 0;
 	s.integ.do_ao = in.do_ao; s.integ.ao_samples = in.ao_samples; s.integ.ao_dist = in.ao_distance;
 	for(int k = 0; k < 3; ++k) s.integ.ao_col[k] = in.ao_color[k];
 	if(in.do_ao && in.ao_samples < 1) return setErr(c, YAFGPU_ERR_INVALID, "AO_samples must be positive");
@@ -661,6 +660,21 @@ int yafgpu_render_pass(yafgpu_ctx *c, const yafgpu_pass_desc *pass)
 	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
 	YG_CUDA(c, cudaSetDevice(c->device));
 	return renderPass(c, pass);
+}
+
+int yafgpu_host_register(void *ptr, size_t bytes)
+{
+	if(!ptr || !bytes) return setErr(nullptr, YAFGPU_ERR_INVALID, "yafgpu_host_register: NULL / empty buffer");
+	const cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+	if(e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return YAFGPU_OK; }
+	return e == cudaSuccess ? YAFGPU_OK : cudaErr(nullptr, e, "cudaHostRegister");
+}
+int yafgpu_host_unregister(void *ptr)
+{
+	if(!ptr) return setErr(nullptr, YAFGPU_ERR_INVALID, "yafgpu_host_unregister: NULL");
+	const cudaError_t e = cudaHostUnregister(ptr);
+	if(e != cudaSuccess) cudaGetLastError();   // not sticky: the next launch must not inherit it
+	return e == cudaSuccess ? YAFGPU_OK : cudaErr(nullptr, e, "cudaHostUnregister");
 }
 
 int yafgpu_sync(yafgpu_ctx *c)

@@ -58,6 +58,12 @@ __device__ __forceinline__ int stAddDepth(unsigned p) { return (p >> 23) & 31; }
 // bit 21: this integrate() was called by the dispersive branch, which sets RenderState::include_lights_ = false for its children
 // (integrator_montecarlo.cc:799 "debatable..."); the glossy / specular branches set it back to true for theirs (:864,977)
 #define YG_ST_NOLIGHTS (1u << 21)
+// bit 28 ("bg_transp_refract"): this integrate() decides the alpha of its camera sample.  integrate() returns alpha = m + (1 - m) * alpha_child with
+// m = Material::getAlpha and alpha_child = what the LAST refracted child returned (integrator_path_tracer.cc:319-323, integrator_montecarlo.cc:954,1023);
+// unrolled from the camera this is alpha = A + B * alpha_here, and the task carries (A, B) in thr.xy, which a TASK_INTEGRATE does not use otherwise.
+#define YG_ST_ALPHA (1u << 28)
+// acc[slot].w holds the alpha of the camera sample as float bits XOR 1.0f's, so that the zero the wave starts from reads as alpha = 1
+__device__ __forceinline__ float alphaEncode(float alpha) { return __int_as_float(__float_as_int(alpha) ^ 0x3f800000); }
 
 // warp-aggregated queue slot allocation
 __device__ __forceinline__ int allocSlot(int *counter)
@@ -253,8 +259,9 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev sc, WaveParams wp, cons
 		q.ray_o[slot] = make_float4(from.x, from.y, from.z, tmin);
 		q.ray_d[slot] = make_float4(dir.x, dir.y, dir.z, tmax);
 		q.wgt[slot] = make_float4(w0, w0, w0, 0.f);
-		q.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-		q.st[slot] = make_uint4((unsigned)slot, 0u, packState(TASK_INTEGRATE, 0, 0, 1, 0, 0), 0u);
+		const bool alpha_chain = sc.integ.transp_refr_bg != 0;
+		q.thr[slot] = alpha_chain ? make_float4(0.f, 1.f, 1.f, 0.f) : make_float4(1.f, 1.f, 1.f, 0.f);
+		q.st[slot] = make_uint4((unsigned)slot, 0u, packState(TASK_INTEGRATE, 0, 0, 1, 0, 0) | (alpha_chain ? YG_ST_ALPHA : 0u), 0u);
 		q.dc[slot] = make_float2(0.f, 0.f);
 	}
 }
@@ -445,22 +452,23 @@ __device__ __forceinline__ void pushShadow(const ShadeCtx &cx, int slot, V3 from
 // (recursiveRaytrace: `integ *= vcol` after integrate(), integrator_montecarlo.cc:841-845,912-915,991-994,1019-1022); 0 = none
 #ifdef YG_NAN_TRAP
 #define pushTask(cx, slot, from, tmin, dir, wgt, ...) pushTaskAt(__LINE__, cx, slot, from, tmin, dir, wgt, __VA_ARGS__)
-__device__ __forceinline__ void pushTaskAt(int line, const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2, int beer = 0)
+__device__ __forceinline__ int pushTaskAt(int line, const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2, int beer = 0)
 {
 	if(!(isfinite(wgt.r) && isfinite(wgt.g) && isfinite(wgt.b) && isfinite(thr.r) && isfinite(thr.g) && isfinite(thr.b) && isfinite(dir.x + dir.y + dir.z) && isfinite(from.x + from.y + from.z)))
 		printf("non-finite task pushed at integrator.cu:%d slot %d wgt (%g %g %g) thr (%g %g %g) dir (%g %g %g) from (%g %g %g) packed %08x\n", line, slot, wgt.r, wgt.g, wgt.b, thr.r, thr.g, thr.b, dir.x, dir.y, dir.z, from.x, from.y, from.z, packed);
 #else
-__device__ __forceinline__ void pushTask(const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2, int beer = 0)
+__device__ __forceinline__ int pushTask(const ShadeCtx &cx, int slot, V3 from, float tmin, V3 dir, Col wgt, Col thr, unsigned offs, unsigned packed, unsigned ray_offset, float dc1, float dc2, int beer = 0)
 {
 #endif
 	const int k = allocSlot(&cx.ctl->n_tasks[cx.iter + 1]);
-	if(k >= cx.wp.task_cap) { cx.ctl->overflow = 1; return; }
+	if(k >= cx.wp.task_cap) { cx.ctl->overflow = 1; return -1; }
 	cx.out.ray_o[k] = make_float4(from.x, from.y, from.z, tmin);
 	cx.out.ray_d[k] = make_float4(dir.x, dir.y, dir.z, -1.f);
 	cx.out.wgt[k] = make_float4(wgt.r, wgt.g, wgt.b, __int_as_float(beer));
 	cx.out.thr[k] = make_float4(thr.r, thr.g, thr.b, 0.f);
 	cx.out.st[k] = make_uint4((unsigned)slot, offs, packed, ray_offset);
 	cx.out.dc[k] = make_float2(dc1, dc2);
+	return k;
 }
 
 // Material::getVolumeHandler(sp.ng_ * ref_ray.dir_ < 0): only the inside handler (vol_i_) exists, created by the glass factories for "absorption"
@@ -620,8 +628,13 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			// ---- PathIntegrator::integrate / DirectLightIntegrator::integrate ----
 			if(MT == MT_MISS || tri < 0)
 			{
-				if(sc.bg.type != YAFGPU_BG_NONE) accAdd(acc, slot, W * bgEval(sc.bg, dir));
-				if(ig.transp_bg && stRaylevel(packed) == 0) ((float *)(acc + slot))[3] = 1.f;   // primary ray missed: alpha stays at its initial 0 (integrator_path_tracer.cc:122)
+				if(sc.bg.type != YAFGPU_BG_NONE && !ig.transp_refr_bg) accAdd(acc, slot, W * bgEval(sc.bg, dir));   // integrator_path_tracer.cc:328
+				if(packed & YG_ST_ALPHA)
+				{	// the refraction chain left the scene: this integrate() returns its initial alpha (integrator_path_tracer.cc:122-123)
+					const float4 ab = in.thr[i];
+					((float *)(acc + slot))[3] = alphaEncode(ab.x + ab.y * (ig.transp_bg ? 0.f : 1.f));
+				}
+				else if(ig.transp_bg && !ig.transp_refr_bg && stRaylevel(packed) == 0) ((float *)(acc + slot))[3] = alphaEncode(0.f);   // primary ray missed: alpha stays at its initial 0 (integrator_path_tracer.cc:122)
 				continue;
 			}
 			SurfPt sp;
@@ -641,6 +654,15 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 			const int raylevel = stRaylevel(packed);
 			const int additional_depth = max(stAddDepth(packed), m.additional_depth);
 			const float2 dcv = in.dc[i];
+			// "bg_transp_refract": alpha of the camera sample = A + B * (m + (1 - m) * alpha_child); carried on by the last refracted child, settled here when there is none
+			float alpha_a = 0.f, alpha_b = 0.f; int alpha_child = -1;
+			const bool alpha_chain = (packed & YG_ST_ALPHA) != 0;
+			if(alpha_chain)
+			{
+				const float4 ab = in.thr[i];
+				const float m_alpha = matAlpha<MT>(sc, m, sp, wo);
+				alpha_a = ab.x + ab.y * m_alpha; alpha_b = ab.y * (1.f - m_alpha);
+			}
 			if(bsdfs & BsdfEmit) accAdd(acc, slot, W * matEmit<MT>(sc, m, sp, wo, !(packed & YG_ST_NOLIGHTS)));
 			if(bsdfs & BsdfDiffuse)
 			{	// estimateAllDirectLight integrator_montecarlo.cc:47-60
@@ -771,9 +793,13 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * f, mkc(1.f), child_wl, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[0]));
 								}
 								if(s.sampled & BsdfTransmit)
-								{
+								{	// `alpha = integ.a_` (:954): the last of these samples decides, and its ray is traced even when it carries no colour
 									const Col f = (mcol[1] * w[1]) * d_1;
-									if(!isBlack(f)) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[1], W * f, mkc(1.f), child_wl, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[1]));
+									if(!isBlack(f) || alpha_chain)
+									{
+										const int k = pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[1], W * f, mkc(1.f), child_wl, child, ray_offset, dc1, dc2, beerOf(m, sp, d2[1]));
+										if(alpha_chain) alpha_child = k;
+									}
 								}
 							}
 						}
@@ -786,7 +812,7 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 					matSpecular<MT>(sc, m, sp, wo, rl, refl, refr, d2, rcol);
 					const unsigned child = packState(TASK_INTEGRATE, rl, 0, ray_division, 0, additional_depth) | mono;
 					if(refl && !isBlack(rcol[0])) pushTask(cx, slot, sp.p, ig.ray_min_dist, d2[0], W * rcol[0], mkc(1.f), child_wl, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[0]));
-					if(refr && !isBlack(rcol[1]))
+					if(refr && (!isBlack(rcol[1]) || alpha_chain))
 					{
 						V3 o = sp.p;
 						float tb = m.transp_bias_factor;
@@ -795,9 +821,19 @@ __global__ void __launch_bounds__(128, MT == YG_MAT_SD_LAMBERT ? YG_SHADE_MINB_L
 							if(m.transp_bias_mult) tb *= (float)rl;
 							o = sp.p + d2[1] * tb;
 						}
-						pushTask(cx, slot, o, ig.ray_min_dist, d2[1], W * rcol[1], mkc(1.f), child_wl, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[1]));
+						const int k = pushTask(cx, slot, o, ig.ray_min_dist, d2[1], W * rcol[1], mkc(1.f), child_wl, child, st.w, dcv.x, dcv.y, beerOf(m, sp, d2[1]));
+						if(alpha_chain) alpha_child = k;   // `alpha = integ.a_` (:1023) overrides the glossy samples'
 					}
 				}
+			}
+			if(alpha_chain)
+			{
+				if(alpha_child >= 0)
+				{
+					cx.out.st[alpha_child].z |= YG_ST_ALPHA;
+					cx.out.thr[alpha_child] = make_float4(alpha_a, alpha_b, 1.f, 0.f);
+				}
+				else ((float *)(acc + slot))[3] = alphaEncode(alpha_a + alpha_b * (ig.transp_bg ? 0.f : 1.f));
 			}
 		}
 		else
@@ -973,7 +1009,7 @@ __global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, c
 		// sample is left out (colour AND weight) and counted in yafgpu_stats.nonfinite_samples, unless option "keep_nonfinite_samples" asks for the reference's behaviour.
 		if(!keep_nonfinite && !(isfinite(a.x) && isfinite(a.y) && isfinite(a.z))) { atomicAdd(&counters[CNT_NONFINITE], 1ull); continue; }
 		Col col = clampProportional(mkc(a.x, a.y, a.z), film.clamp_samples);
-		const float alpha = (film.transp_bg && a.w != 0.f) ? 0.f : 1.f;
+		const float alpha = alphaEncode(a.w);   // decode == encode (XOR); 0 reads as 1
 		const int x = si.x, y = si.y;
 		const double fw = (double)film.filterw;
 		const int dx_0 = max(film.cx0 - x, round2Int((double)dx - fw));

@@ -1111,6 +1111,34 @@ YG_D Col leafTransparency(const MatDev &m, const SurfPt &sp, V3 wo)
 	return mkc(0.f);
 }
 
+// Material::getAlpha (material.h:163 = 1; the wireframe term is refused at upload): what "bg_transp_refract" folds along the refraction chain
+template<int MT>
+YG_D float leafAlpha(const MatDev &m, const SurfPt &sp, V3 wo)
+{
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_SHINYDIFFUSE)
+	{	// material_shiny_diffuse.cc:569-597
+		if(YG_SDL(MT) || !m.is_transparent) return 1.f;
+		const V3 n = faceForward(sp.ng, sp.n, wo);
+		float comp[4]; sdComponents<MT>(m, comp);
+		const float kr = sdFresnel<MT>(m, wo, n);
+		const float refl = (1.f - comp[0] * kr) * comp[1];
+		return 1.f - refl;
+	}
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_GLASS)
+	{	// material_glass.cc:231-240: `1.0 - energy` is a double subtraction
+		const Col t = leafTransparency<MT>(m, sp, wo);
+		float alpha = (float)(1.0 - (double)((t.r + t.g + t.b) * 0.333333f));
+		if(alpha < 0.0f) alpha = 0.0f;
+		return alpha;
+	}
+	if(mtypeOf<MT>(m) == YAFGPU_MAT_ROUGH_GLASS)
+	{	// material_rough_glass.cc:306-315
+		const Col t = leafTransparency<MT>(m, sp, wo);
+		return fmaxf(0.f, fminf(1.f, 1.f - (t.r + t.g + t.b) * 0.333333f));
+	}
+	return 1.f;
+}
+
 // BlendMaterial::initBsdf replaces the surface point by blendSurfacePoints__(sp, sp, ival) (material_blend.cc:77-104,
 // surface.cc:137-151): lerp__(a, a, alpha) = a * alpha + a * (1 - alpha) in float, which is not exactly `a`.
 YG_D V3 blendLerp(V3 a, float al, float ial) { return a * al + a * ial; }
@@ -1133,6 +1161,7 @@ YG_DN Col leafSample2G(const MatDev &m, const SurfPt &sp, V3 wo, V3 *dir, Col &t
 YG_DN void leafSpecularG(const MatDev &m, const SurfPt &sp, V3 wo, int raylevel, bool &refl, bool &refr, V3 *dir, Col *col) { leafSpecular<-1>(m, sp, wo, raylevel, refl, refr, dir, col); }
 YG_DN Col leafEmitG(const MatDev &m, const SurfPt &sp, V3 wo, bool include_lights) { return leafEmit<-1>(m, sp, wo, include_lights); }
 YG_DN Col leafTransparencyG(const MatDev &m, const SurfPt &sp, V3 wo) { return leafTransparency<-1>(m, sp, wo); }
+YG_DN float leafAlphaG(const MatDev &m, const SurfPt &sp, V3 wo) { return leafAlpha<-1>(m, sp, wo); }
 
 #define YG_NOT_BLEND(MT, m) ((MT) >= 0 ? (MT) != YAFGPU_MAT_BLEND : (m).type != YAFGPU_MAT_BLEND)
 
@@ -1217,6 +1246,15 @@ YG_D Col matEmit(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo, b
 	if(YG_NOT_BLEND(MT, m)) return leafEmit<MT>(m, sp, wo, include_lights);
 	const float val = m.blend_val, ival = fminf(1.f, fmaxf(0.f, 1.f - val));
 	return leafEmitG(sc.materials[m.mat1], sp, wo, include_lights) * ival + leafEmitG(sc.materials[m.mat2], sp, wo, include_lights) * val;
+}
+// BlendMaterial::getAlpha material_blend.cc:363-395 (the smaller of the two children's, only when one of them isTransparent()); a mask_mat has
+// been resolved to the chosen child by evalMaterialNodes (material_mask.cc:122-131)
+template<int MT>
+YG_D float matAlpha(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo)
+{
+	if(YG_NOT_BLEND(MT, m)) return leafAlpha<MT>(m, sp, wo);
+	if(!m.is_transparent) return 1.f;
+	return fminf(leafAlphaG(sc.materials[m.mat1], sp, wo), leafAlphaG(sc.materials[m.mat2], sp, wo));
 }
 // used by the shadow kernel on whatever transparent material the segment crosses: generic
 YG_D Col matTransparency(const SceneDev &sc, const MatDev &m, const SurfPt &sp, V3 wo)

@@ -203,6 +203,28 @@ class Group:
             _check(None, capi.lib.yafgpu_reset_stats(capi.lib.yafgpu_group_ctx(self.h, k)))
 
 
+def pin_host_arrays(keep, min_bytes=1 << 20):
+    """Page-lock the numpy arrays of a scene description's keep-alive list (yafgpu_host_register), so that every later upload of
+    them is a DMA at PCIe speed.  Returns the registered arrays; hand them to unpin_host_arrays before they are freed."""
+    done = []
+
+    def walk(o):
+        if isinstance(o, np.ndarray):
+            if o.nbytes >= min_bytes and o.flags["C_CONTIGUOUS"]:
+                _check(None, capi.lib.yafgpu_host_register(o.ctypes.data, o.nbytes))
+                done.append(o)
+        elif isinstance(o, (list, tuple)):
+            for v in o:
+                walk(v)
+    walk(keep)
+    return done
+
+
+def unpin_host_arrays(arrays):
+    for a in arrays:
+        _check(None, capi.lib.yafgpu_host_unregister(a.ctypes.data))
+
+
 def film_to_image(film):
     """Pixel::normalized (util_image_buffers.h:39-43): col / weight when weight != 0."""
     w = film[..., 4:5]

@@ -158,7 +158,8 @@ def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, ray
     return y
 
 
-def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting", filter_type="gauss", bg_transp=False):
+def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting", filter_type="gauss", bg_transp=False, bg_transp_refract=False, see_through=False,
+                       ground_quad=True):
     """Small DirectLight + point-light scene in the spirit of BASELINE config 1 (tests/test01 geometry is 6 cubes on
     a ground quad lit by one point light; its textures are 'next' scope, so flat colours are used)."""
     y = Interface()
@@ -166,15 +167,32 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
     ground = _shiny(y, "ground", (0.8, 0.8, 0.8))
     cols = [(0.9, 0.2, 0.2), (0.2, 0.9, 0.2), (0.2, 0.2, 0.9), (0.9, 0.9, 0.2), (0.9, 0.2, 0.9), (0.2, 0.9, 0.9)]
     mats = [_shiny(y, "cube%d" % i, c, diffuse_reflect=0.5 + 0.1 * (i % 3)) for i, c in enumerate(cols)]
+    if see_through:
+        # materials whose Material::getAlpha is not 1 (the "bg_transp_refract" chain): glass, tinted glass, rough glass, a transparent shinydiffusemat,
+        # and a blend of the last with an opaque one
+        def glass(name, kind="glass", filt=(1.0, 1.0, 1.0), **kw):
+            y.paramsClearAll(); y.paramsSetString("type", kind); y.paramsSetFloat("IOR", 1.5)
+            y.paramsSetColor("filter_color", *filt); y.paramsSetColor("mirror_color", 1.0, 1.0, 1.0)
+            for k, v in kw.items():
+                y.paramsSetFloat(k, v)
+            return y.createMaterial(name)
+        mats[0] = glass("glass0")
+        mats[1] = glass("glass1", filt=(0.9, 0.5, 0.3), transmit_filter=0.8)
+        mats[2] = glass("rglass2", "rough_glass", alpha=0.2)
+        mats[3] = _shiny(y, "transp3", (0.9, 0.9, 0.2), transparency=0.7, transmit_filter=0.5, IOR=1.3, fresnel_effect=True, specular_reflect=0.2)
+        y.paramsClearAll(); y.paramsSetString("type", "blend_mat"); y.paramsSetString("material1", "transp3"); y.paramsSetString("material2", "cube5")
+        y.paramsSetFloat("blend_value", 0.4)
+        mats[4] = y.createMaterial("blend4")
     y.startGeometry()
     for i in range(6):
         y.startTriMesh(1 + i, 8, 12, False, False, 0)
         x0, y0 = -4.4 + 2.6 * (i % 3), 1.4 - 3.4 * (i // 3)
         _box(y, (x0, y0, 1e-5), (x0 + 2.0, y0 + 2.0, 2.0), mats[i], rot_deg=7.0 * i)
         y.endTriMesh()
-    y.startTriMesh(7, 4, 2, False, False, 0)
-    _quad(y, (-10, -10, 0), (10, -10, 0), (10, 10, 0), (-10, 10, 0), ground)
-    y.endTriMesh()
+    if ground_quad:
+        y.startTriMesh(7, 4, 2, False, False, 0)
+        _quad(y, (-10, -10, 0), (10, -10, 0), (10, 10, 0), (-10, 10, 0), ground)
+        y.endTriMesh()
     y.endGeometry()
     y.paramsClearAll()
     y.paramsSetString("type", "pointlight"); y.paramsSetPoint("from", 5.27648, -4.88993, 8.89514)
@@ -193,6 +211,8 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
     y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", 8); y.paramsSetInt("shadowDepth", 2)
     if bg_transp:
         y.paramsSetBool("bg_transp", True)
+    if bg_transp_refract:
+        y.paramsSetBool("bg_transp_refract", True)
     if integrator == "pathtracing":
         y.paramsSetInt("path_samples", 2); y.paramsSetInt("bounces", 3); y.paramsSetInt("russian_roulette_min_bounces", 8)
     y.createIntegrator("pt")

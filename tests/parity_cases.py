@@ -33,6 +33,11 @@ EXACT = {
     # overwrites in the reference (a leftover of its depth-first order, like include_lights_); exact only while the children cannot recurse
     "cornell_dl_rough_dispersion": lambda: scenes.cornell_box(96, 54, 2, integrator="directlighting", dispersion=30.0, rough_glass=True, raydepth=1),
     "simple_dl_bgtransp": lambda: scenes.simple_point_scene(160, 90, 2, filter_type="box", bg_transp=True),
+    # "bg_transp_refract": Material::getAlpha folded along the refraction chain (integrator_path_tracer.cc:319-328, integrator_montecarlo.cc:954,1023);
+    # glass, tinted glass, rough glass, transparent shinydiffuse and a blend in front of the open background, with and without a ground plane behind
+    "simple_dl_bgtransp_refract": lambda: scenes.simple_point_scene(160, 90, 2, filter_type="box", bg_transp=True, bg_transp_refract=True, see_through=True, ground_quad=False),
+    "simple_dl_bgrefract_only": lambda: scenes.simple_point_scene(160, 90, 1, filter_type="box", bg_transp_refract=True, see_through=True),
+    "simple_pt_bgtransp_refract": lambda: scenes.simple_point_scene(96, 54, 2, integrator="pathtracing", filter_type="box", bg_transp=True, bg_transp_refract=True, see_through=True),
     "simple_pt_bgtransp": lambda: scenes.simple_point_scene(160, 90, 4, integrator="pathtracing", filter_type="box", bg_transp=True),
 }
 

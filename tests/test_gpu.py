@@ -115,7 +115,7 @@ def test_render_matches_reference_film(ctx, name):
 FRONTEND_CASES = ["simple_dl_gauss", "cornell_dl_glass", "cornell_dl_mitchell", "cornell_pt_norr", "zoo_dl_point_free", "zoo_pt_mesh_norr",
                   "zoo_dl_hdr_ibl", "zoo_dl_hdr_angular", "cornell_dl_adaptive", "zoo_dl_directional", "zoo_dl_spot_soft", "zoo_dl_sphere",
                   "zoo_dl_gradient_ibl", "zoo_dl_cam_ortho", "zoo_dl_cam_architect", "zoo_dl_cam_angular_stereo", "zoo_dl_cam_equirect",
-                  "tex_dl_basic", "tex_dl_modes_c", "tex_dl_adjust", "tex_pt_norr", "tex_dl_materials", "zoo_dl_beer", "tex_dl_mask", "tex_dl_camera_coords", "zoo_dl_portal_hdr", "zoo_dl_ies", "zoo_dl_ies_soft", "tex_dl_procedural", "cornell_dl_lanczos", "cornell_dl_clamp", "simple_dl_bgtransp", "cornell_dl_dispersion", "cornell_pt_dispersion_norr"]
+                  "tex_dl_basic", "tex_dl_modes_c", "tex_dl_adjust", "tex_pt_norr", "tex_dl_materials", "zoo_dl_beer", "tex_dl_mask", "tex_dl_camera_coords", "zoo_dl_portal_hdr", "zoo_dl_ies", "zoo_dl_ies_soft", "tex_dl_procedural", "cornell_dl_lanczos", "cornell_dl_clamp", "simple_dl_bgtransp", "simple_dl_bgtransp_refract", "cornell_dl_dispersion", "cornell_pt_dispersion_norr"]
 
 
 @pytest.mark.skipif(ou.gpu_frontend_bin() is None, reason="oracle/_ref/yaf_xml_gpu not built (needs the reference sources)")
@@ -242,6 +242,29 @@ def test_leaf_size_changes_the_tree_not_the_film(ctx):
         ctx.set_option("leaf_size", 2)
     assert np.array_equal(a[..., 4], b[..., 4])
     assert np.abs(a[..., :3] - b[..., :3]).max() <= 1e-4 * float(np.abs(a[..., :3]).max())
+
+
+def test_upload_from_page_locked_host_arrays_gives_the_same_hits(ctx):
+    """yafgpu_host_register / yafgpu_host_unregister: page-locking the caller's scene arrays changes how they travel (DMA instead of
+    the driver's staging copy), not what arrives; registering twice is not an error, releasing an unknown pointer is."""
+    from libyafaray_b200 import pin_host_arrays, unpin_host_arrays, capi
+    y = pc.grid_mesh_scene(96, seed=11)
+    rays = pc.trace_rays(1 << 15, (-5, -5, -1), (5, 5, 2), seed=2)
+    desc, keep = y.scene_desc()
+    ctx.upload(desc, keep)
+    a = ctx.trace(rays, 0)
+    pinned = pin_host_arrays(keep, min_bytes=1 << 12)
+    assert len(pinned) >= 2
+    try:
+        assert len(pin_host_arrays(keep, min_bytes=1 << 12)) == len(pinned)   # already registered: accepted
+        ctx.upload(desc, keep)
+        b = ctx.trace(rays, 0)
+    finally:
+        unpin_host_arrays(pinned)
+    assert a.tobytes() == b.tobytes() and (a["tri"] >= 0).any()
+    assert capi.lib.yafgpu_host_unregister(pinned[0].ctypes.data) != 0 and b"cudaHostUnregister" in capi.lib.yafgpu_last_error(None)
+    ctx.upload(desc, keep)   # the failed release left no sticky CUDA error behind
+    assert ctx.trace(rays, 0).tobytes() == a.tobytes()
 
 
 def test_empty_scene_renders_background(ctx):
