@@ -121,8 +121,18 @@ typedef enum yafgpu_texture_type
 	YAFGPU_TEX_IMAGE = 0,
 	YAFGPU_TEX_BLEND = 1,    /* "blend"    texture_basic.cc:680-779: a gradient of the texture point (blend_type, use_flip_axis); a colour ramp is refused.
 	                          * Its factory sets no adjustments. */
-	YAFGPU_TEX_RGB_CUBE = 2  /* "rgb_cube" texture_basic.cc:347-386: colour = the texture point clamped to [0,1]^3, with the adj_* adjustments */
+	YAFGPU_TEX_RGB_CUBE = 2, /* "rgb_cube" texture_basic.cc:347-386: colour = the texture point clamped to [0,1]^3, with the adj_* adjustments */
+	/* noise-based procedurals over NoiseGenerator + turbulence__ (noise_generator.cc:182-630,799-811); they need yafgpu_scene_desc.noise_tables;
+	 * a colour ramp (use_color_ramp) is refused */
+	YAFGPU_TEX_CLOUDS = 3,   /* "clouds" texture_basic.cc:96-171 */
+	YAFGPU_TEX_MARBLE = 4,   /* "marble" texture_basic.cc:177-250 */
+	YAFGPU_TEX_WOOD = 5      /* "wood"   texture_basic.cc:257-343 */
 } yafgpu_texture_type;
+/* what newNoise__(noise_type) constructs, texture_basic.cc:24-52: "blender", "stdperlin", "voronoi_f1|f2|f3|f4|f2f1|crackle" (DistReal metric), "cellnoise"; anything else = new Perlin */
+enum { YAFGPU_NOISE_NEWPERLIN = 0, YAFGPU_NOISE_STDPERLIN = 1, YAFGPU_NOISE_BLENDER = 2, YAFGPU_NOISE_VORONOI_F1 = 3, YAFGPU_NOISE_VORONOI_F2 = 4, YAFGPU_NOISE_VORONOI_F3 = 5,
+       YAFGPU_NOISE_VORONOI_F4 = 6, YAFGPU_NOISE_VORONOI_F2F1 = 7, YAFGPU_NOISE_VORONOI_CRACKLE = 8, YAFGPU_NOISE_CELL = 9 };
+enum { YAFGPU_WAVE_SIN = 0, YAFGPU_WAVE_SAW = 1, YAFGPU_WAVE_TRI = 2 }; /* marble / wood "shape" */
+#define YAFGPU_NOISE_TABLES_BYTES 13340
 enum { YAFGPU_TEXBLEND_LINEAR = 0, YAFGPU_TEXBLEND_QUADRATIC = 1, YAFGPU_TEXBLEND_EASING = 2, YAFGPU_TEXBLEND_DIAGONAL = 3, YAFGPU_TEXBLEND_SPHERICAL = 4,
        YAFGPU_TEXBLEND_QUADRATIC_SPHERE = 5, YAFGPU_TEXBLEND_RADIAL = 6 }; /* BlendTexture::ProgressionType ("stype" lin/quad/ease/diag/sphere/halo|quad_sphere/radial) */
 enum { YAFGPU_TEXINTERP_NONE = 0, YAFGPU_TEXINTERP_BILINEAR = 1, YAFGPU_TEXINTERP_BICUBIC = 2 }; /* "interpolate"; mipmap_* are refused */
@@ -151,6 +161,17 @@ typedef struct yafgpu_texture
 	int32_t adj_clamp;       /* "adj_clamp" */
 	int32_t blend_type;      /* blend: YAFGPU_TEXBLEND_* */
 	int32_t use_flip_axis;   /* blend: "use_flip_axis" */
+	/* clouds / marble / wood: the members of the constructed texture object */
+	int32_t noise_type;      /* YAFGPU_NOISE_* */
+	int32_t noise_depth;     /* "depth" (octaves - 1 of turbulence__) */
+	float noise_size;        /* "size" */
+	int32_t noise_hard;      /* "hard" */
+	float color1[3], color2[3]; /* "color1", "color2" */
+	int32_t clouds_bias;     /* clouds "bias": 0 none, 1 positive, 2 negative */
+	float turbulence;        /* marble, wood "turbulence" */
+	float sharpness;         /* marble: sharpness_ as the constructor stores it (1, or 1 / "sharpness" when that is > 1) */
+	int32_t wave_shape;      /* marble, wood: YAFGPU_WAVE_* */
+	int32_t wood_rings;      /* wood: "wood_type" == "rings" */
 } yafgpu_texture;
 
 typedef enum yafgpu_node_type
@@ -487,6 +508,11 @@ typedef struct yafgpu_scene_desc
 	 * Needed only when a glass / rough_glass material has dispersion_power > 0 (upload fails without it); the reference-side adaptor fills it
 	 * from the reference's own wl2Xyz__, the Python mirror from libyafaray_b200/data/cie_xyz_360_830.npy (tools/make_cie_table.py). */
 	const float *cie_xyz; size_t n_cie_rows;
+	/* Lattice tables of the reference's noise bases, required when a clouds / marble / wood texture is present: YAFGPU_NOISE_TABLES_BYTES bytes laid out as
+	 * f32 hashpntf[768], f32 hashvectf[768], f32 stdp_g[514][3], u8 hash[512], u8 stdp_p[514], 2 pad bytes (noise_generator.cc:25-320; they are file-static
+	 * literal data there).  The adaptor compiles them in from a header that oracle/ref_driver/noise_dump.cc generates out of the reference's own source at
+	 * build time; the Python mirror reads libyafaray_b200/data/noise_tables.bin, written by the same program (tools/make_noise_tables.py). */
+	const void *noise_tables; size_t noise_tables_bytes;
 } yafgpu_scene_desc;
 
 /* ---- rays and hits (parity probe + traversal microbench) -------------------------------- */

@@ -146,8 +146,47 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 		pool.tex_index[t] = index;
 		return true;
 	}
+	const CloudsTexture *clt = dynamic_cast<const CloudsTexture *>(t);
+	const MarbleTexture *mbt = dynamic_cast<const MarbleTexture *>(t);
+	const WoodTexture *wdt = dynamic_cast<const WoodTexture *>(t);
+	if(clt || mbt || wdt)
+	{	// texture_basic.cc:96-343: the members the constructors left behind; the basis is recognised by the dynamic type of n_gen_ (newNoise__ :24-52)
+		if(t->color_ramp_) { err = "a clouds / marble / wood texture with a colour ramp is not implemented on the device"; return false; }
+		const NoiseGenerator *ng = clt ? clt->n_gen_ : mbt ? mbt->n_gen_ : wdt->n_gen_;
+		if(dynamic_cast<const StdPerlinNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_STDPERLIN;
+		else if(dynamic_cast<const BlenderNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_BLENDER;
+		else if(dynamic_cast<const CellNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_CELL;
+		else if(const VoronoiNoiseGenerator *vg = dynamic_cast<const VoronoiNoiseGenerator *>(ng))
+		{
+			if(vg->dm_type_ != VoronoiNoiseGenerator::DistReal) { err = "a Voronoi noise basis with a distance metric other than the factory's default is not implemented on the device"; return false; }
+			r.noise_type = YAFGPU_NOISE_VORONOI_F1 + (int)vg->v_type_;   // Vf1, Vf2, Vf3, Vf4, Vf2F1, VCrackle: the enumerator order of YAFGPU_NOISE_VORONOI_*
+		}
+		else if(dynamic_cast<const NewPerlinNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_NEWPERLIN;
+		else { err = "unknown noise basis"; return false; }
+		const Rgb c1 = clt ? clt->color_1_ : mbt ? mbt->color_1_ : wdt->color_1_, c2 = clt ? clt->color_2_ : mbt ? mbt->color_2_ : wdt->color_2_;
+		r.color1[0] = c1.r_; r.color1[1] = c1.g_; r.color1[2] = c1.b_; r.color2[0] = c2.r_; r.color2[1] = c2.g_; r.color2[2] = c2.b_;
+		r.sharpness = 1.f;
+		if(clt) { r.type = YAFGPU_TEX_CLOUDS; r.noise_depth = clt->depth_; r.noise_size = clt->size_; r.noise_hard = clt->hard_; r.clouds_bias = clt->bias_; }
+		else if(mbt)
+		{
+			r.type = YAFGPU_TEX_MARBLE; r.noise_depth = mbt->octaves_; r.noise_size = mbt->size_; r.noise_hard = mbt->hard_;
+			r.turbulence = mbt->turb_; r.sharpness = mbt->sharpness_; r.wave_shape = (int)mbt->wshape_;
+		}
+		else
+		{
+			r.type = YAFGPU_TEX_WOOD; r.noise_depth = wdt->octaves_; r.noise_size = wdt->size_; r.noise_hard = wdt->hard_;
+			r.turbulence = wdt->turb_; r.wave_shape = (int)wdt->wshape_; r.wood_rings = wdt->rings_;
+		}
+		r.adj_intensity = t->adj_intensity_; r.adj_contrast = t->adj_contrast_; r.adj_saturation = t->adj_saturation_; r.adj_hue = t->adj_hue_;
+		r.adj_mult_red = t->adj_mult_factor_red_; r.adj_mult_green = t->adj_mult_factor_green_; r.adj_mult_blue = t->adj_mult_factor_blue_;
+		r.adj_clamp = t->adj_clamp_;
+		index = (int)pool.textures.size();
+		pool.textures.push_back(r);
+		pool.tex_index[t] = index;
+		return true;
+	}
 	const ImageTexture *it = dynamic_cast<const ImageTexture *>(t);
-	if(!it) { err = "this procedural texture type is not implemented on the device (image, blend and rgb_cube are)"; return false; }
+	if(!it) { err = "this procedural texture type is not implemented on the device (image, blend, rgb_cube, clouds, marble and wood are)"; return false; }
 	r.type = YAFGPU_TEX_IMAGE;
 	ImageHandler *ih = it->image_;
 	r.width = ih->getWidth(); r.height = ih->getHeight();
@@ -733,6 +772,13 @@ bool GpuIntegrator::preprocess()
 	for(int i = 0; i < 470; ++i) { const Rgb c = wl2Xyz__(360.f + (float)i); cie[3 * i] = c.r_; cie[3 * i + 1] = c.g_; cie[3 * i + 2] = c.b_; }
 	{ const Rgb c = wl2Xyz__(829.5f); cie[3 * 470] = 2.f * c.r_ - cie[3 * 469]; cie[3 * 470 + 1] = 2.f * c.g_ - cie[3 * 469 + 1]; cie[3 * 470 + 2] = 2.f * c.b_ - cie[3 * 469 + 2]; }
 	d.cie_xyz = cie.data(); d.n_cie_rows = 471;
+	// lattice tables of the noise bases: file-static data of src/texture/noise_generator.cc, compiled in from the header that
+	// oracle/ref_driver/noise_dump.cc writes out of that very source when the integration is built (oracle/Makefile `gpu`)
+	static const unsigned char noise_tables[] = {
+#include "noise_tables.inc"
+	};
+	static_assert(sizeof(noise_tables) == YAFGPU_NOISE_TABLES_BYTES, "noise table blob");
+	d.noise_tables = noise_tables; d.noise_tables_bytes = sizeof(noise_tables);
 	if(yafgpu_group_upload_scene(grp_, &d) != YAFGPU_OK) return fail("scene upload refused");
 	yafgpu_stats st;
 	yafgpu_group_get_stats(grp_, &st);

@@ -28,7 +28,9 @@ INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
 TRACE_STATIC_MAX_RAYS = 65536  # YAFGPU_TRACE_STATIC_MAX_RAYS
 FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES, FLAG_SHARE_DEVICE = 1, 2, 4
-TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE = range(3)
+TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD = range(6)
+NOISE = {"stdperlin": 1, "blender": 2, "voronoi_f1": 3, "voronoi_f2": 4, "voronoi_f3": 5, "voronoi_f4": 6, "voronoi_f2f1": 7, "voronoi_crackle": 8, "cellnoise": 9}
+NOISE_TABLES_BYTES = 13340
 TEXBLEND = {"lin": 0, "quad": 1, "ease": 2, "diag": 3, "sphere": 4, "halo": 5, "quad_sphere": 5, "radial": 6}
 TEXINTERP = {"none": 0, "bilinear": 1, "bicubic": 2}
 TEXCLIP = {"extend": 0, "clip": 1, "clipcube": 2, "repeat": 3, "checker": 4}
@@ -104,7 +106,9 @@ class Texture(C.Structure):
                 ("checker_even", i32), ("checker_odd", i32), ("checker_dist", f32), ("normalmap", i32),
                 ("color_space", i32), ("gamma", f32), ("adj_intensity", f32), ("adj_contrast", f32),
                 ("adj_saturation", f32), ("adj_hue", f32), ("adj_mult_red", f32), ("adj_mult_green", f32),
-                ("adj_mult_blue", f32), ("adj_clamp", i32), ("blend_type", i32), ("use_flip_axis", i32)]
+                ("adj_mult_blue", f32), ("adj_clamp", i32), ("blend_type", i32), ("use_flip_axis", i32),
+                ("noise_type", i32), ("noise_depth", i32), ("noise_size", f32), ("noise_hard", i32), ("color1", f32 * 3), ("color2", f32 * 3),
+                ("clouds_bias", i32), ("turbulence", f32), ("sharpness", f32), ("wave_shape", i32), ("wood_rings", i32)]
 
 
 class ShaderNode(C.Structure):
@@ -159,7 +163,7 @@ class SceneDesc(C.Structure):
                 ("textures", C.POINTER(Texture)), ("n_textures", C.c_size_t),
                 ("nodes", C.POINTER(ShaderNode)), ("n_nodes", C.c_size_t),
                 ("camera", Camera), ("background", Background), ("film", FilmDesc), ("integrator", IntegratorDesc),
-                ("cie_xyz", C.POINTER(C.c_float)), ("n_cie_rows", C.c_size_t)]
+                ("cie_xyz", C.POINTER(C.c_float)), ("n_cie_rows", C.c_size_t), ("noise_tables", C.c_void_p), ("noise_tables_bytes", C.c_size_t)]
 
 
 class PassDesc(C.Structure):

@@ -63,6 +63,7 @@ static void freeScene(yafgpu_ctx *c)
 	for(void *q : c->tex_ptrs) poolFree(q, c->stream);
 	c->tex_ptrs.clear();
 	poolFree(c->d_cie, c->stream); c->d_cie = nullptr;
+	poolFree(c->d_noise, c->stream); c->d_noise = nullptr;
 	poolFree(c->d_textures, c->stream); c->d_textures = nullptr; poolFree(c->d_shader_nodes, c->stream); c->d_shader_nodes = nullptr;
 	c->d_points = c->d_normals = c->d_uv = c->d_tri_ng = nullptr; c->d_tri_vidx = c->d_tri_mat = nullptr; c->d_mat_triflags = nullptr;
 	c->d_tris = nullptr; c->d_objects = nullptr; c->d_mats = nullptr; c->d_lights = nullptr; c->d_light_tables = nullptr; c->d_bg_tex = nullptr;
@@ -447,9 +448,18 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	}
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
 	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
+	bool any_noise = false;
+	for(const TexDev &t : h_tex) any_noise = any_noise || t.type == YAFGPU_TEX_CLOUDS || t.type == YAFGPU_TEX_MARBLE || t.type == YAFGPU_TEX_WOOD;
+	if(any_noise)
+	{
+		if(!desc->noise_tables || desc->noise_tables_bytes != YAFGPU_NOISE_TABLES_BYTES)
+			return setErr(c, YAFGPU_ERR_INVALID, "a clouds / marble / wood texture is present but yafgpu_scene_desc.noise_tables (13340 bytes) is missing");
+		YG_CUDA(c, upload(c->d_noise, (const NoiseTables *)desc->noise_tables, 1, st));
+	}
 	for(size_t i = 0; i < h_tex.size(); ++i)
 	{
 		float4 *d_px = nullptr;
+		h_tex[i].noise = c->d_noise;
 		if(h_tex[i].type != YAFGPU_TEX_IMAGE) { h_tex[i].tex = nullptr; continue; } // procedural: no texels
 		YG_CUDA(c, upload(d_px, (const float4 *)desc->textures[i].rgba, (size_t)h_tex[i].w * h_tex[i].h, st));
 		c->tex_ptrs.push_back(d_px);

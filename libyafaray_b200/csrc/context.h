@@ -35,6 +35,7 @@ struct yafgpu_ctx
 	yg::Accel *d_light_accels = nullptr;
 	std::vector<void *> light_bvh_ptrs; // node/triangle arrays of the mesh-light accelerators
 	float *d_bg_tex = nullptr, *d_cie = nullptr;
+	yg::NoiseTables *d_noise = nullptr;          // lattice tables of the noise bases (only with clouds / marble / wood textures)
 	yg::TexDev *d_textures = nullptr; yg::NodeDev *d_shader_nodes = nullptr; // image textures and shader nodes (nodes.cuh)
 	std::vector<void *> tex_ptrs;                                            // texel arrays of d_textures
 	yg::FaureTables *d_faure = nullptr;

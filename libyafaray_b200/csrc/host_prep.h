@@ -215,6 +215,18 @@ inline bool prepTexture(const yafgpu_texture &t, TexDev &d, std::string &err)
 		d.adj_intensity = d.adj_contrast = d.adj_saturation = 1.f; d.adj_mult[0] = d.adj_mult[1] = d.adj_mult[2] = 1.f;
 		return true;
 	}
+	const bool noise_tex = t.type == YAFGPU_TEX_CLOUDS || t.type == YAFGPU_TEX_MARBLE || t.type == YAFGPU_TEX_WOOD;
+	if(noise_tex)
+	{	// CloudsTexture / MarbleTexture / WoodTexture after their constructors (texture_basic.cc:96-107,177-188,257-266)
+		if(t.noise_type < YAFGPU_NOISE_NEWPERLIN || t.noise_type > YAFGPU_NOISE_CELL) { err = "noise texture: noise_type"; return false; }
+		if(t.noise_depth < 0 || t.noise_depth > 29) { err = "noise texture: depth must be 0..29 (turbulence__ shifts 1 << (depth + 1))"; return false; }
+		d.noise_type = t.noise_type; d.depth = t.noise_depth; d.size = t.noise_size; d.hard = t.noise_hard ? 1 : 0;
+		for(int k = 0; k < 3; ++k) { d.color1[k] = t.color1[k]; d.color2[k] = t.color2[k]; }
+		d.bias = t.type == YAFGPU_TEX_CLOUDS ? t.clouds_bias : 0; d.turb = t.turbulence; d.sharpness = t.sharpness;
+		d.shape = t.wave_shape; d.rings = t.wood_rings ? 1 : 0;
+		if(d.bias < 0 || d.bias > 2 || d.shape < YAFGPU_WAVE_SIN || d.shape > YAFGPU_WAVE_TRI) { err = "noise texture: bias / shape"; return false; }
+	}
+	else
 	if(t.type != YAFGPU_TEX_IMAGE && t.type != YAFGPU_TEX_RGB_CUBE) { err = "texture type " + std::to_string(t.type) + " is not implemented on the device"; return false; }
 	if(t.type == YAFGPU_TEX_IMAGE)
 	if(!t.rgba || t.width <= 0 || t.height <= 0) { err = "image texture without texels"; return false; }

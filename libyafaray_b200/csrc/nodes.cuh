@@ -290,6 +290,188 @@ YG_D Rgba4 imgInterpolate(const TexDev &t, float px, float py)
 	return ((w11 * c11 + w12 * c12) + w21 * c21) + w22 * c22;
 }
 
+// ---- noise bases and the procedural textures over them ------------------------------------------------------------------------
+// NoiseGenerator::operator() of the five families the factories can construct (noise_generator.cc:182-630), evaluated with the reference's own
+// lattice tables (NoiseTables).  Every double-typed literal of the reference is kept as one: `0.5 + 0.5 * nv`, `1.0 - 3.0 * c + 2.0 * c * o`,
+// `t * t * (3.0 - 2.0 * t)` are double expressions narrowed on assignment.
+YG_D float noiseLerp(float t, float a, float b) { return a + t * (b - a); }
+YG_D float newPerlinGrad(int hash, float x, float y, float z)
+{	// noise_generator.h:50-56: the low four bits pick one of twelve edge directions
+	const int h = hash & 15;
+	const float u = h < 8 ? x : y, v = h < 4 ? y : ((h == 12 || h == 14) ? x : z);
+	return ((h & 1) == 0 ? u : -u) + ((h & 2) == 0 ? v : -v);
+}
+YG_D float newPerlinFade(float t) { return t * t * t * (t * (t * 6 - 15) + 10); }
+YG_D float noiseNewPerlin(const NoiseTables &nt, V3 pt)
+{	// noise_generator.cc:182-205
+	float x = pt.x, y = pt.y, z = pt.z;
+	float u = floorf(x), v = floorf(y), w = floorf(z);
+	const int cx = ((int)u) & 255, cy = ((int)v) & 255, cz = ((int)w) & 255;
+	x -= u; y -= v; z -= w;
+	u = newPerlinFade(x); v = newPerlinFade(y); w = newPerlinFade(z);
+	const unsigned char *hs = nt.hash;
+	const int a = hs[cx] + cy, aa = hs[a] + cz, ab = hs[a + 1] + cz, b = hs[cx + 1] + cy, ba = hs[b] + cz, bb = hs[b + 1] + cz;
+	const float lo = noiseLerp(v, noiseLerp(u, newPerlinGrad(hs[aa], x, y, z), newPerlinGrad(hs[ba], x - 1, y, z)),
+	                              noiseLerp(u, newPerlinGrad(hs[ab], x, y - 1, z), newPerlinGrad(hs[bb], x - 1, y - 1, z)));
+	const float hi = noiseLerp(v, noiseLerp(u, newPerlinGrad(hs[aa + 1], x, y, z - 1), newPerlinGrad(hs[ba + 1], x - 1, y, z - 1)),
+	                              noiseLerp(u, newPerlinGrad(hs[ab + 1], x, y - 1, z - 1), newPerlinGrad(hs[bb + 1], x - 1, y - 1, z - 1)));
+	const float nv = noiseLerp(w, lo, hi);
+	return (float)(0.5 + 0.5 * (double)nv);
+}
+YG_D void stdPerlinSetup(float c, int &b0, int &b1, float &r0, float &r1)
+{	// SETUP, noise_generator.cc:312-317
+	const float t = (float)((double)c + 10000.0);
+	b0 = ((int)t) & 255; b1 = (b0 + 1) & 255;
+	r0 = t - (float)(int)t; r1 = (float)((double)r0 - 1.0);
+}
+YG_D float stdPerlinSurve(float t) { return (float)((double)(t * t) * (3.0 - 2.0 * (double)t)); }
+YG_D float stdPerlinAt(const float *q, float rx, float ry, float rz) { return rx * q[0] + ry * q[1] + rz * q[2]; }
+YG_D float noiseStdPerlin(const NoiseTables &nt, V3 pt)
+{	// noise_generator.cc:323-374
+	int bx0, bx1, by0, by1, bz0, bz1;
+	float rx0, rx1, ry0, ry1, rz0, rz1;
+	stdPerlinSetup(pt.x, bx0, bx1, rx0, rx1); stdPerlinSetup(pt.y, by0, by1, ry0, ry1); stdPerlinSetup(pt.z, bz0, bz1, rz0, rz1);
+	const unsigned char *pp = nt.stdp_p;
+	const int i = pp[bx0], j = pp[bx1];
+	const int b00 = pp[i + by0], b10 = pp[j + by0], b01 = pp[i + by1], b11 = pp[j + by1];
+	const float sx = stdPerlinSurve(rx0), sy = stdPerlinSurve(ry0), sz = stdPerlinSurve(rz0);
+	const float *g = nt.stdp_g;
+	float u = stdPerlinAt(g + 3 * (b00 + bz0), rx0, ry0, rz0), v = stdPerlinAt(g + 3 * (b10 + bz0), rx1, ry0, rz0);
+	float a = noiseLerp(sx, u, v);
+	u = stdPerlinAt(g + 3 * (b01 + bz0), rx0, ry1, rz0); v = stdPerlinAt(g + 3 * (b11 + bz0), rx1, ry1, rz0);
+	float b = noiseLerp(sx, u, v);
+	const float c = noiseLerp(sy, a, b);
+	u = stdPerlinAt(g + 3 * (b00 + bz1), rx0, ry0, rz1); v = stdPerlinAt(g + 3 * (b10 + bz1), rx1, ry0, rz1);
+	a = noiseLerp(sx, u, v);
+	u = stdPerlinAt(g + 3 * (b01 + bz1), rx0, ry1, rz1); v = stdPerlinAt(g + 3 * (b11 + bz1), rx1, ry1, rz1);
+	b = noiseLerp(sx, u, v);
+	const float d = noiseLerp(sy, a, b);
+	return (float)(0.5 + 0.75 * (double)noiseLerp(sz, c, d));
+}
+YG_D float blenderFall(float c, float o, double sign) { return (float)((1.0 - 3.0 * (double)c) + sign * ((2.0 * (double)c) * (double)o)); }
+YG_D float noiseBlender(const NoiseTables &nt, V3 pt)
+{	// noise_generator.cc:411-481: eight lattice corners, cubic fall-off per axis, gradients from hashvectf
+	const float x = pt.x, y = pt.y, z = pt.z;
+	const int ix = (int)floorf(x), iy = (int)floorf(y), iz = (int)floorf(z);
+	const float ox = x - (float)ix, oy = y - (float)iy, oz = z - (float)iz;
+	const float jx = ox - 1, jy = oy - 1, jz = oz - 1;
+	const float fx0 = blenderFall(ox * ox, ox, 1.0), fy0 = blenderFall(oy * oy, oy, 1.0), fz0 = blenderFall(oz * oz, oz, 1.0);
+	const float fx1 = blenderFall(jx * jx, jx, -1.0), fy1 = blenderFall(jy * jy, jy, -1.0), fz1 = blenderFall(jz * jz, jz, -1.0);
+	const unsigned char *hs = nt.hash;
+	const int b00 = hs[hs[ix & 255] + (iy & 255)], b10 = hs[hs[(ix + 1) & 255] + (iy & 255)];
+	const int b01 = hs[hs[ix & 255] + ((iy + 1) & 255)], b11 = hs[hs[(ix + 1) & 255] + ((iy + 1) & 255)];
+	const int b20 = iz & 255, b21 = (iz + 1) & 255;
+	float n = 0.5f;
+	const float *h;
+#define YG_BN(wt, bz, bxy, dx, dy, dz) h = nt.hashvectf + 3 * hs[(bz) + (bxy)]; n += (wt) * (h[0] * (dx) + h[1] * (dy) + h[2] * (dz));
+	YG_BN(fx0 * fy0 * fz0, b20, b00, ox, oy, oz)
+	YG_BN(fx0 * fy0 * fz1, b21, b00, ox, oy, jz)
+	YG_BN(fx0 * fy1 * fz0, b20, b01, ox, jy, oz)
+	YG_BN(fx0 * fy1 * fz1, b21, b01, ox, jy, jz)
+	YG_BN(fx1 * fy0 * fz0, b20, b10, jx, oy, oz)
+	YG_BN(fx1 * fy0 * fz1, b21, b10, jx, oy, jz)
+	YG_BN(fx1 * fy1 * fz0, b20, b11, jx, jy, oz)
+	YG_BN(fx1 * fy1 * fz1, b21, b11, jx, jy, jz)
+#undef YG_BN
+	if(n < 0.f) n = 0.f; else if(n > 1.f) n = 1.f;
+	return n;
+}
+YG_D float noiseVoronoi(const NoiseTables &nt, V3 pt, int kind)
+{	// VoronoiNoiseGenerator::getFeatures + operator() noise_generator.cc:531-600 with the factory's defaults (DistReal): the four nearest of the
+	// 27 jittered feature points around the cell
+	const float x = pt.x, y = pt.y, z = pt.z;
+	const int xi = (int)floorf(x), yi = (int)floorf(y), zi = (int)floorf(z);
+	float da0 = 1e10f, da1 = 1e10f, da2 = 1e10f, da3 = 1e10f;
+	const unsigned char *hs = nt.hash;
+	for(int xx = xi - 1; xx <= xi + 1; ++xx)
+		for(int yy = yi - 1; yy <= yi + 1; ++yy)
+			for(int zz = zi - 1; zz <= zi + 1; ++zz)
+			{
+				const float *p = nt.hashpntf + 3 * hs[(hs[(hs[zz & 255] + yy) & 255] + xx) & 255];
+				const float xd = x - (p[0] + (float)xx), yd = y - (p[1] + (float)yy), zd = z - (p[2] + (float)zz);
+				const float d = fSqrt(xd * xd + yd * yd + zd * zd);
+				if(d < da0) { da3 = da2; da2 = da1; da1 = da0; da0 = d; }
+				else if(d < da1) { da3 = da2; da2 = da1; da1 = d; }
+				else if(d < da2) { da3 = da2; da2 = d; }
+				else if(d < da3) da3 = d;
+			}
+	switch(kind)
+	{
+		case YAFGPU_NOISE_VORONOI_F2: return da1;
+		case YAFGPU_NOISE_VORONOI_F3: return da2;
+		case YAFGPU_NOISE_VORONOI_F4: return da3;
+		case YAFGPU_NOISE_VORONOI_F2F1: return da1 - da0;
+		case YAFGPU_NOISE_VORONOI_CRACKLE: { const float t = (float)(10.0 * (double)(da1 - da0)); return ((double)t > 1.0) ? 1.f : t; }
+		default: return da0;
+	}
+}
+YG_D float noiseCell(V3 pt)
+{	// noise_generator.cc:606-614: an integer hash of the cell, scaled by 2^-32 in double
+	const int xi = (int)floorf(pt.x), yi = (int)floorf(pt.y), zi = (int)floorf(pt.z);
+	unsigned n = (unsigned)xi + (unsigned)yi * 1301u + (unsigned)zi * 314159u;
+	n ^= (n << 13);
+	return (float)((double)(float)(n * (n * n * 15731u + 789221u) + 1376312589u) / 4294967296.0);
+}
+YG_DN float noiseEval(const NoiseTables &nt, int type, V3 p)
+{
+	switch(type)
+	{
+		case YAFGPU_NOISE_STDPERLIN: return noiseStdPerlin(nt, p);
+		case YAFGPU_NOISE_BLENDER: return noiseBlender(nt, p);
+		case YAFGPU_NOISE_CELL: return noiseCell(p);
+		case YAFGPU_NOISE_NEWPERLIN: return noiseNewPerlin(nt, p);
+		default: return noiseVoronoi(nt, p, type);
+	}
+}
+// turbulence__ noise_generator.cc:799-811: depth + 1 octaves, half amplitude and double frequency each; only the Blender basis offsets the point
+YG_D float noiseTurbulence(const TexDev &t, V3 pt)
+{
+	float amp = 1.f, sum = 0.f;
+	V3 tp = (t.noise_type == YAFGPU_NOISE_BLENDER ? pt + mk(1.f, 1.f, 1.f) : pt) * t.size;
+	for(int i = 0; i <= t.depth; ++i, amp *= 0.5f, tp = tp * 2.f)
+	{
+		float val = noiseEval(*t.noise, t.noise_type, tp);
+		if(t.hard) val = (float)fabs(2.0 * (double)val - 1.0);
+		sum += amp * val;
+	}
+	return sum * ((float)(1 << t.depth) / (float)((1 << (t.depth + 1)) - 1));
+}
+// marble / wood wave shapes, texture_basic.cc:190-206,268-291
+YG_D float noiseWave(int shape, float w)
+{
+	switch(shape)
+	{
+		case YAFGPU_WAVE_SAW: w *= (float)(0.5 * 0.318309886183790671538); w -= floorf(w); return w;
+		case YAFGPU_WAVE_TRI: w *= (float)(0.5 * 0.318309886183790671538); return fabsf(2.f * (w - floorf(w)) - 1.f);
+		default: return 0.5f + 0.5f * fSin(w);
+	}
+}
+// CloudsTexture / MarbleTexture / WoodTexture ::getFloat
+YG_D float noiseTexFloat(const TexDev &t, V3 p)
+{
+	if(t.type == YAFGPU_TEX_CLOUDS)
+	{
+		float v = noiseTurbulence(t, p);
+		if(t.bias)
+		{
+			v *= v;
+			if(t.bias == 1) return -v;   // returned without the adjustments, as the reference does (:118)
+		}
+		return texAdjustFloat(t, v);
+	}
+	if(t.type == YAFGPU_TEX_MARBLE)
+	{	// `(x + y + z) * 5.0 + turb * turbulence` is a double sum narrowed into w
+		const double tb = ((double)t.turb == 0.0) ? 0.0 : (double)(t.turb * noiseTurbulence(t, p));
+		const float w = (float)((double)(p.x + p.y + p.z) * 5.0 + tb);
+		return texAdjustFloat(t, fPow(noiseWave(t.shape, w), t.sharpness));
+	}
+	float w;
+	if(t.rings) w = (float)((double)fSqrt(p.x * p.x + p.y * p.y + p.z * p.z) * 20.0);
+	else w = (float)((double)(p.x + p.y + p.z) * 10.0);
+	w = (float)((double)w + (((double)t.turb == 0.0) ? 0.0 : (double)(t.turb * noiseTurbulence(t, p))));
+	return texAdjustFloat(t, noiseWave(t.shape, w));
+}
+
 // BlendTexture::getFloat texture_basic.cc:698-751 (its factory leaves the adjustments unset)
 YG_D float blendTexFloat(const TexDev &t, V3 p)
 {
@@ -323,6 +505,12 @@ YG_D float blendTexFloat(const TexDev &t, V3 p)
 YG_D Rgba4 texGetColor(const TexDev &t, V3 p)
 {
 	if(t.type == YAFGPU_TEX_BLEND) { const float f = blendTexFloat(t, p); return mk4(f, f, f, 1.f); }
+	if(t.type >= YAFGPU_TEX_CLOUDS)
+	{	// color_1_ + getFloat(p) * (color_2_ - color_1_), then applyColorAdjustments (texture_basic.cc:122-126,208-212,293-297)
+		const float f = noiseTexFloat(t, p);
+		const Rgba4 c = mk4(t.color1[0] + f * (t.color2[0] - t.color1[0]), t.color1[1] + f * (t.color2[1] - t.color1[1]), t.color1[2] + f * (t.color2[2] - t.color1[2]), 1.f);
+		return texAdjust(t, c);
+	}
 	if(t.type == YAFGPU_TEX_RGB_CUBE)
 	{
 		Rgba4 c = mk4(fmaxf(0.f, fminf(1.f, p.x)), fmaxf(0.f, fminf(1.f, p.y)), fmaxf(0.f, fminf(1.f, p.z)), 1.f);
@@ -342,6 +530,7 @@ YG_D Rgba4 texGetRawColor(const TexDev &t, V3 p)
 YG_D float texGetFloat(const TexDev &t, V3 p)
 {
 	if(t.type == YAFGPU_TEX_BLEND) return blendTexFloat(t, p);
+	if(t.type >= YAFGPU_TEX_CLOUDS) return noiseTexFloat(t, p);
 	if(t.type == YAFGPU_TEX_RGB_CUBE)
 		return texAdjustFloat(t, (fmaxf(0.f, fminf(1.f, p.x)) + fmaxf(0.f, fminf(1.f, p.y)) + fmaxf(0.f, fminf(1.f, p.z))) * 0.333333f);
 	return texAdjustFloat(t, col2Bri(texGetRawColor(t, p)));

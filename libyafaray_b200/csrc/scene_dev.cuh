@@ -98,6 +98,17 @@ struct MatDev
 
 #define YG_MAX_NODES 16 /* nodes per material (per-thread node stack: 20 B each) */
 
+// Lattice tables of the reference's noise bases in the byte layout of yafgpu_scene_desc.noise_tables (noise_generator.cc:25-320)
+struct NoiseTables
+{
+	float hashpntf[768];      // Voronoi feature points / cell colours
+	float hashvectf[768];     // Blender noise gradients
+	float stdp_g[514 * 3];    // standard Perlin gradients
+	unsigned char hash[512];  // the permutation shared by new Perlin, Blender noise and Voronoi
+	unsigned char stdp_p[516];// standard Perlin permutation (514 used)
+};
+static_assert(sizeof(NoiseTables) == YAFGPU_NOISE_TABLES_BYTES, "noise table blob layout");
+
 // ImageTexture after its factory (texture_image.cc:560-720); texels as ImageHandler::getPixel returns them, RGBA float
 struct TexDev
 {
@@ -108,6 +119,8 @@ struct TexDev
 	int normalmap, color_space; float gamma;
 	int type, blend_type, flip;  // yafgpu_texture_type; blend: progression type, use_flip_axis
 	int adj_set, adj_clamp; float adj_intensity, adj_contrast, adj_saturation, adj_hue, adj_mult[3]; // adj_hue already / 60 (texture.h:154)
+	// clouds / marble / wood (texture_basic.cc:96-343)
+	const NoiseTables *noise; int noise_type, depth, hard, bias, shape, rings; float size, turb, sharpness, color1[3], color2[3];
 };
 
 // One shader node after its factory + configInputs; in1/in2/fac are stack indices (-1 = constant input)

@@ -477,6 +477,31 @@ class Interface:
             self._tex_index[name] = len(self._texs)
             self._texs.append(t)
             return self._tex_index[name]
+        if ttype in ("clouds", "marble", "wood"):   # texture_basic.cc:96-171, 177-250, 257-343 (factories), newNoise__ :24-52
+            if g(p, "use_color_ramp", False):
+                raise NotImplementedError("%s texture with a colour ramp is not implemented on the device" % ttype)
+            t = capi.Texture()
+            t.type = {"clouds": capi.TEX_CLOUDS, "marble": capi.TEX_MARBLE, "wood": capi.TEX_WOOD}[ttype]
+            nt = g(p, "noise_type", "")
+            t.noise_type = capi.NOISE.get(nt, 3 if "voronoi" in nt else 0)
+            t.noise_depth, t.noise_size, t.noise_hard = int(g(p, "depth", 2)), g(p, "size", 1.0), int(g(p, "hard", False))
+            c1, c2 = g(p, "color1", (0.0, 0.0, 0.0)), g(p, "color2", (1.0, 1.0, 1.0))
+            for k in range(3):
+                t.color1[k], t.color2[k] = c1[k], c2[k]
+            t.clouds_bias = {"positive": 1, "negative": 2}.get(g(p, "bias", ""), 0) if ttype == "clouds" else 0
+            t.turbulence = g(p, "turbulence", 1.0)
+            shp = np.float32(g(p, "sharpness", 1.0))
+            t.sharpness = float(np.float32(1.0 / float(shp))) if (ttype == "marble" and shp > 1) else 1.0
+            t.wave_shape = {"saw": 1, "tri": 2}.get(g(p, "shape", ""), 0)
+            t.wood_rings = int(g(p, "wood_type", "") == "rings")
+            t.adj_intensity, t.adj_contrast = g(p, "adj_intensity", 1.0), g(p, "adj_contrast", 1.0)
+            t.adj_saturation, t.adj_hue = g(p, "adj_saturation", 1.0), float(np.float32(g(p, "adj_hue", 0.0)) / np.float32(60.0))
+            t.adj_mult_red, t.adj_mult_green, t.adj_mult_blue = g(p, "adj_mult_factor_red", 1.0), g(p, "adj_mult_factor_green", 1.0), g(p, "adj_mult_factor_blue", 1.0)
+            t.adj_clamp = int(g(p, "adj_clamp", False))
+            self._uses_noise = True
+            self._tex_index[name] = len(self._texs)
+            self._texs.append(t)
+            return self._tex_index[name]
         if ttype != "image":
             raise NotImplementedError("texture type '%s' (image, blend and rgb_cube textures are implemented on the device)" % ttype)
         fn = g(p, "filename", "")
@@ -599,7 +624,7 @@ class Interface:
                 raise KeyError("unknown material '%s'" % n)
             return mat_index[n]
         mats = (capi.Material * max(1, len(mat_names)))()
-        self._nodes, self._texs, self._tex_index, self._tex_keep = [], [], {}, []
+        self._nodes, self._texs, self._tex_index, self._tex_keep, self._uses_noise = [], [], {}, [], False
         for i, n in enumerate(mat_names):
             mats[i] = self._material_record(n, index_of)
 
@@ -809,6 +834,12 @@ class Interface:
             cie = np.ascontiguousarray(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "cie_xyz_360_830.npy")), np.float32).reshape(-1, 3)
             keep.append(cie)
             d.cie_xyz, d.n_cie_rows = cie.ctypes.data_as(C.POINTER(C.c_float)), len(cie)
+        if self._uses_noise:
+            # lattice tables of the noise bases (noise_generator.cc:25-320), dumped from the reference's source by tools/make_noise_tables.py
+            import os
+            nt = np.fromfile(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "noise_tables.bin"), np.uint8)
+            keep.append(nt)
+            d.noise_tables, d.noise_tables_bytes = nt.ctypes.data, nt.nbytes
         return d, keep
 
 

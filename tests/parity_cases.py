@@ -326,6 +326,9 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
     elif variant == "procedural":
         _textured_procedural_materials(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
+    elif variant == "noise":
+        _textured_noise_materials(y, sd, node, mapper, layer)
+        box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     elif variant == "materials":
         _textured_other_materials(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
@@ -382,6 +385,67 @@ def _textured_procedural_materials(y, sd, node, mapper, layer):
     layer("l5c", "m5c", mode=0, colfac=0.8)
     mapper("m5", texture="p_halo", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0), bump_strength=2.0)   # uv coordinates, yet the non-discrete bump branch
     mapper("m5c", texture="p_diag", texco="uv")
+    y.createMaterial("b5")
+
+
+def _textured_noise_materials(y, sd, node, mapper, layer):
+    """The noise-based procedural textures: "clouds", "marble", "wood" (texture_basic.cc:96-343) over every basis newNoise__ can build (new Perlin,
+    standard Perlin, Blender noise, six Voronoi variants, cell noise), soft and hard turbulence, the three wave shapes, ring wood, cloud bias,
+    adjustments; read as colours, as scalars and as bump maps."""
+    def tex(name, typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ); _set_params(y, kw); y.createTexture(name)
+    tex("n_clouds_new", "clouds", noise_type="newperlin", depth=3, size=2.5, color1=(0.1, 0.2, 0.6, 1.0), color2=(1.0, 0.9, 0.7, 1.0))
+    tex("n_clouds_std", "clouds", noise_type="stdperlin", depth=2, size=4.0, hard=True)
+    tex("n_clouds_bl", "clouds", noise_type="blender", depth=4, size=3.0, bias="negative", adj_intensity=1.2, adj_contrast=1.5, adj_clamp=True)
+    tex("n_clouds_pos", "clouds", noise_type="blender", depth=1, size=2.0, bias="positive")
+    tex("n_clouds_cell", "clouds", noise_type="cellnoise", depth=0, size=6.0, color1=(0.9, 0.1, 0.1, 1.0), color2=(0.1, 0.9, 0.3, 1.0))
+    tex("n_marble_sin", "marble", noise_type="blender", depth=3, size=2.0, turbulence=4.0, sharpness=3.0, color1=(0.9, 0.9, 0.85, 1.0), color2=(0.2, 0.25, 0.3, 1.0))
+    tex("n_marble_saw", "marble", noise_type="voronoi_f1", depth=1, size=3.0, turbulence=2.0, shape="saw", hard=True)
+    tex("n_marble_tri", "marble", noise_type="voronoi_crackle", depth=2, size=2.0, turbulence=3.0, shape="tri", sharpness=0.5, adj_saturation=0.6, adj_hue=40.0)
+    tex("n_marble_flat", "marble", noise_type="newperlin", turbulence=0.0, size=1.0, color1=(0.8, 0.5, 0.2, 1.0), color2=(0.1, 0.1, 0.4, 1.0))
+    tex("n_wood_bands", "wood", noise_type="stdperlin", depth=2, size=3.0, turbulence=2.0, color1=(0.45, 0.25, 0.1, 1.0), color2=(0.8, 0.6, 0.35, 1.0))
+    tex("n_wood_rings", "wood", noise_type="voronoi_f2f1", depth=1, size=2.0, turbulence=1.5, wood_type="rings", shape="tri")
+    tex("n_wood_saw", "wood", noise_type="voronoi_f2", depth=0, size=1.5, turbulence=0.5, shape="saw", adj_mult_factor_red=1.2, adj_mult_factor_green=0.8)
+    tex("n_clouds_f3", "clouds", noise_type="voronoi_f3", depth=1, size=3.0)
+    tex("n_clouds_f4", "clouds", noise_type="voronoi_f4", depth=2, size=2.0, hard=True)
+    sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
+    layer("gl", "gm", mode=0, colfac=0.9, upper_color=(0.3, 0.5, 0.8, 1.0))
+    mapper("gm", texture="n_marble_sin", texco="global", scale=(0.3, 0.3, 0.3))
+    y.createMaterial("ground")
+    sd("b0", color=(0.9, 0.9, 0.9, 1.0), diffuse_shader="l0")
+    layer("l0", "m0", mode=0, colfac=0.9)
+    mapper("m0", texture="n_clouds_new", texco="orco", scale=(1.5, 1.5, 1.5), offset=(0.25, 0.25, 0.25))
+    y.createMaterial("b0")
+    sd("b1", color=(0.8, 0.6, 0.4, 1.0), specular_reflect=0.3, mirror_shader="l1s", diffuse_shader="l1c")
+    layer("l1s", "m1", do_color=False, do_scalar=True, color_input=False, def_val=0.6, upper_value=0.1)
+    layer("l1c", "m1b", mode=2, colfac=0.7, upper_color=(0.9, 0.8, 0.3, 1.0))
+    mapper("m1", texture="n_clouds_std", texco="global", scale=(0.6, 0.6, 0.6))
+    mapper("m1b", texture="n_wood_bands", texco="global", scale=(0.4, 0.4, 0.4), offset=(0.3, 0.0, 0.0))
+    y.createMaterial("b1")
+    sd("b2", color=(0.5, 0.8, 0.5, 1.0), transparency=0.1, transmit_filter=0.7, transparency_shader="l2t", diffuse_shader="l2b")
+    layer("l2t", "m2", do_color=False, do_scalar=True, color_input=True, def_val=0.5, upper_value=0.0)
+    layer("l2b", "m2b", mode=0, colfac=0.8)
+    mapper("m2", texture="n_clouds_pos", texco="orco", scale=(2.0, 2.0, 2.0))
+    mapper("m2b", texture="n_marble_tri", texco="orco", scale=(1.5, 1.5, 1.5), offset=(0.25, 0.25, 0.25))
+    y.createMaterial("b2")
+    sd("b3", color=(0.8, 0.8, 0.8, 1.0), diffuse_shader="x3")
+    node(type="mix", name="x3", input1="m3", input2="m3b", value=0.5, mode=0)
+    mapper("m3", texture="n_marble_saw", texco="orco", scale=(1.8, 1.8, 1.8))
+    mapper("m3b", texture="n_clouds_cell", texco="orco")
+    y.createMaterial("b3")
+    sd("b4", color=(0.7, 0.7, 0.9, 1.0), specular_reflect=0.15, bump_shader="l4b", diffuse_shader="x4")
+    layer("l4b", "m4", do_color=False, do_scalar=True, color_input=False)
+    node(type="mix", name="x4", input1="m4c", input2="m4d", value=0.4, mode=1)
+    mapper("m4", texture="n_clouds_bl", texco="orco", scale=(1.5, 1.5, 1.5), bump_strength=3.0)
+    mapper("m4c", texture="n_wood_rings", texco="orco")
+    mapper("m4d", texture="n_clouds_f3", texco="orco", scale=(2.0, 2.0, 2.0))
+    y.createMaterial("b4")
+    sd("b5", color=(0.9, 0.8, 0.6, 1.0), bump_shader="l5b", diffuse_shader="x5")
+    layer("l5b", "m5", do_color=False, do_scalar=True, color_input=False)
+    node(type="mix", name="x5", input1="m5c", input2="m5d", value=0.5, mode=0)
+    mapper("m5", texture="n_marble_flat", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0), bump_strength=2.0)
+    mapper("m5c", texture="n_wood_saw", texco="uv", scale=(3.0, 3.0, 1.0))
+    mapper("m5d", texture="n_clouds_f4", texco="uv", scale=(4.0, 4.0, 1.0))
     y.createMaterial("b5")
 
 
@@ -624,6 +688,8 @@ EXACT["tex_dl_mask"] = lambda: textured_scene(96, 54, 2, variant="mask", raydept
 EXACT["tex_pt_mask_norr"] = lambda: textured_scene(96, 54, 4, variant="mask", integrator="pathtracing", raydepth=4)
 EXACT["tex_dl_procedural"] = lambda: textured_scene(96, 54, 2, variant="procedural")
 EXACT["tex_pt_procedural_norr"] = lambda: textured_scene(96, 54, 4, variant="procedural", integrator="pathtracing")
+EXACT["tex_dl_noise"] = lambda: textured_scene(96, 54, 2, variant="noise")
+EXACT["tex_pt_noise_norr"] = lambda: textured_scene(96, 54, 4, variant="noise", integrator="pathtracing")
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)
 

@@ -80,6 +80,20 @@ def test_descriptor_of_ies_lights_and_procedural_textures():
     assert (capi.TEX_BLEND, capi.TEXBLEND["radial"], 0) in kinds and (capi.TEX_BLEND, capi.TEXBLEND["diag"], 1) in kinds
     cube = [t for t in tex if t.type == capi.TEX_RGB_CUBE and t.adj_clamp]
     assert len(cube) == 1 and abs(cube[0].adj_hue - 25.0 / 60.0) < 1e-6 and abs(cube[0].adj_contrast - 1.4) < 1e-6
+    # clouds / marble / wood: the constructors' members, the basis newNoise__ would build, and the lattice tables attached as data
+    y = pc.EXACT["tex_dl_noise"]()
+    d, keep = y.scene_desc()
+    tex = [d.textures[i] for i in range(d.n_textures)]
+    assert sorted(t.noise_type for t in tex if t.type >= capi.TEX_CLOUDS) == [0, 0, 1, 1, 2, 2, 2, 3, 4, 5, 6, 7, 8, 9]
+    marble = [t for t in tex if t.type == capi.TEX_MARBLE and t.noise_type == capi.NOISE["blender"]][0]
+    assert abs(marble.sharpness - 1.0 / 3.0) < 1e-7 and marble.noise_depth == 3 and marble.turbulence == 4.0 and marble.wave_shape == 0
+    assert [t.sharpness for t in tex if t.type == capi.TEX_MARBLE and t.wave_shape == 2] == [1.0]   # "sharpness" <= 1 is ignored (texture_basic.cc:183)
+    assert sorted(t.clouds_bias for t in tex if t.type == capi.TEX_CLOUDS and t.noise_type == 2) == [1, 2]
+    assert sum(t.wood_rings for t in tex) == 1
+    assert d.noise_tables_bytes == capi.NOISE_TABLES_BYTES == 13340
+    blob = np.frombuffer(ctypes.string_at(d.noise_tables, d.noise_tables_bytes), np.uint8)
+    hash_tab = blob[4 * (768 + 768 + 1542):][:512]
+    assert sorted(hash_tab[:256].tolist()) == list(range(256)) and np.array_equal(hash_tab[:256], hash_tab[256:])   # a permutation, stored twice
     y = pc.EXACT["tex_dl_mask"]()
     d, keep = y.scene_desc()
     masks = [d.materials[i] for i in range(d.n_materials) if d.materials[i].type == capi.MAT_MASK]
