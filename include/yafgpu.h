@@ -126,8 +126,16 @@ typedef enum yafgpu_texture_type
 	 * a colour ramp (use_color_ramp) is refused */
 	YAFGPU_TEX_CLOUDS = 3,   /* "clouds" texture_basic.cc:96-171 */
 	YAFGPU_TEX_MARBLE = 4,   /* "marble" texture_basic.cc:177-250 */
-	YAFGPU_TEX_WOOD = 5      /* "wood"   texture_basic.cc:257-343 */
+	YAFGPU_TEX_WOOD = 5,     /* "wood"   texture_basic.cc:257-343 */
+	YAFGPU_TEX_VORONOI = 6,  /* "voronoi" texture_basic.cc:391-503: weighted feature distances, seven metrics, cell colours */
+	YAFGPU_TEX_MUSGRAVE = 7, /* "musgrave" texture_basic.cc:509-596 over the five fractals of noise_generator.cc:631-784 */
+	YAFGPU_TEX_DISTORTED_NOISE = 8 /* "distorted_noise" texture_basic.cc:602-673 */
 } yafgpu_texture_type;
+/* VoronoiNoiseGenerator::DMetricType ("distance_metric": squared, manhattan, chebychev, minkovsky_half, minkovsky_four, minkovsky; else real) */
+enum { YAFGPU_DIST_REAL = 0, YAFGPU_DIST_SQUARED = 1, YAFGPU_DIST_MANHATTAN = 2, YAFGPU_DIST_CHEBYCHEV = 3, YAFGPU_DIST_MINKOVSKY_HALF = 4,
+       YAFGPU_DIST_MINKOVSKY_FOUR = 5, YAFGPU_DIST_MINKOVSKY = 6 };
+/* "musgrave_type": multifractal, heteroterrain, hybridmf, ridgedmf; anything else = fBm */
+enum { YAFGPU_MUSGRAVE_FBM = 0, YAFGPU_MUSGRAVE_MULTIFRACTAL = 1, YAFGPU_MUSGRAVE_HETEROTERRAIN = 2, YAFGPU_MUSGRAVE_HYBRIDMF = 3, YAFGPU_MUSGRAVE_RIDGEDMF = 4 };
 /* what newNoise__(noise_type) constructs, texture_basic.cc:24-52: "blender", "stdperlin", "voronoi_f1|f2|f3|f4|f2f1|crackle" (DistReal metric), "cellnoise"; anything else = new Perlin */
 enum { YAFGPU_NOISE_NEWPERLIN = 0, YAFGPU_NOISE_STDPERLIN = 1, YAFGPU_NOISE_BLENDER = 2, YAFGPU_NOISE_VORONOI_F1 = 3, YAFGPU_NOISE_VORONOI_F2 = 4, YAFGPU_NOISE_VORONOI_F3 = 5,
        YAFGPU_NOISE_VORONOI_F4 = 6, YAFGPU_NOISE_VORONOI_F2F1 = 7, YAFGPU_NOISE_VORONOI_CRACKLE = 8, YAFGPU_NOISE_CELL = 9 };
@@ -172,6 +180,18 @@ typedef struct yafgpu_texture
 	float sharpness;         /* marble: sharpness_ as the constructor stores it (1, or 1 / "sharpness" when that is > 1) */
 	int32_t wave_shape;      /* marble, wood: YAFGPU_WAVE_* */
 	int32_t wood_rings;      /* wood: "wood_type" == "rings" */
+	/* voronoi (noise_size = "size"; color1/color2 are read by the factory and never used) */
+	float vor_weight[4];     /* "weight1" .. "weight4" */
+	float mk_exponent;       /* "mk_exponent" */
+	float intensity_scale;   /* iscale_ of the constructed texture: musgrave = "intensity"; voronoi = "intensity" / (|w1|+|w2|+|w3|+|w4|), float, summed left to right (0 when all weights are 0) */
+	int32_t distance_metric; /* YAFGPU_DIST_* */
+	int32_t color_type;      /* the factory's "Rgbype" string (sic): 0 intensity, 1 col1, 2 col2, 3 col3 */
+	/* musgrave (noise_type, noise_size, color1/2 as above) */
+	int32_t musgrave_type;   /* YAFGPU_MUSGRAVE_* */
+	float mus_h, mus_lacunarity, mus_octaves, mus_offset, mus_gain; /* "H", "lacunarity", "octaves", "offset", "gain" */
+	/* distorted_noise: noise_type = "noise_type1" (the distortion), noise_type2 = "noise_type2" (the distorted basis) */
+	float distort;           /* "distort" */
+	int32_t noise_type2;
 } yafgpu_texture;
 
 typedef enum yafgpu_node_type

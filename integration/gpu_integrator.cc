@@ -73,6 +73,11 @@
 
 BEGIN_YAFARAY
 
+// the Voronoi distance metrics have external linkage but no declaration in the reference's headers (noise_generator.cc:377-409)
+float distRealF__(float, float, float, float); float distSquaredF__(float, float, float, float); float distChebychevF__(float, float, float, float);
+float distMinkovskyHf__(float, float, float, float); float distMinkovsky4F__(float, float, float, float); float distMinkovskyF__(float, float, float, float);
+
+
 namespace {
 
 // ---- what the wrapped factories remember ----------------------------------------------------------------------------
@@ -146,23 +151,73 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 		pool.tex_index[t] = index;
 		return true;
 	}
+	auto noiseBasis = [&](const NoiseGenerator *ng, int &out) -> bool
+	{	// the basis is recognised by the dynamic type newNoise__ (texture_basic.cc:24-52) constructed
+		if(dynamic_cast<const StdPerlinNoiseGenerator *>(ng)) out = YAFGPU_NOISE_STDPERLIN;
+		else if(dynamic_cast<const BlenderNoiseGenerator *>(ng)) out = YAFGPU_NOISE_BLENDER;
+		else if(dynamic_cast<const CellNoiseGenerator *>(ng)) out = YAFGPU_NOISE_CELL;
+		else if(const VoronoiNoiseGenerator *vg = dynamic_cast<const VoronoiNoiseGenerator *>(ng))
+		{
+			if(vg->distfunc_2_ != distRealF__) { err = "a Voronoi noise basis with a distance metric other than the factory's default is not implemented on the device"; return false; }
+			out = YAFGPU_NOISE_VORONOI_F1 + (int)vg->v_type_;   // Vf1, Vf2, Vf3, Vf4, Vf2F1, VCrackle: the enumerator order of YAFGPU_NOISE_VORONOI_*
+		}
+		else if(dynamic_cast<const NewPerlinNoiseGenerator *>(ng)) out = YAFGPU_NOISE_NEWPERLIN;
+		else { err = "unknown noise basis"; return false; }
+		return true;
+	};
+	auto adjustments = [&]()
+	{
+		r.adj_intensity = t->adj_intensity_; r.adj_contrast = t->adj_contrast_; r.adj_saturation = t->adj_saturation_; r.adj_hue = t->adj_hue_;
+		r.adj_mult_red = t->adj_mult_factor_red_; r.adj_mult_green = t->adj_mult_factor_green_; r.adj_mult_blue = t->adj_mult_factor_blue_;
+		r.adj_clamp = t->adj_clamp_;
+	};
+	auto done = [&]() { index = (int)pool.textures.size(); pool.textures.push_back(r); pool.tex_index[t] = index; return true; };
+	const VoronoiTexture *vot = dynamic_cast<const VoronoiTexture *>(t);
+	const MusgraveTexture *mut = dynamic_cast<const MusgraveTexture *>(t);
+	const DistortedNoiseTexture *dnt = dynamic_cast<const DistortedNoiseTexture *>(t);
+	if(vot || mut || dnt)
+	{	// texture_basic.cc:391-673: the members of the constructed objects
+		if(t->color_ramp_) { err = "a procedural texture with a colour ramp is not implemented on the device"; return false; }
+		if(vot)
+		{
+			r.type = YAFGPU_TEX_VORONOI; r.noise_size = vot->size_; r.color_type = vot->coltype_; r.intensity_scale = vot->iscale_; r.mk_exponent = vot->v_gen_.mk_exp_;
+			r.vor_weight[0] = vot->w_1_; r.vor_weight[1] = vot->w_2_; r.vor_weight[2] = vot->w_3_; r.vor_weight[3] = vot->w_4_;
+			// setDistM (noise_generator.cc:487-521) only swaps the function pointer (and maps "manhattan" to the squared metric): read the metric off it
+			const DistMetricFunc_t fn = vot->v_gen_.distfunc_2_;
+			r.distance_metric = fn == distSquaredF__ ? YAFGPU_DIST_SQUARED : fn == distChebychevF__ ? YAFGPU_DIST_CHEBYCHEV : fn == distMinkovskyHf__ ? YAFGPU_DIST_MINKOVSKY_HALF :
+			                    fn == distMinkovsky4F__ ? YAFGPU_DIST_MINKOVSKY_FOUR : fn == distMinkovskyF__ ? YAFGPU_DIST_MINKOVSKY : YAFGPU_DIST_REAL;
+		}
+		else if(mut)
+		{
+			r.type = YAFGPU_TEX_MUSGRAVE; r.noise_size = mut->size_; r.intensity_scale = mut->iscale_;
+			if(!noiseBasis(mut->n_gen_, r.noise_type)) return false;
+			r.color1[0] = mut->color_1_.r_; r.color1[1] = mut->color_1_.g_; r.color1[2] = mut->color_1_.b_;
+			r.color2[0] = mut->color_2_.r_; r.color2[1] = mut->color_2_.g_; r.color2[2] = mut->color_2_.b_;
+			r.mus_offset = 1.f; r.mus_gain = 1.f;
+			if(const MFractalMusgrave *m = dynamic_cast<const MFractalMusgrave *>(mut->m_gen_)) { r.musgrave_type = YAFGPU_MUSGRAVE_MULTIFRACTAL; r.mus_h = m->h_; r.mus_lacunarity = m->lacunarity_; r.mus_octaves = m->octaves_; }
+			else if(const HeteroTerrainMusgrave *m = dynamic_cast<const HeteroTerrainMusgrave *>(mut->m_gen_)) { r.musgrave_type = YAFGPU_MUSGRAVE_HETEROTERRAIN; r.mus_h = m->h_; r.mus_lacunarity = m->lacunarity_; r.mus_octaves = m->octaves_; r.mus_offset = m->offset_; }
+			else if(const HybridMFractalMusgrave *m = dynamic_cast<const HybridMFractalMusgrave *>(mut->m_gen_)) { r.musgrave_type = YAFGPU_MUSGRAVE_HYBRIDMF; r.mus_h = m->h_; r.mus_lacunarity = m->lacunarity_; r.mus_octaves = m->octaves_; r.mus_offset = m->offset_; r.mus_gain = m->gain_; }
+			else if(const RidgedMFractalMusgrave *m = dynamic_cast<const RidgedMFractalMusgrave *>(mut->m_gen_)) { r.musgrave_type = YAFGPU_MUSGRAVE_RIDGEDMF; r.mus_h = m->h_; r.mus_lacunarity = m->lacunarity_; r.mus_octaves = m->octaves_; r.mus_offset = m->offset_; r.mus_gain = m->gain_; }
+			else if(const FBmMusgrave *m = dynamic_cast<const FBmMusgrave *>(mut->m_gen_)) { r.musgrave_type = YAFGPU_MUSGRAVE_FBM; r.mus_h = m->h_; r.mus_lacunarity = m->lacunarity_; r.mus_octaves = m->octaves_; }
+			else { err = "unknown Musgrave generator"; return false; }
+		}
+		else
+		{
+			r.type = YAFGPU_TEX_DISTORTED_NOISE; r.noise_size = dnt->size_; r.distort = dnt->distort_;
+			if(!noiseBasis(dnt->n_gen_1_, r.noise_type) || !noiseBasis(dnt->n_gen_2_, r.noise_type2)) return false;
+			r.color1[0] = dnt->color_1_.r_; r.color1[1] = dnt->color_1_.g_; r.color1[2] = dnt->color_1_.b_;
+			r.color2[0] = dnt->color_2_.r_; r.color2[1] = dnt->color_2_.g_; r.color2[2] = dnt->color_2_.b_;
+		}
+		adjustments();
+		return done();
+	}
 	const CloudsTexture *clt = dynamic_cast<const CloudsTexture *>(t);
 	const MarbleTexture *mbt = dynamic_cast<const MarbleTexture *>(t);
 	const WoodTexture *wdt = dynamic_cast<const WoodTexture *>(t);
 	if(clt || mbt || wdt)
 	{	// texture_basic.cc:96-343: the members the constructors left behind; the basis is recognised by the dynamic type of n_gen_ (newNoise__ :24-52)
 		if(t->color_ramp_) { err = "a clouds / marble / wood texture with a colour ramp is not implemented on the device"; return false; }
-		const NoiseGenerator *ng = clt ? clt->n_gen_ : mbt ? mbt->n_gen_ : wdt->n_gen_;
-		if(dynamic_cast<const StdPerlinNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_STDPERLIN;
-		else if(dynamic_cast<const BlenderNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_BLENDER;
-		else if(dynamic_cast<const CellNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_CELL;
-		else if(const VoronoiNoiseGenerator *vg = dynamic_cast<const VoronoiNoiseGenerator *>(ng))
-		{
-			if(vg->dm_type_ != VoronoiNoiseGenerator::DistReal) { err = "a Voronoi noise basis with a distance metric other than the factory's default is not implemented on the device"; return false; }
-			r.noise_type = YAFGPU_NOISE_VORONOI_F1 + (int)vg->v_type_;   // Vf1, Vf2, Vf3, Vf4, Vf2F1, VCrackle: the enumerator order of YAFGPU_NOISE_VORONOI_*
-		}
-		else if(dynamic_cast<const NewPerlinNoiseGenerator *>(ng)) r.noise_type = YAFGPU_NOISE_NEWPERLIN;
-		else { err = "unknown noise basis"; return false; }
+		if(!noiseBasis(clt ? clt->n_gen_ : mbt ? mbt->n_gen_ : wdt->n_gen_, r.noise_type)) return false;
 		const Rgb c1 = clt ? clt->color_1_ : mbt ? mbt->color_1_ : wdt->color_1_, c2 = clt ? clt->color_2_ : mbt ? mbt->color_2_ : wdt->color_2_;
 		r.color1[0] = c1.r_; r.color1[1] = c1.g_; r.color1[2] = c1.b_; r.color2[0] = c2.r_; r.color2[1] = c2.g_; r.color2[2] = c2.b_;
 		r.sharpness = 1.f;
@@ -177,16 +232,11 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 			r.type = YAFGPU_TEX_WOOD; r.noise_depth = wdt->octaves_; r.noise_size = wdt->size_; r.noise_hard = wdt->hard_;
 			r.turbulence = wdt->turb_; r.wave_shape = (int)wdt->wshape_; r.wood_rings = wdt->rings_;
 		}
-		r.adj_intensity = t->adj_intensity_; r.adj_contrast = t->adj_contrast_; r.adj_saturation = t->adj_saturation_; r.adj_hue = t->adj_hue_;
-		r.adj_mult_red = t->adj_mult_factor_red_; r.adj_mult_green = t->adj_mult_factor_green_; r.adj_mult_blue = t->adj_mult_factor_blue_;
-		r.adj_clamp = t->adj_clamp_;
-		index = (int)pool.textures.size();
-		pool.textures.push_back(r);
-		pool.tex_index[t] = index;
-		return true;
+		adjustments();
+		return done();
 	}
 	const ImageTexture *it = dynamic_cast<const ImageTexture *>(t);
-	if(!it) { err = "this procedural texture type is not implemented on the device (image, blend, rgb_cube, clouds, marble and wood are)"; return false; }
+	if(!it) { err = "this procedural texture type is not implemented on the device (image, blend, rgb_cube, clouds, marble, wood, voronoi, musgrave and distorted_noise are)"; return false; }
 	r.type = YAFGPU_TEX_IMAGE;
 	ImageHandler *ih = it->image_;
 	r.width = ih->getWidth(); r.height = ih->getHeight();

@@ -28,7 +28,9 @@ INT_DIRECTLIGHT, INT_PATHTRACING = range(2)
 TRACE_CLOSEST, TRACE_SHADOW, TRACE_SHADOW_TRANSP = range(3)
 TRACE_STATIC_MAX_RAYS = 65536  # YAFGPU_TRACE_STATIC_MAX_RAYS
 FLAG_COUNT_TRAVERSAL, FLAG_TIME_STAGES, FLAG_SHARE_DEVICE = 1, 2, 4
-TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD = range(6)
+TEX_IMAGE, TEX_BLEND, TEX_RGB_CUBE, TEX_CLOUDS, TEX_MARBLE, TEX_WOOD, TEX_VORONOI, TEX_MUSGRAVE, TEX_DISTORTED_NOISE = range(9)
+DIST_METRIC = {"squared": 1, "manhattan": 2, "chebychev": 3, "minkovsky_half": 4, "minkovsky_four": 5, "minkovsky": 6}
+MUSGRAVE = {"multifractal": 1, "heteroterrain": 2, "hybridmf": 3, "ridgedmf": 4}
 NOISE = {"stdperlin": 1, "blender": 2, "voronoi_f1": 3, "voronoi_f2": 4, "voronoi_f3": 5, "voronoi_f4": 6, "voronoi_f2f1": 7, "voronoi_crackle": 8, "cellnoise": 9}
 NOISE_TABLES_BYTES = 13340
 TEXBLEND = {"lin": 0, "quad": 1, "ease": 2, "diag": 3, "sphere": 4, "halo": 5, "quad_sphere": 5, "radial": 6}
@@ -108,7 +110,10 @@ class Texture(C.Structure):
                 ("adj_saturation", f32), ("adj_hue", f32), ("adj_mult_red", f32), ("adj_mult_green", f32),
                 ("adj_mult_blue", f32), ("adj_clamp", i32), ("blend_type", i32), ("use_flip_axis", i32),
                 ("noise_type", i32), ("noise_depth", i32), ("noise_size", f32), ("noise_hard", i32), ("color1", f32 * 3), ("color2", f32 * 3),
-                ("clouds_bias", i32), ("turbulence", f32), ("sharpness", f32), ("wave_shape", i32), ("wood_rings", i32)]
+                ("clouds_bias", i32), ("turbulence", f32), ("sharpness", f32), ("wave_shape", i32), ("wood_rings", i32),
+                ("vor_weight", f32 * 4), ("mk_exponent", f32), ("intensity_scale", f32), ("distance_metric", i32), ("color_type", i32),
+                ("musgrave_type", i32), ("mus_h", f32), ("mus_lacunarity", f32), ("mus_octaves", f32), ("mus_offset", f32), ("mus_gain", f32),
+                ("distort", f32), ("noise_type2", i32)]
 
 
 class ShaderNode(C.Structure):

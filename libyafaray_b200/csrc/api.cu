@@ -449,11 +449,11 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, upload(c->d_objects, objs.data(), objs.size(), st));
 	YG_CUDA(c, upload(c->d_mats, c->h_mats.data(), c->h_mats.size(), st));
 	bool any_noise = false;
-	for(const TexDev &t : h_tex) any_noise = any_noise || t.type == YAFGPU_TEX_CLOUDS || t.type == YAFGPU_TEX_MARBLE || t.type == YAFGPU_TEX_WOOD;
+	for(const TexDev &t : h_tex) any_noise = any_noise || t.type >= YAFGPU_TEX_CLOUDS;
 	if(any_noise)
 	{
 		if(!desc->noise_tables || desc->noise_tables_bytes != YAFGPU_NOISE_TABLES_BYTES)
-			return setErr(c, YAFGPU_ERR_INVALID, "a clouds / marble / wood texture is present but yafgpu_scene_desc.noise_tables (13340 bytes) is missing");
+			return setErr(c, YAFGPU_ERR_INVALID, "a noise-based procedural texture is present but yafgpu_scene_desc.noise_tables (13340 bytes) is missing");
 		YG_CUDA(c, upload(c->d_noise, (const NoiseTables *)desc->noise_tables, 1, st));
 	}
 	for(size_t i = 0; i < h_tex.size(); ++i)

@@ -215,8 +215,30 @@ inline bool prepTexture(const yafgpu_texture &t, TexDev &d, std::string &err)
 		d.adj_intensity = d.adj_contrast = d.adj_saturation = 1.f; d.adj_mult[0] = d.adj_mult[1] = d.adj_mult[2] = 1.f;
 		return true;
 	}
+	auto noiseOk = [](int n) { return n >= YAFGPU_NOISE_NEWPERLIN && n <= YAFGPU_NOISE_CELL; };
 	const bool noise_tex = t.type == YAFGPU_TEX_CLOUDS || t.type == YAFGPU_TEX_MARBLE || t.type == YAFGPU_TEX_WOOD;
-	if(noise_tex)
+	if(t.type == YAFGPU_TEX_VORONOI)
+	{	// VoronoiTexture::VoronoiTexture texture_basic.cc:391-420
+		if(t.distance_metric < YAFGPU_DIST_REAL || t.distance_metric > YAFGPU_DIST_MINKOVSKY || t.color_type < 0 || t.color_type > 3) { err = "voronoi texture: distance_metric / colour type"; return false; }
+		d.size = t.noise_size; d.mk_exp = t.mk_exponent; d.dist_metric = t.distance_metric; d.color_type = t.color_type;
+		for(int k = 0; k < 4; ++k) { d.vw[k] = t.vor_weight[k]; d.vaw[k] = std::fabs(t.vor_weight[k]); }
+		d.iscale = t.intensity_scale;
+	}
+	else if(t.type == YAFGPU_TEX_MUSGRAVE)
+	{	// MusgraveTexture::MusgraveTexture texture_basic.cc:509-527
+		if(!noiseOk(t.noise_type) || t.musgrave_type < YAFGPU_MUSGRAVE_FBM || t.musgrave_type > YAFGPU_MUSGRAVE_RIDGEDMF) { err = "musgrave texture: noise_type / musgrave_type"; return false; }
+		if(!(t.mus_octaves >= 0.f && t.mus_octaves <= 64.f)) { err = "musgrave texture: octaves must be 0..64"; return false; }
+		d.noise_type = t.noise_type; d.mus_type = t.musgrave_type; d.size = t.noise_size; d.iscale = t.intensity_scale;
+		d.mus_h = t.mus_h; d.mus_lac = t.mus_lacunarity; d.mus_oct = t.mus_octaves; d.mus_offset = t.mus_offset; d.mus_gain = t.mus_gain;
+		for(int k = 0; k < 3; ++k) { d.color1[k] = t.color1[k]; d.color2[k] = t.color2[k]; }
+	}
+	else if(t.type == YAFGPU_TEX_DISTORTED_NOISE)
+	{	// DistortedNoiseTexture::DistortedNoiseTexture texture_basic.cc:602-610
+		if(!noiseOk(t.noise_type) || !noiseOk(t.noise_type2)) { err = "distorted_noise texture: noise_type1 / noise_type2"; return false; }
+		d.noise_type = t.noise_type; d.noise_type2 = t.noise_type2; d.distort = t.distort; d.size = t.noise_size;
+		for(int k = 0; k < 3; ++k) { d.color1[k] = t.color1[k]; d.color2[k] = t.color2[k]; }
+	}
+	else if(noise_tex)
 	{	// CloudsTexture / MarbleTexture / WoodTexture after their constructors (texture_basic.cc:96-107,177-188,257-266)
 		if(t.noise_type < YAFGPU_NOISE_NEWPERLIN || t.noise_type > YAFGPU_NOISE_CELL) { err = "noise texture: noise_type"; return false; }
 		if(t.noise_depth < 0 || t.noise_depth > 29) { err = "noise texture: depth must be 0..29 (turbulence__ shifts 1 << (depth + 1))"; return false; }
@@ -226,8 +248,7 @@ inline bool prepTexture(const yafgpu_texture &t, TexDev &d, std::string &err)
 		d.shape = t.wave_shape; d.rings = t.wood_rings ? 1 : 0;
 		if(d.bias < 0 || d.bias > 2 || d.shape < YAFGPU_WAVE_SIN || d.shape > YAFGPU_WAVE_TRI) { err = "noise texture: bias / shape"; return false; }
 	}
-	else
-	if(t.type != YAFGPU_TEX_IMAGE && t.type != YAFGPU_TEX_RGB_CUBE) { err = "texture type " + std::to_string(t.type) + " is not implemented on the device"; return false; }
+	else if(t.type != YAFGPU_TEX_IMAGE && t.type != YAFGPU_TEX_RGB_CUBE) { err = "texture type " + std::to_string(t.type) + " is not implemented on the device"; return false; }
 	if(t.type == YAFGPU_TEX_IMAGE)
 	if(!t.rgba || t.width <= 0 || t.height <= 0) { err = "image texture without texels"; return false; }
 	if(t.type == YAFGPU_TEX_IMAGE && (t.interpolate < YAFGPU_TEXINTERP_NONE || t.interpolate > YAFGPU_TEXINTERP_BICUBIC)) { err = "texture interpolation (mipmap_trilinear / mipmap_ewa need ray differentials) is not implemented on the device"; return false; }

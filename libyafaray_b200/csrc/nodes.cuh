@@ -128,7 +128,9 @@ YG_D void hsvToRgb(Rgba4 &c, float h, float s, float v)
 }
 YG_D void clampRgb0(Rgba4 &c) { if(c.r < 0.f) c.r = 0.f; if(c.g < 0.f) c.g = 0.f; if(c.b < 0.f) c.b = 0.f; }
 
-// Texture::applyAdjustments texture.h:203-258
+// Texture::applyColorAdjustments texture.h:226-252: channel factors, saturation and hue (the procedural textures apply intensity / contrast to their scalar instead)
+YG_D Rgba4 texAdjustColor(const TexDev &t, Rgba4 c);
+// Texture::applyAdjustments texture.h:203-258 = applyColorAdjustments(applyIntensityContrastAdjustments(c))
 YG_D Rgba4 texAdjust(const TexDev &t, Rgba4 c)
 {
 	if(!t.adj_set) return c;
@@ -140,6 +142,12 @@ YG_D Rgba4 texAdjust(const TexDev &t, Rgba4 c)
 		ret.b = (c.b - 0.5f) * t.adj_contrast + t.adj_intensity - 0.5f;
 	}
 	if(t.adj_clamp) clampRgb0(ret);
+	return texAdjustColor(t, ret);
+}
+YG_D Rgba4 texAdjustColor(const TexDev &t, Rgba4 c)
+{
+	if(!t.adj_set) return c;
+	Rgba4 ret = c;
 	if(t.adj_mult[0] != 1.f) ret.r *= t.adj_mult[0];
 	if(t.adj_mult[1] != 1.f) ret.g *= t.adj_mult[1];
 	if(t.adj_mult[2] != 1.f) ret.b *= t.adj_mult[2];
@@ -446,9 +454,167 @@ YG_D float noiseWave(int shape, float w)
 		default: return 0.5f + 0.5f * fSin(w);
 	}
 }
+// VoronoiNoiseGenerator distance metrics, noise_generator.cc:377-409; setDistM (:487-521) maps DistManhattan to the SQUARED metric, as the reference does
+YG_D float voronoiDistance(int metric, float x, float y, float z, float e)
+{
+	switch(metric)
+	{
+		case YAFGPU_DIST_SQUARED: case YAFGPU_DIST_MANHATTAN: return x * x + y * y + z * z;
+		case YAFGPU_DIST_CHEBYCHEV: { x = fabsf(x); y = fabsf(y); z = fabsf(z); const float t = (x > y) ? x : y; return (z > t) ? z : t; }
+		case YAFGPU_DIST_MINKOVSKY_HALF: { const float d = fSqrt(fabsf(x)) + fSqrt(fabsf(y)) + fSqrt(fabsf(z)); return d * d; }
+		case YAFGPU_DIST_MINKOVSKY_FOUR: { x *= x; y *= y; z *= z; return fSqrt(fSqrt(x * x + y * y + z * z)); }
+		case YAFGPU_DIST_MINKOVSKY: return fPow(fPow(fabsf(x), e) + fPow(fabsf(y), e) + fPow(fabsf(z), e), 1.f / e);
+		default: return fSqrt(x * x + y * y + z * z);
+	}
+}
+// VoronoiNoiseGenerator::getFeatures noise_generator.cc:531-577 with the feature points kept
+YG_DN void voronoiFeatures(const NoiseTables &nt, int metric, float e, V3 pt, float *da, V3 *pa)
+{
+	const float x = pt.x, y = pt.y, z = pt.z;
+	const int xi = (int)floorf(x), yi = (int)floorf(y), zi = (int)floorf(z);
+	da[0] = da[1] = da[2] = da[3] = 1e10f;
+	pa[0] = pa[1] = pa[2] = pa[3] = mk(0.f);
+	const unsigned char *hs = nt.hash;
+	for(int xx = xi - 1; xx <= xi + 1; ++xx)
+		for(int yy = yi - 1; yy <= yi + 1; ++yy)
+			for(int zz = zi - 1; zz <= zi + 1; ++zz)
+			{
+				const float *p = nt.hashpntf + 3 * hs[(hs[(hs[zz & 255] + yy) & 255] + xx) & 255];
+				const V3 f = mk(p[0] + (float)xx, p[1] + (float)yy, p[2] + (float)zz);
+				const float d = voronoiDistance(metric, x - f.x, y - f.y, z - f.z, e);
+				if(d < da[0]) { da[3] = da[2]; da[2] = da[1]; da[1] = da[0]; da[0] = d; pa[3] = pa[2]; pa[2] = pa[1]; pa[1] = pa[0]; pa[0] = f; }
+				else if(d < da[1]) { da[3] = da[2]; da[2] = da[1]; da[1] = d; pa[3] = pa[2]; pa[2] = pa[1]; pa[1] = f; }
+				else if(d < da[2]) { da[3] = da[2]; da[2] = d; pa[3] = pa[2]; pa[2] = f; }
+				else if(d < da[3]) { da[3] = d; pa[3] = f; }
+			}
+}
+// cellNoiseColor__ noise_generator.cc:789-796
+YG_D Rgba4 cellNoiseColor(const NoiseTables &nt, V3 pt)
+{
+	const int xi = (int)floorf(pt.x), yi = (int)floorf(pt.y), zi = (int)floorf(pt.z);
+	const unsigned char *hs = nt.hash;
+	const float *cl = nt.hashpntf + 3 * hs[(hs[(hs[zi & 255] + yi) & 255] + xi) & 255];
+	return mk4(cl[0], cl[1], cl[2], 1.f);
+}
+// VoronoiTexture::getFloat / getColor texture_basic.cc:422-454 (no colour ramp)
+YG_D float voronoiIntensity(const TexDev &t, const float *da)
+{
+	return t.iscale * fabsf(t.vw[0] * da[0] + t.vw[1] * da[1] + t.vw[2] * da[2] + t.vw[3] * da[3]);
+}
+YG_D Rgba4 voronoiTexColor(const TexDev &t, V3 p)
+{
+	float da[4]; V3 pa[4];
+	voronoiFeatures(*t.noise, t.dist_metric, t.mk_exp, p * t.size, da, pa);
+	const float inte = voronoiIntensity(t, da);
+	if(!t.color_type) return texAdjustColor(t, mk4(inte, inte, inte, inte));
+	Rgba4 col = mk4(0.f, 0.f, 0.f, 0.f);   // Rgba(0.0): alpha 0 as well
+	for(int k = 0; k < 4; ++k) col = col + t.vaw[k] * cellNoiseColor(*t.noise, pa[k]);
+	if(t.color_type >= 2)
+	{
+		float t1 = (float)((double)(da[1] - da[0]) * 10.0);
+		if(t1 > 1) t1 = 1;
+		if(t.color_type == 3) t1 *= inte; else t1 *= t.iscale;
+		col = t1 * col;
+	}
+	else col = t.iscale * col;
+	return texAdjust(t, col);
+}
+// getSignedNoise__ noise_generator.h:263-266
+YG_D float noiseSigned(const NoiseTables &nt, int type, V3 p) { return 2.f * noiseEval(nt, type, p) - 1.f; }
+// the five Musgrave fractals, noise_generator.cc:631-784
+YG_D float musgraveEval(const TexDev &t, V3 pt)
+{
+	const NoiseTables &nt = *t.noise;
+	const int ng = t.noise_type, octs = (int)t.mus_oct;
+	const float lac = t.mus_lac, offs = t.mus_offset, gain = t.mus_gain;
+	const float pw_hl = fPow(lac, -t.mus_h);
+	const float rmd = t.mus_oct - floorf(t.mus_oct);
+	V3 tp = pt;
+	switch(t.mus_type)
+	{
+		case YAFGPU_MUSGRAVE_MULTIFRACTAL:
+		{
+			float value = 1, pwr = 1;
+			for(int i = 0; i < octs; ++i) { value *= (pwr * noiseSigned(nt, ng, tp) + 1.f); pwr *= pw_hl; tp = tp * lac; }
+			if(rmd != 0.f) value *= (rmd * noiseSigned(nt, ng, tp) * pwr + 1.f);
+			return value;
+		}
+		case YAFGPU_MUSGRAVE_HETEROTERRAIN:
+		{
+			float pwr = pw_hl;
+			float value = offs + noiseSigned(nt, ng, tp);
+			tp = tp * lac;
+			for(int i = 1; i < octs; ++i)
+			{
+				const float increment = (noiseSigned(nt, ng, tp) + offs) * pwr * value;
+				value += increment; pwr *= pw_hl; tp = tp * lac;
+			}
+			if(rmd != 0.f) { const float increment = (noiseSigned(nt, ng, tp) + offs) * pwr * value; value += rmd * increment; }
+			return value;
+		}
+		case YAFGPU_MUSGRAVE_HYBRIDMF:
+		{
+			float pwr = pw_hl;
+			float result = noiseSigned(nt, ng, tp) + offs;
+			float weight = gain * result;
+			tp = tp * lac;
+			for(int i = 1; (weight > 0.001f) && (i < octs); ++i)
+			{
+				if(weight > 1.f) weight = 1.f;
+				const float signal = (noiseSigned(nt, ng, tp) + offs) * pwr;
+				pwr *= pw_hl;
+				result += weight * signal;
+				weight *= gain * signal;
+				tp = tp * lac;
+			}
+			if(rmd != 0.f) result += rmd * ((noiseSigned(nt, ng, tp) + offs) * pwr);
+			return result;
+		}
+		case YAFGPU_MUSGRAVE_RIDGEDMF:
+		{
+			float pwr = pw_hl;
+			float signal = offs - fabsf(noiseSigned(nt, ng, tp));
+			signal *= signal;
+			float result = signal, weight = 1.f;
+			for(int i = 1; i < octs; ++i)
+			{
+				tp = tp * lac;
+				weight = signal * gain;
+				if(weight > 1.f) weight = 1.f; else if(weight < 0.f) weight = 0.f;
+				signal = offs - fabsf(noiseSigned(nt, ng, tp));
+				signal *= signal;
+				signal *= weight;
+				result += signal * pwr;
+				pwr *= pw_hl;
+			}
+			return result;
+		}
+		default:
+		{	// fBm
+			float value = 0, pwr = 1;
+			for(int i = 0; i < octs; ++i) { value += noiseSigned(nt, ng, tp) * pwr; pwr *= pw_hl; tp = tp * lac; }
+			if(rmd != 0.f) value += rmd * noiseSigned(nt, ng, tp) * pwr;
+			return value;
+		}
+	}
+}
+
 // CloudsTexture / MarbleTexture / WoodTexture ::getFloat
 YG_D float noiseTexFloat(const TexDev &t, V3 p)
 {
+	if(t.type == YAFGPU_TEX_VORONOI)
+	{
+		float da[4]; V3 pa[4];
+		voronoiFeatures(*t.noise, t.dist_metric, t.mk_exp, p * t.size, da, pa);
+		return texAdjustFloat(t, voronoiIntensity(t, da));
+	}
+	if(t.type == YAFGPU_TEX_MUSGRAVE) return texAdjustFloat(t, t.iscale * musgraveEval(t, p * t.size));
+	if(t.type == YAFGPU_TEX_DISTORTED_NOISE)
+	{	// texture_basic.cc:626-633: a noise vector from the first basis displaces the lookup into the second
+		const V3 ofs = mk(13.5f, 13.5f, 13.5f), tp = p * t.size;
+		const V3 rv = mk(noiseSigned(*t.noise, t.noise_type, tp + ofs), noiseSigned(*t.noise, t.noise_type, tp), noiseSigned(*t.noise, t.noise_type, tp - ofs));
+		return texAdjustFloat(t, noiseSigned(*t.noise, t.noise_type2, tp + rv * t.distort));
+	}
 	if(t.type == YAFGPU_TEX_CLOUDS)
 	{
 		float v = noiseTurbulence(t, p);
@@ -507,9 +673,10 @@ YG_D Rgba4 texGetColor(const TexDev &t, V3 p)
 	if(t.type == YAFGPU_TEX_BLEND) { const float f = blendTexFloat(t, p); return mk4(f, f, f, 1.f); }
 	if(t.type >= YAFGPU_TEX_CLOUDS)
 	{	// color_1_ + getFloat(p) * (color_2_ - color_1_), then applyColorAdjustments (texture_basic.cc:122-126,208-212,293-297)
+		if(t.type == YAFGPU_TEX_VORONOI) return voronoiTexColor(t, p);
 		const float f = noiseTexFloat(t, p);
 		const Rgba4 c = mk4(t.color1[0] + f * (t.color2[0] - t.color1[0]), t.color1[1] + f * (t.color2[1] - t.color1[1]), t.color1[2] + f * (t.color2[2] - t.color1[2]), 1.f);
-		return texAdjust(t, c);
+		return texAdjustColor(t, c);
 	}
 	if(t.type == YAFGPU_TEX_RGB_CUBE)
 	{

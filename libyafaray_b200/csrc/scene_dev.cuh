@@ -121,6 +121,10 @@ struct TexDev
 	int adj_set, adj_clamp; float adj_intensity, adj_contrast, adj_saturation, adj_hue, adj_mult[3]; // adj_hue already / 60 (texture.h:154)
 	// clouds / marble / wood (texture_basic.cc:96-343)
 	const NoiseTables *noise; int noise_type, depth, hard, bias, shape, rings; float size, turb, sharpness, color1[3], color2[3];
+	// voronoi (texture_basic.cc:391-453): weights, their magnitudes, isc / sum of magnitudes; musgrave (:509-551); distorted noise (:602-633)
+	float vw[4], vaw[4], iscale, mk_exp; int dist_metric, color_type;
+	int mus_type; float mus_h, mus_lac, mus_oct, mus_offset, mus_gain;
+	float distort; int noise_type2;
 };
 
 // One shader node after its factory + configInputs; in1/in2/fac are stack indices (-1 = constant input)

@@ -477,6 +477,39 @@ class Interface:
             self._tex_index[name] = len(self._texs)
             self._texs.append(t)
             return self._tex_index[name]
+        if ttype in ("voronoi", "musgrave", "distorted_noise"):   # texture_basic.cc:456-503, 553-596, 635-673 (factories)
+            if g(p, "use_color_ramp", False):
+                raise NotImplementedError("%s texture with a colour ramp is not implemented on the device" % ttype)
+            t = capi.Texture()
+            t.type = {"voronoi": capi.TEX_VORONOI, "musgrave": capi.TEX_MUSGRAVE, "distorted_noise": capi.TEX_DISTORTED_NOISE}[ttype]
+            noise = lambda nt: capi.NOISE.get(nt, 3 if "voronoi" in nt else 0)
+            c1, c2 = g(p, "color1", (0.0, 0.0, 0.0)), g(p, "color2", (1.0, 1.0, 1.0))
+            for k in range(3):
+                t.color1[k], t.color2[k] = c1[k], c2[k]
+            t.noise_size = g(p, "size", 1.0)
+            if ttype == "voronoi":
+                for k, dflt in enumerate((1.0, 0.0, 0.0, 0.0)):
+                    t.vor_weight[k] = g(p, "weight%d" % (k + 1), dflt)
+                t.mk_exponent = g(p, "mk_exponent", 2.5)
+                aw = [np.float32(abs(np.float32(t.vor_weight[k]))) for k in range(4)]
+                s = np.float32(np.float32(np.float32(aw[0] + aw[1]) + aw[2]) + aw[3])     # iscale_ = aw_1_ + aw_2_ + aw_3_ + aw_4_ (texture_basic.cc:417-418)
+                t.intensity_scale = float(np.float32(g(p, "intensity", 1.0)) / s) if s != 0 else 0.0
+                t.distance_metric = capi.DIST_METRIC.get(g(p, "distance_metric", ""), 0)
+                t.color_type = {"col1": 1, "col2": 2, "col3": 3}.get(g(p, "Rgbype", ""), 0)   # the key the factory reads (texture_basic.cc:473)
+            elif ttype == "musgrave":
+                t.noise_type, t.musgrave_type = noise(g(p, "noise_type", "")), capi.MUSGRAVE.get(g(p, "musgrave_type", ""), 0)
+                t.mus_h, t.mus_lacunarity, t.mus_octaves = g(p, "H", 1.0), g(p, "lacunarity", 2.0), g(p, "octaves", 2.0)
+                t.mus_offset, t.mus_gain, t.intensity_scale = g(p, "offset", 1.0), g(p, "gain", 1.0), g(p, "intensity", 1.0)
+            else:
+                t.noise_type, t.noise_type2, t.distort = noise(g(p, "noise_type1", "")), noise(g(p, "noise_type2", "")), g(p, "distort", 1.0)
+            t.adj_intensity, t.adj_contrast = g(p, "adj_intensity", 1.0), g(p, "adj_contrast", 1.0)
+            t.adj_saturation, t.adj_hue = g(p, "adj_saturation", 1.0), float(np.float32(g(p, "adj_hue", 0.0)) / np.float32(60.0))
+            t.adj_mult_red, t.adj_mult_green, t.adj_mult_blue = g(p, "adj_mult_factor_red", 1.0), g(p, "adj_mult_factor_green", 1.0), g(p, "adj_mult_factor_blue", 1.0)
+            t.adj_clamp = int(g(p, "adj_clamp", False))
+            self._uses_noise = True
+            self._tex_index[name] = len(self._texs)
+            self._texs.append(t)
+            return self._tex_index[name]
         if ttype in ("clouds", "marble", "wood"):   # texture_basic.cc:96-171, 177-250, 257-343 (factories), newNoise__ :24-52
             if g(p, "use_color_ramp", False):
                 raise NotImplementedError("%s texture with a colour ramp is not implemented on the device" % ttype)

@@ -326,8 +326,8 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
     elif variant == "procedural":
         _textured_procedural_materials(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
-    elif variant == "noise":
-        _textured_noise_materials(y, sd, node, mapper, layer)
+    elif variant in ("noise", "noise2"):
+        (_textured_noise_materials if variant == "noise" else _textured_noise2_materials)(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     elif variant == "materials":
         _textured_other_materials(y, sd, node, mapper, layer)
@@ -403,7 +403,8 @@ def _textured_noise_materials(y, sd, node, mapper, layer):
     tex("n_marble_saw", "marble", noise_type="voronoi_f1", depth=1, size=3.0, turbulence=2.0, shape="saw", hard=True)
     tex("n_marble_tri", "marble", noise_type="voronoi_crackle", depth=2, size=2.0, turbulence=3.0, shape="tri", sharpness=0.5, adj_saturation=0.6, adj_hue=40.0)
     tex("n_marble_flat", "marble", noise_type="newperlin", turbulence=0.0, size=1.0, color1=(0.8, 0.5, 0.2, 1.0), color2=(0.1, 0.1, 0.4, 1.0))
-    tex("n_wood_bands", "wood", noise_type="stdperlin", depth=2, size=3.0, turbulence=2.0, color1=(0.45, 0.25, 0.1, 1.0), color2=(0.8, 0.6, 0.35, 1.0))
+    tex("n_wood_bands", "wood", noise_type="stdperlin", depth=2, size=3.0, turbulence=2.0, color1=(0.45, 0.25, 0.1, 1.0), color2=(0.8, 0.6, 0.35, 1.0),
+        adj_intensity=1.3, adj_contrast=1.2)   # read as a colour: intensity / contrast act on the scalar only, the colour gets applyColorAdjustments
     tex("n_wood_rings", "wood", noise_type="voronoi_f2f1", depth=1, size=2.0, turbulence=1.5, wood_type="rings", shape="tri")
     tex("n_wood_saw", "wood", noise_type="voronoi_f2", depth=0, size=1.5, turbulence=0.5, shape="saw", adj_mult_factor_red=1.2, adj_mult_factor_green=0.8)
     tex("n_clouds_f3", "clouds", noise_type="voronoi_f3", depth=1, size=3.0)
@@ -446,6 +447,69 @@ def _textured_noise_materials(y, sd, node, mapper, layer):
     mapper("m5", texture="n_marble_flat", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0), bump_strength=2.0)
     mapper("m5c", texture="n_wood_saw", texco="uv", scale=(3.0, 3.0, 1.0))
     mapper("m5d", texture="n_clouds_f4", texco="uv", scale=(4.0, 4.0, 1.0))
+    y.createMaterial("b5")
+
+
+def _textured_noise2_materials(y, sd, node, mapper, layer):
+    """The other noise-based procedurals: "voronoi" (all distance metrics, intensity and the three cell-colour modes), "musgrave" (five fractals, fractional
+    octaves) and "distorted_noise" (texture_basic.cc:391-673)."""
+    def tex(name, typ, **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ); _set_params(y, kw); y.createTexture(name)
+    tex("v_int", "voronoi", size=3.0, weight1=1.0, weight2=-0.5, intensity=1.5)
+    tex("v_col1", "voronoi", size=2.5, Rgbype="col1", weight1=0.6, weight2=0.3, weight3=0.2, weight4=0.1, distance_metric="squared")
+    tex("v_col2", "voronoi", size=2.0, Rgbype="col2", weight1=1.0, weight2=0.5, distance_metric="manhattan", adj_intensity=1.1, adj_contrast=1.3, adj_saturation=0.8)
+    tex("v_col3", "voronoi", size=3.5, Rgbype="col3", weight1=0.2, weight2=1.0, distance_metric="chebychev", intensity=2.0)
+    tex("v_mh", "voronoi", size=2.0, distance_metric="minkovsky_half", weight1=0.7, weight3=0.4)
+    tex("v_m4", "voronoi", size=2.0, distance_metric="minkovsky_four", weight2=1.0, weight1=0.0)
+    tex("v_mk", "voronoi", size=1.5, distance_metric="minkovsky", mk_exponent=3.5, weight1=1.0, weight4=0.5)
+    tex("m_fbm", "musgrave", noise_type="newperlin", musgrave_type="fBm", H=0.8, lacunarity=2.1, octaves=3.5, size=2.0, intensity=0.8,
+        color1=(0.1, 0.1, 0.5, 1.0), color2=(1.0, 0.8, 0.4, 1.0))
+    tex("m_mf", "musgrave", noise_type="blender", musgrave_type="multifractal", H=1.0, lacunarity=2.0, octaves=4.0, size=1.5)
+    tex("m_ht", "musgrave", noise_type="stdperlin", musgrave_type="heteroterrain", H=0.9, lacunarity=2.3, octaves=2.25, offset=0.7, size=2.0, intensity=0.5)
+    tex("m_hy", "musgrave", noise_type="voronoi_f1", musgrave_type="hybridmf", H=0.25, lacunarity=2.0, octaves=5.5, offset=0.7, gain=1.2, size=1.2, adj_hue=30.0)
+    tex("m_ri", "musgrave", noise_type="cellnoise", musgrave_type="ridgedmf", H=1.0, lacunarity=2.0, octaves=4.0, offset=1.0, gain=2.0, size=3.0, intensity=0.6)
+    tex("d_a", "distorted_noise", noise_type1="blender", noise_type2="newperlin", distort=1.5, size=2.0, color1=(0.9, 0.3, 0.1, 1.0), color2=(0.1, 0.3, 0.9, 1.0))
+    tex("d_b", "distorted_noise", noise_type1="voronoi_f2f1", noise_type2="stdperlin", distort=0.7, size=3.0, adj_mult_factor_blue=1.3, adj_clamp=True)
+    sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
+    layer("gl", "gm", mode=0, colfac=0.9, upper_color=(0.3, 0.5, 0.8, 1.0))
+    mapper("gm", texture="v_col1", texco="global", scale=(0.3, 0.3, 0.3))
+    y.createMaterial("ground")
+    sd("b0", color=(0.9, 0.9, 0.9, 1.0), diffuse_shader="x0")
+    node(type="mix", name="x0", input1="m0", input2="m0b", value=0.5, mode=0)
+    mapper("m0", texture="m_fbm", texco="orco", scale=(1.5, 1.5, 1.5), offset=(0.25, 0.25, 0.25))
+    mapper("m0b", texture="v_mk", texco="orco")
+    y.createMaterial("b0")
+    sd("b1", color=(0.8, 0.6, 0.4, 1.0), specular_reflect=0.3, mirror_shader="l1s", diffuse_shader="x1")
+    layer("l1s", "m1", do_color=False, do_scalar=True, color_input=False, def_val=0.6, upper_value=0.1)
+    node(type="mix", name="x1", input1="m1b", input2="m1c", value=0.6, mode=0)
+    mapper("m1", texture="v_int", texco="global", scale=(0.6, 0.6, 0.6))
+    mapper("m1b", texture="m_mf", texco="global", scale=(0.4, 0.4, 0.4), offset=(0.3, 0.0, 0.0))
+    mapper("m1c", texture="v_col3", texco="global", scale=(0.5, 0.5, 0.5))
+    y.createMaterial("b1")
+    sd("b2", color=(0.5, 0.8, 0.5, 1.0), transparency=0.1, transmit_filter=0.7, transparency_shader="l2t", diffuse_shader="x2")
+    layer("l2t", "m2", do_color=False, do_scalar=True, color_input=True, def_val=0.5, upper_value=0.0)
+    node(type="mix", name="x2", input1="m2b", input2="m2c", value=0.5, mode=0)
+    mapper("m2", texture="m_ht", texco="orco", scale=(2.0, 2.0, 2.0))
+    mapper("m2b", texture="d_a", texco="orco", scale=(1.5, 1.5, 1.5), offset=(0.25, 0.25, 0.25))
+    mapper("m2c", texture="v_mh", texco="orco")
+    y.createMaterial("b2")
+    sd("b3", color=(0.8, 0.8, 0.8, 1.0), diffuse_shader="x3")
+    node(type="mix", name="x3", input1="m3", input2="m3b", value=0.5, mode=0)
+    mapper("m3", texture="v_col2", texco="orco", scale=(1.8, 1.8, 1.8))
+    mapper("m3b", texture="m_hy", texco="orco")
+    y.createMaterial("b3")
+    sd("b4", color=(0.7, 0.7, 0.9, 1.0), specular_reflect=0.15, bump_shader="l4b", diffuse_shader="x4")
+    layer("l4b", "m4", do_color=False, do_scalar=True, color_input=False)
+    node(type="mix", name="x4", input1="m4c", input2="m4d", value=0.4, mode=1)
+    mapper("m4", texture="m_ri", texco="orco", scale=(1.5, 1.5, 1.5), bump_strength=3.0)
+    mapper("m4c", texture="d_b", texco="orco")
+    mapper("m4d", texture="v_m4", texco="orco", scale=(2.0, 2.0, 2.0))
+    y.createMaterial("b4")
+    sd("b5", color=(0.9, 0.8, 0.6, 1.0), bump_shader="l5b", diffuse_shader="l5c")
+    layer("l5b", "m5", do_color=False, do_scalar=True, color_input=False)
+    layer("l5c", "m5c", mode=0, colfac=0.8, use_alpha=True)
+    mapper("m5", texture="v_int", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0), bump_strength=2.0)
+    mapper("m5c", texture="v_col1", texco="uv", scale=(3.0, 3.0, 1.0))
     y.createMaterial("b5")
 
 
@@ -689,6 +753,8 @@ EXACT["tex_pt_mask_norr"] = lambda: textured_scene(96, 54, 4, variant="mask", in
 EXACT["tex_dl_procedural"] = lambda: textured_scene(96, 54, 2, variant="procedural")
 EXACT["tex_pt_procedural_norr"] = lambda: textured_scene(96, 54, 4, variant="procedural", integrator="pathtracing")
 EXACT["tex_dl_noise"] = lambda: textured_scene(96, 54, 2, variant="noise")
+EXACT["tex_dl_noise2"] = lambda: textured_scene(96, 54, 2, variant="noise2")
+EXACT["tex_pt_noise2_norr"] = lambda: textured_scene(96, 54, 4, variant="noise2", integrator="pathtracing")
 EXACT["tex_pt_noise_norr"] = lambda: textured_scene(96, 54, 4, variant="noise", integrator="pathtracing")
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)
