@@ -544,7 +544,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
 	phase("lights, film, rest");
-	c->wave_cur_cap = 0;
+	c->wave_cur_cap = 0; c->iters_hint = 0;
 	c->uploaded = true;
 	return YAFGPU_OK;
 }
@@ -739,6 +739,7 @@ int yafgpu_set_option(yafgpu_ctx *c, const char *name, long long value)
 	if(n == "ray_regeneration") { if(value < -1 || value > 3) return setErr(c, YAFGPU_ERR_INVALID, "ray_regeneration: -1..3"); c->ray_regeneration = (int)value; return YAFGPU_OK; }
 	if(n == "regen_threshold") { if(value < 1 || value > 32) return setErr(c, YAFGPU_ERR_INVALID, "regen_threshold: 1..32"); c->regen_threshold = (int)value; return YAFGPU_OK; }
 	if(n == "debug_stack_limit") { if(value < 0 || value > YG_STACK) return setErr(c, YAFGPU_ERR_INVALID, "debug_stack_limit: 0..96"); c->stack_limit = (int)value; return YAFGPU_OK; }
+	if(n == "adaptive_iterations") { c->adaptive_iters = value != 0; return YAFGPU_OK; }
 	if(n == "keep_nonfinite_samples") { c->keep_nonfinite = value != 0; return YAFGPU_OK; }
 	if(n == "queue_fan") { if(value < 1 || value > 64) return setErr(c, YAFGPU_ERR_INVALID, "queue_fan out of range"); c->task_fan_override = (int)value; return YAFGPU_OK; }
 	return setErr(c, YAFGPU_ERR_INVALID, "unknown option " + n);

@@ -62,6 +62,8 @@ struct yafgpu_ctx
 	int regen_threshold = 20;                 // yafgpu_set_option("regen_threshold"): refill a warp as soon as fewer lanes than this are busy
 	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	int *d_fault = nullptr, *h_fault = nullptr; // traversal-stack fault word (Accel::fault) and its pinned mirror
+	int adaptive_iters = 1;                   // yafgpu_set_option("adaptive_iterations"): 0 = always launch the schedule's maximum number of iterations (A/B)
+	int iters_hint = 0;                       // wavefront iterations the previous wave of this scene needed + 1 (0 = unknown: launch the schedule's maximum)
 	int keep_nonfinite = 0;                   // yafgpu_set_option("keep_nonfinite_samples"): splat NaN/Inf camera samples as the reference does instead of dropping them
 	int stack_limit = 0;                      // yafgpu_set_option("debug_stack_limit"): 0 = YG_STACK
 	unsigned long long *d_counters = nullptr; // device-side counters (see wavefront.h CNT_*)

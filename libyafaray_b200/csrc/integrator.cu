@@ -995,9 +995,10 @@ __global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ SceneDev
 __device__ __forceinline__ int round2Int(double v) { return (int)(v + (.5 - 1.4e-11)); } // util_math.h:34-43 (FAST_INT off)
 
 __global__ void __launch_bounds__(256) k_film_add(FilmDev film, WaveParams wp, const uint32_t *__restrict__ pixels, const float4 *__restrict__ acc, const WaveCtl *__restrict__ ctl,
-                                                  int keep_nonfinite, unsigned long long *__restrict__ counters)
+                                                  int keep_nonfinite, unsigned long long *__restrict__ counters, int it_end)
 {
 	if(ctl->overflow) return; // the wave is discarded and re-rendered in smaller pieces
+	if(ctl->n_tasks[it_end] != 0) return; // tasks are still queued behind the iterations launched so far: the host launches more and splats afterwards
 	for(int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < wp.n_slots; slot += gridDim.x * blockDim.x)
 	{
 		const SlotInfo si = slotInfo(wp, pixels, slot);
@@ -1141,7 +1142,13 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	size_t ne = 0;
 	auto mark = [&]() { if(!timed) return; if(ne >= ev.size()) { cudaEvent_t e; cudaEventCreate(&e); ev.push_back(e); } cudaEventRecord(ev[ne++], st); };
 	mark();
-	for(int it = 0; it < max_iters; ++it)
+	// The host cannot see the queue lengths without a round trip, so it launches the number of iterations the previous wave of this scene needed (+ 1) and lets the
+	// DEVICE decide whether that was enough: k_film_add only splats when nothing is queued behind the last launched iteration.  If tasks remain (seen in the control
+	// block the wave-end synchronisation reads anyway), four more iterations and another k_film_add follow.  Empty tail iterations launch nothing any more.
+	int it_end = (c->iters_hint > 0 && c->adaptive_iters) ? std::min(max_iters, c->iters_hint) : max_iters;
+	int it = 0;
+more_iterations:
+	for(; it < it_end; ++it)
 	{
 		int n_launch = 0;
 		TaskQueue &in = w.q[it & 1], &out = w.q[(it + 1) & 1];
@@ -1183,18 +1190,31 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 		mark();
 		c->stats.kernel_launches += 4 + n_launch;
 	}
-	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl, c->keep_nonfinite, c->d_counters);
-	c->stats.kernel_launches += 2;
+	k_film_add<<<g256, 256, 0, st>>>(c->film, wp, w.pixels, w.acc, w.ctl, c->keep_nonfinite, c->d_counters, it_end);
+	c->stats.kernel_launches += 1;
 	YG_CUDA(c, cudaGetLastError());
 	YG_CUDA(c, cudaMemcpyAsync(w.h_ctl, w.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
 	YG_CUDA(c, cudaMemcpyAsync(c->h_fault, c->d_fault, sizeof(int), cudaMemcpyDeviceToHost, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
 	if(int rc = faultCheck(c, false)) return rc;
 	overflow = w.h_ctl->overflow != 0;
+	if(!overflow && it_end < max_iters && w.h_ctl->n_tasks[it_end] != 0)
+	{	// the guess was short: the film is untouched, carry on where the queue stands
+		it_end = std::min(max_iters, it_end + 4);
+		goto more_iterations;
+	}
+	c->stats.kernel_launches += 1; // k_raygen
 	c->stats.waves++;
+	if(!overflow)
+	{	// iterations that held tasks in this wave, plus one for the next wave's guess
+		int used = 0;
+		for(int k = 0; k < max_iters; ++k) if(w.h_ctl->n_tasks[k] > 0) used = k + 1;
+		c->iters_hint = std::min(max_iters, used + 1);
+	}
+	const int launched_iters = it;
 	if(timed && !overflow)
 	{
-		for(int it = 0; it < max_iters; ++it)
+		for(int it = 0; it < launched_iters; ++it)
 		{
 			float a = 0.f, b = 0.f, d = 0.f;
 			cudaEventElapsedTime(&a, ev[3 * it], ev[3 * it + 1]); cudaEventElapsedTime(&b, ev[3 * it + 1], ev[3 * it + 2]); cudaEventElapsedTime(&d, ev[3 * it + 2], ev[3 * it + 3]);
