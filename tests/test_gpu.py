@@ -267,6 +267,31 @@ def test_upload_from_page_locked_host_arrays_gives_the_same_hits(ctx):
     assert ctx.trace(rays, 0).tobytes() == a.tobytes()
 
 
+def test_wave_continues_when_the_iteration_guess_was_short(ctx):
+    """A wave launches as many wavefront iterations as the previous wave needed (+ 1).  After a pass over background pixels only (one iteration) the guess
+    for the full frame is far too short: k_film_add must leave the film alone, the host must launch the rest, and the film must equal the one rendered with
+    the fixed schedule (`adaptive_iterations` 0)."""
+    from libyafaray_b200 import scenes
+    y = scenes.simple_point_scene(160, 90, 2, integrator="pathtracing", filter_type="box")
+    _upload(ctx, y)
+    try:
+        ctx.set_option("adaptive_iterations", 0)
+        ctx.film_clear(); ctx.reset_stats(); ctx.render_pass(2, 0); fixed = ctx.read_film(); n_fixed = ctx.stats()["kernel_launches"]
+        ctx.set_option("adaptive_iterations", 1)
+        _upload(ctx, y)                                     # forgets the guess
+        sky = np.zeros((90, 160), np.uint8); sky[0, :] = 1   # the top row sees only the background
+        ctx.film_clear(); ctx.render_pass(2, 0, adaptive=True, mask=sky)
+        assert sum(1 for v in ctx.stats()["last_wave_tasks"] if v) <= 2   # camera rays and at most their first hit on the far ground
+        ctx.film_clear(); ctx.reset_stats(); ctx.render_pass(2, 0); short = ctx.read_film(); n_short = ctx.stats()["kernel_launches"]
+        ctx.film_clear(); ctx.reset_stats(); ctx.render_pass(2, 0); again = ctx.read_film(); n_again = ctx.stats()["kernel_launches"]
+    finally:
+        ctx.set_option("adaptive_iterations", 1)
+    for f in (short, again):
+        assert np.array_equal(f[..., 3:], fixed[..., 3:])
+        assert np.abs(f[..., :3] - fixed[..., :3]).max() <= 1e-5 * float(np.abs(fixed[..., :3]).max())
+    assert n_again < n_short <= n_fixed + 2 and n_again < n_fixed   # the continuation costs one more k_film_add per round; the settled guess is the cheapest
+
+
 def test_empty_scene_renders_background(ctx):
     from libyafaray_b200 import scenes
     from libyafaray_b200.interface import Interface
