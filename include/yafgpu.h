@@ -642,6 +642,8 @@ int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_
  * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "leaf_size" (triangles per leaf link of the BVH built by
  * the NEXT upload, 1..8), "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3),
  * "debug_stack_limit" (traversal stack entries in use, only to exercise the overflow error path),
+ * "ray_regeneration" (-1, default: the library decides by scene size; 0: one ray per lane and launch; 1: both traversal kernels are warp-persistent and refill idle lanes
+ * from the queue; 2: only the closest-hit kernel; 3: only the shadow kernel), "regen_threshold" (1..32: refill a warp as soon as fewer lanes than this are busy; default 20),
  * "adaptive_iterations" (1, default: a wave launches as many wavefront iterations as the previous wave of the scene needed, + 1, and more only when the device
  * reports tasks still queued; 0: always the schedule's maximum, raydepth + bounces + 2),
  * "keep_nonfinite_samples" (0, default: a camera sample whose radiance is NaN/Inf is left out of the film and counted in yafgpu_stats.nonfinite_samples;

@@ -1127,7 +1127,10 @@ static int runWave(yafgpu_ctx *c, const WaveParams &wp, int max_iters, bool &ove
 	Wavefront &w = c->wf;
 	cudaStream_t st = c->stream;
 	const bool count = (c->flags & YAFGPU_FLAG_COUNT_TRAVERSAL) != 0;
-	const int rr = c->ray_regeneration >= 0 ? c->ray_regeneration : YG_DEFAULT_REGEN;
+	// Default schedule: both traversal kernels regenerate rays on scenes whose rays are long walks (10^7 triangles: shadow kernel 10.4 -> 7.1 ms per 2 spp); on a scene
+	// of a few dozen triangles a shadow ray is a handful of node visits and the refill atomics cost more than the idle lanes did (Cornell: 3.0 -> 5.4 ms per step,
+	// tools/cornell_regen_ab.py), so there only the closest-hit kernel regenerates.
+	const int rr = c->ray_regeneration >= 0 ? c->ray_regeneration : (YG_DEFAULT_REGEN == 1 && c->scene.accel.n_tris < (1 << 15) ? 2 : YG_DEFAULT_REGEN);
 	const bool regen_t = rr == 1 || rr == 2, regen_s = rr == 1 || rr == 3;
 	const int refill = c->regen_threshold;
 	int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
