@@ -551,7 +551,7 @@ typedef struct yafgpu_pass_desc
 {
 	int32_t n_samples;       /* samples per pixel in this pass */
 	int32_t offset;          /* pass_offs: sampling offset incl. base offset (integrator_tiled.cc:263,335) */
-	int32_t adaptive;        /* 1: only pixels flagged in resample_mask are sampled (imagefilm.cc:917-920) */
+	int32_t adaptive;        /* 1: only pixels flagged in resample_mask are sampled (imagefilm.cc:917-920); 2: the mask is the one the last yafgpu_next_pass computed */
 	int32_t aa_pass_number;
 	const uint8_t *resample_mask; /* adaptive only: width*height bytes (host), non-zero = sample this pixel */
 	/* sub-range of the pass's samples to render now: sample indices [sample_begin, sample_end); both 0 = all.
@@ -561,6 +561,18 @@ typedef struct yafgpu_pass_desc
 	 * tile_size x tile_size raster grid of ImageSplitter (imagesplitter.cc:37-50).  part_count <= 1 = whole image. */
 	int32_t part_index, part_count;
 } yafgpu_pass_desc;
+
+/* ImageFilm::setAaNoiseParams / setAaThreshold (imagefilm.h), i.e. the <render> parameters AA_threshold, AA_dark_detection_type (none|linear|curve),
+ * AA_dark_threshold_factor, AA_variance_edge_size, AA_variance_pixels, AA_detect_color_noise */
+enum { YAFGPU_DARK_NONE = 0, YAFGPU_DARK_LINEAR = 1, YAFGPU_DARK_CURVE = 2 };
+typedef struct yafgpu_aa_noise_params
+{
+	float threshold;
+	int32_t dark_detection_type;
+	float dark_threshold_factor;
+	int32_t variance_edge_size, variance_pixels;
+	int32_t detect_color_noise;
+} yafgpu_aa_noise_params;
 
 typedef struct yafgpu_stats
 {
@@ -628,6 +640,11 @@ int yafgpu_film_clear(yafgpu_ctx *ctx);
  * Returns when the pass is in the film accumulators (the wave scheduler reads queue counters back after every wave). */
 int yafgpu_render_pass(yafgpu_ctx *ctx, const yafgpu_pass_desc *pass);
 /* Wait for all queued work; returns the first asynchronous error. */
+/* ImageFilm::nextPass's resampling decision (imagefilm.cc:306-424) evaluated ON THE DEVICE from the film accumulators: flags every pixel whose normalised colour
+ * differs from a right / lower / diagonal neighbour by at least the (dark-scaled) threshold, the variance windows, and pixels without weight.  The film stays in HBM;
+ * only the byte mask (width * height) comes back, is kept by the context and is used by the passes that say adaptive = 2.  *n_resample = flagged pixels
+ * (width * height when threshold <= 0: every pixel is resampled then, imagefilm.cc:917-920).  yafgpu_group_next_pass decides on the summed film of the group. */
+int yafgpu_next_pass(yafgpu_ctx *ctx, const yafgpu_aa_noise_params *params, int64_t *n_resample);
 int yafgpu_sync(yafgpu_ctx *ctx);
 /* Film accumulators, width*height*5 floats: Pixel{Rgba col_; float weight_} (util_image_buffers.h:36-47) row-major. */
 int yafgpu_read_film(yafgpu_ctx *ctx, float *rgbaw);
@@ -680,6 +697,7 @@ int yafgpu_group_film_clear(yafgpu_group *g);
 int yafgpu_group_write_film(yafgpu_group *g, const float *rgbaw); /* resume: the first member takes the film, the others start from zero */
 int yafgpu_group_render_pass(yafgpu_group *g, const yafgpu_pass_desc *pass); /* part_index / part_count are set per member */
 int yafgpu_group_read_film(yafgpu_group *g, float *rgbaw);
+int yafgpu_group_next_pass(yafgpu_group *g, const yafgpu_aa_noise_params *params, int64_t *n_resample);
 int yafgpu_group_sync(yafgpu_group *g); /* yafgpu_sync on every member (the first member's stream also carries the film sum) */
 int yafgpu_group_set_aa_multipliers(yafgpu_group *g, float light_mult, float indirect_mult);
 int yafgpu_group_set_option(yafgpu_group *g, const char *name, long long value);

@@ -177,6 +177,14 @@ class PassDesc(C.Structure):
                 ("part_index", i32), ("part_count", i32)]
 
 
+class AaNoiseParams(C.Structure):
+    _fields_ = [("threshold", f32), ("dark_detection_type", i32), ("dark_threshold_factor", f32), ("variance_edge_size", i32), ("variance_pixels", i32),
+                ("detect_color_noise", i32)]
+
+
+DARK_DETECTION = {"linear": 1, "curve": 2}
+
+
 class Stats(C.Structure):
     _fields_ = [("rays_camera", u64), ("rays_extension", u64), ("rays_shadow", u64), ("rays_shadow_transp", u64),
                 ("rays_light_probe", u64), ("camera_samples", u64), ("kernel_launches", u64), ("bvh_nodes", u64),
@@ -203,6 +211,7 @@ SYMBOLS = {
     "yafgpu_film_clear": (C.c_int, [C.c_void_p]),
     "yafgpu_render_pass": (C.c_int, [C.c_void_p, C.POINTER(PassDesc)]),
     "yafgpu_sync": (C.c_int, [C.c_void_p]),
+    "yafgpu_next_pass": (C.c_int, [C.c_void_p, C.POINTER(AaNoiseParams), C.POINTER(C.c_int64)]),
     "yafgpu_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
     "yafgpu_host_unregister": (C.c_int, [C.c_void_p]),
     "yafgpu_read_film": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -224,6 +233,7 @@ SYMBOLS = {
     "yafgpu_group_render_pass": (C.c_int, [C.c_void_p, C.POINTER(PassDesc)]),
     "yafgpu_group_read_film": (C.c_int, [C.c_void_p, C.c_void_p]),
     "yafgpu_group_sync": (C.c_int, [C.c_void_p]),
+    "yafgpu_group_next_pass": (C.c_int, [C.c_void_p, C.POINTER(AaNoiseParams), C.POINTER(C.c_int64)]),
     "yafgpu_group_set_aa_multipliers": (C.c_int, [C.c_void_p, f32, f32]),
     "yafgpu_group_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),
     "yafgpu_group_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),

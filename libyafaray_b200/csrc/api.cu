@@ -544,7 +544,7 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	YG_CUDA(c, cudaMemsetAsync(c->film.pix, 0, sizeof(float) * 5 * (size_t)c->film.w * c->film.h, st));
 	YG_CUDA(c, cudaStreamSynchronize(st));
 	phase("lights, film, rest");
-	c->wave_cur_cap = 0; c->iters_hint = 0;
+	c->wave_cur_cap = 0; c->iters_hint = 0; c->aa_mask_valid = false; c->aa_mask.clear();
 	c->uploaded = true;
 	return YAFGPU_OK;
 }
@@ -669,7 +669,139 @@ int yafgpu_render_pass(yafgpu_ctx *c, const yafgpu_pass_desc *pass)
 	if(!c || !pass) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
 	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
 	YG_CUDA(c, cudaSetDevice(c->device));
+	if(pass->adaptive == 2)
+	{	// the mask of the last yafgpu_next_pass; an empty one stands for "every pixel" (threshold <= 0)
+		if(!c->aa_mask_valid) return setErr(c, YAFGPU_ERR_STATE, "adaptive = 2 needs a yafgpu_next_pass on this scene first");
+		yafgpu_pass_desc p = *pass;
+		p.adaptive = 1; p.resample_mask = c->aa_mask.empty() ? nullptr : c->aa_mask.data();
+		return renderPass(c, &p);
+	}
 	return renderPass(c, pass);
+}
+
+} // extern "C"
+
+namespace yg {
+// ---- ImageFilm::nextPass on the device (imagefilm.cc:306-424) ---------------------------------------------------------------------------------
+struct AaPix { float r, g, b, a; };
+// Pixel::normalized util_image_buffers.h:39-43 with Rgba / float of color.h:310-314 (the reciprocal is formed in double and narrowed)
+__device__ __forceinline__ AaPix aaNormalized(const float *__restrict__ film, int w, int x, int y)
+{
+	const float *p = film + 5 * ((size_t)y * w + x);
+	float f = p[4];
+	if(f == 0.f) return AaPix{0.f, 0.f, 0.f, 0.f};
+	f = (float)(1.0 / (double)f);
+	return AaPix{p[0] * f, p[1] * f, p[2] * f, p[3] * f};
+}
+__device__ __forceinline__ float aaBri(const AaPix &c) { return 0.2126f * c.r + 0.7152f * c.g + 0.0722f * c.b; }   // Rgb::col2Bri color.h:60
+// Rgba::colorDifference color.h:447-465
+__device__ __forceinline__ float aaDifference(const AaPix &a, const AaPix &b, int rgb_too)
+{
+	float d = fabsf(aaBri(b) - aaBri(a));
+	if(rgb_too)
+	{
+		const float rd = fabsf(b.r - a.r), gd = fabsf(b.g - a.g), bd = fabsf(b.b - a.b), ad = fabsf(b.a - a.a);
+		if(d < rd) d = rd;
+		if(d < gd) d = gd;
+		if(d < bd) d = bd;
+		if(d < ad) d = ad;
+	}
+	return d;
+}
+// ImageFilm::darkThresholdCurveInterpolate imagefilm.cc:1312-1328: a piecewise-linear threshold over the pixel brightness
+__device__ __forceinline__ float aaDarkCurve(float b)
+{
+	const float kx[15] = {0.10f, 0.20f, 0.30f, 0.40f, 0.50f, 0.60f, 0.70f, 0.80f, 0.90f, 1.00f, 1.20f, 1.40f, 1.80f, 0.f, 0.f};
+	const float ky[15] = {0.0001f, 0.0010f, 0.0020f, 0.0035f, 0.0055f, 0.0075f, 0.0100f, 0.0150f, 0.0250f, 0.0400f, 0.0800f, 0.0950f, 0.1000f, 0.f, 0.f};
+	const float kw[15] = {0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.20f, 0.20f, 0.40f, 0.f, 0.f, 0.f};
+	if(b <= 0.10f) return 0.0001f;
+	for(int k = 0; k < 12; ++k)
+		if(b > kx[k] && b <= kx[k + 1]) return (ky[k] + (b - kx[k]) * (ky[k + 1] - ky[k]) / kw[k]);
+	return 0.1000f;
+}
+__global__ void __launch_bounds__(256) k_next_pass(const float *__restrict__ film, int w, int h, yafgpu_aa_noise_params prm, unsigned char *__restrict__ flags)
+{
+	const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+	if(x >= w - 1 || y >= h - 1) return;
+	if(film[5 * ((size_t)y * w + x) + 4] <= 0.f) flags[(size_t)y * w + x] = 1;   // never rendered (a film loaded from disk): sample it
+	const AaPix c = aaNormalized(film, w, x, y);
+	const float bri = 0.2126f * fabsf(c.r) + 0.7152f * fabsf(c.g) + 0.0722f * fabsf(c.b);   // abscol2Bri
+	float thr = prm.threshold;
+	if(prm.dark_detection_type == YAFGPU_DARK_LINEAR && prm.dark_threshold_factor > 0.f) thr = prm.threshold * ((1.f - prm.dark_threshold_factor) + (bri * prm.dark_threshold_factor));
+	else if(prm.dark_detection_type == YAFGPU_DARK_CURVE) thr = aaDarkCurve(bri);
+	const int noise = prm.detect_color_noise;
+	auto set = [&](int xi, int yi) { flags[(size_t)yi * w + xi] = 1; };
+	if(aaDifference(c, aaNormalized(film, w, x + 1, y), noise) >= thr) { set(x, y); set(x + 1, y); }
+	if(aaDifference(c, aaNormalized(film, w, x, y + 1), noise) >= thr) { set(x, y); set(x, y + 1); }
+	if(aaDifference(c, aaNormalized(film, w, x + 1, y + 1), noise) >= thr) { set(x, y); set(x + 1, y + 1); }
+	if(x > 0 && aaDifference(c, aaNormalized(film, w, x - 1, y + 1), noise) >= thr) { set(x, y); set(x - 1, y + 1); }
+	if(prm.variance_pixels > 0)
+	{
+		const int half = prm.variance_edge_size / 2;
+		int vx = 0, vy = 0;
+		for(int xd = -half; xd < half - 1; ++xd)
+		{
+			int xi = x + xd;
+			if(xi < 0) xi = 0; else if(xi >= w - 1) xi = w - 2;
+			if(aaDifference(aaNormalized(film, w, xi, y), aaNormalized(film, w, xi + 1, y), noise) >= thr) ++vx;
+		}
+		for(int yd = -half; yd < half - 1; ++yd)
+		{
+			int yi = y + yd;
+			if(yi < 0) yi = 0; else if(yi >= h - 1) yi = h - 2;
+			if(aaDifference(aaNormalized(film, w, x, yi), aaNormalized(film, w, x, yi + 1), noise) >= thr) ++vy;
+		}
+		if(vx + vy >= prm.variance_pixels)
+			for(int xd = -half; xd < half; ++xd)
+				for(int yd = -half; yd < half; ++yd)
+				{
+					int xi = x + xd, yi = y + yd;
+					if(xi < 0) xi = 0; else if(xi >= w) xi = w - 1;
+					if(yi < 0) yi = 0; else if(yi >= h) yi = h - 1;
+					set(xi, yi);
+				}
+	}
+}
+
+// the decision over `film` (w x h x 5 floats on c's device), mask and count to the host; flags of different pixels only ever store 1, so the order is free
+int nextPassMask(yafgpu_ctx *c, const float *film, const yafgpu_aa_noise_params *prm, std::vector<uint8_t> &mask, int64_t *n_resample)
+{
+	const int w = c->film.w, h = c->film.h;
+	if(!(prm->threshold > 0.f)) { mask.clear(); if(n_resample) *n_resample = (int64_t)w * h; return YAFGPU_OK; }
+	if(prm->dark_detection_type < YAFGPU_DARK_NONE || prm->dark_detection_type > YAFGPU_DARK_CURVE || prm->variance_edge_size < 0 || prm->variance_edge_size > 64)
+		return setErr(c, YAFGPU_ERR_INVALID, "yafgpu_next_pass: dark_detection_type / variance_edge_size (0..64)");
+	unsigned char *d_flags = nullptr;
+	const size_t n = (size_t)w * h;
+	YG_CUDA(c, poolAlloc(&d_flags, n, c->stream));
+	cudaError_t e = cudaMemsetAsync(d_flags, 0, n, c->stream);
+	if(e == cudaSuccess && w > 1 && h > 1)
+	{
+		k_next_pass<<<dim3((unsigned)((w + 255) / 256), (unsigned)h), 256, 0, c->stream>>>(film, w, h, *prm, d_flags);
+		e = cudaGetLastError();
+	}
+	mask.resize(n);
+	if(e == cudaSuccess) e = cudaMemcpyAsync(mask.data(), d_flags, n, cudaMemcpyDeviceToHost, c->stream);
+	if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+	poolFree(d_flags, c->stream);
+	if(e != cudaSuccess) return cudaErr(c, e, "yafgpu_next_pass");
+	int64_t cnt = 0;
+	for(size_t i = 0; i < n; ++i) cnt += mask[i] != 0;
+	if(n_resample) *n_resample = cnt;
+	return YAFGPU_OK;
+}
+} // namespace yg
+
+extern "C" {
+
+int yafgpu_next_pass(yafgpu_ctx *c, const yafgpu_aa_noise_params *prm, int64_t *n_resample)
+{
+	if(!c || !prm) return setErr(c, YAFGPU_ERR_INVALID, "NULL argument");
+	if(!c->uploaded) return setErr(c, YAFGPU_ERR_STATE, "no scene uploaded");
+	YG_CUDA(c, cudaSetDevice(c->device));
+	c->aa_mask_valid = false;
+	const int rc = nextPassMask(c, c->film.pix, prm, c->aa_mask, n_resample);
+	if(rc == YAFGPU_OK) c->aa_mask_valid = true;
+	return rc;
 }
 
 int yafgpu_host_register(void *ptr, size_t bytes)

@@ -62,6 +62,7 @@ struct yafgpu_ctx
 	int regen_threshold = 20;                 // yafgpu_set_option("regen_threshold"): refill a warp as soon as fewer lanes than this are busy
 	int *d_fetch = nullptr;                   // ray-regeneration counter of the batch trace kernel
 	int *d_fault = nullptr, *h_fault = nullptr; // traversal-stack fault word (Accel::fault) and its pinned mirror
+	std::vector<uint8_t> aa_mask; bool aa_mask_valid = false; // resampling mask of the last yafgpu_next_pass (empty = every pixel), used by passes with adaptive = 2
 	int adaptive_iters = 1;                   // yafgpu_set_option("adaptive_iterations"): 0 = always launch the schedule's maximum number of iterations (A/B)
 	int iters_hint = 0;                       // wavefront iterations the previous wave of this scene needed + 1 (0 = unknown: launch the schedule's maximum)
 	int keep_nonfinite = 0;                   // yafgpu_set_option("keep_nonfinite_samples"): splat NaN/Inf camera samples as the reference does instead of dropping them
@@ -78,6 +79,7 @@ namespace yg {
 int setErr(yafgpu_ctx *ctx, int code, const std::string &msg);
 int cudaErr(yafgpu_ctx *ctx, cudaError_t e, const char *what);
 int renderPass(yafgpu_ctx *ctx, const yafgpu_pass_desc *pass); // integrator.cu
+int nextPassMask(yafgpu_ctx *ctx, const float *film, const yafgpu_aa_noise_params *prm, std::vector<uint8_t> &mask, int64_t *n_resample); // api.cu
 void freeWavefront(yafgpu_ctx *ctx);
 int faultCheck(yafgpu_ctx *ctx, bool fetch); // api.cu: YAFGPU_ERR_CUDA when a traversal stack overflowed since the last check (fetch: copy the word first)
 }

@@ -248,6 +248,25 @@ int yafgpu_group_read_film(yafgpu_group *g, float *out)
 	return YAFGPU_OK;
 }
 
+int yafgpu_group_next_pass(yafgpu_group *g, const yafgpu_aa_noise_params *prm, int64_t *n_resample)
+{
+	if(!g || !prm) return gErr(g, YAFGPU_ERR_INVALID, "NULL argument");
+	if(g->ctx.size() == 1)
+	{
+		const int rc = yafgpu_next_pass(g->ctx[0], prm, n_resample);
+		return rc == YAFGPU_OK ? rc : gErr(g, rc, yafgpu_last_error(g->ctx[0]));
+	}
+	if(!g->red) return gErr(g, YAFGPU_ERR_STATE, "no scene uploaded");
+	if(!g->reduced_valid) { const int rc = reduceFilms(g); if(rc != YAFGPU_OK) return rc; }
+	// the decision is taken once, on the summed film (first device, behind the film sum on its stream); every member gets the same mask
+	yafgpu_ctx *c0 = g->ctx[0];
+	cudaSetDevice(g->devices[0]);
+	const int rc = nextPassMask(c0, g->red, prm, c0->aa_mask, n_resample);
+	if(rc != YAFGPU_OK) return gErr(g, rc, yafgpu_last_error(c0));
+	for(size_t k = 0; k < g->ctx.size(); ++k) { if(k) g->ctx[k]->aa_mask = c0->aa_mask; g->ctx[k]->aa_mask_valid = true; }
+	return YAFGPU_OK;
+}
+
 int yafgpu_group_sync(yafgpu_group *g)
 {
 	if(!g) return YAFGPU_ERR_INVALID;

@@ -85,6 +85,13 @@ class Context:
             p.resample_mask = mask.ctypes.data_as(C.POINTER(C.c_uint8))
         _check(self.h, capi.lib.yafgpu_render_pass(self.h, C.byref(p)))
 
+    def next_pass(self, threshold, dark_detection_type=0, dark_threshold_factor=0.0, variance_edge_size=10, variance_pixels=0, detect_color_noise=False):
+        """ImageFilm::nextPass's resampling decision on the device; returns the number of pixels to resample.  Follow with render_pass(adaptive=2)."""
+        prm = capi.AaNoiseParams(threshold, int(dark_detection_type), dark_threshold_factor, int(variance_edge_size), int(variance_pixels), int(detect_color_noise))
+        n = C.c_int64(0)
+        _check(self.h, capi.lib.yafgpu_next_pass(self.h, C.byref(prm), C.byref(n)))
+        return n.value
+
     def sync(self):
         _check(self.h, capi.lib.yafgpu_sync(self.h))
 
@@ -177,6 +184,12 @@ class Group:
         self._check(capi.lib.yafgpu_group_read_film(self.h, out.ctypes.data))
         return out
 
+    def next_pass(self, threshold, dark_detection_type=0, dark_threshold_factor=0.0, variance_edge_size=10, variance_pixels=0, detect_color_noise=False):
+        prm = capi.AaNoiseParams(threshold, int(dark_detection_type), dark_threshold_factor, int(variance_edge_size), int(variance_pixels), int(detect_color_noise))
+        n = C.c_int64(0)
+        self._check(capi.lib.yafgpu_group_next_pass(self.h, C.byref(prm), C.byref(n)))
+        return n.value
+
     def read_film_into(self, ptr):
         self._check(capi.lib.yafgpu_group_read_film(self.h, ptr))
 
@@ -259,7 +272,12 @@ def render_scene(iface, output=None, device=0, ctx=None, image_output_path=None)
     smf = np.float32(g(rp, "AA_sample_multiplier_factor", 1.0))
     lmf = np.float32(g(rp, "AA_light_sample_multiplier_factor", 1.0))
     imf = np.float32(g(rp, "AA_indirect_sample_multiplier_factor", 1.0))
-    threshold = g(rp, "AA_threshold", 0.05)
+    threshold = np.float32(g(rp, "AA_threshold", 0.05))
+    noise_prm = dict(dark_detection_type=capi.DARK_DETECTION.get(g(rp, "AA_dark_detection_type", "none"), 0), dark_threshold_factor=g(rp, "AA_dark_threshold_factor", 0.0),
+                     variance_edge_size=int(g(rp, "AA_variance_edge_size", 10)), variance_pixels=int(g(rp, "AA_variance_pixels", 0)),
+                     detect_color_noise=bool(g(rp, "AA_detect_color_noise", False)))
+    # integrator_tiled.cc:142: the floor below which the threshold is tightened for the following pass
+    floor_pixels = int(math.floor(np.float32(np.float32(g(rp, "AA_resampled_floor", 0.0)) * np.float32(desc.film.width * desc.film.height)) / np.float32(100.0)))
     fsl = g(rp, "film_save_load", "none") if image_output_path is not None else "none"
     node, base_raw = int(g(rp, "adv_computer_node", 0)), int(g(rp, "adv_base_sampling_offset", 0))
     loaded = None
@@ -280,15 +298,27 @@ def render_scene(iface, output=None, device=0, ctx=None, image_output_path=None)
         ctx.render_pass(aa_samples, 0 + base, False, 0)
         acum = sampling_offset = aa_samples
     sm, lm, im = np.float32(1), np.float32(1), np.float32(1)
+    threshold_changed, resampled = True, 0
     for i in range(1, aa_passes):
         sm, lm, im = np.float32(sm * smf), np.float32(lm * lmf), np.float32(im * imf)
         ctx.set_aa_multipliers(float(lm), float(im))
         n = int(math.ceil(np.float32(aa_inc) * sm))
-        if threshold > 0:
-            raise NotImplementedError("adaptive AA (AA_threshold > 0 with AA_passes > 1): set AA_threshold 0")
-        ctx.render_pass(n, acum + base, True, i)  # threshold 0: doMoreSamples() is true for every pixel (imagefilm.cc:917-920)
-        sampling_offset = acum + n                # ImageFilm::setSamplingOffset(offset + samples) (integrator_tiled.cc:270)
+        # integrator_tiled.cc:220-251: the film decides which pixels the pass resamples (ImageFilm::nextPass, evaluated on the device: the film stays in HBM);
+        # a pass after one that resampled nothing is skipped unless the threshold moved; too few resampled pixels tighten the threshold
+        if resampled <= 0 and not threshold_changed:
+            pass
+        else:
+            resampled = ctx.next_pass(float(threshold), **noise_prm)
+            threshold_changed = False
+        if resampled > 0:
+            ctx.render_pass(n, acum + base, 2, i)
+            sampling_offset = acum + n            # ImageFilm::setSamplingOffset(offset + samples) (integrator_tiled.cc:270)
         acum += n
+        if resampled < floor_pixels:
+            ratio = min(np.float32(8.0), np.float32(floor_pixels) / np.float32(resampled)) if resampled else np.float32(8.0)
+            threshold = np.float32(threshold * np.float32(np.float32(1.0) - np.float32(0.1) * ratio))
+            if threshold > 0:
+                threshold_changed = True
     ctx.sync()
     film = ctx.read_film()
     if fsl in ("save", "load-save"):

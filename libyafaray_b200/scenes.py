@@ -159,7 +159,7 @@ def cornell_box(width=1920, height=1080, spp=256, path_samples=1, bounces=8, ray
 
 
 def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting", filter_type="gauss", bg_transp=False, bg_transp_refract=False, see_through=False,
-                       ground_quad=True):
+                       ground_quad=True, aa_passes=1, **render_extra):
     """Small DirectLight + point-light scene in the spirit of BASELINE config 1 (tests/test01 geometry is 6 cubes on
     a ground quad lit by one point light; its textures are 'next' scope, so flat colours are used)."""
     y = Interface()
@@ -217,7 +217,7 @@ def simple_point_scene(width=160, height=90, spp=1, integrator="directlighting",
         y.paramsSetInt("path_samples", 2); y.paramsSetInt("bounces", 3); y.paramsSetInt("russian_roulette_min_bounces", 8)
     y.createIntegrator("pt")
     _vol_none(y)
-    render_block(y, width, height, spp, filter_type=filter_type)
+    render_block(y, width, height, spp, filter_type=filter_type, aa_passes=aa_passes, **render_extra)
     return y
 
 

@@ -266,6 +266,19 @@ EXACT["zoo_dl_cam_equirect"] = lambda: material_zoo_scene(96, 48, 2, camera={"ty
 FRONTEND_ONLY = {
     "cornell_dl_adaptive": lambda: scenes.cornell_box(160, 90, 2, integrator="directlighting", aa_passes=3, AA_threshold=0.02, AA_inc_samples=2),
 }
+# Adaptive AA (AA_threshold > 0, several passes): which pixels a pass resamples is ImageFilm::nextPass's decision (imagefilm.cc:306-424) — taken by the reference's own
+# film in the C++ adaptor, and ON THE DEVICE (yafgpu_next_pass) in the Python mirror.  Both must reach the reference's film.
+ADAPTIVE = dict(FRONTEND_ONLY)
+ADAPTIVE.update({
+    "cornell_dl_adaptive_dark": lambda: scenes.cornell_box(160, 90, 2, integrator="directlighting", aa_passes=4, AA_threshold=0.05, AA_inc_samples=1,
+                                                           AA_dark_detection_type="linear", AA_dark_threshold_factor=0.8),
+    "cornell_dl_adaptive_curve": lambda: scenes.cornell_box(160, 90, 1, integrator="directlighting", aa_passes=3, AA_threshold=0.05, AA_inc_samples=2,
+                                                            AA_dark_detection_type="curve", AA_detect_color_noise=True),
+    "cornell_dl_adaptive_variance": lambda: scenes.cornell_box(160, 90, 2, integrator="directlighting", aa_passes=4, AA_threshold=0.03, AA_inc_samples=1,
+                                                               AA_variance_pixels=3, AA_variance_edge_size=6, AA_resampled_floor=30.0, AA_sample_multiplier_factor=1.5),
+    "simple_dl_adaptive_gauss": lambda: scenes.simple_point_scene(160, 90, 1, aa_passes=3, AA_threshold=0.01, AA_inc_samples=2),
+})
+FRONTEND_ONLY = ADAPTIVE
 CONVERGED["zoo_pt"] = (lambda spp: material_zoo_scene(W, H, spp), 8192)
 
 

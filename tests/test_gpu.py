@@ -111,9 +111,22 @@ def test_render_matches_reference_film(ctx, name):
     _assert_film_matches(render_scene(pc.EXACT[name](), ctx=ctx), gold)
 
 
+@pytest.mark.parametrize("name", list(pc.ADAPTIVE))
+def test_adaptive_passes_decided_on_the_device_reach_the_reference_film(ctx, name):
+    """Several AA passes with AA_threshold > 0: the resampling mask of every pass comes from yafgpu_next_pass (ImageFilm::nextPass restated on the device: neighbour
+    differences, linear / curve dark detection, colour-noise detection, variance windows) and the host mirrors TiledIntegrator::render's threshold schedule
+    (resampled floor, skipped passes).  The film must equal the reference's, whose own ImageFilm took the same decisions."""
+    from libyafaray_b200 import render_scene
+    gold = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
+    film = render_scene(pc.ADAPTIVE[name](), ctx=ctx)
+    assert gold[..., 4].min() < gold[..., 4].max()     # the passes really were selective
+    _assert_film_matches(film, gold)
+
+
 # ---- the drop-in boundary itself: reference XML loader + Scene + ImageFilm with GpuIntegrator linked in ----------------------
 FRONTEND_CASES = ["simple_dl_gauss", "cornell_dl_glass", "cornell_dl_mitchell", "cornell_pt_norr", "zoo_dl_point_free", "zoo_pt_mesh_norr",
-                  "zoo_dl_hdr_ibl", "zoo_dl_hdr_angular", "cornell_dl_adaptive", "zoo_dl_directional", "zoo_dl_spot_soft", "zoo_dl_sphere",
+                  "zoo_dl_hdr_ibl", "zoo_dl_hdr_angular", "cornell_dl_adaptive", "cornell_dl_adaptive_dark", "cornell_dl_adaptive_curve", "cornell_dl_adaptive_variance",
+                  "simple_dl_adaptive_gauss", "zoo_dl_directional", "zoo_dl_spot_soft", "zoo_dl_sphere",
                   "zoo_dl_gradient_ibl", "zoo_dl_cam_ortho", "zoo_dl_cam_architect", "zoo_dl_cam_angular_stereo", "zoo_dl_cam_equirect",
                   "tex_dl_basic", "tex_dl_modes_c", "tex_dl_adjust", "tex_pt_norr", "tex_dl_materials", "zoo_dl_beer", "tex_dl_mask", "tex_dl_camera_coords", "zoo_dl_portal_hdr", "zoo_dl_ies", "zoo_dl_ies_soft", "tex_dl_procedural", "tex_dl_noise", "tex_dl_noise2", "cornell_dl_lanczos", "cornell_dl_clamp", "simple_dl_bgtransp", "simple_dl_bgtransp_refract", "cornell_dl_dispersion", "cornell_pt_dispersion_norr"]
 

@@ -66,6 +66,20 @@ def test_group_members_sharing_one_gpu_sum_to_the_single_context_film(members):
         c.close(); g.close()
 
 
+def test_group_decides_adaptive_passes_on_the_summed_film():
+    """yafgpu_group_next_pass: the resampling mask comes from the SUMMED film on the first device and every member renders its tiles of it; the result is the
+    reference's adaptive film (tests/golden/cornell_dl_adaptive_variance.npz: four passes, variance windows, resampled floor)."""
+    from libyafaray_b200 import Group, capi, render_scene
+    from tests.test_gpu import _assert_film_matches
+    name = "cornell_dl_adaptive_variance"
+    gold = np.load(os.path.join(ou.GOLDEN, name + ".npz"))["film"]
+    g = Group([0, 0, 0], capi.FLAG_SHARE_DEVICE)
+    try:
+        _assert_film_matches(render_scene(pc.ADAPTIVE[name](), ctx=g), gold)
+    finally:
+        g.close()
+
+
 def test_group_rejects_bad_device_lists():
     from libyafaray_b200 import Group, capi
     with pytest.raises(capi.YafGpuError, match="listed twice"):
