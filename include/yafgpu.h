@@ -119,11 +119,10 @@ typedef enum yafgpu_material_type
 typedef enum yafgpu_texture_type
 {
 	YAFGPU_TEX_IMAGE = 0,
-	YAFGPU_TEX_BLEND = 1,    /* "blend"    texture_basic.cc:680-779: a gradient of the texture point (blend_type, use_flip_axis); a colour ramp is refused.
+	YAFGPU_TEX_BLEND = 1,    /* "blend"    texture_basic.cc:680-779: a gradient of the texture point (blend_type, use_flip_axis), optionally through a colour ramp.
 	                          * Its factory sets no adjustments. */
 	YAFGPU_TEX_RGB_CUBE = 2, /* "rgb_cube" texture_basic.cc:347-386: colour = the texture point clamped to [0,1]^3, with the adj_* adjustments */
-	/* noise-based procedurals over NoiseGenerator + turbulence__ (noise_generator.cc:182-630,799-811); they need yafgpu_scene_desc.noise_tables;
-	 * a colour ramp (use_color_ramp) is refused */
+	/* noise-based procedurals over NoiseGenerator + turbulence__ (noise_generator.cc:182-630,799-811); they need yafgpu_scene_desc.noise_tables */
 	YAFGPU_TEX_CLOUDS = 3,   /* "clouds" texture_basic.cc:96-171 */
 	YAFGPU_TEX_MARBLE = 4,   /* "marble" texture_basic.cc:177-250 */
 	YAFGPU_TEX_WOOD = 5,     /* "wood"   texture_basic.cc:257-343 */
@@ -192,7 +191,17 @@ typedef struct yafgpu_texture
 	/* distorted_noise: noise_type = "noise_type1" (the distortion), noise_type2 = "noise_type2" (the distorted basis) */
 	float distort;           /* "distort" */
 	int32_t noise_type2;
+	/* colour ramp of a procedural texture ("use_color_ramp" + "ramp_*", textureReadColorRamp__ texture_basic.cc:54-90; ColorRamp color_ramp.cc:31-164): the texture's
+	 * scalar picks a colour between the two items around it.  ramp_items = 0: no ramp.  The items are r, g, b, a, position, sorted by position as ColorRamp::addItem
+	 * keeps them; the first position must be <= 0 and the last >= 1 (getColorInterpolated reads in front of / behind the array otherwise). */
+	int32_t ramp_items;
+	int32_t ramp_mode;          /* YAFGPU_RAMP_RGB / HSV / HSL ("ramp_color_mode") */
+	int32_t ramp_interpolation; /* 0 constant, 1 linear ("ramp_interpolation": CONSTANT, anything else is linear) */
+	int32_t ramp_hue_interpolation; /* YAFGPU_RAMPHUE_* ("ramp_hue_interpolation": NEAR, FAR, CW, CCW) */
+	const float *ramp;          /* ramp_items * 5 floats */
 } yafgpu_texture;
+enum { YAFGPU_RAMP_RGB = 0, YAFGPU_RAMP_HSV = 1, YAFGPU_RAMP_HSL = 2 };
+enum { YAFGPU_RAMPHUE_NEAR = 0, YAFGPU_RAMPHUE_FAR = 1, YAFGPU_RAMPHUE_CW = 2, YAFGPU_RAMPHUE_CCW = 3 };
 
 typedef enum yafgpu_node_type
 {

@@ -136,21 +136,6 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 	if(f != pool.tex_index.end()) { index = f->second; return true; }
 	yafgpu_texture r;
 	memset(&r, 0, sizeof(r));
-	const BlendTexture *bt = dynamic_cast<const BlendTexture *>(t);
-	const RgbCubeTexture *ct = dynamic_cast<const RgbCubeTexture *>(t);
-	if(bt || ct)
-	{	// texture_basic.cc:680-779, 347-386: fields of the constructed objects
-		if(bt && bt->color_ramp_) { err = "a blend texture with a colour ramp is not implemented on the device"; return false; }
-		r.type = bt ? YAFGPU_TEX_BLEND : YAFGPU_TEX_RGB_CUBE;
-		if(bt) { r.blend_type = (int)bt->progression_type_; r.use_flip_axis = bt->use_flip_axis_; } // same enumerator order as YAFGPU_TEXBLEND_*
-		r.adj_intensity = t->adj_intensity_; r.adj_contrast = t->adj_contrast_; r.adj_saturation = t->adj_saturation_; r.adj_hue = t->adj_hue_;
-		r.adj_mult_red = t->adj_mult_factor_red_; r.adj_mult_green = t->adj_mult_factor_green_; r.adj_mult_blue = t->adj_mult_factor_blue_;
-		r.adj_clamp = t->adj_clamp_;
-		index = (int)pool.textures.size();
-		pool.textures.push_back(r);
-		pool.tex_index[t] = index;
-		return true;
-	}
 	auto noiseBasis = [&](const NoiseGenerator *ng, int &out) -> bool
 	{	// the basis is recognised by the dynamic type newNoise__ (texture_basic.cc:24-52) constructed
 		if(dynamic_cast<const StdPerlinNoiseGenerator *>(ng)) out = YAFGPU_NOISE_STDPERLIN;
@@ -172,12 +157,41 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 		r.adj_clamp = t->adj_clamp_;
 	};
 	auto done = [&]() { index = (int)pool.textures.size(); pool.textures.push_back(r); pool.tex_index[t] = index; return true; };
+	auto colorRamp = [&]() -> bool
+	{	// ColorRamp (include/common/color_ramp.h): the items as addItem keeps them (sorted by position), the enums in declaration order
+		const ColorRamp *cr = t->color_ramp_;
+		if(!cr) return true;
+		pool.texels.emplace_back();
+		std::vector<float> &v = pool.texels.back();
+		for(const ColorRampItem &it : cr->ramp_) { const Rgba c = it.color(); v.push_back(c.r_); v.push_back(c.g_); v.push_back(c.b_); v.push_back(c.a_); v.push_back(it.position()); }
+		r.ramp_items = (int)cr->ramp_.size(); r.ramp = v.data();
+		r.ramp_mode = (int)cr->mode_;                                      // Rgb, Hsv, Hsl
+		r.ramp_interpolation = cr->interpolation_ == ColorRamp::Constant ? 0 : 1;
+		r.ramp_hue_interpolation = cr->hue_interpolation_ == ColorRamp::Far ? YAFGPU_RAMPHUE_FAR : cr->hue_interpolation_ == ColorRamp::Clockwise ? YAFGPU_RAMPHUE_CW :
+		                           cr->hue_interpolation_ == ColorRamp::Counterclockwise ? YAFGPU_RAMPHUE_CCW : YAFGPU_RAMPHUE_NEAR;
+		return true;
+	};
+	const BlendTexture *bt = dynamic_cast<const BlendTexture *>(t);
+	const RgbCubeTexture *ct = dynamic_cast<const RgbCubeTexture *>(t);
+	if(bt || ct)
+	{	// texture_basic.cc:680-779, 347-386: fields of the constructed objects
+		if(bt && !colorRamp()) return false;
+		r.type = bt ? YAFGPU_TEX_BLEND : YAFGPU_TEX_RGB_CUBE;
+		if(bt) { r.blend_type = (int)bt->progression_type_; r.use_flip_axis = bt->use_flip_axis_; } // same enumerator order as YAFGPU_TEXBLEND_*
+		r.adj_intensity = t->adj_intensity_; r.adj_contrast = t->adj_contrast_; r.adj_saturation = t->adj_saturation_; r.adj_hue = t->adj_hue_;
+		r.adj_mult_red = t->adj_mult_factor_red_; r.adj_mult_green = t->adj_mult_factor_green_; r.adj_mult_blue = t->adj_mult_factor_blue_;
+		r.adj_clamp = t->adj_clamp_;
+		index = (int)pool.textures.size();
+		pool.textures.push_back(r);
+		pool.tex_index[t] = index;
+		return true;
+	}
 	const VoronoiTexture *vot = dynamic_cast<const VoronoiTexture *>(t);
 	const MusgraveTexture *mut = dynamic_cast<const MusgraveTexture *>(t);
 	const DistortedNoiseTexture *dnt = dynamic_cast<const DistortedNoiseTexture *>(t);
 	if(vot || mut || dnt)
 	{	// texture_basic.cc:391-673: the members of the constructed objects
-		if(t->color_ramp_) { err = "a procedural texture with a colour ramp is not implemented on the device"; return false; }
+		if(!colorRamp()) return false;
 		if(vot)
 		{
 			r.type = YAFGPU_TEX_VORONOI; r.noise_size = vot->size_; r.color_type = vot->coltype_; r.intensity_scale = vot->iscale_; r.mk_exponent = vot->v_gen_.mk_exp_;
@@ -216,7 +230,7 @@ bool textureRecord(const Texture *t, NodePool &pool, int &index, std::string &er
 	const WoodTexture *wdt = dynamic_cast<const WoodTexture *>(t);
 	if(clt || mbt || wdt)
 	{	// texture_basic.cc:96-343: the members the constructors left behind; the basis is recognised by the dynamic type of n_gen_ (newNoise__ :24-52)
-		if(t->color_ramp_) { err = "a clouds / marble / wood texture with a colour ramp is not implemented on the device"; return false; }
+		if(!colorRamp()) return false;
 		if(!noiseBasis(clt ? clt->n_gen_ : mbt ? mbt->n_gen_ : wdt->n_gen_, r.noise_type)) return false;
 		const Rgb c1 = clt ? clt->color_1_ : mbt ? mbt->color_1_ : wdt->color_1_, c2 = clt ? clt->color_2_ : mbt ? mbt->color_2_ : wdt->color_2_;
 		r.color1[0] = c1.r_; r.color1[1] = c1.g_; r.color1[2] = c1.b_; r.color2[0] = c2.r_; r.color2[1] = c2.g_; r.color2[2] = c2.b_;

@@ -113,7 +113,8 @@ class Texture(C.Structure):
                 ("clouds_bias", i32), ("turbulence", f32), ("sharpness", f32), ("wave_shape", i32), ("wood_rings", i32),
                 ("vor_weight", f32 * 4), ("mk_exponent", f32), ("intensity_scale", f32), ("distance_metric", i32), ("color_type", i32),
                 ("musgrave_type", i32), ("mus_h", f32), ("mus_lacunarity", f32), ("mus_octaves", f32), ("mus_offset", f32), ("mus_gain", f32),
-                ("distort", f32), ("noise_type2", i32)]
+                ("distort", f32), ("noise_type2", i32),
+                ("ramp_items", i32), ("ramp_mode", i32), ("ramp_interpolation", i32), ("ramp_hue_interpolation", i32), ("ramp", C.POINTER(C.c_float))]
 
 
 class ShaderNode(C.Structure):

@@ -460,6 +460,14 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 	{
 		float4 *d_px = nullptr;
 		h_tex[i].noise = c->d_noise;
+		h_tex[i].ramp = nullptr;
+		if(h_tex[i].n_ramp > 0)
+		{
+			float *d_ramp = nullptr;
+			YG_CUDA(c, upload(d_ramp, desc->textures[i].ramp, (size_t)5 * h_tex[i].n_ramp, st));
+			c->tex_ptrs.push_back(d_ramp);
+			h_tex[i].ramp = d_ramp;
+		}
 		if(h_tex[i].type != YAFGPU_TEX_IMAGE) { h_tex[i].tex = nullptr; continue; } // procedural: no texels
 		YG_CUDA(c, upload(d_px, (const float4 *)desc->textures[i].rgba, (size_t)h_tex[i].w * h_tex[i].h, st));
 		c->tex_ptrs.push_back(d_px);

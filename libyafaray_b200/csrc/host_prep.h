@@ -208,6 +208,16 @@ inline bool prepTexture(const yafgpu_texture &t, TexDev &d, std::string &err)
 {
 	memset(&d, 0, sizeof(d));
 	d.type = t.type;
+	if(t.ramp_items != 0)
+	{	// ColorRamp::getColorInterpolated color_ramp.cc:84-164 takes std::prev of the lower bound and dereferences the lower bound itself: defined only while an item sits
+		// at or in front of every position in [0, 1] and one at or behind it
+		if(t.type == YAFGPU_TEX_IMAGE || t.type == YAFGPU_TEX_RGB_CUBE) { err = "a colour ramp on an image / rgb_cube texture (the reference reads none there)"; return false; }
+		if(t.ramp_items < 2 || t.ramp_items > 64 || !t.ramp) { err = "colour ramp: 2..64 items"; return false; }
+		for(int k = 1; k < t.ramp_items; ++k) if(!(t.ramp[5 * k + 4] >= t.ramp[5 * (k - 1) + 4])) { err = "colour ramp: items must be sorted by position"; return false; }
+		if(!(t.ramp[4] <= 0.f) || !(t.ramp[5 * (t.ramp_items - 1) + 4] >= 1.f)) { err = "colour ramp: the first item must sit at position <= 0 and the last at >= 1 (the reference reads outside the ramp otherwise)"; return false; }
+		if(t.ramp_mode < YAFGPU_RAMP_RGB || t.ramp_mode > YAFGPU_RAMP_HSL || t.ramp_hue_interpolation < YAFGPU_RAMPHUE_NEAR || t.ramp_hue_interpolation > YAFGPU_RAMPHUE_CCW) { err = "colour ramp: mode / hue interpolation"; return false; }
+		d.n_ramp = t.ramp_items; d.ramp_mode = t.ramp_mode; d.ramp_interp = t.ramp_interpolation ? 1 : 0; d.ramp_hue = t.ramp_hue_interpolation;
+	}
 	if(t.type == YAFGPU_TEX_BLEND)
 	{	// BlendTexture::factory texture_basic.cc:759-776: setAdjustments is called with the neutral values, whatever the parameters say
 		if(t.blend_type < YAFGPU_TEXBLEND_LINEAR || t.blend_type > YAFGPU_TEXBLEND_RADIAL) { err = "blend texture: progression type"; return false; }

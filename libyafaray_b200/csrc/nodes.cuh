@@ -298,6 +298,66 @@ YG_D Rgba4 imgInterpolate(const TexDev &t, float px, float py)
 	return ((w11 * c11 + w12 * c12) + w21 * c21) + w22 * c22;
 }
 
+// ---- ColorRamp::getColorInterpolated color_ramp.cc:84-164 --------------------------------------------------------------------------------------
+YG_D void rgbToHsl(Rgba4 c, float &h, float &s, float &l)
+{	// color.h:509-529
+	const float r1 = fmaxf(c.r, 0.f), g1 = fmaxf(c.g, 0.f), b1 = fmaxf(c.b, 0.f);
+	const float mx = fmaxf(fmaxf(r1, g1), b1), mn = fminf(fminf(r1, g1), b1);
+	const float range = mx - mn;
+	l = 0.5f * (mx + mn);
+	if(fabsf(range) < 1.0e-6f) { h = 0.f; s = 0.f; }
+	else if(mx == r1) { h = fmodf((g1 - b1) / range, 6.f); s = range / fmaxf((1.f - fabsf((2.f * l) - 1)), 1.0e-6f); }
+	else if(mx == g1) { h = ((b1 - r1) / range) + 2.f; s = range / fmaxf((1.f - fabsf((2.f * l) - 1)), 1.0e-6f); }
+	else if(mx == b1) { h = ((r1 - g1) / range) + 4.f; s = range / fmaxf((1.f - fabsf((2.f * l) - 1)), 1.0e-6f); }
+	else { h = 0.f; s = 0.f; l = 0.f; }
+	if(h < 0.f) h += 6.f;
+}
+// interpolationLinear__ color_ramp.cc:58-82: item 1 is the lower bound (the item at or behind `pos`), item 2 the one in front of it
+YG_D float rampLerp(float pos, float v1, float p1, float v2, float p2)
+{
+	if(pos == p1 || p1 == p2) return v1;
+	if(pos == p2) return v2;
+	return v1 + (((pos - p1) / (p2 - p1)) * (v2 - v1));
+}
+YG_D Rgba4 rampColor(const TexDev &t, float pos)
+{
+	const float *rp = t.ramp;
+	auto item = [&](int k) { return mk4(rp[5 * k], rp[5 * k + 1], rp[5 * k + 2], rp[5 * k + 3]); };
+	if(pos < 0.f) return item(0);
+	if(pos > 1.f) return item(t.n_ramp - 1);
+	int cur = 0;
+	while(cur < t.n_ramp - 1 && rp[5 * cur + 4] < pos) ++cur;   // std::lower_bound over the positions (prepTexture guarantees a last position >= 1)
+	// pos sits exactly on the first item (position <= 0 <= pos): every interpolation below returns item 1's value, whatever std::prev(begin) holds in the reference
+	const int prev = cur > 0 ? cur - 1 : cur;
+	const Rgba4 c1 = item(cur), c2 = item(prev);
+	const float p1 = rp[5 * cur + 4], p2 = rp[5 * prev + 4];
+	if(t.ramp_mode == YAFGPU_RAMP_RGB)
+	{
+		if(!t.ramp_interp) return c1;
+		if(pos == p1 || p1 == p2) return c1;
+		if(pos == p2) return c2;
+		const float f = (pos - p1) / (p2 - p1);
+		return c1 + (f * (c2 - c1));
+	}
+	float h1 = 0.f, s1 = 0.f, v1 = 0.f, h2 = 0.f, s2 = 0.f, v2 = 0.f;
+	if(t.ramp_mode == YAFGPU_RAMP_HSV) { rgbToHsv(c1, h1, s1, v1); rgbToHsv(c2, h2, s2, v2); }
+	else { rgbToHsl(c1, h1, s1, v1); rgbToHsl(c2, h2, s2, v2); }
+	const float s = rampLerp(pos, s1, p1, s2, p2), v = rampLerp(pos, v1, p1, v2, p2), a = rampLerp(pos, c1.a, p1, c2.a, p2);
+	const int hi = t.ramp_hue;
+	if(hi == YAFGPU_RAMPHUE_CW && h1 < h2) h1 += 6.f;
+	else if(hi == YAFGPU_RAMPHUE_CCW && h1 > h2) h2 += 6.f;
+	else if(hi == YAFGPU_RAMPHUE_NEAR && h1 < h2 && (h2 - h1) > 3.f) h1 += 6.f;
+	else if(hi == YAFGPU_RAMPHUE_NEAR && h1 > h2 && (h2 - h1) < -3.f) h2 += 6.f;
+	else if(hi == YAFGPU_RAMPHUE_FAR && h1 < h2 && (h2 - h1) < 3.f) h1 += 6.f;
+	else if(hi == YAFGPU_RAMPHUE_FAR && h1 > h2 && (h2 - h1) > -3.f) h2 += 6.f;
+	float h = rampLerp(pos, h1, p1, h2, p2);
+	if(h < 0.f) h += 6.f; else if(h > 6.f) h -= 6.f;
+	Rgba4 result = mk4(0.f, 0.f, 0.f, 1.f);
+	hsvToRgb(result, h, s, v);   // the HSL mode converts back with hsvToRgb as well (color_ramp.cc:158)
+	result.a = a;
+	return result;
+}
+
 // ---- noise bases and the procedural textures over them ------------------------------------------------------------------------
 // NoiseGenerator::operator() of the five families the factories can construct (noise_generator.cc:182-630), evaluated with the reference's own
 // lattice tables (NoiseTables).  Every double-typed literal of the reference is kept as one: `0.5 + 0.5 * nv`, `1.0 - 3.0 * c + 2.0 * c * o`,
@@ -506,6 +566,7 @@ YG_D Rgba4 voronoiTexColor(const TexDev &t, V3 p)
 	float da[4]; V3 pa[4];
 	voronoiFeatures(*t.noise, t.dist_metric, t.mk_exp, p * t.size, da, pa);
 	const float inte = voronoiIntensity(t, da);
+	if(t.n_ramp) return texAdjustColor(t, rampColor(t, inte));
 	if(!t.color_type) return texAdjustColor(t, mk4(inte, inte, inte, inte));
 	Rgba4 col = mk4(0.f, 0.f, 0.f, 0.f);   // Rgba(0.0): alpha 0 as well
 	for(int k = 0; k < 4; ++k) col = col + t.vaw[k] * cellNoiseColor(*t.noise, pa[k]);
@@ -670,11 +731,12 @@ YG_D float blendTexFloat(const TexDev &t, V3 p)
 // ImageTexture::getColor(Point3) :75-87; BlendTexture::getColor texture_basic.cc:753-757 (no colour ramp); RgbCubeTexture::getColor :347-354
 YG_D Rgba4 texGetColor(const TexDev &t, V3 p)
 {
-	if(t.type == YAFGPU_TEX_BLEND) { const float f = blendTexFloat(t, p); return mk4(f, f, f, 1.f); }
+	if(t.type == YAFGPU_TEX_BLEND) { const float f = blendTexFloat(t, p); return t.n_ramp ? rampColor(t, f) : mk4(f, f, f, 1.f); }
 	if(t.type >= YAFGPU_TEX_CLOUDS)
 	{	// color_1_ + getFloat(p) * (color_2_ - color_1_), then applyColorAdjustments (texture_basic.cc:122-126,208-212,293-297)
 		if(t.type == YAFGPU_TEX_VORONOI) return voronoiTexColor(t, p);
 		const float f = noiseTexFloat(t, p);
+		if(t.n_ramp) return texAdjustColor(t, rampColor(t, f));
 		const Rgba4 c = mk4(t.color1[0] + f * (t.color2[0] - t.color1[0]), t.color1[1] + f * (t.color2[1] - t.color1[1]), t.color1[2] + f * (t.color2[2] - t.color1[2]), 1.f);
 		return texAdjustColor(t, c);
 	}

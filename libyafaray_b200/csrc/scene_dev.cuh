@@ -125,6 +125,8 @@ struct TexDev
 	float vw[4], vaw[4], iscale, mk_exp; int dist_metric, color_type;
 	int mus_type; float mus_h, mus_lac, mus_oct, mus_offset, mus_gain;
 	float distort; int noise_type2;
+	// colour ramp (color_ramp.cc): n_ramp items of r, g, b, a, position
+	const float *ramp; int n_ramp, ramp_mode, ramp_interp, ramp_hue;
 };
 
 // One shader node after its factory + configInputs; in1/in2/fac are stack indices (-1 = constant input)

@@ -455,6 +455,25 @@ class Interface:
         self._nodes += recs
         m.node_count = len(recs)
 
+    def _color_ramp(self, t, p):
+        """textureReadColorRamp__ (texture_basic.cc:54-90) + ColorRamp's constructor and addItem (color_ramp.cc:31-56): items sorted by position."""
+        g = self._g
+        n = int(g(p, "ramp_num_items", 0))
+        if not g(p, "use_color_ramp", False) or n <= 0:
+            return
+        items = []
+        for i in range(n):
+            col = g(p, "ramp_item_%d_color" % i, (0.0, 0.0, 0.0, 1.0))
+            items.append((np.float32(g(p, "ramp_item_%d_position" % i, 0.0)), [np.float32(col[0]), np.float32(col[1]), np.float32(col[2]), np.float32(g(p, "ramp_item_%d_alpha" % i, 1.0))]))
+        items.sort(key=lambda it: it[0])
+        arr = np.array([c + [pos] for pos, c in items], np.float32)
+        self._tex_keep.append(arr)
+        t.ramp_items, t.ramp = n, arr.ctypes.data_as(C.POINTER(C.c_float))
+        # the constructor accepts exactly the upper- and the lower-case spelling of each keyword
+        t.ramp_mode = {"HSV": 1, "hsv": 1, "HSL": 2, "hsl": 2}.get(g(p, "ramp_color_mode", ""), 0)
+        t.ramp_interpolation = 0 if g(p, "ramp_interpolation", "") in ("CONSTANT", "constant") else 1
+        t.ramp_hue_interpolation = {"FAR": 1, "far": 1, "CW": 2, "cw": 2, "CCW": 3, "ccw": 3}.get(g(p, "ramp_hue_interpolation", ""), 0)
+
     def _texture_index(self, name):
         if name in self._tex_index:
             return self._tex_index[name]
@@ -464,8 +483,7 @@ class Interface:
             t = capi.Texture()
             t.adj_intensity = t.adj_contrast = t.adj_saturation = t.adj_mult_red = t.adj_mult_green = t.adj_mult_blue = 1.0
             if ttype == "blend":
-                if g(p, "use_color_ramp", False):
-                    raise NotImplementedError("blend texture with a colour ramp is not implemented on the device")
+                self._color_ramp(t, p)
                 t.type, t.blend_type = capi.TEX_BLEND, capi.TEXBLEND.get(g(p, "stype", ""), 0)   # unknown strings: linear
                 t.use_flip_axis = int(g(p, "use_flip_axis", False))
             else:
@@ -478,9 +496,8 @@ class Interface:
             self._texs.append(t)
             return self._tex_index[name]
         if ttype in ("voronoi", "musgrave", "distorted_noise"):   # texture_basic.cc:456-503, 553-596, 635-673 (factories)
-            if g(p, "use_color_ramp", False):
-                raise NotImplementedError("%s texture with a colour ramp is not implemented on the device" % ttype)
             t = capi.Texture()
+            self._color_ramp(t, p)
             t.type = {"voronoi": capi.TEX_VORONOI, "musgrave": capi.TEX_MUSGRAVE, "distorted_noise": capi.TEX_DISTORTED_NOISE}[ttype]
             noise = lambda nt: capi.NOISE.get(nt, 3 if "voronoi" in nt else 0)
             c1, c2 = g(p, "color1", (0.0, 0.0, 0.0)), g(p, "color2", (1.0, 1.0, 1.0))
@@ -511,9 +528,8 @@ class Interface:
             self._texs.append(t)
             return self._tex_index[name]
         if ttype in ("clouds", "marble", "wood"):   # texture_basic.cc:96-171, 177-250, 257-343 (factories), newNoise__ :24-52
-            if g(p, "use_color_ramp", False):
-                raise NotImplementedError("%s texture with a colour ramp is not implemented on the device" % ttype)
             t = capi.Texture()
+            self._color_ramp(t, p)
             t.type = {"clouds": capi.TEX_CLOUDS, "marble": capi.TEX_MARBLE, "wood": capi.TEX_WOOD}[ttype]
             nt = g(p, "noise_type", "")
             t.noise_type = capi.NOISE.get(nt, 3 if "voronoi" in nt else 0)

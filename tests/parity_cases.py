@@ -339,8 +339,8 @@ def textured_scene(width=96, height=54, spp=2, integrator="directlighting", tex=
     elif variant == "procedural":
         _textured_procedural_materials(y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
-    elif variant in ("noise", "noise2"):
-        (_textured_noise_materials if variant == "noise" else _textured_noise2_materials)(y, sd, node, mapper, layer)
+    elif variant in ("noise", "noise2", "ramp"):
+        {"noise": _textured_noise_materials, "noise2": _textured_noise2_materials, "ramp": _textured_ramp_materials}[variant](y, sd, node, mapper, layer)
         box_mats = (("b0", True, False), ("b1", False, False), ("b2", True, False), ("b3", True, False), ("b4", True, False), ("b5", False, True))
     elif variant == "materials":
         _textured_other_materials(y, sd, node, mapper, layer)
@@ -523,6 +523,60 @@ def _textured_noise2_materials(y, sd, node, mapper, layer):
     layer("l5c", "m5c", mode=0, colfac=0.8, use_alpha=True)
     mapper("m5", texture="v_int", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0), bump_strength=2.0)
     mapper("m5c", texture="v_col1", texco="uv", scale=(3.0, 3.0, 1.0))
+    y.createMaterial("b5")
+
+
+def _textured_ramp_materials(y, sd, node, mapper, layer):
+    """Colour ramps (ColorRamp::getColorInterpolated, color_ramp.cc:84-164) on every texture type that reads one: RGB linear / constant, HSV and HSL with the four hue
+    interpolations, ramp alpha through a use_alpha layer, items given out of order, scalars beyond [0, 1] (negated cloud bias, Musgrave)."""
+    def tex(name, typ, ramp, mode="RGB", interp="LINEAR", hue="NEAR", **kw):
+        y.paramsClearAll(); y.paramsSetString("type", typ); _set_params(y, kw)
+        y.paramsSetBool("use_color_ramp", True); y.paramsSetString("ramp_color_mode", mode); y.paramsSetString("ramp_interpolation", interp)
+        y.paramsSetString("ramp_hue_interpolation", hue); y.paramsSetInt("ramp_num_items", len(ramp))
+        for i, (pos, col) in enumerate(ramp):
+            y.paramsSetColor("ramp_item_%d_color" % i, col[0], col[1], col[2], 1.0); y.paramsSetFloat("ramp_item_%d_alpha" % i, col[3]); y.paramsSetFloat("ramp_item_%d_position" % i, pos)
+        y.createTexture(name)
+    fire = [(0.0, (0.05, 0.0, 0.0, 1.0)), (0.4, (0.9, 0.1, 0.0, 1.0)), (0.7, (1.0, 0.8, 0.1, 0.6)), (1.0, (1.0, 1.0, 0.9, 0.2))]
+    unordered = [(1.0, (0.1, 0.2, 0.9, 1.0)), (0.0, (0.9, 0.9, 0.2, 1.0)), (0.5, (0.1, 0.8, 0.3, 0.5))]
+    two = [(0.0, (0.9, 0.1, 0.1, 1.0)), (1.0, (0.1, 0.1, 0.9, 1.0))]
+    tex("r_blend", "blend", fire, stype="lin")
+    tex("r_clouds", "clouds", unordered, noise_type="blender", depth=2, size=3.0)
+    tex("r_clouds_neg", "clouds", fire, interp="CONSTANT", noise_type="newperlin", depth=1, size=2.0, bias="positive")
+    tex("r_marble", "marble", two, mode="HSV", hue="NEAR", noise_type="stdperlin", depth=2, size=2.0, turbulence=3.0)
+    tex("r_wood", "wood", two, mode="HSV", hue="FAR", noise_type="blender", depth=1, size=2.0, turbulence=1.0, adj_saturation=0.8)
+    tex("r_voronoi", "voronoi", unordered, mode="HSV", hue="CW", size=3.0, weight1=1.0, weight2=0.3)
+    tex("r_musgrave", "musgrave", fire, mode="HSV", hue="CCW", noise_type="newperlin", musgrave_type="fBm", octaves=3.0, size=2.0, intensity=0.7)
+    tex("r_dist", "distorted_noise", unordered, mode="HSL", noise_type1="blender", noise_type2="stdperlin", distort=1.0, size=2.0)
+    tex("r_blend_hsl", "blend", two, mode="hsl", hue="ccw", stype="sphere")
+    sd("ground", color=(0.7, 0.7, 0.7, 1.0), diffuse_shader="gl")
+    layer("gl", "gm", mode=0, colfac=0.9, upper_color=(0.3, 0.5, 0.8, 1.0))
+    mapper("gm", texture="r_marble", texco="global", scale=(0.3, 0.3, 0.3))
+    y.createMaterial("ground")
+    sd("b0", color=(0.9, 0.9, 0.9, 1.0), diffuse_shader="l0")
+    layer("l0", "m0", mode=0, colfac=0.9, use_alpha=True, upper_color=(0.2, 0.2, 0.2, 1.0))
+    mapper("m0", texture="r_blend", texco="orco")
+    y.createMaterial("b0")
+    sd("b1", color=(0.8, 0.6, 0.4, 1.0), diffuse_shader="x1")
+    node(type="mix", name="x1", input1="m1", input2="m1b", value=0.5, mode=0)
+    mapper("m1", texture="r_clouds", texco="global", scale=(0.6, 0.6, 0.6))
+    mapper("m1b", texture="r_clouds_neg", texco="global", scale=(0.4, 0.4, 0.4), offset=(0.3, 0.0, 0.0))
+    y.createMaterial("b1")
+    sd("b2", color=(0.5, 0.8, 0.5, 1.0), diffuse_shader="l2b")
+    layer("l2b", "m2b", mode=0, colfac=0.8)
+    mapper("m2b", texture="r_wood", texco="orco", scale=(1.5, 1.5, 1.5), offset=(0.25, 0.25, 0.25))
+    y.createMaterial("b2")
+    sd("b3", color=(0.8, 0.8, 0.8, 1.0), diffuse_shader="x3")
+    node(type="mix", name="x3", input1="m3", input2="m3b", value=0.5, mode=0)
+    mapper("m3", texture="r_voronoi", texco="orco", scale=(1.8, 1.8, 1.8))
+    mapper("m3b", texture="r_musgrave", texco="orco")
+    y.createMaterial("b3")
+    sd("b4", color=(0.7, 0.7, 0.9, 1.0), diffuse_shader="l4c")
+    layer("l4c", "m4c", mode=0, colfac=0.9, use_alpha=True, upper_color=(0.9, 0.4, 0.3, 1.0))
+    mapper("m4c", texture="r_dist", texco="orco")
+    y.createMaterial("b4")
+    sd("b5", color=(0.9, 0.8, 0.6, 1.0), diffuse_shader="l5c")
+    layer("l5c", "m5c", mode=0, colfac=0.8)
+    mapper("m5c", texture="r_blend_hsl", texco="uv", scale=(2.0, 2.0, 1.0), offset=(-0.5, -0.5, 0.0))
     y.createMaterial("b5")
 
 
@@ -768,6 +822,7 @@ EXACT["tex_pt_procedural_norr"] = lambda: textured_scene(96, 54, 4, variant="pro
 EXACT["tex_dl_noise"] = lambda: textured_scene(96, 54, 2, variant="noise")
 EXACT["tex_dl_noise2"] = lambda: textured_scene(96, 54, 2, variant="noise2")
 EXACT["tex_pt_noise2_norr"] = lambda: textured_scene(96, 54, 4, variant="noise2", integrator="pathtracing")
+EXACT["tex_dl_ramp"] = lambda: textured_scene(96, 54, 2, variant="ramp")
 EXACT["tex_pt_noise_norr"] = lambda: textured_scene(96, 54, 4, variant="noise", integrator="pathtracing")
 EXACT["tex_dl_materials"] = lambda: textured_scene(96, 54, 2, variant="materials", raydepth=4)
 EXACT["tex_pt_materials_norr"] = lambda: textured_scene(96, 54, 4, variant="materials", integrator="pathtracing", raydepth=4)

@@ -128,7 +128,7 @@ FRONTEND_CASES = ["simple_dl_gauss", "cornell_dl_glass", "cornell_dl_mitchell", 
                   "zoo_dl_hdr_ibl", "zoo_dl_hdr_angular", "cornell_dl_adaptive", "cornell_dl_adaptive_dark", "cornell_dl_adaptive_curve", "cornell_dl_adaptive_variance",
                   "simple_dl_adaptive_gauss", "zoo_dl_directional", "zoo_dl_spot_soft", "zoo_dl_sphere",
                   "zoo_dl_gradient_ibl", "zoo_dl_cam_ortho", "zoo_dl_cam_architect", "zoo_dl_cam_angular_stereo", "zoo_dl_cam_equirect",
-                  "tex_dl_basic", "tex_dl_modes_c", "tex_dl_adjust", "tex_pt_norr", "tex_dl_materials", "zoo_dl_beer", "tex_dl_mask", "tex_dl_camera_coords", "zoo_dl_portal_hdr", "zoo_dl_ies", "zoo_dl_ies_soft", "tex_dl_procedural", "tex_dl_noise", "tex_dl_noise2", "cornell_dl_lanczos", "cornell_dl_clamp", "simple_dl_bgtransp", "simple_dl_bgtransp_refract", "cornell_dl_dispersion", "cornell_pt_dispersion_norr"]
+                  "tex_dl_basic", "tex_dl_modes_c", "tex_dl_adjust", "tex_pt_norr", "tex_dl_materials", "zoo_dl_beer", "tex_dl_mask", "tex_dl_camera_coords", "zoo_dl_portal_hdr", "zoo_dl_ies", "zoo_dl_ies_soft", "tex_dl_procedural", "tex_dl_noise", "tex_dl_noise2", "tex_dl_ramp", "cornell_dl_lanczos", "cornell_dl_clamp", "simple_dl_bgtransp", "simple_dl_bgtransp_refract", "cornell_dl_dispersion", "cornell_pt_dispersion_norr"]
 
 
 @pytest.mark.skipif(ou.gpu_frontend_bin() is None, reason="oracle/_ref/yaf_xml_gpu not built (needs the reference sources)")
