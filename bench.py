@@ -56,7 +56,7 @@ def config_dict(args, world, spp_per_step):
             "triangles": args.tris, "integrator": "pathtracing", "path_samples": 1, "bounces": 8, "raydepth": 8, "rr_min_bounces": 2,
             "lights": "sunlight + arealight, samples=1", "materials": "glossy x2, coated_glossy x2, rough_glass, shinydiffusemat, light_mat",
             "spp_per_step_per_gpu": spp_per_step, "camera_samples_per_step": args.width * args.height * spp_per_step * world,
-            "partition": "tiles32 interleaved x%d, scene replicated" % world,
+            "partition": "8x8-pixel blocks interleaved x%d (shifted rows), scene replicated" % world,
             "cache": "working set (1.1 GB of BVH + triangles, > 1 GB of wavefront queues per wave) exceeds the 126 MB L2; no explicit flush"}
 
 

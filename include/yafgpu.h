@@ -566,8 +566,9 @@ typedef struct yafgpu_pass_desc
 	/* sub-range of the pass's samples to render now: sample indices [sample_begin, sample_end); both 0 = all.
 	 * Lets a caller split one pass into bounded steps without changing any sample's random numbers. */
 	int32_t sample_begin, sample_end;
-	/* image partition for multi-GPU: this context renders tiles t with (t % part_count) == part_index, tiles being the
-	 * tile_size x tile_size raster grid of ImageSplitter (imagesplitter.cc:37-50).  part_count <= 1 = whole image. */
+	/* image partition for multi-GPU: this context renders the blocks (tx, ty) with (tx + ty * stride) % part_count == part_index of a raster grid of
+	 * min(tile_size, 8)-pixel square blocks (the shape of ImageSplitter's tile grid, imagesplitter.cc:37-50); stride = the integer nearest 0.618 * part_count that is
+	 * coprime with it, so that every part walks through all columns.  The parts of one pass are disjoint and cover the image.  part_count <= 1 = whole image. */
 	int32_t part_index, part_count;
 } yafgpu_pass_desc;
 
@@ -691,7 +692,7 @@ int yafgpu_host_unregister(void *ptr);
  * Replaces, for a single 8-GPU node, what the reference does with worker threads pulling tiles from ImageSplitter
  * (integrator_tiled.cc:223-259, imagesplitter.cc:37-50) and, across machines, with the sum of accumulator films
  * (ImageFilm::imageFilmLoadAllInFolder, imagefilm.cc:1506-1535): the scene is replicated, member k of N renders the
- * tile_size x tile_size raster tiles t with t mod N == k of every pass, and after each pass the members' films are summed on the
+ * interleaved pixel blocks of every pass that yafgpu_pass_desc.part_index / part_count describe, and after each pass the members' films are summed on the
  * first device (peer copies over NVLink + an add kernel, asynchronous to the host).  Every call mirrors the single-context call of the
  * same name; `yafgpu_group_read_film` returns the SUMMED film.  A group of one device behaves exactly like a plain context. */
 typedef struct yafgpu_group yafgpu_group;

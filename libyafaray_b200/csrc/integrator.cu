@@ -1085,23 +1085,40 @@ static cudaError_t allocWavefront(yafgpu_ctx *c, int wave_cap, int task_cap, int
 	return cudaSuccess;
 }
 
+// Owner of tile (tx, ty) among `n` partitions: (tx + ty * stride) mod n with stride = the integer nearest to 0.618 n that is coprime with n.  The plain raster
+// rule (t mod n) gives a partition whole columns of tiles whenever the row length shares a factor with n (60 tiles per row, 8 GPUs: ranks k and k + 4 own the same
+// columns), and the cost of a tile varies mostly across the frame: the slowest partition of the bench frame was 6 % above the mean.  The shifted rule walks every
+// partition through all columns within n rows (tools/partition_balance.py).  Same rule in libyafaray_b200/parallel.py owner_map.
+#ifndef YG_PARTITION_UNIT
+#define YG_PARTITION_UNIT 8
+#endif
+static int partitionStride(int n)
+{
+	auto gcd = [](int a, int b) { while(b) { const int t = a % b; a = b; b = t; } return a; };
+	int s = std::max(1, (int)floor(0.618 * n + 0.5));
+	while(gcd(s, n) != 1) ++s;
+	return s % n ? s % n : 1;
+}
+
 // pixel list of a pass in tile order: ImageSplitter raster tiles (imagesplitter.cc:37-50), rows inside a tile
 static int buildPixelList(yafgpu_ctx *c, const yafgpu_pass_desc *p, size_t &n_out)
 {
 	Wavefront &w = c->wf;
 	const FilmDev &f = c->film;
-	const int ts = c->tile_size;
 	const int part_count = p->part_count > 1 ? p->part_count : 1, part_index = p->part_count > 1 ? p->part_index : 0;
+	// a partitioned pass interleaves blocks of at most 8 x 8 pixels: the finer the unit, the closer the partitions' costs (bench frame, 8 parts: slowest partition
+	// 3.8 % above the mean with 32 x 32 tiles, 2.2 % with 8 x 8; tools/partition_balance.py); an unpartitioned pass walks the reference's tile_size grid
+	const int ts = part_count > 1 ? std::min(c->tile_size, YG_PARTITION_UNIT) : c->tile_size;
 	const bool masked = p->adaptive && p->resample_mask;
 	std::vector<int> key = {f.w, f.h, f.cx0, f.cy0, ts, part_index, part_count};
 	if(!masked && w.pixels && w.pixels_key == key) { n_out = w.pixels_n; return YAFGPU_OK; }
 	std::vector<uint32_t> px;
 	px.reserve((size_t)f.w * f.h / part_count + 1024);
 	const int ntx = (f.w + ts - 1) / ts, nty = (f.h + ts - 1) / ts;
+	const int pstride = partitionStride(part_count);
 	for(int ty = 0; ty < nty; ++ty) for(int tx = 0; tx < ntx; ++tx)
 	{
-		const int t = ty * ntx + tx;
-		if(t % part_count != part_index) continue;
+		if(part_count > 1 && (tx + ty * pstride) % part_count != part_index) continue;
 		const int x0 = tx * ts, y0 = ty * ts, x1 = std::min(x0 + ts, f.w), y1 = std::min(y0 + ts, f.h);
 		for(int y = y0; y < y1; ++y) for(int x = x0; x < x1; ++x)
 		{

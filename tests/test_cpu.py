@@ -146,7 +146,11 @@ def test_tile_owner_map_partitions_image():
     from libyafaray_b200 import parallel
     om = parallel.owner_map(100, 70, 32, 3)
     assert om.shape == (70, 100) and set(np.unique(om)) == {0, 1, 2}
-    assert om[0, 0] == 0 and om[0, 32] == 1 and om[0, 64] == 2 and om[0, 96] == 0 and om[32, 0] == 1  # 4 tiles per row
+    # blocks of 8 x 8 pixels, owner (tx + 2 ty) mod 3 (stride 2: nearest integer to 0.618 * 3 that is coprime with 3)
+    assert om[0, 0] == 0 and om[0, 8] == 1 and om[0, 16] == 2 and om[0, 24] == 0 and om[8, 0] == 2 and om[7, 7] == 0
+    assert [parallel.partition_stride(n) for n in (1, 2, 3, 4, 5, 6, 7, 8)] == [1, 1, 2, 3, 3, 5, 4, 5]
+    counts = np.bincount(parallel.owner_map(1920, 1080, 32, 8).ravel())
+    assert counts.max() - counts.min() <= 64 * 8   # every rank owns the same share of the frame up to a few blocks
 
 
 def _gloo_worker(rank, world, port, q):
