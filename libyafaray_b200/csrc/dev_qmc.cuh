@@ -62,7 +62,11 @@ struct HaltonB
 		value = 0.0;
 		while(i > 0)
 		{
-			value += (double)(i % BASE) * factor;
+			const uint32_t d = i % BASE;
+			// (double)d * factor without the int -> double conversion (a slow instruction inside a 20-step dependent chain): 2 * factor is exact, so
+			// factor + factor == 2.0 * factor, and value + 0.0 == value; the sum below has the bits of the reference's `value += (double)d * factor`
+			if(BASE == 3) value += (d == 0 ? 0.0 : (d == 1 ? factor : factor + factor));
+			else value += (double)d * factor;
 			i /= BASE;
 			factor *= inv_base;
 		}
@@ -124,24 +128,32 @@ struct FaureTables
 	int offset[YG_SCR_DIMS];      // start of sigma for dimension d
 	int base[YG_SCR_DIMS];        // prims__[d]
 	double inv_base[YG_SCR_DIMS]; // inv_prims__[d] (9-decimal literals of the reference, NOT 1.0/base)
+	unsigned long long magic[YG_SCR_DIMS]; // floor(2^64 / base) + 1: floor(n / base) == mulhi64(n, magic) for every 32-bit n (base >= 2)
 	short sigma[YG_FAURE_TOTAL];
+	double sigma_d[YG_FAURE_TOTAL];        // the same permutation values as doubles, so that the digit loop loads its addend instead of converting it
 };
 
 // scrHalton__ scr_halton.h:52-76.  `tab` lives in global memory on the device (indexed per thread: L1-cached loads, not the constant bank).
 YG_HD double scrHaltonT(const FaureTables &tab, int dim, uint32_t n)
 {
 	double value = 0.0;
-	const short *sigma = tab.sigma + tab.offset[dim];
+	const double *sigma = tab.sigma_d + tab.offset[dim];
 	const uint32_t base = (uint32_t)tab.base[dim];
-	// n % base without an integer division: floor(n / base) = (uint)(n * (1/base) + 2^-10) is exact for n < 2^32, base <= 227
-	// (the product is off by < 2^-20, the fractional part of n / base is a multiple of 1/base <= 1 - 1/227)
-	const double true_inv = 1.0 / (double)base;
+	// n % base by an exact integer reciprocal: with M = floor(2^64 / base) + 1 the error of n * M / 2^64 against n / base is below n / 2^64 < 2^-32, and the
+	// fractional part of n / base is at most 1 - 1/base, so the floor is that of n / base for every 32-bit n.  The reference's own digit extraction is NOT an
+	// integer division (dn *= f with the 9-decimal f, n = (unsigned)dn) and is kept as it is; only `n % base` and the int -> double conversion of the permuted
+	// digit are replaced by bit-identical cheaper forms (4 conversions per digit before, 1 now).
+	const unsigned long long magic = tab.magic[dim];
 	double f, factor, dn = (double)n;
 	f = factor = tab.inv_base[dim];
 	while(n > 0)
 	{
-		const uint32_t q = (uint32_t)((double)n * true_inv + 0.0009765625);
-		value += (double)sigma[n - q * base] * factor;
+#ifdef __CUDA_ARCH__
+		const uint32_t q = (uint32_t)__umul64hi((unsigned long long)n, magic);
+#else
+		const uint32_t q = (uint32_t)(((unsigned __int128)n * magic) >> 64);
+#endif
+		value += sigma[n - q * base] * factor;
 		dn *= f;
 		n = (uint32_t)dn;
 		factor *= f;

@@ -45,9 +45,11 @@ void yg_build_faure_tables(yg::FaureTables &t)
 	{
 		t.base[d] = prims[d];
 		t.inv_base[d] = inv_prims[d];
+		t.magic[d] = prims[d] >= 2 ? ~0ull / (unsigned long long)prims[d] + 1ull : 0ull;   // floor((2^64 - 1) / b) + 1 = floor(2^64 / b) + 1 for every odd b; 2^63 for b = 2, which divides exactly as well
 		if(d < 2) { t.offset[d] = 0; continue; } // faure__[0], faure__[1] alias the base-3 table
 		std::vector<int> p = faurePerm(prims[d]);
 		t.offset[d] = pos;
 		for(int v : p) t.sigma[pos++] = (short)v;
 	}
+	for(int k = 0; k < YG_FAURE_TOTAL; ++k) t.sigma_d[k] = (double)t.sigma[k];
 }
