@@ -122,6 +122,7 @@ SCALE = {
     # name: (kwargs of scenes.procedural_mesh, rays per set)
     "c4": (dict(n_tris=1_000_000, mesh_lights=3, blend=True), 1 << 20),
     "c3": (dict(n_tris=10_000_000), 1 << 20),
+    "c5": (dict(n_tris=20_000_000, seed=23456), 1 << 20),   # BASELINE configs[4]: the config-3 generator at 2 * 10^7 triangles, seed 23456
 }
 
 
