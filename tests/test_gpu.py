@@ -305,6 +305,28 @@ def test_wave_continues_when_the_iteration_guess_was_short(ctx):
     assert n_again < n_short <= n_fixed + 2 and n_again < n_fixed   # the continuation costs one more k_film_add per round; the settled guess is the cheapest
 
 
+@pytest.mark.parametrize("n_tris", [8192, 600_000])
+def test_bad_index_is_refused_before_any_kernel_reads_it(ctx, n_tris):
+    """The index arrays are checked on host threads while the copies to the device are in flight (one thread below 2^18 triangles, up to eight above); a
+    bad index must fail the upload with a message, not reach the BVH build, and leave the context usable."""
+    from libyafaray_b200 import scenes
+    y = pc.grid_mesh_scene(64, seed=3) if n_tris < 100_000 else scenes.procedural_mesh(n_tris, 64, 36, 1, integrator="directlighting")
+    desc, keep = y.scene_desc()
+    n = desc.geometry.n_tris
+    good = desc.geometry.tri_vidx[3 * (n - 2) + 1]
+    desc.geometry.tri_vidx[3 * (n - 2) + 1] = 2_000_000_000
+    with pytest.raises(RuntimeError, match="tri_vidx out of range"):
+        ctx.upload(desc, keep)
+    desc.geometry.tri_vidx[3 * (n - 2) + 1] = good
+    desc.geometry.tri_mat[n // 2] = -1
+    with pytest.raises(RuntimeError, match="tri_mat out of range"):
+        ctx.upload(desc, keep)
+    desc.geometry.tri_mat[n // 2] = 0
+    ctx.upload(desc, keep)
+    ctx.film_clear(); ctx.render_pass(1, 0)
+    assert np.isfinite(ctx.read_film()).all()
+
+
 def test_empty_scene_renders_background(ctx):
     from libyafaray_b200 import scenes
     from libyafaray_b200.interface import Interface
