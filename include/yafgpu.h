@@ -665,7 +665,7 @@ int yafgpu_write_film(yafgpu_ctx *ctx, const float *rgbaw);
 /* Update per-pass AA multipliers between passes (integrator_tiled.cc:216-218). */
 int yafgpu_set_aa_multipliers(yafgpu_ctx *ctx, float light_mult, float indirect_mult);
 
-/* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^23, limited to a quarter of the free device memory),
+/* Tuning knobs that have no counterpart in the reference: "wave_size" (camera samples per wavefront wave; default: up to 2^24, limited to a quarter of the free device memory),
  * "queue_fan" (task/shadow queue capacity as a multiple of wave_size, default 8), "leaf_size" (triangles per leaf link of the BVH built by
  * the NEXT upload, 1..8), "shade_streams" (1..3 CUDA streams the per-material-type shading kernels of one iteration are spread over; default 3),
  * "debug_stack_limit" (traversal stack entries in use, only to exercise the overflow error path),

@@ -1292,12 +1292,13 @@ int renderPass(yafgpu_ctx *c, const yafgpu_pass_desc *p)
 	const size_t per_sample = (size_t)task_fan * (2 * 112) + (size_t)shadow_fan * 48 + 16;
 	int wave_cap = c->wave_cap_override;
 	if(wave_cap <= 0)
-	{	// Default: as large as a quarter of the free HBM allows, at most 2^23 camera samples.  Large waves amortise the thin tail
-		// iterations of a wave (a few thousand tasks per launch at depth 8+): Cornell bench 3.57 -> 4.35 Grays/s from 2^20 to 2^23
+	{	// Default: as large as a quarter of the free HBM allows, at most 2^24 camera samples (38 GB of queues on the bench scene).  Large waves amortise the thin
+		// tail iterations of a wave (a few thousand tasks per launch at depth 8+): 10^7-triangle bench frame 1 622 / 1 690 / 1 722 Mrays/s at 2^22 / 2^23 / 2^24
+		// (tools/wave_sweep.sh); Cornell bench 3.57 -> 4.35 Grays/s from 2^20 to 2^23
 		// (profiles/r1_wave_size.md).
 		const size_t pass_samples = n_pix * (size_t)(s_end - s_begin);
 		Wavefront &w0 = c->wf;
-		int want = 1 << 23;
+		int want = 1 << 24;
 		while(want > (1 << 16) && (size_t)(want >> 1) >= pass_samples) want >>= 1; // no larger than this call needs
 		if(w0.allocated && w0.wave_cap >= want && w0.task_cap == w0.wave_cap * task_fan && w0.shadow_cap == w0.wave_cap * shadow_fan) wave_cap = w0.wave_cap;   // keep what is there
 		else
