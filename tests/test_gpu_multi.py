@@ -80,6 +80,29 @@ def test_group_decides_adaptive_passes_on_the_summed_film():
         g.close()
 
 
+@pytest.mark.parametrize("parts", [2, 3, 8])
+def test_device_partition_is_the_owner_map_of_the_python_mirror(parts):
+    """part_index / part_count on the device (csrc/integrator.cu buildPixelList: 8 x 8 blocks, shifted rows) against libyafaray_b200/parallel.py owner_map,
+    pixel by pixel: with a one-pixel box filter a sample only touches its own pixel, so the pixels that carry weight after rendering part k are exactly k's."""
+    from libyafaray_b200 import Context, parallel, scenes
+    w, h = 100, 70
+    y = scenes.simple_point_scene(w, h, 1, filter_type="box", AA_pixelwidth=1.0)
+    desc, keep = y.scene_desc()
+    om = parallel.owner_map(w, h, desc.film.tile_size, parts)
+    c = Context(0)
+    try:
+        c.upload(desc, keep)
+        seen = np.zeros((h, w), np.int32)
+        for k in range(parts):
+            c.film_clear(); c.render_pass(1, 0, part_index=k, part_count=parts)
+            mine = c.read_film()[..., 4] > 0
+            assert np.array_equal(mine, om == k), (k, int((mine != (om == k)).sum()))
+            seen += mine
+        assert (seen == 1).all()
+    finally:
+        c.close()
+
+
 def test_group_rejects_bad_device_lists():
     from libyafaray_b200 import Group, capi
     with pytest.raises(capi.YafGpuError, match="listed twice"):
