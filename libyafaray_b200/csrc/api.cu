@@ -341,9 +341,6 @@ int yafgpu_upload_scene(yafgpu_ctx *c, const yafgpu_scene_desc *desc)
 		std::string err;
 		if(!prepCamera(desc->camera, s.cam, err)) return setErr(c, YAFGPU_ERR_UNSUPPORTED, err);
 	}
-	for(const NodeDev &nd : h_nodes)
-		if(nd.type == YAFGPU_NODE_TEXTURE_MAPPER && nd.coords == YAFGPU_TEXCO_WINDOW && desc->camera.type != YAFGPU_CAM_PERSPECTIVE)
-			return setErr(c, YAFGPU_ERR_UNSUPPORTED, "texture_mapper texco window is implemented for the perspective camera only");
 	const yafgpu_integrator_desc &in = desc->integrator;
 	if(in.type != YAFGPU_INT_DIRECTLIGHT && in.type != YAFGPU_INT_PATHTRACING) return setErr(c, YAFGPU_ERR_UNSUPPORTED, "integrator type");
 	// bg_transp: the alpha of a camera sample is 0 when its primary ray leaves the scene, 1 otherwise (integrator_path_tracer.cc:122-123,324;

@@ -749,7 +749,7 @@ inline bool prepCamera(const yafgpu_camera &c, CameraDev &d, std::string &err)
 		const V3 p0 = pos - (float)(0.5 * (double)c.scale) * (vup + vright);
 		vup = vup * (c.scale / (float)c.resy);
 		vright = vright * (c.scale / (float)c.resx);
-		st3(d.pos, p0); st3(d.vright, vright); st3(d.vup, vup);
+		st3(d.pos, p0); st3(d.vright, vright); st3(d.vup, vup); d.ortho_scale = c.scale;
 		return true;
 	}
 	if(c.type == YAFGPU_CAM_ANGULAR)

@@ -831,11 +831,34 @@ YG_D void mapperGetCoords(const CameraDev &cam, const NodeDev &nd, const SurfPt 
 			break;
 		}
 		case YAFGPU_TEXCO_WINDOW:
-		{	// PerspectiveCamera::screenproject camera_perspective.cc:158-173 (other camera types are refused at upload)
-			const V3 dir = sp.p - ldv(cam.pos);
-			const float dx = dot(dir, ldv(cam.axis_x)), dy = dot(dir, ldv(cam.axis_y)), dz = dot(dir, ldv(cam.axis_z));
-			texpt = mk(2.0f * dx * cam.focal / dz, -2.0f * dy * cam.focal / (dz * cam.aspect_ratio), 0.f);
+		{	// Camera::screenproject of the five camera types
+			const V3 cx = ldv(cam.axis_x), cy = ldv(cam.axis_y), cz = ldv(cam.axis_z);
+			V3 dir = sp.p - ldv(cam.pos);   // orthographic: cam.pos holds pos_ (the corner of the image plane), as screenproject uses it
 			ng = sp.ng;
+			if(cam.type == YAFGPU_CAM_ORTHOGRAPHIC)
+			{	// camera_orthographic.cc:65-80
+				const float dz = dot(cz, dir);
+				const V3 proj = dir - dz * cz;
+				texpt = mk(2 * (dot(proj, cx) / cam.ortho_scale) - 1.0f, dot(-2.f * proj, cy) / (cam.aspect_ratio * cam.ortho_scale) + 1.0f, 0.f);
+			}
+			else if(cam.type == YAFGPU_CAM_ANGULAR || cam.type == YAFGPU_CAM_EQUIRECTANGULAR)
+			{	// camera_angular.cc:123-140, camera_equirectangular.cc:92-109: the same (FIXME-marked) formula, the quotient formed in double
+				dir = normalize(dir);
+				const float dx = dot(cx, dir), dy = dot(cy, dir), dz = dot(cz, dir);
+				texpt = mk((float)((double)-dx / (4.0 * YG_M_PI * (double)dz)), (float)((double)-dy / (4.0 * YG_M_PI * (double)dz)), 0.f);
+			}
+			else if(cam.type == YAFGPU_CAM_ARCHITECT)
+			{	// camera_architect.cc:68-91: vertical axis fixed to world z, focal distance corrected by the tilt
+				const V3 camy = mk(0.f, 0.f, 1.f), camz = cross(camy, cx), camx = cross(camz, camy);
+				const float dx = dot(dir, camx), dy = dot(dir, cy), dz = dot(dir, camz);
+				const float fod = dot(cam.focal * camy, cy) / dot(camx, cx);
+				texpt = mk(2 * dx * fod / dz, 2 * dy * cam.focal / (dz * cam.aspect_ratio), 0.f);
+			}
+			else
+			{	// camera_perspective.cc:158-173
+				const float dx = dot(dir, cx), dy = dot(dir, cy), dz = dot(dir, cz);
+				texpt = mk(2.0f * dx * cam.focal / dz, -2.0f * dy * cam.focal / (dz * cam.aspect_ratio), 0.f);
+			}
 			break;
 		}
 		case YAFGPU_TEXCO_NORMAL: // Camera::getAxis; sp.n is the (possibly bumped) shading normal at this point of initBsdf

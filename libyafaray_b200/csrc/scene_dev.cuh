@@ -177,6 +177,7 @@ struct CameraDev
 	float aspect_ratio;          // Camera::aspect_ratio_ = aspect * resy / resx (camera.cc:47)
 	float cam_to[3];             // orthographic / angular / equirectangular: vto_ = cam_z_ (vright/vup hold their own vright_/vup_)
 	float max_radius, focal_length; int circular, projection; // angular (camera_angular.cc:28-42)
+	float ortho_scale;           // OrthographicCamera::scale_ (screenproject)
 	float axis_x[3], axis_y[3], axis_z[3], focal;              // Camera::cam_x_/cam_y_/cam_z_ (unit axes, camera.cc:46-66) and PerspectiveCamera::focal_distance_
 };
 

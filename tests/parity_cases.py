@@ -786,7 +786,9 @@ def _textured_geometry_and_rest(y, box_mats, width, height, spp, integrator, int
         y.paramsSetPoint("point2", 2.0, -1.0, 5.0); y.paramsSetColor("color", 0.8, 0.9, 1.0); y.paramsSetFloat("power", 25.0); y.paramsSetInt("samples", 2); y.createLight("A")
     y.paramsClearAll(); y.paramsSetString("type", "perspective")
     y.paramsSetPoint("from", 0.5, -7.5, 4.5); y.paramsSetPoint("to", 0.0, 1.0, 0.6); y.paramsSetPoint("up", 0.5, -7.5, 5.5)
-    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3); y.createCamera("cam")
+    y.paramsSetInt("resx", width); y.paramsSetInt("resy", height); y.paramsSetFloat("focal", 1.3)
+    _set_params(y, integ.get("camera", {}))   # e.g. {"type": "orthographic", "scale": 9.0}: the other camera types under the same view
+    y.createCamera("cam")
     y.paramsClearAll(); y.paramsSetString("type", "constant"); y.paramsSetColor("color", 0.3, 0.4, 0.6); y.paramsSetFloat("power", 0.7); y.createBackground("bg")
     y.paramsClearAll(); y.paramsSetString("type", integrator); y.paramsSetInt("raydepth", integ.get("raydepth", 3)); y.paramsSetInt("shadowDepth", 3)
     if integrator == "pathtracing":
@@ -815,6 +817,11 @@ EXACT["tex_dl_checker"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "ch
 EXACT["tex_dl_clip"] = lambda: textured_scene(96, 54, 2, tex={"clipping": "clip", "cropmin_y": 0.2})
 EXACT["tex_pt_norr"] = lambda: textured_scene(96, 54, 4, integrator="pathtracing")
 EXACT["tex_dl_camera_coords"] = lambda: textured_scene(96, 54, 2, variant="camera_coords")
+# texco "window" = Camera::screenproject of the other four camera types (camera_orthographic.cc:65, camera_architect.cc:68, camera_angular.cc:123, camera_equirectangular.cc:92)
+EXACT["tex_dl_window_ortho"] = lambda: textured_scene(96, 54, 2, variant="camera_coords", camera={"type": "orthographic", "scale": 9.0})
+EXACT["tex_dl_window_architect"] = lambda: textured_scene(96, 54, 2, variant="camera_coords", camera={"type": "architect", "focal": 1.1})
+EXACT["tex_dl_window_angular"] = lambda: textured_scene(96, 54, 2, variant="camera_coords", camera={"type": "angular", "angle": 60.0, "max_angle": 60.0, "circular": False})
+EXACT["tex_dl_window_equirect"] = lambda: textured_scene(96, 48, 2, variant="camera_coords", camera={"type": "equirectangular"})
 EXACT["tex_dl_mask"] = lambda: textured_scene(96, 54, 2, variant="mask", raydepth=4)
 EXACT["tex_pt_mask_norr"] = lambda: textured_scene(96, 54, 4, variant="mask", integrator="pathtracing", raydepth=4)
 EXACT["tex_dl_procedural"] = lambda: textured_scene(96, 54, 2, variant="procedural")
